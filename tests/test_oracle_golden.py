@@ -1,0 +1,99 @@
+"""The oracle vs fixtures produced by executing the reference (tests/golden/make_golden.py)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import loss_oracle, retrieval_oracle
+
+NAMES = ["image", "dna", "text"]
+
+
+def _load(path):
+    z = np.load(path)
+    feats = [torch.from_numpy(z[f"x_{n}"]) if f"x_{n}" in z else None for n in NAMES]
+    return z, feats, torch.from_numpy(z["labels"])
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "loss_*.npz"))))
+def test_loss_oracle_matches_reference_fixture(path):
+    z, feats, labels = _load(path)
+    loss, grads = loss_oracle.contrastive_loss_and_grads(feats, labels, float(z["logit_scale"]))
+    ref = float(z["loss"])
+    assert abs(float(loss) - ref) <= 2e-6 * max(1.0, abs(ref))
+    for n, g in zip(NAMES, grads):
+        if g is None:
+            assert f"g_{n}" not in z
+            continue
+        gr = torch.from_numpy(z[f"g_{n}"])
+        assert (g - gr).abs().max() <= 2e-6 * gr.abs().max() + 1e-9
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "loss_*.npz"))))
+def test_closed_form_matches_reference_fixture(path):
+    z, feats, labels = _load(path)
+    loss, grads = loss_oracle.closed_form_grads(feats, labels, float(z["logit_scale"]))
+    assert abs(float(loss) - float(z["loss"])) <= 5e-6 * max(1.0, abs(float(z["loss"])))
+    for n, g in zip(NAMES, grads):
+        if g is None:
+            continue
+        gr = torch.from_numpy(z[f"g_{n}"]).double()
+        assert (g - gr).abs().max() <= 2e-5 * gr.abs().max() + 1e-9
+
+
+def test_too_few_modalities_message():
+    x = torch.randn(4, 8)
+    with pytest.raises(ValueError, match="Too less element"):
+        loss_oracle.contrastive_loss([x, None, None], torch.arange(4))
+
+
+def test_cliploss_fixture_equals_global_loss(golden_dir):
+    z = np.load(os.path.join(golden_dir, "cliploss_w2.npz"))
+    feats = [torch.from_numpy(z[f"x_{n}"]) for n in NAMES]
+    labels = torch.from_numpy(z["labels"])
+    loss, grads = loss_oracle.contrastive_loss_and_grads(feats, labels, float(z["logit_scale"]))
+    n = labels.shape[0] // 2
+    for r in range(2):
+        assert abs(float(z[f"loss_rank{r}"]) - float(loss)) <= 2e-6 * abs(float(loss))
+        for k, nm in enumerate(NAMES):
+            gr = torch.from_numpy(z[f"g_{nm}_rank{r}"])
+            assert (grads[k][r * n:(r + 1) * n] - gr).abs().max() <= 2e-6 * gr.abs().max() + 1e-9
+
+
+def test_normalize_matches_sklearn_fixture(golden_dir):
+    z = np.load(os.path.join(golden_dir, "retrieval_normalize.npz"))
+    y = retrieval_oracle.l2_normalize_rows(z["x"]).astype(np.float32)
+    np.testing.assert_array_equal(y, z["y"])
+    assert not y[3].any()
+
+
+def test_search_blocked_equals_full_sort_with_ties():
+    rng = np.random.default_rng(5)
+    keys = retrieval_oracle.l2_normalize_rows(rng.standard_normal((700, 32))).astype(np.float32)
+    keys[500] = keys[20]  # exact duplicates: lowest index must win
+    keys[650] = keys[20]
+    q = retrieval_oracle.l2_normalize_rows(keys[[20, 3, 99]] + 0.05 * rng.standard_normal((3, 32))).astype(np.float32)
+    s1, i1 = retrieval_oracle.search_ip(keys, q, 5, block=128)
+    s2, i2 = retrieval_oracle.search_ip_full_sort(keys, q, 5)
+    np.testing.assert_array_equal(i1, i2)
+    np.testing.assert_array_equal(s1, s2)
+    assert list(i1[0, :3]) == [20, 500, 650]
+
+
+def test_search_pads_when_k_exceeds_bank():
+    keys = np.eye(3, 8, dtype=np.float32)
+    s, i = retrieval_oracle.search_ip(keys, keys[:1], 5)
+    assert list(i[0, 3:]) == [-1, -1] and i[0, 0] == 0
+    assert s[0, 4] == retrieval_oracle.FAISS_NEG
+
+
+def test_make_prediction_return_forms():
+    rng = np.random.default_rng(0)
+    keys = rng.standard_normal((20, 8))
+    labels = [{lv: f"{lv}{i % 4}" for lv in retrieval_oracle.LEVELS} for i in range(20)]
+    p = retrieval_oracle.make_prediction(keys[:3], keys, labels, max_k=3)
+    assert isinstance(p, list) and p[0]["species"][0] == labels[0]["species"]
+    p, s, i = retrieval_oracle.make_prediction(keys[:3], keys, labels, True, True, 3)
+    assert s.dtype == np.float32 and i.dtype == np.int64 and i.shape == (3, 3)
