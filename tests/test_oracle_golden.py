@@ -78,7 +78,7 @@ def test_search_blocked_equals_full_sort_with_ties():
     s1, i1 = retrieval_oracle.search_ip(keys, q, 5, block=128)
     s2, i2 = retrieval_oracle.search_ip_full_sort(keys, q, 5)
     np.testing.assert_array_equal(i1, i2)
-    np.testing.assert_array_equal(s1, s2)
+    np.testing.assert_allclose(s1, s2, rtol=0, atol=2e-6)  # sgemm blocking differs with the operand shape
     assert list(i1[0, :3]) == [20, 500, 650]
 
 
