@@ -1,0 +1,160 @@
+"""Tensor-level wrappers over the C ABI: one method per entry point of include/bsc_hot.h.
+
+``CudaOps`` is the only implementation the package ships.  The orchestration in ``loss.py`` takes the ops
+object as an argument so that the multi-rank host logic can be exercised on CPU (gloo) by the tests with a
+stand-in defined under ``tests/`` -- the product modules always construct ``CudaOps``.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import byref, c_size_t, c_void_p
+from dataclasses import dataclass, field
+from typing import List, Optional
+
+import torch
+
+from . import _lib
+from ._lib import MODE_F32, MODE_TC16, NORM_SKLEARN, NORM_TORCH, InfoNceDesc, check, lib, ptr, stream_ptr
+
+
+@dataclass
+class Problem:
+    """One InfoNCE evaluation: the gathered, normalised global batch and this rank's row range."""
+    xh: List[Optional[torch.Tensor]]  # 3 entries, [n_global, d] float16 (TC16) / float32 (F32) or None
+    n_global: int
+    n_local: int
+    row0: int
+    d: int
+    mode: int
+    scale: float
+    r: torch.Tensor = None      # [n_global] float32   label-matrix row sums
+    rep: torch.Tensor = None    # [n_global] int32     class representative
+    nxt: torch.Tensor = None    # [n_global] int32     next member of the class
+    rmax: torch.Tensor = None   # [1] float32
+    workspace: torch.Tensor = None
+    _desc: InfoNceDesc = field(default=None, repr=False)
+
+
+class CudaOps:
+    name = "cuda"
+
+    # ---- K1 -------------------------------------------------------------------------------------
+    def normalize(self, x: torch.Tensor, out_dtype: torch.dtype, zero_rule: int = NORM_TORCH) -> torch.Tensor:
+        """Rows of x scaled to unit L2 norm (F.normalize / sklearn rule), written as out_dtype."""
+        _lib.require_device(x.device)
+        assert x.dim() == 2
+        if x.stride(1) != 1:
+            x = x.contiguous()
+        n, d = x.shape
+        y = torch.empty((n, d), dtype=out_dtype, device=x.device)
+        y16 = y if out_dtype in (torch.float16, torch.bfloat16) else None
+        y32 = y if out_dtype == torch.float32 else None
+        if y16 is None and y32 is None:
+            raise _lib.BscError(f"normalize: unsupported output dtype {out_dtype}")
+        with torch.cuda.device(x.device):
+            check(lib().bsc_l2norm_fwd(x.data_ptr(), _lib.dtype_code(x.dtype), n, d, x.stride(0), ptr(y16),
+                                       _lib.dtype_code(out_dtype) if y16 is not None else _lib.BSC_F16, ptr(y32),
+                                       0, zero_rule, stream_ptr(x.device)))
+        return y
+
+    # ---- K2 -------------------------------------------------------------------------------------
+    def label_stats(self, labels: torch.Tensor):
+        _lib.require_device(labels.device)
+        labels = labels.to(torch.int64).contiguous()
+        n = labels.numel()
+        dev = labels.device
+        r = torch.empty(n, dtype=torch.float32, device=dev)
+        rep = torch.empty(n, dtype=torch.int32, device=dev)
+        nxt = torch.empty(n, dtype=torch.int32, device=dev)
+        rmax = torch.empty(1, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(lib().bsc_label_stats(labels.data_ptr(), n, r.data_ptr(), rep.data_ptr(), nxt.data_ptr(),
+                                        rmax.data_ptr(), stream_ptr(dev)))
+        return r, rep, nxt, rmax
+
+    # ---- InfoNCE --------------------------------------------------------------------------------
+    def _desc(self, p: Problem) -> InfoNceDesc:
+        if p._desc is None:
+            d = InfoNceDesc()
+            d.n_global, d.n_local, d.row0 = p.n_global, p.n_local, p.row0
+            d.d, d.mode, d.logit_scale = p.d, p.mode, float(p.scale)
+            for m in range(3):
+                d.xh[m] = ptr(p.xh[m]) or None
+            d.r, d.rep, d.next, d.rmax = p.r.data_ptr(), p.rep.data_ptr(), p.nxt.data_ptr(), p.rmax.data_ptr()
+            p._desc = d
+        return p._desc
+
+    def _device(self, p: Problem) -> torch.device:
+        return next(t for t in p.xh if t is not None).device
+
+    def stats_len(self, n_global: int) -> int:
+        return int(lib().bsc_infonce_stats_len(n_global))
+
+    def _ensure_workspace(self, p: Problem) -> None:
+        if p.workspace is None:
+            nbytes = c_size_t(0)
+            check(lib().bsc_infonce_workspace_bytes(byref(self._desc(p)), byref(nbytes)))
+            p.workspace = torch.empty(int(nbytes.value), dtype=torch.uint8, device=self._device(p))
+
+    def infonce_fwd(self, p: Problem) -> torch.Tensor:
+        dev = self._device(p)
+        _lib.require_device(dev)
+        self._ensure_workspace(p)
+        stats = torch.empty(self.stats_len(p.n_global), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(lib().bsc_infonce_fwd(byref(self._desc(p)), stats.data_ptr(), p.workspace.data_ptr(),
+                                        p.workspace.numel(), stream_ptr(dev)))
+        return stats
+
+    def infonce_loss(self, p: Problem, stats: torch.Tensor) -> torch.Tensor:
+        dev = self._device(p)
+        loss = torch.empty((), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(lib().bsc_infonce_loss(byref(self._desc(p)), stats.data_ptr(), loss.data_ptr(), stream_ptr(dev)))
+        return loss
+
+    def infonce_bwd(self, p: Problem, stats: torch.Tensor, xs, grad_out: torch.Tensor):
+        """xs: this rank's original rows per modality (None when absent).  Returns grads of the same shapes."""
+        dev = self._device(p)
+        grad_out = grad_out.to(device=dev, dtype=torch.float32).reshape(1).contiguous()
+        first = next(x for x in xs if x is not None)
+        xs = [None if x is None else (x if x.is_contiguous() else x.contiguous()) for x in xs]
+        grads = [None if x is None else torch.empty_like(x) for x in xs]
+        xp = (c_void_p * 3)(*[ptr(x) or None for x in xs])
+        gp = (c_void_p * 3)(*[ptr(g) or None for g in grads])
+        with torch.cuda.device(dev):
+            check(lib().bsc_infonce_bwd(byref(self._desc(p)), stats.data_ptr(), xp, _lib.dtype_code(first.dtype),
+                                        first.stride(0), grad_out.data_ptr(), gp, p.workspace.data_ptr(),
+                                        p.workspace.numel(), stream_ptr(dev)))
+        return grads
+
+    # ---- retrieval ------------------------------------------------------------------------------
+    def bank_search(self, queries: torch.Tensor, bank: torch.Tensor, k: int, base_id: int, mode: int):
+        dev = bank.device
+        _lib.require_device(dev)
+        nq, d = queries.shape
+        nb = bank.shape[0]
+        nbytes = c_size_t(0)
+        check(lib().bsc_bank_search_workspace_bytes(nq, nb, d, k, mode, byref(nbytes)))
+        ws = torch.empty(int(nbytes.value), dtype=torch.uint8, device=dev)
+        scores = torch.empty((nq, k), dtype=torch.float32, device=dev)
+        ids = torch.empty((nq, k), dtype=torch.int64, device=dev)
+        with torch.cuda.device(dev):
+            check(lib().bsc_bank_search(queries.data_ptr(), nq, bank.data_ptr(), nb, d, k, base_id, mode,
+                                        scores.data_ptr(), ids.data_ptr(), ws.data_ptr(), ws.numel(),
+                                        stream_ptr(dev)))
+        return scores, ids
+
+    def topk_merge(self, cand_scores: torch.Tensor, cand_ids: torch.Tensor):
+        """[parts, nq, k] candidate lists -> [nq, k] (score desc, id asc)."""
+        parts, nq, k = cand_scores.shape
+        dev = cand_scores.device
+        _lib.require_device(dev)
+        cand_scores = cand_scores.contiguous()
+        cand_ids = cand_ids.contiguous()
+        scores = torch.empty((nq, k), dtype=torch.float32, device=dev)
+        ids = torch.empty((nq, k), dtype=torch.int64, device=dev)
+        with torch.cuda.device(dev):
+            check(lib().bsc_topk_merge(cand_scores.data_ptr(), cand_ids.data_ptr(), parts, nq, k, scores.data_ptr(),
+                                       ids.data_ptr(), stream_ptr(dev)))
+        return scores, ids

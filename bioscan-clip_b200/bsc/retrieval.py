@@ -1,0 +1,133 @@
+"""Drop-in for the reference's closest-embedding retrieval.
+
+* ``IndexFlatIP(d)`` with ``add`` / ``search`` / ``ntotal`` / ``reset`` -- the faiss surface used at
+  scripts/inference_and_eval.py:415-421, bioscanclip/epoch/eval_epoch.py:153-154,203 and
+  bioscanclip/util/util.py:163-165.  ``search`` returns ``(float32[nq,k], int64[nq,k])`` host arrays, scores
+  descending, equal scores ordered by lowest id, ``-1`` / ``-3.4028235e38`` padding when k > ntotal.
+* ``make_prediction(query_feature, keys_feature, keys_label, with_similarity, with_indices, max_k)``
+  -- scripts/inference_and_eval.py:414-445, same return forms.
+
+The bank lives in HBM, split row-wise over ``devices`` at ``add`` time (one shard per GPU); a search scans
+every shard on its own GPU and merges the per-shard top-k with ``bsc_topk_merge``.
+``precision="fp32"`` is the exact mode (float32 bank, indices comparable bit for bit with a float32 CPU
+search); ``precision="bf16"`` stores the bank in bfloat16 and scans it with the tcgen05 kernel.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from ._lib import MODE_F32, MODE_TC16, NORM_SKLEARN, BscError
+
+LEVELS = ["order", "family", "genus", "species"]
+
+
+def _as_f32_tensor(x, device) -> torch.Tensor:
+    if isinstance(x, torch.Tensor):
+        return x.to(device=device, dtype=torch.float32).contiguous()
+    arr = np.ascontiguousarray(np.asarray(x), dtype=np.float32)  # faiss takes float32 (inference_and_eval.py:416)
+    return torch.from_numpy(arr).to(device)
+
+
+class IndexFlatIP:
+    def __init__(self, d: int, precision: str = "fp32", devices: Optional[Sequence] = None, ops=None,
+                 base_id: int = 0):
+        if precision not in ("fp32", "bf16"):
+            raise ValueError("precision must be 'fp32' or 'bf16'")
+        self.d = int(d)
+        self.precision = precision
+        if devices is None:
+            devices = [torch.device("cuda", torch.cuda.current_device())] if torch.cuda.is_available() else []
+        self.devices = [torch.device(dv) for dv in devices]
+        if not self.devices:
+            raise BscError("IndexFlatIP needs at least one CUDA device; there is no CPU path")
+        if ops is None:
+            from .ops import CudaOps
+
+            ops = CudaOps()
+        self._ops = ops
+        self._mode = MODE_F32 if precision == "fp32" else MODE_TC16
+        self._dtype = torch.float32 if precision == "fp32" else torch.bfloat16
+        self._base_id = int(base_id)
+        self._chunks: List[List[torch.Tensor]] = [[] for _ in self.devices]  # per device: list of (base, rows)
+        self._bases: List[List[int]] = [[] for _ in self.devices]
+        self.ntotal = 0
+
+    def reset(self) -> None:
+        self._chunks = [[] for _ in self.devices]
+        self._bases = [[] for _ in self.devices]
+        self.ntotal = 0
+
+    def add(self, x) -> None:
+        """Append rows (no normalisation, as faiss).  Rows are split evenly over the devices."""
+        n = x.shape[0]
+        if n == 0:
+            return
+        if x.shape[1] != self.d:
+            raise ValueError(f"expected vectors of dimension {self.d}, got {x.shape[1]}")
+        nd = len(self.devices)
+        per = (n + nd - 1) // nd
+        for k, dev in enumerate(self.devices):
+            lo, hi = min(n, k * per), min(n, (k + 1) * per)
+            if hi <= lo:
+                continue
+            part = _as_f32_tensor(x[lo:hi], dev)
+            self._chunks[k].append(part.to(self._dtype).contiguous())
+            self._bases[k].append(self._base_id + self.ntotal + lo)
+        self.ntotal += n
+
+    def search_device(self, q, k: int):
+        """Search returning device tensors (scores, ids) on the first device."""
+        dev0 = self.devices[0]
+        q0 = _as_f32_tensor(q, dev0)
+        if q0.shape[1] != self.d:
+            raise ValueError(f"expected queries of dimension {self.d}, got {q0.shape[1]}")
+        cand_s, cand_i = [], []
+        for kdev, dev in enumerate(self.devices):
+            if not self._chunks[kdev]:
+                continue
+            qd = q0.to(dev).to(self._dtype).contiguous()
+            for base, rows in zip(self._bases[kdev], self._chunks[kdev]):
+                s, i = self._ops.bank_search(qd, rows, k, base, self._mode)
+                cand_s.append(s.to(dev0))
+                cand_i.append(i.to(dev0))
+        nq = q0.shape[0]
+        if not cand_s:
+            cs = torch.empty((0, nq, k), dtype=torch.float32, device=dev0)
+            ci = torch.empty((0, nq, k), dtype=torch.int64, device=dev0)
+        elif len(cand_s) == 1:
+            return cand_s[0], cand_i[0]
+        else:
+            cs, ci = torch.stack(cand_s), torch.stack(cand_i)
+        return self._ops.topk_merge(cs, ci)
+
+    def search(self, q, k: int):
+        s, i = self.search_device(q, k)
+        return s.cpu().numpy(), i.cpu().numpy()
+
+
+def make_prediction(query_feature, keys_feature, keys_label, with_similarity=False, with_indices=False, max_k=5,
+                    precision: str = "fp32", devices=None, ops=None):
+    """scripts/inference_and_eval.py:414-445 on the GPU: L2-normalise both sides with sklearn's zero rule,
+    float32, inner-product top-max_k, then map the hits to their taxonomy labels."""
+    if ops is None:
+        from .ops import CudaOps
+
+        ops = CudaOps()
+    index = IndexFlatIP(keys_feature.shape[-1], precision=precision, devices=devices, ops=ops)
+    dev0 = index.devices[0]
+    keys = ops.normalize(_as_f32_tensor(keys_feature, dev0), torch.float32, NORM_SKLEARN)
+    queries = ops.normalize(_as_f32_tensor(query_feature, dev0), torch.float32, NORM_SKLEARN)
+    index.add(keys)
+    similarities, indices = index.search(queries, max_k)
+    pred_list = []
+    for key_indices in indices:
+        pred_list.append({level: [keys_label[int(i)][level] for i in key_indices] for level in LEVELS})
+    out = [pred_list]
+    if with_similarity:
+        out.append(similarities)
+    if with_indices:
+        out.append(indices)
+    return out[0] if len(out) == 1 else out

@@ -1,0 +1,353 @@
+// C ABI of libbsc_hot.so (see include/bsc_hot.h) and the host-side glue: argument checks, workspace
+// layout, tensor-map encoding, launch counting and the optional CUDA-event timing used by bench.py.
+#include <cstring>
+#include <mutex>
+
+#include "tc_common.cuh"
+
+namespace bsc {
+
+// launchers from prep.cu
+int l2norm_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, int y16_dtype, float* y32,
+                  float* inv_norm, int zero_rule, cudaStream_t st);
+int label_stats_launch(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
+                       cudaStream_t st);
+int class_sum_launch(const void* xh, int dtype, int64_t n, int d, const int32_t* rep, const int32_t* next,
+                     float* csum, cudaStream_t st);
+int pos_rows_launch(const PosArgs& a, int dtype, cudaStream_t st);
+int pos_reduce_launch(const float* posrow, int64_t n, float* out, cudaStream_t st);
+int loss_launch(const float* stats, const float* r, int64_t n, unsigned present_mask, float scale, float* loss,
+                cudaStream_t st);
+int uv_launch(const float* stats, const float* r, int64_t n, const float* rmax, int use_gs, float* uv, float* gsbuf,
+              cudaStream_t st);
+int combine_launch(const CombineArgs& a, int x_dtype, cudaStream_t st);
+int topk_merge_launch(const float* cs, const int64_t* ci, int parts, int64_t nq, int k, float* os, int64_t* oi,
+                      cudaStream_t st);
+void tc_fwd_tiling(int64_t n_local, int64_t n_global, int n_pairs, int* n_iblk, int* n_jtile, int* jpc,
+                   int* n_jchunk);
+
+// ---- thread-local state -----------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+static thread_local int64_t g_launches = 0;
+static thread_local int g_timing = 0;
+static thread_local cudaEvent_t g_ev[3][2] = {{nullptr, nullptr}, {nullptr, nullptr}, {nullptr, nullptr}};
+static thread_local bool g_ev_valid[3] = {false, false, false};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+  return BSC_ECUDA;
+}
+
+void count_launch(int n) { g_launches += n; }
+
+void timing_begin(int which, cudaStream_t st) {
+  if (!g_timing) return;
+  if (!g_ev[which][0]) {
+    cudaEventCreate(&g_ev[which][0]);
+    cudaEventCreate(&g_ev[which][1]);
+  }
+  cudaEventRecord(g_ev[which][0], st);
+}
+void timing_end(int which, cudaStream_t st) {
+  if (!g_timing) return;
+  cudaEventRecord(g_ev[which][1], st);
+  g_ev_valid[which] = true;
+}
+
+// ---- TMA tensor maps ------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encoder() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)sym;
+  });
+  return fn;
+}
+
+int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, int64_t rows, int64_t cols, int box_rows) {
+  EncodeTiledFn enc = get_encoder();
+  BSC_REQUIRE(enc != nullptr, BSC_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  BSC_REQUIRE(((uintptr_t)base & 15) == 0, BSC_EINVAL, "TMA operand base must be 16-byte aligned");
+  BSC_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0, BSC_EINVAL, "TMA operand needs rows > 0 and cols %% 8 == 0");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)cols * 2};
+  cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1u, 1u};
+  CUtensorMapDataType dt = dtype == BSC_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  CUresult r = enc(out, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  BSC_REQUIRE(r == CUDA_SUCCESS, BSC_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return BSC_OK;
+}
+
+// ---- workspace layout ---------------------------------------------------------------------------
+static int present_count(const bsc_infonce_desc* p, unsigned* mask) {
+  int m = 0;
+  unsigned k = 0;
+  for (int a = 0; a < 3; ++a)
+    if (p->xh[a]) {
+      ++m;
+      k |= 1u << a;
+    }
+  if (mask) *mask = k;
+  return m;
+}
+
+InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p) {
+  InfoNceWs L{};
+  const int64_t N = p->n_global, n = p->n_local;
+  const int D = p->d;
+  const int m = present_count(p, nullptr);
+  const int n_pairs = m * (m - 1) / 2;
+  if (p->mode == BSC_MODE_TC16) {
+    tc_fwd_tiling(n, N, n_pairs, &L.n_iblk, &L.n_jtile, &L.jtiles_per_chunk, &L.n_jchunk);
+  } else {
+    L.n_iblk = (int)((n + kSimtT - 1) / kSimtT);
+    L.n_jtile = (int)((N + kSimtT - 1) / kSimtT);
+    L.jtiles_per_chunk = 1;
+    L.n_jchunk = L.n_jtile;
+  }
+  L.n_local_pad = (int64_t)align_up((size_t)(n > 0 ? n : 1), 64);
+  L.n_global_pad = (int64_t)align_up((size_t)(N > 0 ? N : 1), 64);
+  L.g_rows = n < 2048 ? (n > 0 ? n : 1) : 2048;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off += align_up(bytes, 256);
+    return o;
+  };
+  L.csum = take((size_t)3 * N * D * sizeof(float));
+  L.uv = take((size_t)6 * N * sizeof(float));
+  L.gs = take(4 * sizeof(float));
+  L.posrow = take((size_t)L.n_local_pad * sizeof(float));
+  L.rowpart = take((size_t)3 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
+  L.colpart = take((size_t)3 * (L.n_iblk > 0 ? L.n_iblk : 1) * L.n_global_pad * sizeof(float));
+  L.dxraw = take((size_t)3 * 2 * (n > 0 ? n : 1) * D * sizeof(float));
+  L.gscratch = (p->mode == BSC_MODE_F32) ? take((size_t)L.g_rows * N * sizeof(float)) : off;
+  L.total = off;
+  return L;
+}
+
+static int check_desc(const bsc_infonce_desc* p, const char* who) {
+  BSC_REQUIRE(p != nullptr, BSC_EINVAL, "%s: null descriptor", who);
+  BSC_REQUIRE(p->mode == BSC_MODE_F32 || p->mode == BSC_MODE_TC16, BSC_EINVAL, "%s: unknown mode %d", who, p->mode);
+  BSC_REQUIRE(p->n_global >= 1 && p->n_local >= 0 && p->row0 >= 0 && p->row0 + p->n_local <= p->n_global, BSC_EINVAL,
+              "%s: bad row partition (n_global=%lld n_local=%lld row0=%lld)", who, (long long)p->n_global,
+              (long long)p->n_local, (long long)p->row0);
+  BSC_REQUIRE(p->d >= 1, BSC_EINVAL, "%s: d must be positive", who);
+  BSC_REQUIRE(present_count(p, nullptr) >= 2, BSC_EINVAL, "%s: Too less element for calculating the contrastive loss.",
+              who);
+  BSC_REQUIRE(p->r && p->rep && p->next && p->rmax, BSC_EINVAL, "%s: label statistics pointers are null", who);
+  return BSC_OK;
+}
+
+}  // namespace bsc
+
+using namespace bsc;
+
+extern "C" {
+
+int bsc_version(void) { return BSC_VERSION; }
+const char* bsc_last_error(void) { return g_err; }
+
+int bsc_device_check(void) {
+  int dev = 0;
+  BSC_CUDA(cudaGetDevice(&dev));
+  cudaDeviceProp prop;
+  BSC_CUDA(cudaGetDeviceProperties(&prop, dev));
+  BSC_REQUIRE(prop.major == 10, BSC_EUNSUPPORTED, "device %d is sm_%d%d; libbsc_hot.so is built for sm_100a only",
+              dev, prop.major, prop.minor);
+  BSC_REQUIRE(get_encoder() != nullptr, BSC_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  return BSC_OK;
+}
+
+int bsc_set_timing(int enabled) {
+  g_timing = enabled ? 1 : 0;
+  return BSC_OK;
+}
+
+float bsc_last_kernel_ms(int which) {
+  if (which < 0 || which > 2 || !g_ev_valid[which]) return -1.0f;
+  if (cudaEventSynchronize(g_ev[which][1]) != cudaSuccess) return -1.0f;
+  float ms = -1.0f;
+  if (cudaEventElapsedTime(&ms, g_ev[which][0], g_ev[which][1]) != cudaSuccess) return -1.0f;
+  return ms;
+}
+
+int64_t bsc_launch_count(int reset) {
+  int64_t v = g_launches;
+  if (reset) g_launches = 0;
+  return v;
+}
+
+int bsc_l2norm_fwd(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, int y16_dtype, float* y32,
+                   float* inv_norm, int zero_rule, void* stream) {
+  BSC_REQUIRE(x != nullptr || n == 0, BSC_EINVAL, "bsc_l2norm_fwd: x is null");
+  BSC_REQUIRE(n >= 0 && d >= 1 && ldx >= d, BSC_EINVAL, "bsc_l2norm_fwd: bad shape n=%lld d=%d ldx=%lld", (long long)n,
+              d, (long long)ldx);
+  BSC_REQUIRE(zero_rule == BSC_NORM_TORCH || zero_rule == BSC_NORM_SKLEARN, BSC_EINVAL,
+              "bsc_l2norm_fwd: unknown zero_rule %d", zero_rule);
+  return l2norm_launch(x, x_dtype, n, d, ldx, y16, y16_dtype, y32, inv_norm, zero_rule, (cudaStream_t)stream);
+}
+
+int bsc_label_stats(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
+                    void* stream) {
+  BSC_REQUIRE(labels && r && rep && next && rmax, BSC_EINVAL, "bsc_label_stats: null pointer");
+  BSC_REQUIRE(n >= 0 && n < (1ll << 31), BSC_EINVAL, "bsc_label_stats: n out of range");
+  return label_stats_launch(labels, n, r, rep, next, rmax, (cudaStream_t)stream);
+}
+
+int64_t bsc_infonce_stats_len(int64_t n_global) { return 6 * n_global + kStatsExtra; }
+
+int bsc_infonce_workspace_bytes(const bsc_infonce_desc* p, size_t* bytes) {
+  int rc = check_desc(p, "bsc_infonce_workspace_bytes");
+  if (rc) return rc;
+  BSC_REQUIRE(bytes != nullptr, BSC_EINVAL, "bsc_infonce_workspace_bytes: bytes is null");
+  *bytes = infonce_ws_layout(p).total;
+  return BSC_OK;
+}
+
+int bsc_infonce_fwd(const bsc_infonce_desc* p, float* stats, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_desc(p, "bsc_infonce_fwd");
+  if (rc) return rc;
+  BSC_REQUIRE(stats && workspace, BSC_EINVAL, "bsc_infonce_fwd: null pointer");
+  const InfoNceWs L = infonce_ws_layout(p);
+  BSC_REQUIRE(workspace_bytes >= L.total, BSC_EWORKSPACE, "bsc_infonce_fwd: workspace %zu < %zu", workspace_bytes,
+              L.total);
+  cudaStream_t st = (cudaStream_t)stream;
+  char* ws = (char*)workspace;
+  const int64_t N = p->n_global;
+  const int xdt = p->mode == BSC_MODE_F32 ? BSC_F32 : BSC_F16;
+  BSC_CUDA(cudaMemsetAsync(stats, 0, (size_t)bsc_infonce_stats_len(N) * sizeof(float), st));
+  // class sums (all rows: classes span ranks) and the positive term of the local rows
+  PosArgs pa{};
+  for (int m = 0; m < 3; ++m) {
+    pa.xh[m] = p->xh[m];
+    pa.csum[m] = (const float*)(ws + L.csum) + (size_t)m * N * p->d;
+    if (p->xh[m]) {
+      rc = class_sum_launch(p->xh[m], xdt, N, p->d, p->rep, p->next, (float*)pa.csum[m], st);
+      if (rc) return rc;
+    }
+  }
+  pa.rep = p->rep;
+  pa.posrow = (float*)(ws + L.posrow);
+  pa.row0 = p->row0;
+  pa.n_local = p->n_local;
+  pa.d = p->d;
+  rc = pos_rows_launch(pa, xdt, st);
+  if (rc) return rc;
+  rc = pos_reduce_launch(pa.posrow, p->n_local, stats + 6 * N, st);
+  if (rc) return rc;
+  if (p->n_local == 0) return BSC_OK;
+  if (p->mode == BSC_MODE_F32) return simt_fwd_stats(p, L, ws, stats, st);
+  return tc_fwd_stats(p, L, ws, stats, st);
+}
+
+int bsc_infonce_loss(const bsc_infonce_desc* p, const float* stats, float* loss, void* stream) {
+  int rc = check_desc(p, "bsc_infonce_loss");
+  if (rc) return rc;
+  BSC_REQUIRE(stats && loss, BSC_EINVAL, "bsc_infonce_loss: null pointer");
+  unsigned mask = 0;
+  present_count(p, &mask);
+  return loss_launch(stats, p->r, p->n_global, mask, p->logit_scale, loss, (cudaStream_t)stream);
+}
+
+int bsc_infonce_bwd(const bsc_infonce_desc* p, const float* stats, const void* const* x, int x_dtype, int64_t ldx,
+                    const float* grad_out, void* const* grad, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_desc(p, "bsc_infonce_bwd");
+  if (rc) return rc;
+  BSC_REQUIRE(stats && x && grad && grad_out && workspace, BSC_EINVAL, "bsc_infonce_bwd: null pointer");
+  BSC_REQUIRE(ldx >= p->d, BSC_EINVAL, "bsc_infonce_bwd: ldx < d");
+  const InfoNceWs L = infonce_ws_layout(p);
+  BSC_REQUIRE(workspace_bytes >= L.total, BSC_EWORKSPACE, "bsc_infonce_bwd: workspace %zu < %zu", workspace_bytes,
+              L.total);
+  cudaStream_t st = (cudaStream_t)stream;
+  char* ws = (char*)workspace;
+  const int64_t N = p->n_global;
+  unsigned mask = 0;
+  const int m = present_count(p, &mask);
+  for (int a = 0; a < 3; ++a)
+    BSC_REQUIRE(!p->xh[a] || (x[a] && grad[a]), BSC_EINVAL, "bsc_infonce_bwd: x/grad pointer missing for modality %d",
+                a);
+  if (p->n_local == 0) return BSC_OK;
+  rc = uv_launch(stats, p->r, N, p->rmax, p->mode == BSC_MODE_TC16, (float*)(ws + L.uv), (float*)(ws + L.gs), st);
+  if (rc) return rc;
+  rc = (p->mode == BSC_MODE_F32) ? simt_bwd_raw(p, L, ws, st) : tc_bwd_raw(p, L, ws, st);
+  if (rc) return rc;
+  CombineArgs ca{};
+  for (int a = 0; a < 3; ++a) {
+    ca.x[a] = p->xh[a] ? x[a] : nullptr;
+    ca.grad[a] = p->xh[a] ? grad[a] : nullptr;
+    ca.raw[a] = (const float*)(ws + L.dxraw) + (size_t)a * 2 * p->n_local * p->d;
+    ca.csum[a] = (const float*)(ws + L.csum) + (size_t)a * N * p->d;
+  }
+  ca.rep = p->rep;
+  ca.gsbuf = (const float*)(ws + L.gs);
+  ca.grad_out = grad_out;
+  ca.row0 = p->row0;
+  ca.n_local = p->n_local;
+  ca.n_global = N;
+  ca.ldx = ldx;
+  ca.d = p->d;
+  ca.n_slots = m - 1;
+  ca.present_mask = mask;
+  ca.scale = p->logit_scale;
+  return combine_launch(ca, x_dtype, st);
+}
+
+int bsc_bank_search_workspace_bytes(int64_t nq, int64_t nb, int d, int k, int mode, size_t* bytes) {
+  BSC_REQUIRE(bytes != nullptr && nq >= 0 && nb >= 0 && d >= 1 && k >= 1, BSC_EINVAL,
+              "bsc_bank_search_workspace_bytes: bad argument");
+  if (mode == BSC_MODE_F32)
+    *bytes = simt_bank_ws(nq, nb, d, k);
+  else if (mode == BSC_MODE_TC16)
+    *bytes = tc_bank_ws(nq, nb, d, k);
+  else {
+    set_error("bsc_bank_search_workspace_bytes: unknown mode %d", mode);
+    return BSC_EINVAL;
+  }
+  if (*bytes == 0) *bytes = 256;
+  return BSC_OK;
+}
+
+int bsc_bank_search(const void* queries, int64_t nq, const void* bank, int64_t nb, int d, int k, int64_t base_id,
+                    int mode, float* out_scores, int64_t* out_ids, void* workspace, size_t workspace_bytes,
+                    void* stream) {
+  BSC_REQUIRE(nq >= 0 && nb >= 0 && d >= 1 && k >= 1, BSC_EINVAL, "bsc_bank_search: bad shape");
+  BSC_REQUIRE((queries || nq == 0) && (bank || nb == 0) && (out_scores && out_ids || nq == 0) && workspace, BSC_EINVAL,
+              "bsc_bank_search: null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode == BSC_MODE_F32)
+    return simt_bank_search((const float*)queries, nq, (const float*)bank, nb, d, k, base_id, out_scores, out_ids,
+                            (char*)workspace, workspace_bytes, st);
+  if (mode == BSC_MODE_TC16)
+    return tc_bank_search(queries, nq, bank, nb, d, k, base_id, out_scores, out_ids, (char*)workspace,
+                          workspace_bytes, st);
+  set_error("bsc_bank_search: unknown mode %d", mode);
+  return BSC_EINVAL;
+}
+
+int bsc_topk_merge(const float* cand_scores, const int64_t* cand_ids, int parts, int64_t nq, int k, float* out_scores,
+                   int64_t* out_ids, void* stream) {
+  BSC_REQUIRE(parts >= 0 && nq >= 0 && k >= 1, BSC_EINVAL, "bsc_topk_merge: bad shape");
+  BSC_REQUIRE((cand_scores && cand_ids) || parts == 0 || nq == 0, BSC_EINVAL, "bsc_topk_merge: null candidates");
+  BSC_REQUIRE((out_scores && out_ids) || nq == 0, BSC_EINVAL, "bsc_topk_merge: null outputs");
+  return topk_merge_launch(cand_scores, cand_ids, parts, nq, k, out_scores, out_ids, (cudaStream_t)stream);
+}
+
+}  // extern "C"

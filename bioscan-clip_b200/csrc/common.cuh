@@ -1,0 +1,116 @@
+// Shared host/device helpers for libbsc_hot.so (sm_100a only).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+
+#include "../../include/bsc_hot.h"
+
+namespace bsc {
+
+// ---- error plumbing ---------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+void count_launch(int n = 1);
+
+#define BSC_CUDA(call)                                   \
+  do {                                                   \
+    cudaError_t e__ = (call);                            \
+    if (e__ != cudaSuccess) return ::bsc::cuda_fail(e__, #call); \
+  } while (0)
+
+#define BSC_LAUNCH_CHECK(name)                           \
+  do {                                                   \
+    cudaError_t e__ = cudaGetLastError();                \
+    if (e__ != cudaSuccess) return ::bsc::cuda_fail(e__, name); \
+    ::bsc::count_launch();                               \
+  } while (0)
+
+#define BSC_REQUIRE(cond, code, ...)  \
+  do {                                \
+    if (!(cond)) {                    \
+      ::bsc::set_error(__VA_ARGS__);  \
+      return (code);                  \
+    }                                 \
+  } while (0)
+
+// ---- ordered-pair bookkeeping -------------------------------------------------------------------
+// Ordered pair (a,b), a != b, of modality slots 0..2 -> 0..5.
+__host__ __device__ inline int pair_id(int a, int b) { return a * 2 + (b > a ? b - 1 : b); }
+
+constexpr int kStatsExtra = 4;  // scalars after the 6*N sum-exp rows; [0] = sum_ij T_ij S_ij / s (local part)
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// ---- workspace layout of the infonce calls -----------------------------------------------------
+struct InfoNceWs {
+  size_t csum;      // float [3][N][D]       class sums of normalised rows
+  size_t uv;        // float [6][N]          r_i / sumexp
+  size_t gs;        // float [4]             {gs, 1/gs}
+  size_t posrow;    // float [n_local]
+  size_t rowpart;   // float [3][n_jchunk][n_local_pad]
+  size_t colpart;   // float [3][n_iblk][N_pad]
+  size_t dxraw;     // float [3][2][n_local][D]
+  size_t gscratch;  // float [g_rows][N]     fp32 mode only
+  size_t total;
+  // tiling facts shared by host and kernels
+  int n_iblk, n_jtile, n_jchunk, jtiles_per_chunk;
+  int64_t n_local_pad, n_global_pad, g_rows;
+};
+
+InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p);
+
+
+// ---- argument blocks of the O(N*D) kernels in prep.cu ----------------------------------------------
+struct PosArgs {
+  const void* xh[3];
+  const float* csum[3];
+  const int32_t* rep;
+  float* posrow;
+  int64_t row0, n_local;
+  int d;
+};
+
+struct CombineArgs {
+  const void* x[3];      // original local rows (un-normalised), null when the modality is absent
+  void* grad[3];
+  const float* raw[3];   // [2][n_local][d] per modality
+  const float* csum[3];  // [N][d]
+  const int32_t* rep;
+  const float* gsbuf;
+  const float* grad_out;
+  int64_t row0, n_local, n_global, ldx;
+  int d, n_slots;
+  unsigned present_mask;
+  float scale;
+};
+
+// ---- sub-launchers implemented in the .cu files ---------------------------------------------------
+int simt_fwd_stats(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, float* stats, cudaStream_t st);
+int simt_bwd_raw(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st);
+int tc_fwd_stats(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, float* stats, cudaStream_t st);
+int tc_bwd_raw(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st);
+
+int simt_bank_search(const float* q, int64_t nq, const float* bank, int64_t nb, int d, int k, int64_t base_id,
+                     float* out_s, int64_t* out_i, char* ws, size_t ws_bytes, cudaStream_t st);
+int tc_bank_search(const void* q, int64_t nq, const void* bank, int64_t nb, int d, int k, int64_t base_id,
+                   float* out_s, int64_t* out_i, char* ws, size_t ws_bytes, cudaStream_t st);
+size_t simt_bank_ws(int64_t nq, int64_t nb, int d, int k);
+size_t tc_bank_ws(int64_t nq, int64_t nb, int d, int k);
+
+// tile shapes of the tensor-core kernels (host needs them for the workspace layout)
+constexpr int kTcBM = 128;   // rows per CTA tile (TMEM lanes)
+constexpr int kTcBNF = 256;  // forward: columns per tile
+constexpr int kTcBNB = 128;  // backward: columns per tile
+constexpr int kSimtT = 64;   // SIMT tile edge
+
+// timing slots (bench instrumentation)
+void timing_begin(int which, cudaStream_t st);
+void timing_end(int which, cudaStream_t st);
+
+}  // namespace bsc

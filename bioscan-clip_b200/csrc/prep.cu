@@ -1,0 +1,451 @@
+// O(N*D) and O(N^2)-integer kernels around the similarity sweeps: row L2 normalisation (K1), label
+// statistics (K2), class sums, the positive-pair term, the loss scalar and the normalize backward (K6).
+// All of them are HBM- or latency-bound; none touches an N x N float matrix.
+#include "common.cuh"
+
+namespace bsc {
+
+template <typename T>
+__device__ __forceinline__ float to_f32(T v);
+template <>
+__device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <>
+__device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
+
+template <typename T>
+__device__ __forceinline__ T from_f32(float v);
+template <>
+__device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <>
+__device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1: one warp per row.  Two passes over the row (second pass hits L1/L2).
+// ---------------------------------------------------------------------------------------------
+template <typename TI, typename TO>
+__global__ void __launch_bounds__(256) l2norm_rows_kernel(const TI* __restrict__ x, int64_t n, int d, int64_t ldx,
+                                                          TO* __restrict__ y16, float* __restrict__ y32,
+                                                          float* __restrict__ inv_norm, int zero_rule) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= n) return;
+  const TI* xr = x + row * ldx;
+  float ss = 0.f;
+  for (int c = lane; c < d; c += 32) {
+    float v = to_f32<TI>(xr[c]);
+    ss = fmaf(v, v, ss);
+  }
+  ss = warp_sum(ss);
+  float nrm = sqrtf(ss);
+  float inv;
+  if (zero_rule == BSC_NORM_SKLEARN) {
+    inv = (nrm < 2.220446049250313e-15f) ? 1.0f : 1.0f / nrm;
+  } else {
+    inv = 1.0f / fmaxf(nrm, 1e-12f);
+  }
+  if (inv_norm != nullptr && lane == 0) inv_norm[row] = inv;
+  for (int c = lane; c < d; c += 32) {
+    float v = to_f32<TI>(xr[c]) * inv;
+    if (y16 != nullptr) y16[row * (int64_t)d + c] = from_f32<TO>(v);
+    if (y32 != nullptr) y32[row * (int64_t)d + c] = v;
+  }
+}
+
+template <typename TI>
+static int l2norm_dispatch_out(const void* x, int64_t n, int d, int64_t ldx, void* y16, int y16_dtype, float* y32,
+                               float* inv_norm, int zero_rule, cudaStream_t st) {
+  dim3 block(256), grid((unsigned)((n + 7) / 8));
+  if (y16 == nullptr || y16_dtype == BSC_F16) {
+    l2norm_rows_kernel<TI, __half><<<grid, block, 0, st>>>((const TI*)x, n, d, ldx, (__half*)y16, y32, inv_norm,
+                                                          zero_rule);
+  } else if (y16_dtype == BSC_BF16) {
+    l2norm_rows_kernel<TI, __nv_bfloat16><<<grid, block, 0, st>>>((const TI*)x, n, d, ldx, (__nv_bfloat16*)y16,
+                                                                 y32, inv_norm, zero_rule);
+  } else {
+    set_error("bsc_l2norm_fwd: y16_dtype must be BSC_F16 or BSC_BF16");
+    return BSC_EINVAL;
+  }
+  BSC_LAUNCH_CHECK("l2norm_rows_kernel");
+  return BSC_OK;
+}
+
+int l2norm_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, int y16_dtype, float* y32,
+                  float* inv_norm, int zero_rule, cudaStream_t st) {
+  if (n == 0) return BSC_OK;
+  switch (x_dtype) {
+    case BSC_F32: return l2norm_dispatch_out<float>(x, n, d, ldx, y16, y16_dtype, y32, inv_norm, zero_rule, st);
+    case BSC_BF16:
+      return l2norm_dispatch_out<__nv_bfloat16>(x, n, d, ldx, y16, y16_dtype, y32, inv_norm, zero_rule, st);
+    case BSC_F16: return l2norm_dispatch_out<__half>(x, n, d, ldx, y16, y16_dtype, y32, inv_norm, zero_rule, st);
+  }
+  set_error("bsc_l2norm_fwd: unknown x_dtype %d", x_dtype);
+  return BSC_EINVAL;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2: label statistics.  Brute force over label tiles staged in shared memory: N^2 integer compares,
+// no N x N matrix.  Thread i scans j ascending, so rep/next come out as first matches.
+// ---------------------------------------------------------------------------------------------
+constexpr int kLabelTile = 2048;
+
+__global__ void __launch_bounds__(256) label_stats_kernel(const int64_t* __restrict__ labels, int64_t n,
+                                                          float* __restrict__ r, int32_t* __restrict__ rep,
+                                                          int32_t* __restrict__ next, int* __restrict__ rmax_bits) {
+  __shared__ int64_t tile[kLabelTile];
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t mine = (i < n) ? labels[i] : 0;
+  int count = 0;
+  int first = -1, nxt = -1;
+  for (int64_t base = 0; base < n; base += kLabelTile) {
+    const int len = (int)min((int64_t)kLabelTile, n - base);
+    __syncthreads();
+    for (int t = threadIdx.x; t < len; t += blockDim.x) tile[t] = labels[base + t];
+    __syncthreads();
+    if (i < n) {
+#pragma unroll 8
+      for (int t = 0; t < len; ++t) {
+        const bool eq = (tile[t] == mine);
+        const int j = (int)(base + t);
+        count += eq ? 1 : 0;
+        if (eq && first < 0) first = j;
+        if (eq && nxt < 0 && j > (int)i) nxt = j;
+      }
+    }
+  }
+  if (i < n) {
+    r[i] = (float)count;
+    rep[i] = first;
+    next[i] = nxt;
+  }
+  // block max -> one atomic per warp (positive floats order like their bit patterns)
+  float c = (float)count;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c = fmaxf(c, __shfl_xor_sync(0xffffffffu, c, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(rmax_bits, __float_as_int(c));
+}
+
+int label_stats_launch(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
+                       cudaStream_t st) {
+  BSC_CUDA(cudaMemsetAsync(rmax, 0, sizeof(float), st));
+  if (n == 0) return BSC_OK;
+  label_stats_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(labels, n, r, rep, next, (int*)rmax);
+  BSC_LAUNCH_CHECK("label_stats_kernel");
+  return BSC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Class sums: csum[m][i][:] = sum over the label class of i of xh_m rows, stored at the class
+// representative only, accumulated in index order (deterministic).  With labels = arange this is a copy.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) class_sum_kernel(const T* __restrict__ xh, int64_t n, int d,
+                                                        const int32_t* __restrict__ rep,
+                                                        const int32_t* __restrict__ next, float* __restrict__ csum) {
+  const int64_t i = blockIdx.x;
+  if (rep[i] != (int32_t)i) return;
+  for (int c0 = threadIdx.x; c0 < d; c0 += blockDim.x) {
+    float acc = 0.f;
+    for (int64_t j = i; j >= 0; j = next[j]) acc += to_f32<T>(xh[j * (int64_t)d + c0]);
+    csum[i * (int64_t)d + c0] = acc;
+  }
+}
+
+int class_sum_launch(const void* xh, int dtype, int64_t n, int d, const int32_t* rep, const int32_t* next,
+                     float* csum, cudaStream_t st) {
+  if (n == 0) return BSC_OK;
+  if (dtype == BSC_F32)
+    class_sum_kernel<float><<<(unsigned)n, 256, 0, st>>>((const float*)xh, n, d, rep, next, csum);
+  else if (dtype == BSC_F16)
+    class_sum_kernel<__half><<<(unsigned)n, 256, 0, st>>>((const __half*)xh, n, d, rep, next, csum);
+  else
+    class_sum_kernel<__nv_bfloat16><<<(unsigned)n, 256, 0, st>>>((const __nv_bfloat16*)xh, n, d, rep, next, csum);
+  BSC_LAUNCH_CHECK("class_sum_kernel");
+  return BSC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Positive-pair term for the local rows: posrow[i] = sum_{x} sum_{y != x} <xh_x[i], csum_y[rep_i]>
+// (= sum_j T_ij S_ij / s summed over the ordered pairs).  One warp per row.
+// ---------------------------------------------------------------------------------------------
+
+template <typename T>
+__global__ void __launch_bounds__(256) pos_rows_kernel(PosArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t il = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (il >= a.n_local) return;
+  const int64_t i = a.row0 + il;
+  const int64_t ri = a.rep[i];
+  float acc = 0.f;
+  for (int c = lane; c < a.d; c += 32) {
+    float xs[3], cs[3];
+#pragma unroll
+    for (int m = 0; m < 3; ++m) {
+      xs[m] = a.xh[m] ? to_f32<T>(((const T*)a.xh[m])[i * (int64_t)a.d + c]) : 0.f;
+      cs[m] = a.xh[m] ? a.csum[m][ri * (int64_t)a.d + c] : 0.f;
+    }
+    const float ct = cs[0] + cs[1] + cs[2];
+#pragma unroll
+    for (int m = 0; m < 3; ++m) acc = fmaf(xs[m], ct - cs[m], acc);
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) a.posrow[il] = acc;
+}
+
+int pos_rows_launch(const PosArgs& a, int dtype, cudaStream_t st) {
+  if (a.n_local == 0) return BSC_OK;
+  dim3 grid((unsigned)((a.n_local + 7) / 8));
+  if (dtype == BSC_F32)
+    pos_rows_kernel<float><<<grid, 256, 0, st>>>(a);
+  else
+    pos_rows_kernel<__half><<<grid, 256, 0, st>>>(a);
+  BSC_LAUNCH_CHECK("pos_rows_kernel");
+  return BSC_OK;
+}
+
+// Deterministic single-block sum (double accumulation) of posrow into stats extra slot 0.
+__global__ void __launch_bounds__(1024) pos_reduce_kernel(const float* __restrict__ posrow, int64_t n,
+                                                          float* __restrict__ out) {
+  __shared__ double sh[1024];
+  double acc = 0.0;
+  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) acc += (double)posrow[i];
+  sh[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = 512; s > 0; s >>= 1) {
+    if ((int)threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[0] = (float)sh[0];
+}
+
+int pos_reduce_launch(const float* posrow, int64_t n, float* out, cudaStream_t st) {
+  pos_reduce_kernel<<<1, 1024, 0, st>>>(posrow, n, out);
+  BSC_LAUNCH_CHECK("pos_reduce_kernel");
+  return BSC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Partial-sum reduction of the sweeps: stats[pid(a,b)][row0+i] = sum_chunk rowpart, stats[pid(b,a)][j] =
+// sum_iblk colpart, in a fixed order.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) reduce_parts_kernel(const float* __restrict__ part, int nparts,
+                                                           int64_t part_stride, int64_t n,
+                                                           float* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float acc = 0.f;
+  for (int p = 0; p < nparts; ++p) acc += part[p * part_stride + i];
+  out[i] = acc;
+}
+
+int reduce_parts_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float* out, cudaStream_t st) {
+  if (n == 0) return BSC_OK;
+  reduce_parts_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(part, nparts, part_stride, n, out);
+  BSC_LAUNCH_CHECK("reduce_parts_kernel");
+  return BSC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Loss scalar (loss_func.py:54): c * [ sum_pairs sum_i r_i (s + log sumexp_i) - s * pos ],
+// c = 1 / (N * M(M-1)).  Single block, double accumulation, fixed order.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) loss_kernel(const float* __restrict__ stats, const float* __restrict__ r,
+                                                    int64_t n, unsigned present_mask, float scale,
+                                                    float* __restrict__ loss) {
+  __shared__ double sh[1024];
+  double acc = 0.0;
+  int m = 0;
+  for (int a = 0; a < 3; ++a) m += (present_mask >> a) & 1;
+  for (int a = 0; a < 3; ++a) {
+    if (!((present_mask >> a) & 1)) continue;
+    for (int b = 0; b < 3; ++b) {
+      if (b == a || !((present_mask >> b) & 1)) continue;
+      const float* se = stats + (int64_t)pair_id(a, b) * n;
+      for (int64_t i = threadIdx.x; i < n; i += blockDim.x)
+        acc += (double)r[i] * ((double)scale + (double)logf(se[i]));
+    }
+  }
+  sh[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = 512; s > 0; s >>= 1) {
+    if ((int)threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double pos = (double)stats[6 * n];
+    const double c = 1.0 / ((double)n * m * (m - 1));
+    loss[0] = (float)(c * (sh[0] - (double)scale * pos));
+  }
+}
+
+int loss_launch(const float* stats, const float* r, int64_t n, unsigned present_mask, float scale, float* loss,
+                cudaStream_t st) {
+  loss_kernel<<<1, 1024, 0, st>>>(stats, r, n, present_mask, scale, loss);
+  BSC_LAUNCH_CHECK("loss_kernel");
+  return BSC_OK;
+}
+
+// uv[pid][i] = r_i / sumexp_pid[i];  gsbuf = {gs, 1/gs} with gs the power of two that keeps
+// gs * 2 * rmax <= 32768 (the fp16 range of the gradient-weight tile in TC16 mode).
+__global__ void __launch_bounds__(256) uv_kernel(const float* __restrict__ stats, const float* __restrict__ r,
+                                                 int64_t n, const float* __restrict__ rmax, int use_gs,
+                                                 float* __restrict__ uv, float* __restrict__ gsbuf) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) {
+    float gs = 1.0f;
+    if (use_gs) gs = exp2f(floorf(log2f(16384.0f / fmaxf(rmax[0], 1.0f))));
+    gsbuf[0] = gs;
+    gsbuf[1] = 1.0f / gs;
+  }
+  if (i >= n) return;
+  const float ri = r[i];
+#pragma unroll
+  for (int p = 0; p < 6; ++p) {
+    const float se = stats[(int64_t)p * n + i];
+    uv[(int64_t)p * n + i] = se > 0.f ? ri / se : 0.f;
+  }
+}
+
+int uv_launch(const float* stats, const float* r, int64_t n, const float* rmax, int use_gs, float* uv, float* gsbuf,
+              cudaStream_t st) {
+  uv_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(stats, r, n, rmax, use_gs, uv, gsbuf);
+  BSC_LAUNCH_CHECK("uv_kernel");
+  return BSC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K6: combine the raw sweep output with the positive term and chain through F.normalize:
+//   ghat = c*s*( (raw0+raw1)/gs - 2*sum_{y!=x} csum_y[rep_i] ),  dx = gout * (ghat - xhat <xhat,ghat>) / ||x||
+// One warp per (row, modality).
+// ---------------------------------------------------------------------------------------------
+
+template <typename T>
+__global__ void __launch_bounds__(256) combine_kernel(CombineArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t il = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int m = blockIdx.y;
+  if (il >= a.n_local || a.x[m] == nullptr) return;
+  int mcount = 0;
+  for (int q = 0; q < 3; ++q) mcount += (a.present_mask >> q) & 1;
+  const float c = 1.0f / ((float)a.n_global * (float)(mcount * (mcount - 1)));
+  const float cs = c * a.scale;
+  const float inv_gs = a.gsbuf[1];
+  const float gout = a.grad_out[0];
+  const int64_t ri = a.rep[a.row0 + il];
+  const T* xr = (const T*)a.x[m] + il * a.ldx;
+  T* gr = (T*)a.grad[m] + il * a.ldx;
+  const float* raw0 = a.raw[m] + il * (int64_t)a.d;
+  const float* raw1 = raw0 + a.n_local * (int64_t)a.d;
+
+  float ss = 0.f;
+  for (int cidx = lane; cidx < a.d; cidx += 32) {
+    const float v = to_f32<T>(xr[cidx]);
+    ss = fmaf(v, v, ss);
+  }
+  ss = warp_sum(ss);
+  const float nrm = sqrtf(ss);
+  const bool clamped = nrm < 1e-12f;
+  const float inv = 1.0f / fmaxf(nrm, 1e-12f);
+
+  auto ghat_at = [&](int cidx) -> float {
+    float raw = raw0[cidx];
+    if (a.n_slots > 1) raw += raw1[cidx];
+    float w = 0.f;
+#pragma unroll
+    for (int y = 0; y < 3; ++y)
+      if (y != m && ((a.present_mask >> y) & 1)) w += a.csum[y][ri * (int64_t)a.d + cidx];
+    return cs * (raw * inv_gs - 2.0f * w);
+  };
+
+  float dot = 0.f;
+  for (int cidx = lane; cidx < a.d; cidx += 32) dot = fmaf(to_f32<T>(xr[cidx]) * inv, ghat_at(cidx), dot);
+  dot = warp_sum(dot);
+  if (clamped) dot = 0.f;  // y = x / eps: the Jacobian is I / eps
+  for (int cidx = lane; cidx < a.d; cidx += 32) {
+    const float xh = to_f32<T>(xr[cidx]) * inv;
+    gr[cidx] = from_f32<T>(gout * inv * (ghat_at(cidx) - xh * dot));
+  }
+}
+
+int combine_launch(const CombineArgs& a, int x_dtype, cudaStream_t st) {
+  if (a.n_local == 0) return BSC_OK;
+  dim3 grid((unsigned)((a.n_local + 7) / 8), 3);
+  if (x_dtype == BSC_F32)
+    combine_kernel<float><<<grid, 256, 0, st>>>(a);
+  else if (x_dtype == BSC_BF16)
+    combine_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(a);
+  else if (x_dtype == BSC_F16)
+    combine_kernel<__half><<<grid, 256, 0, st>>>(a);
+  else {
+    set_error("bsc_infonce_bwd: unknown x_dtype %d", x_dtype);
+    return BSC_EINVAL;
+  }
+  BSC_LAUNCH_CHECK("combine_kernel");
+  return BSC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// k-way merge of candidate lists (cross-CTA and cross-GPU): one thread per query, ordering
+// (score desc, id asc), ids < 0 are padding.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) topk_merge_kernel(const float* __restrict__ cs, const int64_t* __restrict__ ci,
+                                                         int parts, int64_t nq, int k, float* __restrict__ os,
+                                                         int64_t* __restrict__ oi) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= nq) return;
+  constexpr int KMAX = 32;
+  float bs[KMAX];
+  int64_t bi[KMAX];
+  for (int t = 0; t < k; ++t) {
+    bs[t] = -3.4028234663852886e38f;
+    bi[t] = -1;
+  }
+  for (int p = 0; p < parts; ++p) {
+    for (int t = 0; t < k; ++t) {
+      const float s = cs[((int64_t)p * nq + q) * k + t];
+      const int64_t id = ci[((int64_t)p * nq + q) * k + t];
+      if (id < 0) continue;
+      // insertion: better than slot u if higher score, or equal score and lower id
+      int pos = k;
+      for (int u = k - 1; u >= 0; --u) {
+        const bool better = (bi[u] < 0) || (s > bs[u]) || (s == bs[u] && id < bi[u]);
+        if (better) pos = u; else break;
+      }
+      if (pos < k) {
+        for (int u = k - 1; u > pos; --u) {
+          bs[u] = bs[u - 1];
+          bi[u] = bi[u - 1];
+        }
+        bs[pos] = s;
+        bi[pos] = id;
+      }
+    }
+  }
+  for (int t = 0; t < k; ++t) {
+    os[q * k + t] = bs[t];
+    oi[q * k + t] = bi[t];
+  }
+}
+
+int topk_merge_launch(const float* cs, const int64_t* ci, int parts, int64_t nq, int k, float* os, int64_t* oi,
+                      cudaStream_t st) {
+  if (nq == 0) return BSC_OK;
+  if (k > 32) {
+    set_error("bsc_topk_merge: k=%d > 32 unsupported", k);
+    return BSC_EUNSUPPORTED;
+  }
+  topk_merge_kernel<<<(unsigned)((nq + 127) / 128), 128, 0, st>>>(cs, ci, parts, nq, k, os, oi);
+  BSC_LAUNCH_CHECK("topk_merge_kernel");
+  return BSC_OK;
+}
+
+}  // namespace bsc

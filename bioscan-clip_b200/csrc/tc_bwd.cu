@@ -1,0 +1,428 @@
+// tcgen05 InfoNCE backward sweep (the autograd of loss_func.py:46-51 without the N x N matrices).
+//
+// For an ordered modality pair (x, y) and the local row block I (128 rows):
+//     dXhat_x[I, :] (+)= sum_J  G[I, J] * Yhat[J, :],    G = gs * exp(s*S - s) * (u_i + v_j),  S = Xhat_I Yhat_J^T
+// with u_i = r_i / sumexp_xy[i], v_j = r_j / sumexp_yx[j] (softmax rows and columns share one exp).
+//
+// One CTA owns (x, y, I, column chunk of D): TMEM holds the chunk accumulator (<= 384 fp32 columns) plus one
+// 128 x 128 S tile.  Per column tile J: S is recomputed on the tensor cores (K = D), the epilogue warps turn
+// it into the fp16 tile G in 128B-swizzled shared memory, and a second tcgen05.mma chain (A = G K-major,
+// B = the Yhat tile read MN-major from the very bytes TMA delivered) accumulates into TMEM.
+// MMA issue order is software pipelined -- S(t+1) is queued before grad(t) -- so the tensor pipe executes
+// grad(t-1) while the epilogue is reading S(t) out of TMEM.
+// Warp roles (256 threads): 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator, 4..7 = epilogue.
+#include "tc_common.cuh"
+
+namespace bsc {
+namespace {
+
+constexpr int BM = kTcBM;   // 128 rows of I
+constexpr int BN = kTcBNB;  // 128 columns of J per tile
+constexpr int BK = 64;
+constexpr int SLOT = 16384;           // one TMA box: 128 rows x 128 bytes
+constexpr int STAGE_BYTES = 2 * SLOT; // S stage: {Xhat k-block, Yhat k-block}; grad stage: 128 d-columns of Yhat_J
+constexpr int STAGES = 5;
+constexpr int G_BYTES = BM * BN * 2;  // 32 KB fp16 tile, two 64-column swizzle spans
+constexpr int TMEM_COLS = 512;
+constexpr int ACC_COL0 = 128;         // accumulator columns start after the S tile
+constexpr int MAX_GROUPS = 3;         // 3 x 128 accumulator columns per CTA
+
+struct BwdParams {
+  CUtensorMap tmap[3];
+  int n_xy;
+  int xy_x[6], xy_y[6], xy_slot[6];
+  int n_iblk, n_jtile, kblocks;
+  int n_chunks;          // column chunks of D per row block
+  int groups_per_chunk;  // 128-column groups per chunk (last chunk may hold fewer)
+  int n_groups;          // d / 128
+  int num_items;
+  int d;
+  int64_t n_global, n_local, row0;
+  float k1, k2;
+  const float* uv;     // [6][N]
+  const float* gsbuf;  // {gs, 1/gs}
+  float* dxraw;        // [3][2][n_local][d]
+};
+
+struct __align__(8) BwdSmemTail {
+  uint64_t full[STAGES];
+  uint64_t empty[STAGES];
+  uint64_t s_full, s_free;
+  uint64_t g_ready[2], g_free[2];
+  uint64_t acc_full, acc_free;
+  uint32_t tmem_base;
+  uint32_t pad;
+  float vgs[2][BN];  // gs * v_j of the current / next column tile
+};
+
+constexpr size_t BWD_SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + 2 * (size_t)G_BYTES + sizeof(BwdSmemTail);
+static_assert(BWD_SMEM_BYTES <= 232448, "backward kernel exceeds the 227 KB shared-memory limit");
+
+__device__ __forceinline__ void decode_item(const BwdParams& p, int item, int& xy, int& iblk, int& chunk) {
+  chunk = item % p.n_chunks;
+  const int rest = item / p.n_chunks;
+  iblk = rest % p.n_iblk;
+  xy = rest / p.n_iblk;
+}
+
+__device__ __forceinline__ int chunk_groups(const BwdParams& p, int chunk) {
+  const int g0 = chunk * p.groups_per_chunk;
+  return min(p.groups_per_chunk, p.n_groups - g0);
+}
+
+__global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ BwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = ptx::smem_u32(smem_raw);
+  const uint32_t ring = (raw_addr + 1023u) & ~1023u;
+  uint8_t* ring_ptr = smem_raw + (ring - raw_addr);
+  const uint32_t gbuf = ring + STAGES * STAGE_BYTES;
+  uint8_t* gbuf_ptr = ring_ptr + (size_t)STAGES * STAGE_BYTES;
+  BwdSmemTail* tail = reinterpret_cast<BwdSmemTail*>(gbuf_ptr + 2 * (size_t)G_BYTES);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(ptx::smem_u32(&tail->full[s]), 1);
+      ptx::mbar_init(ptx::smem_u32(&tail->empty[s]), 1);
+    }
+    ptx::mbar_init(ptx::smem_u32(&tail->s_full), 1);
+    ptx::mbar_init(ptx::smem_u32(&tail->s_free), 4);
+    for (int b = 0; b < 2; ++b) {
+      ptx::mbar_init(ptx::smem_u32(&tail->g_ready[b]), 4);
+      ptx::mbar_init(ptx::smem_u32(&tail->g_free[b]), 1);
+    }
+    ptx::mbar_init(ptx::smem_u32(&tail->acc_full), 1);
+    ptx::mbar_init(ptx::smem_u32(&tail->acc_free), 4);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&p.tmap[0]);
+    ptx::prefetch_tmap(&p.tmap[1]);
+    ptx::prefetch_tmap(&p.tmap[2]);
+  }
+  if (warp == 2) {
+    ptx::tmem_alloc(ptx::smem_u32(&tail->tmem_base), TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = tail->tmem_base;
+  const int T = p.n_jtile;
+
+  if (warp == 0) {
+    // ================= TMA producer: stages in exactly the order the MMA warp consumes them =================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      auto next_stage = [&]() {
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      };
+      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+        int xy, iblk, chunk;
+        decode_item(p, item, xy, iblk, chunk);
+        const CUtensorMap* mx = &p.tmap[p.xy_x[xy]];
+        const CUtensorMap* my = &p.tmap[p.xy_y[xy]];
+        const int xrow = (int)(p.row0 + (int64_t)iblk * BM);
+        const int ng = chunk_groups(p, chunk);
+        const int dcol0 = chunk * p.groups_per_chunk * 128;
+        auto load_s = [&](int t) {
+          for (int kb = 0; kb < p.kblocks; ++kb) {
+            ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 100 + stage);
+            const uint32_t full = ptx::smem_u32(&tail->full[stage]);
+            const uint32_t sa = ring + stage * STAGE_BYTES;
+            ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
+            ptx::tma_load_2d(sa, mx, full, kb * BK, xrow);
+            ptx::tma_load_2d(sa + SLOT, my, full, kb * BK, t * BN);
+            next_stage();
+          }
+        };
+        auto load_g = [&](int t) {
+          for (int g = 0; g < ng; ++g) {
+            ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 110 + stage);
+            const uint32_t full = ptx::smem_u32(&tail->full[stage]);
+            const uint32_t sa = ring + stage * STAGE_BYTES;
+            ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
+            ptx::tma_load_2d(sa, my, full, dcol0 + g * 128, t * BN);
+            ptx::tma_load_2d(sa + SLOT, my, full, dcol0 + g * 128 + 64, t * BN);
+            next_stage();
+          }
+        };
+        load_s(0);
+        for (int t = 0; t < T; ++t) {
+          if (t + 1 < T) load_s(t + 1);
+          load_g(t);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    constexpr uint32_t idesc_s = umma_idesc(BM, BN, 0, 0, 0);   // S = Xhat_I * Yhat_J^T, both K-major
+    constexpr uint32_t idesc_g = umma_idesc(BM, 128, 0, 0, 1);  // acc += G (K-major) * Yhat_J (MN-major)
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t s_count = 0;    // S tiles issued so far (all items)
+    uint32_t g_count = 0;    // grad tiles issued so far
+    uint32_t item_count = 0;
+    auto next_stage = [&]() {
+      if (++stage == STAGES) {
+        stage = 0;
+        phase ^= 1u;
+      }
+    };
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++item_count) {
+      int xy, iblk, chunk;
+      decode_item(p, item, xy, iblk, chunk);
+      const int ng = chunk_groups(p, chunk);
+      auto issue_s = [&]() {
+        // the single S buffer is free once the epilogue has pulled the previous tile into registers
+        ptx::mbar_wait(ptx::smem_u32(&tail->s_free), (s_count & 1u) ^ 1u, 200);
+        ptx::tc_fence_after();
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 300 + stage);
+          ptx::tc_fence_after();
+          if (lane == 0) {
+            const uint32_t sa = ring + stage * STAGE_BYTES;
+            const uint32_t sb = sa + SLOT;
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = ptx::umma_desc_sw128(sa + k * 32, 16, 1024);
+              const uint64_t db = ptx::umma_desc_sw128(sb + k * 32, 16, 1024);
+              ptx::umma_f16(tmem_base, da, db, idesc_s, (kb | k) != 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(ptx::smem_u32(&tail->empty[stage]));
+            if (kb == p.kblocks - 1) ptx::umma_commit(ptx::smem_u32(&tail->s_full));
+          }
+          __syncwarp();
+          next_stage();
+        }
+        ++s_count;
+      };
+      auto issue_g = [&](int t) {
+        const uint32_t buf = g_count & 1u;
+        const uint32_t use = g_count >> 1;
+        if (t == 0) {
+          // first accumulation of the item overwrites TMEM: the previous item must have been drained
+          ptx::mbar_wait(ptx::smem_u32(&tail->acc_free), (item_count & 1u) ^ 1u, 210);
+        }
+        ptx::mbar_wait(ptx::smem_u32(&tail->g_ready[buf]), use & 1u, 220 + buf);
+        ptx::tc_fence_after();
+        for (int g = 0; g < ng; ++g) {
+          ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 310 + stage);
+          ptx::tc_fence_after();
+          if (lane == 0) {
+            const uint32_t sb = ring + stage * STAGE_BYTES;
+            const uint32_t ga = gbuf + buf * G_BYTES;
+            const uint32_t d_tmem = tmem_base + ACC_COL0 + g * 128;
+#pragma unroll
+            for (int kk = 0; kk < BN / 16; ++kk) {
+              // A: G[128 x 128] K-major, two 64-column spans of 16 KB; 32 bytes per K=16 step inside a span
+              const uint64_t da = ptx::umma_desc_sw128(ga + (kk >> 2) * SLOT + (kk & 3) * 32, 16, 1024);
+              // B: Yhat[j][d] read MN-major: 8-row (j) groups 1024 B apart, 64-column (d) groups one box apart
+              const uint64_t db = ptx::umma_desc_sw128(sb + kk * 2048, SLOT, 1024);
+              ptx::umma_f16(d_tmem, da, db, idesc_g, (t | kk) != 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(ptx::smem_u32(&tail->empty[stage]));
+            if (g == ng - 1) {
+              ptx::umma_commit(ptx::smem_u32(&tail->g_free[buf]));
+              if (t == T - 1) ptx::umma_commit(ptx::smem_u32(&tail->acc_full));
+            }
+          }
+          __syncwarp();
+          next_stage();
+        }
+        ++g_count;
+      };
+      issue_s();
+      for (int t = 0; t < T; ++t) {
+        if (t + 1 < T) issue_s();
+        issue_g(t);
+      }
+    }
+  } else if (warp >= 4) {
+    // ================= epilogue: S (TMEM) -> G (fp16, swizzled smem); final accumulator drain =================
+    const int q = warp & 3;
+    const int row_in_tile = q * 32 + lane;
+    const int et = threadIdx.x - 128;
+    const float gs = p.gsbuf[0];
+    uint32_t tile_count = 0;  // == s_count == g_count on this side
+    uint32_t item_count = 0;
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++item_count) {
+      int xy, iblk, chunk;
+      decode_item(p, item, xy, iblk, chunk);
+      const int x = p.xy_x[xy], y = p.xy_y[xy];
+      const int64_t arow = (int64_t)iblk * BM + row_in_tile;
+      const bool row_ok = arow < p.n_local;
+      const float ugs = row_ok ? gs * p.uv[(int64_t)pair_id(x, y) * p.n_global + p.row0 + arow] : 0.f;
+      const float* vrow = p.uv + (int64_t)pair_id(y, x) * p.n_global;
+      const int ng = chunk_groups(p, chunk);
+
+      for (int t = 0; t < T; ++t, ++tile_count) {
+        const uint32_t buf = tile_count & 1u;
+        const uint32_t use = tile_count >> 1;
+        // stage gs * v_j for this tile (one column per thread), visible to the 4 epilogue warps
+        {
+          const int64_t j = (int64_t)t * BN + et;
+          tail->vgs[buf][et] = (j < p.n_global) ? gs * vrow[j] : 0.f;
+        }
+        ptx::named_bar_sync(1, 128);
+        ptx::mbar_wait(ptx::smem_u32(&tail->s_full), tile_count & 1u, 400);
+        ptx::tc_fence_after();
+        // G buffer `buf` was last read by the grad MMAs of tile_count - 2
+        ptx::mbar_wait(ptx::smem_u32(&tail->g_free[buf]), (use & 1u) ^ 1u, 410 + buf);
+
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+        const uint32_t grow = gbuf + buf * G_BYTES + (uint32_t)(row_in_tile >> 3) * 1024u +
+                              (uint32_t)(row_in_tile & 7) * 128u;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t r0[32], r1[32];
+          ptx::tmem_ld_32x32(taddr + h * 64, r0);
+          ptx::tmem_ld_32x32(taddr + h * 64 + 32, r1);
+          ptx::tmem_ld_wait();
+          if (h == 1) {
+            // S is now entirely in registers: hand the TMEM tile back to the MMA warp
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tail->s_free));
+          }
+          const float* vg = &tail->vgs[buf][h * 64];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {  // 16-byte units of 8 columns
+            uint32_t pk[4];
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+              const int c = u * 8 + w * 2;
+              const float a0 = __uint_as_float(c < 32 ? r0[c & 31] : r1[c & 31]);
+              const float a1 = __uint_as_float(c + 1 < 32 ? r0[(c + 1) & 31] : r1[(c + 1) & 31]);
+              const float g0 = ptx::ex2(fmaf(a0, p.k1, -p.k2)) * (ugs + vg[c]);
+              const float g1 = ptx::ex2(fmaf(a1, p.k1, -p.k2)) * (ugs + vg[c + 1]);
+              const __half2 hh = __floats2half2_rn(g0, g1);
+              pk[w] = *reinterpret_cast<const uint32_t*>(&hh);
+            }
+            const uint32_t addr = grow + h * SLOT + ((uint32_t)(u ^ (row_in_tile & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]),
+                         "r"(pk[3])
+                         : "memory");
+          }
+        }
+        // generic-proxy writes -> visible to the tensor core's async-proxy reads, then signal
+        ptx::fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tail->g_ready[buf]));
+      }
+
+      // ---- drain the accumulator chunk of this item ----
+      ptx::mbar_wait(ptx::smem_u32(&tail->acc_full), item_count & 1u, 420);
+      ptx::tc_fence_after();
+      {
+        const int slot = p.xy_slot[xy];
+        float* out = p.dxraw + (((int64_t)(x * 2 + slot) * p.n_local + arow) * p.d) +
+                     (int64_t)chunk * p.groups_per_chunk * 128;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + ACC_COL0;
+        for (int c = 0; c < ng * 4; ++c) {
+          uint32_t raw[32];
+          ptx::tmem_ld_32x32(taddr + c * 32, raw);
+          ptx::tmem_ld_wait();
+          if (row_ok) {
+#pragma unroll
+            for (int w = 0; w < 8; ++w) {
+              float4 v = make_float4(__uint_as_float(raw[w * 4]), __uint_as_float(raw[w * 4 + 1]),
+                                     __uint_as_float(raw[w * 4 + 2]), __uint_as_float(raw[w * 4 + 3]));
+              *reinterpret_cast<float4*>(out + c * 32 + w * 4) = v;
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tail->acc_free));
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+}  // namespace
+
+int tc_bwd_raw(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStream_t st) {
+  BSC_REQUIRE(d->d % 128 == 0, BSC_EUNSUPPORTED, "TC16 backward needs d %% 128 == 0 (got %d); use BSC_MODE_F32",
+              d->d);
+  BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
+  BwdParams p{};
+  int first = -1;
+  for (int a = 0; a < 3; ++a)
+    if (d->xh[a]) {
+      int rc = make_tmap_2d(&p.tmap[a], d->xh[a], BSC_F16, d->n_global, d->d, 128);
+      if (rc) return rc;
+      if (first < 0) first = a;
+    }
+  for (int a = 0; a < 3; ++a)
+    if (!d->xh[a]) p.tmap[a] = p.tmap[first];
+  int n = 0;
+  for (int x = 0; x < 3; ++x) {
+    if (!d->xh[x]) continue;
+    int slot = 0;
+    for (int y = 0; y < 3; ++y) {
+      if (y == x || !d->xh[y]) continue;
+      p.xy_x[n] = x;
+      p.xy_y[n] = y;
+      p.xy_slot[n] = slot++;
+      ++n;
+    }
+  }
+  p.n_xy = n;
+  p.n_iblk = (int)((d->n_local + BM - 1) / BM);
+  p.n_jtile = (int)((d->n_global + BN - 1) / BN);
+  p.kblocks = d->d / BK;
+  p.n_groups = d->d / 128;
+  p.n_chunks = (p.n_groups + MAX_GROUPS - 1) / MAX_GROUPS;
+  p.groups_per_chunk = (p.n_groups + p.n_chunks - 1) / p.n_chunks;
+  p.num_items = n * p.n_iblk * p.n_chunks;
+  p.d = d->d;
+  p.n_global = d->n_global;
+  p.n_local = d->n_local;
+  p.row0 = d->row0;
+  const float log2e = 1.4426950408889634f;
+  p.k1 = d->logit_scale * log2e;
+  p.k2 = d->logit_scale * log2e;
+  p.uv = (const float*)(ws + L.uv);
+  p.gsbuf = (const float*)(ws + L.gs);
+  p.dxraw = (float*)(ws + L.dxraw);
+  if (p.num_items == 0 || p.n_jtile == 0) return BSC_OK;
+
+  static bool attr_done = false;
+  if (!attr_done) {
+    BSC_CUDA(cudaFuncSetAttribute(tc_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM_BYTES));
+    attr_done = true;
+  }
+  const int grid = p.num_items < sm_count() ? p.num_items : sm_count();
+  timing_begin(1, st);
+  tc_bwd_kernel<<<grid, 256, BWD_SMEM_BYTES, st>>>(p);
+  timing_end(1, st);
+  BSC_LAUNCH_CHECK("tc_bwd_kernel");
+  return BSC_OK;
+}
+
+}  // namespace bsc

@@ -1,0 +1,482 @@
+// tcgen05 similarity sweep: S = A * B^T over 128 x 256 tiles, operands streamed by TMA into a 4-stage
+// 128B-swizzled shared-memory ring, accumulators double-buffered in TMEM (2 x 256 columns), epilogue
+// applied straight out of TMEM so the N x N tile never reaches HBM.  Two epilogues:
+//   EPI_STATS  exp(s*S - s) row sums and column sums            (InfoNCE forward, loss_func.py:46-51)
+//   EPI_TOPK   per-row running top-k over the B rows            (IndexFlatIP.search, inference_and_eval.py:421)
+// Warp roles (256 threads): 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator, 4..7 = epilogue.
+#include "tc_common.cuh"
+
+namespace bsc {
+
+int reduce_parts_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float* out, cudaStream_t st);
+int topk_merge_launch(const float* cs, const int64_t* ci, int parts, int64_t nq, int k, float* os, int64_t* oi,
+                      cudaStream_t st);
+
+namespace {
+
+constexpr int BM = kTcBM;    // 128
+constexpr int BN = kTcBNF;   // 256
+constexpr int BK = 64;       // one 128-byte swizzle span of 16-bit elements
+constexpr int STAGES = 4;
+constexpr int A_BYTES = BM * BK * 2;            // 16 KB
+constexpr int B_BYTES = BN * BK * 2;            // 32 KB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;  // 48 KB
+constexpr int TMEM_COLS = 512;
+constexpr int KTOP = 8;  // register-resident top-k capacity of the TOPK epilogue
+
+enum { EPI_STATS = 0, EPI_TOPK = 1 };
+
+struct SimParams {
+  CUtensorMap tmap[3];  // per operand matrix: [rows][d], box {64, 128}
+  // work decomposition: item = (pair, jchunk, iblk), iblk fastest
+  int n_pairs;
+  int pair_a[3], pair_b[3];
+  int n_iblk, n_jtile, n_jchunk, jpc;
+  int num_items;
+  int kblocks;  // d / 64
+  int64_t a_rows;    // valid A rows (local rows of the stripe)
+  int64_t a_row0;    // first A row inside the A matrix
+  int64_t b_rows;    // valid B rows
+  // EPI_STATS
+  float k1, k2;      // exp(s*x - s) = ex2(x*k1 - k2)
+  float* rowpart;    // [pair][jchunk][a_pad]
+  float* colpart;    // [pair][iblk][b_pad]
+  int64_t a_pad, b_pad;
+  // EPI_TOPK
+  int k;
+  int64_t base_id;
+  float* cand_s;     // [jchunk][a_rows][k]
+  int64_t* cand_i;
+};
+
+struct __align__(8) SimSmemTail {
+  uint64_t full[STAGES];
+  uint64_t empty[STAGES];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint32_t tmem_base;
+  uint32_t pad;
+  float cs[2][4][BN];  // per-warp column partial sums, double-buffered by tile parity
+};
+
+constexpr size_t SIM_SMEM_BYTES = 1024 /*align slack*/ + (size_t)STAGES * STAGE_BYTES + sizeof(SimSmemTail);
+
+__device__ __forceinline__ void decode_item(const SimParams& p, int item, int& pair, int& jchunk, int& iblk) {
+  iblk = item % p.n_iblk;
+  const int rest = item / p.n_iblk;
+  jchunk = rest % p.n_jchunk;
+  pair = rest / p.n_jchunk;
+}
+
+// Butterfly transpose-reduce: on entry every lane holds 32 column values of its own row; on exit lane l
+// holds the sum over the warp's 32 rows of column l.  31 shuffles.
+__device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int k = 0; k < off; ++k) {
+      const float send = upper ? v[k] : v[k + off];
+      const float keep = upper ? v[k + off] : v[k];
+      v[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
+
+template <int EPI, int FMT>
+__global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ SimParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = ptx::smem_u32(smem_raw);
+  const uint32_t ring = (raw_addr + 1023u) & ~1023u;
+  uint8_t* ring_ptr = smem_raw + (ring - raw_addr);
+  SimSmemTail* tail = reinterpret_cast<SimSmemTail*>(ring_ptr + (size_t)STAGES * STAGE_BYTES);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(ptx::smem_u32(&tail->full[s]), 1);
+      ptx::mbar_init(ptx::smem_u32(&tail->empty[s]), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      ptx::mbar_init(ptx::smem_u32(&tail->tmem_full[b]), 1);
+      ptx::mbar_init(ptx::smem_u32(&tail->tmem_empty[b]), 4);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&p.tmap[0]);
+    ptx::prefetch_tmap(&p.tmap[1]);
+    ptx::prefetch_tmap(&p.tmap[2]);
+  }
+  if (warp == 2) {
+    ptx::tmem_alloc(ptx::smem_u32(&tail->tmem_base), TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = tail->tmem_base;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+        int pair, jchunk, iblk;
+        decode_item(p, item, pair, jchunk, iblk);
+        const CUtensorMap* ma = &p.tmap[p.pair_a[pair]];
+        const CUtensorMap* mb = &p.tmap[p.pair_b[pair]];
+        const int arow = (int)(p.a_row0 + (int64_t)iblk * BM);
+        const int jt_end = min(p.n_jtile, (jchunk + 1) * p.jpc);
+        for (int jt = jchunk * p.jpc; jt < jt_end; ++jt) {
+          const int brow = jt * BN;
+          for (int kb = 0; kb < p.kblocks; ++kb) {
+            ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 100 + stage);
+            const uint32_t full = ptx::smem_u32(&tail->full[stage]);
+            const uint32_t sa = ring + stage * STAGE_BYTES;
+            ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
+            ptx::tma_load_2d(sa, ma, full, kb * BK, arow);
+            ptx::tma_load_2d(sa + A_BYTES, mb, full, kb * BK, brow);
+            ptx::tma_load_2d(sa + A_BYTES + B_BYTES / 2, mb, full, kb * BK, brow + 128);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1u;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    constexpr uint32_t idesc = umma_idesc(BM, BN, FMT, 0, 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t tile_count = 0;
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      int pair, jchunk, iblk;
+      decode_item(p, item, pair, jchunk, iblk);
+      const int jt_end = min(p.n_jtile, (jchunk + 1) * p.jpc);
+      for (int jt = jchunk * p.jpc; jt < jt_end; ++jt, ++tile_count) {
+        const uint32_t buf = tile_count & 1u;
+        const uint32_t use = tile_count >> 1;
+        ptx::mbar_wait(ptx::smem_u32(&tail->tmem_empty[buf]), (use & 1u) ^ 1u, 200 + buf);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * BN;
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 300 + stage);
+          ptx::tc_fence_after();
+          if (lane == 0) {
+            const uint32_t sa = ring + stage * STAGE_BYTES;
+            const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = ptx::umma_desc_sw128(sa + k * 32, 16, 1024);
+              const uint64_t db = ptx::umma_desc_sw128(sb + k * 32, 16, 1024);
+              ptx::umma_f16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(ptx::smem_u32(&tail->empty[stage]));
+            if (kb == p.kblocks - 1) ptx::umma_commit(ptx::smem_u32(&tail->tmem_full[buf]));
+          }
+          __syncwarp();
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ================= epilogue (4 warps, thread <-> TMEM lane) =================
+    const int q = warp & 3;
+    const int row_in_tile = q * 32 + lane;
+    const int et = threadIdx.x - 128;  // 0..127
+    uint32_t tile_count = 0;
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      int pair, jchunk, iblk;
+      decode_item(p, item, pair, jchunk, iblk);
+      const int64_t arow = (int64_t)iblk * BM + row_in_tile;  // row inside the stripe
+      const bool row_ok = arow < p.a_rows;
+      const int jt_end = min(p.n_jtile, (jchunk + 1) * p.jpc);
+
+      float rowsum = 0.f;
+      float ts[KTOP];
+      int ti[KTOP];
+      if (EPI == EPI_TOPK) {
+#pragma unroll
+        for (int t = 0; t < KTOP; ++t) {
+          ts[t] = -3.4028234663852886e38f;
+          ti[t] = -1;
+        }
+      }
+
+      for (int jt = jchunk * p.jpc; jt < jt_end; ++jt, ++tile_count) {
+        const uint32_t buf = tile_count & 1u;
+        const uint32_t use = tile_count >> 1;
+        ptx::mbar_wait(ptx::smem_u32(&tail->tmem_full[buf]), use & 1u, 400 + buf);
+        ptx::tc_fence_after();
+        const int64_t col0 = (int64_t)jt * BN;
+        const bool edge = (col0 + BN > p.b_rows) || ((int64_t)iblk * BM + BM > p.a_rows);
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN;
+        float* cs = tail->cs[buf][q];
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t raw[32];
+          ptx::tmem_ld_32x32(taddr + c * 32, raw);
+          ptx::tmem_ld_wait();
+          if (EPI == EPI_STATS) {
+            float e[32];
+#pragma unroll
+            for (int t = 0; t < 32; ++t) e[t] = ptx::ex2(fmaf(__uint_as_float(raw[t]), p.k1, -p.k2));
+            if (edge) {
+#pragma unroll
+              for (int t = 0; t < 32; ++t) {
+                const bool ok = row_ok && (col0 + c * 32 + t < p.b_rows);
+                e[t] = ok ? e[t] : 0.f;
+              }
+            }
+            float s = 0.f;
+#pragma unroll
+            for (int t = 0; t < 32; ++t) s += e[t];
+            rowsum += s;
+            cs[c * 32 + lane] = warp_colsum32(e, lane);
+          } else {
+            const int jbase = (int)(col0 + c * 32);
+#pragma unroll
+            for (int t = 0; t < 32; ++t) {
+              const float s = __uint_as_float(raw[t]);
+              const int j = jbase + t;
+              // candidate only if it beats the current KTOP-th best (ties keep the earlier = lower id);
+              // zero-filled rows past the end of the bank never compete
+              if (s > ts[KTOP - 1] && j < p.b_rows) {
+                int pos = KTOP - 1;
+#pragma unroll
+                for (int u = KTOP - 1; u > 0; --u)
+                  if (pos == u && s > ts[u - 1]) pos = u - 1;
+#pragma unroll
+                for (int u = KTOP - 1; u > 0; --u)
+                  if (u > pos) {
+                    ts[u] = ts[u - 1];
+                    ti[u] = ti[u - 1];
+                  }
+#pragma unroll
+                for (int u = 0; u < KTOP; ++u)
+                  if (u == pos) {
+                    ts[u] = s;
+                    ti[u] = j;
+                  }
+              }
+            }
+          }
+        }
+        // release the accumulator buffer to the MMA warp
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tail->tmem_empty[buf]));
+
+        if (EPI == EPI_STATS) {
+          ptx::named_bar_sync(1, 128);
+          float* out = p.colpart + ((int64_t)pair * p.n_iblk + iblk) * p.b_pad + col0;
+          for (int col = et; col < BN; col += 128) {
+            if (col0 + col < p.b_rows)
+              out[col] = (tail->cs[buf][0][col] + tail->cs[buf][1][col]) +
+                         (tail->cs[buf][2][col] + tail->cs[buf][3][col]);
+          }
+        }
+      }
+
+      if (EPI == EPI_STATS) {
+        if (row_ok) p.rowpart[((int64_t)pair * p.n_jchunk + jchunk) * p.a_pad + arow] = rowsum;
+      } else {
+        if (row_ok) {
+          const int64_t o = ((int64_t)jchunk * p.a_rows + arow) * p.k;
+#pragma unroll
+          for (int t = 0; t < KTOP; ++t) {
+            if (t < p.k) {
+              p.cand_s[o + t] = ts[t];
+              p.cand_i[o + t] = ti[t] < 0 ? (int64_t)-1 : p.base_id + ti[t];
+            }
+          }
+        }
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+template <int EPI, int FMT>
+int launch_sim(const SimParams& p, cudaStream_t st) {
+  auto kern = tc_sim_kernel<EPI, FMT>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    BSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SIM_SMEM_BYTES));
+    attr_done = true;
+  }
+  const int grid = p.num_items < num_sms() ? p.num_items : num_sms();
+  if (grid <= 0) return BSC_OK;
+  kern<<<grid, 256, SIM_SMEM_BYTES, st>>>(p);
+  BSC_LAUNCH_CHECK("tc_sim_kernel");
+  return BSC_OK;
+}
+
+}  // namespace
+
+// Choose how many column tiles one work item sweeps so that there are several items per SM but the
+// row-partial buffer stays small.
+static int pick_jpc(int n_iblk, int n_jtile, int n_pairs) {
+  const int target_items = num_sms() * 4;
+  int jpc = (int)(((int64_t)n_pairs * n_iblk * n_jtile + target_items - 1) / target_items);
+  if (jpc < 1) jpc = 1;
+  if (jpc > n_jtile) jpc = n_jtile;
+  return jpc;
+}
+
+void tc_fwd_tiling(int64_t n_local, int64_t n_global, int n_pairs, int* n_iblk, int* n_jtile, int* jpc,
+                   int* n_jchunk) {
+  *n_iblk = (int)((n_local + BM - 1) / BM);
+  *n_jtile = (int)((n_global + BN - 1) / BN);
+  *jpc = pick_jpc(*n_iblk, *n_jtile, n_pairs > 0 ? n_pairs : 1);
+  *n_jchunk = (*n_jtile + *jpc - 1) / *jpc;
+}
+
+int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, float* stats, cudaStream_t st) {
+  BSC_REQUIRE(d->d % BK == 0, BSC_EUNSUPPORTED, "TC16 mode needs d %% 64 == 0 (got %d); use BSC_MODE_F32", d->d);
+  BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
+  SimParams p{};
+  int np = 0;
+  for (int a = 0; a < 3; ++a) {
+    if (d->xh[a]) {
+      int rc = make_tmap_2d(&p.tmap[a], d->xh[a], BSC_F16, d->n_global, d->d, 128);
+      if (rc) return rc;
+    }
+    for (int b = a + 1; b < 3; ++b)
+      if (d->xh[a] && d->xh[b]) {
+        p.pair_a[np] = a;
+        p.pair_b[np] = b;
+        ++np;
+      }
+  }
+  for (int a = 0; a < 3; ++a)
+    if (!d->xh[a]) p.tmap[a] = p.tmap[p.pair_a[0]];
+  p.n_pairs = np;
+  p.n_iblk = L.n_iblk;
+  p.n_jtile = L.n_jtile;
+  p.n_jchunk = L.n_jchunk;
+  p.jpc = L.jtiles_per_chunk;
+  p.num_items = np * L.n_jchunk * L.n_iblk;
+  p.kblocks = d->d / BK;
+  p.a_rows = d->n_local;
+  p.a_row0 = d->row0;
+  p.b_rows = d->n_global;
+  const float log2e = 1.4426950408889634f;
+  p.k1 = d->logit_scale * log2e;
+  p.k2 = d->logit_scale * log2e;
+  p.rowpart = (float*)(ws + L.rowpart);
+  p.colpart = (float*)(ws + L.colpart);
+  p.a_pad = L.n_local_pad;
+  p.b_pad = L.n_global_pad;
+  timing_begin(0, st);
+  int rc = launch_sim<EPI_STATS, 0>(p, st);
+  timing_end(0, st);
+  if (rc) return rc;
+  for (int q = 0; q < np; ++q) {
+    const int a = p.pair_a[q], b = p.pair_b[q];
+    rc = reduce_parts_launch(p.rowpart + (int64_t)q * L.n_jchunk * L.n_local_pad, L.n_jchunk, L.n_local_pad,
+                             d->n_local, stats + (int64_t)pair_id(a, b) * d->n_global + d->row0, st);
+    if (rc) return rc;
+    rc = reduce_parts_launch(p.colpart + (int64_t)q * L.n_iblk * L.n_global_pad, L.n_iblk, L.n_global_pad,
+                             d->n_global, stats + (int64_t)pair_id(b, a) * d->n_global, st);
+    if (rc) return rc;
+  }
+  return BSC_OK;
+}
+
+// ---- retrieval ---------------------------------------------------------------------------------------
+static void bank_tiling(int64_t nq, int64_t nb, int* n_iblk, int* n_jtile, int* jpc, int* n_jchunk) {
+  *n_iblk = (int)((nq + BM - 1) / BM);
+  *n_jtile = (int)((nb + BN - 1) / BN);
+  // enough items to fill the machine a few times, few enough that the candidate lists stay small
+  const int target = num_sms() * 2;
+  int chunks = (target + *n_iblk - 1) / *n_iblk;
+  if (chunks < 1) chunks = 1;
+  if (chunks > *n_jtile) chunks = *n_jtile > 0 ? *n_jtile : 1;
+  *jpc = (*n_jtile + chunks - 1) / chunks;
+  if (*jpc < 1) *jpc = 1;
+  *n_jchunk = (*n_jtile + *jpc - 1) / *jpc;
+}
+
+size_t tc_bank_ws(int64_t nq, int64_t nb, int d, int k) {
+  (void)d;
+  int n_iblk, n_jtile, jpc, n_jchunk;
+  bank_tiling(nq, nb, &n_iblk, &n_jtile, &jpc, &n_jchunk);
+  const size_t cand = (size_t)n_jchunk * (size_t)nq * (size_t)k;
+  return align_up(cand * sizeof(float), 256) + align_up(cand * sizeof(int64_t), 256);
+}
+
+int tc_bank_search(const void* q, int64_t nq, const void* bank, int64_t nb, int d, int k, int64_t base_id,
+                   float* out_s, int64_t* out_i, char* ws, size_t ws_bytes, cudaStream_t st) {
+  BSC_REQUIRE(d % BK == 0, BSC_EUNSUPPORTED, "TC16 retrieval needs d %% 64 == 0 (got %d); use BSC_MODE_F32", d);
+  BSC_REQUIRE(k >= 1 && k <= KTOP, BSC_EUNSUPPORTED, "TC16 retrieval supports k <= %d (got %d); use BSC_MODE_F32",
+              KTOP, k);
+  BSC_REQUIRE(nb < (1ll << 31) - 512 && nq < (1ll << 31) - 512, BSC_EUNSUPPORTED,
+              "shard too large for 32-bit TMA coordinates");
+  BSC_REQUIRE(ws_bytes >= tc_bank_ws(nq, nb, d, k), BSC_EWORKSPACE, "bsc_bank_search: workspace too small");
+  if (nq == 0) return BSC_OK;
+  SimParams p{};
+  int rc = make_tmap_2d(&p.tmap[0], q, BSC_BF16, nq, d, 128);
+  if (rc) return rc;
+  if (nb > 0) {
+    rc = make_tmap_2d(&p.tmap[1], bank, BSC_BF16, nb, d, 128);
+    if (rc) return rc;
+  } else {
+    p.tmap[1] = p.tmap[0];
+  }
+  p.tmap[2] = p.tmap[0];
+  p.n_pairs = 1;
+  p.pair_a[0] = 0;
+  p.pair_b[0] = 1;
+  bank_tiling(nq, nb, &p.n_iblk, &p.n_jtile, &p.jpc, &p.n_jchunk);
+  p.num_items = nb > 0 ? p.n_jchunk * p.n_iblk : 0;
+  p.kblocks = d / BK;
+  p.a_rows = nq;
+  p.a_row0 = 0;
+  p.b_rows = nb;
+  p.k = k;
+  p.base_id = base_id;
+  const size_t cand = (size_t)p.n_jchunk * (size_t)nq * (size_t)k;
+  p.cand_s = (float*)ws;
+  p.cand_i = (int64_t*)(ws + align_up(cand * sizeof(float), 256));
+  int parts = p.n_jchunk;
+  if (nb == 0) {
+    // nothing to scan: the merge of zero parts writes the padding
+    parts = 0;
+  } else {
+    timing_begin(2, st);
+    rc = launch_sim<EPI_TOPK, 1>(p, st);
+    timing_end(2, st);
+    if (rc) return rc;
+  }
+  return topk_merge_launch(p.cand_s, p.cand_i, parts, nq, k, out_s, out_i, st);
+}
+
+}  // namespace bsc

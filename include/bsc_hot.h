@@ -1,0 +1,152 @@
+/*
+ * bsc_hot.h -- C ABI of libbsc_hot.so: the B200 (sm_100a) contrastive hot path of BIOSCAN-CLIP.
+ *
+ * The reference (bioscan-ml/bioscan-clip @ 382d5ff) is pure Python and has no FFI; the entry points
+ * below are what a binding for its two leaf computations would bind:
+ *
+ *   loss       bioscanclip/model/loss_func.py:23-54 (ContrastiveLoss) and :94-165 (ClipLoss),
+ *              called from bioscanclip/epoch/train_epoch.py:37-38
+ *   retrieval  scripts/inference_and_eval.py:414-421 (make_prediction: normalize + IndexFlatIP
+ *              add/search), bioscanclip/epoch/eval_epoch.py:153-154,203, bioscanclip/util/util.py:163-165
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative BSC_E* code; bsc_last_error() returns a
+ *     thread-local message for the last failure on the calling thread;
+ *   - the caller owns ALL memory: every pointer is a device pointer obtained by the caller
+ *     (torch tensors in the Python host code) unless its name starts with h_; scratch space is one
+ *     caller-allocated workspace whose size comes from the matching *_workspace_bytes call;
+ *   - every launch goes to the cudaStream_t passed as `stream` (as void*); no function synchronises
+ *     the host with the device, allocates device memory or keeps global mutable state;
+ *   - there is no CPU fallback: without an sm_100 device the launches fail and the error is returned.
+ *
+ * Row-major everywhere; `ld` arguments are row strides in ELEMENTS.
+ */
+#ifndef BSC_HOT_H
+#define BSC_HOT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BSC_VERSION 100
+
+/* error codes */
+#define BSC_OK 0
+#define BSC_EINVAL (-1)       /* bad argument (null pointer, bad shape, bad enum)            */
+#define BSC_EUNSUPPORTED (-2) /* legal request this build does not implement (message says)  */
+#define BSC_ECUDA (-3)        /* a CUDA runtime / driver call failed (message has the text)  */
+#define BSC_EWORKSPACE (-4)   /* workspace too small                                          */
+
+/* element types */
+#define BSC_F32 0
+#define BSC_BF16 1
+#define BSC_F16 2
+
+/* arithmetic modes */
+#define BSC_MODE_F32 0  /* SIMT fp32 path: exact-parity mode (1e-5 vs the fp32 reference)          */
+#define BSC_MODE_TC16 1 /* tcgen05 path: 16-bit normalised operands, fp32 accumulate in TMEM       */
+
+/* zero-norm rules for bsc_l2norm_fwd */
+#define BSC_NORM_TORCH 0   /* F.normalize: x / max(||x||, 1e-12)            (loss_func.py:43-44)   */
+#define BSC_NORM_SKLEARN 1 /* sklearn normalize: ||x|| < 10*eps64 -> x kept (inference_and_eval.py:416) */
+
+#define BSC_MAX_MODALITIES 3
+
+int bsc_version(void);
+const char* bsc_last_error(void);
+/* 0 when the current device is sm_100 and the tcgen05 kernels can be launched. */
+int bsc_device_check(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * K1  row L2 normalisation (F.normalize / sklearn normalize) -- loss_func.py:43-44,150-151,
+ *     simple_clip.py:34-49, inference_and_eval.py:416-417.
+ *     y16 (BSC_F16 or BSC_BF16, may be NULL) and y32 (float, may be NULL) receive x * inv_norm;
+ *     inv_norm[n] (may be NULL) receives the factor itself.
+ * ---------------------------------------------------------------------------------------------- */
+int bsc_l2norm_fwd(const void* x, int x_dtype, int64_t n, int d, int64_t ldx,
+                   void* y16, int y16_dtype, float* y32, float* inv_norm, int zero_rule, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * K2  label statistics replacing construct_label_metrix (loss_func.py:18-21): for labels[n]
+ *     r[i]    = #{j : labels[j] == labels[i]}      (row sum of the 0/1 label matrix)
+ *     rep[i]  = min{j : labels[j] == labels[i]}    (class representative)
+ *     next[i] = min{j > i : labels[j] == labels[i]} or -1
+ *     rmax[0] = max_i r[i] (float)
+ * ---------------------------------------------------------------------------------------------- */
+int bsc_label_stats(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
+                    void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * InfoNCE loss -- ContrastiveLoss.forward / ClipLoss.forward.
+ *
+ * The problem descriptor.  xh[m] points to the GLOBAL (already gathered) batch of modality m:
+ * n_global normalised rows of d elements, float (BSC_MODE_F32) or fp16 (BSC_MODE_TC16), NULL when the
+ * modality is absent.  This rank owns rows [row0, row0 + n_local).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct bsc_infonce_desc {
+  int64_t n_global;
+  int64_t n_local;
+  int64_t row0;
+  int32_t d;
+  int32_t mode;        /* BSC_MODE_*                                              */
+  float logit_scale;   /* s = 1/0.07 in the reference (scripts/train_cl.py:190)   */
+  int32_t reserved;
+  const void* xh[BSC_MAX_MODALITIES];
+  const float* r;      /* [n_global] from bsc_label_stats                          */
+  const int32_t* rep;  /* [n_global]                                               */
+  const int32_t* next; /* [n_global]                                               */
+  const float* rmax;   /* [1]                                                      */
+} bsc_infonce_desc;
+
+/* number of floats in the statistics vector: 6 ordered-pair sum-exp rows of n_global + 4 scalars */
+int64_t bsc_infonce_stats_len(int64_t n_global);
+int bsc_infonce_workspace_bytes(const bsc_infonce_desc* p, size_t* bytes);
+
+/* Forward sweep.  stats (bsc_infonce_stats_len floats, overwritten) receives, for every ordered pair
+ * (a,b) of present modalities, sum_j exp(S_ab[i,j] - s) for the rows this rank can complete and the
+ * PARTIAL column sums over its local rows, plus the local part of sum_i sum_j T_ij S_ij.  With more
+ * than one rank the caller sums `stats` over ranks (one all_reduce) before the next two calls.   */
+int bsc_infonce_fwd(const bsc_infonce_desc* p, float* stats, void* workspace, size_t workspace_bytes,
+                    void* stream);
+
+/* loss[0] = the scalar of loss_func.py:54 / :163 from the (rank-summed) statistics. */
+int bsc_infonce_loss(const bsc_infonce_desc* p, const float* stats, float* loss, void* stream);
+
+/* Backward.  x[m] are this rank's ORIGINAL (un-normalised) local rows, dtype x_dtype, row stride ldx;
+ * grad[m] (same dtype, same stride) receives grad_out[0] * dLoss/dx[m] for the local rows.        */
+int bsc_infonce_bwd(const bsc_infonce_desc* p, const float* stats, const void* const* x, int x_dtype,
+                    int64_t ldx, const float* grad_out, void* const* grad, void* workspace,
+                    size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Retrieval -- IndexFlatIP.search on one bank shard (inference_and_eval.py:418-421).
+ *   bank    [nb, d] normalised rows, float (BSC_MODE_F32) or bf16 (BSC_MODE_TC16)
+ *   queries [nq, d] same dtype
+ *   out_scores [nq, k] float descending, out_ids [nq, k] int64 = base_id + row; equal scores are
+ *   ordered by lowest id; missing entries (k > nb) are id -1 / score -3.4028235e38 as faiss does.
+ * ---------------------------------------------------------------------------------------------- */
+int bsc_bank_search_workspace_bytes(int64_t nq, int64_t nb, int d, int k, int mode, size_t* bytes);
+int bsc_bank_search(const void* queries, int64_t nq, const void* bank, int64_t nb, int d, int k,
+                    int64_t base_id, int mode, float* out_scores, int64_t* out_ids, void* workspace,
+                    size_t workspace_bytes, void* stream);
+/* k-way merge of `parts` candidate lists [parts][nq][k] (e.g. one per GPU after an all_gather). */
+int bsc_topk_merge(const float* cand_scores, const int64_t* cand_ids, int parts, int64_t nq, int k,
+                   float* out_scores, int64_t* out_ids, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Instrumentation for bench.py: CUDA-event time of the dominant kernel of the last call made with
+ * bsc_set_timing(1) on this thread (milliseconds, -1 if none).  which: 0 = infonce forward sweep,
+ * 1 = infonce backward sweep, 2 = bank scan.  Reading it synchronises on the recorded events only.
+ * ---------------------------------------------------------------------------------------------- */
+int bsc_set_timing(int enabled);
+float bsc_last_kernel_ms(int which);
+/* kernels launched by this library on this thread since the last reset */
+int64_t bsc_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BSC_HOT_H */

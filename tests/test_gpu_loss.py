@@ -1,0 +1,125 @@
+"""GPU parity: the CUDA loss (through the C ABI) vs the oracle and vs the committed reference fixtures."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import loss_oracle
+from tests.synth import loss_inputs
+
+pytestmark = pytest.mark.gpu
+NAMES = ["image", "dna", "text"]
+FP32_TOL = 1e-5   # north_star: loss and gradients within 1e-5 relative in fp32
+TC16_TOL = 2e-3   # and 2e-3 in the 16-bit tensor-core mode
+
+
+def _run(feats, labels, precision, scale=1 / 0.07):
+    import bsc
+
+    leaves = [None if f is None else f.detach().clone().cuda().requires_grad_(True) for f in feats]
+    crit = bsc.ContrastiveLoss(torch.nn.CrossEntropyLoss(), scale, precision=precision)
+    loss = crit(leaves[0], leaves[1], leaves[2], labels.cuda())
+    loss.backward()
+    torch.cuda.synchronize()
+    return loss.detach().cpu(), [None if l is None else l.grad.detach().float().cpu() for l in leaves]
+
+
+def _compare(loss, grads, ref_loss, ref_grads, tol):
+    assert abs(float(loss) - float(ref_loss)) <= tol * max(abs(float(ref_loss)), 1e-3), (float(loss), float(ref_loss))
+    for g, gr in zip(grads, ref_grads):
+        if gr is None:
+            assert g is None
+            continue
+        err = (g.double() - gr.double()).abs().max().item()
+        assert err <= tol * gr.abs().max().item() + 1e-12, (err, gr.abs().max().item())
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "loss_*.npz"))))
+def test_fp32_mode_matches_reference_fixtures(path):
+    z = np.load(path)
+    feats = [torch.from_numpy(z[f"x_{n}"]) if f"x_{n}" in z else None for n in NAMES]
+    labels = torch.from_numpy(z["labels"])
+    loss, grads = _run(feats, labels, "fp32", float(z["logit_scale"]))
+    ref_grads = [torch.from_numpy(z[f"g_{n}"]) if f"g_{n}" in z else None for n in NAMES]
+    _compare(loss, grads, float(z["loss"]), ref_grads, FP32_TOL)
+
+
+@pytest.mark.parametrize("n,d,present,labels,normalised", [
+    (256, 768, (True, True, False), "arange", True),    # BASELINE config 1
+    (300, 200, (True, True, True), "multi", False),     # ragged N, d not a multiple of 16
+    (129, 768, (True, False, True), "multi", True),
+    (1024, 768, (True, True, True), "arange", True),
+    (64, 32, (True, True, True), "same", False),        # every label equal: r_i = N
+])
+def test_fp32_mode_matches_oracle(n, d, present, labels, normalised):
+    feats, lab = loss_inputs(n, d, present, seed=n, normalised=normalised, labels=labels)
+    ref_loss, ref_grads = loss_oracle.closed_form_grads(feats, lab)  # fp64 evaluation of the reference maths
+    loss, grads = _run(feats, lab, "fp32")
+    _compare(loss, grads, ref_loss, ref_grads, FP32_TOL)
+
+
+@pytest.mark.parametrize("n,d,present,labels,shared", [
+    (256, 768, (True, True, False), "arange", 0.5),
+    (512, 768, (True, True, True), "multi", 0.5),
+    (1000, 768, (True, True, True), "arange", 0.5),     # ragged N (not a tile multiple)
+    (384, 256, (True, False, True), "multi", 0.0),      # flat softmax, d = 2 column groups
+    (2048, 768, (True, True, True), "arange", 0.5),
+])
+def test_tc16_mode_matches_oracle_on_bf16_inputs(n, d, present, labels, shared):
+    feats, lab = loss_inputs(n, d, present, seed=n + 1, labels=labels, shared=shared, dtype=torch.bfloat16)
+    ref_in = [None if f is None else f.float() for f in feats]  # the fp32 reference on the same rounded inputs
+    ref_loss, ref_grads = loss_oracle.closed_form_grads(ref_in, lab)
+    loss, grads = _run(feats, lab, "tc16")
+    _compare(loss, grads, ref_loss, ref_grads, TC16_TOL)
+
+
+def test_tc16_config2_4096_three_modalities():
+    """BASELINE config 2: image-DNA-text, global batch 4096, bf16 inputs."""
+    feats, lab = loss_inputs(4096, 768, seed=7, labels="arange", dtype=torch.bfloat16)
+    ref_in = [f.float() for f in feats]
+    torch.set_num_threads(os.cpu_count() or 8)
+    ref_loss, ref_grads = loss_oracle.contrastive_loss_and_grads(ref_in, lab)
+    loss, grads = _run(feats, lab, "tc16")
+    _compare(loss, grads, ref_loss, ref_grads, TC16_TOL)
+
+
+def test_properties_at_full_size():
+    """Size-independent checks at N = 32768 (the oracle cannot run there): permutation invariance of the
+    batch, and agreement of the two arithmetic modes on a strided sample of gradient rows."""
+    n = 32768
+    feats, lab = loss_inputs(n, 768, seed=3, labels="multi", dtype=torch.bfloat16)
+    loss, grads = _run(feats, lab, "tc16")
+    perm = torch.randperm(n, generator=torch.Generator().manual_seed(5))
+    loss_p, grads_p = _run([f[perm] for f in feats], lab[perm], "tc16")
+    assert abs(float(loss) - float(loss_p)) <= 1e-4 * abs(float(loss))
+    for g, gp in zip(grads, grads_p):
+        assert (g[perm] - gp).abs().max() <= 2e-3 * g.abs().max()
+    assert all(torch.isfinite(g).all() for g in grads)
+
+
+def test_error_behaviour():
+    import bsc
+
+    x = torch.randn(8, 64, device="cuda")
+    with pytest.raises(ValueError, match="Too less element"):
+        bsc.ContrastiveLoss(torch.nn.CrossEntropyLoss(), 1 / 0.07)(x, None, None, torch.arange(8).cuda())
+    with pytest.raises(NotImplementedError):
+        bsc.ContrastiveLoss(torch.nn.CrossEntropyLoss(label_smoothing=0.1), 1 / 0.07)
+    with pytest.raises(bsc.BscError):
+        bsc.ContrastiveLoss(None, 1 / 0.07)(x.cpu(), x.cpu(), None, torch.arange(8))
+    # d not a multiple of 128 is a loud error in the tensor-core mode, not a silent detour
+    y = torch.randn(8, 72, device="cuda", dtype=torch.bfloat16)
+    with pytest.raises(bsc.BscError, match="BSC_MODE_F32"):
+        bsc.ContrastiveLoss(None, 1 / 0.07, precision="tc16")(y, y, None, torch.arange(8).cuda())
+
+
+def test_cliploss_single_rank_output_dict():
+    import bsc
+
+    feats, lab = loss_inputs(96, 64, seed=9, labels="multi")
+    ref_loss, _ = loss_oracle.closed_form_grads(feats, lab)
+    crit = bsc.ClipLoss(rank=0, world_size=1, criterion=torch.nn.CrossEntropyLoss())
+    out = crit(feats[0].cuda(), feats[1].cuda(), feats[2].cuda(), lab.cuda(), 1 / 0.07, output_dict=True)
+    assert abs(float(out["contrastive_loss"]) - float(ref_loss)) <= FP32_TOL * abs(float(ref_loss))

@@ -1,0 +1,94 @@
+"""GPU parity: bank scan top-k (through the C ABI) vs the retrieval oracle."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import retrieval_oracle as ro
+from tests.synth import bank_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("nb,nq,d,k", [(5000, 257, 768, 5), (70000, 64, 128, 5), (333, 10, 40, 3), (3, 4, 16, 5)])
+def test_fp32_indices_bit_exact(nb, nq, d, k):
+    import bsc
+
+    bank, q, pi = bank_inputs(nb, nq, d, seed=nb)
+    ref_s, ref_i = ro.search_ip(bank, q, k)
+    index = bsc.IndexFlatIP(d, precision="fp32")
+    index.add(bank)
+    s, i = index.search(q, k)
+    assert s.dtype == np.float32 and i.dtype == np.int64 and i.shape == (nq, k)
+    np.testing.assert_array_equal(i, ref_i)
+    np.testing.assert_allclose(s, ref_s, rtol=0, atol=3e-6)
+
+
+@pytest.mark.parametrize("nb,nq,d,k", [(4096, 128, 768, 5), (10000, 300, 768, 5), (777, 33, 128, 1), (70000, 32, 768, 5)])
+def test_bf16_scan_matches_oracle_on_rounded_bank(nb, nq, d, k):
+    """bf16 mode: the oracle sees the same bf16-rounded bank and queries, so planted neighbours and exact
+    duplicates must come back with identical ids; scores agree to fp32 accumulation error."""
+    import bsc
+
+    bank, q, pi = bank_inputs(nb, nq, d, seed=nb + 1)
+    bank_r = torch.from_numpy(bank).bfloat16().float().numpy()
+    q_r = torch.from_numpy(q).bfloat16().float().numpy()
+    ref_s, ref_i = ro.search_ip(bank_r, q_r, k)
+    index = bsc.IndexFlatIP(d, precision="bf16")
+    index.add(bank)
+    s, i = index.search(q, k)
+    # top-1 is planted (margin >> rounding); deeper ranks may swap only inside fp32 near-ties
+    np.testing.assert_array_equal(i[:, 0], ref_i[:, 0])
+    np.testing.assert_allclose(s, ref_s, rtol=0, atol=2e-5)
+    mism = i != ref_i
+    if mism.any():
+        gap = np.abs(s - ref_s)[mism]
+        assert gap.max() <= 2e-5
+
+
+def test_make_prediction_forms_and_labels():
+    import bsc
+
+    bank, q, pi = bank_inputs(600, 20, 64, seed=4)
+    labels = [{lv: f"{lv}_{i % 7}" for lv in ro.LEVELS} for i in range(600)]
+    ref = ro.make_prediction(q * 3.0, bank * 0.5, labels, True, True, 5)
+    out = bsc.make_prediction(q * 3.0, bank * 0.5, labels, True, True, 5)
+    assert out[0] == ref[0]
+    np.testing.assert_array_equal(out[2], ref[2])
+    np.testing.assert_allclose(out[1], ref[1], atol=3e-6)
+    only = bsc.make_prediction(q, bank, labels, max_k=3)
+    assert isinstance(only, list) and len(only) == 20 and len(only[0]["species"]) == 3
+
+
+def test_merge_across_incremental_adds_and_ties():
+    import bsc
+
+    bank, q, pi = bank_inputs(3000, 50, 96, seed=8)
+    ref_s, ref_i = ro.search_ip(bank, q, 5)
+    index = bsc.IndexFlatIP(96)
+    index.add(bank[:1000])
+    index.add(bank[1000:])
+    assert index.ntotal == 3000
+    s, i = index.search(q, 5)
+    np.testing.assert_array_equal(i, ref_i)
+
+
+def test_full_size_properties():
+    """625k x 768 bf16 shard (one GPU's share of the 5M bank): every query must find its planted row first,
+    and searching the two halves separately then merging must equal the one-pass search."""
+    import bsc
+
+    nb, nq, d = 625_000, 256, 768
+    g = torch.Generator(device="cuda").manual_seed(3)
+    bank = torch.nn.functional.normalize(torch.randn(nb, d, device="cuda", generator=g), dim=1)
+    pi = torch.randint(0, nb, (nq,), device="cuda", generator=g)
+    q = torch.nn.functional.normalize(bank[pi] + 0.3 / d ** 0.5 * torch.randn(nq, d, device="cuda", generator=g), dim=1)
+    index = bsc.IndexFlatIP(d, precision="bf16")
+    index.add(bank)
+    s, i = index.search_device(q, 5)
+    assert (i[:, 0] == pi).all()
+    assert (s[:, :-1] >= s[:, 1:]).all()
+    two = bsc.IndexFlatIP(d, precision="bf16")
+    two.add(bank[: nb // 2])
+    two.add(bank[nb // 2:])
+    s2, i2 = two.search_device(q, 5)
+    assert (i2 == i).all() and torch.equal(s2, s)

@@ -1,0 +1,89 @@
+"""CPU-only checks: the C-ABI library loads and exports every symbol the header declares, the host modules
+refuse to run without a CUDA device, and the argument handling mirrors the reference."""
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def built_lib():
+    sys.path.insert(0, os.path.join(ROOT, "bioscan-clip_b200"))
+    import build as bsc_build
+
+    return bsc_build.build_lib()
+
+
+def test_library_exports_every_declared_symbol(built_lib):
+    import ctypes
+
+    header = open(os.path.join(ROOT, "include", "bsc_hot.h")).read()
+    declared = set(re.findall(r"^\s*(?:const\s+)?[a-z_0-9]+\*?\s+\*?(bsc_[a-z0-9_]+)\s*\(", header, re.M))
+    assert {"bsc_infonce_fwd", "bsc_infonce_bwd", "bsc_bank_search", "bsc_topk_merge", "bsc_l2norm_fwd"} <= declared
+    lib = ctypes.CDLL(built_lib)
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in bsc_hot.h but not exported"
+    lib.bsc_version.restype = ctypes.c_int
+    assert lib.bsc_version() == 100
+    from bsc import _lib
+
+    assert set(_lib.EXPORTS) == declared
+
+
+def test_sass_contains_blackwell_tensor_and_tma_ops(built_lib):
+    out = subprocess.run(["cuobjdump", "-sass", built_lib], capture_output=True, text=True).stdout
+    assert "UTCHMMA" in out, "tcgen05.mma missing from the SASS"
+    assert "LDTM" in out, "tcgen05.ld missing from the SASS"
+    assert "UTMALDG" in out, "TMA loads missing from the SASS"
+    assert "HMMA.16" not in out.replace("UTCHMMA", ""), "legacy mma.sync path present"
+
+
+def test_argument_errors_without_gpu(built_lib):
+    import ctypes
+
+    from bsc import _lib
+
+    L = _lib.lib()
+    rc = L.bsc_l2norm_fwd(None, 0, 4, 8, 8, None, 2, None, None, 0, None)
+    assert rc == -1 and b"x is null" in L.bsc_last_error()
+    nbytes = ctypes.c_size_t(0)
+    assert L.bsc_bank_search_workspace_bytes(10, 100, 64, 5, 7, ctypes.byref(nbytes)) == -1
+    assert L.bsc_bank_search_workspace_bytes(10, 100, 64, 5, 0, ctypes.byref(nbytes)) == 0 and nbytes.value > 0
+    d = _lib.InfoNceDesc()
+    d.n_global, d.n_local, d.row0, d.d, d.mode = 8, 8, 0, 64, 1
+    assert L.bsc_infonce_workspace_bytes(ctypes.byref(d), ctypes.byref(nbytes)) == -1
+    assert b"Too less element" in L.bsc_last_error()
+
+
+def test_modules_refuse_cpu_tensors(built_lib):
+    import bsc
+
+    x = torch.randn(4, 8)
+    with pytest.raises(ValueError, match="Too less element for calculating the contrastive loss."):
+        bsc.ContrastiveLoss(torch.nn.CrossEntropyLoss(), 1 / 0.07)(x, None, None, torch.arange(4))
+    with pytest.raises(bsc.BscError, match="no CPU path"):
+        bsc.ContrastiveLoss(torch.nn.CrossEntropyLoss(), 1 / 0.07)(x, x, None, torch.arange(4))
+    with pytest.raises(NotImplementedError):
+        bsc.ClipLoss(criterion=torch.nn.CrossEntropyLoss(reduction="sum"))
+    with pytest.raises(NotImplementedError):
+        bsc.ClipLoss(use_horovod=True)
+    if not torch.cuda.is_available():
+        with pytest.raises(bsc.BscError):
+            bsc.IndexFlatIP(8)
+
+
+def test_resolve_mode():
+    from bsc._lib import MODE_F32, MODE_TC16
+    from bsc.loss import resolve_mode
+
+    f32, b16 = torch.zeros(1), torch.zeros(1, dtype=torch.bfloat16)
+    assert resolve_mode("auto", [f32, f32]) == MODE_F32
+    assert resolve_mode("auto", [f32, b16]) == MODE_TC16
+    assert resolve_mode("tc16", [f32]) == MODE_TC16 and resolve_mode("fp32", [b16]) == MODE_F32
+    with pytest.raises(ValueError):
+        resolve_mode("fp8", [f32])
