@@ -1,0 +1,449 @@
+#!/usr/bin/env python
+"""bench.py -- the driver's measurement contract for the BIOSCAN-CLIP contrastive hot path.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one process per GPU)
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path (oracle port) on host cores
+
+One "step" = one fwd+bwd of the three-modality InfoNCE loss (image, DNA, text; 768-d; bf16 inputs; labels =
+arange as util/dataset.py:147) at GLOBAL batch 32768 -- the configuration BASELINE.json's metric is quoted on.
+With N ranks every rank owns 32768/N rows (strong scaling: the global batch is fixed) and the step includes the
+all_gather of the normalised rows and the all_reduce of the sum-exp statistics.
+
+Printed (rank 0, ONE JSON line): metric/value/unit (samples/s, inputs resident in HBM, CUDA-event timed, max over
+ranks), e2e (same metric with pinned-host inputs copied in and loss + gradients copied out inside the timed
+region), roofline of the dominant kernel (the backward sweep; algorithmic FLOPs / CUDA-event kernel time /
+MEASURED_PEAKS.json), cpu_baseline (oracle port on the host cores, bounded sample), clocks, gpu_launches, and a
+`retrieval` object with the second half of the metric (queries/s of the bank scan).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "bioscan-clip_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "InfoNCE fwd+bwd samples/s @32k global batch"
+UNIT = "samples/s"
+N_GLOBAL = 32768
+DIM = 768
+SCALE = 1 / 0.07
+CPU_SAMPLE_N = 4096
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--n-global", type=int, default=N_GLOBAL)
+    ap.add_argument("--no-retrieval", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--bank-rows", type=int, default=5_000_000)
+    ap.add_argument("--queries", type=int, default=100_000)
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------
+# helpers
+# ---------------------------------------------------------------------------------------------
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            z = json.load(f)
+        return {"hbm_gbs": float(z["hbm_gbs"]), "tflops_burst": float(z["bf16_tflops"]),
+                "tflops_sustained": float(z.get("bf16_tflops_sustained", z["bf16_tflops"])), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "tflops_burst": 1590.0, "tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i",
+                 str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                smax = float(parts[1])
+            except ValueError:
+                continue
+            for nm, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def synth_loss_rows(torch, n_global, row0, n_local, device, dtype):
+    """X_m = normalize(Z + 0.5 E_m) with a shared component Z so matched pairs have
+    cos ~ 0.8.  Generated per global row so every world size sees the same global batch."""
+    feats = []
+    gz = torch.Generator(device=device).manual_seed(7)
+    z = torch.randn(n_global, DIM, generator=gz, device=device)[row0:row0 + n_local]
+    for m in range(3):
+        gm = torch.Generator(device=device).manual_seed(1000 + m)
+        e = torch.randn(n_global, DIM, generator=gm, device=device)[row0:row0 + n_local]
+        feats.append(torch.nn.functional.normalize(z + 0.5 * e, dim=1).to(dtype).contiguous())
+        del e
+    labels = torch.arange(row0, row0 + n_local, device=device, dtype=torch.int64)
+    return feats, labels
+
+
+def cpu_loss_baseline(n, repeats=2):
+    """The reference's loss maths (oracle port of loss_func.py:29-54) fwd+bwd in fp32 on the host cores."""
+    import torch
+
+    from oracle import loss_oracle
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    feats, labels = synth_loss_rows(torch, n, 0, n, "cpu", torch.float32)
+    loss_oracle.contrastive_loss_and_grads(feats, labels, SCALE)  # warm-up
+    best = float("inf")
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        loss_oracle.contrastive_loss_and_grads(feats, labels, SCALE)
+        best = min(best, time.perf_counter() - t0)
+    return {"value": n / best, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"oracle port of ContrastiveLoss fwd+bwd, fp32, 3 modalities, N={n} (N=32768 needs >100 GB of "
+                      f"N x N tensors on the CPU path and is not runnable as written); best of {repeats}",
+            "seconds": best}
+
+
+# ---------------------------------------------------------------------------------------------
+# reference arm: the reference's CPU path (oracle port) on the host cores
+# ---------------------------------------------------------------------------------------------
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+
+    from oracle import loss_oracle
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    n = CPU_SAMPLE_N
+    feats, labels = synth_loss_rows(torch, n, 0, n, "cpu", torch.float32)
+    for _ in range(max(1, min(args.warmup, 2))):
+        loss_oracle.contrastive_loss_and_grads(feats, labels, SCALE)
+    steps = max(1, min(args.steps, 5))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        loss_oracle.contrastive_loss_and_grads(feats, labels, SCALE)
+    dt = (time.perf_counter() - t0) / steps
+    value = n / dt
+    sample = (f"each step = fwd+bwd of the oracle port of loss_func.py ContrastiveLoss, fp32, 3 modalities, N={n} "
+              f"rows (bounded sample of the 32768-row workload, which the CPU path cannot hold in memory)")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "image-DNA-text 3-pair InfoNCE fwd+bwd, global batch 32768, 768-d", "sample_rows": n},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# native arm
+# ---------------------------------------------------------------------------------------------
+def run_native(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the bsc ops have no CPU path")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
+
+    import bsc
+    from bsc import _lib
+
+    n_global = args.n_global
+    assert n_global % world == 0, "global batch must divide over the ranks"
+    n_local = n_global // world
+    row0 = rank * n_local
+    feats, labels = synth_loss_rows(torch, n_global, row0, n_local, device, torch.bfloat16)
+    torch.cuda.empty_cache()
+    if world > 1:
+        crit = bsc.ClipLoss(rank=rank, world_size=world, criterion=torch.nn.CrossEntropyLoss(), precision="tc16")
+
+        def call(fs):
+            return crit(fs[0], fs[1], fs[2], labels, SCALE)
+    else:
+        crit = bsc.ContrastiveLoss(torch.nn.CrossEntropyLoss(), SCALE, precision="tc16")
+
+        def call(fs):
+            return crit(fs[0], fs[1], fs[2], labels)
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        leaves = [f.detach().requires_grad_(True) for f in feats]
+        loss = call(leaves)
+        loss.backward()
+        return loss, leaves
+
+    # ---------------- value: inputs resident in HBM ----------------
+    for _ in range(args.warmup):
+        step_resident()
+    barrier()
+    _lib.set_timing(True)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    fwd_ms, bwd_ms = [], []
+    _lib.launch_count(reset=True)
+    barrier()
+    t_wall0 = time.perf_counter()
+    for k in range(args.steps):
+        flush.zero_()  # L2 flush between timed iterations (outside the event pair)
+        if world > 1:
+            dist.barrier()
+        ev[k][0].record()
+        loss, leaves = step_resident()
+        ev[k][1].record()
+        ev[k][1].synchronize()
+        fwd_ms.append(_lib.last_kernel_ms(0))
+        bwd_ms.append(_lib.last_kernel_ms(1))
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    launches = _lib.launch_count(reset=True)  # kernels launched by libbsc_hot.so inside the timed loop
+    clocks = sampler.stop() if rank == 0 else None
+    _lib.set_timing(False)
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(total_ms.item())
+    ms_per_step = total_ms / args.steps
+    value = n_global / (ms_per_step * 1e-3)
+    loss_value = float(loss)
+
+    # ---------------- e2e: pinned host buffers in, loss + gradients out ----------------
+    host_in = [f.cpu().pin_memory() for f in feats]
+    host_lab = labels.cpu().pin_memory()
+    host_grad = [torch.empty_like(h).pin_memory() for h in host_in]
+    host_loss = torch.empty((), dtype=torch.float32).pin_memory()
+    dev_in = [torch.empty_like(f) for f in feats]
+    dev_lab = torch.empty_like(labels)
+    h2d = sum(h.numel() * h.element_size() for h in host_in) + host_lab.numel() * host_lab.element_size()
+    d2h = sum(h.numel() * h.element_size() for h in host_grad) + 4
+
+    def step_e2e():
+        for dst, src in zip(dev_in, host_in):
+            dst.copy_(src, non_blocking=True)
+        dev_lab.copy_(host_lab, non_blocking=True)
+        leaves = [t.detach().requires_grad_(True) for t in dev_in]
+        if world > 1:
+            loss = crit(leaves[0], leaves[1], leaves[2], dev_lab, SCALE)
+        else:
+            loss = crit(leaves[0], leaves[1], leaves[2], dev_lab)
+        loss.backward()
+        for dst, leaf in zip(host_grad, leaves):
+            dst.copy_(leaf.grad, non_blocking=True)
+        host_loss.copy_(loss.detach(), non_blocking=True)
+
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    e2e_ms = []
+    for k in range(e2e_steps):
+        flush.zero_()
+        if world > 1:
+            dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        step_e2e()
+        b.record()
+        b.synchronize()
+        e2e_ms.append(a.elapsed_time(b))
+    barrier()
+    e2e_total = torch.tensor([sum(e2e_ms)], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(e2e_total, op=dist.ReduceOp.MAX)
+    e2e_value = n_global / (float(e2e_total.item()) / e2e_steps * 1e-3)
+
+    # ---------------- roofline of the dominant kernel (backward sweep) ----------------
+    peaks = measured_peaks()
+    bwd_avg = sum(bwd_ms) / len(bwd_ms) if bwd_ms and min(bwd_ms) > 0 else None
+    fwd_avg = sum(fwd_ms) / len(fwd_ms) if fwd_ms and min(fwd_ms) > 0 else None
+    # algorithmic work of one launch on this rank: 2 gradient GEMMs per unordered pair, 3 pairs
+    bwd_flops = 12.0 * n_local * n_global * DIM
+    fwd_flops = 6.0 * n_local * n_global * DIM
+    roofline = None
+    if bwd_avg:
+        ach = bwd_flops / (bwd_avg * 1e-3) / 1e12
+        roofline = {"bound": "tensor", "kernel": "tc_bwd_kernel", "achieved": ach, "peak": peaks["tflops_sustained"],
+                    "unit": "TFLOP/s", "frac": ach / peaks["tflops_sustained"], "traffic": None,
+                    "peak_source": peaks["source"] + " bf16_tflops_sustained (kernel timed inside a long step)",
+                    "kernel_ms": bwd_avg, "fwd_kernel_ms": fwd_avg,
+                    "fwd_achieved": (fwd_flops / (fwd_avg * 1e-3) / 1e12) if fwd_avg else None,
+                    "step_achieved": 18.0 * n_local * n_global * DIM / (ms_per_step * 1e-3) / 1e12,
+                    "algorithmic_flops_per_launch": bwd_flops}
+
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": f"image-DNA-text 3-pair InfoNCE fwd+bwd, global batch {n_global}, 768-d, bf16 inputs, "
+                               f"labels=arange, all_gather over {world} rank(s)",
+                   "global_batch": n_global, "rows_per_gpu": n_local, "dim": DIM, "l2": "flushed between steps "
+                   "(256 MiB write outside the event pair)", "parallelism": f"rows{world}"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": e2e_steps},
+        "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks, "loss": loss_value,
+        "wall_s_timed_loop": t_wall,
+    }
+
+    # ---------------- second half of the metric: bank scan ----------------
+    if not args.no_retrieval:
+        try:
+            out["retrieval"] = bench_retrieval(args, torch, dist, bsc, _lib, device, rank, world, peaks)
+        except Exception as e:  # the loss line must survive a retrieval failure
+            out["retrieval"] = {"error": f"{type(e).__name__}: {e}"}
+
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_loss_baseline(CPU_SAMPLE_N)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def bench_retrieval(args, torch, dist, bsc, _lib, device, rank, world, peaks):
+    """cfg 4: 100k planted queries vs a 5M x 768 bf16 bank, rows sharded over the ranks; queries/s of the whole
+    job (mode B, tensor-bound) and GB/s of a 32-query pass (mode S, HBM-bound)."""
+    nb_total, nq = args.bank_rows, args.queries
+    nb = nb_total // world
+    base = rank * nb
+    g = torch.Generator(device=device).manual_seed(21 + rank)
+    bank = torch.empty((nb, DIM), dtype=torch.bfloat16, device=device)
+    for lo in range(0, nb, 262144):
+        hi = min(nb, lo + 262144)
+        bank[lo:hi] = torch.nn.functional.normalize(torch.randn(hi - lo, DIM, generator=g, device=device), dim=1)
+    gq = torch.Generator(device=device).manual_seed(99)
+    pi = torch.randint(0, nb_total, (nq,), generator=gq, device=device)
+    # planted neighbours: every rank builds the same queries from the owner rows (exchange through all_reduce)
+    q = torch.zeros((nq, DIM), dtype=torch.float32, device=device)
+    mine = (pi >= base) & (pi < base + nb)
+    q[mine] = bank[(pi[mine] - base)].float()
+    if world > 1:
+        dist.all_reduce(q)
+    q = torch.nn.functional.normalize(q + 0.3 / DIM ** 0.5 * torch.randn(nq, DIM, generator=gq, device=device), dim=1)
+    index = bsc.IndexFlatIP(DIM, precision="bf16", devices=[device], base_id=base)
+    index.add(bank)
+
+    def search(queries):
+        s, i = index.search_device(queries, 5)
+        if world > 1:
+            cs = [torch.empty_like(s) for _ in range(world)]
+            ci = [torch.empty_like(i) for _ in range(world)]
+            dist.all_gather(cs, s)
+            dist.all_gather(ci, i)
+            s, i = index._ops.topk_merge(torch.stack(cs), torch.stack(ci))
+        return s, i
+
+    _lib.set_timing(True)
+    res = {}
+    for name, queries, steps in (("bulk", q, 3), ("stream32", q[:32].contiguous(), 20)):
+        for _ in range(2):
+            search(queries)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        kms = []
+        for _ in range(steps):
+            s, i = search(queries)
+        b.record()
+        b.synchronize()
+        kms.append(_lib.last_kernel_ms(2))
+        ms = torch.tensor([a.elapsed_time(b) / steps], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms = float(ms.item())
+        nqq = queries.shape[0]
+        res[name] = {"queries": nqq, "ms_per_search": ms, "queries_per_s": nqq / (ms * 1e-3),
+                     "scan_kernel_ms": kms[-1],
+                     "scan_gbs_per_gpu": nb * DIM * 2 / (kms[-1] * 1e-3) / 1e9 if kms[-1] > 0 else None,
+                     "scan_tflops_per_gpu": 2.0 * nqq * nb * DIM / (kms[-1] * 1e-3) / 1e12 if kms[-1] > 0 else None}
+        if name == "bulk":
+            res[name]["top1_planted_hit_rate"] = float((i[:, 0] == pi).float().mean().item())
+    _lib.set_timing(False)
+    res["bank_rows_total"] = nb_total
+    res["bank_rows_per_gpu"] = nb
+    res["hbm_peak_gbs"] = peaks["hbm_gbs"]
+    return res
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_native(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -73,8 +73,12 @@ class IndexFlatIP:
             lo, hi = min(n, k * per), min(n, (k + 1) * per)
             if hi <= lo:
                 continue
-            part = _as_f32_tensor(x[lo:hi], dev)
-            self._chunks[k].append(part.to(self._dtype).contiguous())
+            rows = x[lo:hi]
+            if isinstance(rows, torch.Tensor) and rows.dtype == self._dtype:
+                part = rows.to(dev).contiguous()  # already in the bank's storage type: no float32 round trip
+            else:
+                part = _as_f32_tensor(rows, dev).to(self._dtype).contiguous()
+            self._chunks[k].append(part)
             self._bases[k].append(self._base_id + self.ntotal + lo)
         self.ntotal += n
 
