@@ -1,5 +1,6 @@
 // C ABI of libbsc_hot.so (see include/bsc_hot.h) and the host-side glue: argument checks, workspace
 // layout, tensor-map encoding, launch counting and the optional CUDA-event timing used by bench.py.
+#include <atomic>
 #include <cstring>
 #include <mutex>
 
@@ -12,10 +13,6 @@ int l2norm_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, voi
                   float* inv_norm, int zero_rule, cudaStream_t st);
 int label_stats_launch(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
                        cudaStream_t st);
-int class_sum_launch(const void* xh, int dtype, int64_t n, int d, const int32_t* rep, const int32_t* next,
-                     float* csum, cudaStream_t st);
-int pos_rows_launch(const PosArgs& a, int dtype, cudaStream_t st);
-int pos_reduce_launch(const float* posrow, int64_t n, float* out, cudaStream_t st);
 int loss_launch(const float* stats, const float* r, int64_t n, unsigned present_mask, float scale, float* loss,
                 cudaStream_t st);
 int uv_launch(const float* stats, const float* r, int64_t n, const float* rmax, int use_gs, float* uv, float* gsbuf,
@@ -27,11 +24,14 @@ void tc_fwd_tiling(int64_t n_local, int64_t n_global, int n_pairs, int* n_iblk, 
                    int* n_jchunk);
 
 // ---- thread-local state -----------------------------------------------------------------------
+// The error text is per thread.  Launch counter and timing slots are per process: torch runs the backward of
+// an autograd function on its own thread, and bench.py reads both from the main thread.
 static thread_local char g_err[512] = "";
-static thread_local int64_t g_launches = 0;
-static thread_local int g_timing = 0;
-static thread_local cudaEvent_t g_ev[3][2] = {{nullptr, nullptr}, {nullptr, nullptr}, {nullptr, nullptr}};
-static thread_local bool g_ev_valid[3] = {false, false, false};
+static std::atomic<int64_t> g_launches{0};
+static std::atomic<int> g_timing{0};
+static std::mutex g_ev_mutex;
+static cudaEvent_t g_ev[3][2] = {{nullptr, nullptr}, {nullptr, nullptr}, {nullptr, nullptr}};
+static bool g_ev_valid[3] = {false, false, false};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -49,6 +49,7 @@ void count_launch(int n) { g_launches += n; }
 
 void timing_begin(int which, cudaStream_t st) {
   if (!g_timing) return;
+  std::lock_guard<std::mutex> lock(g_ev_mutex);
   if (!g_ev[which][0]) {
     cudaEventCreate(&g_ev[which][0]);
     cudaEventCreate(&g_ev[which][1]);
@@ -57,6 +58,7 @@ void timing_begin(int which, cudaStream_t st) {
 }
 void timing_end(int which, cudaStream_t st) {
   if (!g_timing) return;
+  std::lock_guard<std::mutex> lock(g_ev_mutex);
   cudaEventRecord(g_ev[which][1], st);
   g_ev_valid[which] = true;
 }
@@ -131,11 +133,11 @@ InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p) {
     off += align_up(bytes, 256);
     return o;
   };
-  L.csum = take((size_t)3 * N * D * sizeof(float));
   L.uv = take((size_t)6 * N * sizeof(float));
   L.gs = take(4 * sizeof(float));
-  L.posrow = take((size_t)L.n_local_pad * sizeof(float));
   L.rowpart = take((size_t)3 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
+  L.rowpos = take((size_t)3 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
+  L.jrange = take((size_t)(L.n_jtile > 0 ? L.n_jtile : 1) * 2 * sizeof(int));
   L.colpart = take((size_t)3 * (L.n_iblk > 0 ? L.n_iblk : 1) * L.n_global_pad * sizeof(float));
   L.dxraw = take((size_t)3 * 2 * (n > 0 ? n : 1) * D * sizeof(float));
   L.gscratch = (p->mode == BSC_MODE_F32) ? take((size_t)L.g_rows * N * sizeof(float)) : off;
@@ -182,6 +184,7 @@ int bsc_set_timing(int enabled) {
 }
 
 float bsc_last_kernel_ms(int which) {
+  std::lock_guard<std::mutex> lock(g_ev_mutex);
   if (which < 0 || which > 2 || !g_ev_valid[which]) return -1.0f;
   if (cudaEventSynchronize(g_ev[which][1]) != cudaSuccess) return -1.0f;
   float ms = -1.0f;
@@ -190,9 +193,7 @@ float bsc_last_kernel_ms(int which) {
 }
 
 int64_t bsc_launch_count(int reset) {
-  int64_t v = g_launches;
-  if (reset) g_launches = 0;
-  return v;
+  return reset ? g_launches.exchange(0) : g_launches.load();
 }
 
 int bsc_l2norm_fwd(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, int y16_dtype, float* y32,
@@ -232,27 +233,7 @@ int bsc_infonce_fwd(const bsc_infonce_desc* p, float* stats, void* workspace, si
   cudaStream_t st = (cudaStream_t)stream;
   char* ws = (char*)workspace;
   const int64_t N = p->n_global;
-  const int xdt = p->mode == BSC_MODE_F32 ? BSC_F32 : BSC_F16;
   BSC_CUDA(cudaMemsetAsync(stats, 0, (size_t)bsc_infonce_stats_len(N) * sizeof(float), st));
-  // class sums (all rows: classes span ranks) and the positive term of the local rows
-  PosArgs pa{};
-  for (int m = 0; m < 3; ++m) {
-    pa.xh[m] = p->xh[m];
-    pa.csum[m] = (const float*)(ws + L.csum) + (size_t)m * N * p->d;
-    if (p->xh[m]) {
-      rc = class_sum_launch(p->xh[m], xdt, N, p->d, p->rep, p->next, (float*)pa.csum[m], st);
-      if (rc) return rc;
-    }
-  }
-  pa.rep = p->rep;
-  pa.posrow = (float*)(ws + L.posrow);
-  pa.row0 = p->row0;
-  pa.n_local = p->n_local;
-  pa.d = p->d;
-  rc = pos_rows_launch(pa, xdt, st);
-  if (rc) return rc;
-  rc = pos_reduce_launch(pa.posrow, p->n_local, stats + 6 * N, st);
-  if (rc) return rc;
   if (p->n_local == 0) return BSC_OK;
   if (p->mode == BSC_MODE_F32) return simt_fwd_stats(p, L, ws, stats, st);
   return tc_fwd_stats(p, L, ws, stats, st);
@@ -294,9 +275,7 @@ int bsc_infonce_bwd(const bsc_infonce_desc* p, const float* stats, const void* c
     ca.x[a] = p->xh[a] ? x[a] : nullptr;
     ca.grad[a] = p->xh[a] ? grad[a] : nullptr;
     ca.raw[a] = (const float*)(ws + L.dxraw) + (size_t)a * 2 * p->n_local * p->d;
-    ca.csum[a] = (const float*)(ws + L.csum) + (size_t)a * N * p->d;
   }
-  ca.rep = p->rep;
   ca.gsbuf = (const float*)(ws + L.gs);
   ca.grad_out = grad_out;
   ca.row0 = p->row0;

@@ -43,18 +43,19 @@ void count_launch(int n = 1);
 // Ordered pair (a,b), a != b, of modality slots 0..2 -> 0..5.
 __host__ __device__ inline int pair_id(int a, int b) { return a * 2 + (b > a ? b - 1 : b); }
 
-constexpr int kStatsExtra = 4;  // scalars after the 6*N sum-exp rows; [0] = sum_ij T_ij S_ij / s (local part)
+constexpr int kStatsExtra = 4;  // scalars after the 6*N sum-exp rows; [0] = sum over unordered pairs and local rows of
+                                // sum_j T_ij (s*S_ij - s)
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 // ---- workspace layout of the infonce calls -----------------------------------------------------
 struct InfoNceWs {
-  size_t csum;      // float [3][N][D]       class sums of normalised rows
   size_t uv;        // float [6][N]          r_i / sumexp
   size_t gs;        // float [4]             {gs, 1/gs}
-  size_t posrow;    // float [n_local]
-  size_t rowpart;   // float [3][n_jchunk][n_local_pad]
+  size_t rowpart;   // float [3][n_jchunk][n_local_pad]   row sum-exp partials
+  size_t rowpos;    // float [3][n_jchunk][n_local_pad]   positive-pair partials
   size_t colpart;   // float [3][n_iblk][N_pad]
+  size_t jrange;    // int2  [n_jtile]       label-class range of every column tile
   size_t dxraw;     // float [3][2][n_local][D]
   size_t gscratch;  // float [g_rows][N]     fp32 mode only
   size_t total;
@@ -67,21 +68,10 @@ InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p);
 
 
 // ---- argument blocks of the O(N*D) kernels in prep.cu ----------------------------------------------
-struct PosArgs {
-  const void* xh[3];
-  const float* csum[3];
-  const int32_t* rep;
-  float* posrow;
-  int64_t row0, n_local;
-  int d;
-};
-
 struct CombineArgs {
   const void* x[3];      // original local rows (un-normalised), null when the modality is absent
   void* grad[3];
   const float* raw[3];   // [2][n_local][d] per modality
-  const float* csum[3];  // [N][d]
-  const int32_t* rep;
   const float* gsbuf;
   const float* grad_out;
   int64_t row0, n_local, n_global, ldx;

@@ -144,92 +144,70 @@ int label_stats_launch(const int64_t* labels, int64_t n, float* r, int32_t* rep,
 }
 
 // ---------------------------------------------------------------------------------------------
-// Class sums: csum[m][i][:] = sum over the label class of i of xh_m rows, stored at the class
-// representative only, accumulated in index order (deterministic).  With labels = arange this is a copy.
+// Label-class range of every column tile: out[t] = {min, max} of rep over rows [t*tile, (t+1)*tile).
+// The sweeps use it to skip the label compare on tiles that cannot contain a positive pair.
 // ---------------------------------------------------------------------------------------------
-template <typename T>
-__global__ void __launch_bounds__(256) class_sum_kernel(const T* __restrict__ xh, int64_t n, int d,
-                                                        const int32_t* __restrict__ rep,
-                                                        const int32_t* __restrict__ next, float* __restrict__ csum) {
-  const int64_t i = blockIdx.x;
-  if (rep[i] != (int32_t)i) return;
-  for (int c0 = threadIdx.x; c0 < d; c0 += blockDim.x) {
-    float acc = 0.f;
-    for (int64_t j = i; j >= 0; j = next[j]) acc += to_f32<T>(xh[j * (int64_t)d + c0]);
-    csum[i * (int64_t)d + c0] = acc;
-  }
-}
-
-int class_sum_launch(const void* xh, int dtype, int64_t n, int d, const int32_t* rep, const int32_t* next,
-                     float* csum, cudaStream_t st) {
-  if (n == 0) return BSC_OK;
-  if (dtype == BSC_F32)
-    class_sum_kernel<float><<<(unsigned)n, 256, 0, st>>>((const float*)xh, n, d, rep, next, csum);
-  else if (dtype == BSC_F16)
-    class_sum_kernel<__half><<<(unsigned)n, 256, 0, st>>>((const __half*)xh, n, d, rep, next, csum);
-  else
-    class_sum_kernel<__nv_bfloat16><<<(unsigned)n, 256, 0, st>>>((const __nv_bfloat16*)xh, n, d, rep, next, csum);
-  BSC_LAUNCH_CHECK("class_sum_kernel");
-  return BSC_OK;
-}
-
-// ---------------------------------------------------------------------------------------------
-// Positive-pair term for the local rows: posrow[i] = sum_{x} sum_{y != x} <xh_x[i], csum_y[rep_i]>
-// (= sum_j T_ij S_ij / s summed over the ordered pairs).  One warp per row.
-// ---------------------------------------------------------------------------------------------
-
-template <typename T>
-__global__ void __launch_bounds__(256) pos_rows_kernel(PosArgs a) {
-  const int lane = threadIdx.x & 31;
-  const int64_t il = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (il >= a.n_local) return;
-  const int64_t i = a.row0 + il;
-  const int64_t ri = a.rep[i];
-  float acc = 0.f;
-  for (int c = lane; c < a.d; c += 32) {
-    float xs[3], cs[3];
-#pragma unroll
-    for (int m = 0; m < 3; ++m) {
-      xs[m] = a.xh[m] ? to_f32<T>(((const T*)a.xh[m])[i * (int64_t)a.d + c]) : 0.f;
-      cs[m] = a.xh[m] ? a.csum[m][ri * (int64_t)a.d + c] : 0.f;
+__global__ void __launch_bounds__(256) rep_range_kernel(const int32_t* __restrict__ rep, int64_t n, int tile,
+                                                        int2* __restrict__ out) {
+  __shared__ int smin[8], smax[8];
+  const int64_t base = (int64_t)blockIdx.x * tile;
+  int lo = 0x7fffffff, hi = -1;
+  for (int t = threadIdx.x; t < tile; t += blockDim.x) {
+    const int64_t j = base + t;
+    if (j < n) {
+      const int v = rep[j];
+      lo = min(lo, v);
+      hi = max(hi, v);
     }
-    const float ct = cs[0] + cs[1] + cs[2];
-#pragma unroll
-    for (int m = 0; m < 3; ++m) acc = fmaf(xs[m], ct - cs[m], acc);
   }
-  acc = warp_sum(acc);
-  if (lane == 0) a.posrow[il] = acc;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    smin[threadIdx.x >> 5] = lo;
+    smax[threadIdx.x >> 5] = hi;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) {
+      lo = min(lo, smin[w]);
+      hi = max(hi, smax[w]);
+    }
+    out[blockIdx.x] = make_int2(lo, hi);
+  }
 }
 
-int pos_rows_launch(const PosArgs& a, int dtype, cudaStream_t st) {
-  if (a.n_local == 0) return BSC_OK;
-  dim3 grid((unsigned)((a.n_local + 7) / 8));
-  if (dtype == BSC_F32)
-    pos_rows_kernel<float><<<grid, 256, 0, st>>>(a);
-  else
-    pos_rows_kernel<__half><<<grid, 256, 0, st>>>(a);
-  BSC_LAUNCH_CHECK("pos_rows_kernel");
+int rep_range_launch(const int32_t* rep, int64_t n, int tile, int2* out, cudaStream_t st) {
+  if (n == 0) return BSC_OK;
+  rep_range_kernel<<<(unsigned)((n + tile - 1) / tile), 256, 0, st>>>(rep, n, tile, out);
+  BSC_LAUNCH_CHECK("rep_range_kernel");
   return BSC_OK;
 }
 
-// Deterministic single-block sum (double accumulation) of posrow into stats extra slot 0.
-__global__ void __launch_bounds__(1024) pos_reduce_kernel(const float* __restrict__ posrow, int64_t n,
-                                                          float* __restrict__ out) {
+// Deterministic single-block sum (double accumulation, fixed order) of nparts rows of n floats:
+// out[0] = scale * sum_p sum_{i<n} part[p*stride + i].
+__global__ void __launch_bounds__(1024) sum_rows_kernel(const float* __restrict__ part, int nparts,
+                                                        int64_t part_stride, int64_t n, float scale,
+                                                        float* __restrict__ out) {
   __shared__ double sh[1024];
   double acc = 0.0;
-  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) acc += (double)posrow[i];
+  for (int p = 0; p < nparts; ++p)
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) acc += (double)part[p * part_stride + i];
   sh[threadIdx.x] = acc;
   __syncthreads();
   for (int s = 512; s > 0; s >>= 1) {
     if ((int)threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
     __syncthreads();
   }
-  if (threadIdx.x == 0) out[0] = (float)sh[0];
+  if (threadIdx.x == 0) out[0] = (float)((double)scale * sh[0]);
 }
 
-int pos_reduce_launch(const float* posrow, int64_t n, float* out, cudaStream_t st) {
-  pos_reduce_kernel<<<1, 1024, 0, st>>>(posrow, n, out);
-  BSC_LAUNCH_CHECK("pos_reduce_kernel");
+int sum_rows_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float scale, float* out,
+                    cudaStream_t st) {
+  sum_rows_kernel<<<1, 1024, 0, st>>>(part, nparts, part_stride, n, scale, out);
+  BSC_LAUNCH_CHECK("sum_rows_kernel");
   return BSC_OK;
 }
 
@@ -255,8 +233,9 @@ int reduce_parts_launch(const float* part, int nparts, int64_t part_stride, int6
 }
 
 // ---------------------------------------------------------------------------------------------
-// Loss scalar (loss_func.py:54): c * [ sum_pairs sum_i r_i (s + log sumexp_i) - s * pos ],
-// c = 1 / (N * M(M-1)).  Single block, double accumulation, fixed order.
+// Loss scalar (loss_func.py:54).  With a_ij = s*S_ij - s and sumexp_i = sum_j exp(a_ij):
+//   L = c * [ sum over ordered pairs sum_i r_i log(sumexp_i)  -  2 * sum over unordered pairs sum_ij T_ij a_ij ],
+// c = 1 / (N * M(M-1))  (r_i*s cancels against the s inside a_ij).  Single block, double accumulation, fixed order.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024) loss_kernel(const float* __restrict__ stats, const float* __restrict__ r,
                                                     int64_t n, unsigned present_mask, float scale,
@@ -271,7 +250,7 @@ __global__ void __launch_bounds__(1024) loss_kernel(const float* __restrict__ st
       if (b == a || !((present_mask >> b) & 1)) continue;
       const float* se = stats + (int64_t)pair_id(a, b) * n;
       for (int64_t i = threadIdx.x; i < n; i += blockDim.x)
-        acc += (double)r[i] * ((double)scale + (double)logf(se[i]));
+        acc += (double)r[i] * (double)logf(se[i]);
     }
   }
   sh[threadIdx.x] = acc;
@@ -283,7 +262,8 @@ __global__ void __launch_bounds__(1024) loss_kernel(const float* __restrict__ st
   if (threadIdx.x == 0) {
     const double pos = (double)stats[6 * n];
     const double c = 1.0 / ((double)n * m * (m - 1));
-    loss[0] = (float)(c * (sh[0] - (double)scale * pos));
+    loss[0] = (float)(c * (sh[0] - 2.0 * pos));
+    (void)scale;
   }
 }
 
@@ -324,7 +304,8 @@ int uv_launch(const float* stats, const float* r, int64_t n, const float* rmax, 
 
 // ---------------------------------------------------------------------------------------------
 // K6: combine the raw sweep output with the positive term and chain through F.normalize:
-//   ghat = c*s*( (raw0+raw1)/gs - 2*sum_{y!=x} csum_y[rep_i] ),  dx = gout * (ghat - xhat <xhat,ghat>) / ||x||
+//   ghat = c*s*(raw0+raw1)/gs   (the -2*T_ij term is already inside the sweep's weights),
+//   dx = gout * (ghat - xhat <xhat,ghat>) / ||x||
 // One warp per (row, modality).
 // ---------------------------------------------------------------------------------------------
 
@@ -340,7 +321,6 @@ __global__ void __launch_bounds__(256) combine_kernel(CombineArgs a) {
   const float cs = c * a.scale;
   const float inv_gs = a.gsbuf[1];
   const float gout = a.grad_out[0];
-  const int64_t ri = a.rep[a.row0 + il];
   const T* xr = (const T*)a.x[m] + il * a.ldx;
   T* gr = (T*)a.grad[m] + il * a.ldx;
   const float* raw0 = a.raw[m] + il * (int64_t)a.d;
@@ -359,11 +339,7 @@ __global__ void __launch_bounds__(256) combine_kernel(CombineArgs a) {
   auto ghat_at = [&](int cidx) -> float {
     float raw = raw0[cidx];
     if (a.n_slots > 1) raw += raw1[cidx];
-    float w = 0.f;
-#pragma unroll
-    for (int y = 0; y < 3; ++y)
-      if (y != m && ((a.present_mask >> y) & 1)) w += a.csum[y][ri * (int64_t)a.d + cidx];
-    return cs * (raw * inv_gs - 2.0f * w);
+    return cs * (raw * inv_gs);
   };
 
   float dot = 0.f;

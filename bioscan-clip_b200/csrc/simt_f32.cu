@@ -7,6 +7,8 @@
 namespace bsc {
 
 int reduce_parts_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float* out, cudaStream_t st);
+int sum_rows_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float scale, float* out,
+                    cudaStream_t st);
 
 namespace {
 
@@ -81,6 +83,8 @@ struct SimArgs {
   // forward outputs
   float* rowpart;  // [n_jtile][n_local_pad]
   float* colpart;  // [n_iblk][n_global_pad]
+  float* rowpos;   // [n_jtile][n_local_pad]  sum_j T_ij (s*S_ij - s) of the tile
+  const int32_t* rep;  // [N] label class representative: T_ij = (rep[i] == rep[j])
   int64_t n_local_pad, n_global_pad;
   // G outputs
   const float* u;  // [N] weights of the row side
@@ -104,14 +108,30 @@ __global__ void __launch_bounds__(256) simt_sim_kernel(SimArgs a) {
   // rows are addressed in the global batch: row0 + local
   tile_gemm<false>(a.xa, a.d, a.row0 + a.n_local, a.row0 + il0, a.xb, a.d, a.n_global, j0, a.d, acc, As, Bs);
 
+  // label classes of the thread's rows and columns; -2 / -1 never match
+  int repr[4], repc[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int64_t il = il0 + ty * 4 + r;
+    repr[r] = il < a.n_local ? a.rep[a.row0 + il] : -2;
+  }
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const int64_t j = j0 + tx * 4 + c;
+    repc[c] = j < a.n_global ? a.rep[j] : -1;
+  }
   float e[4][4];
+  float pos[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
   for (int r = 0; r < 4; ++r)
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
       const int64_t il = il0 + ty * 4 + r, j = j0 + tx * 4 + c;
       const bool ok = il < a.n_local && j < a.n_global;
-      e[r][c] = ok ? expf(fmaf(a.scale, acc[r][c], -a.scale)) : 0.f;
+      const float lg = fmaf(a.scale, acc[r][c], -a.scale);
+      e[r][c] = ok ? expf(lg) : 0.f;
+      // the positive term uses the very logit that enters the exponential (cancels like log_softmax)
+      if (repr[r] == repc[c]) pos[r] += lg;
     }
 
   if constexpr (WRITE_G) {
@@ -123,7 +143,8 @@ __global__ void __launch_bounds__(256) simt_sim_kernel(SimArgs a) {
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         const int64_t j = j0 + tx * 4 + c;
-        if (j < a.n_global) a.g[(il - a.g_row0) * a.n_global + j] = e[r][c] * (ui + a.v[j]);
+        if (j < a.n_global)
+          a.g[(il - a.g_row0) * a.n_global + j] = fmaf(e[r][c], ui + a.v[j], repr[r] == repc[c] ? -2.0f : 0.0f);
       }
     }
     return;
@@ -132,10 +153,17 @@ __global__ void __launch_bounds__(256) simt_sim_kernel(SimArgs a) {
 #pragma unroll
   for (int r = 0; r < 4; ++r) {
     float s = (e[r][0] + e[r][1]) + (e[r][2] + e[r][3]);
+    float ps = pos[r];
 #pragma unroll
-    for (int o = 8; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    for (int o = 8; o > 0; o >>= 1) {
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+      ps += __shfl_xor_sync(0xffffffffu, ps, o);
+    }
     const int64_t il = il0 + ty * 4 + r;
-    if (tx == 0 && il < a.n_local) a.rowpart[(int64_t)blockIdx.x * a.n_local_pad + il] = s;
+    if (tx == 0 && il < a.n_local) {
+      a.rowpart[(int64_t)blockIdx.x * a.n_local_pad + il] = s;
+      a.rowpos[(int64_t)blockIdx.x * a.n_local_pad + il] = ps;
+    }
   }
   // column sums: over the thread's 4 rows, then over ty through shared memory
 #pragma unroll
@@ -245,6 +273,7 @@ __global__ void topk_init_kernel(float* s, int64_t* i, int64_t n) {
 int simt_fwd_stats(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, float* stats, cudaStream_t st) {
   const int64_t N = p->n_global;
   int pair = 0;
+  int npairs_done = 0;
   for (int a = 0; a < 3; ++a)
     for (int b = a + 1; b < 3; ++b, ++pair) {
       if (!p->xh[a] || !p->xh[b]) continue;
@@ -259,6 +288,8 @@ int simt_fwd_stats(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, floa
       s.n_local_pad = L.n_local_pad;
       s.n_global_pad = L.n_global_pad;
       s.rowpart = (float*)(ws + L.rowpart) + (int64_t)pair * L.n_jchunk * L.n_local_pad;
+      s.rowpos = (float*)(ws + L.rowpos) + (int64_t)pair * L.n_jchunk * L.n_local_pad;
+      s.rep = p->rep;
       s.colpart = (float*)(ws + L.colpart) + (int64_t)pair * L.n_iblk * L.n_global_pad;
       dim3 grid((unsigned)L.n_jtile, (unsigned)L.n_iblk);
       simt_sim_kernel<false><<<grid, 256, 0, st>>>(s);
@@ -268,8 +299,13 @@ int simt_fwd_stats(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, floa
       if (rc) return rc;
       rc = reduce_parts_launch(s.colpart, L.n_iblk, L.n_global_pad, N, stats + (int64_t)pair_id(b, a) * N, st);
       if (rc) return rc;
+      // compact the positive partials of this pair into slot `npairs_done` so one sum covers all pairs
+      rc = reduce_parts_launch(s.rowpos, L.n_jchunk, L.n_local_pad, p->n_local,
+                               (float*)(ws + L.rowpart) + (int64_t)npairs_done * L.n_local_pad, st);
+      if (rc) return rc;
+      ++npairs_done;
     }
-  return BSC_OK;
+  return sum_rows_launch((float*)(ws + L.rowpart), npairs_done, L.n_local_pad, p->n_local, 1.0f, stats + 6 * N, st);
 }
 
 int simt_bwd_raw(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st) {
@@ -292,6 +328,7 @@ int simt_bwd_raw(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaSt
         s.row0 = p->row0;
         s.d = p->d;
         s.scale = p->logit_scale;
+        s.rep = p->rep;
         s.u = uv + (int64_t)pair_id(x, y) * N;
         s.v = uv + (int64_t)pair_id(y, x) * N;
         s.g = g;

@@ -1,8 +1,10 @@
 // tcgen05 InfoNCE backward sweep (the autograd of loss_func.py:46-51 without the N x N matrices).
 //
 // For an ordered modality pair (x, y) and the local row block I (128 rows):
-//     dXhat_x[I, :] (+)= sum_J  G[I, J] * Yhat[J, :],    G = gs * exp(s*S - s) * (u_i + v_j),  S = Xhat_I Yhat_J^T
-// with u_i = r_i / sumexp_xy[i], v_j = r_j / sumexp_yx[j] (softmax rows and columns share one exp).
+//     dXhat_x[I, :] (+)= sum_J  G[I, J] * Yhat[J, :],    G = gs * (exp(s*S - s) * (u_i + v_j) - 2 T_ij),  S = Xhat_I Yhat_J^T
+// with u_i = r_i / sumexp_xy[i], v_j = r_j / sumexp_yx[j] (softmax rows and columns share one exp) and
+// T_ij = [label_i == label_j].  The target is subtracted BEFORE the tile is rounded to fp16: for a peaked softmax
+// r_i P_ij - T_ij cancels to ~1e-3 of its terms, which a 11-bit operand could not represent after the fact.
 //
 // One CTA owns (x, y, I, column chunk of D): TMEM holds the chunk accumulator (<= 384 fp32 columns) plus one
 // 128 x 128 S tile.  Per column tile J: S is recomputed on the tensor cores (K = D), the epilogue warps turn
@@ -40,6 +42,7 @@ struct BwdParams {
   int64_t n_global, n_local, row0;
   float k1, k2;
   const float* uv;     // [6][N]
+  const int32_t* rep;  // [N] label class representative: T_ij = (rep[i] == rep[j])
   const float* gsbuf;  // {gs, 1/gs}
   float* dxraw;        // [3][2][n_local][d]
 };
@@ -53,9 +56,11 @@ struct __align__(8) BwdSmemTail {
   uint32_t tmem_base;
   uint32_t pad;
   float vgs[2][BN];  // gs * v_j of the current / next column tile
+  int repj[2][BN];   // label class of the tile's columns (-1 past the end of the batch)
 };
 
-constexpr size_t BWD_SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + 2 * (size_t)G_BYTES + sizeof(BwdSmemTail);
+// dynamic shared memory starts 1024-byte aligned (no static __shared__ in this kernel; checked at run time)
+constexpr size_t BWD_SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 2 * (size_t)G_BYTES + sizeof(BwdSmemTail);
 static_assert(BWD_SMEM_BYTES <= 232448, "backward kernel exceeds the 227 KB shared-memory limit");
 
 __device__ __forceinline__ void decode_item(const BwdParams& p, int item, int& xy, int& iblk, int& chunk) {
@@ -71,10 +76,13 @@ __device__ __forceinline__ int chunk_groups(const BwdParams& p, int chunk) {
 }
 
 __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ BwdParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t raw_addr = ptx::smem_u32(smem_raw);
-  const uint32_t ring = (raw_addr + 1023u) & ~1023u;
-  uint8_t* ring_ptr = smem_raw + (ring - raw_addr);
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t ring = ptx::smem_u32(smem_raw);
+  if ((ring & 1023u) != 0) {
+    if (threadIdx.x == 0) printf("bsc: dynamic shared memory is not 1024-byte aligned (0x%x)\n", ring);
+    __trap();
+  }
+  uint8_t* ring_ptr = smem_raw;
   const uint32_t gbuf = ring + STAGES * STAGE_BYTES;
   uint8_t* gbuf_ptr = ring_ptr + (size_t)STAGES * STAGE_BYTES;
   BwdSmemTail* tail = reinterpret_cast<BwdSmemTail*>(gbuf_ptr + 2 * (size_t)G_BYTES);
@@ -259,6 +267,8 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
       const int64_t arow = (int64_t)iblk * BM + row_in_tile;
       const bool row_ok = arow < p.n_local;
       const float ugs = row_ok ? gs * p.uv[(int64_t)pair_id(x, y) * p.n_global + p.row0 + arow] : 0.f;
+      const int rep_i = row_ok ? p.rep[p.row0 + arow] : -2;
+      const float two_gs = 2.0f * gs;
       const float* vrow = p.uv + (int64_t)pair_id(y, x) * p.n_global;
       const int ng = chunk_groups(p, chunk);
 
@@ -269,6 +279,7 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
         {
           const int64_t j = (int64_t)t * BN + et;
           tail->vgs[buf][et] = (j < p.n_global) ? gs * vrow[j] : 0.f;
+          tail->repj[buf][et] = (j < p.n_global) ? p.rep[j] : -1;
         }
         ptx::named_bar_sync(1, 128);
         ptx::mbar_wait(ptx::smem_u32(&tail->s_full), tile_count & 1u, 400);
@@ -292,6 +303,7 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
             if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tail->s_free));
           }
           const float* vg = &tail->vgs[buf][h * 64];
+          const int* rj = &tail->repj[buf][h * 64];
 #pragma unroll
           for (int u = 0; u < 8; ++u) {  // 16-byte units of 8 columns
             uint32_t pk[4];
@@ -300,8 +312,9 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
               const int c = u * 8 + w * 2;
               const float a0 = __uint_as_float(c < 32 ? r0[c & 31] : r1[c & 31]);
               const float a1 = __uint_as_float(c + 1 < 32 ? r0[(c + 1) & 31] : r1[(c + 1) & 31]);
-              const float g0 = ptx::ex2(fmaf(a0, p.k1, -p.k2)) * (ugs + vg[c]);
-              const float g1 = ptx::ex2(fmaf(a1, p.k1, -p.k2)) * (ugs + vg[c + 1]);
+              const float g0 = fmaf(ptx::ex2(fmaf(a0, p.k1, -p.k2)), ugs + vg[c], rj[c] == rep_i ? -two_gs : 0.f);
+              const float g1 =
+                  fmaf(ptx::ex2(fmaf(a1, p.k1, -p.k2)), ugs + vg[c + 1], rj[c + 1] == rep_i ? -two_gs : 0.f);
               const __half2 hh = __floats2half2_rn(g0, g1);
               pk[w] = *reinterpret_cast<const uint32_t*>(&hh);
             }
@@ -408,6 +421,7 @@ int tc_bwd_raw(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
   p.k1 = d->logit_scale * log2e;
   p.k2 = d->logit_scale * log2e;
   p.uv = (const float*)(ws + L.uv);
+  p.rep = d->rep;
   p.gsbuf = (const float*)(ws + L.gs);
   p.dxraw = (float*)(ws + L.dxraw);
   if (p.num_items == 0 || p.n_jtile == 0) return BSC_OK;

@@ -9,6 +9,9 @@
 namespace bsc {
 
 int reduce_parts_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float* out, cudaStream_t st);
+int rep_range_launch(const int32_t* rep, int64_t n, int tile, int2* out, cudaStream_t st);
+int sum_rows_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float scale, float* out,
+                    cudaStream_t st);
 int topk_merge_launch(const float* cs, const int64_t* ci, int parts, int64_t nq, int k, float* os, int64_t* oi,
                       cudaStream_t st);
 
@@ -41,6 +44,9 @@ struct SimParams {
   float k1, k2;      // exp(s*x - s) = ex2(x*k1 - k2)
   float* rowpart;    // [pair][jchunk][a_pad]
   float* colpart;    // [pair][iblk][b_pad]
+  float* rowpos;     // [pair][jchunk][a_pad]  sum_j T_ij * (S_ij*k1 - k2)   (log2 units)
+  const int32_t* rep;   // [b_rows] class representative of every row of the global batch (T_ij = rep_i == rep_j)
+  const int2* jrange;   // [n_jtile] {min, max} of rep over the columns of a tile
   int64_t a_pad, b_pad;
   // EPI_TOPK
   int k;
@@ -203,6 +209,19 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
       const int jt_end = min(p.n_jtile, (jchunk + 1) * p.jpc);
 
       float rowsum = 0.f;
+      float rowpos = 0.f;
+      int rep_i = -2, wmin = 0, wmax = -1;
+      if (EPI == EPI_STATS) {
+        // label class of this thread's row and the class range of the warp's 32 rows
+        if (row_ok) rep_i = p.rep[p.a_row0 + arow];
+        wmin = row_ok ? rep_i : 0x7fffffff;
+        wmax = row_ok ? rep_i : -1;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          wmin = min(wmin, __shfl_xor_sync(0xffffffffu, wmin, o));
+          wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+        }
+      }
       float ts[KTOP];
       int ti[KTOP];
       if (EPI == EPI_TOPK) {
@@ -222,6 +241,11 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
         const bool edge = (col0 + BN > p.b_rows) || ((int64_t)iblk * BM + BM > p.a_rows);
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN;
         float* cs = tail->cs[buf][q];
+        bool tile_pos = false;  // can any (row of this warp, column of this tile) pair share a label?
+        if (EPI == EPI_STATS) {
+          const int2 jr = p.jrange[jt];
+          tile_pos = (wmax >= jr.x) && (wmin <= jr.y);
+        }
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
           uint32_t raw[32];
@@ -229,8 +253,22 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
           ptx::tmem_ld_wait();
           if (EPI == EPI_STATS) {
             float e[32];
+            if (tile_pos) {
+              // positive-pair term from the very logits that enter the exponentials, so that the
+              // r_i*log(sumexp_i) - sum_j T_ij a_ij difference cancels like log_softmax does
+              const int64_t jcol = col0 + c * 32 + lane;
+              const int repv = jcol < p.b_rows ? p.rep[jcol] : -1;
 #pragma unroll
-            for (int t = 0; t < 32; ++t) e[t] = ptx::ex2(fmaf(__uint_as_float(raw[t]), p.k1, -p.k2));
+              for (int t = 0; t < 32; ++t) {
+                const float a = fmaf(__uint_as_float(raw[t]), p.k1, -p.k2);
+                const int rj = __shfl_sync(0xffffffffu, repv, t);
+                rowpos += (rj == rep_i) ? a : 0.f;
+                e[t] = ptx::ex2(a);
+              }
+            } else {
+#pragma unroll
+              for (int t = 0; t < 32; ++t) e[t] = ptx::ex2(fmaf(__uint_as_float(raw[t]), p.k1, -p.k2));
+            }
             if (edge) {
 #pragma unroll
               for (int t = 0; t < 32; ++t) {
@@ -289,7 +327,10 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
       }
 
       if (EPI == EPI_STATS) {
-        if (row_ok) p.rowpart[((int64_t)pair * p.n_jchunk + jchunk) * p.a_pad + arow] = rowsum;
+        if (row_ok) {
+          p.rowpart[((int64_t)pair * p.n_jchunk + jchunk) * p.a_pad + arow] = rowsum;
+          p.rowpos[((int64_t)pair * p.n_jchunk + jchunk) * p.a_pad + arow] = rowpos;
+        }
       } else {
         if (row_ok) {
           const int64_t o = ((int64_t)jchunk * p.a_rows + arow) * p.k;
@@ -393,11 +434,20 @@ int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, float*
   p.k2 = d->logit_scale * log2e;
   p.rowpart = (float*)(ws + L.rowpart);
   p.colpart = (float*)(ws + L.colpart);
+  p.rowpos = (float*)(ws + L.rowpos);
+  p.rep = d->rep;
+  p.jrange = (const int2*)(ws + L.jrange);
   p.a_pad = L.n_local_pad;
   p.b_pad = L.n_global_pad;
+  int rc = rep_range_launch(d->rep, d->n_global, BN, (int2*)(ws + L.jrange), st);
+  if (rc) return rc;
   timing_begin(0, st);
-  int rc = launch_sim<EPI_STATS, 0>(p, st);
+  rc = launch_sim<EPI_STATS, 0>(p, st);
   timing_end(0, st);
+  if (rc) return rc;
+  // sum_ij T_ij (s*S_ij - s) over the local rows and all pairs, in natural-log units
+  rc = sum_rows_launch(p.rowpos, np * L.n_jchunk, L.n_local_pad, d->n_local, 0.6931471805599453f,
+                       stats + 6 * d->n_global, st);
   if (rc) return rc;
   for (int q = 0; q < np; ++q) {
     const int a = p.pair_a[q], b = p.pair_b[q];

@@ -107,8 +107,9 @@ int bsc_infonce_workspace_bytes(const bsc_infonce_desc* p, size_t* bytes);
 
 /* Forward sweep.  stats (bsc_infonce_stats_len floats, overwritten) receives, for every ordered pair
  * (a,b) of present modalities, sum_j exp(S_ab[i,j] - s) for the rows this rank can complete and the
- * PARTIAL column sums over its local rows, plus the local part of sum_i sum_j T_ij S_ij.  With more
- * than one rank the caller sums `stats` over ranks (one all_reduce) before the next two calls.   */
+ * PARTIAL column sums over its local rows, plus (slot 6*n_global) the local part of
+ * sum over unordered pairs sum_ij T_ij (S_ab[i,j] - s), taken from the same logits as the exponentials.
+ * With more than one rank the caller sums `stats` over ranks (one all_reduce) before the next two calls. */
 int bsc_infonce_fwd(const bsc_infonce_desc* p, float* stats, void* workspace, size_t workspace_bytes,
                     void* stream);
 

@@ -37,12 +37,12 @@ class FakeOps:
                 e = torch.exp(p.scale * p.xh[a][sl] @ p.xh[b].T - p.scale)
                 stats[pair_id(a, b) * n + p.row0: pair_id(a, b) * n + p.row0 + p.n_local] = e.sum(1)
                 stats[pair_id(b, a) * n: pair_id(b, a) * n + n] += e.sum(0)
-        pos = 0.0
+        pos = 0.0  # sum over unordered pairs and local rows of sum_j T_ij (s*S_ij - s)
         for a in range(3):
-            for b in range(3):
-                if a == b or p.xh[a] is None or p.xh[b] is None:
+            for b in range(a + 1, 3):
+                if p.xh[a] is None or p.xh[b] is None:
                     continue
-                pos = pos + ((p.xh[a][sl] @ p.xh[b].T) * t[sl]).sum()
+                pos = pos + ((p.scale * p.xh[a][sl] @ p.xh[b].T - p.scale) * t[sl]).sum()
         stats[6 * n] = pos
         return stats
 
@@ -54,8 +54,8 @@ class FakeOps:
         for a in present:
             for b in present:
                 if a != b:
-                    tot = tot + (p.r * (p.scale + torch.log(stats[pair_id(a, b) * n: pair_id(a, b) * n + n]))).sum()
-        return ((tot - p.scale * stats[6 * n]) / (n * m * (m - 1))).float()
+                    tot = tot + (p.r * torch.log(stats[pair_id(a, b) * n: pair_id(a, b) * n + n])).sum()
+        return ((tot - 2.0 * stats[6 * n]) / (n * m * (m - 1))).float()
 
     def infonce_bwd(self, p, stats, xs, grad_out):
         n = p.n_global

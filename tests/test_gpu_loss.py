@@ -26,14 +26,30 @@ def _run(feats, labels, precision, scale=1 / 0.07):
     return loss.detach().cpu(), [None if l is None else l.grad.detach().float().cpu() for l in leaves]
 
 
-def _compare(loss, grads, ref_loss, ref_grads, tol):
-    assert abs(float(loss) - float(ref_loss)) <= tol * max(abs(float(ref_loss)), 1e-3), (float(loss), float(ref_loss))
-    for g, gr in zip(grads, ref_grads):
+LOSS_FLOOR = 5e-7  # half an ulp of a float32 logit near s = 14.3: the reference's own logits carry this much
+
+
+def _compare(loss, grads, ref_loss, ref_grads, tol, noise_loss=0.0, noise_grads=None):
+    """|ours - ref| <= tol * |ref|  (+ the float32 rounding noise of the reference arithmetic itself, measured
+    as the distance between a float32 and a float64 evaluation of the reference on the same inputs)."""
+    bound = tol * abs(float(ref_loss)) + 2.0 * noise_loss + LOSS_FLOOR
+    assert abs(float(loss) - float(ref_loss)) <= bound, (float(loss), float(ref_loss), bound)
+    for k, (g, gr) in enumerate(zip(grads, ref_grads)):
         if gr is None:
             assert g is None
             continue
         err = (g.double() - gr.double()).abs().max().item()
-        assert err <= tol * gr.abs().max().item() + 1e-12, (err, gr.abs().max().item())
+        noise = 0.0 if noise_grads is None else noise_grads[k]
+        bound = tol * gr.abs().max().item() + 2.0 * noise + 1e-12
+        assert err <= bound, (k, err, gr.abs().max().item(), bound)
+
+
+def _fp32_noise(feats, labels, ref_loss64, ref_grads64, scale=1 / 0.07):
+    """Distance between the float32 reference arithmetic (oracle port, autograd) and the float64 closed form."""
+    l32, g32 = loss_oracle.contrastive_loss_and_grads(feats, labels, scale)
+    nl = abs(float(l32) - float(ref_loss64))
+    ng = [0.0 if g is None else (g.double() - r.double()).abs().max().item() for g, r in zip(g32, ref_grads64)]
+    return nl, ng
 
 
 @pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "loss_*.npz"))))
@@ -41,9 +57,15 @@ def test_fp32_mode_matches_reference_fixtures(path):
     z = np.load(path)
     feats = [torch.from_numpy(z[f"x_{n}"]) if f"x_{n}" in z else None for n in NAMES]
     labels = torch.from_numpy(z["labels"])
-    loss, grads = _run(feats, labels, "fp32", float(z["logit_scale"]))
+    scale = float(z["logit_scale"])
+    loss, grads = _run(feats, labels, "fp32", scale)
     ref_grads = [torch.from_numpy(z[f"g_{n}"]) if f"g_{n}" in z else None for n in NAMES]
-    _compare(loss, grads, float(z["loss"]), ref_grads, FP32_TOL)
+    # the fixture is the reference's own float32 output: its distance from the float64 closed form on the same
+    # inputs is the rounding noise of the reference arithmetic
+    l64, g64 = loss_oracle.closed_form_grads(feats, labels, scale)
+    nl = abs(float(z["loss"]) - float(l64))
+    ng = [0.0 if g is None else (g.double() - r.double()).abs().max().item() for g, r in zip(ref_grads, g64)]
+    _compare(loss, grads, float(z["loss"]), ref_grads, FP32_TOL, nl, ng)
 
 
 @pytest.mark.parametrize("n,d,present,labels,normalised", [
@@ -56,8 +78,9 @@ def test_fp32_mode_matches_reference_fixtures(path):
 def test_fp32_mode_matches_oracle(n, d, present, labels, normalised):
     feats, lab = loss_inputs(n, d, present, seed=n, normalised=normalised, labels=labels)
     ref_loss, ref_grads = loss_oracle.closed_form_grads(feats, lab)  # fp64 evaluation of the reference maths
+    nl, ng = _fp32_noise(feats, lab, ref_loss, ref_grads)
     loss, grads = _run(feats, lab, "fp32")
-    _compare(loss, grads, ref_loss, ref_grads, FP32_TOL)
+    _compare(loss, grads, ref_loss, ref_grads, FP32_TOL, nl, ng)
 
 
 @pytest.mark.parametrize("n,d,present,labels,shared", [
