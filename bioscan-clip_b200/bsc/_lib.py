@@ -19,7 +19,7 @@ MODE_F32, MODE_TC16 = 0, 1
 NORM_TORCH, NORM_SKLEARN = 0, 1
 
 EXPORTS = [
-    "bsc_version", "bsc_last_error", "bsc_device_check", "bsc_l2norm_fwd", "bsc_label_stats",
+    "bsc_version", "bsc_last_error", "bsc_device_check", "bsc_l2norm_fwd", "bsc_rows_to_f16", "bsc_label_stats",
     "bsc_infonce_stats_len", "bsc_infonce_workspace_bytes", "bsc_infonce_fwd", "bsc_infonce_loss",
     "bsc_infonce_bwd", "bsc_bank_search_workspace_bytes", "bsc_bank_search", "bsc_topk_merge",
     "bsc_set_timing", "bsc_last_kernel_ms", "bsc_launch_count",
@@ -33,8 +33,8 @@ class BscError(RuntimeError):
 class InfoNceDesc(ctypes.Structure):
     _fields_ = [
         ("n_global", c_int64), ("n_local", c_int64), ("row0", c_int64),
-        ("d", c_int32), ("mode", c_int32), ("logit_scale", c_float), ("reserved", c_int32),
-        ("xh", c_void_p * 3), ("r", c_void_p), ("rep", c_void_p), ("next", c_void_p), ("rmax", c_void_p),
+        ("d", c_int32), ("mode", c_int32), ("logit_scale", c_float), ("x16_dtype", c_int32),
+        ("xh", c_void_p * 3), ("inv", c_void_p * 3), ("r", c_void_p), ("rep", c_void_p), ("next", c_void_p), ("rmax", c_void_p),
     ]
 
 
@@ -56,6 +56,7 @@ def lib():
     L.bsc_device_check.restype = c_int
     L.bsc_l2norm_fwd.argtypes = [c_void_p, c_int, c_int64, c_int, c_int64, c_void_p, c_int, c_void_p, c_void_p,
                                  c_int, c_void_p]
+    L.bsc_rows_to_f16.argtypes = [c_void_p, c_int, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p]
     L.bsc_label_stats.argtypes = [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
     L.bsc_infonce_stats_len.argtypes = [c_int64]
     L.bsc_infonce_stats_len.restype = c_int64

@@ -81,13 +81,27 @@ def infonce_forward(ops, comm, feats: List[Optional[torch.Tensor]], labels: torc
             raise ValueError("all modalities must have the same [batch, dim] shape")
     if labels.shape[0] != n_local:
         raise ValueError("label batch does not match the feature batch")
-    op_dtype = torch.float32 if mode == MODE_F32 else torch.float16
-    xh = [None if f is None else comm.all_gather_rows(ops.normalize(f.detach(), op_dtype)) for f in feats]
+    inv = None
+    if mode == MODE_F32:
+        xh = [None if f is None else comm.all_gather_rows(ops.normalize(f.detach(), torch.float32)) for f in feats]
+    else:
+        # tensor-core mode: the MMA operands are the caller's values times an exact per-row power of two, held in
+        # float16 (exact for bf16 / fp16 inputs; float32 inputs are rounded once to 11 bits).  Normalised rows are
+        # never re-rounded: the inverse norms enter as float32 scales inside the kernels.
+        xh, inv = [], []
+        for f in feats:
+            if f is None:
+                xh.append(None)
+                inv.append(None)
+                continue
+            y16, iv = ops.rows_to_f16(f.detach())
+            xh.append(comm.all_gather_rows(y16))
+            inv.append(comm.all_gather_rows(iv))
     all_labels = comm.all_gather_rows(labels.detach().to(torch.int64).contiguous())
     n_global = all_labels.shape[0]
     r, rep, nxt, rmax = ops.label_stats(all_labels)
     prob = Problem(xh=xh, n_global=n_global, n_local=n_local, row0=comm.rank * n_local, d=d, mode=mode,
-                   scale=scale, r=r, rep=rep, nxt=nxt, rmax=rmax)
+                   scale=scale, r=r, rep=rep, nxt=nxt, rmax=rmax, inv=inv)
     stats = ops.infonce_fwd(prob)
     stats = comm.all_reduce_sum(stats)
     loss = ops.infonce_loss(prob, stats)

@@ -20,7 +20,9 @@ from ._lib import MODE_F32, MODE_TC16, NORM_SKLEARN, NORM_TORCH, InfoNceDesc, ch
 @dataclass
 class Problem:
     """One InfoNCE evaluation: the gathered, normalised global batch and this rank's row range."""
-    xh: List[Optional[torch.Tensor]]  # 3 entries, [n_global, d] float16 (TC16) / float32 (F32) or None
+    # 3 entries or None: F32 mode -> [n_global, d] float32 L2-normalised rows;
+    # TC16 mode -> [n_global, d] RAW bfloat16 / float16 rows plus their inverse norms in ``inv``
+    xh: List[Optional[torch.Tensor]]
     n_global: int
     n_local: int
     row0: int
@@ -31,6 +33,7 @@ class Problem:
     rep: torch.Tensor = None    # [n_global] int32     class representative
     nxt: torch.Tensor = None    # [n_global] int32     next member of the class
     rmax: torch.Tensor = None   # [1] float32
+    inv: List[Optional[torch.Tensor]] = None  # TC16: [n_global] float32 1 / max(||row||, 1e-12) per modality
     workspace: torch.Tensor = None
     _desc: InfoNceDesc = field(default=None, repr=False)
 
@@ -57,6 +60,20 @@ class CudaOps:
                                        0, zero_rule, stream_ptr(x.device)))
         return y
 
+    def rows_to_f16(self, x: torch.Tensor):
+        """TC16 operands: (x * 2^k_row as float16 -- exact for 16-bit inputs --, 2^-k_row / max(||x_row||, 1e-12))."""
+        _lib.require_device(x.device)
+        assert x.dim() == 2
+        if x.stride(1) != 1:
+            x = x.contiguous()
+        n, d = x.shape
+        y = torch.empty((n, d), dtype=torch.float16, device=x.device)
+        inv = torch.empty(n, dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            check(lib().bsc_rows_to_f16(x.data_ptr(), _lib.dtype_code(x.dtype), n, d, x.stride(0), y.data_ptr(),
+                                        inv.data_ptr(), stream_ptr(x.device)))
+        return y, inv
+
     # ---- K2 -------------------------------------------------------------------------------------
     def label_stats(self, labels: torch.Tensor):
         _lib.require_device(labels.device)
@@ -78,8 +95,11 @@ class CudaOps:
             d = InfoNceDesc()
             d.n_global, d.n_local, d.row0 = p.n_global, p.n_local, p.row0
             d.d, d.mode, d.logit_scale = p.d, p.mode, float(p.scale)
+            first = next(t for t in p.xh if t is not None)
+            d.x16_dtype = _lib.dtype_code(first.dtype) if p.mode == MODE_TC16 else 0
             for m in range(3):
                 d.xh[m] = ptr(p.xh[m]) or None
+                d.inv[m] = (ptr(p.inv[m]) if p.inv is not None else 0) or None
             d.r, d.rep, d.next, d.rmax = p.r.data_ptr(), p.rep.data_ptr(), p.nxt.data_ptr(), p.rmax.data_ptr()
             p._desc = d
         return p._desc

@@ -11,12 +11,14 @@ namespace bsc {
 // launchers from prep.cu
 int l2norm_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, int y16_dtype, float* y32,
                   float* inv_norm, int zero_rule, cudaStream_t st);
+int rows_to_f16_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, float* inv,
+                       cudaStream_t st);
 int label_stats_launch(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
                        cudaStream_t st);
 int loss_launch(const float* stats, const float* r, int64_t n, unsigned present_mask, float scale, float* loss,
                 cudaStream_t st);
-int uv_launch(const float* stats, const float* r, int64_t n, const float* rmax, int use_gs, float* uv, float* gsbuf,
-              cudaStream_t st);
+int uv_launch(const float* stats, const float* r, int64_t n, const float* rmax, const float* const* inv, int use_gs,
+              float* uv, float* gsbuf, float* invmax, cudaStream_t st);
 int combine_launch(const CombineArgs& a, int x_dtype, cudaStream_t st);
 int topk_merge_launch(const float* cs, const int64_t* ci, int parts, int64_t nq, int k, float* os, int64_t* oi,
                       cudaStream_t st);
@@ -134,7 +136,7 @@ InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p) {
     return o;
   };
   L.uv = take((size_t)6 * N * sizeof(float));
-  L.gs = take(4 * sizeof(float));
+  L.gs = take(16 * sizeof(float));  // [6][2] {gs, 1/gs} per ordered pair, then [3] max inverse norms
   L.rowpart = take((size_t)3 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
   L.rowpos = take((size_t)3 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
   L.jrange = take((size_t)(L.n_jtile > 0 ? L.n_jtile : 1) * 2 * sizeof(int));
@@ -155,6 +157,15 @@ static int check_desc(const bsc_infonce_desc* p, const char* who) {
   BSC_REQUIRE(present_count(p, nullptr) >= 2, BSC_EINVAL, "%s: Too less element for calculating the contrastive loss.",
               who);
   BSC_REQUIRE(p->r && p->rep && p->next && p->rmax, BSC_EINVAL, "%s: label statistics pointers are null", who);
+  if (p->mode == BSC_MODE_TC16) {
+    BSC_REQUIRE(p->x16_dtype == BSC_F16, BSC_EUNSUPPORTED,
+                "%s: TC16 mode takes float16 rows prepared by bsc_rows_to_f16 (exact for bfloat16 values); "
+                "tcgen05 kind::f16 cannot mix the fp16 weight tile with bfloat16 rows (x16_dtype=%d)",
+                who, p->x16_dtype);
+    for (int a = 0; a < 3; ++a)
+      BSC_REQUIRE(!p->xh[a] || p->inv[a], BSC_EINVAL, "%s: TC16 mode needs the inverse row norms of modality %d", who,
+                  a);
+  }
   return BSC_OK;
 }
 
@@ -204,6 +215,13 @@ int bsc_l2norm_fwd(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, vo
   BSC_REQUIRE(zero_rule == BSC_NORM_TORCH || zero_rule == BSC_NORM_SKLEARN, BSC_EINVAL,
               "bsc_l2norm_fwd: unknown zero_rule %d", zero_rule);
   return l2norm_launch(x, x_dtype, n, d, ldx, y16, y16_dtype, y32, inv_norm, zero_rule, (cudaStream_t)stream);
+}
+
+int bsc_rows_to_f16(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, float* inv, void* stream) {
+  BSC_REQUIRE((x && y16 && inv) || n == 0, BSC_EINVAL, "bsc_rows_to_f16: null pointer");
+  BSC_REQUIRE(n >= 0 && d >= 1 && ldx >= d, BSC_EINVAL, "bsc_rows_to_f16: bad shape n=%lld d=%d ldx=%lld", (long long)n,
+              d, (long long)ldx);
+  return rows_to_f16_launch(x, x_dtype, n, d, ldx, y16, inv, (cudaStream_t)stream);
 }
 
 int bsc_label_stats(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
@@ -266,7 +284,8 @@ int bsc_infonce_bwd(const bsc_infonce_desc* p, const float* stats, const void* c
     BSC_REQUIRE(!p->xh[a] || (x[a] && grad[a]), BSC_EINVAL, "bsc_infonce_bwd: x/grad pointer missing for modality %d",
                 a);
   if (p->n_local == 0) return BSC_OK;
-  rc = uv_launch(stats, p->r, N, p->rmax, p->mode == BSC_MODE_TC16, (float*)(ws + L.uv), (float*)(ws + L.gs), st);
+  rc = uv_launch(stats, p->r, N, p->rmax, p->inv, p->mode == BSC_MODE_TC16, (float*)(ws + L.uv), (float*)(ws + L.gs),
+                 (float*)(ws + L.gs) + 12, st);
   if (rc) return rc;
   rc = (p->mode == BSC_MODE_F32) ? simt_bwd_raw(p, L, ws, st) : tc_bwd_raw(p, L, ws, st);
   if (rc) return rc;

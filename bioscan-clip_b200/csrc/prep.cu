@@ -61,6 +61,72 @@ __global__ void __launch_bounds__(256) l2norm_rows_kernel(const TI* __restrict__
   }
 }
 
+// TC16 operand preparation: y16[i,:] = fp16(x[i,:] * 2^k_i) with k_i chosen so the largest |element| of the row
+// lands in [1, 2), inv[i] = 2^-k_i / max(||x_i||, 1e-12).  A power-of-two scale is exact, and bf16 / fp16 values
+// convert to fp16 without rounding (elements below 2^-24 of the row maximum aside), so the tensor cores see the
+// caller's numbers verbatim; cos_ij = <y16_i, y16_j> * inv_i * inv_j is then formed in fp32.
+template <typename TI>
+__global__ void __launch_bounds__(256) rows_to_f16_kernel(const TI* __restrict__ x, int64_t n, int d, int64_t ldx,
+                                                          __half* __restrict__ y16, float* __restrict__ inv) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= n) return;
+  const TI* xr = x + row * ldx;
+  float ss = 0.f, amax = 0.f;
+  for (int c = lane; c < d; c += 32) {
+    const float v = to_f32<TI>(xr[c]);
+    ss = fmaf(v, v, ss);
+    amax = fmaxf(amax, fabsf(v));
+  }
+  ss = warp_sum(ss);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+  int k = 0;
+  if (amax > 0.f && amax < 3.0e38f) k = -ilogbf(amax);
+  k = max(-120, min(120, k));
+  const float scale = exp2f((float)k);
+  const float nrm = sqrtf(ss);
+  // ss itself can overflow / underflow for extreme rows; the scaled row never does
+  float inv_row;
+  if (nrm > 1e-12f && nrm < 3.0e38f) {
+    inv_row = exp2f((float)-k) / nrm;
+  } else {
+    float s2 = 0.f;
+    for (int c = lane; c < d; c += 32) {
+      const float v = to_f32<TI>(xr[c]) * scale;
+      s2 = fmaf(v, v, s2);
+    }
+    s2 = warp_sum(s2);
+    const float n2 = sqrtf(s2);                     // norm of the scaled row = ||x|| * 2^k
+    const float true_nrm = n2 * exp2f((float)-k);   // may flush to zero: then F.normalize clamps at 1e-12
+    inv_row = n2 > 0.f ? (true_nrm >= 1e-12f ? 1.0f / n2 : exp2f((float)-k) * 1e12f) : 0.f;
+  }
+  if (lane == 0) inv[row] = inv_row;
+  for (int c = lane; c < d; c += 32) y16[row * (int64_t)d + c] = __float2half_rn(to_f32<TI>(xr[c]) * scale);
+}
+
+int rows_to_f16_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, float* inv,
+                       cudaStream_t st) {
+  if (n == 0) return BSC_OK;
+  dim3 block(256), grid((unsigned)((n + 7) / 8));
+  switch (x_dtype) {
+    case BSC_F32:
+      rows_to_f16_kernel<float><<<grid, block, 0, st>>>((const float*)x, n, d, ldx, (__half*)y16, inv);
+      break;
+    case BSC_BF16:
+      rows_to_f16_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)x, n, d, ldx, (__half*)y16, inv);
+      break;
+    case BSC_F16:
+      rows_to_f16_kernel<__half><<<grid, block, 0, st>>>((const __half*)x, n, d, ldx, (__half*)y16, inv);
+      break;
+    default:
+      set_error("bsc_rows_to_f16: unknown x_dtype %d", x_dtype);
+      return BSC_EINVAL;
+  }
+  BSC_LAUNCH_CHECK("rows_to_f16_kernel");
+  return BSC_OK;
+}
+
 template <typename TI>
 static int l2norm_dispatch_out(const void* x, int64_t n, int d, int64_t ldx, void* y16, int y16_dtype, float* y32,
                                float* inv_norm, int zero_rule, cudaStream_t st) {
@@ -274,17 +340,42 @@ int loss_launch(const float* stats, const float* r, int64_t n, unsigned present_
   return BSC_OK;
 }
 
-// uv[pid][i] = r_i / sumexp_pid[i];  gsbuf = {gs, 1/gs} with gs the power of two that keeps
-// gs * 2 * rmax <= 32768 (the fp16 range of the gradient-weight tile in TC16 mode).
+// Largest inverse row norm of every present modality (grid = 3 blocks): bounds the fp16 range of the
+// gradient-weight tile in TC16 mode, where 1/||y_j|| is folded into the weights.
+__global__ void __launch_bounds__(256) invmax_kernel(const float* __restrict__ i0, const float* __restrict__ i1,
+                                                     const float* __restrict__ i2, int64_t n,
+                                                     float* __restrict__ out) {
+  __shared__ float sh[8];
+  const float* src = blockIdx.x == 0 ? i0 : (blockIdx.x == 1 ? i1 : i2);
+  float m = 0.f;
+  if (src != nullptr)
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) m = fmaxf(m, src[i]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) m = fmaxf(m, sh[w]);
+    out[blockIdx.x] = src != nullptr ? m : 1.0f;
+  }
+}
+
+// uv[pid][i] = r_i / sumexp_pid[i];  gsbuf[pid] = {gs, 1/gs} with gs the power of two that keeps the weight tile
+// of the ordered pair (x, y), |gs * (e*(u+v) - 2T) / ||y_j||| <= 4 * gs * rmax * max_j(1/||y_j||), inside fp16.
 __global__ void __launch_bounds__(256) uv_kernel(const float* __restrict__ stats, const float* __restrict__ r,
-                                                 int64_t n, const float* __restrict__ rmax, int use_gs,
+                                                 int64_t n, const float* __restrict__ rmax,
+                                                 const float* __restrict__ invmax, int use_gs,
                                                  float* __restrict__ uv, float* __restrict__ gsbuf) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i == 0) {
-    float gs = 1.0f;
-    if (use_gs) gs = exp2f(floorf(log2f(16384.0f / fmaxf(rmax[0], 1.0f))));
-    gsbuf[0] = gs;
-    gsbuf[1] = 1.0f / gs;
+    for (int x = 0; x < 3; ++x)
+      for (int y = 0; y < 3; ++y) {
+        if (x == y) continue;
+        float gs = 1.0f;
+        if (use_gs) gs = exp2f(floorf(log2f(8192.0f / (fmaxf(rmax[0], 1.0f) * fmaxf(invmax[y], 1e-30f)))));
+        gsbuf[2 * pair_id(x, y)] = gs;
+        gsbuf[2 * pair_id(x, y) + 1] = 1.0f / gs;
+      }
   }
   if (i >= n) return;
   const float ri = r[i];
@@ -295,16 +386,19 @@ __global__ void __launch_bounds__(256) uv_kernel(const float* __restrict__ stats
   }
 }
 
-int uv_launch(const float* stats, const float* r, int64_t n, const float* rmax, int use_gs, float* uv, float* gsbuf,
-              cudaStream_t st) {
-  uv_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(stats, r, n, rmax, use_gs, uv, gsbuf);
+int uv_launch(const float* stats, const float* r, int64_t n, const float* rmax, const float* const* inv, int use_gs,
+              float* uv, float* gsbuf, float* invmax, cudaStream_t st) {
+  invmax_kernel<<<3, 256, 0, st>>>(use_gs ? inv[0] : nullptr, use_gs ? inv[1] : nullptr, use_gs ? inv[2] : nullptr, n,
+                                   invmax);
+  BSC_LAUNCH_CHECK("invmax_kernel");
+  uv_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(stats, r, n, rmax, invmax, use_gs, uv, gsbuf);
   BSC_LAUNCH_CHECK("uv_kernel");
   return BSC_OK;
 }
 
 // ---------------------------------------------------------------------------------------------
 // K6: combine the raw sweep output with the positive term and chain through F.normalize:
-//   ghat = c*s*(raw0+raw1)/gs   (the -2*T_ij term is already inside the sweep's weights),
+//   ghat = c*s*(raw0/gs0 + raw1/gs1)   (the -2*T_ij term is already inside the sweep's weights),
 //   dx = gout * (ghat - xhat <xhat,ghat>) / ||x||
 // One warp per (row, modality).
 // ---------------------------------------------------------------------------------------------
@@ -319,7 +413,13 @@ __global__ void __launch_bounds__(256) combine_kernel(CombineArgs a) {
   for (int q = 0; q < 3; ++q) mcount += (a.present_mask >> q) & 1;
   const float c = 1.0f / ((float)a.n_global * (float)(mcount * (mcount - 1)));
   const float cs = c * a.scale;
-  const float inv_gs = a.gsbuf[1];
+  // raw0 / raw1 are the sweeps against the first / second other present modality
+  float inv_gs[2] = {0.f, 0.f};
+  {
+    int slot = 0;
+    for (int y = 0; y < 3; ++y)
+      if (y != m && ((a.present_mask >> y) & 1)) inv_gs[slot++] = a.gsbuf[2 * pair_id(m, y) + 1];
+  }
   const float gout = a.grad_out[0];
   const T* xr = (const T*)a.x[m] + il * a.ldx;
   T* gr = (T*)a.grad[m] + il * a.ldx;
@@ -337,9 +437,9 @@ __global__ void __launch_bounds__(256) combine_kernel(CombineArgs a) {
   const float inv = 1.0f / fmaxf(nrm, 1e-12f);
 
   auto ghat_at = [&](int cidx) -> float {
-    float raw = raw0[cidx];
-    if (a.n_slots > 1) raw += raw1[cidx];
-    return cs * (raw * inv_gs);
+    float raw = raw0[cidx] * inv_gs[0];
+    if (a.n_slots > 1) raw = fmaf(raw1[cidx], inv_gs[1], raw);
+    return cs * raw;
   };
 
   float dot = 0.f;

@@ -43,7 +43,8 @@ struct BwdParams {
   float k1, k2;
   const float* uv;     // [6][N]
   const int32_t* rep;  // [N] label class representative: T_ij = (rep[i] == rep[j])
-  const float* gsbuf;  // {gs, 1/gs}
+  const float* gsbuf;  // [6][2] {gs, 1/gs} per ordered pair
+  const float* inv[3]; // inverse row norms per modality
   float* dxraw;        // [3][2][n_local][d]
 };
 
@@ -55,8 +56,10 @@ struct __align__(8) BwdSmemTail {
   uint64_t acc_full, acc_free;
   uint32_t tmem_base;
   uint32_t pad;
-  float vgs[2][BN];  // gs * v_j of the current / next column tile
-  int repj[2][BN];   // label class of the tile's columns (-1 past the end of the batch)
+  // per-column facts of the current tile (single buffer, two named barriers per tile)
+  float sc[BN];   // k1 / ||y_j||
+  float vi[BN];   // gs * v_j / ||y_j||
+  int repj[BN];   // label class (-1 past the end of the batch)
 };
 
 // dynamic shared memory starts 1024-byte aligned (no static __shared__ in this kernel; checked at run time)
@@ -75,6 +78,7 @@ __device__ __forceinline__ int chunk_groups(const BwdParams& p, int chunk) {
   return min(p.groups_per_chunk, p.n_groups - g0);
 }
 
+template <int FMT>
 __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ BwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t ring = ptx::smem_u32(smem_raw);
@@ -170,8 +174,8 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    constexpr uint32_t idesc_s = umma_idesc(BM, BN, 0, 0, 0);   // S = Xhat_I * Yhat_J^T, both K-major
-    constexpr uint32_t idesc_g = umma_idesc(BM, 128, 0, 0, 1);  // acc += G (K-major) * Yhat_J (MN-major)
+    constexpr uint32_t idesc_s = umma_idesc(BM, BN, FMT, FMT, 0, 0);   // S = X_I * Y_J^T, both K-major
+    constexpr uint32_t idesc_g = umma_idesc(BM, 128, 0, FMT, 0, 1);   // acc += G (fp16, K-major) * Y_J (MN-major)
     int stage = 0;
     uint32_t phase = 0;
     uint32_t s_count = 0;    // S tiles issued so far (all items)
@@ -257,7 +261,7 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
     const int q = warp & 3;
     const int row_in_tile = q * 32 + lane;
     const int et = threadIdx.x - 128;
-    const float gs = p.gsbuf[0];
+    const float inv_k1 = 1.0f / p.k1;
     uint32_t tile_count = 0;  // == s_count == g_count on this side
     uint32_t item_count = 0;
     for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++item_count) {
@@ -266,20 +270,28 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
       const int x = p.xy_x[xy], y = p.xy_y[xy];
       const int64_t arow = (int64_t)iblk * BM + row_in_tile;
       const bool row_ok = arow < p.n_local;
-      const float ugs = row_ok ? gs * p.uv[(int64_t)pair_id(x, y) * p.n_global + p.row0 + arow] : 0.f;
+      const float gs = p.gsbuf[2 * pair_id(x, y)];
+      // row facts: inverse norm, gs*u_i/k1 and 2*gs/k1 (both later multiplied by sc_j = k1/||y_j||)
+      const float inv_i = row_ok ? p.inv[x][p.row0 + arow] : 0.f;
+      const float ugk = row_ok ? gs * inv_k1 * p.uv[(int64_t)pair_id(x, y) * p.n_global + p.row0 + arow] : 0.f;
       const int rep_i = row_ok ? p.rep[p.row0 + arow] : -2;
-      const float two_gs = 2.0f * gs;
+      const float m2gk = -2.0f * gs * inv_k1;
       const float* vrow = p.uv + (int64_t)pair_id(y, x) * p.n_global;
+      const float* invy = p.inv[y];
       const int ng = chunk_groups(p, chunk);
 
       for (int t = 0; t < T; ++t, ++tile_count) {
         const uint32_t buf = tile_count & 1u;
         const uint32_t use = tile_count >> 1;
-        // stage gs * v_j for this tile (one column per thread), visible to the 4 epilogue warps
+        // stage the column facts of this tile (one column per thread) for the 4 epilogue warps
+        ptx::named_bar_sync(2, 128);  // everyone is done with the previous tile's columns
         {
           const int64_t j = (int64_t)t * BN + et;
-          tail->vgs[buf][et] = (j < p.n_global) ? gs * vrow[j] : 0.f;
-          tail->repj[buf][et] = (j < p.n_global) ? p.rep[j] : -1;
+          const bool ok = j < p.n_global;
+          const float ij = ok ? invy[j] : 0.f;
+          tail->sc[et] = p.k1 * ij;
+          tail->vi[et] = ok ? gs * vrow[j] * ij : 0.f;
+          tail->repj[et] = ok ? p.rep[j] : -1;
         }
         ptx::named_bar_sync(1, 128);
         ptx::mbar_wait(ptx::smem_u32(&tail->s_full), tile_count & 1u, 400);
@@ -302,20 +314,28 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tail->s_free));
           }
-          const float* vg = &tail->vgs[buf][h * 64];
-          const int* rj = &tail->repj[buf][h * 64];
+          const float* sc = &tail->sc[h * 64];
+          const float* vi = &tail->vi[h * 64];
+          const int* rj = &tail->repj[h * 64];
 #pragma unroll
           for (int u = 0; u < 8; ++u) {  // 16-byte units of 8 columns
             uint32_t pk[4];
 #pragma unroll
             for (int w = 0; w < 4; ++w) {
               const int c = u * 8 + w * 2;
-              const float a0 = __uint_as_float(c < 32 ? r0[c & 31] : r1[c & 31]);
-              const float a1 = __uint_as_float(c + 1 < 32 ? r0[(c + 1) & 31] : r1[(c + 1) & 31]);
-              const float g0 = fmaf(ptx::ex2(fmaf(a0, p.k1, -p.k2)), ugs + vg[c], rj[c] == rep_i ? -two_gs : 0.f);
-              const float g1 =
-                  fmaf(ptx::ex2(fmaf(a1, p.k1, -p.k2)), ugs + vg[c + 1], rj[c + 1] == rep_i ? -two_gs : 0.f);
-              const __half2 hh = __floats2half2_rn(g0, g1);
+              float gq[2];
+#pragma unroll
+              for (int z = 0; z < 2; ++z) {
+                const int cc = c + z;
+                const float dot = __uint_as_float(cc < 32 ? r0[cc & 31] : r1[cc & 31]);
+                const float scj = sc[cc];
+                // e = exp(s*cos - s), cos = dot * inv_i * inv_j;  weight = gs*(u_i + v_j)/||y_j||
+                const float e = ptx::ex2(fmaf(dot, inv_i * scj, -p.k2));
+                const float wgt = fmaf(ugk, scj, vi[cc]);
+                const float tv = (rj[cc] == rep_i) ? m2gk * scj : 0.f;
+                gq[z] = fmaf(e, wgt, tv);
+              }
+              const __half2 hh = __floats2half2_rn(gq[0], gq[1]);
               pk[w] = *reinterpret_cast<const uint32_t*>(&hh);
             }
             const uint32_t addr = grow + h * SLOT + ((uint32_t)(u ^ (row_in_tile & 7)) << 4);
@@ -387,8 +407,9 @@ int tc_bwd_raw(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
   int first = -1;
   for (int a = 0; a < 3; ++a)
     if (d->xh[a]) {
-      int rc = make_tmap_2d(&p.tmap[a], d->xh[a], BSC_F16, d->n_global, d->d, 128);
+      int rc = make_tmap_2d(&p.tmap[a], d->xh[a], d->x16_dtype, d->n_global, d->d, 128);
       if (rc) return rc;
+      p.inv[a] = d->inv[a];
       if (first < 0) first = a;
     }
   for (int a = 0; a < 3; ++a)
@@ -426,14 +447,16 @@ int tc_bwd_raw(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
   p.dxraw = (float*)(ws + L.dxraw);
   if (p.num_items == 0 || p.n_jtile == 0) return BSC_OK;
 
-  static bool attr_done = false;
-  if (!attr_done) {
-    BSC_CUDA(cudaFuncSetAttribute(tc_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM_BYTES));
-    attr_done = true;
+  auto kern = d->x16_dtype == BSC_BF16 ? tc_bwd_kernel<1> : tc_bwd_kernel<0>;
+  static bool attr_done[2] = {false, false};
+  const int ki = d->x16_dtype == BSC_BF16 ? 1 : 0;
+  if (!attr_done[ki]) {
+    BSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM_BYTES));
+    attr_done[ki] = true;
   }
   const int grid = p.num_items < sm_count() ? p.num_items : sm_count();
   timing_begin(1, st);
-  tc_bwd_kernel<<<grid, 256, BWD_SMEM_BYTES, st>>>(p);
+  kern<<<grid, 256, BWD_SMEM_BYTES, st>>>(p);
   timing_end(1, st);
   BSC_LAUNCH_CHECK("tc_bwd_kernel");
   return BSC_OK;

@@ -149,8 +149,9 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr, uint32_t lbo
 // Instruction descriptor for kind::f16 with fp32 accumulation.
 //   [4,6) c_format = 1 (f32)  [7,10) a_format  [10,13) b_format (0 = f16, 1 = bf16)
 //   [15] a_major  [16] b_major (0 = K-major, 1 = MN-major)  [17,23) N >> 3  [24,29) M >> 4
-__host__ __device__ constexpr uint32_t umma_idesc(int m, int n, int ab_format, int a_mn_major, int b_mn_major) {
-  return (1u << 4) | ((uint32_t)ab_format << 7) | ((uint32_t)ab_format << 10) | ((uint32_t)a_mn_major << 15) |
+__host__ __device__ constexpr uint32_t umma_idesc(int m, int n, int a_format, int b_format, int a_mn_major,
+                                                  int b_mn_major) {
+  return (1u << 4) | ((uint32_t)a_format << 7) | ((uint32_t)b_format << 10) | ((uint32_t)a_mn_major << 15) |
          ((uint32_t)b_mn_major << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 

@@ -46,6 +46,7 @@ struct SimParams {
   float* colpart;    // [pair][iblk][b_pad]
   float* rowpos;     // [pair][jchunk][a_pad]  sum_j T_ij * (S_ij*k1 - k2)   (log2 units)
   const int32_t* rep;   // [b_rows] class representative of every row of the global batch (T_ij = rep_i == rep_j)
+  const float* inv[3];  // per operand matrix: inverse row norms (EPI_STATS: cos_ij = <a_i, b_j> * inv_i * inv_j)
   const int2* jrange;   // [n_jtile] {min, max} of rep over the columns of a tile
   int64_t a_pad, b_pad;
   // EPI_TOPK
@@ -63,6 +64,7 @@ struct __align__(8) SimSmemTail {
   uint32_t tmem_base;
   uint32_t pad;
   float cs[2][4][BN];  // per-warp column partial sums, double-buffered by tile parity
+  float invb[2][BN];   // k1 * inverse norms of the tile's columns, double-buffered by tile parity
 };
 
 constexpr size_t SIM_SMEM_BYTES = 1024 /*align slack*/ + (size_t)STAGES * STAGE_BYTES + sizeof(SimSmemTail);
@@ -158,7 +160,7 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    constexpr uint32_t idesc = umma_idesc(BM, BN, FMT, 0, 0);
+    constexpr uint32_t idesc = umma_idesc(BM, BN, FMT, FMT, 0, 0);
     int stage = 0;
     uint32_t phase = 0;
     uint32_t tile_count = 0;
@@ -211,7 +213,11 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
       float rowsum = 0.f;
       float rowpos = 0.f;
       int rep_i = -2, wmin = 0, wmax = -1;
+      float inv_i = 0.f;
+      const float* invb_g = nullptr;
       if (EPI == EPI_STATS) {
+        if (row_ok) inv_i = p.inv[p.pair_a[pair]][p.a_row0 + arow];
+        invb_g = p.inv[p.pair_b[pair]];
         // label class of this thread's row and the class range of the warp's 32 rows
         if (row_ok) rep_i = p.rep[p.a_row0 + arow];
         wmin = row_ok ? rep_i : 0x7fffffff;
@@ -235,12 +241,21 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
       for (int jt = jchunk * p.jpc; jt < jt_end; ++jt, ++tile_count) {
         const uint32_t buf = tile_count & 1u;
         const uint32_t use = tile_count >> 1;
+        const int64_t col0 = (int64_t)jt * BN;
+        if (EPI == EPI_STATS) {
+          // stage k1 / ||b_j|| of the tile's columns (2 per thread) while the MMAs of this tile are in flight
+          for (int col = et; col < BN; col += 128) {
+            const int64_t j = col0 + col;
+            tail->invb[buf][col] = j < p.b_rows ? p.k1 * invb_g[j] : 0.f;
+          }
+          ptx::named_bar_sync(2, 128);
+        }
         ptx::mbar_wait(ptx::smem_u32(&tail->tmem_full[buf]), use & 1u, 400 + buf);
         ptx::tc_fence_after();
-        const int64_t col0 = (int64_t)jt * BN;
         const bool edge = (col0 + BN > p.b_rows) || ((int64_t)iblk * BM + BM > p.a_rows);
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN;
         float* cs = tail->cs[buf][q];
+        const float* ivb = tail->invb[buf];
         bool tile_pos = false;  // can any (row of this warp, column of this tile) pair share a label?
         if (EPI == EPI_STATS) {
           const int2 jr = p.jrange[jt];
@@ -260,14 +275,15 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
               const int repv = jcol < p.b_rows ? p.rep[jcol] : -1;
 #pragma unroll
               for (int t = 0; t < 32; ++t) {
-                const float a = fmaf(__uint_as_float(raw[t]), p.k1, -p.k2);
+                const float a = fmaf(__uint_as_float(raw[t]), inv_i * ivb[c * 32 + t], -p.k2);
                 const int rj = __shfl_sync(0xffffffffu, repv, t);
                 rowpos += (rj == rep_i) ? a : 0.f;
                 e[t] = ptx::ex2(a);
               }
             } else {
 #pragma unroll
-              for (int t = 0; t < 32; ++t) e[t] = ptx::ex2(fmaf(__uint_as_float(raw[t]), p.k1, -p.k2));
+              for (int t = 0; t < 32; ++t)
+                e[t] = ptx::ex2(fmaf(__uint_as_float(raw[t]), inv_i * ivb[c * 32 + t], -p.k2));
             }
             if (edge) {
 #pragma unroll
@@ -407,9 +423,10 @@ int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, float*
   int np = 0;
   for (int a = 0; a < 3; ++a) {
     if (d->xh[a]) {
-      int rc = make_tmap_2d(&p.tmap[a], d->xh[a], BSC_F16, d->n_global, d->d, 128);
+      int rc = make_tmap_2d(&p.tmap[a], d->xh[a], d->x16_dtype, d->n_global, d->d, 128);
       if (rc) return rc;
     }
+    p.inv[a] = d->inv[a];
     for (int b = a + 1; b < 3; ++b)
       if (d->xh[a] && d->xh[b]) {
         p.pair_a[np] = a;
@@ -442,7 +459,7 @@ int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, float*
   int rc = rep_range_launch(d->rep, d->n_global, BN, (int2*)(ws + L.jrange), st);
   if (rc) return rc;
   timing_begin(0, st);
-  rc = launch_sim<EPI_STATS, 0>(p, st);
+  rc = d->x16_dtype == BSC_BF16 ? launch_sim<EPI_STATS, 1>(p, st) : launch_sim<EPI_STATS, 0>(p, st);
   timing_end(0, st);
   if (rc) return rc;
   // sum_ij T_ij (s*S_ij - s) over the local rows and all pairs, in natural-log units

@@ -47,7 +47,8 @@ extern "C" {
 
 /* arithmetic modes */
 #define BSC_MODE_F32 0  /* SIMT fp32 path: exact-parity mode (1e-5 vs the fp32 reference)          */
-#define BSC_MODE_TC16 1 /* tcgen05 path: 16-bit normalised operands, fp32 accumulate in TMEM       */
+#define BSC_MODE_TC16 1 /* tcgen05 path: the caller's 16-bit rows as operands, fp32 accumulate in TMEM,
+                           row norms applied as fp32 scales in the epilogue                           */
 
 /* zero-norm rules for bsc_l2norm_fwd */
 #define BSC_NORM_TORCH 0   /* F.normalize: x / max(||x||, 1e-12)            (loss_func.py:43-44)   */
@@ -69,6 +70,12 @@ int bsc_device_check(void);
 int bsc_l2norm_fwd(const void* x, int x_dtype, int64_t n, int d, int64_t ldx,
                    void* y16, int y16_dtype, float* y32, float* inv_norm, int zero_rule, void* stream);
 
+/* TC16 operand preparation: y16[n][d] (fp16) = x * 2^k_row with the row maximum scaled into [1,2) -- exact for
+ * bfloat16 / float16 values -- and inv[n] = 2^-k_row / max(||x_row||, 1e-12), so that
+ * cos_ij = <y16_i, y16_j> * inv_i * inv_j equals the reference's normalised dot product without re-rounding
+ * any operand (F.normalize, loss_func.py:43-44). */
+int bsc_rows_to_f16(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, float* inv, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * K2  label statistics replacing construct_label_metrix (loss_func.py:18-21): for labels[n]
  *     r[i]    = #{j : labels[j] == labels[i]}      (row sum of the 0/1 label matrix)
@@ -82,9 +89,13 @@ int bsc_label_stats(const int64_t* labels, int64_t n, float* r, int32_t* rep, in
 /* ------------------------------------------------------------------------------------------------
  * InfoNCE loss -- ContrastiveLoss.forward / ClipLoss.forward.
  *
- * The problem descriptor.  xh[m] points to the GLOBAL (already gathered) batch of modality m:
- * n_global normalised rows of d elements, float (BSC_MODE_F32) or fp16 (BSC_MODE_TC16), NULL when the
- * modality is absent.  This rank owns rows [row0, row0 + n_local).
+ * The problem descriptor.  xh[m] points to the GLOBAL (already gathered) batch of modality m, NULL when the
+ * modality is absent; this rank owns rows [row0, row0 + n_local).
+ *   BSC_MODE_F32   xh[m] = n_global L2-NORMALISED rows of d floats (bsc_l2norm_fwd); inv[m] is ignored.
+ *   BSC_MODE_TC16  xh[m] = n_global rows of d fp16 elements (x16_dtype = BSC_F16) and inv[m][n_global], both
+ *                  from bsc_rows_to_f16: the caller's values times an exact power of two per row.  The tensor
+ *                  cores multiply those rows; cos_ij = <x_i, y_j> * inv_i * inv_j is formed in fp32, so no
+ *                  operand is re-rounded.
  * ---------------------------------------------------------------------------------------------- */
 typedef struct bsc_infonce_desc {
   int64_t n_global;
@@ -93,8 +104,9 @@ typedef struct bsc_infonce_desc {
   int32_t d;
   int32_t mode;        /* BSC_MODE_*                                              */
   float logit_scale;   /* s = 1/0.07 in the reference (scripts/train_cl.py:190)   */
-  int32_t reserved;
+  int32_t x16_dtype;   /* BSC_MODE_TC16: element type of xh (BSC_F16)             */
   const void* xh[BSC_MAX_MODALITIES];
+  const float* inv[BSC_MAX_MODALITIES]; /* BSC_MODE_TC16: inverse row norms          */
   const float* r;      /* [n_global] from bsc_label_stats                          */
   const int32_t* rep;  /* [n_global]                                               */
   const int32_t* next; /* [n_global]                                               */

@@ -20,6 +20,10 @@ class FakeOps:
         n = x.norm(dim=1, keepdim=True)
         return (x / n.clamp_min(1e-12)).to(torch.float64)
 
+    def rows_to_f16(self, x):
+        x = x.double()
+        return x, 1.0 / x.norm(dim=1).clamp_min(1e-12)
+
     def label_stats(self, labels):
         t = (labels[None, :] == labels[:, None])
         r = t.sum(1).double()

@@ -54,9 +54,11 @@ STAGES["tc_fwd"] = """
 # forward statistics of the tcgen05 sweep vs a dense torch evaluation on the same fp16 operands
 for (n, d) in [(128, 64), (256, 768), (1000, 768), (4096, 768)]:
     feats, labels = loss_inputs(n, d, seed=n, labels='multi', dtype=torch.bfloat16, device='cuda')
-    xh = [ops.normalize(f, torch.float16) for f in feats]
+    prep = [ops.rows_to_f16(f) for f in feats]
+    inv = [q[1] for q in prep]
+    xh = [torch.nn.functional.normalize(f.double(), dim=1) for f in feats]
     r, rep, nxt, rmax = ops.label_stats(labels)
-    p = Problem(xh=xh, n_global=n, n_local=n, row0=0, d=d, mode=_lib.MODE_TC16, scale=1/0.07, r=r, rep=rep, nxt=nxt, rmax=rmax)
+    p = Problem(xh=[q[0] for q in prep], n_global=n, n_local=n, row0=0, d=d, mode=_lib.MODE_TC16, scale=1/0.07, r=r, rep=rep, nxt=nxt, rmax=rmax, inv=inv)
     t0 = time.time(); stats = ops.infonce_fwd(p); torch.cuda.synchronize(); dt = time.time() - t0
     s = 1/0.07
     worst = 0
@@ -68,7 +70,7 @@ for (n, d) in [(128, 64), (256, 768), (1000, 768), (4096, 768)]:
             got = stats[pid*n:(pid+1)*n].double()
             worst = max(worst, ((got - e).abs() / e).max().item())
     t = (labels[None] == labels[:, None]).double()
-    pos = sum(((xh[a].double() @ xh[b].double().T) * t).sum() for a in range(3) for b in range(3) if a != b)
+    pos = sum(((s * xh[a].double() @ xh[b].double().T - s) * t).sum() for a in range(3) for b in range(a + 1, 3))
     print(n, d, 'sumexp worst rel', worst, 'pos rel', abs(stats[6*n].item() - pos.item())/abs(pos.item()), 'time', dt)
 """
 
@@ -76,12 +78,13 @@ STAGES["tc_loss"] = """
 for (n, d, pres, lab, sh) in [(256, 768, (1,1,0), 'arange', 0.5), (512, 768, (1,1,1), 'multi', 0.5), (1000, 768, (1,1,1), 'arange', 0.5), (384, 256, (1,0,1), 'multi', 0.0), (4096, 768, (1,1,1), 'arange', 0.5)]:
     feats, labels = loss_inputs(n, d, tuple(bool(p) for p in pres), seed=n+1, labels=lab, shared=sh, dtype=torch.bfloat16)
     ref_loss, ref_grads = loss_oracle.closed_form_grads([None if f is None else f.float() for f in feats], labels, dtype=torch.float32 if n > 2048 else torch.float64)
-    leaves = [None if f is None else f.cuda().requires_grad_(True) for f in feats]
-    loss = bsc.ContrastiveLoss(None, 1/0.07, precision='tc16')(*leaves, labels.cuda())
-    loss.backward(); torch.cuda.synchronize()
-    print(n, d, 'loss', float(loss), float(ref_loss), 'rel', abs(float(loss)-float(ref_loss))/abs(float(ref_loss)))
-    for l, g in zip(leaves, ref_grads):
-        if l is not None: print('   grad rel', rel(l.grad.float(), g))
+    for io in ('bf16', 'fp32'):
+        leaves = [None if f is None else (f if io == 'bf16' else f.float()).cuda().requires_grad_(True) for f in feats]
+        loss = bsc.ContrastiveLoss(None, 1/0.07, precision='tc16')(*leaves, labels.cuda())
+        loss.backward(); torch.cuda.synchronize()
+        print(n, d, io, 'loss', float(loss.detach()), float(ref_loss), 'rel', abs(float(loss.detach())-float(ref_loss))/abs(float(ref_loss)))
+        for l, g in zip(leaves, ref_grads):
+            if l is not None: print('   grad rel', rel(l.grad.float(), g))
 """
 
 STAGES["retr_fp32"] = """
