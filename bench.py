@@ -351,7 +351,8 @@ def run_native(args):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps},
         "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks, "loss": loss_value,
-        "wall_s_timed_loop": t_wall,
+        "wall_s_timed_loop": t_wall, "step_ms": [round(v, 3) for v in step_ms],
+        "e2e_step_ms": [round(v, 3) for v in e2e_ms],
     }
 
     # ---------------- second half of the metric: bank scan ----------------
