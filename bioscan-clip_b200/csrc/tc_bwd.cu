@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
 
   if (warp == 0) {
     // ================= TMA producer: stages in exactly the order the MMA warp consumes them =================
-    if (lane == 0) {
+    if (ptx::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       auto next_stage = [&]() {
@@ -173,87 +173,83 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    constexpr uint32_t idesc_s = umma_idesc(BM, BN, FMT, FMT, 0, 0);   // S = X_I * Y_J^T, both K-major
-    constexpr uint32_t idesc_g = umma_idesc(BM, 128, 0, FMT, 0, 1);   // acc += G (fp16, K-major) * Y_J (MN-major)
-    int stage = 0;
-    uint32_t phase = 0;
-    uint32_t s_count = 0;    // S tiles issued so far (all items)
-    uint32_t g_count = 0;    // grad tiles issued so far
-    uint32_t item_count = 0;
-    auto next_stage = [&]() {
-      if (++stage == STAGES) {
-        stage = 0;
-        phase ^= 1u;
-      }
-    };
-    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++item_count) {
-      int xy, iblk, chunk;
-      decode_item(p, item, xy, iblk, chunk);
-      const int ng = chunk_groups(p, chunk);
-      auto issue_s = [&]() {
-        // the single S buffer is free once the epilogue has pulled the previous tile into registers
-        ptx::mbar_wait(ptx::smem_u32(&tail->s_free), (s_count & 1u) ^ 1u, 200);
-        ptx::tc_fence_after();
-        for (int kb = 0; kb < p.kblocks; ++kb) {
-          ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 300 + stage);
+    // ================= MMA issuer (one elected thread runs the whole role) =================
+    if (ptx::elect_one()) {
+      constexpr uint32_t idesc_s = umma_idesc(BM, BN, FMT, FMT, 0, 0);  // S = X_I * Y_J^T, both K-major
+      constexpr uint32_t idesc_g = umma_idesc(BM, 128, 0, FMT, 0, 1);  // acc += G (fp16, K-major) * Y_J (MN-major)
+      // descriptors differ only in the start-address field: desc(addr) = base + (addr >> 4)
+      const uint64_t desc_k = ptx::umma_desc_sw128(0, 16, 1024);     // K-major operands (X, Y for S; G for grad)
+      const uint64_t desc_mn = ptx::umma_desc_sw128(0, SLOT, 1024);  // Y tile read MN-major for the grad MMA
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t s_count = 0;  // S tiles issued so far (all items)
+      uint32_t g_count = 0;  // grad tiles issued so far
+      uint32_t item_count = 0;
+      auto next_stage = [&]() {
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      };
+      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++item_count) {
+        int xy, iblk, chunk;
+        decode_item(p, item, xy, iblk, chunk);
+        const int ng = chunk_groups(p, chunk);
+        auto issue_s = [&]() {
+          // the single S buffer is free once the epilogue has pulled the previous tile into registers
+          ptx::mbar_wait(ptx::smem_u32(&tail->s_free), (s_count & 1u) ^ 1u, 200);
           ptx::tc_fence_after();
-          if (lane == 0) {
+          for (int kb = 0; kb < p.kblocks; ++kb) {
+            ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 300 + stage);
+            ptx::tc_fence_after();
             const uint32_t sa = ring + stage * STAGE_BYTES;
-            const uint32_t sb = sa + SLOT;
+            const uint64_t da = desc_k + (uint64_t)(sa >> 4);
+            const uint64_t db = desc_k + (uint64_t)((sa + SLOT) >> 4);
 #pragma unroll
-            for (int k = 0; k < BK / 16; ++k) {
-              const uint64_t da = ptx::umma_desc_sw128(sa + k * 32, 16, 1024);
-              const uint64_t db = ptx::umma_desc_sw128(sb + k * 32, 16, 1024);
-              ptx::umma_f16(tmem_base, da, db, idesc_s, (kb | k) != 0 ? 1u : 0u);
-            }
+            for (int k = 0; k < BK / 16; ++k)
+              ptx::umma_f16(tmem_base, da + 2 * k, db + 2 * k, idesc_s, (kb | k) != 0 ? 1u : 0u);
             ptx::umma_commit(ptx::smem_u32(&tail->empty[stage]));
             if (kb == p.kblocks - 1) ptx::umma_commit(ptx::smem_u32(&tail->s_full));
+            next_stage();
           }
-          __syncwarp();
-          next_stage();
-        }
-        ++s_count;
-      };
-      auto issue_g = [&](int t) {
-        const uint32_t buf = g_count & 1u;
-        const uint32_t use = g_count >> 1;
-        if (t == 0) {
-          // first accumulation of the item overwrites TMEM: the previous item must have been drained
-          ptx::mbar_wait(ptx::smem_u32(&tail->acc_free), (item_count & 1u) ^ 1u, 210);
-        }
-        ptx::mbar_wait(ptx::smem_u32(&tail->g_ready[buf]), use & 1u, 220 + buf);
-        ptx::tc_fence_after();
-        for (int g = 0; g < ng; ++g) {
-          ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 310 + stage);
+          ++s_count;
+        };
+        auto issue_g = [&](int t) {
+          const uint32_t buf = g_count & 1u;
+          const uint32_t use = g_count >> 1;
+          if (t == 0) {
+            // first accumulation of the item overwrites TMEM: the previous item must have been drained
+            ptx::mbar_wait(ptx::smem_u32(&tail->acc_free), (item_count & 1u) ^ 1u, 210);
+          }
+          ptx::mbar_wait(ptx::smem_u32(&tail->g_ready[buf]), use & 1u, 220 + buf);
           ptx::tc_fence_after();
-          if (lane == 0) {
+          for (int g = 0; g < ng; ++g) {
+            ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 310 + stage);
+            ptx::tc_fence_after();
             const uint32_t sb = ring + stage * STAGE_BYTES;
-            const uint32_t ga = gbuf + buf * G_BYTES;
+            // A: G[128 x 128] K-major, two 64-column spans of 16 KB, 32 bytes per K=16 step inside a span
+            const uint64_t ga = desc_k + (uint64_t)((gbuf + buf * G_BYTES) >> 4);
+            // B: Y[j][d] read MN-major: 8-row (j) groups 1024 B apart, 64-column (d) groups one box apart
+            const uint64_t yb = desc_mn + (uint64_t)(sb >> 4);
             const uint32_t d_tmem = tmem_base + ACC_COL0 + g * 128;
 #pragma unroll
-            for (int kk = 0; kk < BN / 16; ++kk) {
-              // A: G[128 x 128] K-major, two 64-column spans of 16 KB; 32 bytes per K=16 step inside a span
-              const uint64_t da = ptx::umma_desc_sw128(ga + (kk >> 2) * SLOT + (kk & 3) * 32, 16, 1024);
-              // B: Yhat[j][d] read MN-major: 8-row (j) groups 1024 B apart, 64-column (d) groups one box apart
-              const uint64_t db = ptx::umma_desc_sw128(sb + kk * 2048, SLOT, 1024);
-              ptx::umma_f16(d_tmem, da, db, idesc_g, (t | kk) != 0 ? 1u : 0u);
-            }
+            for (int kk = 0; kk < BN / 16; ++kk)
+              ptx::umma_f16(d_tmem, ga + (uint64_t)(((kk >> 2) * SLOT + (kk & 3) * 32) >> 4), yb + (uint64_t)(kk * 128),
+                            idesc_g, (t | kk) != 0 ? 1u : 0u);
             ptx::umma_commit(ptx::smem_u32(&tail->empty[stage]));
             if (g == ng - 1) {
               ptx::umma_commit(ptx::smem_u32(&tail->g_free[buf]));
               if (t == T - 1) ptx::umma_commit(ptx::smem_u32(&tail->acc_full));
             }
+            next_stage();
           }
-          __syncwarp();
-          next_stage();
+          ++g_count;
+        };
+        issue_s();
+        for (int t = 0; t < T; ++t) {
+          if (t + 1 < T) issue_s();
+          issue_g(t);
         }
-        ++g_count;
-      };
-      issue_s();
-      for (int t = 0; t < T; ++t) {
-        if (t + 1 < T) issue_s();
-        issue_g(t);
       }
     }
   } else if (warp >= 4) {

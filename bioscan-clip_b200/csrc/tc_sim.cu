@@ -129,8 +129,8 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
   const uint32_t tmem_base = tail->tmem_base;
 
   if (warp == 0) {
-    // ================= TMA producer =================
-    if (lane == 0) {
+    // ================= TMA producer (one elected thread) =================
+    if (ptx::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
@@ -159,40 +159,39 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    constexpr uint32_t idesc = umma_idesc(BM, BN, FMT, FMT, 0, 0);
-    int stage = 0;
-    uint32_t phase = 0;
-    uint32_t tile_count = 0;
-    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
-      int pair, jchunk, iblk;
-      decode_item(p, item, pair, jchunk, iblk);
-      const int jt_end = min(p.n_jtile, (jchunk + 1) * p.jpc);
-      for (int jt = jchunk * p.jpc; jt < jt_end; ++jt, ++tile_count) {
-        const uint32_t buf = tile_count & 1u;
-        const uint32_t use = tile_count >> 1;
-        ptx::mbar_wait(ptx::smem_u32(&tail->tmem_empty[buf]), (use & 1u) ^ 1u, 200 + buf);
-        ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + buf * BN;
-        for (int kb = 0; kb < p.kblocks; ++kb) {
-          ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 300 + stage);
+    // ================= MMA issuer (one elected thread runs the whole role) =================
+    if (ptx::elect_one()) {
+      constexpr uint32_t idesc = umma_idesc(BM, BN, FMT, FMT, 0, 0);
+      // K-major SWIZZLE_128B descriptors differ only in the start-address field: desc(addr) = base + (addr >> 4)
+      const uint64_t desc0 = ptx::umma_desc_sw128(0, 16, 1024);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t tile_count = 0;
+      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+        int pair, jchunk, iblk;
+        decode_item(p, item, pair, jchunk, iblk);
+        const int jt_end = min(p.n_jtile, (jchunk + 1) * p.jpc);
+        for (int jt = jchunk * p.jpc; jt < jt_end; ++jt, ++tile_count) {
+          const uint32_t buf = tile_count & 1u;
+          const uint32_t use = tile_count >> 1;
+          ptx::mbar_wait(ptx::smem_u32(&tail->tmem_empty[buf]), (use & 1u) ^ 1u, 200 + buf);
           ptx::tc_fence_after();
-          if (lane == 0) {
+          const uint32_t d_tmem = tmem_base + buf * BN;
+          for (int kb = 0; kb < p.kblocks; ++kb) {
+            ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 300 + stage);
+            ptx::tc_fence_after();
             const uint32_t sa = ring + stage * STAGE_BYTES;
-            const uint32_t sb = sa + A_BYTES;
+            const uint64_t da = desc0 + (uint64_t)(sa >> 4);
+            const uint64_t db = desc0 + (uint64_t)((sa + A_BYTES) >> 4);
 #pragma unroll
-            for (int k = 0; k < BK / 16; ++k) {
-              const uint64_t da = ptx::umma_desc_sw128(sa + k * 32, 16, 1024);
-              const uint64_t db = ptx::umma_desc_sw128(sb + k * 32, 16, 1024);
-              ptx::umma_f16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
-            }
+            for (int k = 0; k < BK / 16; ++k)
+              ptx::umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
             ptx::umma_commit(ptx::smem_u32(&tail->empty[stage]));
             if (kb == p.kblocks - 1) ptx::umma_commit(ptx::smem_u32(&tail->tmem_full[buf]));
-          }
-          __syncwarp();
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1u;
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1u;
+            }
           }
         }
       }
