@@ -137,8 +137,9 @@ InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p) {
   };
   L.uv = take((size_t)6 * N * sizeof(float));
   L.gs = take(16 * sizeof(float));  // [6][2] {gs, 1/gs} per ordered pair, then [3] max inverse norms
-  L.rowpart = take((size_t)3 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
-  L.rowpos = take((size_t)3 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
+  // x2: the tensor-core forward sweep keeps one partial per epilogue warp group (tc_sim.cu NG)
+  L.rowpart = take((size_t)3 * 2 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
+  L.rowpos = take((size_t)3 * 2 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
   L.jrange = take((size_t)(L.n_jtile > 0 ? L.n_jtile : 1) * 2 * sizeof(int));
   L.colpart = take((size_t)3 * (L.n_iblk > 0 ? L.n_iblk : 1) * L.n_global_pad * sizeof(float));
   L.dxraw = take((size_t)3 * 2 * (n > 0 ? n : 1) * D * sizeof(float));

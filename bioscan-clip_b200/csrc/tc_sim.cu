@@ -26,6 +26,8 @@ constexpr int B_BYTES = BN * BK * 2;            // 32 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;  // 48 KB
 constexpr int TMEM_COLS = 512;
 constexpr int KTOP = 8;  // register-resident top-k capacity of the TOPK epilogue
+constexpr int NG = 2;    // epilogue warp groups: each takes BN / NG columns of every tile (2 warps per SM sub-partition)
+constexpr int NTHREADS = 128 + NG * 128;
 
 enum { EPI_STATS = 0, EPI_TOPK = 1 };
 
@@ -93,7 +95,7 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
 }
 
 template <int EPI, int FMT>
-__global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ SimParams p) {
+__global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_constant__ SimParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
   const uint32_t ring = (raw_addr + 1023u) & ~1023u;
@@ -110,7 +112,7 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
     }
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(ptx::smem_u32(&tail->tmem_full[b]), 1);
-      ptx::mbar_init(ptx::smem_u32(&tail->tmem_empty[b]), 4);
+      ptx::mbar_init(ptx::smem_u32(&tail->tmem_empty[b]), 4 * NG);
     }
     ptx::fence_barrier_init();
   }
@@ -198,9 +200,11 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
     }
   } else if (warp >= 4) {
     // ================= epilogue (4 warps, thread <-> TMEM lane) =================
-    const int q = warp & 3;
+    const int q = warp & 3;            // TMEM lane quarter this warp may read
+    const int grp = (warp - 4) >> 2;   // column group of the tile
+    constexpr int GC = BN / NG;        // columns per group
     const int row_in_tile = q * 32 + lane;
-    const int et = threadIdx.x - 128;  // 0..127
+    const int et = (threadIdx.x - 128) & 127;  // 0..127 inside the group
     uint32_t tile_count = 0;
     for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
       int pair, jchunk, iblk;
@@ -243,11 +247,11 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
         const int64_t col0 = (int64_t)jt * BN;
         if (EPI == EPI_STATS) {
           // stage k1 / ||b_j|| of the tile's columns (2 per thread) while the MMAs of this tile are in flight
-          for (int col = et; col < BN; col += 128) {
+          for (int col = grp * GC + et; col < (grp + 1) * GC; col += 128) {
             const int64_t j = col0 + col;
             tail->invb[buf][col] = j < p.b_rows ? p.k1 * invb_g[j] : 0.f;
           }
-          ptx::named_bar_sync(2, 128);
+          ptx::named_bar_sync(2 + 2 * grp, 128);
         }
         ptx::mbar_wait(ptx::smem_u32(&tail->tmem_full[buf]), use & 1u, 400 + buf);
         ptx::tc_fence_after();
@@ -261,7 +265,7 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
           tile_pos = (wmax >= jr.x) && (wmin <= jr.y);
         }
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
+        for (int c = grp * (GC / 32); c < (grp + 1) * (GC / 32); ++c) {
           uint32_t raw[32];
           ptx::tmem_ld_32x32(taddr + c * 32, raw);
           ptx::tmem_ld_wait();
@@ -331,9 +335,9 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
         if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tail->tmem_empty[buf]));
 
         if (EPI == EPI_STATS) {
-          ptx::named_bar_sync(1, 128);
+          ptx::named_bar_sync(1 + 2 * grp, 128);
           float* out = p.colpart + ((int64_t)pair * p.n_iblk + iblk) * p.b_pad + col0;
-          for (int col = et; col < BN; col += 128) {
+          for (int col = grp * GC + et; col < (grp + 1) * GC; col += 128) {
             if (col0 + col < p.b_rows)
               out[col] = (tail->cs[buf][0][col] + tail->cs[buf][1][col]) +
                          (tail->cs[buf][2][col] + tail->cs[buf][3][col]);
@@ -343,12 +347,12 @@ __global__ void __launch_bounds__(256, 1) tc_sim_kernel(const __grid_constant__ 
 
       if (EPI == EPI_STATS) {
         if (row_ok) {
-          p.rowpart[((int64_t)pair * p.n_jchunk + jchunk) * p.a_pad + arow] = rowsum;
-          p.rowpos[((int64_t)pair * p.n_jchunk + jchunk) * p.a_pad + arow] = rowpos;
+          p.rowpart[(((int64_t)pair * p.n_jchunk + jchunk) * NG + grp) * p.a_pad + arow] = rowsum;
+          p.rowpos[(((int64_t)pair * p.n_jchunk + jchunk) * NG + grp) * p.a_pad + arow] = rowpos;
         }
       } else {
         if (row_ok) {
-          const int64_t o = ((int64_t)jchunk * p.a_rows + arow) * p.k;
+          const int64_t o = (((int64_t)jchunk * NG + grp) * p.a_rows + arow) * p.k;
 #pragma unroll
           for (int t = 0; t < KTOP; ++t) {
             if (t < p.k) {
@@ -390,7 +394,7 @@ int launch_sim(const SimParams& p, cudaStream_t st) {
   }
   const int grid = p.num_items < num_sms() ? p.num_items : num_sms();
   if (grid <= 0) return BSC_OK;
-  kern<<<grid, 256, SIM_SMEM_BYTES, st>>>(p);
+  kern<<<grid, NTHREADS, SIM_SMEM_BYTES, st>>>(p);
   BSC_LAUNCH_CHECK("tc_sim_kernel");
   return BSC_OK;
 }
@@ -462,12 +466,12 @@ int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, float*
   timing_end(0, st);
   if (rc) return rc;
   // sum_ij T_ij (s*S_ij - s) over the local rows and all pairs, in natural-log units
-  rc = sum_rows_launch(p.rowpos, np * L.n_jchunk, L.n_local_pad, d->n_local, 0.6931471805599453f,
+  rc = sum_rows_launch(p.rowpos, np * L.n_jchunk * NG, L.n_local_pad, d->n_local, 0.6931471805599453f,
                        stats + 6 * d->n_global, st);
   if (rc) return rc;
   for (int q = 0; q < np; ++q) {
     const int a = p.pair_a[q], b = p.pair_b[q];
-    rc = reduce_parts_launch(p.rowpart + (int64_t)q * L.n_jchunk * L.n_local_pad, L.n_jchunk, L.n_local_pad,
+    rc = reduce_parts_launch(p.rowpart + (int64_t)q * L.n_jchunk * NG * L.n_local_pad, L.n_jchunk * NG, L.n_local_pad,
                              d->n_local, stats + (int64_t)pair_id(a, b) * d->n_global + d->row0, st);
     if (rc) return rc;
     rc = reduce_parts_launch(p.colpart + (int64_t)q * L.n_iblk * L.n_global_pad, L.n_iblk, L.n_global_pad,
@@ -495,7 +499,7 @@ size_t tc_bank_ws(int64_t nq, int64_t nb, int d, int k) {
   (void)d;
   int n_iblk, n_jtile, jpc, n_jchunk;
   bank_tiling(nq, nb, &n_iblk, &n_jtile, &jpc, &n_jchunk);
-  const size_t cand = (size_t)n_jchunk * (size_t)nq * (size_t)k;
+  const size_t cand = (size_t)n_jchunk * NG * (size_t)nq * (size_t)k;
   return align_up(cand * sizeof(float), 256) + align_up(cand * sizeof(int64_t), 256);
 }
 
@@ -529,10 +533,10 @@ int tc_bank_search(const void* q, int64_t nq, const void* bank, int64_t nb, int 
   p.b_rows = nb;
   p.k = k;
   p.base_id = base_id;
-  const size_t cand = (size_t)p.n_jchunk * (size_t)nq * (size_t)k;
+  const size_t cand = (size_t)p.n_jchunk * NG * (size_t)nq * (size_t)k;
   p.cand_s = (float*)ws;
   p.cand_i = (int64_t*)(ws + align_up(cand * sizeof(float), 256));
-  int parts = p.n_jchunk;
+  int parts = p.n_jchunk * NG;
   if (nb == 0) {
     // nothing to scan: the merge of zero parts writes the padding
     parts = 0;
