@@ -13,6 +13,8 @@
 // MMA issue order is software pipelined -- S(t+1) is queued before grad(t) -- so the tensor pipe executes
 // grad(t-1) while the epilogue is reading S(t) out of TMEM.
 // Warp roles (256 threads): 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator, 4..7 = epilogue.
+#include <cstdlib>
+
 #include "tc_common.cuh"
 
 namespace bsc {
@@ -203,8 +205,8 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
             ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 300 + stage);
             ptx::tc_fence_after();
             const uint32_t sa = ring + stage * STAGE_BYTES;
-            const uint64_t da = desc_k + (uint64_t)(sa >> 4);
-            const uint64_t db = desc_k + (uint64_t)((sa + SLOT) >> 4);
+            const uint64_t da = desc_k + ptx::desc_addr(sa);
+            const uint64_t db = desc_k + ptx::desc_addr(sa + SLOT);
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k)
               ptx::umma_f16(tmem_base, da + 2 * k, db + 2 * k, idesc_s, (kb | k) != 0 ? 1u : 0u);
@@ -228,9 +230,9 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
             ptx::tc_fence_after();
             const uint32_t sb = ring + stage * STAGE_BYTES;
             // A: G[128 x 128] K-major, two 64-column spans of 16 KB, 32 bytes per K=16 step inside a span
-            const uint64_t ga = desc_k + (uint64_t)((gbuf + buf * G_BYTES) >> 4);
+            const uint64_t ga = desc_k + ptx::desc_addr(gbuf + buf * G_BYTES);
             // B: Y[j][d] read MN-major: 8-row (j) groups 1024 B apart, 64-column (d) groups one box apart
-            const uint64_t yb = desc_mn + (uint64_t)(sb >> 4);
+            const uint64_t yb = desc_mn + ptx::desc_addr(sb);
             const uint32_t d_tmem = tmem_base + ACC_COL0 + g * 128;
 #pragma unroll
             for (int kk = 0; kk < BN / 16; ++kk)
@@ -382,6 +384,319 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Paired variant (d split in exactly two column chunks): the two CTAs of a 2-CTA cluster own the two chunks of the
+// SAME (ordered pair, row block).  S is computed once per column tile -- by CTA (t & 1) -- and the fp16 weight tile
+// is written into local shared memory and bulk-copied (cp.async.bulk shared::cta -> shared::cluster) into the
+// peer's, so the tensor cores execute
+// 2 + 2 instead of 2*2 + 2 GEMM-units per ordered pair.  G buffer b is always written by CTA b.
+//   g_ready[b]  CTA b: 4 arrivals per use (its epilogue warps); peer: 1 remote arrive.expect_tx + 32 KB of bulk-copy bytes
+//   g_free[b]   (CTA b only) 2 arrivals per use: the grad MMAs of both CTAs (tcgen05.commit multicast to CTA b)
+// ---------------------------------------------------------------------------------------------------------------
+template <int FMT>
+__global__ void __launch_bounds__(256, 1) tc_bwd_pair_kernel(const __grid_constant__ BwdParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t ring = ptx::smem_u32(smem_raw);
+  if ((ring & 1023u) != 0) {
+    if (threadIdx.x == 0) printf("bsc: dynamic shared memory is not 1024-byte aligned (0x%x)\n", ring);
+    __trap();
+  }
+  const uint32_t gbuf = ring + STAGES * STAGE_BYTES;
+  BwdSmemTail* tail = reinterpret_cast<BwdSmemTail*>(smem_raw + (size_t)STAGES * STAGE_BYTES + 2 * (size_t)G_BYTES);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t crank = ptx::cluster_ctarank();  // 0 / 1 = column chunk of D owned by this CTA
+  const uint32_t peer = crank ^ 1u;
+  const int cluster = (int)ptx::cluster_id_x();
+  const int n_clusters = (int)ptx::n_clusters_x();
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(ptx::smem_u32(&tail->full[s]), 1);
+      ptx::mbar_init(ptx::smem_u32(&tail->empty[s]), 1);
+    }
+    ptx::mbar_init(ptx::smem_u32(&tail->s_full), 1);
+    ptx::mbar_init(ptx::smem_u32(&tail->s_free), 4);
+    for (int b = 0; b < 2; ++b) {
+      // own buffer: the 4 local epilogue warps; peer's buffer: one remote arrive.expect_tx + the bulk copy's bytes
+      ptx::mbar_init(ptx::smem_u32(&tail->g_ready[b]), (uint32_t)b == crank ? 4u : 1u);
+      ptx::mbar_init(ptx::smem_u32(&tail->g_free[b]), 2);
+    }
+    ptx::mbar_init(ptx::smem_u32(&tail->acc_full), 1);
+    ptx::mbar_init(ptx::smem_u32(&tail->acc_free), 4);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&p.tmap[0]);
+    ptx::prefetch_tmap(&p.tmap[1]);
+    ptx::prefetch_tmap(&p.tmap[2]);
+  }
+  if (warp == 2) {
+    ptx::tmem_alloc(ptx::smem_u32(&tail->tmem_base), TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync_all();  // the peer's barriers are initialised before anything is signalled across CTAs
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = tail->tmem_base;
+  const int T = p.n_jtile;
+  const int chunk = (int)crank;
+  const int ng = chunk_groups(p, chunk);
+  const int dcol0 = chunk * p.groups_per_chunk * 128;
+
+  if (warp == 0) {
+    // ================= TMA producer: stages in exactly the order the MMA thread consumes them =================
+    if (ptx::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      auto next_stage = [&]() {
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      };
+      for (int item = cluster; item < p.num_items; item += n_clusters) {
+        const int iblk = item % p.n_iblk;
+        const int xy = item / p.n_iblk;
+        const CUtensorMap* mx = &p.tmap[p.xy_x[xy]];
+        const CUtensorMap* my = &p.tmap[p.xy_y[xy]];
+        const int xrow = (int)(p.row0 + (int64_t)iblk * BM);
+        auto load_s = [&](int t) {
+          for (int kb = 0; kb < p.kblocks; ++kb) {
+            ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 100 + stage);
+            const uint32_t full = ptx::smem_u32(&tail->full[stage]);
+            const uint32_t sa = ring + stage * STAGE_BYTES;
+            ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
+            ptx::tma_load_2d(sa, mx, full, kb * BK, xrow);
+            ptx::tma_load_2d(sa + SLOT, my, full, kb * BK, t * BN);
+            next_stage();
+          }
+        };
+        auto load_g = [&](int t) {
+          for (int g = 0; g < ng; ++g) {
+            ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 110 + stage);
+            const uint32_t full = ptx::smem_u32(&tail->full[stage]);
+            const uint32_t sa = ring + stage * STAGE_BYTES;
+            ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
+            ptx::tma_load_2d(sa, my, full, dcol0 + g * 128, t * BN);
+            ptx::tma_load_2d(sa + SLOT, my, full, dcol0 + g * 128 + 64, t * BN);
+            next_stage();
+          }
+        };
+        if ((int)crank < T) load_s((int)crank);
+        for (int t = 0; t < T; ++t) {
+          if ((uint32_t)(t & 1) == crank && t + 2 < T) load_s(t + 2);
+          load_g(t);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer (one elected thread) =================
+    if (ptx::elect_one()) {
+      constexpr uint32_t idesc_s = umma_idesc(BM, BN, FMT, FMT, 0, 0);
+      constexpr uint32_t idesc_g = umma_idesc(BM, 128, 0, FMT, 0, 1);
+      const uint64_t desc_k = ptx::umma_desc_sw128(0, 16, 1024);
+      const uint64_t desc_mn = ptx::umma_desc_sw128(0, SLOT, 1024);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t s_count = 0;          // S tiles issued by this CTA
+      uint32_t gu[2] = {0u, 0u};     // uses of weight-tile buffer 0 / 1 so far
+      uint32_t item_count = 0;
+      auto next_stage = [&]() {
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      };
+      for (int item = cluster; item < p.num_items; item += n_clusters, ++item_count) {
+        auto issue_s = [&]() {
+          ptx::mbar_wait(ptx::smem_u32(&tail->s_free), (s_count & 1u) ^ 1u, 200);
+          ptx::tc_fence_after();
+          for (int kb = 0; kb < p.kblocks; ++kb) {
+            ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 300 + stage);
+            ptx::tc_fence_after();
+            const uint32_t sa = ring + stage * STAGE_BYTES;
+            const uint64_t da = desc_k + ptx::desc_addr(sa);
+            const uint64_t db = desc_k + ptx::desc_addr(sa + SLOT);
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k)
+              ptx::umma_f16(tmem_base, da + 2 * k, db + 2 * k, idesc_s, (kb | k) != 0 ? 1u : 0u);
+            ptx::umma_commit(ptx::smem_u32(&tail->empty[stage]));
+            if (kb == p.kblocks - 1) ptx::umma_commit(ptx::smem_u32(&tail->s_full));
+            next_stage();
+          }
+          ++s_count;
+        };
+        auto issue_g = [&](int t) {
+          const uint32_t buf = (uint32_t)(t & 1);
+          if (t == 0) ptx::mbar_wait(ptx::smem_u32(&tail->acc_free), (item_count & 1u) ^ 1u, 210);
+          // the weight tile of column tile t was written (here and in the peer) by CTA `buf`
+          ptx::mbar_wait_cluster(ptx::smem_u32(&tail->g_ready[buf]), gu[buf] & 1u, 220 + buf);
+          ptx::fence_proxy_async_all();  // the tile may have been written by the peer CTA through DSMEM
+          ptx::tc_fence_after();
+          for (int g = 0; g < ng; ++g) {
+            ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 310 + stage);
+            ptx::tc_fence_after();
+            const uint32_t sb = ring + stage * STAGE_BYTES;
+            const uint64_t ga = desc_k + ptx::desc_addr(gbuf + buf * G_BYTES);
+            const uint64_t yb = desc_mn + ptx::desc_addr(sb);
+            const uint32_t d_tmem = tmem_base + ACC_COL0 + g * 128;
+#pragma unroll
+            for (int kk = 0; kk < BN / 16; ++kk)
+              ptx::umma_f16(d_tmem, ga + (uint64_t)(((kk >> 2) * SLOT + (kk & 3) * 32) >> 4), yb + (uint64_t)(kk * 128),
+                            idesc_g, (t | kk) != 0 ? 1u : 0u);
+            ptx::umma_commit(ptx::smem_u32(&tail->empty[stage]));
+            if (g == ng - 1) {
+              // tell the writer of this buffer (CTA `buf`) that this CTA's reads of it are done
+              ptx::umma_commit_mcast(ptx::smem_u32(&tail->g_free[buf]), (uint16_t)(1u << buf));
+              if (t == T - 1) ptx::umma_commit(ptx::smem_u32(&tail->acc_full));
+            }
+            next_stage();
+          }
+          ++gu[buf];
+        };
+        if ((int)crank < T) issue_s();
+        for (int t = 0; t < T; ++t) {
+          if ((uint32_t)(t & 1) == crank && t + 2 < T) issue_s();
+          issue_g(t);
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ================= epilogue: S (TMEM) -> weight tile in BOTH CTAs' shared memory; accumulator drain ==========
+    const int q = warp & 3;
+    const int row_in_tile = q * 32 + lane;
+    const int et = threadIdx.x - 128;
+    const float inv_k1 = 1.0f / p.k1;
+    const uint32_t my_gbuf = gbuf + crank * G_BYTES;          // the buffer this CTA writes (here and in the peer)
+    const uint32_t peer_gbuf = ptx::mapa(my_gbuf, peer);
+    const uint32_t my_ready = ptx::smem_u32(&tail->g_ready[crank]);
+    const uint32_t peer_ready = ptx::mapa(my_ready, peer);
+    uint32_t dcount = 0;  // duty tiles processed so far by this CTA (all items)
+    uint32_t item_count = 0;
+    for (int item = cluster; item < p.num_items; item += n_clusters, ++item_count) {
+      const int iblk = item % p.n_iblk;
+      const int xy = item / p.n_iblk;
+      const int x = p.xy_x[xy], y = p.xy_y[xy];
+      const int64_t arow = (int64_t)iblk * BM + row_in_tile;
+      const bool row_ok = arow < p.n_local;
+      const float gs = p.gsbuf[2 * pair_id(x, y)];
+      const float inv_i = row_ok ? p.inv[x][p.row0 + arow] : 0.f;
+      const float ugk = row_ok ? gs * inv_k1 * p.uv[(int64_t)pair_id(x, y) * p.n_global + p.row0 + arow] : 0.f;
+      const int rep_i = row_ok ? p.rep[p.row0 + arow] : -2;
+      const float m2gk = -2.0f * gs * inv_k1;
+      const float* vrow = p.uv + (int64_t)pair_id(y, x) * p.n_global;
+      const float* invy = p.inv[y];
+
+      for (int t = (int)crank; t < T; t += 2, ++dcount) {
+        ptx::named_bar_sync(2, 128);  // everyone is done with the previous tile's column facts
+        {
+          const int64_t j = (int64_t)t * BN + et;
+          const bool ok = j < p.n_global;
+          const float ij = ok ? invy[j] : 0.f;
+          tail->sc[et] = p.k1 * ij;
+          tail->vi[et] = ok ? gs * vrow[j] * ij : 0.f;
+          tail->repj[et] = ok ? p.rep[j] : -1;
+        }
+        ptx::named_bar_sync(1, 128);
+        ptx::mbar_wait(ptx::smem_u32(&tail->s_full), dcount & 1u, 400);
+        ptx::tc_fence_after();
+        // buffer `crank` was last read by the grad MMAs (of both CTAs) of this CTA's previous duty tile
+        ptx::mbar_wait_cluster(ptx::smem_u32(&tail->g_free[crank]), (dcount & 1u) ^ 1u, 410);
+
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+        const uint32_t goff = (uint32_t)(row_in_tile >> 3) * 1024u + (uint32_t)(row_in_tile & 7) * 128u;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t r0[32], r1[32];
+          ptx::tmem_ld_32x32(taddr + h * 64, r0);
+          ptx::tmem_ld_32x32(taddr + h * 64 + 32, r1);
+          ptx::tmem_ld_wait();
+          if (h == 1) {
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tail->s_free));
+          }
+          const float* sc = &tail->sc[h * 64];
+          const float* vi = &tail->vi[h * 64];
+          const int* rj = &tail->repj[h * 64];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            uint32_t pk[4];
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+              const int c = u * 8 + w * 2;
+              float gq[2];
+#pragma unroll
+              for (int z = 0; z < 2; ++z) {
+                const int cc = c + z;
+                const float dot = __uint_as_float(cc < 32 ? r0[cc & 31] : r1[cc & 31]);
+                const float scj = sc[cc];
+                const float e = ptx::ex2(fmaf(dot, inv_i * scj, -p.k2));
+                const float wgt = fmaf(ugk, scj, vi[cc]);
+                const float tv = (rj[cc] == rep_i) ? m2gk * scj : 0.f;
+                gq[z] = fmaf(e, wgt, tv);
+              }
+              const __half2 hh = __floats2half2_rn(gq[0], gq[1]);
+              pk[w] = *reinterpret_cast<const uint32_t*>(&hh);
+            }
+            const uint32_t off = goff + h * SLOT + ((uint32_t)(u ^ (row_in_tile & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_gbuf + off), "r"(pk[0]), "r"(pk[1]),
+                         "r"(pk[2]), "r"(pk[3])
+                         : "memory");
+          }
+        }
+        // generic-proxy writes (local and DSMEM) -> visible to both tensor cores' async-proxy reads, then signal
+        // generic-proxy writes -> async proxy; then the local tensor core may read the tile, and one thread ships it to
+        // the peer CTA with a shared::cta -> shared::cluster bulk copy that completes (in bytes) on the PEER's barrier
+        ptx::fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(my_ready);
+        ptx::named_bar_sync(3, 128);
+        if (et == 0) {
+          ptx::mbar_arrive_expect_tx_remote(peer_ready, G_BYTES);
+          ptx::bulk_copy_to_peer(peer_gbuf, my_gbuf, G_BYTES, peer_ready);
+        }
+      }
+
+      // ---- drain this CTA's accumulator chunk ----
+      ptx::mbar_wait(ptx::smem_u32(&tail->acc_full), item_count & 1u, 420);
+      ptx::tc_fence_after();
+      {
+        const int slot = p.xy_slot[xy];
+        float* out = p.dxraw + (((int64_t)(x * 2 + slot) * p.n_local + arow) * p.d) + (int64_t)dcol0;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + ACC_COL0;
+        for (int c = 0; c < ng * 4; ++c) {
+          uint32_t raw[32];
+          ptx::tmem_ld_32x32(taddr + c * 32, raw);
+          ptx::tmem_ld_wait();
+          if (row_ok) {
+#pragma unroll
+            for (int w = 0; w < 8; ++w) {
+              float4 v = make_float4(__uint_as_float(raw[w * 4]), __uint_as_float(raw[w * 4 + 1]),
+                                     __uint_as_float(raw[w * 4 + 2]), __uint_as_float(raw[w * 4 + 3]));
+              *reinterpret_cast<float4*>(out + c * 32 + w * 4) = v;
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tail->acc_free));
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync_all();  // neither CTA leaves while the other may still write into its shared memory
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
 int sm_count() {
   static int n = 0;
   if (n == 0) {
@@ -443,6 +758,39 @@ int tc_bwd_raw(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
   p.dxraw = (float*)(ws + L.dxraw);
   if (p.num_items == 0 || p.n_jtile == 0) return BSC_OK;
 
+  // two column chunks: CTA pairs share the S recompute through DSMEM (BSC_BWD_PAIR=0 forces the unpaired kernel)
+  static const bool pair_ok = []() {
+    const char* e = getenv("BSC_BWD_PAIR");
+    return !(e && e[0] == '0');
+  }();
+  if (p.n_chunks == 2 && pair_ok && sm_count() >= 2) {
+    auto pk = tc_bwd_pair_kernel<0>;
+    static bool pair_attr = false;
+    if (!pair_attr) {
+      BSC_CUDA(cudaFuncSetAttribute(pk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM_BYTES));
+      pair_attr = true;
+    }
+    p.num_items = n * p.n_iblk;  // the chunk is the cluster rank
+    int clusters = sm_count() / 2;
+    if (clusters > p.num_items) clusters = p.num_items;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(2 * clusters));
+    cfg.blockDim = dim3(256);
+    cfg.dynamicSmemBytes = BWD_SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    timing_begin(1, st);
+    BSC_CUDA(cudaLaunchKernelEx(&cfg, pk, p));
+    timing_end(1, st);
+    BSC_LAUNCH_CHECK("tc_bwd_pair_kernel");
+    return BSC_OK;
+  }
   auto kern = d->x16_dtype == BSC_BF16 ? tc_bwd_kernel<1> : tc_bwd_kernel<0>;
   static bool attr_done[2] = {false, false};
   const int ki = d->x16_dtype == BSC_BF16 ? 1 : 0;

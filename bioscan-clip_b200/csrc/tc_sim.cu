@@ -4,6 +4,8 @@
 //   EPI_STATS  exp(s*S - s) row sums and column sums            (InfoNCE forward, loss_func.py:46-51)
 //   EPI_TOPK   per-row running top-k over the B rows            (IndexFlatIP.search, inference_and_eval.py:421)
 // Warp roles (256 threads): 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator, 4..7 = epilogue.
+#include <cstdlib>
+
 #include "tc_common.cuh"
 
 namespace bsc {
@@ -183,8 +185,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
             ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 300 + stage);
             ptx::tc_fence_after();
             const uint32_t sa = ring + stage * STAGE_BYTES;
-            const uint64_t da = desc0 + (uint64_t)(sa >> 4);
-            const uint64_t db = desc0 + (uint64_t)((sa + A_BYTES) >> 4);
+            const uint64_t da = desc0 + ptx::desc_addr(sa);
+            const uint64_t db = desc0 + ptx::desc_addr(sa + A_BYTES);
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k)
               ptx::umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);

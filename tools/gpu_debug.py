@@ -87,6 +87,30 @@ for (n, d, pres, lab, sh) in [(256, 768, (1,1,0), 'arange', 0.5), (512, 768, (1,
             if l is not None: print('   grad rel', rel(l.grad.float(), g))
 """
 
+STAGES["pair_diag"] = """
+for (n, pres) in [(128, (1,1,0)), (256, (1,1,0)), (512, (1,1,1))]:
+    feats, labels = loss_inputs(n, 768, tuple(bool(p) for p in pres), seed=n+1, labels='arange', shared=0.5, dtype=torch.bfloat16)
+    ref_loss, ref_grads = loss_oracle.closed_form_grads([None if f is None else f.float() for f in feats], labels)
+    leaves = [None if f is None else f.float().cuda().requires_grad_(True) for f in feats]
+    loss = bsc.ContrastiveLoss(None, 1/0.07, precision='tc16')(*leaves, labels.cuda())
+    loss.backward(); torch.cuda.synchronize()
+    for m, (l, g) in enumerate(zip(leaves, ref_grads)):
+        if l is None: continue
+        e = (l.grad.double().cpu() - g).abs(); sc = g.abs().max()
+        print(n, 'mod', m, 'chunk0 err', (e[:, :384].max()/sc).item(), 'chunk1 err', (e[:, 384:].max()/sc).item(),
+              'rowblk errs', [(e[i:i+128].max()/sc).item() for i in range(0, n, 128)])
+        if n == 128 and m == 0:
+            # undo the projection to look at the raw sweep output: dx = (ghat - xh (xh.ghat))/|x| ; compare the component orthogonal to xh
+            o = l.grad.double().cpu(); xh = torch.nn.functional.normalize(feats[m].double(), dim=1)
+            for blk in range(6):
+                a = o[:, blk*128:(blk+1)*128]; b = g[:, blk*128:(blk+1)*128]
+                print('      colblk', blk, 'corr', (a*b).sum().item() / (a.norm()*b.norm()).item(), 'norm ratio', (a.norm()/b.norm()).item())
+            d = (o - g); print('      row err norms first 8 rows', [round(d[i, 384:].norm().item() / g[i, 384:].norm().item(), 3) for i in range(8)])
+            print('      row err norms rows 64..72', [round(d[i, 384:].norm().item() / g[i, 384:].norm().item(), 3) for i in range(64, 72)])
+        ratio = (l.grad.double().cpu() / g)
+        print('    median ratio chunk0', ratio[:, :384].median().item(), 'chunk1', ratio[:, 384:].median().item())
+"""
+
 STAGES["retr_fp32"] = """
 for (nb, nq, d, k) in [(333, 10, 40, 3), (5000, 257, 768, 5), (3, 4, 16, 5)]:
     bank, q, pi = bank_inputs(nb, nq, d, seed=nb)
