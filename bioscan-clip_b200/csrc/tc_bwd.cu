@@ -390,11 +390,11 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_kernel(const __grid_constant__ 
 // is written into local shared memory and bulk-copied (cp.async.bulk shared::cta -> shared::cluster) into the
 // peer's, so the tensor cores execute
 // 2 + 2 instead of 2*2 + 2 GEMM-units per ordered pair.  G buffer b is always written by CTA b.
-//   g_ready[b]  CTA b: 4 arrivals per use (its epilogue warps); peer: 1 remote arrive.expect_tx + 32 KB of bulk-copy bytes
+//   g_ready[b]  CTA b: 8 arrivals per use (its epilogue warps); peer: 8 remote arrive.expect_tx + 8 x 4 KB of bulk-copy bytes
 //   g_free[b]   (CTA b only) 2 arrivals per use: the grad MMAs of both CTAs (tcgen05.commit multicast to CTA b)
 // ---------------------------------------------------------------------------------------------------------------
 template <int FMT>
-__global__ void __launch_bounds__(256, 1) tc_bwd_pair_kernel(const __grid_constant__ BwdParams p) {
+__global__ void __launch_bounds__(384, 1) tc_bwd_pair_kernel(const __grid_constant__ BwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t ring = ptx::smem_u32(smem_raw);
   if ((ring & 1023u) != 0) {
@@ -417,14 +417,14 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_pair_kernel(const __grid_consta
       ptx::mbar_init(ptx::smem_u32(&tail->empty[s]), 1);
     }
     ptx::mbar_init(ptx::smem_u32(&tail->s_full), 1);
-    ptx::mbar_init(ptx::smem_u32(&tail->s_free), 4);
+    ptx::mbar_init(ptx::smem_u32(&tail->s_free), 8);
     for (int b = 0; b < 2; ++b) {
-      // own buffer: the 4 local epilogue warps; peer's buffer: one remote arrive.expect_tx + the bulk copy's bytes
-      ptx::mbar_init(ptx::smem_u32(&tail->g_ready[b]), (uint32_t)b == crank ? 4u : 1u);
+      // own buffer: the 8 local epilogue warps; peer's buffer: 8 remote arrive.expect_tx + the bulk copies' bytes
+      ptx::mbar_init(ptx::smem_u32(&tail->g_ready[b]), 8);
       ptx::mbar_init(ptx::smem_u32(&tail->g_free[b]), 2);
     }
     ptx::mbar_init(ptx::smem_u32(&tail->acc_full), 1);
-    ptx::mbar_init(ptx::smem_u32(&tail->acc_free), 4);
+    ptx::mbar_init(ptx::smem_u32(&tail->acc_free), 8);
     ptx::fence_barrier_init();
   }
   if (warp == 0 && lane == 0) {
@@ -565,15 +565,22 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_pair_kernel(const __grid_consta
       }
     }
   } else if (warp >= 4) {
-    // ================= epilogue: S (TMEM) -> weight tile in BOTH CTAs' shared memory; accumulator drain ==========
-    const int q = warp & 3;
+    // ================= epilogue (8 warps): S (TMEM) -> weight tile in BOTH CTAs' shared memory; accumulator drain =====
+    // warp e = warp - 4: TMEM lane quadrant q = e & 3 (rows 32q..32q+31), column span h = e >> 2 (64 columns).
+    // Per duty tile a thread turns 64 dot products into 64 fp16 weights.  The latency chain between the tensor
+    // pipes of the two CTAs is kept short: S is pulled out of TMEM and the weights are computed BEFORE waiting for
+    // the previous use of the weight buffer to retire, and every warp ships its own 4 KB piece to the peer.
+    const int e8 = warp - 4;
+    const int q = e8 & 3;
+    const int h = e8 >> 2;
     const int row_in_tile = q * 32 + lane;
-    const int et = threadIdx.x - 128;
+    const int et = threadIdx.x - 128;  // 0..255; threads < 128 also stage the column facts
     const float inv_k1 = 1.0f / p.k1;
     const uint32_t my_gbuf = gbuf + crank * G_BYTES;          // the buffer this CTA writes (here and in the peer)
     const uint32_t peer_gbuf = ptx::mapa(my_gbuf, peer);
     const uint32_t my_ready = ptx::smem_u32(&tail->g_ready[crank]);
     const uint32_t peer_ready = ptx::mapa(my_ready, peer);
+    const uint32_t piece = (uint32_t)h * SLOT + (uint32_t)q * 4096u;  // this warp's 32 rows x 128 B of span h
     uint32_t dcount = 0;  // duty tiles processed so far by this CTA (all items)
     uint32_t item_count = 0;
     for (int item = cluster; item < p.num_items; item += n_clusters, ++item_count) {
@@ -590,85 +597,105 @@ __global__ void __launch_bounds__(256, 1) tc_bwd_pair_kernel(const __grid_consta
       const float* vrow = p.uv + (int64_t)pair_id(y, x) * p.n_global;
       const float* invy = p.inv[y];
 
-      for (int t = (int)crank; t < T; t += 2, ++dcount) {
-        ptx::named_bar_sync(2, 128);  // everyone is done with the previous tile's column facts
-        {
+      // column facts of a duty tile, fetched one tile ahead into registers (threads et < 128, one column each)
+      float f_sc = 0.f, f_vi = 0.f;
+      int f_rep = -1;
+      auto fetch_facts = [&](int t) {
+        if (et < BN && t < T) {
           const int64_t j = (int64_t)t * BN + et;
           const bool ok = j < p.n_global;
           const float ij = ok ? invy[j] : 0.f;
-          tail->sc[et] = p.k1 * ij;
-          tail->vi[et] = ok ? gs * vrow[j] * ij : 0.f;
-          tail->repj[et] = ok ? p.rep[j] : -1;
+          f_sc = p.k1 * ij;
+          f_vi = ok ? gs * vrow[j] * ij : 0.f;
+          f_rep = ok ? p.rep[j] : -1;
         }
-        ptx::named_bar_sync(1, 128);
+      };
+      auto publish_facts = [&]() {
+        if (et < BN) {
+          tail->sc[et] = f_sc;
+          tail->vi[et] = f_vi;
+          tail->repj[et] = f_rep;
+        }
+      };
+      fetch_facts((int)crank);
+      ptx::named_bar_sync(2, 256);  // the previous item's last tile is done with the facts
+      publish_facts();
+      ptx::named_bar_sync(1, 256);
+
+      for (int t = (int)crank; t < T; t += 2, ++dcount) {
+        fetch_facts(t + 2);  // global loads in flight while this tile is processed
         ptx::mbar_wait(ptx::smem_u32(&tail->s_full), dcount & 1u, 400);
         ptx::tc_fence_after();
-        // buffer `crank` was last read by the grad MMAs (of both CTAs) of this CTA's previous duty tile
-        ptx::mbar_wait_cluster(ptx::smem_u32(&tail->g_free[crank]), (dcount & 1u) ^ 1u, 410);
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * 64);
+        uint32_t r0[32], r1[32];
+        ptx::tmem_ld_32x32(taddr, r0);
+        ptx::tmem_ld_32x32(taddr + 32, r1);
+        ptx::tmem_ld_wait();
+        // this warp's part of S is in registers: hand the TMEM tile back to the MMA thread
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tail->s_free));
 
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-        const uint32_t goff = (uint32_t)(row_in_tile >> 3) * 1024u + (uint32_t)(row_in_tile & 7) * 128u;
+        const float* sc = &tail->sc[h * 64];
+        const float* vi = &tail->vi[h * 64];
+        const int* rj = &tail->repj[h * 64];
+        uint32_t pk[32];
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          uint32_t r0[32], r1[32];
-          ptx::tmem_ld_32x32(taddr + h * 64, r0);
-          ptx::tmem_ld_32x32(taddr + h * 64 + 32, r1);
-          ptx::tmem_ld_wait();
-          if (h == 1) {
-            ptx::tc_fence_before();
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tail->s_free));
+        for (int c = 0; c < 64; c += 2) {
+          float gq[2];
+#pragma unroll
+          for (int z = 0; z < 2; ++z) {
+            const int cc = c + z;
+            const float dot = __uint_as_float(cc < 32 ? r0[cc & 31] : r1[cc & 31]);
+            const float scj = sc[cc];
+            const float ex = ptx::ex2(fmaf(dot, inv_i * scj, -p.k2));
+            const float wgt = fmaf(ugk, scj, vi[cc]);
+            const float tv = (rj[cc] == rep_i) ? m2gk * scj : 0.f;
+            gq[z] = fmaf(ex, wgt, tv);
           }
-          const float* sc = &tail->sc[h * 64];
-          const float* vi = &tail->vi[h * 64];
-          const int* rj = &tail->repj[h * 64];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            uint32_t pk[4];
-#pragma unroll
-            for (int w = 0; w < 4; ++w) {
-              const int c = u * 8 + w * 2;
-              float gq[2];
-#pragma unroll
-              for (int z = 0; z < 2; ++z) {
-                const int cc = c + z;
-                const float dot = __uint_as_float(cc < 32 ? r0[cc & 31] : r1[cc & 31]);
-                const float scj = sc[cc];
-                const float e = ptx::ex2(fmaf(dot, inv_i * scj, -p.k2));
-                const float wgt = fmaf(ugk, scj, vi[cc]);
-                const float tv = (rj[cc] == rep_i) ? m2gk * scj : 0.f;
-                gq[z] = fmaf(e, wgt, tv);
-              }
-              const __half2 hh = __floats2half2_rn(gq[0], gq[1]);
-              pk[w] = *reinterpret_cast<const uint32_t*>(&hh);
-            }
-            const uint32_t off = goff + h * SLOT + ((uint32_t)(u ^ (row_in_tile & 7)) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_gbuf + off), "r"(pk[0]), "r"(pk[1]),
-                         "r"(pk[2]), "r"(pk[3])
-                         : "memory");
-          }
+          const __half2 hh = __floats2half2_rn(gq[0], gq[1]);
+          pk[c >> 1] = *reinterpret_cast<const uint32_t*>(&hh);
         }
-        // generic-proxy writes (local and DSMEM) -> visible to both tensor cores' async-proxy reads, then signal
-        // generic-proxy writes -> async proxy; then the local tensor core may read the tile, and one thread ships it to
-        // the peer CTA with a shared::cta -> shared::cluster bulk copy that completes (in bytes) on the PEER's barrier
+        // buffer `crank` was last read by the grad MMAs (of both CTAs) of this CTA's previous duty tile; the barrier
+        // is signalled by tcgen05.commit, no data is acquired through it (write-after-read on shared memory only)
+        ptx::mbar_wait(ptx::smem_u32(&tail->g_free[crank]), (dcount & 1u) ^ 1u, 410);
+        const uint32_t goff = (uint32_t)h * SLOT + (uint32_t)(row_in_tile >> 3) * 1024u + (uint32_t)(row_in_tile & 7) * 128u;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const uint32_t off = goff + ((uint32_t)(u ^ (row_in_tile & 7)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_gbuf + off), "r"(pk[4 * u]), "r"(pk[4 * u + 1]),
+                       "r"(pk[4 * u + 2]), "r"(pk[4 * u + 3])
+                       : "memory");
+        }
+        // generic-proxy writes -> async proxy; then the local tensor core may read this warp's rows, and lane 0 ships
+        // them to the peer CTA with a shared::cta -> shared::cluster bulk copy that completes (in bytes) on the PEER's
+        // barrier (8 warps x {arrive.expect_tx 4096 + 4096 bytes} per use)
         ptx::fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(my_ready);
-        ptx::named_bar_sync(3, 128);
-        if (et == 0) {
-          ptx::mbar_arrive_expect_tx_remote(peer_ready, G_BYTES);
-          ptx::bulk_copy_to_peer(peer_gbuf, my_gbuf, G_BYTES, peer_ready);
+        if (lane == 0) {
+          ptx::mbar_arrive(my_ready);
+          ptx::mbar_arrive_expect_tx_remote(peer_ready, 4096u);
+          ptx::bulk_copy_to_peer(peer_gbuf + piece, my_gbuf + piece, 4096u, peer_ready);
+        }
+        // column facts of the next duty tile (off the critical path: the weight tile is already on its way)
+        if (t + 2 < T) {
+          ptx::named_bar_sync(2, 256);
+          publish_facts();
+          ptx::named_bar_sync(1, 256);
         }
       }
 
-      // ---- drain this CTA's accumulator chunk ----
+      // ---- drain this CTA's accumulator chunk: quadrant q, half h of the 32-column groups ----
       ptx::mbar_wait(ptx::smem_u32(&tail->acc_full), item_count & 1u, 420);
       ptx::tc_fence_after();
       {
         const int slot = p.xy_slot[xy];
         float* out = p.dxraw + (((int64_t)(x * 2 + slot) * p.n_local + arow) * p.d) + (int64_t)dcol0;
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + ACC_COL0;
-        for (int c = 0; c < ng * 4; ++c) {
+        const int nc = ng * 4;
+        const int c_lo = h == 0 ? 0 : nc / 2;
+        const int c_hi = h == 0 ? nc / 2 : nc;
+        for (int c = c_lo; c < c_hi; ++c) {
           uint32_t raw[32];
           ptx::tmem_ld_32x32(taddr + c * 32, raw);
           ptx::tmem_ld_wait();
@@ -775,7 +802,7 @@ int tc_bwd_raw(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
     if (clusters > p.num_items) clusters = p.num_items;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned)(2 * clusters));
-    cfg.blockDim = dim3(256);
+    cfg.blockDim = dim3(384);
     cfg.dynamicSmemBytes = BWD_SMEM_BYTES;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
