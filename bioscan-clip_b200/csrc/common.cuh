@@ -85,6 +85,8 @@ int simt_fwd_stats(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, floa
 int simt_bwd_raw(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st);
 int tc_fwd_stats(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, float* stats, cudaStream_t st);
 int tc_bwd_raw(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st);
+// CTA-pair (cta_group::2) sweep; returns 1 when the shape is not covered and the caller must use tc_bwd_raw's own kernels
+int tc_bwd_duo(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st);
 
 int simt_bank_search(const float* q, int64_t nq, const float* bank, int64_t nb, int d, int k, int64_t base_id,
                      float* out_s, int64_t* out_i, char* ws, size_t ws_bytes, cudaStream_t st);

@@ -48,6 +48,7 @@ struct BwdParams {
   const float* gsbuf;  // [6][2] {gs, 1/gs} per ordered pair
   const float* inv[3]; // inverse row norms per modality
   float* dxraw;        // [3][2][n_local][d]
+  int dbg_skip_tma;    // timing experiment only (BSC_DBG_SKIP_TMA=1): stages after the first ring round are not loaded
 };
 
 struct __align__(8) BwdSmemTail {
@@ -451,6 +452,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_pair_kernel(const __grid_consta
     if (ptx::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      uint32_t nloads = 0;
       auto next_stage = [&]() {
         if (++stage == STAGES) {
           stage = 0;
@@ -468,9 +470,14 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_pair_kernel(const __grid_consta
             ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 100 + stage);
             const uint32_t full = ptx::smem_u32(&tail->full[stage]);
             const uint32_t sa = ring + stage * STAGE_BYTES;
-            ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
-            ptx::tma_load_2d(sa, mx, full, kb * BK, xrow);
-            ptx::tma_load_2d(sa + SLOT, my, full, kb * BK, t * BN);
+            if (p.dbg_skip_tma && nloads >= STAGES) {
+              ptx::mbar_arrive(full);
+            } else {
+              ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
+              ptx::tma_load_2d(sa, mx, full, kb * BK, xrow);
+              ptx::tma_load_2d(sa + SLOT, my, full, kb * BK, t * BN);
+            }
+            ++nloads;
             next_stage();
           }
         };
@@ -479,9 +486,14 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_pair_kernel(const __grid_consta
             ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 110 + stage);
             const uint32_t full = ptx::smem_u32(&tail->full[stage]);
             const uint32_t sa = ring + stage * STAGE_BYTES;
-            ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
-            ptx::tma_load_2d(sa, my, full, dcol0 + g * 128, t * BN);
-            ptx::tma_load_2d(sa + SLOT, my, full, dcol0 + g * 128 + 64, t * BN);
+            if (p.dbg_skip_tma && nloads >= STAGES) {
+              ptx::mbar_arrive(full);
+            } else {
+              ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
+              ptx::tma_load_2d(sa, my, full, dcol0 + g * 128, t * BN);
+              ptx::tma_load_2d(sa + SLOT, my, full, dcol0 + g * 128 + 64, t * BN);
+            }
+            ++nloads;
             next_stage();
           }
         };
@@ -741,6 +753,10 @@ int tc_bwd_raw(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
   BSC_REQUIRE(d->d % 128 == 0, BSC_EUNSUPPORTED, "TC16 backward needs d %% 128 == 0 (got %d); use BSC_MODE_F32",
               d->d);
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
+  {
+    const int rc2 = tc_bwd_duo(d, L, ws, st);  // cta_group::2 sweep for d in {256, 512, 768}
+    if (rc2 <= 0) return rc2;
+  }
   BwdParams p{};
   int first = -1;
   for (int a = 0; a < 3; ++a)
@@ -783,6 +799,10 @@ int tc_bwd_raw(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
   p.rep = d->rep;
   p.gsbuf = (const float*)(ws + L.gs);
   p.dxraw = (float*)(ws + L.dxraw);
+  {
+    const char* e = getenv("BSC_DBG_SKIP_TMA");
+    p.dbg_skip_tma = (e && e[0] == '1') ? 1 : 0;
+  }
   if (p.num_items == 0 || p.n_jtile == 0) return BSC_OK;
 
   // two column chunks: CTA pairs share the S recompute through DSMEM (BSC_BWD_PAIR=0 forces the unpaired kernel)

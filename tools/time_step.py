@@ -1,0 +1,22 @@
+"""Kernel times of the bench workload (CUDA events inside the library): python tools/time_step.py [n] [steps]"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "bioscan-clip_b200"))
+import torch
+import bench, bsc
+from bsc import _lib
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 32768
+steps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
+torch.cuda.set_device(0)
+feats, labels = bench.synth_loss_rows(torch, n, 0, n, torch.device("cuda", 0), torch.bfloat16)
+crit = bsc.ContrastiveLoss(torch.nn.CrossEntropyLoss(), bench.SCALE, precision="tc16")
+_lib.set_timing(True)
+f, b = [], []
+for k in range(2 + steps):
+    leaves = [x.detach().requires_grad_(True) for x in feats]
+    loss = crit(leaves[0], leaves[1], leaves[2], labels)
+    loss.backward()
+    torch.cuda.synchronize()
+    if k >= 2:
+        f.append(_lib.last_kernel_ms(0)); b.append(_lib.last_kernel_ms(1))
+print("loss %.6f fwd_ms %.3f bwd_ms %.3f" % (float(loss.detach()), sum(f) / len(f), sum(b) / len(b)))
