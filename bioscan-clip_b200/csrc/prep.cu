@@ -160,18 +160,22 @@ int l2norm_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, voi
 
 // ---------------------------------------------------------------------------------------------
 // K2: label statistics.  Brute force over label tiles staged in shared memory: N^2 integer compares,
-// no N x N matrix.  Thread i scans j ascending, so rep/next come out as first matches.
+// no N x N matrix.  rep / next are minima over the matches, so they do not depend on how the scan is split.
 // ---------------------------------------------------------------------------------------------
 constexpr int kLabelTile = 2048;
 
+// 32 rows per block, 8 threads per row: thread (row, sub) scans elements sub, sub+8, ... of every staged tile and the 8
+// partial results are folded with shuffles (counts add, first / next are minima, so the result does not depend on the split).
 __global__ void __launch_bounds__(256) label_stats_kernel(const int64_t* __restrict__ labels, int64_t n,
                                                           float* __restrict__ r, int32_t* __restrict__ rep,
                                                           int32_t* __restrict__ next, int* __restrict__ rmax_bits) {
   __shared__ int64_t tile[kLabelTile];
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int sub = threadIdx.x & 7;
+  const int64_t i = (int64_t)blockIdx.x * 32 + (threadIdx.x >> 3);
   const int64_t mine = (i < n) ? labels[i] : 0;
+  constexpr int kNone = 0x7fffffff;
   int count = 0;
-  int first = -1, nxt = -1;
+  int first = kNone, nxt = kNone;
   for (int64_t base = 0; base < n; base += kLabelTile) {
     const int len = (int)min((int64_t)kLabelTile, n - base);
     __syncthreads();
@@ -179,22 +183,28 @@ __global__ void __launch_bounds__(256) label_stats_kernel(const int64_t* __restr
     __syncthreads();
     if (i < n) {
 #pragma unroll 8
-      for (int t = 0; t < len; ++t) {
+      for (int t = sub; t < len; t += 8) {
         const bool eq = (tile[t] == mine);
         const int j = (int)(base + t);
         count += eq ? 1 : 0;
-        if (eq && first < 0) first = j;
-        if (eq && nxt < 0 && j > (int)i) nxt = j;
+        if (eq) first = min(first, j);
+        if (eq && j > (int)i) nxt = min(nxt, j);
       }
     }
   }
-  if (i < n) {
+#pragma unroll
+  for (int o = 1; o < 8; o <<= 1) {
+    count += __shfl_xor_sync(0xffffffffu, count, o);
+    first = min(first, __shfl_xor_sync(0xffffffffu, first, o));
+    nxt = min(nxt, __shfl_xor_sync(0xffffffffu, nxt, o));
+  }
+  if (i < n && sub == 0) {
     r[i] = (float)count;
     rep[i] = first;
-    next[i] = nxt;
+    next[i] = nxt == kNone ? -1 : nxt;
   }
   // block max -> one atomic per warp (positive floats order like their bit patterns)
-  float c = (float)count;
+  float c = (i < n) ? (float)count : 0.f;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) c = fmaxf(c, __shfl_xor_sync(0xffffffffu, c, o));
   if ((threadIdx.x & 31) == 0) atomicMax(rmax_bits, __float_as_int(c));
@@ -204,7 +214,7 @@ int label_stats_launch(const int64_t* labels, int64_t n, float* r, int32_t* rep,
                        cudaStream_t st) {
   BSC_CUDA(cudaMemsetAsync(rmax, 0, sizeof(float), st));
   if (n == 0) return BSC_OK;
-  label_stats_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(labels, n, r, rep, next, (int*)rmax);
+  label_stats_kernel<<<(unsigned)((n + 31) / 32), 256, 0, st>>>(labels, n, r, rep, next, (int*)rmax);
   BSC_LAUNCH_CHECK("label_stats_kernel");
   return BSC_OK;
 }

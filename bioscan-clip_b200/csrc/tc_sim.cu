@@ -258,6 +258,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
         ptx::mbar_wait(ptx::smem_u32(&tail->tmem_full[buf]), use & 1u, 400 + buf);
         ptx::tc_fence_after();
         const bool edge = (col0 + BN > p.b_rows) || ((int64_t)iblk * BM + BM > p.a_rows);
+        const bool col_edge = col0 + BN > p.b_rows;
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN;
         float* cs = tail->cs[buf][q];
         const float* ivb = tail->invb[buf];
@@ -303,14 +304,27 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
             rowsum += s;
             cs[c * 32 + lane] = warp_colsum32(e, lane);
           } else {
+            // Scan path (always executed, kept tiny so it stays in the instruction cache): which of the 32 scores beat
+            // this row's current KTOP-th best?  Rare path: the union of those columns over the warp is re-read from
+            // TMEM one column at a time (uniform address) and inserted, ascending in id so ties keep the lower id.
             const int jbase = (int)(col0 + c * 32);
+            const float thr = ts[KTOP - 1];
+            uint32_t m = 0;
 #pragma unroll
-            for (int t = 0; t < 32; ++t) {
-              const float s = __uint_as_float(raw[t]);
-              const int j = jbase + t;
-              // candidate only if it beats the current KTOP-th best (ties keep the earlier = lower id);
+            for (int t = 0; t < 32; ++t) m |= (__uint_as_float(raw[t]) > thr) ? (1u << t) : 0u;
+            if (col_edge) {
               // zero-filled rows past the end of the bank never compete
-              if (s > ts[KTOP - 1] && j < p.b_rows) {
+              const int64_t valid = p.b_rows - jbase;
+              m &= valid >= 32 ? 0xffffffffu : (valid <= 0 ? 0u : ((1u << (int)valid) - 1u));
+            }
+            uint32_t um = __reduce_or_sync(0xffffffffu, m);
+            while (um) {
+              const int t = __ffs(um) - 1;
+              um &= um - 1;
+              const float s = __uint_as_float(ptx::tmem_ld_32x32_x1(taddr + c * 32 + t));
+              ptx::tmem_ld_wait();
+              if (((m >> t) & 1u) && s > ts[KTOP - 1]) {
+                const int j = jbase + t;
                 int pos = KTOP - 1;
 #pragma unroll
                 for (int u = KTOP - 1; u > 0; --u)
