@@ -11,7 +11,7 @@ all_gather of the normalised rows and the all_reduce of the sum-exp statistics.
 
 Printed (rank 0, ONE JSON line): metric/value/unit (samples/s, inputs resident in HBM, CUDA-event timed, max over
 ranks), e2e (same metric with pinned-host inputs copied in and loss + gradients copied out inside the timed
-region), roofline of the dominant kernel (the backward sweep; algorithmic FLOPs / CUDA-event kernel time /
+region, the copies of neighbouring steps overlapped with compute on separate streams), roofline of the dominant kernel (the backward sweep; algorithmic FLOPs / CUDA-event kernel time /
 MEASURED_PEAKS.json), cpu_baseline (oracle port on the host cores, bounded sample), clocks, gpu_launches, and a
 `retrieval` object with the second half of the metric (queries/s of the bank scan).
 """
@@ -275,52 +275,84 @@ def run_native(args):
     total_ms = float(total_ms.item())
     ms_per_step = total_ms / args.steps
     value = n_global / (ms_per_step * 1e-3)
-    loss_value = float(loss)
+    loss_value = float(loss.detach())
 
     # ---------------- e2e: pinned host buffers in, loss + gradients out ----------------
     host_in = [f.cpu().pin_memory() for f in feats]
     host_lab = labels.cpu().pin_memory()
     host_grad = [torch.empty_like(h).pin_memory() for h in host_in]
     host_loss = torch.empty((), dtype=torch.float32).pin_memory()
-    dev_in = [torch.empty_like(f) for f in feats]
-    dev_lab = torch.empty_like(labels)
     h2d = sum(h.numel() * h.element_size() for h in host_in) + host_lab.numel() * host_lab.element_size()
     d2h = sum(h.numel() * h.element_size() for h in host_grad) + 4
 
-    def step_e2e():
-        for dst, src in zip(dev_in, host_in):
-            dst.copy_(src, non_blocking=True)
-        dev_lab.copy_(host_lab, non_blocking=True)
-        leaves = [t.detach().requires_grad_(True) for t in dev_in]
-        if world > 1:
-            loss = crit(leaves[0], leaves[1], leaves[2], dev_lab, SCALE)
-        else:
-            loss = crit(leaves[0], leaves[1], leaves[2], dev_lab)
-        loss.backward()
-        for dst, leaf in zip(host_grad, leaves):
-            dst.copy_(leaf.grad, non_blocking=True)
-        host_loss.copy_(loss.detach(), non_blocking=True)
+    # Three streams, double-buffered device inputs: step k+1's inputs are copied in while step k computes, and step
+    # k's gradients are copied out while step k+1 computes.  Every step still moves ITS inputs from pinned host
+    # memory and ITS loss + gradients back to the host inside the timed region (first copy-in and last copy-out are
+    # not hidden and are included).
+    main = torch.cuda.current_stream()
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+    dev_in = [[torch.empty_like(f) for f in feats] for _ in range(2)]
+    dev_lab = [torch.empty_like(labels) for _ in range(2)]
+    ev_in = [torch.cuda.Event() for _ in range(2)]
+    ev_free = [torch.cuda.Event() for _ in range(2)]
+    ev_out = torch.cuda.Event()
 
-    e2e_steps = max(3, min(args.steps, 10))
-    for _ in range(2):
-        step_e2e()
+    def copy_in(b):
+        with torch.cuda.stream(s_in):
+            s_in.wait_event(ev_free[b])  # the step that last used buffer b has finished with it
+            for dst, src in zip(dev_in[b], host_in):
+                dst.copy_(src, non_blocking=True)
+            dev_lab[b].copy_(host_lab, non_blocking=True)
+            ev_in[b].record(s_in)
+
+    def run_e2e(nsteps):
+        keep = []
+        for b in range(2):
+            ev_free[b].record(main)
+        copy_in(0)
+        for k in range(nsteps):
+            b = k & 1
+            if k + 1 < nsteps:
+                copy_in(b ^ 1)
+            flush.zero_()
+            if world > 1:
+                dist.barrier()
+            main.wait_event(ev_in[b])
+            leaves = [t.detach().requires_grad_(True) for t in dev_in[b]]
+            if world > 1:
+                loss = crit(leaves[0], leaves[1], leaves[2], dev_lab[b], SCALE)
+            else:
+                loss = crit(leaves[0], leaves[1], leaves[2], dev_lab[b])
+            loss.backward()
+            ev_free[b].record(main)
+            done = torch.cuda.Event()
+            done.record(main)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(done)
+                for dst, leaf in zip(host_grad, leaves):
+                    dst.copy_(leaf.grad, non_blocking=True)
+                host_loss.copy_(loss.detach(), non_blocking=True)
+                ev_out.record(s_out)
+            keep.append((leaves, loss))  # gradients stay alive until their copy-out has run
+        main.wait_event(ev_out)
+        return keep
+
+    e2e_steps = max(10, min(args.steps, 40))
+    run_e2e(3)
     barrier()
-    e2e_ms = []
-    for k in range(e2e_steps):
-        flush.zero_()
-        if world > 1:
-            dist.barrier()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        step_e2e()
-        b.record()
-        b.synchronize()
-        e2e_ms.append(a.elapsed_time(b))
+    a, b_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    kept = run_e2e(e2e_steps)
+    b_ev.record()
+    b_ev.synchronize()
     barrier()
-    e2e_total = torch.tensor([sum(e2e_ms)], dtype=torch.float64, device=device)
+    del kept
+    e2e_ms = [a.elapsed_time(b_ev) / e2e_steps]
+    e2e_total = torch.tensor([a.elapsed_time(b_ev)], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(e2e_total, op=dist.ReduceOp.MAX)
     e2e_value = n_global / (float(e2e_total.item()) / e2e_steps * 1e-3)
+    e2e_loss = float(host_loss)
 
     # ---------------- roofline of the dominant kernel (backward sweep) ----------------
     peaks = measured_peaks()
@@ -332,8 +364,12 @@ def run_native(args):
     roofline = None
     if bwd_avg:
         ach = bwd_flops / (bwd_avg * 1e-3) / 1e12
-        roofline = {"bound": "tensor", "kernel": "tc_bwd_kernel", "achieved": ach, "peak": peaks["tflops_sustained"],
-                    "unit": "TFLOP/s", "frac": ach / peaks["tflops_sustained"], "traffic": None,
+        roofline = {"bound": "tensor", "achieved": ach, "peak": peaks["tflops_sustained"],
+                    "unit": "TFLOP/s", "frac": ach / peaks["tflops_sustained"],
+                    # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the `ncu --set full` capture
+                    # summarised in profiles/r1_bwd_duo.txt (taken at world=1, N=32768 only)
+                    "traffic": 2.164e9 if (world == 1 and n_global == 32768) else None, "traffic_unit": "B",
+                    "kernel": "tc_bwd_duo_kernel",
                     "peak_source": peaks["source"] + " bf16_tflops_sustained (kernel timed inside a long step)",
                     "kernel_ms": bwd_avg, "fwd_kernel_ms": fwd_avg,
                     "fwd_achieved": (fwd_flops / (fwd_avg * 1e-3) / 1e12) if fwd_avg else None,
@@ -349,7 +385,8 @@ def run_native(args):
                    "global_batch": n_global, "rows_per_gpu": n_local, "dim": DIM, "l2": "flushed between steps "
                    "(256 MiB write outside the event pair)", "parallelism": f"rows{world}"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e2e_steps},
+                "steps": e2e_steps, "loss_read_back": e2e_loss,
+                "pipeline": "copy-in / compute / copy-out on three streams, double-buffered inputs"},
         "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks, "loss": loss_value,
         "wall_s_timed_loop": t_wall, "step_ms": [round(v, 3) for v in step_ms],
         "e2e_step_ms": [round(v, 3) for v in e2e_ms],

@@ -480,45 +480,59 @@ int combine_launch(const CombineArgs& a, int x_dtype, cudaStream_t st) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// k-way merge of candidate lists (cross-CTA and cross-GPU): one thread per query, ordering
+// k-way merge of candidate lists (cross-CTA and cross-GPU): one warp per query, ordering
 // (score desc, id asc), ids < 0 are padding.
 // ---------------------------------------------------------------------------------------------
+// One warp per query.  Round t selects the best candidate that comes strictly after round t-1's pick in the total
+// order (score desc, id asc); ids are unique across parts, so no "taken" marks are needed and the result does not
+// depend on how the candidates are spread over lanes.
 __global__ void __launch_bounds__(128) topk_merge_kernel(const float* __restrict__ cs, const int64_t* __restrict__ ci,
                                                          int parts, int64_t nq, int k, float* __restrict__ os,
                                                          int64_t* __restrict__ oi) {
-  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int64_t q = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
   if (q >= nq) return;
-  constexpr int KMAX = 32;
-  float bs[KMAX];
-  int64_t bi[KMAX];
-  for (int t = 0; t < k; ++t) {
-    bs[t] = -3.4028234663852886e38f;
-    bi[t] = -1;
-  }
-  for (int p = 0; p < parts; ++p) {
-    for (int t = 0; t < k; ++t) {
-      const float s = cs[((int64_t)p * nq + q) * k + t];
-      const int64_t id = ci[((int64_t)p * nq + q) * k + t];
+  constexpr float kLowest = -3.4028234663852886e38f;
+  const int total = parts * k;
+  float prev_s = 0.f;
+  int64_t prev_i = -1;
+  int t = 0;
+  for (; t < k; ++t) {
+    float best_s = kLowest;
+    int64_t best_i = -1;
+    for (int c = lane; c < total; c += 32) {
+      const int64_t idx = ((int64_t)(c / k) * nq + q) * k + (c % k);
+      const int64_t id = ci[idx];
       if (id < 0) continue;
-      // insertion: better than slot u if higher score, or equal score and lower id
-      int pos = k;
-      for (int u = k - 1; u >= 0; --u) {
-        const bool better = (bi[u] < 0) || (s > bs[u]) || (s == bs[u] && id < bi[u]);
-        if (better) pos = u; else break;
-      }
-      if (pos < k) {
-        for (int u = k - 1; u > pos; --u) {
-          bs[u] = bs[u - 1];
-          bi[u] = bi[u - 1];
-        }
-        bs[pos] = s;
-        bi[pos] = id;
+      const float s = cs[idx];
+      const bool after_prev = (t == 0) || (s < prev_s) || (s == prev_s && id > prev_i);
+      const bool better = (best_i < 0) || (s > best_s) || (s == best_s && id < best_i);
+      if (after_prev && better) {
+        best_s = s;
+        best_i = id;
       }
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float s2 = __shfl_xor_sync(0xffffffffu, best_s, o);
+      const int64_t i2 = __shfl_xor_sync(0xffffffffu, best_i, o);
+      const bool take = (i2 >= 0) && ((best_i < 0) || (s2 > best_s) || (s2 == best_s && i2 < best_i));
+      if (take) {
+        best_s = s2;
+        best_i = i2;
+      }
+    }
+    if (best_i < 0) break;  // only padding is left
+    if (lane == 0) {
+      os[q * k + t] = best_s;
+      oi[q * k + t] = best_i;
+    }
+    prev_s = best_s;
+    prev_i = best_i;
   }
-  for (int t = 0; t < k; ++t) {
-    os[q * k + t] = bs[t];
-    oi[q * k + t] = bi[t];
+  for (int u = t + lane; u < k; u += 32) {
+    os[q * k + u] = kLowest;
+    oi[q * k + u] = -1;
   }
 }
 
@@ -529,7 +543,7 @@ int topk_merge_launch(const float* cs, const int64_t* ci, int parts, int64_t nq,
     set_error("bsc_topk_merge: k=%d > 32 unsupported", k);
     return BSC_EUNSUPPORTED;
   }
-  topk_merge_kernel<<<(unsigned)((nq + 127) / 128), 128, 0, st>>>(cs, ci, parts, nq, k, os, oi);
+  topk_merge_kernel<<<(unsigned)((nq + 3) / 4), 128, 0, st>>>(cs, ci, parts, nq, k, os, oi);
   BSC_LAUNCH_CHECK("topk_merge_kernel");
   return BSC_OK;
 }
