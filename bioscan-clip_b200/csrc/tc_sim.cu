@@ -22,10 +22,12 @@ namespace {
 constexpr int BM = kTcBM;    // 128
 constexpr int BN = kTcBNF;   // 256
 constexpr int BK = 64;       // one 128-byte swizzle span of 16-bit elements
-constexpr int STAGES = 4;
+constexpr int STAGES = 4;         // cta_group::1: 4 x 48 KB
+constexpr int STAGES2 = 6;        // cta_group::2: 6 x 32 KB (every CTA stages its A rows and HALF of the B tile)
 constexpr int A_BYTES = BM * BK * 2;            // 16 KB
 constexpr int B_BYTES = BN * BK * 2;            // 32 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;  // 48 KB
+constexpr int STAGE2_BYTES = A_BYTES + B_BYTES / 2;  // 32 KB
 constexpr int TMEM_COLS = 512;
 constexpr int KTOP = 8;  // register-resident top-k capacity of the TOPK epilogue
 constexpr int NG = 2;    // epilogue warp groups: each takes BN / NG columns of every tile (2 warps per SM sub-partition)
@@ -39,6 +41,7 @@ struct SimParams {
   int n_pairs;
   int pair_a[3], pair_b[3];
   int n_iblk, n_jtile, n_jchunk, jpc;
+  int n_iblk_items;  // row blocks per work item index: n_iblk (cta_group::1) or n_iblk / 2 (CTA pairs)
   int num_items;
   int kblocks;  // d / 64
   int64_t a_rows;    // valid A rows (local rows of the stripe)
@@ -61,8 +64,8 @@ struct SimParams {
 };
 
 struct __align__(8) SimSmemTail {
-  uint64_t full[STAGES];
-  uint64_t empty[STAGES];
+  uint64_t full[STAGES2];
+  uint64_t empty[STAGES2];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
   uint32_t tmem_base;
@@ -72,10 +75,11 @@ struct __align__(8) SimSmemTail {
 };
 
 constexpr size_t SIM_SMEM_BYTES = 1024 /*align slack*/ + (size_t)STAGES * STAGE_BYTES + sizeof(SimSmemTail);
+static_assert(STAGES2 * STAGE2_BYTES == STAGES * STAGE_BYTES, "both ring shapes use the same shared memory");
 
 __device__ __forceinline__ void decode_item(const SimParams& p, int item, int& pair, int& jchunk, int& iblk) {
-  iblk = item % p.n_iblk;
-  const int rest = item / p.n_iblk;
+  iblk = item % p.n_iblk_items;
+  const int rest = item / p.n_iblk_items;
   jchunk = rest % p.n_jchunk;
   pair = rest / p.n_jchunk;
 }
@@ -96,25 +100,34 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
   return v[0];
 }
 
-template <int EPI, int FMT>
+// PAIR = 1: the two CTAs of a 2-CTA cluster own two adjacent row blocks of the SAME column chunk and run every MMA as
+// one tcgen05.mma.cta_group::2 (M = 256, N = 256): each CTA stages its own 128 A rows and half of the B tile, which
+// cuts the shared-memory operand bytes per MMA cycle from 96 to 64 per SM (measured: the cta_group::1 sweep is bound by
+// operand fetch at ~62 % tensor-pipe activity).  The epilogue is unchanged: every CTA reads its own 128 x 256 fp32 tile.
+template <int EPI, int FMT, int PAIR>
 __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_constant__ SimParams p) {
+  constexpr int NST = PAIR ? STAGES2 : STAGES;
+  constexpr int SB = PAIR ? STAGE2_BYTES : STAGE_BYTES;
+  const uint32_t crank = PAIR ? ptx::cluster_ctarank() : 0u;
+  const int item0 = PAIR ? (int)ptx::cluster_id_x() : (int)blockIdx.x;
+  const int item_step = PAIR ? (int)ptx::n_clusters_x() : (int)gridDim.x;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
   const uint32_t ring = (raw_addr + 1023u) & ~1023u;
   uint8_t* ring_ptr = smem_raw + (ring - raw_addr);
-  SimSmemTail* tail = reinterpret_cast<SimSmemTail*>(ring_ptr + (size_t)STAGES * STAGE_BYTES);
+  SimSmemTail* tail = reinterpret_cast<SimSmemTail*>(ring_ptr + (size_t)NST * SB);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) {
+    for (int s = 0; s < NST; ++s) {
       ptx::mbar_init(ptx::smem_u32(&tail->full[s]), 1);
       ptx::mbar_init(ptx::smem_u32(&tail->empty[s]), 1);
     }
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(ptx::smem_u32(&tail->tmem_full[b]), 1);
-      ptx::mbar_init(ptx::smem_u32(&tail->tmem_empty[b]), 4 * NG);
+      ptx::mbar_init(ptx::smem_u32(&tail->tmem_empty[b]), (PAIR ? 2 : 1) * 4 * NG);
     }
     ptx::fence_barrier_init();
   }
@@ -124,11 +137,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
     ptx::prefetch_tmap(&p.tmap[2]);
   }
   if (warp == 2) {
-    ptx::tmem_alloc(ptx::smem_u32(&tail->tmem_base), TMEM_COLS);
-    ptx::tmem_relinquish();
+    if (PAIR) {
+      ptx::tmem_alloc_2cta(ptx::smem_u32(&tail->tmem_base), TMEM_COLS);
+      ptx::tmem_relinquish_2cta();
+    } else {
+      ptx::tmem_alloc(ptx::smem_u32(&tail->tmem_base), TMEM_COLS);
+      ptx::tmem_relinquish();
+    }
   }
   ptx::tc_fence_before();
   __syncthreads();
+  if (PAIR) ptx::cluster_sync_all();  // the peer's barriers and TMEM exist before anything crosses the pair
   ptx::tc_fence_after();
   const uint32_t tmem_base = tail->tmem_base;
 
@@ -137,9 +156,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
     if (ptx::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      for (int item = item0; item < p.num_items; item += item_step) {
         int pair, jchunk, iblk;
         decode_item(p, item, pair, jchunk, iblk);
+        if (PAIR) iblk = 2 * iblk + (int)crank;
         const CUtensorMap* ma = &p.tmap[p.pair_a[pair]];
         const CUtensorMap* mb = &p.tmap[p.pair_b[pair]];
         const int arow = (int)(p.a_row0 + (int64_t)iblk * BM);
@@ -149,12 +169,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
           for (int kb = 0; kb < p.kblocks; ++kb) {
             ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 100 + stage);
             const uint32_t full = ptx::smem_u32(&tail->full[stage]);
-            const uint32_t sa = ring + stage * STAGE_BYTES;
-            ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
-            ptx::tma_load_2d(sa, ma, full, kb * BK, arow);
-            ptx::tma_load_2d(sa + A_BYTES, mb, full, kb * BK, brow);
-            ptx::tma_load_2d(sa + A_BYTES + B_BYTES / 2, mb, full, kb * BK, brow + 128);
-            if (++stage == STAGES) {
+            const uint32_t sa = ring + stage * SB;
+            if (PAIR) {
+              // both CTAs' bytes complete on the leader's barrier; the leader expects the total
+              const uint32_t full_l = ptx::mapa(full, 0);
+              if (crank == 0) ptx::mbar_arrive_expect_tx(full, 2 * SB);
+              ptx::tma_load_2d_2cta(sa, ma, full_l, kb * BK, arow);
+              ptx::tma_load_2d_2cta(sa + A_BYTES, mb, full_l, kb * BK, brow + 128 * (int)crank);
+            } else {
+              ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
+              ptx::tma_load_2d(sa, ma, full, kb * BK, arow);
+              ptx::tma_load_2d(sa + A_BYTES, mb, full, kb * BK, brow);
+              ptx::tma_load_2d(sa + A_BYTES + B_BYTES / 2, mb, full, kb * BK, brow + 128);
+            }
+            if (++stage == NST) {
               stage = 0;
               phase ^= 1u;
             }
@@ -164,35 +192,46 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
     }
   } else if (warp == 1) {
     // ================= MMA issuer (one elected thread runs the whole role) =================
-    if (ptx::elect_one()) {
-      constexpr uint32_t idesc = umma_idesc(BM, BN, FMT, FMT, 0, 0);
+    if ((!PAIR || crank == 0) && ptx::elect_one()) {
+      constexpr uint32_t idesc = umma_idesc(PAIR ? 2 * BM : BM, BN, FMT, FMT, 0, 0);
       // K-major SWIZZLE_128B descriptors differ only in the start-address field: desc(addr) = base + (addr >> 4)
       const uint64_t desc0 = ptx::umma_desc_sw128(0, 16, 1024);
       int stage = 0;
       uint32_t phase = 0;
       uint32_t tile_count = 0;
-      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      for (int item = item0; item < p.num_items; item += item_step) {
         int pair, jchunk, iblk;
         decode_item(p, item, pair, jchunk, iblk);
         const int jt_end = min(p.n_jtile, (jchunk + 1) * p.jpc);
         for (int jt = jchunk * p.jpc; jt < jt_end; ++jt, ++tile_count) {
           const uint32_t buf = tile_count & 1u;
           const uint32_t use = tile_count >> 1;
-          ptx::mbar_wait(ptx::smem_u32(&tail->tmem_empty[buf]), (use & 1u) ^ 1u, 200 + buf);
+          if (PAIR)
+            ptx::mbar_wait_cluster(ptx::smem_u32(&tail->tmem_empty[buf]), (use & 1u) ^ 1u, 200 + buf);
+          else
+            ptx::mbar_wait(ptx::smem_u32(&tail->tmem_empty[buf]), (use & 1u) ^ 1u, 200 + buf);
           ptx::tc_fence_after();
           const uint32_t d_tmem = tmem_base + buf * BN;
           for (int kb = 0; kb < p.kblocks; ++kb) {
             ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 300 + stage);
             ptx::tc_fence_after();
-            const uint32_t sa = ring + stage * STAGE_BYTES;
+            const uint32_t sa = ring + stage * SB;
             const uint64_t da = desc0 + ptx::desc_addr(sa);
             const uint64_t db = desc0 + ptx::desc_addr(sa + A_BYTES);
+            if (PAIR) {
 #pragma unroll
-            for (int k = 0; k < BK / 16; ++k)
-              ptx::umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-            ptx::umma_commit(ptx::smem_u32(&tail->empty[stage]));
-            if (kb == p.kblocks - 1) ptx::umma_commit(ptx::smem_u32(&tail->tmem_full[buf]));
-            if (++stage == STAGES) {
+              for (int k = 0; k < BK / 16; ++k)
+                ptx::umma_f16_2cta(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+              ptx::umma_commit_2cta(ptx::smem_u32(&tail->empty[stage]), 3);
+              if (kb == p.kblocks - 1) ptx::umma_commit_2cta(ptx::smem_u32(&tail->tmem_full[buf]), 3);
+            } else {
+#pragma unroll
+              for (int k = 0; k < BK / 16; ++k)
+                ptx::umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+              ptx::umma_commit(ptx::smem_u32(&tail->empty[stage]));
+              if (kb == p.kblocks - 1) ptx::umma_commit(ptx::smem_u32(&tail->tmem_full[buf]));
+            }
+            if (++stage == NST) {
               stage = 0;
               phase ^= 1u;
             }
@@ -208,9 +247,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
     const int row_in_tile = q * 32 + lane;
     const int et = (threadIdx.x - 128) & 127;  // 0..127 inside the group
     uint32_t tile_count = 0;
-    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+    const uint32_t empty_l0 = PAIR ? ptx::mapa(ptx::smem_u32(&tail->tmem_empty[0]), 0) : 0u;
+    for (int item = item0; item < p.num_items; item += item_step) {
       int pair, jchunk, iblk;
       decode_item(p, item, pair, jchunk, iblk);
+      if (PAIR) iblk = 2 * iblk + (int)crank;
       const int64_t arow = (int64_t)iblk * BM + row_in_tile;  // row inside the stripe
       const bool row_ok = arow < p.a_rows;
       const int jt_end = min(p.n_jtile, (jchunk + 1) * p.jpc);
@@ -348,7 +389,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
         // release the accumulator buffer to the MMA warp
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tail->tmem_empty[buf]));
+        if (lane == 0) {
+          if (PAIR)
+            ptx::mbar_arrive_remote(empty_l0 + buf * 8u);  // the leader's barrier counts both CTAs' epilogue warps
+          else
+            ptx::mbar_arrive(ptx::smem_u32(&tail->tmem_empty[buf]));
+        }
 
         if (EPI == EPI_STATS) {
           ptx::named_bar_sync(1 + 2 * grp, 128);
@@ -383,9 +429,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
 
   ptx::tc_fence_before();
   __syncthreads();
+  if (PAIR) ptx::cluster_sync_all();
   if (warp == 2) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+    if (PAIR)
+      ptx::tmem_dealloc_2cta(tmem_base, TMEM_COLS);
+    else
+      ptx::tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
@@ -401,15 +451,53 @@ int num_sms() {
 }
 
 template <int EPI, int FMT>
-int launch_sim(const SimParams& p, cudaStream_t st) {
-  auto kern = tc_sim_kernel<EPI, FMT>;
+int launch_sim(const SimParams& p_in, cudaStream_t st) {
+  SimParams p = p_in;
+  p.n_iblk_items = p.n_iblk;
+  if (p.num_items <= 0) return BSC_OK;
+  // Measured (B200, N = 32768): the forward sweep already keeps the tensor pipe 80 % busy at the power-capped clock and
+  // is 9 % SLOWER on CTA pairs (3.85 vs 3.54 ms: two epilogues run in lock step); the bulk bank scan is 1 % faster.
+  // Default: pairs for the scan only.  BSC_SIM_PAIR=1 forces pairs everywhere, =0 disables them.
+  static const int pair_env = []() {
+    const char* e = getenv("BSC_SIM_PAIR");
+    return e ? (e[0] == '0' ? 0 : 1) : -1;
+  }();
+  const bool pair_ok = pair_env < 0 ? (EPI == EPI_TOPK) : (pair_env == 1);
+  // CTA pairs need an even number of row blocks (the two CTAs of a pair take blocks 2m and 2m+1 of one column chunk)
+  if (pair_ok && p.n_iblk >= 2 && (p.n_iblk % 2) == 0 && num_sms() >= 2) {
+    auto kern = tc_sim_kernel<EPI, FMT, 1>;
+    static bool attr_done = false;
+    if (!attr_done) {
+      BSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SIM_SMEM_BYTES));
+      attr_done = true;
+    }
+    p.n_iblk_items = p.n_iblk / 2;
+    p.num_items = p.num_items / 2;
+    int clusters = num_sms() / 2;
+    if (clusters > p.num_items) clusters = p.num_items;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(2 * clusters));
+    cfg.blockDim = dim3(NTHREADS);
+    cfg.dynamicSmemBytes = SIM_SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    BSC_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
+    BSC_LAUNCH_CHECK("tc_sim_kernel (CTA pairs)");
+    return BSC_OK;
+  }
+  auto kern = tc_sim_kernel<EPI, FMT, 0>;
   static bool attr_done = false;
   if (!attr_done) {
     BSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SIM_SMEM_BYTES));
     attr_done = true;
   }
   const int grid = p.num_items < num_sms() ? p.num_items : num_sms();
-  if (grid <= 0) return BSC_OK;
   kern<<<grid, NTHREADS, SIM_SMEM_BYTES, st>>>(p);
   BSC_LAUNCH_CHECK("tc_sim_kernel");
   return BSC_OK;
