@@ -19,7 +19,7 @@ MODE_F32, MODE_TC16 = 0, 1
 NORM_TORCH, NORM_SKLEARN = 0, 1
 
 EXPORTS = [
-    "bsc_version", "bsc_last_error", "bsc_device_check", "bsc_l2norm_fwd", "bsc_rows_to_f16", "bsc_label_stats",
+    "bsc_version", "bsc_last_error", "bsc_device_check", "bsc_l2norm_fwd", "bsc_rows_to_f16", "bsc_label_stats", "bsc_label_stats_workspace_bytes",
     "bsc_infonce_stats_len", "bsc_infonce_workspace_bytes", "bsc_infonce_fwd", "bsc_infonce_loss",
     "bsc_infonce_bwd", "bsc_bank_search_workspace_bytes", "bsc_bank_search", "bsc_topk_merge",
     "bsc_set_timing", "bsc_last_kernel_ms", "bsc_launch_count",
@@ -57,7 +57,9 @@ def lib():
     L.bsc_l2norm_fwd.argtypes = [c_void_p, c_int, c_int64, c_int, c_int64, c_void_p, c_int, c_void_p, c_void_p,
                                  c_int, c_void_p]
     L.bsc_rows_to_f16.argtypes = [c_void_p, c_int, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p]
-    L.bsc_label_stats.argtypes = [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
+    L.bsc_label_stats.argtypes = [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                                  c_void_p]
+    L.bsc_label_stats_workspace_bytes.argtypes = [c_int64, POINTER(c_size_t)]
     L.bsc_infonce_stats_len.argtypes = [c_int64]
     L.bsc_infonce_stats_len.restype = c_int64
     L.bsc_infonce_workspace_bytes.argtypes = [POINTER(InfoNceDesc), POINTER(c_size_t)]

@@ -84,9 +84,12 @@ class CudaOps:
         rep = torch.empty(n, dtype=torch.int32, device=dev)
         nxt = torch.empty(n, dtype=torch.int32, device=dev)
         rmax = torch.empty(1, dtype=torch.float32, device=dev)
+        nbytes = c_size_t(0)
+        check(lib().bsc_label_stats_workspace_bytes(n, byref(nbytes)))
+        ws = torch.empty(int(nbytes.value), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             check(lib().bsc_label_stats(labels.data_ptr(), n, r.data_ptr(), rep.data_ptr(), nxt.data_ptr(),
-                                        rmax.data_ptr(), stream_ptr(dev)))
+                                        rmax.data_ptr(), ws.data_ptr(), ws.numel(), stream_ptr(dev)))
         return r, rep, nxt, rmax
 
     # ---- InfoNCE --------------------------------------------------------------------------------

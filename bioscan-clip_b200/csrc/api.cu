@@ -13,7 +13,8 @@ int l2norm_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, voi
                   float* inv_norm, int zero_rule, cudaStream_t st);
 int rows_to_f16_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, float* inv,
                        cudaStream_t st);
-int label_stats_launch(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
+size_t label_stats_ws_bytes(int64_t n);
+int label_stats_launch(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax, char* ws,
                        cudaStream_t st);
 int loss_launch(const float* stats, const float* r, int64_t n, unsigned present_mask, float scale, float* loss,
                 cudaStream_t st);
@@ -225,11 +226,19 @@ int bsc_rows_to_f16(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, v
   return rows_to_f16_launch(x, x_dtype, n, d, ldx, y16, inv, (cudaStream_t)stream);
 }
 
+int bsc_label_stats_workspace_bytes(int64_t n, size_t* bytes) {
+  BSC_REQUIRE(bytes && n >= 0 && n < (1ll << 30), BSC_EINVAL, "bsc_label_stats_workspace_bytes: bad arguments");
+  *bytes = label_stats_ws_bytes(n);
+  return BSC_OK;
+}
+
 int bsc_label_stats(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
-                    void* stream) {
+                    void* workspace, size_t workspace_bytes, void* stream) {
   BSC_REQUIRE(labels && r && rep && next && rmax, BSC_EINVAL, "bsc_label_stats: null pointer");
-  BSC_REQUIRE(n >= 0 && n < (1ll << 31), BSC_EINVAL, "bsc_label_stats: n out of range");
-  return label_stats_launch(labels, n, r, rep, next, rmax, (cudaStream_t)stream);
+  BSC_REQUIRE(n >= 0 && n < (1ll << 30), BSC_EINVAL, "bsc_label_stats: n out of range");
+  BSC_REQUIRE(workspace && workspace_bytes >= label_stats_ws_bytes(n), BSC_EWORKSPACE,
+              "bsc_label_stats: workspace too small");
+  return label_stats_launch(labels, n, r, rep, next, rmax, (char*)workspace, (cudaStream_t)stream);
 }
 
 int64_t bsc_infonce_stats_len(int64_t n_global) { return 6 * n_global + kStatsExtra; }

@@ -159,63 +159,143 @@ int l2norm_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, voi
 }
 
 // ---------------------------------------------------------------------------------------------
-// K2: label statistics.  Brute force over label tiles staged in shared memory: N^2 integer compares,
-// no N x N matrix.  rep / next are minima over the matches, so they do not depend on how the scan is split.
+// K2: label statistics without an N x N matrix and (for the reference's default labels) without N^2 work.
+//   1. every row inserts its label into an open-addressing table (slot = index of the first row that claimed it);
+//      the claimer is the class "head".  count[head] += 1, minidx[head] = min(minidx[head], i): both results are
+//      independent of the order in which the atomics land.
+//   2. r[i] = count[head_i], rep[i] = minidx[head_i], rmax = max r.
+//   3. next[i] = min{j > i : label_j == label_i}: only row blocks that contain a row with r > 1 scan the labels
+//      (tiles staged in shared memory); with labels = arange (util/dataset.py:147) no block does.
 // ---------------------------------------------------------------------------------------------
 constexpr int kLabelTile = 2048;
 
-// 32 rows per block, 8 threads per row: thread (row, sub) scans elements sub, sub+8, ... of every staged tile and the 8
-// partial results are folded with shuffles (counts add, first / next are minima, so the result does not depend on the split).
-__global__ void __launch_bounds__(256) label_stats_kernel(const int64_t* __restrict__ labels, int64_t n,
-                                                          float* __restrict__ r, int32_t* __restrict__ rep,
-                                                          int32_t* __restrict__ next, int* __restrict__ rmax_bits) {
+__device__ __forceinline__ uint32_t label_hash(int64_t v) {
+  uint64_t x = (uint64_t)v;
+  x ^= x >> 33;
+  x *= 0xff51afd7ed558ccdull;
+  x ^= x >> 33;
+  x *= 0xc4ceb9fe1a85ec53ull;
+  x ^= x >> 33;
+  return (uint32_t)x;
+}
+
+__global__ void __launch_bounds__(256) label_insert_kernel(const int64_t* __restrict__ labels, int64_t n, int* slots,
+                                                           uint32_t mask, int* __restrict__ head, int* count,
+                                                           int* minidx) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int64_t key = labels[i];
+  uint32_t h = label_hash(key) & mask;
+  int hd;
+  for (;;) {
+    int cur = ((volatile int*)slots)[h];
+    if (cur < 0) {
+      const int old = atomicCAS(&slots[h], -1, (int)i);
+      if (old < 0) {
+        hd = (int)i;
+        break;
+      }
+      cur = old;
+    }
+    if (labels[cur] == key) {
+      hd = cur;
+      break;
+    }
+    h = (h + 1) & mask;
+  }
+  head[i] = hd;
+  atomicAdd(&count[hd], 1);
+  atomicMin(&minidx[hd], (int)i);
+}
+
+__global__ void __launch_bounds__(256) label_finish_kernel(int64_t n, const int* __restrict__ head,
+                                                           const int* __restrict__ count, const int* __restrict__ minidx,
+                                                           float* __restrict__ r, int32_t* __restrict__ rep,
+                                                           int* __restrict__ rmax_bits) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  float c = 0.f;
+  if (i < n) {
+    const int hd = head[i];
+    c = (float)count[hd];
+    r[i] = c;
+    rep[i] = minidx[hd];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c = fmaxf(c, __shfl_xor_sync(0xffffffffu, c, o));
+  // positive floats order like their bit patterns
+  if ((threadIdx.x & 31) == 0) atomicMax(rmax_bits, __float_as_int(c));
+}
+
+// 32 rows per block, 8 threads per row; a block whose rows are all alone in their class has nothing to look for.
+__global__ void __launch_bounds__(256) label_next_kernel(const int64_t* __restrict__ labels, int64_t n,
+                                                         const float* __restrict__ r, int32_t* __restrict__ next) {
   __shared__ int64_t tile[kLabelTile];
   const int sub = threadIdx.x & 7;
   const int64_t i = (int64_t)blockIdx.x * 32 + (threadIdx.x >> 3);
+  const bool multi = i < n && r[i] > 1.5f;
+  if (!__syncthreads_or(multi ? 1 : 0)) {
+    if (i < n && sub == 0) next[i] = -1;
+    return;
+  }
   const int64_t mine = (i < n) ? labels[i] : 0;
   constexpr int kNone = 0x7fffffff;
-  int count = 0;
-  int first = kNone, nxt = kNone;
-  for (int64_t base = 0; base < n; base += kLabelTile) {
+  int nxt = kNone;
+  // members after row i can only live in tiles at or after row i's own tile
+  const int64_t base0 = ((int64_t)blockIdx.x * 32 / kLabelTile) * kLabelTile;
+  for (int64_t base = base0; base < n; base += kLabelTile) {
     const int len = (int)min((int64_t)kLabelTile, n - base);
     __syncthreads();
     for (int t = threadIdx.x; t < len; t += blockDim.x) tile[t] = labels[base + t];
     __syncthreads();
-    if (i < n) {
+    if (multi) {
 #pragma unroll 8
       for (int t = sub; t < len; t += 8) {
-        const bool eq = (tile[t] == mine);
         const int j = (int)(base + t);
-        count += eq ? 1 : 0;
-        if (eq) first = min(first, j);
-        if (eq && j > (int)i) nxt = min(nxt, j);
+        if (tile[t] == mine && j > (int)i) nxt = min(nxt, j);
       }
     }
+    // all members found so far are minima of their sub-sequence; a hit in this tile ends the search for the row
+    int found = nxt != kNone ? 1 : 0;
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) found |= __shfl_xor_sync(0xffffffffu, found, o);
+    if (__syncthreads_and((!multi || found) ? 1 : 0)) break;
   }
 #pragma unroll
-  for (int o = 1; o < 8; o <<= 1) {
-    count += __shfl_xor_sync(0xffffffffu, count, o);
-    first = min(first, __shfl_xor_sync(0xffffffffu, first, o));
-    nxt = min(nxt, __shfl_xor_sync(0xffffffffu, nxt, o));
-  }
-  if (i < n && sub == 0) {
-    r[i] = (float)count;
-    rep[i] = first;
-    next[i] = nxt == kNone ? -1 : nxt;
-  }
-  // block max -> one atomic per warp (positive floats order like their bit patterns)
-  float c = (i < n) ? (float)count : 0.f;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) c = fmaxf(c, __shfl_xor_sync(0xffffffffu, c, o));
-  if ((threadIdx.x & 31) == 0) atomicMax(rmax_bits, __float_as_int(c));
+  for (int o = 1; o < 8; o <<= 1) nxt = min(nxt, __shfl_xor_sync(0xffffffffu, nxt, o));
+  if (i < n && sub == 0) next[i] = nxt == kNone ? -1 : nxt;
+}
+
+static uint32_t label_table_slots(int64_t n) {
+  uint32_t m = 1024;
+  while ((int64_t)m < 2 * n) m <<= 1;
+  return m;
+}
+
+size_t label_stats_ws_bytes(int64_t n) {
+  // slots[m] | head[n] | count[n] | minidx[n], all int32
+  return align_up((size_t)label_table_slots(n) * 4, 256) + 3 * align_up((size_t)(n > 0 ? n : 1) * 4, 256);
 }
 
 int label_stats_launch(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
-                       cudaStream_t st) {
+                       char* ws, cudaStream_t st) {
   BSC_CUDA(cudaMemsetAsync(rmax, 0, sizeof(float), st));
   if (n == 0) return BSC_OK;
-  label_stats_kernel<<<(unsigned)((n + 31) / 32), 256, 0, st>>>(labels, n, r, rep, next, (int*)rmax);
-  BSC_LAUNCH_CHECK("label_stats_kernel");
+  const uint32_t m = label_table_slots(n);
+  const size_t nb = align_up((size_t)n * 4, 256);
+  int* slots = (int*)ws;
+  int* head = (int*)(ws + align_up((size_t)m * 4, 256));
+  int* count = (int*)((char*)head + nb);
+  int* minidx = (int*)((char*)count + nb);
+  BSC_CUDA(cudaMemsetAsync(slots, 0xff, (size_t)m * 4, st));   // -1 = empty
+  BSC_CUDA(cudaMemsetAsync(count, 0, (size_t)n * 4, st));
+  BSC_CUDA(cudaMemsetAsync(minidx, 0x7f, (size_t)n * 4, st));  // 0x7f7f7f7f > any row index
+  const unsigned grid = (unsigned)((n + 255) / 256);
+  label_insert_kernel<<<grid, 256, 0, st>>>(labels, n, slots, m - 1, head, count, minidx);
+  BSC_LAUNCH_CHECK("label_insert_kernel");
+  label_finish_kernel<<<grid, 256, 0, st>>>(n, head, count, minidx, r, rep, (int*)rmax);
+  BSC_LAUNCH_CHECK("label_finish_kernel");
+  label_next_kernel<<<(unsigned)((n + 31) / 32), 256, 0, st>>>(labels, n, r, next);
+  BSC_LAUNCH_CHECK("label_next_kernel");
   return BSC_OK;
 }
 

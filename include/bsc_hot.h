@@ -82,9 +82,11 @@ int bsc_rows_to_f16(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, v
  *     rep[i]  = min{j : labels[j] == labels[i]}    (class representative)
  *     next[i] = min{j > i : labels[j] == labels[i]} or -1
  *     rmax[0] = max_i r[i] (float)
+ *     workspace: caller-owned device scratch of bsc_label_stats_workspace_bytes(n) bytes (hash table of the labels).
  * ---------------------------------------------------------------------------------------------- */
+int bsc_label_stats_workspace_bytes(int64_t n, size_t* bytes);
 int bsc_label_stats(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
-                    void* stream);
+                    void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * InfoNCE loss -- ContrastiveLoss.forward / ClipLoss.forward.

@@ -94,6 +94,8 @@ TC16_CASES = [
     (1000, 768, (True, True, True), "arange", 0.5),     # ragged N (not a tile multiple)
     (384, 256, (True, False, True), "multi", 0.0),      # flat softmax, d = 2 column groups
     (2048, 768, (True, True, True), "arange", 0.5),
+    (640, 512, (True, True, True), "multi", 0.5),       # odd number of column tiles (pair sweep pads one), d = 2 x 256
+    (130, 768, (False, True, True), "multi", 0.5),      # two row blocks, the second almost empty
 ]
 
 
@@ -192,3 +194,34 @@ def test_cliploss_single_rank_output_dict():
     crit = bsc.ClipLoss(rank=0, world_size=1, criterion=torch.nn.CrossEntropyLoss())
     out = crit(feats[0].cuda(), feats[1].cuda(), feats[2].cuda(), lab.cuda(), 1 / 0.07, output_dict=True)
     assert abs(float(out["contrastive_loss"]) - float(ref_loss)) <= FP32_TOL * abs(float(ref_loss))
+
+
+@pytest.mark.parametrize("n,classes", [(1, 1), (300, 50), (5000, 5000), (4097, 3), (20000, 700)])
+def test_label_stats_match_label_matrix(n, classes):
+    """r / rep / next / rmax of bsc_label_stats vs construct_label_metrix (loss_func.py:18-21), bit-exact."""
+    from bsc.ops import CudaOps
+
+    g = torch.Generator().manual_seed(n)
+    lab = torch.randint(-(2 ** 40), 2 ** 40, (classes,), generator=g)[torch.randint(0, classes, (n,), generator=g)]
+    if classes == n:
+        lab = torch.arange(n) * 7919 - 3
+    r, rep, nxt, rmax = CudaOps().label_stats(lab.cuda())
+    ln = lab.numpy()
+    order = np.argsort(ln, kind="stable")
+    want_r = np.empty(n, np.float32)
+    want_rep = np.empty(n, np.int32)
+    want_next = np.full(n, -1, np.int32)
+    start = 0
+    while start < n:
+        end = start
+        while end < n and ln[order[end]] == ln[order[start]]:
+            end += 1
+        members = order[start:end]
+        want_r[members] = end - start
+        want_rep[members] = members[0]
+        want_next[members[:-1]] = members[1:]
+        start = end
+    assert np.array_equal(r.cpu().numpy(), want_r)
+    assert np.array_equal(rep.cpu().numpy(), want_rep)
+    assert np.array_equal(nxt.cpu().numpy(), want_next)
+    assert float(rmax) == want_r.max()
