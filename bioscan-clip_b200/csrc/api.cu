@@ -14,6 +14,10 @@ int l2norm_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, voi
 int rows_to_f16_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, float* inv,
                        cudaStream_t st);
 size_t label_stats_ws_bytes(int64_t n);
+void gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3], size_t* off_labels, size_t* total);
+int gather_push_launch(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels,
+                       int64_t n_local, int64_t row0, int64_t n_global, int d, void* const* peers, int world,
+                       cudaStream_t st);
 int label_stats_launch(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax, char* ws,
                        cudaStream_t st);
 int loss_launch(const float* stats, const float* r, int64_t n, unsigned present_mask, float scale, float* loss,
@@ -224,6 +228,30 @@ int bsc_rows_to_f16(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, v
   BSC_REQUIRE(n >= 0 && d >= 1 && ldx >= d, BSC_EINVAL, "bsc_rows_to_f16: bad shape n=%lld d=%d ldx=%lld", (long long)n,
               d, (long long)ldx);
   return rows_to_f16_launch(x, x_dtype, n, d, ldx, y16, inv, (cudaStream_t)stream);
+}
+
+int bsc_gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3], size_t* off_labels,
+                      size_t* total_bytes) {
+  BSC_REQUIRE(off_xh && off_inv && off_labels && total_bytes, BSC_EINVAL, "bsc_gather_layout: null pointer");
+  BSC_REQUIRE(n_global >= 0 && d >= 1, BSC_EINVAL, "bsc_gather_layout: bad shape");
+  gather_layout(n_global, d, off_xh, off_inv, off_labels, total_bytes);
+  return BSC_OK;
+}
+
+int bsc_gather_push(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels, int64_t n_local,
+                    int64_t row0, int64_t n_global, int d, void* const* peer_buffers, int world, void* stream) {
+  BSC_REQUIRE(x && ldx && peer_buffers, BSC_EINVAL, "bsc_gather_push: null pointer");
+  BSC_REQUIRE(world >= 1 && world <= kMaxPeers, BSC_EUNSUPPORTED, "bsc_gather_push: world=%d (1..%d supported)", world,
+              kMaxPeers);
+  BSC_REQUIRE(d >= 8 && d % 8 == 0, BSC_EUNSUPPORTED, "bsc_gather_push: d %% 8 != 0 (got %d)", d);
+  BSC_REQUIRE(n_local >= 0 && row0 >= 0 && row0 + n_local <= n_global, BSC_EINVAL,
+              "bsc_gather_push: rows [%lld, %lld) outside the global batch of %lld", (long long)row0,
+              (long long)(row0 + n_local), (long long)n_global);
+  for (int m = 0; m < 3; ++m)
+    BSC_REQUIRE(!x[m] || ldx[m] >= d, BSC_EINVAL, "bsc_gather_push: ldx[%d] < d", m);
+  for (int r = 0; r < world; ++r) BSC_REQUIRE(peer_buffers[r], BSC_EINVAL, "bsc_gather_push: peer %d is null", r);
+  return gather_push_launch(x, x_dtype, ldx, labels, n_local, row0, n_global, d, peer_buffers, world,
+                            (cudaStream_t)stream);
 }
 
 int bsc_label_stats_workspace_bytes(int64_t n, size_t* bytes) {

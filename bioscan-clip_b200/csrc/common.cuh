@@ -43,6 +43,7 @@ void count_launch(int n = 1);
 // Ordered pair (a,b), a != b, of modality slots 0..2 -> 0..5.
 __host__ __device__ inline int pair_id(int a, int b) { return a * 2 + (b > a ? b - 1 : b); }
 
+constexpr int kMaxPeers = 16;  // ranks of one NVLink domain addressed by the fused gather
 constexpr int kStatsExtra = 4;  // scalars after the 6*N sum-exp rows; [0] = sum over unordered pairs and local rows of
                                 // sum_j T_ij (s*S_ij - s)
 

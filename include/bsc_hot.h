@@ -77,6 +77,22 @@ int bsc_l2norm_fwd(const void* x, int x_dtype, int64_t n, int d, int64_t ldx,
 int bsc_rows_to_f16(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, float* inv, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * K1+gather  TC16 operand preparation fused with the all_gather of gather_features (loss_func.py:58-91, the
+ * default gather_with_grad=False branch :84-89 where only values cross ranks) over NVLink peer memory.
+ * Every rank owns a buffer of bsc_gather_layout().total_bytes that is mapped into all ranks of the node
+ * (peer_buffers[r] = address of rank r's buffer in THIS process, e.g. torch symmetric memory):
+ *     xh[m]  at off_xh[m]:  n_global x d fp16      inv[m] at off_inv[m]: n_global fp32      labels at off_labels: int64
+ * bsc_gather_push computes, for the n_local rows of every present modality, what bsc_rows_to_f16 computes and stores
+ * row row0 + l (fp16 row, scale, label) into EVERY rank's buffer.  The caller must run a cross-rank barrier on the
+ * stream after the call before any rank reads its buffer, and must not push into a buffer a peer may still read
+ * (alternate two buffers by step).  All modalities share x_dtype; x[m] = NULL marks an absent modality.
+ * ---------------------------------------------------------------------------------------------- */
+int bsc_gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3], size_t* off_labels,
+                      size_t* total_bytes);
+int bsc_gather_push(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels, int64_t n_local,
+                    int64_t row0, int64_t n_global, int d, void* const* peer_buffers, int world, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * K2  label statistics replacing construct_label_metrix (loss_func.py:18-21): for labels[n]
  *     r[i]    = #{j : labels[j] == labels[i]}      (row sum of the 0/1 label matrix)
  *     rep[i]  = min{j : labels[j] == labels[i]}    (class representative)
