@@ -14,6 +14,10 @@ int l2norm_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, voi
 int rows_to_f16_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, float* inv,
                        cudaStream_t st);
 size_t label_stats_ws_bytes(int64_t n);
+int taxo_launch(const int64_t* indices, int64_t nq, int k, const int32_t* key_ids, int64_t nb, const int32_t* gt_ids,
+                int levels, const int32_t* k_list, int nk, const int64_t* class_off, int64_t total_classes,
+                int32_t* pred_ids, uint8_t* first_hit, int64_t* micro, int32_t* pred_counts, int32_t* gt_counts,
+                cudaStream_t st);
 void gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3], size_t* off_labels, size_t* total);
 int gather_push_launch(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels,
                        int64_t n_local, int64_t row0, int64_t n_global, int d, void* const* peers, int world,
@@ -252,6 +256,18 @@ int bsc_gather_push(const void* const x[3], int x_dtype, const int64_t ldx[3], c
   for (int r = 0; r < world; ++r) BSC_REQUIRE(peer_buffers[r], BSC_EINVAL, "bsc_gather_push: peer %d is null", r);
   return gather_push_launch(x, x_dtype, ldx, labels, n_local, row0, n_global, d, peer_buffers, world,
                             (cudaStream_t)stream);
+}
+
+int bsc_taxonomy_eval(const int64_t* indices, int64_t nq, int k, const int32_t* key_ids, int64_t nb,
+                      const int32_t* gt_ids, int levels, const int32_t* k_list, int nk, const int64_t* class_off,
+                      int64_t total_classes, int32_t* pred_ids, uint8_t* first_hit, int64_t* micro,
+                      int32_t* pred_counts, int32_t* gt_counts, void* stream) {
+  BSC_REQUIRE(nq >= 0 && nb >= 0 && total_classes >= 0, BSC_EINVAL, "bsc_taxonomy_eval: negative size");
+  BSC_REQUIRE((indices && gt_ids) || nq == 0, BSC_EINVAL, "bsc_taxonomy_eval: null query arrays");
+  BSC_REQUIRE(key_ids || nb == 0, BSC_EINVAL, "bsc_taxonomy_eval: null key_ids");
+  BSC_REQUIRE(k_list && class_off && micro && pred_counts && gt_counts, BSC_EINVAL, "bsc_taxonomy_eval: null pointer");
+  return taxo_launch(indices, nq, k, key_ids, nb, gt_ids, levels, k_list, nk, class_off, total_classes, pred_ids,
+                     first_hit, micro, pred_counts, gt_counts, (cudaStream_t)stream);
 }
 
 int bsc_label_stats_workspace_bytes(int64_t n, size_t* bytes) {

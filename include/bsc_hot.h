@@ -168,6 +168,23 @@ int bsc_topk_merge(const float* cand_scores, const int64_t* cand_ids, int parts,
                    float* out_scores, int64_t* out_ids, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Taxonomy bookkeeping of a search result (scripts/inference_and_eval.py:422-433 label mapping, :448-464
+ * top_k_micro_accuracy, :467-511 top_k_macro_accuracy) on label ids: every taxonomy level's strings are interned
+ * to int32 ids 0..classes_l-1 by the caller (-1 = no label); class_off[l] is the first slot of level l in the
+ * per-class arrays of total_classes entries.
+ *   indices [nq,k] int64 (-1 = padding)      key_ids [nb,levels]      gt_ids [nq,levels]      k_list[nk] (nk <= 8)
+ *   pred_ids   [nq,k,levels] label id of every hit (NULL to skip)
+ *   first_hit  [nq,levels]   smallest rank t with key_ids[indices[q,t],l] == gt_ids[q,l], 255 = none (NULL to skip)
+ *   micro      [nk,levels]   #queries whose ground truth is among the first k_list[kk] hits (int64)
+ *   pred_counts[nk,total_classes], gt_counts[total_classes]  the reference's pred_counts / gt_counts per class
+ * Outputs are zeroed by the call.  All arithmetic is integer: results are exact.
+ * ---------------------------------------------------------------------------------------------- */
+int bsc_taxonomy_eval(const int64_t* indices, int64_t nq, int k, const int32_t* key_ids, int64_t nb,
+                      const int32_t* gt_ids, int levels, const int32_t* k_list, int nk, const int64_t* class_off,
+                      int64_t total_classes, int32_t* pred_ids, uint8_t* first_hit, int64_t* micro,
+                      int32_t* pred_counts, int32_t* gt_counts, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Instrumentation for bench.py: CUDA-event time of the dominant kernel of the last call made with
  * bsc_set_timing(1) on this thread (milliseconds, -1 if none).  which: 0 = infonce forward sweep,
  * 1 = infonce backward sweep, 2 = bank scan.  Reading it synchronises on the recorded events only.

@@ -121,9 +121,52 @@ def run_normalize_case():
     np.savez_compressed(os.path.join(HERE, "retrieval_normalize.npz"), x=x, y=y)
 
 
+def run_accuracy_case():
+    """scripts/inference_and_eval.py cannot be imported (faiss, hydra, h5py ... are missing), so the SOURCE of
+    top_k_micro_accuracy / top_k_macro_accuracy and of the label loop of make_prediction is cut out of the file
+    with ``ast`` and executed verbatim; inputs and outputs go to accuracy_small.json."""
+    import ast
+    import json
+
+    path = os.path.join(REF, "scripts", "inference_and_eval.py")
+    src = open(path).read()
+    tree = ast.parse(src)
+    env = {"LEVELS": ["order", "family", "genus", "species"]}
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name in ("top_k_micro_accuracy", "top_k_macro_accuracy"):
+            exec(compile(ast.Module(body=[node], type_ignores=[]), path, "exec"), env)
+    rng = np.random.default_rng(5)
+    nb, nq, k = 60, 40, 5
+    names = {"order": 3, "family": 5, "genus": 9, "species": 14}
+
+    def rand_label():
+        return {lv: f"{lv}_{int(rng.integers(0, c))}" for lv, c in names.items()}
+
+    keys_label = [rand_label() for _ in range(nb)]
+    gt_list = [rand_label() for _ in range(nq)]
+    indices = np.stack([rng.permutation(nb)[:k] for _ in range(nq)]).astype(np.int64)
+    # the label loop of make_prediction (inference_and_eval.py:422-433), executed from its own source lines
+    fn = next(n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "make_prediction")
+    loop = next(n for n in fn.body if isinstance(n, ast.For))
+    loc = {"indices": indices, "keys_label": keys_label, "pred_list": [], "LEVELS": env["LEVELS"]}
+    exec(compile(ast.Module(body=[loop], type_ignores=[]), path, "exec"), loc)
+    pred_list = loc["pred_list"]
+    k_list = [1, 3, 5]
+    micro = env["top_k_micro_accuracy"](pred_list, gt_list, k_list=k_list)
+    macro, per_class = env["top_k_macro_accuracy"](pred_list, gt_list, k_list=k_list)
+    out = {"keys_label": keys_label, "gt_list": gt_list, "indices": indices.tolist(), "k_list": k_list,
+           "pred_list": pred_list,
+           "micro": {str(a): b for a, b in micro.items()}, "macro": {str(a): b for a, b in macro.items()},
+           "per_class": {str(a): b for a, b in per_class.items()}}
+    with open(os.path.join(HERE, "accuracy_small.json"), "w") as f:
+        json.dump(out, f)
+    print("accuracy_small.json", micro[1], macro[5])
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
     torch.set_num_threads(4)
     run_loss_cases()
     run_clip_case()
     run_normalize_case()
+    run_accuracy_case()

@@ -1,4 +1,6 @@
 """GPU parity: bank scan top-k (through the C ABI) vs the retrieval oracle."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -92,3 +94,44 @@ def test_full_size_properties():
     two.add(bank[nb // 2:])
     s2, i2 = two.search_device(q, 5)
     assert (i2 == i).all() and torch.equal(s2, s)
+
+
+def _rand_taxonomy(rng, n, sizes=(4, 9, 30, 80)):
+    levels = ["order", "family", "genus", "species"]
+    return [{lv: f"{lv}{int(rng.integers(0, c))}" for lv, c in zip(levels, sizes)} for _ in range(n)]
+
+
+def test_taxonomy_accuracy_matches_reference_fixture():
+    """bsc.TaxonomyEval / top_k_*_accuracy vs outputs of the reference's own function source, exact (==)."""
+    import json
+
+    import bsc
+
+    z = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "accuracy_small.json")))
+    micro, macro, per_class = bsc.TaxonomyEval(z["keys_label"]).evaluate(np.array(z["indices"]), z["gt_list"], z["k_list"])
+    micro2 = bsc.top_k_micro_accuracy(z["pred_list"], z["gt_list"], z["k_list"])
+    macro2, per2 = bsc.top_k_macro_accuracy(z["pred_list"], z["gt_list"], z["k_list"])
+    for k in z["k_list"]:
+        assert micro[k] == z["micro"][str(k)] == micro2[k]
+        assert macro[k] == z["macro"][str(k)] == macro2[k]
+        assert per_class[k] == z["per_class"][str(k)] == per2[k]
+
+
+@pytest.mark.parametrize("nq,nb,k", [(1, 7, 5), (3000, 5000, 5), (20000, 300, 8)])
+def test_taxonomy_accuracy_matches_oracle(nq, nb, k):
+    import bsc
+    from oracle import accuracy_oracle as ao
+
+    rng = np.random.default_rng(nq)
+    keys, gts = _rand_taxonomy(rng, nb), _rand_taxonomy(rng, nq)
+    idx = rng.integers(0, nb, size=(nq, k)).astype(np.int64)
+    idx[rng.random((nq, k)) < 0.05] = -1  # faiss padding
+    k_list = [1, 3, k]
+    pred = [{lv: [keys[i][lv] if i >= 0 else None for i in row] for lv in ao.LEVELS} for row in idx]
+    want_micro = ao.top_k_micro_accuracy(pred, gts, k_list)
+    want_macro, want_pc = ao.top_k_macro_accuracy(pred, gts, k_list)
+    micro, macro, pc, pred_ids = bsc.TaxonomyEval(keys).evaluate(torch.from_numpy(idx).cuda(), gts, k_list,
+                                                                 with_pred_ids=True)
+    assert micro == want_micro and macro == want_macro and pc == want_pc
+    assert pred_ids.shape == (nq, k, 4)
+    assert bool((pred_ids[torch.from_numpy(idx).cuda() < 0] == -1).all())

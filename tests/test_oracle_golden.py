@@ -97,3 +97,20 @@ def test_make_prediction_return_forms():
     assert isinstance(p, list) and p[0]["species"][0] == labels[0]["species"]
     p, s, i = retrieval_oracle.make_prediction(keys[:3], keys, labels, True, True, 3)
     assert s.dtype == np.float32 and i.dtype == np.int64 and i.shape == (3, 3)
+
+
+def test_accuracy_oracle_matches_reference_source_outputs():
+    """accuracy_small.json was written by executing the reference's own function source (make_golden.py)."""
+    import json
+
+    from oracle import accuracy_oracle as ao
+
+    z = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "accuracy_small.json")))
+    pred = ao.map_hits_to_labels(z["indices"], z["keys_label"])
+    assert pred == z["pred_list"]
+    micro = ao.top_k_micro_accuracy(pred, z["gt_list"], z["k_list"])
+    macro, per_class = ao.top_k_macro_accuracy(pred, z["gt_list"], z["k_list"])
+    for k in z["k_list"]:
+        assert micro[k] == z["micro"][str(k)]
+        assert macro[k] == z["macro"][str(k)]
+        assert per_class[k] == z["per_class"][str(k)]
