@@ -42,14 +42,21 @@ class CudaOps:
     name = "cuda"
 
     # ---- K1 -------------------------------------------------------------------------------------
-    def normalize(self, x: torch.Tensor, out_dtype: torch.dtype, zero_rule: int = NORM_TORCH) -> torch.Tensor:
-        """Rows of x scaled to unit L2 norm (F.normalize / sklearn rule), written as out_dtype."""
+    def normalize(self, x: torch.Tensor, out_dtype: torch.dtype, zero_rule: int = NORM_TORCH,
+                  out: torch.Tensor = None) -> torch.Tensor:
+        """Rows of x scaled to unit L2 norm (F.normalize / sklearn rule), written as out_dtype (into ``out``, a
+        contiguous [n, d] tensor of that dtype, when given -- e.g. a slice of a preallocated embedding bank)."""
         _lib.require_device(x.device)
         assert x.dim() == 2
         if x.stride(1) != 1:
             x = x.contiguous()
         n, d = x.shape
-        y = torch.empty((n, d), dtype=out_dtype, device=x.device)
+        if out is not None:
+            if out.shape != (n, d) or out.dtype != out_dtype or not out.is_contiguous() or out.device != x.device:
+                raise _lib.BscError("normalize: out must be a contiguous [n, d] tensor of out_dtype on x's device")
+            y = out
+        else:
+            y = torch.empty((n, d), dtype=out_dtype, device=x.device)
         y16 = y if out_dtype in (torch.float16, torch.bfloat16) else None
         y32 = y if out_dtype == torch.float32 else None
         if y16 is None and y32 is None:

@@ -135,3 +135,56 @@ def test_taxonomy_accuracy_matches_oracle(nq, nb, k):
     assert micro == want_micro and macro == want_macro and pc == want_pc
     assert pred_ids.shape == (nq, k, 4)
     assert bool((pred_ids[torch.from_numpy(idx).cuda() < 0] == -1).all())
+
+
+class _ToyModel(torch.nn.Module):
+    """Three linear 'encoders' with the attribute names get_feature_and_label reads (inference_epoch.py:12-17)."""
+
+    def __init__(self, d_in=24, d=64):
+        super().__init__()
+        g = torch.Generator().manual_seed(3)
+        self.image_encoder = torch.nn.Linear(d_in, d)
+        self.dna_encoder = torch.nn.Linear(d_in, d)
+        self._lang = torch.nn.Linear(d_in, d)
+        for p in self.parameters():
+            p.data = torch.randn(p.shape, generator=g)
+
+    def language_encoder(self, inp):
+        return self._lang(inp["input_ids"].float())
+
+
+def _toy_batches(n_batches=3, bs=5, d_in=24):
+    g = torch.Generator().manual_seed(9)
+    out = []
+    for b in range(n_batches):
+        ids = [f"p{b}_{i}" for i in range(bs)]
+        lab = {lv: [f"{lv}{(b + i) % 3}" for i in range(bs)] for lv in ["order", "family", "genus", "species"]}
+        out.append((ids, torch.randn(bs, d_in, generator=g), torch.randn(bs, d_in, generator=g),
+                    torch.randint(0, 9, (bs, d_in), generator=g), torch.zeros(bs, d_in), torch.ones(bs, d_in), lab))
+    return out
+
+
+def test_embedding_extraction_device_bank_matches_reference_steps():
+    """inference_epoch.py:8-68 restated inline: F.normalize(encoder(x)) per batch, rows in loader order."""
+    import bsc
+
+    model = _ToyModel().cuda()
+    batches = _toy_batches()
+    for kind, col, enc in (("image", 1, model.image_encoder), ("dna", 2, model.dna_encoder)):
+        names, feats, labels = bsc.get_feature_and_label(batches, model, "cuda", type_of_feature=kind)
+        with torch.no_grad():
+            want = torch.cat([torch.nn.functional.normalize(enc(b[col].cuda()), dim=-1) for b in batches]).cpu()
+        assert feats.dtype == np.float64 and feats.shape == (15, 64)
+        assert np.abs(feats - want.double().numpy()).max() <= 2e-7
+        assert names == [n for b in batches for n in b[0]]
+        assert labels[6] == {lv: f"{lv}{(1 + 1) % 3}" for lv in ["order", "family", "genus", "species"]}
+        _, dev_feats, _ = bsc.get_feature_and_label(batches, model, "cuda", type_of_feature=kind, device_resident=True)
+        assert dev_feats.is_cuda and np.array_equal(dev_feats.cpu().numpy().astype(np.float64), feats)
+    d = bsc.get_features_and_label(batches, model, "cuda", for_key_set=True, device_resident=True)
+    assert set(d) == {"file_name_list", "encoded_dna_feature", "encoded_image_feature", "encoded_language_feature",
+                      "averaged_feature", "concatenated_feature", "label_list", "all_key_features",
+                      "all_key_features_label"}
+    assert d["concatenated_feature"].shape == (15, 128) and d["all_key_features"].shape == (45, 64)
+    assert len(d["all_key_features_label"]) == 45
+    with pytest.raises(TypeError):
+        bsc.get_feature_and_label(batches, model, "cuda", type_of_feature="audio")
