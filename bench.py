@@ -469,6 +469,26 @@ def bench_retrieval(args, torch, dist, bsc, _lib, device, rank, world, peaks):
         if name == "bulk":
             res[name]["top1_planted_hit_rate"] = float((i[:, 0] == pi).float().mean().item())
     _lib.set_timing(False)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # bounded CPU sample of the same search: 2048 of the queries against the first 1M bank rows
+        import numpy as np
+
+        from oracle import retrieval_oracle
+
+        rows, nqs = min(nb, 1_000_000), min(nq, 2048)
+        kb = bank[:rows].float().cpu().numpy()
+        qb = q[:nqs].float().cpu().numpy()
+        cores = os.cpu_count() or 1
+        retrieval_oracle.search_ip_topk_torch(kb[:50_000], qb, 5, threads=cores)
+        t0 = time.perf_counter()
+        _, ci = retrieval_oracle.search_ip_topk_torch(kb, qb, 5, threads=cores)
+        dt = time.perf_counter() - t0
+        # scaled to the full bank: the search is linear in the number of bank rows
+        res["cpu_baseline"] = {"value": nqs / dt * rows / nb_total, "unit": "queries/s on the 5M bank", "cores": cores,
+                               "kind": "port", "seconds": dt,
+                               "sample": f"{nqs} queries x {rows} bank rows, float32 blocked sgemm + torch.topk (oracle "
+                                         f"restatement of IndexFlatIP.search), rate scaled by {rows}/{nb_total}"}
+        del kb, qb
     res["bank_rows_total"] = nb_total
     res["bank_rows_per_gpu"] = nb
     res["hbm_peak_gbs"] = peaks["hbm_gbs"]

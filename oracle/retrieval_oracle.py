@@ -106,3 +106,29 @@ def score_margins_fp64(keys, queries, indices):
     masked = s.copy()
     masked[np.arange(nq)[:, None], indices] = -np.inf
     return kth - masked.max(axis=1)
+
+
+def search_ip_topk_torch(keys, queries, k: int, block: int = 262144, threads: int = 0):
+    """The same search as search_ip with the selection done by torch.topk per bank block and a running merge --
+    how a CPU IndexFlatIP spends its time (blocked sgemm + k-selection, inference_and_eval.py:418-421).  Used as the
+    timed CPU baseline of the retrieval half of the metric; scores equal search_ip's, ids
+    agree wherever the k-th and (k+1)-th scores differ (torch.topk does not promise the lowest id among ties)."""
+    import torch
+
+    if threads:
+        torch.set_num_threads(threads)
+    kt = torch.as_tensor(np.ascontiguousarray(keys, dtype=np.float32))
+    qt = torch.as_tensor(np.ascontiguousarray(queries, dtype=np.float32))
+    nq, nb = qt.shape[0], kt.shape[0]
+    best_s = torch.full((nq, k), float(FAISS_NEG), dtype=torch.float32)
+    best_i = torch.full((nq, k), -1, dtype=torch.int64)
+    for lo in range(0, nb, block):
+        hi = min(nb, lo + block)
+        s = qt @ kt[lo:hi].T
+        kk = min(k, hi - lo)
+        ts, ti = torch.topk(s, kk, dim=1)
+        cs = torch.cat([best_s, ts], dim=1)
+        ci = torch.cat([best_i, ti + lo], dim=1)
+        ms, mi = torch.topk(cs, k, dim=1)
+        best_s, best_i = ms, torch.gather(ci, 1, mi)
+    return best_s.numpy(), best_i.numpy()

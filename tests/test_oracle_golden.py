@@ -114,3 +114,14 @@ def test_accuracy_oracle_matches_reference_source_outputs():
         assert micro[k] == z["micro"][str(k)]
         assert macro[k] == z["macro"][str(k)]
         assert per_class[k] == z["per_class"][str(k)]
+
+
+def test_torch_topk_search_agrees_with_sorted_search():
+    from oracle import retrieval_oracle as ro
+
+    rng = np.random.default_rng(4)
+    keys = rng.standard_normal((3000, 32)).astype(np.float32)
+    q = rng.standard_normal((17, 32)).astype(np.float32)
+    s0, i0 = ro.search_ip(keys, q, 5)
+    s1, i1 = ro.search_ip_topk_torch(keys, q, 5, block=1024)
+    assert np.array_equal(s0, s1) and np.array_equal(i0, i1)  # continuous random scores: no ties
