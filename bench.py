@@ -315,8 +315,8 @@ def run_native(args):
             if k + 1 < nsteps:
                 copy_in(b ^ 1)
             flush.zero_()
-            if world > 1:
-                dist.barrier()
+            # no per-step dist.barrier() here: it would block the host and serialise the copy / compute pipeline; the
+            # ranks meet inside every step's collectives, and the timed region is bracketed by barrier + synchronize
             main.wait_event(ev_in[b])
             leaves = [t.detach().requires_grad_(True) for t in dev_in[b]]
             if world > 1:
