@@ -151,7 +151,8 @@ InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p) {
   L.rowpos = take((size_t)3 * 2 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
   L.jrange = take((size_t)(L.n_jtile > 0 ? L.n_jtile : 1) * 2 * sizeof(int));
   L.colpart = take((size_t)3 * (L.n_iblk > 0 ? L.n_iblk : 1) * L.n_global_pad * sizeof(float));
-  L.dxraw = take((size_t)3 * 2 * (n > 0 ? n : 1) * D * sizeof(float));
+  L.bwd_jsplit = tc_bwd_duo_jsplit(p);
+  L.dxraw = take((size_t)3 * 2 * L.bwd_jsplit * (n > 0 ? n : 1) * D * sizeof(float));
   L.gscratch = (p->mode == BSC_MODE_F32) ? take((size_t)L.g_rows * N * sizeof(float)) : off;
   L.total = off;
   return L;
@@ -347,7 +348,7 @@ int bsc_infonce_bwd(const bsc_infonce_desc* p, const float* stats, const void* c
   for (int a = 0; a < 3; ++a) {
     ca.x[a] = p->xh[a] ? x[a] : nullptr;
     ca.grad[a] = p->xh[a] ? grad[a] : nullptr;
-    ca.raw[a] = (const float*)(ws + L.dxraw) + (size_t)a * 2 * p->n_local * p->d;
+    ca.raw[a] = (const float*)(ws + L.dxraw) + (size_t)a * 2 * L.bwd_jsplit * p->n_local * p->d;
   }
   ca.gsbuf = (const float*)(ws + L.gs);
   ca.grad_out = grad_out;
@@ -357,6 +358,7 @@ int bsc_infonce_bwd(const bsc_infonce_desc* p, const float* stats, const void* c
   ca.ldx = ldx;
   ca.d = p->d;
   ca.n_slots = m - 1;
+  ca.n_parts = L.bwd_jsplit;
   ca.present_mask = mask;
   ca.scale = p->logit_scale;
   return combine_launch(ca, x_dtype, st);

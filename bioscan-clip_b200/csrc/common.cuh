@@ -57,11 +57,12 @@ struct InfoNceWs {
   size_t rowpos;    // float [3][n_jchunk][n_local_pad]   positive-pair partials
   size_t colpart;   // float [3][n_iblk][N_pad]
   size_t jrange;    // int2  [n_jtile]       label-class range of every column tile
-  size_t dxraw;     // float [3][2][n_local][D]
+  size_t dxraw;     // float [3][2][bwd_jsplit][n_local][D]
   size_t gscratch;  // float [g_rows][N]     fp32 mode only
   size_t total;
   // tiling facts shared by host and kernels
   int n_iblk, n_jtile, n_jchunk, jtiles_per_chunk;
+  int bwd_jsplit;   // dxraw parts per (modality, slot): > 1 only for the CTA-pair backward sweep (tc_bwd2.cu)
   int64_t n_local_pad, n_global_pad, g_rows;
 };
 
@@ -77,6 +78,7 @@ struct CombineArgs {
   const float* grad_out;
   int64_t row0, n_local, n_global, ldx;
   int d, n_slots;
+  int n_parts;           // partial sums per slot (column-sweep parts of the backward), >= 1
   unsigned present_mask;
   float scale;
 };
@@ -88,6 +90,7 @@ int tc_fwd_stats(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, float*
 int tc_bwd_raw(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st);
 // CTA-pair (cta_group::2) sweep; returns 1 when the shape is not covered and the caller must use tc_bwd_raw's own kernels
 int tc_bwd_duo(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st);
+int tc_bwd_duo_jsplit(const bsc_infonce_desc* p);
 
 int simt_bank_search(const float* q, int64_t nq, const float* bank, int64_t nb, int d, int k, int64_t base_id,
                      float* out_s, int64_t* out_i, char* ws, size_t ws_bytes, cudaStream_t st);

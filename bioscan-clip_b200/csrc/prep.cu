@@ -628,8 +628,9 @@ __global__ void __launch_bounds__(256) combine_kernel(CombineArgs a) {
   const float gout = a.grad_out[0];
   const T* xr = (const T*)a.x[m] + il * a.ldx;
   T* gr = (T*)a.grad[m] + il * a.ldx;
+  const int64_t part_stride = a.n_local * (int64_t)a.d;
   const float* raw0 = a.raw[m] + il * (int64_t)a.d;
-  const float* raw1 = raw0 + a.n_local * (int64_t)a.d;
+  const float* raw1 = raw0 + a.n_parts * part_stride;
 
   float ss = 0.f;
   for (int cidx = lane; cidx < a.d; cidx += 32) {
@@ -642,8 +643,14 @@ __global__ void __launch_bounds__(256) combine_kernel(CombineArgs a) {
   const float inv = 1.0f / fmaxf(nrm, 1e-12f);
 
   auto ghat_at = [&](int cidx) -> float {
-    float raw = raw0[cidx] * inv_gs[0];
-    if (a.n_slots > 1) raw = fmaf(raw1[cidx], inv_gs[1], raw);
+    float s0 = raw0[cidx];
+    for (int q = 1; q < a.n_parts; ++q) s0 += raw0[q * part_stride + cidx];  // fixed order: deterministic
+    float raw = s0 * inv_gs[0];
+    if (a.n_slots > 1) {
+      float s1 = raw1[cidx];
+      for (int q = 1; q < a.n_parts; ++q) s1 += raw1[q * part_stride + cidx];
+      raw = fmaf(s1, inv_gs[1], raw);
+    }
     return cs * raw;
   };
 

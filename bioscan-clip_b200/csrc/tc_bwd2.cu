@@ -53,14 +53,27 @@ struct DuoParams {
   int n_xy;
   int xy_x[6], xy_y[6], xy_slot[6];
   int n_iblk, n_jtile, n_steps, kblocks, nblk, num_items, d;
+  int jsplit;  // the column sweep of a (pair, row block) is cut into jsplit items (own dxraw slot each) so that the
+               // number of items per cluster is not quantised coarsely when there are few row blocks (many ranks)
   int64_t n_global, n_local, row0;
   float k1, k2;
   const float* uv;      // [6][N]
   const int32_t* rep;   // [N]
   const float* gsbuf;   // [6][2]
   const float* inv[3];
-  float* dxraw;         // [3][2][n_local][d]
+  float* dxraw;         // [3][2][jsplit][n_local][d]
 };
+
+// item -> (ordered pair, row block, part of the column sweep); steps [s_lo, s_hi) of part `part`
+__device__ __forceinline__ void duo_item(const DuoParams& p, int item, int& xy, int& iblk, int& part, int& s_lo,
+                                         int& s_hi) {
+  part = item % p.jsplit;
+  const int rest = item / p.jsplit;
+  iblk = rest % p.n_iblk;
+  xy = rest / p.n_iblk;
+  s_lo = (int)((int64_t)part * p.n_steps / p.jsplit);
+  s_hi = (int)((int64_t)(part + 1) * p.n_steps / p.jsplit);
+}
 
 struct __align__(8) DuoTail {
   uint64_t full[STAGES];
@@ -130,7 +143,6 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
   ptx::cluster_sync_all();  // both CTAs' barriers and TMEM exist before anything crosses the pair
   ptx::tc_fence_after();
   const uint32_t tmem_base = tail->tmem_base;
-  const int NS = p.n_steps;
   const int nblk = p.nblk;
 
   if (warp == 0) {
@@ -145,8 +157,8 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
         }
       };
       for (int item = cluster; item < p.num_items; item += n_clusters) {
-        const int iblk = item % p.n_iblk;
-        const int xy = item / p.n_iblk;
+        int xy, iblk, part, s_lo, s_hi;
+        duo_item(p, item, xy, iblk, part, s_lo, s_hi);
         const int x = p.xy_x[xy], y = p.xy_y[xy];
         const CUtensorMap* my = &p.tmap128[y];
         const CUtensorMap* mx = &p.tmap64[x];
@@ -175,9 +187,9 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
             next_stage();
           }
         };
-        load_s(0);
-        for (int s = 0; s < NS; ++s) {
-          if (s + 1 < NS) load_s(s + 1);
+        load_s(s_lo);
+        for (int s = s_lo; s < s_hi; ++s) {
+          if (s + 1 < s_hi) load_s(s + 1);
           load_g(2 * s);
           load_g(2 * s + 1);
         }
@@ -204,6 +216,8 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
           }
         };
         for (int item = cluster; item < p.num_items; item += n_clusters, ++item_count) {
+          int xy, iblk, part, s_lo, s_hi;
+          duo_item(p, item, xy, iblk, part, s_lo, s_hi);
           auto issue_s = [&]() {
             ptx::mbar_wait_cluster(ptx::smem_u32(&tail->s_free), (s_count & 1u) ^ 1u, 200);
             ptx::tc_fence_after();
@@ -249,10 +263,10 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
             ++gu[pb];
           };
           issue_s();
-          for (int s = 0; s < NS; ++s) {
-            if (s + 1 < NS) issue_s();
-            issue_g(2 * s, s == 0, false);
-            issue_g(2 * s + 1, false, s == NS - 1);
+          for (int s = s_lo; s < s_hi; ++s) {
+            if (s + 1 < s_hi) issue_s();
+            issue_g(2 * s, s == s_lo, false);
+            issue_g(2 * s + 1, false, s == s_hi - 1);
           }
         }
       }
@@ -261,12 +275,15 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
       if (ptx::elect_one()) {
         const uint32_t ready0_l = ptx::mapa(ptx::smem_u32(&tail->g_ready[0]), 0);
         uint32_t n = 0;
-        for (int item = cluster; item < p.num_items; item += n_clusters)
-          for (int s = 0; s < NS; ++s, ++n) {
+        for (int item = cluster; item < p.num_items; item += n_clusters) {
+          int xy, iblk, part, s_lo, s_hi;
+          duo_item(p, item, xy, iblk, part, s_lo, s_hi);
+          for (int s = s_lo; s < s_hi; ++s, ++n) {
             ptx::mbar_wait_cluster(ptx::smem_u32(&tail->rx), n & 1u, 500);
             ptx::fence_proxy_async_all();
             ptx::mbar_arrive_remote(ready0_l);
           }
+        }
       }
     }
   } else if (warp >= 4) {
@@ -292,8 +309,8 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
     uint32_t dcount = 0;  // steps processed so far (all items)
     uint32_t item_count = 0;
     for (int item = cluster; item < p.num_items; item += n_clusters, ++item_count) {
-      const int iblk = item % p.n_iblk;
-      const int xy = item / p.n_iblk;
+      int xy, iblk, part, s_lo, s_hi;
+      duo_item(p, item, xy, iblk, part, s_lo, s_hi);
       const int x = p.xy_x[xy], y = p.xy_y[xy];
       const float gs = p.gsbuf[2 * pair_id(x, y)];
       const float m2gk = -2.0f * gs * inv_k1;
@@ -319,16 +336,16 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
         n_vi = 0.f;
         n_rep = -1;
         const int64_t j = (int64_t)(2 * s + (int)crank) * BN + jl;
-        if (s < NS && j < p.n_global) {
+        if (s < s_hi && j < p.n_global) {
           const float ij = invy[j];
           n_sc = p.k1 * ij;
           n_vi = gs * vrow[j] * ij;
           n_rep = p.rep[j];
         }
       };
-      fetch_j(0);
+      fetch_j(s_lo);
 
-      for (int s = 0; s < NS; ++s, ++dcount) {
+      for (int s = s_lo; s < s_hi; ++s, ++dcount) {
         const float sc_j = n_sc, vi_j = n_vi;
         const int rep_j = n_rep;
         const float tvj = m2gk * sc_j;
@@ -390,7 +407,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
       ptx::tc_fence_after();
       {
         const int slot = p.xy_slot[xy];
-        float* out = p.dxraw + ((int64_t)(x * 2 + slot) * p.n_local + (int64_t)iblk * BM) * p.d;
+        float* out = p.dxraw + ((int64_t)((x * 2 + slot) * p.jsplit + part) * p.n_local + (int64_t)iblk * BM) * p.d;
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + ACC_COL0;
         const int nc = nblk * 4;  // 32-column chunks
         const int c_lo = h == 0 ? 0 : nc / 2;
@@ -436,13 +453,51 @@ int sm_count2() {
 
 }  // namespace
 
-// Returns BSC_OK when the paired kernel ran, 1 when this shape is not covered (caller falls back), < 0 on error.
-int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStream_t st) {
+static bool duo_covers(const bsc_infonce_desc* d) {
   static const bool enabled = []() {
     const char* e = getenv("BSC_BWD_DUO");
     return !(e && e[0] == '0');
   }();
-  if (!enabled || d->x16_dtype != BSC_F16 || d->d % 256 != 0 || d->d > 768 || sm_count2() < 2) return 1;
+  return enabled && d->mode == BSC_MODE_TC16 && d->x16_dtype == BSC_F16 && d->d % 256 == 0 && d->d <= 768 &&
+         sm_count2() >= 2;
+}
+
+// In how many parts to cut every (ordered pair, row block) column sweep: the clusters take whole items, so with few
+// row blocks (n_local small: many ranks) ceil(items / clusters) wastes up to a whole sweep.  Cost model per item:
+// steps * (cycles per step) + a fixed fill / drain cost; pick the split in {1, 2, 4, 8} with the lowest makespan.
+int tc_bwd_duo_jsplit(const bsc_infonce_desc* d) {
+  if (!duo_covers(d)) return 1;
+  static const int forced = []() {
+    const char* e = getenv("BSC_BWD_JSPLIT");
+    return e ? atoi(e) : 0;
+  }();
+  int m = 0;
+  for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
+  const int64_t items0 = (int64_t)m * (m - 1) * ((d->n_local + BM - 1) / BM);
+  const int64_t steps = ((d->n_global + BN - 1) / BN + 1) / 2;
+  const int clusters = sm_count2() / 2;
+  if (items0 <= 0 || steps <= 0) return 1;
+  if (forced > 0) return (int)(forced > steps ? steps : forced);
+  // measured on B200 (1 GPU, N = 4096 and 8192, split forced to 1): 10.25 k cycles per step, 35 k per item (pipeline
+  // fill + accumulator drain are not overlapped across items yet)
+  const double step_cost = 10250.0, item_cost = 35000.0;
+  int best = 1;
+  double best_t = 1e300;
+  for (int s = 1; s <= 8; s *= 2) {
+    if (s > steps) break;
+    const double rounds = (double)((items0 * s + clusters - 1) / clusters);
+    const double t = rounds * ((double)steps / s * step_cost + item_cost);
+    if (t < best_t * 0.995) {
+      best_t = t;
+      best = s;
+    }
+  }
+  return best;
+}
+
+// Returns BSC_OK when the paired kernel ran, 1 when this shape is not covered (caller falls back), < 0 on error.
+int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStream_t st) {
+  if (!duo_covers(d)) return 1;
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
   DuoParams p{};
   int first = -1;
@@ -478,7 +533,9 @@ int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
   p.n_steps = (p.n_jtile + 1) / 2;
   p.kblocks = d->d / BK;
   p.nblk = d->d / 256;
-  p.num_items = n * p.n_iblk;
+  p.jsplit = L.bwd_jsplit > 0 ? L.bwd_jsplit : 1;
+  if (p.jsplit > p.n_steps) p.jsplit = p.n_steps > 0 ? p.n_steps : 1;
+  p.num_items = n * p.n_iblk * p.jsplit;
   p.d = d->d;
   p.n_global = d->n_global;
   p.n_local = d->n_local;
