@@ -168,6 +168,10 @@ def test_properties_at_full_size():
         # both sides are rounded to bf16 once: allow two roundings on top of the 2e-3 arithmetic bound
         assert ((g[perm] - gp).abs() <= 2e-3 * g.abs().max() + 2 * _bf16_round_bound(gp)).all()
     assert all(torch.isfinite(g).all() for g in grads)
+    # run-to-run determinism: fixed summation orders everywhere, so repeated evaluations give the same bits
+    loss2, grads2 = _run(feats, lab, "tc16")
+    assert float(loss) == float(loss2)
+    assert all(torch.equal(g, g2) for g, g2 in zip(grads, grads2))
 
 
 def test_error_behaviour():

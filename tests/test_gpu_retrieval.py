@@ -188,3 +188,19 @@ def test_embedding_extraction_device_bank_matches_reference_steps():
     assert len(d["all_key_features_label"]) == 45
     with pytest.raises(TypeError):
         bsc.get_feature_and_label(batches, model, "cuda", type_of_feature="audio")
+
+
+def test_stream_to_index_equals_single_add(tmp_path):
+    import bsc
+    from bsc import storage
+
+    bank, q, _ = bank_inputs(5000, 40, 64, seed=12)
+    np.save(tmp_path / "bank.npy", bank)
+    mm = np.load(tmp_path / "bank.npy", mmap_mode="r")
+    a = bsc.IndexFlatIP(64)
+    a.add(bank)
+    b = bsc.IndexFlatIP(64)
+    assert storage.stream_to_index(b, mm, chunk_rows=1500) == 5000 and b.ntotal == 5000
+    sa, ia = a.search(q, 5)
+    sb, ib = b.search(q, 5)
+    assert np.array_equal(ia, ib) and np.array_equal(sa, sb)

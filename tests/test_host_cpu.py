@@ -87,3 +87,37 @@ def test_resolve_mode():
     assert resolve_mode("tc16", [f32]) == MODE_TC16 and resolve_mode("fp32", [b16]) == MODE_F32
     with pytest.raises(ValueError):
         resolve_mode("fp8", [f32])
+
+
+def test_extracted_feature_container_round_trip(tmp_path):
+    """Directory container with the reference's /split/feature_type tree and labels json
+    (scripts/inference_and_eval.py:804-831, :863-884)."""
+    import numpy as np
+
+    from bsc import storage
+
+    rng = np.random.default_rng(0)
+
+    def split(n, with_all=False):
+        d = {"encoded_image_feature": rng.standard_normal((n, 8)), "encoded_dna_feature": rng.standard_normal((n, 8)),
+             "encoded_language_feature": None, "averaged_feature": rng.standard_normal((n, 8)),
+             "concatenated_feature": rng.standard_normal((n, 16)),
+             "label_list": [{"order": f"o{i}", "family": "f", "genus": "g", "species": f"s{i}"} for i in range(n)]}
+        if with_all:
+            d["all_key_features"] = rng.standard_normal((3 * n, 8))
+        return d
+
+    seen, unseen, keys = split(5), split(3), split(7, True)
+    root, labels = str(tmp_path / "feats"), str(tmp_path / "labels_val.json")
+    storage.save_extracted_features(root, labels, seen, unseen, keys)
+    s2, u2, k2 = storage.load_extracted_features(root, labels, mmap=True)
+    for a, b in ((seen, s2), (unseen, u2), (keys, k2)):
+        for ft in storage.ALL_TYPE_OF_FEATURES_OF_KEY:
+            if a.get(ft) is None:
+                assert ft not in b
+            else:
+                assert np.array_equal(np.asarray(b[ft]), a[ft])
+        assert b["label_list"] == a["label_list"]
+    assert k2["all_key_features_label"] == keys["label_list"] * 3
+    import json
+    assert set(json.load(open(labels))) == {"seen_gt_dict", "unseen_gt_dict", "key_gt_dict"}
