@@ -229,3 +229,29 @@ def test_label_stats_match_label_matrix(n, classes):
     assert np.array_equal(rep.cpu().numpy(), want_rep)
     assert np.array_equal(nxt.cpu().numpy(), want_next)
     assert float(rmax) == want_r.max()
+
+
+def test_synthetic_train_step_with_fused_loss():
+    """Caller side (train_epoch.py:29-40 + simple_clip.py:27-50) with small random-init encoders: the loss drives LoRA
+    and head gradients only, base weights stay frozen, and the loss value equals the oracle's on the same embeddings."""
+    import bsc
+    from bsc import harness
+
+    torch.manual_seed(1)
+    model = harness.build_synthetic_model(vit_layers=1, dna_layers=1, text_layers=1).cuda()
+    params = [p for p in model.parameters() if p.requires_grad]
+    before = [p.detach().clone() for p in params]
+    frozen = model.image_encoder.vit.encoder.layer[0].attention.attention.query.base.weight
+    frozen_before = frozen.detach().clone()
+    opt = torch.optim.SGD(params, lr=0.1)
+    batch = harness.synthetic_batch(48, "cuda", seed=2)
+    crit = bsc.ContrastiveLoss(torch.nn.CrossEntropyLoss(), 1 / 0.07, precision="fp32")
+    loss = harness.train_step(model, crit, opt, batch, autocast_dtype=None)
+    assert torch.isfinite(loss)
+    assert torch.equal(frozen, frozen_before) and frozen.grad is None
+    assert any(not torch.equal(p, b) for p, b in zip(params, before))
+    with torch.no_grad():
+        outs = model(*batch[:3])
+    ref, _ = loss_oracle.closed_form_grads([o.float().cpu() for o in outs], batch[3].cpu())
+    got = crit(*[o.detach().requires_grad_(True) for o in outs], batch[3])
+    assert abs(float(got) - float(ref)) <= FP32_TOL * abs(float(ref)) + LOSS_FLOOR
