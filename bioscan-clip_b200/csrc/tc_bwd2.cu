@@ -478,9 +478,9 @@ int tc_bwd_duo_jsplit(const bsc_infonce_desc* d) {
   const int clusters = sm_count2() / 2;
   if (items0 <= 0 || steps <= 0) return 1;
   if (forced > 0) return (int)(forced > steps ? steps : forced);
-  // measured on B200 (1 GPU, N = 4096 and 8192, split forced to 1): 10.25 k cycles per step, 35 k per item (pipeline
-  // fill + accumulator drain are not overlapped across items yet)
-  const double step_cost = 10250.0, item_cost = 35000.0;
+  // measured on B200 (1 GPU, N = 8192 and 32768, BSC_BWD_JSPLIT = 1, 2, 4, 8): T = K0 + rounds * (steps * c + F) fits
+  // with c = 5.2 us (9.9 k cycles) per step and F = 10 us (19 k cycles) per item; K0 (86 us per launch) is common
+  const double step_cost = 9900.0, item_cost = 19000.0;
   int best = 1;
   double best_t = 1e300;
   for (int s = 1; s <= 8; s *= 2) {
