@@ -22,7 +22,7 @@ EXPORTS = [
     "bsc_version", "bsc_last_error", "bsc_device_check", "bsc_l2norm_fwd", "bsc_rows_to_f16", "bsc_label_stats", "bsc_label_stats_workspace_bytes",
     "bsc_gather_layout", "bsc_gather_push",
     "bsc_infonce_stats_len", "bsc_infonce_workspace_bytes", "bsc_infonce_fwd", "bsc_infonce_loss",
-    "bsc_infonce_bwd", "bsc_bank_search_workspace_bytes", "bsc_bank_search", "bsc_topk_merge", "bsc_taxonomy_eval",
+    "bsc_infonce_bwd", "bsc_bank_search_workspace_bytes", "bsc_bank_search", "bsc_bank_screen_parts", "bsc_bank_screen", "bsc_bank_rescore", "bsc_topk_merge", "bsc_taxonomy_eval",
     "bsc_set_timing", "bsc_last_kernel_ms", "bsc_launch_count",
 ]
 
@@ -61,6 +61,10 @@ def lib():
     L.bsc_label_stats.argtypes = [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                   c_void_p]
     L.bsc_label_stats_workspace_bytes.argtypes = [c_int64, POINTER(c_size_t)]
+    L.bsc_bank_screen_parts.argtypes = [c_int64, c_int64, c_int, POINTER(c_int)]
+    L.bsc_bank_screen.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p]
+    L.bsc_bank_rescore.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p, c_int, c_int,
+                                   c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
     L.bsc_taxonomy_eval.argtypes = [c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_int, POINTER(c_int32), c_int,
                                     POINTER(c_int64), c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
     L.bsc_gather_layout.argtypes = [c_int64, c_int, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t),

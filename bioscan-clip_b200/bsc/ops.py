@@ -7,7 +7,7 @@ stand-in defined under ``tests/`` -- the product modules always construct ``Cuda
 from __future__ import annotations
 
 import ctypes
-from ctypes import byref, c_size_t, c_void_p
+from ctypes import byref, c_int, c_size_t, c_void_p
 from dataclasses import dataclass, field
 from typing import List, Optional
 
@@ -174,6 +174,43 @@ class CudaOps:
                                         scores.data_ptr(), ids.data_ptr(), ws.data_ptr(), ws.numel(),
                                         stream_ptr(dev)))
         return scores, ids
+
+    def bank_search_exact(self, queries32: torch.Tensor, bank32: torch.Tensor, bank16: torch.Tensor, k: int,
+                          base_id: int, max_row_norm: float, min_parts: int = 16):
+        """Exact float32 top-k through the bf16 screening pass + float32 re-scoring; queries whose result the bound
+        cannot prove are re-run with the exhaustive float32 kernel.  Returns (scores, ids, n_rechecked)."""
+        dev = bank32.device
+        _lib.require_device(dev)
+        nq, d = queries32.shape
+        nb = bank32.shape[0]
+        if k > 8 or d % 64 != 0 or nb == 0 or nq == 0:
+            s, i = self.bank_search(queries32, bank32, k, base_id, MODE_F32)
+            return s, i, nq
+        parts = c_int(0)
+        check(lib().bsc_bank_screen_parts(nq, nb, min_parts, byref(parts)))
+        parts = int(parts.value)
+        q16 = queries32.to(torch.bfloat16).contiguous()
+        cs = torch.empty((parts, nq, 8), dtype=torch.float32, device=dev)
+        ci = torch.empty((parts, nq, 8), dtype=torch.int64, device=dev)
+        scores = torch.empty((nq, k), dtype=torch.float32, device=dev)
+        ids = torch.empty((nq, k), dtype=torch.int64, device=dev)
+        unsure = torch.empty(nq, dtype=torch.int32, device=dev)
+        n_unsure = torch.empty(1, dtype=torch.int32, device=dev)
+        # |<q,b> - <bf16(q),bf16(b)>| <= (2 * 2^-9 + 2^-18) |q||b|; 1.05 covers the fp32 accumulation of both sides
+        eps_scale = 1.05 * (2.0 ** -8 + 2.0 ** -18) * float(max_row_norm)
+        with torch.cuda.device(dev):
+            check(lib().bsc_bank_screen(q16.data_ptr(), nq, bank16.data_ptr(), nb, d, base_id, min_parts, cs.data_ptr(),
+                                        ci.data_ptr(), stream_ptr(dev)))
+            check(lib().bsc_bank_rescore(queries32.data_ptr(), nq, bank32.data_ptr(), nb, d, base_id, cs.data_ptr(),
+                                         ci.data_ptr(), parts, k, eps_scale, scores.data_ptr(), ids.data_ptr(),
+                                         unsure.data_ptr(), n_unsure.data_ptr(), stream_ptr(dev)))
+        n_bad = int(n_unsure.item())
+        if n_bad:
+            rows = torch.nonzero(unsure, as_tuple=False).flatten()
+            s2, i2 = self.bank_search(queries32[rows].contiguous(), bank32, k, base_id, MODE_F32)
+            scores[rows] = s2
+            ids[rows] = i2
+        return scores, ids, n_bad
 
     def topk_merge(self, cand_scores: torch.Tensor, cand_ids: torch.Tensor):
         """[parts, nq, k] candidate lists -> [nq, k] (score desc, id asc)."""

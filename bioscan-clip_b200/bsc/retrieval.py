@@ -10,7 +10,9 @@
 The bank lives in HBM, split row-wise over ``devices`` at ``add`` time (one shard per GPU); a search scans
 every shard on its own GPU and merges the per-shard top-k with ``bsc_topk_merge``.
 ``precision="fp32"`` is the exact mode (float32 bank, indices comparable bit for bit with a float32 CPU
-search); ``precision="bf16"`` stores the bank in bfloat16 and scans it with the tcgen05 kernel.
+search, exhaustive CUDA-core kernel); ``precision="exact"`` returns the same float32 results at tensor-core speed
+(bf16 screening pass + exact re-scoring of the candidates + a proof per query, unproven queries re-run
+exhaustively); ``precision="bf16"`` stores the bank in bfloat16 and scans it with the tcgen05 kernel.
 """
 from __future__ import annotations
 
@@ -34,8 +36,8 @@ def _as_f32_tensor(x, device) -> torch.Tensor:
 class IndexFlatIP:
     def __init__(self, d: int, precision: str = "fp32", devices: Optional[Sequence] = None, ops=None,
                  base_id: int = 0):
-        if precision not in ("fp32", "bf16"):
-            raise ValueError("precision must be 'fp32' or 'bf16'")
+        if precision not in ("fp32", "bf16", "exact"):
+            raise ValueError("precision must be 'fp32', 'bf16' or 'exact'")
         self.d = int(d)
         self.precision = precision
         if devices is None:
@@ -48,8 +50,12 @@ class IndexFlatIP:
 
             ops = CudaOps()
         self._ops = ops
-        self._mode = MODE_F32 if precision == "fp32" else MODE_TC16
-        self._dtype = torch.float32 if precision == "fp32" else torch.bfloat16
+        self._mode = MODE_TC16 if precision == "bf16" else MODE_F32
+        self._dtype = torch.bfloat16 if precision == "bf16" else torch.float32
+        # "exact": float32 results (same as "fp32") found through a bf16 tensor-core screening pass over a bf16 copy of
+        # the bank and exact re-scoring of the candidates; unproven queries fall back to the exhaustive float32 kernel
+        self._screen: List[List[tuple]] = [[] for _ in self.devices]
+        self.last_rechecked = 0
         self._base_id = int(base_id)
         self._chunks: List[List[torch.Tensor]] = [[] for _ in self.devices]  # per device: list of (base, rows)
         self._bases: List[List[int]] = [[] for _ in self.devices]
@@ -58,6 +64,7 @@ class IndexFlatIP:
     def reset(self) -> None:
         self._chunks = [[] for _ in self.devices]
         self._bases = [[] for _ in self.devices]
+        self._screen = [[] for _ in self.devices]
         self.ntotal = 0
 
     def add(self, x) -> None:
@@ -80,12 +87,16 @@ class IndexFlatIP:
                 part = _as_f32_tensor(rows, dev).to(self._dtype).contiguous()
             self._chunks[k].append(part)
             self._bases[k].append(self._base_id + self.ntotal + lo)
+            if self.precision == "exact":
+                max_norm = float(torch.linalg.vector_norm(part, dim=1).max().item())
+                self._screen[k].append((part.to(torch.bfloat16).contiguous(), max_norm))
         self.ntotal += n
 
     def search_device(self, q, k: int):
         """Search returning device tensors (scores, ids) on the first device."""
         dev0 = self.devices[0]
         q0 = _as_f32_tensor(q, dev0)
+        self.last_rechecked = 0
         if q0.shape[1] != self.d:
             raise ValueError(f"expected queries of dimension {self.d}, got {q0.shape[1]}")
         cand_s, cand_i = [], []
@@ -93,8 +104,13 @@ class IndexFlatIP:
             if not self._chunks[kdev]:
                 continue
             qd = q0.to(dev).to(self._dtype).contiguous()
-            for base, rows in zip(self._bases[kdev], self._chunks[kdev]):
-                s, i = self._ops.bank_search(qd, rows, k, base, self._mode)
+            for ci, (base, rows) in enumerate(zip(self._bases[kdev], self._chunks[kdev])):
+                if self.precision == "exact":
+                    rows16, max_norm = self._screen[kdev][ci]
+                    s, i, nbad = self._ops.bank_search_exact(qd, rows, rows16, k, base, max_norm)
+                    self.last_rechecked += nbad
+                else:
+                    s, i = self._ops.bank_search(qd, rows, k, base, self._mode)
                 cand_s.append(s.to(dev0))
                 cand_i.append(i.to(dev0))
         nq = q0.shape[0]

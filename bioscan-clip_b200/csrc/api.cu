@@ -14,6 +14,12 @@ int l2norm_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, voi
 int rows_to_f16_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, float* inv,
                        cudaStream_t st);
 size_t label_stats_ws_bytes(int64_t n);
+int tc_bank_screen_parts(int64_t nq, int64_t nb, int min_parts);
+int tc_bank_screen(const void* q, int64_t nq, const void* bank, int64_t nb, int d, int64_t base_id, int min_parts,
+                   float* cand_s, int64_t* cand_i, cudaStream_t st);
+int rescore_launch(const float* q, int64_t nq, const float* bank, int64_t nb, int d, int64_t base_id, const float* cs,
+                   const int64_t* ci, int parts, int k, float eps_scale, float* os, int64_t* oi, int32_t* unsure,
+                   int32_t* n_unsure, cudaStream_t st);
 int taxo_launch(const int64_t* indices, int64_t nq, int k, const int32_t* key_ids, int64_t nb, const int32_t* gt_ids,
                 int levels, const int32_t* k_list, int nk, const int64_t* class_off, int64_t total_classes,
                 int32_t* pred_ids, uint8_t* first_hit, int64_t* micro, int32_t* pred_counts, int32_t* gt_counts,
@@ -394,6 +400,33 @@ int bsc_bank_search(const void* queries, int64_t nq, const void* bank, int64_t n
                           workspace_bytes, st);
   set_error("bsc_bank_search: unknown mode %d", mode);
   return BSC_EINVAL;
+}
+
+int bsc_bank_screen_parts(int64_t nq, int64_t nb, int min_parts, int* parts) {
+  BSC_REQUIRE(parts && nq >= 0 && nb >= 0 && min_parts >= 0, BSC_EINVAL, "bsc_bank_screen_parts: bad argument");
+  *parts = tc_bank_screen_parts(nq, nb, min_parts);
+  return BSC_OK;
+}
+
+int bsc_bank_screen(const void* queries_bf16, int64_t nq, const void* bank_bf16, int64_t nb, int d, int64_t base_id,
+                    int min_parts, float* cand_scores, int64_t* cand_ids, void* stream) {
+  BSC_REQUIRE(nq >= 0 && nb >= 1 && d >= 1, BSC_EINVAL, "bsc_bank_screen: bad shape");
+  BSC_REQUIRE((queries_bf16 && cand_scores && cand_ids) || nq == 0, BSC_EINVAL, "bsc_bank_screen: null pointer");
+  BSC_REQUIRE(bank_bf16, BSC_EINVAL, "bsc_bank_screen: null bank");
+  return tc_bank_screen(queries_bf16, nq, bank_bf16, nb, d, base_id, min_parts, cand_scores, cand_ids,
+                        (cudaStream_t)stream);
+}
+
+int bsc_bank_rescore(const float* queries, int64_t nq, const float* bank, int64_t nb, int d, int64_t base_id,
+                     const float* cand_scores, const int64_t* cand_ids, int parts, int k, float eps_scale,
+                     float* out_scores, int64_t* out_ids, int32_t* unsure, int32_t* n_unsure, void* stream) {
+  BSC_REQUIRE(nq >= 0 && nb >= 1 && d >= 1 && parts >= 1, BSC_EINVAL, "bsc_bank_rescore: bad shape");
+  BSC_REQUIRE((queries && cand_scores && cand_ids && out_scores && out_ids && unsure) || nq == 0, BSC_EINVAL,
+              "bsc_bank_rescore: null pointer");
+  BSC_REQUIRE(bank && n_unsure, BSC_EINVAL, "bsc_bank_rescore: null pointer");
+  BSC_REQUIRE(eps_scale >= 0.f, BSC_EINVAL, "bsc_bank_rescore: negative eps_scale");
+  return rescore_launch(queries, nq, bank, nb, d, base_id, cand_scores, cand_ids, parts, k, eps_scale, out_scores,
+                        out_ids, unsure, n_unsure, (cudaStream_t)stream);
 }
 
 int bsc_topk_merge(const float* cand_scores, const int64_t* cand_ids, int parts, int64_t nq, int k, float* out_scores,

@@ -586,13 +586,31 @@ int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, float*
 }
 
 // ---- retrieval ---------------------------------------------------------------------------------------
-static void bank_tiling(int64_t nq, int64_t nb, int* n_iblk, int* n_jtile, int* jpc, int* n_jchunk) {
+static void bank_tiling(int64_t nq, int64_t nb, int* n_iblk, int* n_jtile, int* jpc, int* n_jchunk,
+                        int min_parts = 0) {
   *n_iblk = (int)((nq + BM - 1) / BM);
   *n_jtile = (int)((nb + BN - 1) / BN);
   // enough items to fill the machine a few times, few enough that the candidate lists stay small
   const int target = num_sms() * 2;
   int chunks = (target + *n_iblk - 1) / *n_iblk;
   if (chunks < 1) chunks = 1;
+  if (*n_iblk > target) {
+    // many query blocks: whole passes over the bank per work item.  Cut the bank in a few chunks so that the last
+    // round of items does not leave most SMs idle (782 blocks on 74 CTA pairs: 5.3 rounds -> 6 without chunks)
+    const bool pairs = (*n_iblk % 2) == 0;
+    const double units = pairs ? num_sms() / 2 : num_sms();
+    const double per_chunk = pairs ? *n_iblk / 2 : *n_iblk;
+    double best = 1e30;
+    for (int c = 1; c <= 16; ++c) {
+      const double rounds = per_chunk * c / units;
+      const double waste = (double)(int64_t)(rounds + 0.999999) / rounds;
+      if (waste < best * 0.99) {
+        best = waste;
+        chunks = c;
+      }
+    }
+  }
+  if (chunks * NG < min_parts) chunks = (min_parts + NG - 1) / NG;  // screening pass: at least min_parts lists
   if (chunks > *n_jtile) chunks = *n_jtile > 0 ? *n_jtile : 1;
   *jpc = (*n_jtile + chunks - 1) / chunks;
   if (*jpc < 1) *jpc = 1;
@@ -651,6 +669,46 @@ int tc_bank_search(const void* q, int64_t nq, const void* bank, int64_t nb, int 
     if (rc) return rc;
   }
   return topk_merge_launch(p.cand_s, p.cand_i, parts, nq, k, out_s, out_i, st);
+}
+
+// Screening pass of the exact search: the bf16 scan with every (column chunk, epilogue group) candidate list of KTOP
+// entries handed out unmerged.  parts = number of lists; a bank row that is in no list scored (in bf16) at most the
+// last entry of its own list.
+int tc_bank_screen_parts(int64_t nq, int64_t nb, int min_parts) {
+  int n_iblk, n_jtile, jpc, n_jchunk;
+  bank_tiling(nq, nb, &n_iblk, &n_jtile, &jpc, &n_jchunk, min_parts);
+  return n_jchunk * NG;
+}
+
+int tc_bank_screen(const void* q, int64_t nq, const void* bank, int64_t nb, int d, int64_t base_id, int min_parts,
+                   float* cand_s, int64_t* cand_i, cudaStream_t st) {
+  BSC_REQUIRE(d % BK == 0, BSC_EUNSUPPORTED, "screening needs d %% 64 == 0 (got %d)", d);
+  BSC_REQUIRE(nb > 0 && nb < (1ll << 31) - 512 && nq < (1ll << 31) - 512, BSC_EUNSUPPORTED,
+              "shard size unsupported by the screening pass");
+  if (nq == 0) return BSC_OK;
+  SimParams p{};
+  int rc = make_tmap_2d(&p.tmap[0], q, BSC_BF16, nq, d, 128);
+  if (rc) return rc;
+  rc = make_tmap_2d(&p.tmap[1], bank, BSC_BF16, nb, d, 128);
+  if (rc) return rc;
+  p.tmap[2] = p.tmap[0];
+  p.n_pairs = 1;
+  p.pair_a[0] = 0;
+  p.pair_b[0] = 1;
+  bank_tiling(nq, nb, &p.n_iblk, &p.n_jtile, &p.jpc, &p.n_jchunk, min_parts);
+  p.num_items = p.n_jchunk * p.n_iblk;
+  p.kblocks = d / BK;
+  p.a_rows = nq;
+  p.a_row0 = 0;
+  p.b_rows = nb;
+  p.k = KTOP;
+  p.base_id = base_id;
+  p.cand_s = cand_s;
+  p.cand_i = cand_i;
+  timing_begin(2, st);
+  rc = launch_sim<EPI_TOPK, 1>(p, st);
+  timing_end(2, st);
+  return rc;
 }
 
 }  // namespace bsc

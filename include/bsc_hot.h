@@ -163,6 +163,24 @@ int bsc_bank_search_workspace_bytes(int64_t nq, int64_t nb, int d, int k, int mo
 int bsc_bank_search(const void* queries, int64_t nq, const void* bank, int64_t nb, int d, int k,
                     int64_t base_id, int mode, float* out_scores, int64_t* out_ids, void* workspace,
                     size_t workspace_bytes, void* stream);
+/* ------------------------------------------------------------------------------------------------
+ * Exact float32 search at tensor-core speed (same results as BSC_MODE_F32 of bsc_bank_search, i.e. as
+ * IndexFlatIP.search on float32 data): screen + rescore.
+ *   bsc_bank_screen   bf16 scan of a bf16 copy of the shard; hands out `parts` unmerged candidate lists of 8 entries
+ *                     [parts][nq][8] (score, id; id -1 = empty).  parts = bsc_bank_screen_parts(nq, nb, min_parts)
+ *                     >= min_parts.  A row that is in no list has a bf16 score <= the last entry of its own list.
+ *   bsc_bank_rescore  exact float32 dot products of every candidate with the float32 query, ordered (score desc,
+ *                     id asc) -> out [nq,k], k <= 8.  unsure[q] = 0 when the k-th exact score exceeds the best
+ *                     possible score of any non-candidate (its list's last bf16 score + eps_scale * ||q||, eps_scale =
+ *                     2^-8 * max bank row norm * slack): then the result provably equals the exhaustive float32 search.
+ *                     Queries with unsure[q] = 1 (n_unsure of them) must be re-run with bsc_bank_search(BSC_MODE_F32).
+ * ---------------------------------------------------------------------------------------------- */
+int bsc_bank_screen_parts(int64_t nq, int64_t nb, int min_parts, int* parts);
+int bsc_bank_screen(const void* queries_bf16, int64_t nq, const void* bank_bf16, int64_t nb, int d, int64_t base_id,
+                    int min_parts, float* cand_scores, int64_t* cand_ids, void* stream);
+int bsc_bank_rescore(const float* queries, int64_t nq, const float* bank, int64_t nb, int d, int64_t base_id,
+                     const float* cand_scores, const int64_t* cand_ids, int parts, int k, float eps_scale,
+                     float* out_scores, int64_t* out_ids, int32_t* unsure, int32_t* n_unsure, void* stream);
 /* k-way merge of `parts` candidate lists [parts][nq][k] (e.g. one per GPU after an all_gather). */
 int bsc_topk_merge(const float* cand_scores, const int64_t* cand_ids, int parts, int64_t nq, int k,
                    float* out_scores, int64_t* out_ids, void* stream);

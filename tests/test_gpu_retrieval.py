@@ -204,3 +204,27 @@ def test_stream_to_index_equals_single_add(tmp_path):
     sa, ia = a.search(q, 5)
     sb, ib = b.search(q, 5)
     assert np.array_equal(ia, ib) and np.array_equal(sa, sb)
+
+
+@pytest.mark.parametrize("nb,nq,d,n_random", [(50000, 96, 768, 32), (20000, 300, 128, 300), (700, 40, 64, 10)])
+def test_exact_mode_screen_and_rescore_equals_exhaustive_float32(nb, nq, d, n_random):
+    """precision='exact' (bf16 screening + float32 re-scoring + per-query proof) returns the indices of the exhaustive
+    float32 search: planted neighbours, pure-random queries (small margins) and duplicated bank rows (ties)."""
+    import bsc
+
+    bank, q, _ = bank_inputs(nb, nq, d, seed=nb % 17, n_random=n_random)
+    want_s, want_i = ro.search_ip(bank, q, 5)
+    idx = bsc.IndexFlatIP(d, precision="exact")
+    idx.add(bank)
+    s, i = idx.search(q, 5)
+    assert np.array_equal(i, want_i)
+    assert np.abs(s - want_s).max() <= 2e-6
+    assert 0 <= idx.last_rechecked <= nq
+    ref = bsc.IndexFlatIP(d, precision="fp32")
+    ref.add(bank)
+    assert np.array_equal(ref.search(q, 5)[1], i)
+    # un-normalised rows of mixed scale: the bound scales with the largest row norm
+    scale = np.random.default_rng(1).uniform(0.5, 3.0, size=(nb, 1)).astype(np.float32)
+    idx2 = bsc.IndexFlatIP(d, precision="exact")
+    idx2.add(bank * scale)
+    assert np.array_equal(idx2.search(q, 5)[1], ro.search_ip(bank * scale, q, 5)[1])
