@@ -249,7 +249,7 @@ def run_native(args):
     if rank == 0:
         sampler.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    fwd_ms, bwd_ms = [], []
+    fwd_ms, bwd_ms, rev_ms = [], [], []
     _lib.launch_count(reset=True)
     barrier()
     t_wall0 = time.perf_counter()
@@ -263,6 +263,7 @@ def run_native(args):
         ev[k][1].synchronize()
         fwd_ms.append(_lib.last_kernel_ms(0))
         bwd_ms.append(_lib.last_kernel_ms(1))
+        rev_ms.append(_lib.last_kernel_ms(3))  # -1 unless the stored-weight backward ran (one GPU)
     barrier()
     t_wall = time.perf_counter() - t_wall0
     launches = _lib.launch_count(reset=True)  # kernels launched by libbsc_hot.so inside the timed loop
@@ -358,23 +359,39 @@ def run_native(args):
     peaks = measured_peaks()
     bwd_avg = sum(bwd_ms) / len(bwd_ms) if bwd_ms and min(bwd_ms) > 0 else None
     fwd_avg = sum(fwd_ms) / len(fwd_ms) if fwd_ms and min(fwd_ms) > 0 else None
-    # algorithmic work of one launch on this rank: 2 gradient GEMMs per unordered pair, 3 pairs
-    bwd_flops = 12.0 * n_local * n_global * DIM
+    rev_avg = sum(rev_ms) / len(rev_ms) if rev_ms and min(rev_ms) > 0 else None
+    # Algorithmic work: one forward GEMM + two gradient GEMMs per unordered pair, 3 pairs; recomputing S in
+    # the backward is NOT counted.  Recomputing sweep (several GPUs): one launch forms both gradient GEMMs of every
+    # pair (12 n N D).  Stored-weight backward (one GPU): the sweep forms one gradient GEMM per pair (6 n N D; it
+    # EXECUTES 12: S once + that GEMM) and tc_bwd_rev_kernel the other one from the stored weights (6 n N D).
+    stored = rev_avg is not None
+    bwd_flops = (6.0 if stored else 12.0) * n_local * n_global * DIM
     fwd_flops = 6.0 * n_local * n_global * DIM
     roofline = None
     if bwd_avg:
         ach = bwd_flops / (bwd_avg * 1e-3) / 1e12
+        traffic = None
+        if world == 1 and n_global == 32768:
+            # dram__bytes_read.sum + dram__bytes_write.sum of one launch from the `ncu --set full` captures summarised
+            # in profiles/ (r1_bwd_duo_store.txt: 1.57 GB read + 6.99 GB of stored weights; r1_bwd_duo.txt otherwise)
+            traffic = 8.566e9 if stored else 2.164e9
         roofline = {"bound": "tensor", "achieved": ach, "peak": peaks["tflops_sustained"],
                     "unit": "TFLOP/s", "frac": ach / peaks["tflops_sustained"],
-                    # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the `ncu --set full` capture
-                    # summarised in profiles/r1_bwd_duo.txt (taken at world=1, N=32768 only)
-                    "traffic": 2.164e9 if (world == 1 and n_global == 32768) else None, "traffic_unit": "B",
+                    "traffic": traffic, "traffic_unit": "B",
                     "kernel": "tc_bwd_duo_kernel",
                     "peak_source": peaks["source"] + " bf16_tflops_sustained (kernel timed inside a long step)",
                     "kernel_ms": bwd_avg, "fwd_kernel_ms": fwd_avg,
                     "fwd_achieved": (fwd_flops / (fwd_avg * 1e-3) / 1e12) if fwd_avg else None,
                     "step_achieved": 18.0 * n_local * n_global * DIM / (ms_per_step * 1e-3) / 1e12,
-                    "algorithmic_flops_per_launch": bwd_flops}
+                    "step_frac": 18.0 * n_local * n_global * DIM / (ms_per_step * 1e-3) / 1e12 / peaks["tflops_sustained"],
+                    "algorithmic_flops_per_launch": bwd_flops,
+                    "executed_tflops": 12.0 * n_local * n_global * DIM / (bwd_avg * 1e-3) / 1e12 * (1.0 if stored else 2.0),
+                    "backward": "stored weights: sweep per unordered pair + tc_bwd_rev_kernel" if stored
+                                else "recomputing sweep per ordered pair"}
+        if stored:
+            roofline["rev_kernel_ms"] = rev_avg
+            roofline["rev_achieved"] = 6.0 * n_local * n_global * DIM / (rev_avg * 1e-3) / 1e12
+            roofline["bwd_achieved"] = 12.0 * n_local * n_global * DIM / ((bwd_avg + rev_avg) * 1e-3) / 1e12
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

@@ -47,8 +47,8 @@ static thread_local char g_err[512] = "";
 static std::atomic<int64_t> g_launches{0};
 static std::atomic<int> g_timing{0};
 static std::mutex g_ev_mutex;
-static cudaEvent_t g_ev[3][2] = {{nullptr, nullptr}, {nullptr, nullptr}, {nullptr, nullptr}};
-static bool g_ev_valid[3] = {false, false, false};
+static cudaEvent_t g_ev[4][2] = {{nullptr, nullptr}, {nullptr, nullptr}, {nullptr, nullptr}, {nullptr, nullptr}};
+static bool g_ev_valid[4] = {false, false, false, false};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -114,6 +114,21 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, int64_t rows, in
   return BSC_OK;
 }
 
+int make_tmap_raw128(CUtensorMap* out, const void* base, int64_t rows, int box_rows) {
+  EncodeTiledFn enc = get_encoder();
+  BSC_REQUIRE(enc != nullptr, BSC_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  BSC_REQUIRE(((uintptr_t)base & 127) == 0 && rows > 0, BSC_EINVAL, "raw TMA operand must be 128-byte aligned");
+  cuuint64_t gdim[2] = {64u, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {128u};
+  cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  BSC_REQUIRE(r == CUDA_SUCCESS, BSC_ECUDA, "cuTensorMapEncodeTiled (raw) failed with CUresult %d", (int)r);
+  return BSC_OK;
+}
+
 // ---- workspace layout ---------------------------------------------------------------------------
 static int present_count(const bsc_infonce_desc* p, unsigned* mask) {
   int m = 0;
@@ -157,8 +172,15 @@ InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p) {
   L.rowpos = take((size_t)3 * 2 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
   L.jrange = take((size_t)(L.n_jtile > 0 ? L.n_jtile : 1) * 2 * sizeof(int));
   L.colpart = take((size_t)3 * (L.n_iblk > 0 ? L.n_iblk : 1) * L.n_global_pad * sizeof(float));
+  L.bwd_gstore = tc_bwd_gstore(p) ? 1 : 0;
   L.bwd_jsplit = tc_bwd_duo_jsplit(p);
   L.dxraw = take((size_t)3 * 2 * L.bwd_jsplit * (n > 0 ? n : 1) * D * sizeof(float));
+  if (L.bwd_gstore) {
+    L.xunit = take((size_t)3 * N * D * 2);
+    L.gimg = take(tc_bwd_gimg_bytes(p));
+  } else {
+    L.xunit = L.gimg = off;
+  }
   L.gscratch = (p->mode == BSC_MODE_F32) ? take((size_t)L.g_rows * N * sizeof(float)) : off;
   L.total = off;
   return L;
@@ -213,7 +235,7 @@ int bsc_set_timing(int enabled) {
 
 float bsc_last_kernel_ms(int which) {
   std::lock_guard<std::mutex> lock(g_ev_mutex);
-  if (which < 0 || which > 2 || !g_ev_valid[which]) return -1.0f;
+  if (which < 0 || which > 3 || !g_ev_valid[which]) return -1.0f;
   if (cudaEventSynchronize(g_ev[which][1]) != cudaSuccess) return -1.0f;
   float ms = -1.0f;
   if (cudaEventElapsedTime(&ms, g_ev[which][0], g_ev[which][1]) != cudaSuccess) return -1.0f;

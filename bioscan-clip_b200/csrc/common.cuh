@@ -59,10 +59,13 @@ struct InfoNceWs {
   size_t jrange;    // int2  [n_jtile]       label-class range of every column tile
   size_t dxraw;     // float [3][2][bwd_jsplit][n_local][D]
   size_t gscratch;  // float [g_rows][N]     fp32 mode only
+  size_t xunit;     // half  [3][N][D]       unit rows (stored-weight backward only)
+  size_t gimg;      // half  [pairs][2*n_steps][2*n_iblk][128][64]  weight spans of the backward sweep (stored-weight only)
   size_t total;
   // tiling facts shared by host and kernels
   int n_iblk, n_jtile, n_jchunk, jtiles_per_chunk;
   int bwd_jsplit;   // dxraw parts per (modality, slot): > 1 only for the CTA-pair backward sweep (tc_bwd2.cu)
+  int bwd_gstore;   // 1: the sweep runs once per UNORDERED pair and stores its weights; tc_bwd3.cu forms the other side
   int64_t n_local_pad, n_global_pad, g_rows;
 };
 
@@ -91,6 +94,12 @@ int tc_bwd_raw(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStre
 // CTA-pair (cta_group::2) sweep; returns 1 when the shape is not covered and the caller must use tc_bwd_raw's own kernels
 int tc_bwd_duo(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st);
 int tc_bwd_duo_jsplit(const bsc_infonce_desc* p);
+// stored-weight backward (all rows local): is it used for this problem, and how many bytes of weight spans it keeps
+bool tc_bwd_gstore(const bsc_infonce_desc* p);
+size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* p);
+int tc_bwd_rev(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_pairs,
+               const int* pairs_x, const int* pairs_y, int n_jb, int n_i64, cudaStream_t st);
+int rows_unit_f16_launch(const void* x16, const float* inv, int64_t n, int d, void* out, cudaStream_t st);
 
 int simt_bank_search(const float* q, int64_t nq, const float* bank, int64_t nb, int d, int k, int64_t base_id,
                      float* out_s, int64_t* out_i, char* ws, size_t ws_bytes, cudaStream_t st);

@@ -127,6 +127,27 @@ int rows_to_f16_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx
   return BSC_OK;
 }
 
+// fp16 unit rows from the scaled fp16 rows: out = half(x16 * inv).  B operand of the stored-weight backward (tc_bwd3.cu).
+__global__ void __launch_bounds__(256) rows_unit_f16_kernel(const __half2* __restrict__ x, const float* __restrict__ inv,
+                                                            int64_t n, int d2, __half2* __restrict__ out) {
+  const int64_t total = n * (int64_t)d2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const float s = inv[i / d2];
+    const float2 v = __half22float2(x[i]);
+    out[i] = __floats2half2_rn(v.x * s, v.y * s);
+  }
+}
+
+int rows_unit_f16_launch(const void* x16, const float* inv, int64_t n, int d, void* out, cudaStream_t st) {
+  if (n == 0) return BSC_OK;
+  BSC_REQUIRE(d % 2 == 0, BSC_EUNSUPPORTED, "rows_unit_f16: odd d");
+  const int64_t total = n * (int64_t)(d / 2);
+  const unsigned grid = (unsigned)((total + 255) / 256 > 148 * 16 ? 148 * 16 : (total + 255) / 256);
+  rows_unit_f16_kernel<<<grid, 256, 0, st>>>((const __half2*)x16, inv, n, d / 2, (__half2*)out);
+  BSC_LAUNCH_CHECK("rows_unit_f16_kernel");
+  return BSC_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Fused TC16 operand preparation + all-gather over NVLink peer memory (gather_features, loss_func.py:58-91, for the
 // default gather_with_grad=False where only values travel).  Every rank holds a symmetric buffer

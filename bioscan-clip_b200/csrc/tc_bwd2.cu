@@ -62,6 +62,11 @@ struct DuoParams {
   const float* gsbuf;   // [6][2]
   const float* inv[3];
   float* dxraw;         // [3][2][jsplit][n_local][d]
+  // stored-weight mode (all rows local, one item list over the UNORDERED pairs): every weight span is also copied to
+  // gimg[(xy * 2 n_steps + j tile) * n_i64 + (2 iblk + h)][16 KB] for tc_bwd_rev_kernel (tc_bwd3.cu); null = off
+  uint8_t* gimg;
+  int n_i64;
+  int dbg_nostore;  // experiment knob (BSC_DBG_NOSTORE=1): stored-weight item list without the copies (results invalid)
 };
 
 // item -> (ordered pair, row block, part of the column sweep); steps [s_lo, s_hi) of part `part`
@@ -359,7 +364,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
         ptx::tmem_ld_wait();
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive_remote(s_free_l);
+        if (lane == 0) ptx::mbar_arrive_remote_nodata(s_free_l);
 
         const float* fi = &tail->inv_i[h * 64];
         const float* fu = &tail->ugk_i[h * 64];
@@ -394,10 +399,28 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
         __syncwarp();
         if (lane == 0) {
           if (keep) {
-            ptx::mbar_arrive_remote(ready_l);
+            ptx::mbar_arrive_remote_nodata(ready_l);
           } else {
-            ptx::mbar_arrive_expect_tx_remote(ship_bar, 4096u);
+            ptx::mbar_arrive_expect_tx_remote_cta(ship_bar, 4096u);
             ptx::bulk_copy_to_peer(peer_dst, dst_local + piece, 4096u, ship_bar);
+          }
+        }
+        if (p.gimg != nullptr && p.dbg_nostore != 1) {
+          // The same bytes at the same offsets of the span's image in HBM: the warp reads its own 4 KB piece back from
+          // shared memory so that every store instruction covers 512 contiguous bytes, after the hand-over above.
+          // Measured (N = 32768, sweep alone): 8.4 ms without the stores, 8.7 ms with the read-back only, 10.2-10.6 ms
+          // with the stores -- the same for a bulk copy out of shared memory, for 16-byte stores from registers and for
+          // stores that hit one L2-resident buffer: bytes LEAVING the SM slow the pair MMAs, whatever their route.
+          const int64_t span = ((int64_t)xy * (2 * p.n_steps) + (2 * s + (int)crank)) * p.n_i64 + (2 * iblk + h);
+          uint8_t* gdst = p.gimg + span * GSPAN + piece + lane * 16;
+          const uint32_t src = dst_local + piece + lane * 16;
+#pragma unroll
+          for (int t = 0; t < 8; ++t) {
+            uint4 v;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                         : "r"(src + t * 512));
+            __stcs(reinterpret_cast<uint4*>(gdst + t * 512), v);
           }
         }
       }
@@ -427,7 +450,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_remote(acc_free_l);
+      if (lane == 0) ptx::mbar_arrive_remote_nodata(acc_free_l);
     }
   }
 
@@ -462,6 +485,27 @@ static bool duo_covers(const bsc_infonce_desc* d) {
          sm_count2() >= 2;
 }
 
+// Stored-weight backward: with all rows on this GPU the weight matrix of an unordered pair serves both directions, so
+// the sweep runs once per unordered pair, copies its fp16 weight spans to HBM (2 N^2 bytes per pair) and a plain GEMM
+// (tc_bwd3.cu) forms the other side.  BSC_BWD_GSTORE=0 turns it off; spans above BSC_BWD_GSTORE_GB (default 48) too.
+size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* d) {
+  int m = 0;
+  for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
+  const size_t n_iblk = (size_t)((d->n_local + BM - 1) / BM);
+  const size_t n_steps = (size_t)(((d->n_global + BN - 1) / BN + 1) / 2);
+  return (size_t)(m * (m - 1) / 2) * (2 * n_steps) * (2 * n_iblk) * GSPAN;
+}
+
+bool tc_bwd_gstore(const bsc_infonce_desc* d) {
+  if (!duo_covers(d)) return false;
+  if (d->n_local != d->n_global || d->row0 != 0) return false;
+  const char* e = getenv("BSC_BWD_GSTORE");
+  if (e && e[0] == '0') return false;
+  const char* g = getenv("BSC_BWD_GSTORE_GB");
+  const double cap = (g ? atof(g) : 48.0) * 1073741824.0;
+  return (double)tc_bwd_gimg_bytes(d) <= cap;
+}
+
 // In how many parts to cut every (ordered pair, row block) column sweep: the clusters take whole items, so with few
 // row blocks (n_local small: many ranks) ceil(items / clusters) wastes up to a whole sweep.  Cost model per item:
 // steps * (cycles per step) + a fixed fill / drain cost; pick the split in {1, 2, 4, 8} with the lowest makespan.
@@ -473,7 +517,7 @@ int tc_bwd_duo_jsplit(const bsc_infonce_desc* d) {
   }();
   int m = 0;
   for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
-  const int64_t items0 = (int64_t)m * (m - 1) * ((d->n_local + BM - 1) / BM);
+  const int64_t items0 = (int64_t)m * (m - 1) / (tc_bwd_gstore(d) ? 2 : 1) * ((d->n_local + BM - 1) / BM);
   const int64_t steps = ((d->n_global + BN - 1) / BN + 1) / 2;
   const int clusters = sm_count2() / 2;
   if (items0 <= 0 || steps <= 0) return 1;
@@ -515,16 +559,20 @@ int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
       p.tmap128[a] = p.tmap128[first];
       p.tmap64[a] = p.tmap64[first];
     }
+  const bool gstore = L.bwd_gstore != 0;
   int n = 0;
   for (int x = 0; x < 3; ++x) {
     if (!d->xh[x]) continue;
     int slot = 0;
     for (int y = 0; y < 3; ++y) {
       if (y == x || !d->xh[y]) continue;
-      p.xy_x[n] = x;
-      p.xy_y[n] = y;
-      p.xy_slot[n] = slot++;
-      ++n;
+      if (!gstore || y > x) {  // stored-weight mode: unordered pairs x < y; y's side comes from tc_bwd_rev
+        p.xy_x[n] = x;
+        p.xy_y[n] = y;
+        p.xy_slot[n] = slot;
+        ++n;
+      }
+      ++slot;
     }
   }
   p.n_xy = n;
@@ -547,6 +595,12 @@ int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
   p.rep = d->rep;
   p.gsbuf = (const float*)(ws + L.gs);
   p.dxraw = (float*)(ws + L.dxraw);
+  p.gimg = gstore ? (uint8_t*)(ws + L.gimg) : nullptr;
+  p.n_i64 = 2 * p.n_iblk;
+  {
+    const char* e = getenv("BSC_DBG_NOSTORE");
+    p.dbg_nostore = e ? atoi(e) : 0;
+  }
   if (p.num_items == 0 || p.n_jtile == 0) return BSC_OK;
 
   static bool attr_done = false;
@@ -572,6 +626,23 @@ int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
   BSC_CUDA(cudaLaunchKernelEx(&cfg, tc_bwd_duo_kernel, p));
   timing_end(1, st);
   BSC_LAUNCH_CHECK("tc_bwd_duo_kernel");
+  if (gstore) {
+    // unit rows of every modality that is the x side of a pair, then the y sides from the stored spans
+    const void* xunit[3] = {nullptr, nullptr, nullptr};
+    int px[3], py[3];
+    for (int q = 0; q < n; ++q) {
+      px[q] = p.xy_x[q];
+      py[q] = p.xy_y[q];
+      const int a = px[q];
+      if (!xunit[a]) {
+        void* dst = ws + L.xunit + (size_t)a * d->n_global * d->d * 2;
+        int rc = rows_unit_f16_launch(d->xh[a], d->inv[a], d->n_global, d->d, dst, st);
+        if (rc) return rc;
+        xunit[a] = dst;
+      }
+    }
+    return tc_bwd_rev(d, L, ws, xunit, n, px, py, p.n_steps, p.n_i64, st);
+  }
   return BSC_OK;
 }
 

@@ -94,6 +94,20 @@ __device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// Same arrival with CTA-scope release: for hand-overs that carry no data through memory (a TMEM buffer was read with
+// tcgen05.ld + wait::ld + fence::before_thread_sync).  The cluster-scope release compiles to an ERRBAR that waits for
+// every outstanding global store of the thread.
+__device__ __forceinline__ void mbar_arrive_remote_nodata(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cta.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// expect_tx on a peer's barrier with CTA-scope release.  Used where the bytes the waiter will consume were written to
+// THIS CTA's shared memory (complete before the CTA-scope fence returns) and are read by the async proxy after a
+// fence.proxy.async: the cluster-scope form costs MEMBAR.ALL.GPU + ERRBAR + CGAERRBAR per arrival (16 % of the
+// epilogue's samples in the backward sweep).
+__device__ __forceinline__ void mbar_arrive_expect_tx_remote_cta(uint32_t cluster_addr, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.release.cta.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_addr), "r"(bytes)
+               : "memory");
+}
 __device__ __forceinline__ void st_cluster_v4(uint32_t cluster_addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(cluster_addr), "r"(a), "r"(b), "r"(c), "r"(d)
                : "memory");
@@ -112,6 +126,34 @@ __device__ __forceinline__ void bulk_copy_to_peer(uint32_t dst_cluster, uint32_t
                "r"(src_cta), "r"(bytes), "r"(bar_cluster)
                : "memory");
 }
+// bulk copy of local shared memory to global memory (async proxy), tracked by the issuing thread's bulk async-groups
+__device__ __forceinline__ void bulk_store_global(void* dst, uint32_t src_cta, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"((uint64_t)dst), "r"(src_cta),
+               "r"(bytes)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+// L2 eviction policies for streams that must not push the resident operands out of L2
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_store_global_hint(void* dst, uint32_t src_cta, uint32_t bytes, uint64_t policy) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"((uint64_t)dst),
+               "r"(src_cta), "r"(bytes), "l"(policy)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+// the sources of all bulk groups of this thread have been read (the shared memory may be overwritten)
+__device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// all bulk groups of this thread are complete (the global writes are performed)
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -254,6 +296,15 @@ __device__ __forceinline__ void tma_load_2d_2cta(uint32_t dst, const void* tmap,
       : "memory");
 }
 
+__device__ __forceinline__ void tma_load_2d_2cta_hint(uint32_t dst, const void* tmap, uint32_t bar_cluster, int32_t c0,
+                                                      int32_t c1, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+      "[%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst),
+      "l"((uint64_t)tmap), "r"(bar_cluster), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+
 // ---- descriptors ------------------------------------------------------------------------------------
 // Shared-memory matrix descriptor, SWIZZLE_128B (layout_type 2), descriptor version 1 (Blackwell).
 //   bits [0,14)  start address >> 4      bits [16,30) leading byte offset >> 4
@@ -286,5 +337,7 @@ __host__ __device__ constexpr uint32_t umma_idesc(int m, int n, int a_format, in
 
 // Host: encode a 2-D row-major [rows][cols] 16-bit tensor map with a {64 x box_rows} box and 128B swizzle.
 int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, int64_t rows, int64_t cols, int box_rows);
+// Host: [rows][64] 16-bit rows (128 bytes each) copied as they are: {64 x box_rows} box, no swizzle.
+int make_tmap_raw128(CUtensorMap* out, const void* base, int64_t rows, int box_rows);
 
 }  // namespace bsc

@@ -391,7 +391,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
         __syncwarp();
         if (lane == 0) {
           if (PAIR)
-            ptx::mbar_arrive_remote(empty_l0 + buf * 8u);  // the leader's barrier counts both CTAs' epilogue warps
+            ptx::mbar_arrive_remote_nodata(empty_l0 + buf * 8u);  // the leader's barrier counts both CTAs' epilogue warps
           else
             ptx::mbar_arrive(ptx::smem_u32(&tail->tmem_empty[buf]));
         }

@@ -125,6 +125,27 @@ def test_tc16_mode_matches_oracle_on_16bit_inputs(n, d, present, labels, shared,
         assert (err <= bound + 1e-12).all(), (err.max().item(), gr.abs().max().item())
 
 
+@pytest.mark.parametrize("n,d,present,labels,shared", TC16_CASES)
+def test_tc16_recomputing_sweep_matches_oracle_and_stored_weight_backward(n, d, present, labels, shared, monkeypatch):
+    """On one GPU the backward keeps the weight tiles of every unordered pair and forms the second side with
+    tc_bwd_rev_kernel (the default, exercised by the test above); BSC_BWD_GSTORE=0 selects the sweep that recomputes
+    S per ordered pair -- the path every rank of a multi-GPU run takes.  Both against the oracle, and against each
+    other (they share every weight bit; only the second side's row operand is rounded differently)."""
+    feats, lab = loss_inputs(n, d, present, seed=n + 1, labels=labels, shared=shared, dtype=torch.bfloat16)
+    ref_in = [None if f is None else f.float() for f in feats]
+    ref_loss, ref_grads = loss_oracle.closed_form_grads(ref_in, lab)
+    loss_s, grads_s = _run(ref_in, lab, "tc16")
+    monkeypatch.setenv("BSC_BWD_GSTORE", "0")
+    loss_r, grads_r = _run(ref_in, lab, "tc16")
+    assert float(loss_r) == float(loss_s)  # the forward does not depend on the backward mode
+    _compare(loss_r, grads_r, ref_loss, ref_grads, TC16_TOL)
+    for gs_, gr_ in zip(grads_s, grads_r):
+        if gr_ is None:
+            assert gs_ is None
+            continue
+        assert (gs_ - gr_).abs().max().item() <= 1e-3 * gr_.abs().max().item()
+
+
 def test_tc16_unnormalised_rows_of_mixed_scale():
     """Rows whose norms span 0.05 .. 40: the inverse norms live in the fp32 epilogue and in the weight tile."""
     feats, lab = loss_inputs(640, 768, seed=77, labels="multi", normalised=False, dtype=torch.bfloat16)
