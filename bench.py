@@ -117,6 +117,9 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+TRAFFIC_GEMMS = None  # filled in from the ncu capture of tc_bwd_rev_kernel (profiles/r1_bwd_gemms.txt)
+
+
 def synth_loss_rows(torch, n_global, row0, n_local, device, dtype):
     """X_m = normalize(Z + 0.5 E_m) with a shared component Z so matched pairs have
     cos ~ 0.8.  Generated per global row so every world size sees the same global batch."""
@@ -360,38 +363,42 @@ def run_native(args):
     bwd_avg = sum(bwd_ms) / len(bwd_ms) if bwd_ms and min(bwd_ms) > 0 else None
     fwd_avg = sum(fwd_ms) / len(fwd_ms) if fwd_ms and min(fwd_ms) > 0 else None
     rev_avg = sum(rev_ms) / len(rev_ms) if rev_ms and min(rev_ms) > 0 else None
-    # Algorithmic work: one forward GEMM + two gradient GEMMs per unordered pair, 3 pairs; recomputing S in
-    # the backward is NOT counted.  Recomputing sweep (several GPUs): one launch forms both gradient GEMMs of every
-    # pair (12 n N D).  Stored-weight backward (one GPU): the sweep forms one gradient GEMM per pair (6 n N D; it
-    # EXECUTES 12: S once + that GEMM) and tc_bwd_rev_kernel the other one from the stored weights (6 n N D).
-    stored = rev_avg is not None
-    bwd_flops = (6.0 if stored else 12.0) * n_local * n_global * DIM
-    fwd_flops = 6.0 * n_local * n_global * DIM
+    bwd_mode = _lib.last_bwd_mode()
+    # Algorithmic work: one forward GEMM + two gradient GEMMs per unordered pair, 3 pairs = 18 n N D per
+    # step; recomputing S in the backward is NOT counted.  Which kernel forms the gradient GEMMs depends on the mode:
+    #   0 (several GPUs) tc_bwd_duo_kernel recomputes S per ordered pair and forms both GEMMs of a pair: 12 n N D.
+    #   1 tc_bwd_duo_kernel per unordered pair: one GEMM per pair (6 n N D), tc_bwd_rev_kernel the other (6 n N D).
+    #   2 (one GPU, default) tc_sim_kernel<EPI_WEIGHTS> writes the weight matrix (0 algorithmic, executes 6 n N D),
+    #     tc_bwd_rev_kernel forms both GEMMs of every pair from it: 12 n N D -- the dominant kernel.
+    unit = float(n_local) * n_global * DIM
+    fwd_flops = 6.0 * unit
     roofline = None
     if bwd_avg:
-        ach = bwd_flops / (bwd_avg * 1e-3) / 1e12
-        traffic = None
-        if world == 1 and n_global == 32768:
-            # dram__bytes_read.sum + dram__bytes_write.sum of one launch from the `ncu --set full` captures summarised
-            # in profiles/ (r1_bwd_duo_store.txt: 1.57 GB read + 6.99 GB of stored weights; r1_bwd_duo.txt otherwise)
-            traffic = 8.566e9 if stored else 2.164e9
+        if bwd_mode == 2 and rev_avg:
+            kernel, k_ms, k_flops, k_exec = "tc_bwd_rev_kernel", rev_avg, 12.0 * unit, 12.0 * unit
+            # r1_bwd_gemms.txt: dram__bytes_read.sum + dram__bytes_write.sum of one launch
+            traffic = TRAFFIC_GEMMS if (world == 1 and n_global == 32768) else None
+        elif bwd_mode == 1 and rev_avg:
+            kernel, k_ms, k_flops, k_exec = "tc_bwd_duo_kernel", bwd_avg, 6.0 * unit, 12.0 * unit
+            traffic = 8.566e9 if (world == 1 and n_global == 32768) else None
+        else:
+            kernel, k_ms, k_flops, k_exec = "tc_bwd_duo_kernel", bwd_avg, 12.0 * unit, 24.0 * unit
+            traffic = 2.164e9 if (world == 1 and n_global == 32768) else None  # profiles/r1_bwd_duo.txt
+        ach = k_flops / (k_ms * 1e-3) / 1e12
+        bwd_total_ms = bwd_avg + (rev_avg or 0.0)
         roofline = {"bound": "tensor", "achieved": ach, "peak": peaks["tflops_sustained"],
                     "unit": "TFLOP/s", "frac": ach / peaks["tflops_sustained"],
-                    "traffic": traffic, "traffic_unit": "B",
-                    "kernel": "tc_bwd_duo_kernel",
+                    "traffic": traffic, "traffic_unit": "B", "kernel": kernel,
                     "peak_source": peaks["source"] + " bf16_tflops_sustained (kernel timed inside a long step)",
-                    "kernel_ms": bwd_avg, "fwd_kernel_ms": fwd_avg,
+                    "kernel_ms": k_ms, "algorithmic_flops_per_launch": k_flops,
+                    "executed_tflops": k_exec / (k_ms * 1e-3) / 1e12,
+                    "backward_mode": bwd_mode,
+                    "backward_kernels_ms": {"sweep_or_weights": bwd_avg, "gemms_from_stored_weights": rev_avg},
+                    "bwd_achieved": 12.0 * unit / (bwd_total_ms * 1e-3) / 1e12,
+                    "fwd_kernel_ms": fwd_avg,
                     "fwd_achieved": (fwd_flops / (fwd_avg * 1e-3) / 1e12) if fwd_avg else None,
-                    "step_achieved": 18.0 * n_local * n_global * DIM / (ms_per_step * 1e-3) / 1e12,
-                    "step_frac": 18.0 * n_local * n_global * DIM / (ms_per_step * 1e-3) / 1e12 / peaks["tflops_sustained"],
-                    "algorithmic_flops_per_launch": bwd_flops,
-                    "executed_tflops": 12.0 * n_local * n_global * DIM / (bwd_avg * 1e-3) / 1e12 * (1.0 if stored else 2.0),
-                    "backward": "stored weights: sweep per unordered pair + tc_bwd_rev_kernel" if stored
-                                else "recomputing sweep per ordered pair"}
-        if stored:
-            roofline["rev_kernel_ms"] = rev_avg
-            roofline["rev_achieved"] = 6.0 * n_local * n_global * DIM / (rev_avg * 1e-3) / 1e12
-            roofline["bwd_achieved"] = 12.0 * n_local * n_global * DIM / ((bwd_avg + rev_avg) * 1e-3) / 1e12
+                    "step_achieved": 18.0 * unit / (ms_per_step * 1e-3) / 1e12,
+                    "step_frac": 18.0 * unit / (ms_per_step * 1e-3) / 1e12 / peaks["tflops_sustained"]}
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

@@ -23,7 +23,7 @@ EXPORTS = [
     "bsc_gather_layout", "bsc_gather_push",
     "bsc_infonce_stats_len", "bsc_infonce_workspace_bytes", "bsc_infonce_fwd", "bsc_infonce_loss",
     "bsc_infonce_bwd", "bsc_bank_search_workspace_bytes", "bsc_bank_search", "bsc_bank_screen_parts", "bsc_bank_screen", "bsc_bank_rescore", "bsc_topk_merge", "bsc_taxonomy_eval",
-    "bsc_set_timing", "bsc_last_kernel_ms", "bsc_launch_count",
+    "bsc_set_timing", "bsc_last_kernel_ms", "bsc_launch_count", "bsc_last_bwd_mode",
 ]
 
 
@@ -85,6 +85,8 @@ def lib():
     L.bsc_set_timing.argtypes = [c_int]
     L.bsc_last_kernel_ms.argtypes = [c_int]
     L.bsc_last_kernel_ms.restype = c_float
+    L.bsc_last_bwd_mode.argtypes = []
+    L.bsc_last_bwd_mode.restype = c_int
     L.bsc_launch_count.argtypes = [c_int]
     L.bsc_launch_count.restype = c_int64
     for name in EXPORTS:
@@ -138,6 +140,10 @@ def launch_count(reset: bool = False) -> int:
 
 def set_timing(on: bool) -> None:
     lib().bsc_set_timing(1 if on else 0)
+
+
+def last_bwd_mode() -> int:
+    return int(lib().bsc_last_bwd_mode())
 
 
 def last_kernel_ms(which: int) -> float:

@@ -45,6 +45,7 @@ void tc_fwd_tiling(int64_t n_local, int64_t n_global, int n_pairs, int* n_iblk, 
 // an autograd function on its own thread, and bench.py reads both from the main thread.
 static thread_local char g_err[512] = "";
 static std::atomic<int64_t> g_launches{0};
+static std::atomic<int> g_bwd_mode{-1};
 static std::atomic<int> g_timing{0};
 static std::mutex g_ev_mutex;
 static cudaEvent_t g_ev[4][2] = {{nullptr, nullptr}, {nullptr, nullptr}, {nullptr, nullptr}, {nullptr, nullptr}};
@@ -166,18 +167,18 @@ InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p) {
     return o;
   };
   L.uv = take((size_t)6 * N * sizeof(float));
-  L.gs = take(16 * sizeof(float));  // [6][2] {gs, 1/gs} per ordered pair, then [3] max inverse norms
+  L.gs = take(32 * sizeof(float));  // [6][2] {gs, 1/gs} per ordered pair, [12..14] max inverse norms, [16..17] {gs, 1/gs} of unscaled weights
   // x2: the tensor-core forward sweep keeps one partial per epilogue warp group (tc_sim.cu NG)
   L.rowpart = take((size_t)3 * 2 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
   L.rowpos = take((size_t)3 * 2 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
   L.jrange = take((size_t)(L.n_jtile > 0 ? L.n_jtile : 1) * 2 * sizeof(int));
   L.colpart = take((size_t)3 * (L.n_iblk > 0 ? L.n_iblk : 1) * L.n_global_pad * sizeof(float));
-  L.bwd_gstore = tc_bwd_gstore(p) ? 1 : 0;
-  L.bwd_jsplit = tc_bwd_duo_jsplit(p);
+  L.bwd_gstore = tc_bwd_gstore(p);
+  L.bwd_jsplit = L.bwd_gstore == 2 ? 1 : tc_bwd_duo_jsplit(p);
   L.dxraw = take((size_t)3 * 2 * L.bwd_jsplit * (n > 0 ? n : 1) * D * sizeof(float));
   if (L.bwd_gstore) {
     L.xunit = take((size_t)3 * N * D * 2);
-    L.gimg = take(tc_bwd_gimg_bytes(p));
+    L.gimg = take(tc_bwd_gimg_bytes(p, L.bwd_gstore));
   } else {
     L.xunit = L.gimg = off;
   }
@@ -241,6 +242,8 @@ float bsc_last_kernel_ms(int which) {
   if (cudaEventElapsedTime(&ms, g_ev[which][0], g_ev[which][1]) != cudaSuccess) return -1.0f;
   return ms;
 }
+
+int bsc_last_bwd_mode(void) { return g_bwd_mode.load(); }
 
 int64_t bsc_launch_count(int reset) {
   return reset ? g_launches.exchange(0) : g_launches.load();
@@ -370,6 +373,7 @@ int bsc_infonce_bwd(const bsc_infonce_desc* p, const float* stats, const void* c
   rc = uv_launch(stats, p->r, N, p->rmax, p->inv, p->mode == BSC_MODE_TC16, (float*)(ws + L.uv), (float*)(ws + L.gs),
                  (float*)(ws + L.gs) + 12, st);
   if (rc) return rc;
+  if (p->mode == BSC_MODE_TC16) g_bwd_mode.store(L.bwd_gstore);
   rc = (p->mode == BSC_MODE_F32) ? simt_bwd_raw(p, L, ws, st) : tc_bwd_raw(p, L, ws, st);
   if (rc) return rc;
   CombineArgs ca{};

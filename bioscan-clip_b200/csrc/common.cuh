@@ -65,7 +65,7 @@ struct InfoNceWs {
   // tiling facts shared by host and kernels
   int n_iblk, n_jtile, n_jchunk, jtiles_per_chunk;
   int bwd_jsplit;   // dxraw parts per (modality, slot): > 1 only for the CTA-pair backward sweep (tc_bwd2.cu)
-  int bwd_gstore;   // 1: the sweep runs once per UNORDERED pair and stores its weights; tc_bwd3.cu forms the other side
+  int bwd_gstore;   // tc_bwd_gstore(): 0 recompute, 1 stored spans of the pair sweep, 2 weight matrix + GEMMs
   int64_t n_local_pad, n_global_pad, g_rows;
 };
 
@@ -95,8 +95,13 @@ int tc_bwd_raw(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStre
 int tc_bwd_duo(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st);
 int tc_bwd_duo_jsplit(const bsc_infonce_desc* p);
 // stored-weight backward (all rows local): is it used for this problem, and how many bytes of weight spans it keeps
-bool tc_bwd_gstore(const bsc_infonce_desc* p);
-size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* p);
+// 0 = recomputing sweep, 1 = pair sweep per unordered pair + stored spans, 2 = weight matrix + two GEMMs per pair
+int tc_bwd_gstore(const bsc_infonce_desc* p);
+size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* p, int mode);
+void tc_bwd_matrix_dims(const bsc_infonce_desc* d, int* n_iblk_pad, int* n_j64);
+int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStream_t st);
+int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_iblk_pad,
+                 int n_j64, cudaStream_t st);
 int tc_bwd_rev(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_pairs,
                const int* pairs_x, const int* pairs_y, int n_jb, int n_i64, cudaStream_t st);
 int rows_unit_f16_launch(const void* x16, const float* inv, int64_t n, int d, void* out, cudaStream_t st);

@@ -602,6 +602,10 @@ __global__ void __launch_bounds__(256) uv_kernel(const float* __restrict__ stats
         gsbuf[2 * pair_id(x, y)] = gs;
         gsbuf[2 * pair_id(x, y) + 1] = 1.0f / gs;
       }
+    // weights kept without an operand scale (weight-matrix backward): |gs (e (u + v) - 2 T)| <= 4 gs rmax <= 32768
+    const float gw = use_gs ? exp2f(floorf(log2f(8192.0f / fmaxf(rmax[0], 1.0f)))) : 1.0f;
+    gsbuf[16] = gw;
+    gsbuf[17] = 1.0f / gw;
   }
   if (i >= n) return;
   const float ri = r[i];

@@ -488,22 +488,32 @@ static bool duo_covers(const bsc_infonce_desc* d) {
 // Stored-weight backward: with all rows on this GPU the weight matrix of an unordered pair serves both directions, so
 // the sweep runs once per unordered pair, copies its fp16 weight spans to HBM (2 N^2 bytes per pair) and a plain GEMM
 // (tc_bwd3.cu) forms the other side.  BSC_BWD_GSTORE=0 turns it off; spans above BSC_BWD_GSTORE_GB (default 48) too.
-size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* d) {
+size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* d, int mode) {
   int m = 0;
   for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
+  const size_t pairs = (size_t)(m * (m - 1) / 2);
+  if (mode == 2) {
+    int n_iblk_pad, n_j64;
+    tc_bwd_matrix_dims(d, &n_iblk_pad, &n_j64);
+    return pairs * (size_t)n_iblk_pad * (size_t)n_j64 * GSPAN;
+  }
   const size_t n_iblk = (size_t)((d->n_local + BM - 1) / BM);
   const size_t n_steps = (size_t)(((d->n_global + BN - 1) / BN + 1) / 2);
-  return (size_t)(m * (m - 1) / 2) * (2 * n_steps) * (2 * n_iblk) * GSPAN;
+  return pairs * (2 * n_steps) * (2 * n_iblk) * GSPAN;
 }
 
-bool tc_bwd_gstore(const bsc_infonce_desc* d) {
-  if (!duo_covers(d)) return false;
-  if (d->n_local != d->n_global || d->row0 != 0) return false;
+// BSC_BWD_GSTORE = 0 | 1 | 2 picks the mode (default 2 where it applies); weight storage above BSC_BWD_GSTORE_GB
+// (default 48) falls back to the recomputing sweep.
+int tc_bwd_gstore(const bsc_infonce_desc* d) {
+  if (!duo_covers(d)) return 0;
+  if (d->n_local != d->n_global || d->row0 != 0) return 0;
+  int mode = 2;
   const char* e = getenv("BSC_BWD_GSTORE");
-  if (e && e[0] == '0') return false;
+  if (e && e[0] >= '0' && e[0] <= '2') mode = e[0] - '0';
+  if (mode == 0) return 0;
   const char* g = getenv("BSC_BWD_GSTORE_GB");
   const double cap = (g ? atof(g) : 48.0) * 1073741824.0;
-  return (double)tc_bwd_gimg_bytes(d) <= cap;
+  return (double)tc_bwd_gimg_bytes(d, mode) <= cap ? mode : 0;
 }
 
 // In how many parts to cut every (ordered pair, row block) column sweep: the clusters take whole items, so with few
@@ -517,7 +527,7 @@ int tc_bwd_duo_jsplit(const bsc_infonce_desc* d) {
   }();
   int m = 0;
   for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
-  const int64_t items0 = (int64_t)m * (m - 1) / (tc_bwd_gstore(d) ? 2 : 1) * ((d->n_local + BM - 1) / BM);
+  const int64_t items0 = (int64_t)m * (m - 1) / (tc_bwd_gstore(d) == 1 ? 2 : 1) * ((d->n_local + BM - 1) / BM);
   const int64_t steps = ((d->n_global + BN - 1) / BN + 1) / 2;
   const int clusters = sm_count2() / 2;
   if (items0 <= 0 || steps <= 0) return 1;
@@ -542,6 +552,7 @@ int tc_bwd_duo_jsplit(const bsc_infonce_desc* d) {
 // Returns BSC_OK when the paired kernel ran, 1 when this shape is not covered (caller falls back), < 0 on error.
 int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStream_t st) {
   if (!duo_covers(d)) return 1;
+  if (L.bwd_gstore == 2) return tc_bwd_matrix(d, L, ws, st);
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
   DuoParams p{};
   int first = -1;
@@ -559,7 +570,7 @@ int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
       p.tmap128[a] = p.tmap128[first];
       p.tmap64[a] = p.tmap64[first];
     }
-  const bool gstore = L.bwd_gstore != 0;
+  const bool gstore = L.bwd_gstore == 1;
   int n = 0;
   for (int x = 0; x < 3; ++x) {
     if (!d->xh[x]) continue;

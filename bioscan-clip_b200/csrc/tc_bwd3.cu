@@ -33,11 +33,17 @@ constexpr int TMEM_COLS = 512;
 constexpr int BN = 256;  // d columns per item
 
 struct RevParams {
-  CUtensorMap tmap_g;     // gimg as [rows][64] fp16, box 64 x 128, no swizzle (the bytes are already swizzled)
-  CUtensorMap tmap_x[3];  // unit rows per modality, box 64 d x 64 rows, SWIZZLE_128B
-  int n_pairs;
-  int pair_x[3], pair_y[3], pair_slot[3];  // slot = index of x among y's partner modalities
-  int n_jb, n_i64, nchunk, kparts, num_items, d;
+  CUtensorMap tmap_g128;  // gimg as [rows][64] fp16, box 64 x 128, no swizzle (the bytes are already swizzled)
+  CUtensorMap tmap_g64;   // same, box 64 x 64: half an image (MN-major jobs)
+  CUtensorMap tmap_u[3];  // unit rows per modality, box 64 d x 64 rows, SWIZZLE_128B
+  // job = one gradient GEMM  out[M rows][d] = A[M][K] * unit_in[K][d];  image(pair, r, c) = (pair * img_r + r) * img_c + c
+  //   K-major job:  A block (128 rows mblk, 64 K kb)  = image(pair, mblk, kb)
+  //   MN-major job: A block (128 rows mblk, 64 K kb)  = rows 64 (kb & 1) .. + 63 of images (pair, kb >> 1, 2 mblk + {0, 1})
+  int n_jobs;
+  int job_pair[6], job_mn[6], job_out[6], job_in[6], job_slot[6], job_nk[6];
+  int job_fnum[6], job_fden[6], job_finv[6];  // epilogue row factor gsbuf[fnum] * gsbuf[fden] (/ inv_out[row] if finv)
+  int img_r, img_c;
+  int n_mb, nchunk, kparts, num_items, d;
   int64_t n;
   const float* inv[3];
   const float* gsbuf;
@@ -55,16 +61,17 @@ struct __align__(8) RevTail {
 
 constexpr size_t REV_SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + sizeof(RevTail);
 
-__device__ __forceinline__ void rev_item(const RevParams& p, int item, int& pair, int& jb, int& part, int& c, int& kb_lo,
+__device__ __forceinline__ void rev_item(const RevParams& p, int item, int& job, int& mb, int& part, int& c, int& kb_lo,
                                          int& kb_hi) {
-  c = item % p.nchunk;  // the d chunks of one (j block, K part) run on neighbouring clusters: they share A through L2
+  c = item % p.nchunk;  // the d chunks of one (row block, K part) run on neighbouring clusters: they share A through L2
   int rest = item / p.nchunk;
   part = rest % p.kparts;
   rest /= p.kparts;
-  jb = rest % p.n_jb;
-  pair = rest / p.n_jb;
-  kb_lo = (int)((int64_t)part * p.n_i64 / p.kparts);
-  kb_hi = (int)((int64_t)(part + 1) * p.n_i64 / p.kparts);
+  mb = rest % p.n_mb;
+  job = rest / p.n_mb;
+  const int nk = p.job_nk[job];
+  kb_lo = (int)((int64_t)part * nk / p.kparts);
+  kb_hi = (int)((int64_t)(part + 1) * nk / p.kparts);
 }
 
 __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constant__ RevParams p) {
@@ -90,8 +97,9 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
     ptx::fence_barrier_init();
   }
   if (warp == 0 && lane == 0) {
-    ptx::prefetch_tmap(&p.tmap_g);
-    for (int a = 0; a < 3; ++a) ptx::prefetch_tmap(&p.tmap_x[a]);
+    ptx::prefetch_tmap(&p.tmap_g128);
+    ptx::prefetch_tmap(&p.tmap_g64);
+    for (int a = 0; a < 3; ++a) ptx::prefetch_tmap(&p.tmap_u[a]);
   }
   if (warp == 2) {
     ptx::tmem_alloc_2cta(ptx::smem_u32(&tail->tmem_base), TMEM_COLS);
@@ -105,14 +113,16 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
 
   if (warp == 0) {
     if (ptx::elect_one()) {
-      const uint64_t pol_stream = ptx::l2_policy_evict_first();  // spans are read nchunk times back to back, then never
+      const uint64_t pol_stream = ptx::l2_policy_evict_first();  // images are read nchunk times back to back, then never
       int stage = 0;
       uint32_t phase = 0;
       for (int item = item0; item < p.num_items; item += item_step) {
-        int pair, jb, part, c, kb_lo, kb_hi;
-        rev_item(p, item, pair, jb, part, c, kb_lo, kb_hi);
-        const CUtensorMap* mx = &p.tmap_x[p.pair_x[pair]];
-        const int64_t span0 = ((int64_t)pair * (2 * p.n_jb) + (2 * jb + (int)crank)) * p.n_i64;
+        int job, mb, part, c, kb_lo, kb_hi;
+        rev_item(p, item, job, mb, part, c, kb_lo, kb_hi);
+        const CUtensorMap* mu = &p.tmap_u[p.job_in[job]];
+        const int mblk = 2 * mb + (int)crank;
+        const int64_t pair0 = (int64_t)p.job_pair[job] * p.img_r;
+        const bool mn = p.job_mn[job] != 0;
         const int d0 = BN * c + 128 * (int)crank;
         for (int kb = kb_lo; kb < kb_hi; ++kb) {
           ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 100 + stage);
@@ -120,9 +130,17 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
           const uint32_t full_l = ptx::mapa(full, 0);
           const uint32_t sa = ring + stage * STAGE_BYTES;
           if (crank == 0) ptx::mbar_arrive_expect_tx(full, 2 * STAGE_BYTES);
-          ptx::tma_load_2d_2cta_hint(sa, &p.tmap_g, full_l, 0, (int32_t)((span0 + kb) * 128), pol_stream);
-          ptx::tma_load_2d_2cta(sa + A_BYTES, mx, full_l, d0, kb * BK);
-          ptx::tma_load_2d_2cta(sa + A_BYTES + B_BOX, mx, full_l, d0 + 64, kb * BK);
+          if (!mn) {
+            const int64_t img = (pair0 + mblk) * p.img_c + kb;
+            ptx::tma_load_2d_2cta_hint(sa, &p.tmap_g128, full_l, 0, (int32_t)(img * 128), pol_stream);
+          } else {
+            const int64_t img = (pair0 + (kb >> 1)) * p.img_c + 2 * mblk;
+            const int32_t r0 = (int32_t)(img * 128) + 64 * (kb & 1);
+            ptx::tma_load_2d_2cta_hint(sa, &p.tmap_g64, full_l, 0, r0, pol_stream);
+            ptx::tma_load_2d_2cta_hint(sa + A_BYTES / 2, &p.tmap_g64, full_l, 0, r0 + 128, pol_stream);
+          }
+          ptx::tma_load_2d_2cta(sa + A_BYTES, mu, full_l, d0, kb * BK);
+          ptx::tma_load_2d_2cta(sa + A_BYTES + B_BOX, mu, full_l, d0 + 64, kb * BK);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1u;
@@ -132,15 +150,21 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
     }
   } else if (warp == 1) {
     if (crank == 0 && ptx::elect_one()) {
-      constexpr uint32_t idesc = umma_idesc(256, BN, 0, 0, 0, 1);  // A K-major, B MN-major
-      const uint64_t desc_a = ptx::umma_desc_sw128(0, 16, 1024);
+      constexpr uint32_t idesc_k = umma_idesc(256, BN, 0, 0, 0, 1);   // A K-major, B MN-major
+      constexpr uint32_t idesc_mn = umma_idesc(256, BN, 0, 0, 1, 1);  // A MN-major, B MN-major
+      const uint64_t desc_ak = ptx::umma_desc_sw128(0, 16, 1024);
+      const uint64_t desc_amn = ptx::umma_desc_sw128(0, A_BYTES / 2, 1024);  // two 64-wide M chunks 8 KB apart
       const uint64_t desc_b = ptx::umma_desc_sw128(0, B_BOX, 1024);
       int stage = 0;
       uint32_t phase = 0;
       uint32_t count = 0;
       for (int item = item0; item < p.num_items; item += item_step, ++count) {
-        int pair, jb, part, c, kb_lo, kb_hi;
-        rev_item(p, item, pair, jb, part, c, kb_lo, kb_hi);
+        int job, mb, part, c, kb_lo, kb_hi;
+        rev_item(p, item, job, mb, part, c, kb_lo, kb_hi);
+        const bool mn = p.job_mn[job] != 0;
+        const uint32_t idesc = mn ? idesc_mn : idesc_k;
+        const uint64_t desc_a = mn ? desc_amn : desc_ak;
+        const uint64_t a_step = mn ? 128u : 2u;  // 16 K rows of 128 bytes / 32 bytes along a K-major row
         const uint32_t buf = count & 1u;
         ptx::mbar_wait_cluster(ptx::smem_u32(&tail->tmem_empty[buf]), ((count >> 1) & 1u) ^ 1u, 200 + buf);
         ptx::tc_fence_after();
@@ -153,7 +177,8 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
           const uint64_t db = desc_b + ptx::desc_addr(sa + A_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)
-            ptx::umma_f16_2cta(d_tmem, da + 2 * k, db + (uint64_t)(k * 128), idesc, (kb != kb_lo || k != 0) ? 1u : 0u);
+            ptx::umma_f16_2cta(d_tmem, da + a_step * k, db + (uint64_t)(k * 128), idesc,
+                               (kb != kb_lo || k != 0) ? 1u : 0u);
           ptx::umma_commit_2cta(ptx::smem_u32(&tail->empty[stage]), 3);
           if (kb == kb_hi - 1) ptx::umma_commit_2cta(ptx::smem_u32(&tail->tmem_full[buf]), 3);
           if (++stage == STAGES) {
@@ -169,17 +194,20 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
     const uint32_t empty_l0 = ptx::mapa(ptx::smem_u32(&tail->tmem_empty[0]), 0);
     uint32_t count = 0;
     for (int item = item0; item < p.num_items; item += item_step, ++count) {
-      int pair, jb, part, c, kb_lo, kb_hi;
-      rev_item(p, item, pair, jb, part, c, kb_lo, kb_hi);
-      const int x = p.pair_x[pair], y = p.pair_y[pair];
+      int job, mb, part, c, kb_lo, kb_hi;
+      rev_item(p, item, job, mb, part, c, kb_lo, kb_hi);
+      const int mo = p.job_out[job];
       const uint32_t buf = count & 1u;
-      const int64_t j = ((int64_t)(2 * jb + (int)crank)) * 128 + q * 32 + lane;
+      const int64_t row = ((int64_t)(2 * mb + (int)crank)) * 128 + q * 32 + lane;
       float f = 0.f;
-      if (j < p.n) {
-        const float ij = p.inv[y][j];
-        if (ij > 0.f) f = p.gsbuf[2 * pair_id(y, x)] * p.gsbuf[2 * pair_id(x, y) + 1] / ij;
+      if (row < p.n) {
+        f = p.gsbuf[p.job_fnum[job]] * p.gsbuf[p.job_fden[job]];
+        if (p.job_finv[job]) {
+          const float iv = p.inv[mo][row];
+          f = iv > 0.f ? f / iv : 0.f;
+        }
       }
-      float* out = p.dxraw + (((int64_t)(y * 2 + p.pair_slot[pair]) * p.kparts + part) * p.n + j) * p.d + BN * c;
+      float* out = p.dxraw + (((int64_t)(mo * 2 + p.job_slot[job]) * p.kparts + part) * p.n + row) * p.d + BN * c;
       if (kb_hi > kb_lo) {
         ptx::mbar_wait(ptx::smem_u32(&tail->tmem_full[buf]), (count >> 1) & 1u, 400 + buf);
         ptx::tc_fence_after();
@@ -195,7 +223,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
 #pragma unroll
           for (int t = 0; t < 32; ++t) raw[t] = 0u;
         }
-        if (j < p.n) {
+        if (row < p.n) {
           float4* o4 = reinterpret_cast<float4*>(out + cc * 32);
 #pragma unroll
           for (int t = 0; t < 8; ++t)
@@ -231,51 +259,8 @@ int sm_count3() {
 
 }  // namespace
 
-// dYhat of every unordered pair from the stored weight spans.  `pairs_x/y` list the unordered pairs in the order the
-// sweep stored them; xunit[a] = fp16 unit rows of modality a (only the x side of a pair is read).
-int tc_bwd_rev(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_pairs,
-               const int* pairs_x, const int* pairs_y, int n_jb, int n_i64, cudaStream_t st) {
-  RevParams p{};
-  const int64_t N = d->n_global;
-  int rc = make_tmap_raw128(&p.tmap_g, ws + L.gimg, (int64_t)n_pairs * 2 * n_jb * n_i64 * 128, 128);
-  if (rc) return rc;
-  int first = -1;
-  for (int a = 0; a < 3; ++a)
-    if (xunit[a]) {
-      rc = make_tmap_2d(&p.tmap_x[a], xunit[a], BSC_F16, N, d->d, 64);
-      if (rc) return rc;
-      if (first < 0) first = a;
-    }
-  BSC_REQUIRE(first >= 0, BSC_EINVAL, "tc_bwd_rev: no unit rows");
-  for (int a = 0; a < 3; ++a) {
-    if (!xunit[a]) p.tmap_x[a] = p.tmap_x[first];
-    p.inv[a] = d->inv[a];
-  }
-  p.n_pairs = n_pairs;
-  for (int q = 0; q < n_pairs; ++q) {
-    const int x = pairs_x[q], y = pairs_y[q];
-    p.pair_x[q] = x;
-    p.pair_y[q] = y;
-    int slot = 0;  // index of x among the present modalities other than y, in ascending order
-    for (int z = 0; z < x; ++z)
-      if (z != y && d->xh[z]) ++slot;
-    p.pair_slot[q] = slot;
-  }
-  p.n_jb = n_jb;
-  p.n_i64 = n_i64;
-  p.nchunk = d->d / BN;
-  p.kparts = L.bwd_jsplit > 0 ? L.bwd_jsplit : 1;
-  if (p.kparts > n_i64) p.kparts = n_i64;
-  p.d = d->d;
-  p.n = N;
-  p.gsbuf = (const float*)(ws + L.gs);
-  p.dxraw = (float*)(ws + L.dxraw);
-  p.num_items = n_pairs * n_jb * p.kparts * p.nchunk;
-  // parts of the K split that this kernel does not produce (kparts clipped) must still read as zero in combine
-  BSC_REQUIRE(p.kparts == (L.bwd_jsplit > 0 ? L.bwd_jsplit : 1), BSC_EUNSUPPORTED,
-              "tc_bwd_rev: column split %d exceeds the %d row spans", L.bwd_jsplit, n_i64);
+static int rev_launch(RevParams& p, cudaStream_t st) {
   if (p.num_items == 0) return BSC_OK;
-
   static bool attr_done = false;
   if (!attr_done) {
     BSC_CUDA(cudaFuncSetAttribute(tc_bwd_rev_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)REV_SMEM_BYTES));
@@ -300,6 +285,112 @@ int tc_bwd_rev(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const vo
   timing_end(3, st);
   BSC_LAUNCH_CHECK("tc_bwd_rev_kernel");
   return BSC_OK;
+}
+
+static int rev_common(RevParams& p, const bsc_infonce_desc* d, const InfoNceWs& L, char* ws,
+                      const void* const xunit[3], int64_t img_rows) {
+  const int64_t N = d->n_global;
+  int rc = make_tmap_raw128(&p.tmap_g128, ws + L.gimg, img_rows, 128);
+  if (rc) return rc;
+  rc = make_tmap_raw128(&p.tmap_g64, ws + L.gimg, img_rows, 64);
+  if (rc) return rc;
+  int first = -1;
+  for (int a = 0; a < 3; ++a)
+    if (xunit[a]) {
+      rc = make_tmap_2d(&p.tmap_u[a], xunit[a], BSC_F16, N, d->d, 64);
+      if (rc) return rc;
+      if (first < 0) first = a;
+    }
+  BSC_REQUIRE(first >= 0, BSC_EINVAL, "tc_bwd_rev: no unit rows");
+  for (int a = 0; a < 3; ++a) {
+    if (!xunit[a]) p.tmap_u[a] = p.tmap_u[first];
+    p.inv[a] = d->inv[a];
+  }
+  p.nchunk = d->d / BN;
+  p.kparts = L.bwd_jsplit > 0 ? L.bwd_jsplit : 1;
+  p.d = d->d;
+  p.n = N;
+  p.n_mb = (int)((N + 255) / 256);
+  p.gsbuf = (const float*)(ws + L.gs);
+  p.dxraw = (float*)(ws + L.dxraw);
+  return BSC_OK;
+}
+
+// slot of partner modality `other` among the present modalities other than `m`, ascending
+static int slot_of(const bsc_infonce_desc* d, int m, int other) {
+  int slot = 0;
+  for (int z = 0; z < other; ++z)
+    if (z != m && d->xh[z]) ++slot;
+  return slot;
+}
+
+// Stored-span mode (L.bwd_gstore == 1): dYhat of every unordered pair from the spans the pair sweep stored,
+// gimg[(pair * 2 n_steps + j tile) * n_i64 + i64] = [128 j][64 i].  `pairs_x/y` list the pairs in the sweep's order;
+// xunit[a] = fp16 unit rows of modality a (only the x side of a pair is read).
+int tc_bwd_rev(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_pairs,
+               const int* pairs_x, const int* pairs_y, int n_jb, int n_i64, cudaStream_t st) {
+  RevParams p{};
+  int rc = rev_common(p, d, L, ws, xunit, (int64_t)n_pairs * 2 * n_jb * n_i64 * 128);
+  if (rc) return rc;
+  p.img_r = 2 * n_jb;
+  p.img_c = n_i64;
+  p.n_jobs = n_pairs;
+  for (int q = 0; q < n_pairs; ++q) {
+    const int x = pairs_x[q], y = pairs_y[q];
+    p.job_pair[q] = q;
+    p.job_mn[q] = 0;
+    p.job_out[q] = y;
+    p.job_in[q] = x;
+    p.job_slot[q] = slot_of(d, y, x);
+    p.job_nk[q] = n_i64;
+    // a stored weight carries gs(x,y) / |y_j|; combine expects gs(y,x) * sum
+    p.job_fnum[q] = 2 * pair_id(y, x);
+    p.job_fden[q] = 2 * pair_id(x, y) + 1;
+    p.job_finv[q] = 1;
+  }
+  BSC_REQUIRE(p.kparts <= n_i64, BSC_EUNSUPPORTED, "tc_bwd_rev: column split %d exceeds the %d row spans", p.kparts,
+              n_i64);
+  p.num_items = p.n_jobs * p.n_mb * p.kparts * p.nchunk;
+  return rev_launch(p, st);
+}
+
+// Weight-matrix mode (L.bwd_gstore == 2): both gradient GEMMs of every unordered pair (x, y) from the images
+// gimg[(pair * n_iblk_pad + iblk) * n_j64 + j64] = G[128 i][64 j] that tc_bwd_weights wrote:
+//   dXhat = G * Yunit   (A K-major: image rows are i, K runs over j),   dYhat = G^T * Xunit   (A MN-major, K over i).
+int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_iblk_pad,
+                 int n_j64, cudaStream_t st) {
+  RevParams p{};
+  int np = 0;
+  for (int x = 0; x < 3; ++x)
+    for (int y = x + 1; y < 3; ++y)
+      if (d->xh[x] && d->xh[y]) ++np;
+  int rc = rev_common(p, d, L, ws, xunit, (int64_t)np * n_iblk_pad * n_j64 * 128);
+  if (rc) return rc;
+  p.img_r = n_iblk_pad;
+  p.img_c = n_j64;
+  const int nk64 = (int)((d->n_global + 63) / 64);
+  int q = 0, job = 0;
+  for (int x = 0; x < 3; ++x)
+    for (int y = x + 1; y < 3; ++y) {
+      if (!d->xh[x] || !d->xh[y]) continue;
+      for (int side = 0; side < 2; ++side, ++job) {
+        const int mo = side == 0 ? x : y, mi = side == 0 ? y : x;
+        p.job_pair[job] = q;
+        p.job_mn[job] = side;
+        p.job_out[job] = mo;
+        p.job_in[job] = mi;
+        p.job_slot[job] = slot_of(d, mo, mi);
+        p.job_nk[job] = nk64;  // K blocks of 64 columns j (side 0) / 64 rows i (side 1): both modalities have N rows
+        p.job_fnum[job] = 2 * pair_id(mo, mi);
+        p.job_fden[job] = 17;  // 1 / gs of the stored weights
+        p.job_finv[job] = 0;
+      }
+      ++q;
+    }
+  p.n_jobs = job;
+  BSC_REQUIRE(p.kparts == 1, BSC_EUNSUPPORTED, "tc_bwd_gemms: the weight-matrix backward does not split K");
+  p.num_items = p.n_jobs * p.n_mb * p.kparts * p.nchunk;
+  return rev_launch(p, st);
 }
 
 }  // namespace bsc

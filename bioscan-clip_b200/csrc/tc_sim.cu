@@ -33,7 +33,7 @@ constexpr int KTOP = 8;  // register-resident top-k capacity of the TOPK epilogu
 constexpr int NG = 2;    // epilogue warp groups: each takes BN / NG columns of every tile (2 warps per SM sub-partition)
 constexpr int NTHREADS = 128 + NG * 128;
 
-enum { EPI_STATS = 0, EPI_TOPK = 1 };
+enum { EPI_STATS = 0, EPI_TOPK = 1, EPI_WEIGHTS = 2 };
 
 struct SimParams {
   CUtensorMap tmap[3];  // per operand matrix: [rows][d], box {64, 128}
@@ -61,6 +61,13 @@ struct SimParams {
   int64_t base_id;
   float* cand_s;     // [jchunk][a_rows][k]
   int64_t* cand_i;
+  // EPI_WEIGHTS: the fp16 weight matrix of every unordered pair, G_ij = gs (e_ij (u_i + v_j) - 2 T_ij), written as
+  // 128B-swizzled [128 i][64 j] images (K-major A operand over j, MN-major A operand over i: tc_bwd3.cu)
+  const float* uv;     // [6][N]
+  const float* gsbuf;  // [16] = gs of the stored weights
+  uint8_t* gimg;       // [pair][n_iblk_pad][n_j64][16 KB]
+  int n_iblk_pad, n_j64;
+  int dbg;  // experiment knob BSC_DBG_W: 1 = no stores, 2 = no label compare (results invalid)
 };
 
 struct __align__(8) SimSmemTail {
@@ -72,6 +79,7 @@ struct __align__(8) SimSmemTail {
   uint32_t pad;
   float cs[2][4][BN];  // per-warp column partial sums, double-buffered by tile parity
   float invb[2][BN];   // k1 * inverse norms of the tile's columns, double-buffered by tile parity
+  __align__(16) uint8_t wst[8][2048];  // EPI_WEIGHTS: per-warp staging of 32 half rows (64 bytes each)
 };
 
 constexpr size_t SIM_SMEM_BYTES = 1024 /*align slack*/ + (size_t)STAGES * STAGE_BYTES + sizeof(SimSmemTail);
@@ -274,6 +282,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
           wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
         }
       }
+      float ugs_i = 0.f, gsw = 0.f;
+      const float* vcol_g = nullptr;
+      if (EPI == EPI_WEIGHTS) {
+        gsw = p.gsbuf[16];
+        if (row_ok) {
+          inv_i = p.inv[p.pair_a[pair]][p.a_row0 + arow];
+          rep_i = p.rep[p.a_row0 + arow];
+          ugs_i = gsw * p.uv[(int64_t)pair_id(p.pair_a[pair], p.pair_b[pair]) * p.b_rows + p.a_row0 + arow];
+        }
+        invb_g = p.inv[p.pair_b[pair]];
+        vcol_g = p.uv + (int64_t)pair_id(p.pair_b[pair], p.pair_a[pair]) * p.b_rows;
+      }
       float ts[KTOP];
       int ti[KTOP];
       if (EPI == EPI_TOPK) {
@@ -293,6 +313,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
           for (int col = grp * GC + et; col < (grp + 1) * GC; col += 128) {
             const int64_t j = col0 + col;
             tail->invb[buf][col] = j < p.b_rows ? p.k1 * invb_g[j] : 0.f;
+          }
+          ptx::named_bar_sync(2 + 2 * grp, 128);
+        }
+        if (EPI == EPI_WEIGHTS) {
+          // column facts of the tile: k1 / |b_j|, gs * v_j, label class (the column-sum scratch is free in this mode)
+          float* vgb = &tail->cs[0][0][0] + buf * BN;
+          int* repb = reinterpret_cast<int*>(&tail->cs[1][0][0]) + buf * BN;
+          for (int col = grp * GC + et; col < (grp + 1) * GC; col += 128) {
+            const int64_t j = col0 + col;
+            const bool ok = j < p.b_rows;
+            tail->invb[buf][col] = ok ? p.k1 * invb_g[j] : 0.f;
+            vgb[col] = ok ? gsw * vcol_g[j] : 0.f;
+            repb[col] = ok ? p.rep[j] : -1;
           }
           ptx::named_bar_sync(2 + 2 * grp, 128);
         }
@@ -344,6 +377,50 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
             for (int t = 0; t < 32; ++t) s += e[t];
             rowsum += s;
             cs[c * 32 + lane] = warp_colsum32(e, lane);
+          } else if (EPI == EPI_WEIGHTS) {
+            const float* vgb = &tail->cs[0][0][0] + buf * BN + c * 32;
+            const int* repb = reinterpret_cast<const int*>(&tail->cs[1][0][0]) + buf * BN + c * 32;
+            const float m2g = -2.0f * gsw;
+            uint32_t pk[16];
+#pragma unroll
+            for (int t = 0; t < 32; t += 2) {
+              float g2[2];
+#pragma unroll
+              for (int z = 0; z < 2; ++z) {
+                const float ex = ptx::ex2(fmaf(__uint_as_float(raw[t + z]), inv_i * ivb[c * 32 + t + z], -p.k2));
+                const float tv = (p.dbg != 2 && repb[t + z] == rep_i) ? m2g : 0.f;
+                g2[z] = fmaf(ex, ugs_i + vgb[t + z], tv);
+              }
+              const __half2 hh = __floats2half2_rn(g2[0], g2[1]);
+              pk[t >> 1] = *reinterpret_cast<const uint32_t*>(&hh);
+            }
+            // Half a row (64 bytes) of image (iblk, 4 jt + c / 2) per lane.  Staged through 2 KB of shared memory per
+            // warp so that four lanes write the 64 contiguous bytes of one row: one 16-byte store per lane to 32
+            // different lines kept the load/store unit busy for two thirds of a tile's MMA time (5.5 ms, 4.0 without
+            // the stores).  Staging slot of (row r, chunk u) = u ^ ((r >> 1) & 3): conflict-free both ways.
+            uint8_t* stg = tail->wst[warp - 4];
+            {
+              const int r = lane;
+#pragma unroll
+              for (int u = 0; u < 4; ++u)
+                *reinterpret_cast<uint4*>(stg + r * 64 + ((u ^ ((r >> 1) & 3)) << 4)) =
+                    make_uint4(pk[4 * u], pk[4 * u + 1], pk[4 * u + 2], pk[4 * u + 3]);
+            }
+            __syncwarp();
+            const int64_t img = ((int64_t)pair * p.n_iblk_pad + iblk) * p.n_j64 + (int64_t)jt * 4 + (c >> 1);
+            uint8_t* img_base = p.gimg + img * 16384;
+            const int t4 = lane & 3;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const int r = 8 * k + (lane >> 2);        // row inside the warp's 32
+              const int rt = q * 32 + r;                // row inside the tile = row of the image
+              const int u = t4 ^ (r & 3);               // the chunk that belongs at 16-byte slot t4 of the row's half
+              const uint4 v = *reinterpret_cast<const uint4*>(stg + r * 64 + ((u ^ ((r >> 1) & 3)) << 4));
+              const int half_off = (((c & 1) * 4) ^ (rt & 4)) << 4;  // 128B swizzle: slot = chunk ^ (row & 7)
+              if (p.dbg != 1 || v.x == 0x12345678u)
+                __stcs(reinterpret_cast<uint4*>(img_base + (rt >> 3) * 1024 + (rt & 7) * 128 + half_off + (t4 << 4)), v);
+            }
+            __syncwarp();
           } else {
             // Scan path (always executed, kept tiny so it stays in the instruction cache): which of the 32 scores beat
             // this row's current KTOP-th best?  Rare path: the union of those columns over the warp is re-read from
@@ -412,7 +489,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
           p.rowpart[(((int64_t)pair * p.n_jchunk + jchunk) * NG + grp) * p.a_pad + arow] = rowsum;
           p.rowpos[(((int64_t)pair * p.n_jchunk + jchunk) * NG + grp) * p.a_pad + arow] = rowpos;
         }
-      } else {
+      } else if (EPI == EPI_TOPK) {
         if (row_ok) {
           const int64_t o = (((int64_t)jchunk * NG + grp) * p.a_rows + arow) * p.k;
 #pragma unroll
@@ -583,6 +660,72 @@ int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, float*
     if (rc) return rc;
   }
   return BSC_OK;
+}
+
+// ---- weight-matrix backward (one GPU) -------------------------------------------------------------------
+// 1. this file's sweep with the EPI_WEIGHTS epilogue recomputes S per unordered pair (the forward's 128 x 256 tiles,
+//    cta_group::1) and writes G = gs (e (u + v) - 2 T) as fp16 images; 2. tc_bwd_gemms (tc_bwd3.cu) forms G * Yunit and
+//    G^T * Xunit.  Executes 6 + 12 N^2 D like the stored-span mode, but every kernel is a plain pipelined GEMM.
+void tc_bwd_matrix_dims(const bsc_infonce_desc* d, int* n_iblk_pad, int* n_j64) {
+  const int n_iblk = (int)((d->n_local + BM - 1) / BM);
+  *n_iblk_pad = 2 * ((n_iblk + 1) / 2);
+  *n_j64 = 4 * (int)((d->n_global + BN - 1) / BN);
+}
+
+int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStream_t st) {
+  BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
+  const void* xunit[3] = {nullptr, nullptr, nullptr};
+  for (int a = 0; a < 3; ++a)
+    if (d->xh[a]) {
+      void* dst = ws + L.xunit + (size_t)a * d->n_global * d->d * 2;
+      int rc = rows_unit_f16_launch(d->xh[a], d->inv[a], d->n_global, d->d, dst, st);
+      if (rc) return rc;
+      xunit[a] = dst;
+    }
+  SimParams p{};
+  int np = 0;
+  for (int a = 0; a < 3; ++a) {
+    if (d->xh[a]) {
+      int rc = make_tmap_2d(&p.tmap[a], d->xh[a], d->x16_dtype, d->n_global, d->d, 128);
+      if (rc) return rc;
+    }
+    p.inv[a] = d->inv[a];
+    for (int b = a + 1; b < 3; ++b)
+      if (d->xh[a] && d->xh[b]) {
+        p.pair_a[np] = a;
+        p.pair_b[np] = b;
+        ++np;
+      }
+  }
+  for (int a = 0; a < 3; ++a)
+    if (!d->xh[a]) p.tmap[a] = p.tmap[p.pair_a[0]];
+  p.n_pairs = np;
+  p.n_iblk = L.n_iblk;
+  p.n_jtile = L.n_jtile;
+  p.n_jchunk = L.n_jchunk;
+  p.jpc = L.jtiles_per_chunk;
+  p.num_items = np * L.n_jchunk * L.n_iblk;
+  p.kblocks = d->d / BK;
+  p.a_rows = d->n_local;
+  p.a_row0 = d->row0;
+  p.b_rows = d->n_global;
+  const float log2e = 1.4426950408889634f;
+  p.k1 = d->logit_scale * log2e;
+  p.k2 = d->logit_scale * log2e;
+  p.rep = d->rep;
+  p.uv = (const float*)(ws + L.uv);
+  p.gsbuf = (const float*)(ws + L.gs);
+  p.gimg = (uint8_t*)(ws + L.gimg);
+  tc_bwd_matrix_dims(d, &p.n_iblk_pad, &p.n_j64);
+  {
+    const char* e = getenv("BSC_DBG_W");
+    p.dbg = e ? atoi(e) : 0;
+  }
+  timing_begin(1, st);
+  int rc = launch_sim<EPI_WEIGHTS, 0>(p, st);
+  timing_end(1, st);
+  if (rc) return rc;
+  return tc_bwd_gemms(d, L, ws, xunit, p.n_iblk_pad, p.n_j64, st);
 }
 
 // ---- retrieval ---------------------------------------------------------------------------------------

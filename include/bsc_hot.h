@@ -205,10 +205,16 @@ int bsc_taxonomy_eval(const int64_t* indices, int64_t nq, int k, const int32_t* 
 /* ------------------------------------------------------------------------------------------------
  * Instrumentation for bench.py: CUDA-event time of the dominant kernel of the last call made with
  * bsc_set_timing(1) on this thread (milliseconds, -1 if none).  which: 0 = infonce forward sweep,
- * 1 = infonce backward sweep, 2 = bank scan.  Reading it synchronises on the recorded events only.
+ * 1 = infonce backward sweep (mode 2 below: the weight-matrix kernel), 2 = bank scan, 3 = gradient GEMMs from stored
+ * weights (backward modes 1 and 2).  Reading it synchronises on the recorded events only.
+ * bsc_last_bwd_mode: how the most recent bsc_infonce_bwd in TC16 mode formed the gradients --
+ *   0 the sweep recomputes S per ordered pair (any number of GPUs), 1 pair sweep per unordered pair + its stored
+ *   weight spans (one GPU, BSC_BWD_GSTORE=1), 2 weight matrix written once + two GEMMs per pair (one GPU, default);
+ *   -1 before the first call.
  * ---------------------------------------------------------------------------------------------- */
 int bsc_set_timing(int enabled);
 float bsc_last_kernel_ms(int which);
+int bsc_last_bwd_mode(void);
 /* kernels launched by this library on this thread since the last reset */
 int64_t bsc_launch_count(int reset);
 

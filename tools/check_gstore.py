@@ -1,4 +1,4 @@
-"""Stored-weight backward (BSC_BWD_GSTORE=1, default on one GPU) against the recomputing sweep (=0): gradients and times.
+"""Backward modes on one GPU (BSC_BWD_GSTORE = 0 recomputing sweep, 1 stored spans, 2 weight matrix + GEMMs): gradients and times.
     python tools/check_gstore.py [n ...]"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -14,7 +14,7 @@ _lib.set_timing(True)
 
 
 def run(n, store, reps):
-    os.environ["BSC_BWD_GSTORE"] = "1" if store else "0"
+    os.environ["BSC_BWD_GSTORE"] = str(int(store))
     feats, labels = bench.synth_loss_rows(torch, n, 0, n, dev, torch.bfloat16)
     if n <= 4096:  # repeated labels: positives off the diagonal
         labels = labels // 3
@@ -35,12 +35,14 @@ def run(n, store, reps):
 
 for n in sizes:
     reps = 4 if n >= 8192 else 2
-    l0, g0, a0, _, t0 = run(n, False, reps)
-    l1, g1, a1, b1, t1 = run(n, True, reps)
-    worst = 0.0
-    for m in range(3):
-        scale = g0[m].abs().max().item()
-        worst = max(worst, (g0[m] - g1[m]).abs().max().item() / scale)
-    print(f"n={n}: loss {l0:.6f} / {l1:.6f}; max |dgrad| / max |grad| = {worst:.3e}; "
-          f"recompute: sweep {a0:.3f} ms, step {t0:.3f} ms; stored: sweep {a1:.3f} + rev {b1:.3f} ms, step {t1:.3f} ms")
+    l0, g0, a0, _, t0 = run(n, 0, reps)
+    print(f"n={n}: loss {l0:.6f}; recompute: sweep {a0:.3f} ms, step {t0:.3f} ms")
+    for mode in (1, 2):
+        l1, g1, a1, b1, t1 = run(n, mode, reps)
+        worst = 0.0
+        for m in range(3):
+            scale = g0[m].abs().max().item()
+            worst = max(worst, (g0[m] - g1[m]).abs().max().item() / scale)
+        print(f"   mode {mode}: loss {l1:.6f}; max |dgrad| / max |grad| = {worst:.3e}; "
+              f"first kernel {a1:.3f} + gemm {b1:.3f} ms, step {t1:.3f} ms")
     torch.cuda.empty_cache()
