@@ -117,7 +117,7 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-TRAFFIC_GEMMS = None  # filled in from the ncu capture of tc_bwd_rev_kernel (profiles/r1_bwd_gemms.txt)
+TRAFFIC_GEMMS = 2.559e10  # ncu: 24.98 GB read + 0.61 GB written per launch of tc_bwd_rev_kernel (profiles/r1_bwd_gemms.txt)
 
 
 def synth_loss_rows(torch, n_global, row0, n_local, device, dtype):
@@ -390,6 +390,7 @@ def run_native(args):
                     "unit": "TFLOP/s", "frac": ach / peaks["tflops_sustained"],
                     "traffic": traffic, "traffic_unit": "B", "kernel": kernel,
                     "peak_source": peaks["source"] + " bf16_tflops_sustained (kernel timed inside a long step)",
+                    "peak_burst": peaks["tflops_burst"], "frac_of_burst": ach / peaks["tflops_burst"],
                     "kernel_ms": k_ms, "algorithmic_flops_per_launch": k_flops,
                     "executed_tflops": k_exec / (k_ms * 1e-3) / 1e12,
                     "backward_mode": bwd_mode,

@@ -113,7 +113,6 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
 
   if (warp == 0) {
     if (ptx::elect_one()) {
-      const uint64_t pol_stream = ptx::l2_policy_evict_first();  // images are read nchunk times back to back, then never
       int stage = 0;
       uint32_t phase = 0;
       for (int item = item0; item < p.num_items; item += item_step) {
@@ -132,12 +131,12 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
           if (crank == 0) ptx::mbar_arrive_expect_tx(full, 2 * STAGE_BYTES);
           if (!mn) {
             const int64_t img = (pair0 + mblk) * p.img_c + kb;
-            ptx::tma_load_2d_2cta_hint(sa, &p.tmap_g128, full_l, 0, (int32_t)(img * 128), pol_stream);
+            ptx::tma_load_2d_2cta(sa, &p.tmap_g128, full_l, 0, (int32_t)(img * 128));
           } else {
             const int64_t img = (pair0 + (kb >> 1)) * p.img_c + 2 * mblk;
             const int32_t r0 = (int32_t)(img * 128) + 64 * (kb & 1);
-            ptx::tma_load_2d_2cta_hint(sa, &p.tmap_g64, full_l, 0, r0, pol_stream);
-            ptx::tma_load_2d_2cta_hint(sa + A_BYTES / 2, &p.tmap_g64, full_l, 0, r0 + 128, pol_stream);
+            ptx::tma_load_2d_2cta(sa, &p.tmap_g64, full_l, 0, r0);
+            ptx::tma_load_2d_2cta(sa + A_BYTES / 2, &p.tmap_g64, full_l, 0, r0 + 128);
           }
           ptx::tma_load_2d_2cta(sa + A_BYTES, mu, full_l, d0, kb * BK);
           ptx::tma_load_2d_2cta(sa + A_BYTES + B_BOX, mu, full_l, d0 + 64, kb * BK);

@@ -293,6 +293,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
         }
         invb_g = p.inv[p.pair_b[pair]];
         vcol_g = p.uv + (int64_t)pair_id(p.pair_b[pair], p.pair_a[pair]) * p.b_rows;
+        wmin = row_ok ? rep_i : 0x7fffffff;
+        wmax = row_ok ? rep_i : -1;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          wmin = min(wmin, __shfl_xor_sync(0xffffffffu, wmin, o));
+          wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+        }
       }
       float ts[KTOP];
       int ti[KTOP];
@@ -337,7 +344,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
         float* cs = tail->cs[buf][q];
         const float* ivb = tail->invb[buf];
         bool tile_pos = false;  // can any (row of this warp, column of this tile) pair share a label?
-        if (EPI == EPI_STATS) {
+        if (EPI == EPI_STATS || EPI == EPI_WEIGHTS) {
           const int2 jr = p.jrange[jt];
           tile_pos = (wmax >= jr.x) && (wmin <= jr.y);
         }
@@ -382,17 +389,31 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
             const int* repb = reinterpret_cast<const int*>(&tail->cs[1][0][0]) + buf * BN + c * 32;
             const float m2g = -2.0f * gsw;
             uint32_t pk[16];
+            if (tile_pos && p.dbg != 2) {  // some (row of this warp, column of this tile) pair may share a label
 #pragma unroll
-            for (int t = 0; t < 32; t += 2) {
-              float g2[2];
+              for (int t = 0; t < 32; t += 2) {
+                float g2[2];
 #pragma unroll
-              for (int z = 0; z < 2; ++z) {
-                const float ex = ptx::ex2(fmaf(__uint_as_float(raw[t + z]), inv_i * ivb[c * 32 + t + z], -p.k2));
-                const float tv = (p.dbg != 2 && repb[t + z] == rep_i) ? m2g : 0.f;
-                g2[z] = fmaf(ex, ugs_i + vgb[t + z], tv);
+                for (int z = 0; z < 2; ++z) {
+                  const float ex = ptx::ex2(fmaf(__uint_as_float(raw[t + z]), inv_i * ivb[c * 32 + t + z], -p.k2));
+                  const float tv = (repb[t + z] == rep_i) ? m2g : 0.f;
+                  g2[z] = fmaf(ex, ugs_i + vgb[t + z], tv);
+                }
+                const __half2 hh = __floats2half2_rn(g2[0], g2[1]);
+                pk[t >> 1] = *reinterpret_cast<const uint32_t*>(&hh);
               }
-              const __half2 hh = __floats2half2_rn(g2[0], g2[1]);
-              pk[t >> 1] = *reinterpret_cast<const uint32_t*>(&hh);
+            } else {
+#pragma unroll
+              for (int t = 0; t < 32; t += 2) {
+                float g2[2];
+#pragma unroll
+                for (int z = 0; z < 2; ++z) {
+                  const float ex = ptx::ex2(fmaf(__uint_as_float(raw[t + z]), inv_i * ivb[c * 32 + t + z], -p.k2));
+                  g2[z] = ex * (ugs_i + vgb[t + z]);
+                }
+                const __half2 hh = __floats2half2_rn(g2[0], g2[1]);
+                pk[t >> 1] = *reinterpret_cast<const uint32_t*>(&hh);
+              }
             }
             // Half a row (64 bytes) of image (iblk, 4 jt + c / 2) per lane.  Staged through 2 KB of shared memory per
             // warp so that four lanes write the 64 contiguous bytes of one row: one 16-byte store per lane to 32
@@ -717,6 +738,11 @@ int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaS
   p.gsbuf = (const float*)(ws + L.gs);
   p.gimg = (uint8_t*)(ws + L.gimg);
   tc_bwd_matrix_dims(d, &p.n_iblk_pad, &p.n_j64);
+  p.jrange = (const int2*)(ws + L.jrange);
+  {
+    int rc = rep_range_launch(d->rep, d->n_global, BN, (int2*)(ws + L.jrange), st);
+    if (rc) return rc;
+  }
   {
     const char* e = getenv("BSC_DBG_W");
     p.dbg = e ? atoi(e) : 0;
