@@ -27,10 +27,22 @@ namespace {
 constexpr int BK = 64;
 constexpr int A_BYTES = 16384;            // one stored span
 constexpr int B_BOX = 8192;               // [64 i][64 d] fp16
-constexpr int STAGE_BYTES = A_BYTES + 2 * B_BOX;  // 32 KB per CTA
-constexpr int STAGES = 6;
 constexpr int TMEM_COLS = 512;
-constexpr int BN = 256;  // d columns per item
+constexpr int MAX_STAGES = 6;
+// WIDE = 0: 256 d columns per item, one accumulator (N = 256), TMEM double-buffered over items, 6 x 32 KB stages.
+// WIDE = 1: 384 d columns per item, two accumulators (N = 256 and N = 128) fed by the SAME A tile -- d = 768 is covered
+//           by two items instead of three, i.e. the weight images are read twice per GEMM instead of three times (the
+//           three sibling clusters of WIDE = 0 share them through L2 only partly: 25-31 GB of DRAM reads per launch
+//           where 2 x 2 x 6.4 GB are needed); one TMEM buffer (384 of 512 columns), 5 x 40 KB stages.
+template <int WIDE>
+struct Cfg {
+  static constexpr int BN = WIDE ? 384 : 256;
+  static constexpr int NBOX = WIDE ? 3 : 2;  // 64-column boxes of B per CTA and stage
+  static constexpr int STAGE_BYTES = A_BYTES + NBOX * B_BOX;
+  static constexpr int STAGES = WIDE ? 5 : 6;
+  static constexpr int NBUF = WIDE ? 1 : 2;
+  static constexpr size_t SMEM = 1024 + (size_t)STAGES * STAGE_BYTES + 256;
+};
 
 struct RevParams {
   CUtensorMap tmap_g128;  // gimg as [rows][64] fp16, box 64 x 128, no swizzle (the bytes are already swizzled)
@@ -44,6 +56,7 @@ struct RevParams {
   int job_fnum[6], job_fden[6], job_finv[6];  // epilogue row factor gsbuf[fnum] * gsbuf[fden] (/ inv_out[row] if finv)
   int img_r, img_c;
   int n_mb, nchunk, kparts, num_items, d;
+  int wide;  // 384-wide items (two accumulators), d % 384 == 0
   int64_t n;
   const float* inv[3];
   const float* gsbuf;
@@ -51,15 +64,15 @@ struct RevParams {
 };
 
 struct __align__(8) RevTail {
-  uint64_t full[STAGES];
-  uint64_t empty[STAGES];
+  uint64_t full[MAX_STAGES];
+  uint64_t empty[MAX_STAGES];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
   uint32_t tmem_base;
   uint32_t pad;
 };
 
-constexpr size_t REV_SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + sizeof(RevTail);
+static_assert(sizeof(RevTail) <= 256, "tail budget");
 
 __device__ __forceinline__ void rev_item(const RevParams& p, int item, int& job, int& mb, int& part, int& c, int& kb_lo,
                                          int& kb_hi) {
@@ -74,7 +87,12 @@ __device__ __forceinline__ void rev_item(const RevParams& p, int item, int& job,
   kb_hi = (int)((int64_t)(part + 1) * nk / p.kparts);
 }
 
+template <int WIDE>
 __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constant__ RevParams p) {
+  constexpr int BN = Cfg<WIDE>::BN;
+  constexpr int STAGES = Cfg<WIDE>::STAGES;
+  constexpr int STAGE_BYTES = Cfg<WIDE>::STAGE_BYTES;
+  constexpr int NBUF = Cfg<WIDE>::NBUF;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
   const uint32_t ring = (raw_addr + 1023u) & ~1023u;
@@ -122,7 +140,8 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
         const int mblk = 2 * mb + (int)crank;
         const int64_t pair0 = (int64_t)p.job_pair[job] * p.img_r;
         const bool mn = p.job_mn[job] != 0;
-        const int d0 = BN * c + 128 * (int)crank;
+        const int d0 = BN * c + 128 * (int)crank;       // this CTA's half of the N = 256 accumulator
+        const int d1 = BN * c + 256 + 64 * (int)crank;  // ... and of the N = 128 accumulator (WIDE)
         for (int kb = kb_lo; kb < kb_hi; ++kb) {
           ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 100 + stage);
           const uint32_t full = ptx::smem_u32(&tail->full[stage]);
@@ -140,6 +159,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
           }
           ptx::tma_load_2d_2cta(sa + A_BYTES, mu, full_l, d0, kb * BK);
           ptx::tma_load_2d_2cta(sa + A_BYTES + B_BOX, mu, full_l, d0 + 64, kb * BK);
+          if (WIDE) ptx::tma_load_2d_2cta(sa + A_BYTES + 2 * B_BOX, mu, full_l, d1, kb * BK);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1u;
@@ -149,8 +169,10 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
     }
   } else if (warp == 1) {
     if (crank == 0 && ptx::elect_one()) {
-      constexpr uint32_t idesc_k = umma_idesc(256, BN, 0, 0, 0, 1);   // A K-major, B MN-major
-      constexpr uint32_t idesc_mn = umma_idesc(256, BN, 0, 0, 1, 1);  // A MN-major, B MN-major
+      constexpr uint32_t idesc_k = umma_idesc(256, 256, 0, 0, 0, 1);    // A K-major, B MN-major
+      constexpr uint32_t idesc_mn = umma_idesc(256, 256, 0, 0, 1, 1);   // A MN-major, B MN-major
+      constexpr uint32_t idesc_k2 = umma_idesc(256, 128, 0, 0, 0, 1);   // second accumulator (WIDE): N = 128
+      constexpr uint32_t idesc_mn2 = umma_idesc(256, 128, 0, 0, 1, 1);
       const uint64_t desc_ak = ptx::umma_desc_sw128(0, 16, 1024);
       const uint64_t desc_amn = ptx::umma_desc_sw128(0, A_BYTES / 2, 1024);  // two 64-wide M chunks 8 KB apart
       const uint64_t desc_b = ptx::umma_desc_sw128(0, B_BOX, 1024);
@@ -162,10 +184,12 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
         rev_item(p, item, job, mb, part, c, kb_lo, kb_hi);
         const bool mn = p.job_mn[job] != 0;
         const uint32_t idesc = mn ? idesc_mn : idesc_k;
+        const uint32_t idesc2 = mn ? idesc_mn2 : idesc_k2;
         const uint64_t desc_a = mn ? desc_amn : desc_ak;
         const uint64_t a_step = mn ? 128u : 2u;  // 16 K rows of 128 bytes / 32 bytes along a K-major row
-        const uint32_t buf = count & 1u;
-        ptx::mbar_wait_cluster(ptx::smem_u32(&tail->tmem_empty[buf]), ((count >> 1) & 1u) ^ 1u, 200 + buf);
+        const uint32_t buf = NBUF == 2 ? (count & 1u) : 0u;
+        const uint32_t use = NBUF == 2 ? (count >> 1) : count;
+        ptx::mbar_wait_cluster(ptx::smem_u32(&tail->tmem_empty[buf]), (use & 1u) ^ 1u, 200 + buf);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * BN;
         for (int kb = kb_lo; kb < kb_hi; ++kb) {
@@ -175,9 +199,14 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
           const uint64_t da = desc_a + ptx::desc_addr(sa);
           const uint64_t db = desc_b + ptx::desc_addr(sa + A_BYTES);
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            ptx::umma_f16_2cta(d_tmem, da + a_step * k, db + (uint64_t)(k * 128), idesc,
-                               (kb != kb_lo || k != 0) ? 1u : 0u);
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint32_t acc = (kb != kb_lo || k != 0) ? 1u : 0u;
+            ptx::umma_f16_2cta(d_tmem, da + a_step * k, db + (uint64_t)(k * 128), idesc, acc);
+            if (WIDE) {
+              const uint64_t db2 = desc_b + ptx::desc_addr(sa + A_BYTES + 2 * B_BOX);
+              ptx::umma_f16_2cta(d_tmem + 256, da + a_step * k, db2 + (uint64_t)(k * 128), idesc2, acc);
+            }
+          }
           ptx::umma_commit_2cta(ptx::smem_u32(&tail->empty[stage]), 3);
           if (kb == kb_hi - 1) ptx::umma_commit_2cta(ptx::smem_u32(&tail->tmem_full[buf]), 3);
           if (++stage == STAGES) {
@@ -189,14 +218,16 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
     }
   } else if (warp >= 4) {
     const int q = warp & 3;
-    const int grp = (warp - 4) >> 2;  // 128-column half of the accumulator
+    const int grp = (warp - 4) >> 2;  // column half of the item's accumulators
+    constexpr int CPG = BN / 64;      // 32-column chunks per warp group
     const uint32_t empty_l0 = ptx::mapa(ptx::smem_u32(&tail->tmem_empty[0]), 0);
     uint32_t count = 0;
     for (int item = item0; item < p.num_items; item += item_step, ++count) {
       int job, mb, part, c, kb_lo, kb_hi;
       rev_item(p, item, job, mb, part, c, kb_lo, kb_hi);
       const int mo = p.job_out[job];
-      const uint32_t buf = count & 1u;
+      const uint32_t buf = NBUF == 2 ? (count & 1u) : 0u;
+      const uint32_t use = NBUF == 2 ? (count >> 1) : count;
       const int64_t row = ((int64_t)(2 * mb + (int)crank)) * 128 + q * 32 + lane;
       float f = 0.f;
       if (row < p.n) {
@@ -208,12 +239,12 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
       }
       float* out = p.dxraw + (((int64_t)(mo * 2 + p.job_slot[job]) * p.kparts + part) * p.n + row) * p.d + BN * c;
       if (kb_hi > kb_lo) {
-        ptx::mbar_wait(ptx::smem_u32(&tail->tmem_full[buf]), (count >> 1) & 1u, 400 + buf);
+        ptx::mbar_wait(ptx::smem_u32(&tail->tmem_full[buf]), use & 1u, 400 + buf);
         ptx::tc_fence_after();
       }
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN;
 #pragma unroll 1
-      for (int cc = grp * 4; cc < grp * 4 + 4; ++cc) {
+      for (int cc = grp * CPG; cc < grp * CPG + CPG; ++cc) {
         uint32_t raw[32];
         if (kb_hi > kb_lo) {
           ptx::tmem_ld_32x32(taddr + cc * 32, raw);
@@ -260,9 +291,13 @@ int sm_count3() {
 
 static int rev_launch(RevParams& p, cudaStream_t st) {
   if (p.num_items == 0) return BSC_OK;
+  const bool wide = p.wide != 0;
   static bool attr_done = false;
   if (!attr_done) {
-    BSC_CUDA(cudaFuncSetAttribute(tc_bwd_rev_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)REV_SMEM_BYTES));
+    BSC_CUDA(cudaFuncSetAttribute(tc_bwd_rev_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)Cfg<0>::SMEM));
+    BSC_CUDA(cudaFuncSetAttribute(tc_bwd_rev_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)Cfg<1>::SMEM));
     attr_done = true;
   }
   int clusters = sm_count3() / 2;
@@ -270,7 +305,7 @@ static int rev_launch(RevParams& p, cudaStream_t st) {
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)(2 * clusters));
   cfg.blockDim = dim3(384);
-  cfg.dynamicSmemBytes = REV_SMEM_BYTES;
+  cfg.dynamicSmemBytes = wide ? Cfg<1>::SMEM : Cfg<0>::SMEM;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -280,7 +315,10 @@ static int rev_launch(RevParams& p, cudaStream_t st) {
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   timing_begin(3, st);
-  BSC_CUDA(cudaLaunchKernelEx(&cfg, tc_bwd_rev_kernel, p));
+  if (wide)
+    BSC_CUDA(cudaLaunchKernelEx(&cfg, tc_bwd_rev_kernel<1>, p));
+  else
+    BSC_CUDA(cudaLaunchKernelEx(&cfg, tc_bwd_rev_kernel<0>, p));
   timing_end(3, st);
   BSC_LAUNCH_CHECK("tc_bwd_rev_kernel");
   return BSC_OK;
@@ -305,7 +343,11 @@ static int rev_common(RevParams& p, const bsc_infonce_desc* d, const InfoNceWs& 
     if (!xunit[a]) p.tmap_u[a] = p.tmap_u[first];
     p.inv[a] = d->inv[a];
   }
-  p.nchunk = d->d / BN;
+  {
+    const char* e = getenv("BSC_BWD_WIDE");  // 0 forces 256-wide items
+    p.wide = (d->d % 384 == 0 && !(e && e[0] == '0')) ? 1 : 0;
+  }
+  p.nchunk = d->d / (p.wide ? 384 : 256);
   p.kparts = L.bwd_jsplit > 0 ? L.bwd_jsplit : 1;
   p.d = d->d;
   p.n = N;
