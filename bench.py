@@ -370,11 +370,13 @@ def run_native(args):
     #   1 tc_bwd_duo_kernel per unordered pair: one GEMM per pair (6 n N D), tc_bwd_rev_kernel the other (6 n N D).
     #   2 (one GPU, default) tc_sim_kernel<EPI_WEIGHTS> writes the weight matrix (0 algorithmic, executes 6 n N D),
     #     tc_bwd_rev_kernel forms both GEMMs of every pair from it: 12 n N D -- the dominant kernel.
+    #   3 (several GPUs, default) the same two kernels per ORDERED pair on this rank's rows: weights execute 12 n N D,
+    #     the GEMMs 12 n N D (all algorithmic).
     unit = float(n_local) * n_global * DIM
     fwd_flops = 6.0 * unit
     roofline = None
     if bwd_avg:
-        if bwd_mode == 2 and rev_avg:
+        if bwd_mode in (2, 3) and rev_avg:
             kernel, k_ms, k_flops, k_exec = "tc_bwd_rev_kernel", rev_avg, 12.0 * unit, 12.0 * unit
             # r1_bwd_gemms.txt: dram__bytes_read.sum + dram__bytes_write.sum of one launch
             traffic = TRAFFIC_GEMMS if (world == 1 and n_global == 32768) else None

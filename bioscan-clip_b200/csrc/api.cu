@@ -174,7 +174,7 @@ InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p) {
   L.jrange = take((size_t)(L.n_jtile > 0 ? L.n_jtile : 1) * 2 * sizeof(int));
   L.colpart = take((size_t)3 * (L.n_iblk > 0 ? L.n_iblk : 1) * L.n_global_pad * sizeof(float));
   L.bwd_gstore = tc_bwd_gstore(p);
-  L.bwd_jsplit = L.bwd_gstore == 2 ? 1 : tc_bwd_duo_jsplit(p);
+  L.bwd_jsplit = L.bwd_gstore >= 2 ? tc_bwd_gemm_ksplit(p, L.bwd_gstore) : tc_bwd_duo_jsplit(p);
   L.dxraw = take((size_t)3 * 2 * L.bwd_jsplit * (n > 0 ? n : 1) * D * sizeof(float));
   if (L.bwd_gstore) {
     L.xunit = take((size_t)3 * N * D * 2);

@@ -96,12 +96,14 @@ int tc_bwd_duo(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStre
 int tc_bwd_duo_jsplit(const bsc_infonce_desc* p);
 // stored-weight backward (all rows local): is it used for this problem, and how many bytes of weight spans it keeps
 // 0 = recomputing sweep, 1 = pair sweep per unordered pair + stored spans, 2 = weight matrix + two GEMMs per pair
+// (all rows local), 3 = weight blocks per ordered pair + one GEMM each (this rank's rows of a multi-GPU run)
 int tc_bwd_gstore(const bsc_infonce_desc* p);
 size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* p, int mode);
 void tc_bwd_matrix_dims(const bsc_infonce_desc* d, int* n_iblk_pad, int* n_j64);
+int tc_bwd_gemm_ksplit(const bsc_infonce_desc* d, int mode);
 int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStream_t st);
 int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_iblk_pad,
-                 int n_j64, cudaStream_t st);
+                 int n_j64, int n_pairs, const int* pairs_a, const int* pairs_b, int ordered, cudaStream_t st);
 int tc_bwd_rev(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_pairs,
                const int* pairs_x, const int* pairs_y, int n_jb, int n_i64, cudaStream_t st);
 int rows_unit_f16_launch(const void* x16, const float* inv, int64_t n, int d, void* out, cudaStream_t st);

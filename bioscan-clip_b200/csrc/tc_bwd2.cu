@@ -476,6 +476,10 @@ int sm_count2() {
 
 }  // namespace
 
+// measured on 2 GPUs (N = 32768): weight blocks per ordered pair + K-major GEMMs 7.4 ms against 8.6 ms for the pair sweep
+// (same 24 n N D executed; the GEMM kernels run closer to the tensor peak), step 11.96 -> 10.49 ms
+constexpr int kMultiGpuDefaultMode = 3;
+
 static bool duo_covers(const bsc_infonce_desc* d) {
   static const bool enabled = []() {
     const char* e = getenv("BSC_BWD_DUO");
@@ -492,25 +496,28 @@ size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* d, int mode) {
   int m = 0;
   for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
   const size_t pairs = (size_t)(m * (m - 1) / 2);
-  if (mode == 2) {
+  if (mode >= 2) {
     int n_iblk_pad, n_j64;
     tc_bwd_matrix_dims(d, &n_iblk_pad, &n_j64);
-    return pairs * (size_t)n_iblk_pad * (size_t)n_j64 * GSPAN;
+    return (mode == 3 ? 2 : 1) * pairs * (size_t)n_iblk_pad * (size_t)n_j64 * GSPAN;
   }
   const size_t n_iblk = (size_t)((d->n_local + BM - 1) / BM);
   const size_t n_steps = (size_t)(((d->n_global + BN - 1) / BN + 1) / 2);
   return pairs * (2 * n_steps) * (2 * n_iblk) * GSPAN;
 }
 
-// BSC_BWD_GSTORE = 0 | 1 | 2 picks the mode (default 2 where it applies); weight storage above BSC_BWD_GSTORE_GB
-// (default 48) falls back to the recomputing sweep.
+// BSC_BWD_GSTORE = 0 | 1 | 2 | 3 picks the mode where it applies (1 and 2 need all rows local, 3 is their multi-GPU
+// counterpart); default: 2 on one GPU, BSC_BWD_MULTI (0 or 3, default below) otherwise.  Weight storage above
+// BSC_BWD_GSTORE_GB (default 48) falls back to the recomputing sweep.
 int tc_bwd_gstore(const bsc_infonce_desc* d) {
   if (!duo_covers(d)) return 0;
-  if (d->n_local != d->n_global || d->row0 != 0) return 0;
-  int mode = 2;
+  const bool all_local = d->n_local == d->n_global && d->row0 == 0;
+  int mode = all_local ? 2 : kMultiGpuDefaultMode;
   const char* e = getenv("BSC_BWD_GSTORE");
-  if (e && e[0] >= '0' && e[0] <= '2') mode = e[0] - '0';
-  if (mode == 0) return 0;
+  if (e && e[0] >= '0' && e[0] <= '3') mode = e[0] - '0';
+  if (all_local && mode == 3) mode = 2;
+  if (!all_local && (mode == 1 || mode == 2)) mode = 3;
+  if (mode == 0 || d->n_local == 0) return 0;
   const char* g = getenv("BSC_BWD_GSTORE_GB");
   const double cap = (g ? atof(g) : 48.0) * 1073741824.0;
   return (double)tc_bwd_gimg_bytes(d, mode) <= cap ? mode : 0;
@@ -552,7 +559,7 @@ int tc_bwd_duo_jsplit(const bsc_infonce_desc* d) {
 // Returns BSC_OK when the paired kernel ran, 1 when this shape is not covered (caller falls back), < 0 on error.
 int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStream_t st) {
   if (!duo_covers(d)) return 1;
-  if (L.bwd_gstore == 2) return tc_bwd_matrix(d, L, ws, st);
+  if (L.bwd_gstore >= 2) return tc_bwd_matrix(d, L, ws, st);
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
   DuoParams p{};
   int first = -1;

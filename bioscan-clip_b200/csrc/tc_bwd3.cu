@@ -395,41 +395,68 @@ int tc_bwd_rev(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const vo
   return rev_launch(p, st);
 }
 
-// Weight-matrix mode (L.bwd_gstore == 2): both gradient GEMMs of every unordered pair (x, y) from the images
-// gimg[(pair * n_iblk_pad + iblk) * n_j64 + j64] = G[128 i][64 j] that tc_bwd_weights wrote:
-//   dXhat = G * Yunit   (A K-major: image rows are i, K runs over j),   dYhat = G^T * Xunit   (A MN-major, K over i).
+// K split of the gradient GEMMs (= dxraw parts that combine_kernel sums in a fixed order): the clusters take whole items,
+// so a few hundred items on 74 clusters (many ranks: 192 at 8 GPUs) would leave the last round mostly idle.
+int tc_bwd_gemm_ksplit(const bsc_infonce_desc* d, int mode) {
+  int m = 0;
+  for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
+  const int64_t jobs = (int64_t)m * (m - 1);  // 2 per unordered pair (mode 2) = 1 per ordered pair (mode 3)
+  const int64_t n_mb = (d->n_local + 255) / 256;
+  const int64_t nchunk = d->d % 384 == 0 ? d->d / 384 : d->d / 256;
+  const int64_t items0 = jobs * n_mb * nchunk;
+  const int64_t nk = (d->n_global + 63) / 64;
+  const int clusters = sm_count3() / 2;
+  (void)mode;
+  if (items0 <= 0) return 1;
+  int best = 1;
+  double best_cost = 1e300;
+  for (int s = 1; s <= 8; ++s) {
+    if (s > nk) break;
+    const double rounds = (double)((items0 * s + clusters - 1) / clusters);
+    // cost in K blocks: rounds * (K blocks per item + ~12 blocks' worth of pipeline fill and accumulator drain)
+    const double cost = rounds * ((double)nk / s + 12.0);
+    if (cost < best_cost * 0.99) {
+      best_cost = cost;
+      best = s;
+    }
+  }
+  return best;
+}
+
+// Weight-matrix modes: the gradient GEMMs from the images gimg[(pair * n_iblk_pad + iblk) * n_j64 + j64] = G[128 i][64 j]
+// that tc_bwd_matrix wrote.
+//   mode 2 (all rows local, unordered pairs (x, y)):  dXhat = G * Yunit (A K-major: image rows are i, K runs over j) and
+//                                                     dYhat = G^T * Xunit (A MN-major from the same images, K over i);
+//   mode 3 (ordered pairs (a, b), this rank's rows of a):  dAhat = G_ab * Bunit, K-major only.
 int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_iblk_pad,
-                 int n_j64, cudaStream_t st) {
+                 int n_j64, int n_pairs, const int* pairs_a, const int* pairs_b, int ordered, cudaStream_t st) {
   RevParams p{};
-  int np = 0;
-  for (int x = 0; x < 3; ++x)
-    for (int y = x + 1; y < 3; ++y)
-      if (d->xh[x] && d->xh[y]) ++np;
-  int rc = rev_common(p, d, L, ws, xunit, (int64_t)np * n_iblk_pad * n_j64 * 128);
+  int rc = rev_common(p, d, L, ws, xunit, (int64_t)n_pairs * n_iblk_pad * n_j64 * 128);
   if (rc) return rc;
   p.img_r = n_iblk_pad;
   p.img_c = n_j64;
+  p.n = d->n_local;  // output rows (== n_global in mode 2)
+  p.n_mb = (int)((d->n_local + 255) / 256);
   const int nk64 = (int)((d->n_global + 63) / 64);
-  int q = 0, job = 0;
-  for (int x = 0; x < 3; ++x)
-    for (int y = x + 1; y < 3; ++y) {
-      if (!d->xh[x] || !d->xh[y]) continue;
-      for (int side = 0; side < 2; ++side, ++job) {
-        const int mo = side == 0 ? x : y, mi = side == 0 ? y : x;
-        p.job_pair[job] = q;
-        p.job_mn[job] = side;
-        p.job_out[job] = mo;
-        p.job_in[job] = mi;
-        p.job_slot[job] = slot_of(d, mo, mi);
-        p.job_nk[job] = nk64;  // K blocks of 64 columns j (side 0) / 64 rows i (side 1): both modalities have N rows
-        p.job_fnum[job] = 2 * pair_id(mo, mi);
-        p.job_fden[job] = 17;  // 1 / gs of the stored weights
-        p.job_finv[job] = 0;
-      }
-      ++q;
+  int job = 0;
+  for (int q = 0; q < n_pairs; ++q) {
+    const int x = pairs_a[q], y = pairs_b[q];
+    for (int side = 0; side < (ordered ? 1 : 2); ++side, ++job) {
+      const int mo = side == 0 ? x : y, mi = side == 0 ? y : x;
+      p.job_pair[job] = q;
+      p.job_mn[job] = side;
+      p.job_out[job] = mo;
+      p.job_in[job] = mi;
+      p.job_slot[job] = slot_of(d, mo, mi);
+      p.job_nk[job] = nk64;  // K blocks of 64 columns j (side 0) / 64 rows i (side 1, where n_local == n_global)
+      p.job_fnum[job] = 2 * pair_id(mo, mi);
+      p.job_fden[job] = 17;  // 1 / gs of the stored weights
+      p.job_finv[job] = 0;
     }
+  }
   p.n_jobs = job;
-  BSC_REQUIRE(p.kparts == 1, BSC_EUNSUPPORTED, "tc_bwd_gemms: the weight-matrix backward does not split K");
+  BSC_REQUIRE(p.kparts >= 1 && p.kparts <= nk64, BSC_EUNSUPPORTED, "tc_bwd_gemms: K split %d of %d blocks", p.kparts,
+              nk64);
   p.num_items = p.n_jobs * p.n_mb * p.kparts * p.nchunk;
   return rev_launch(p, st);
 }

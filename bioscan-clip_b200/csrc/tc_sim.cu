@@ -39,7 +39,7 @@ struct SimParams {
   CUtensorMap tmap[3];  // per operand matrix: [rows][d], box {64, 128}
   // work decomposition: item = (pair, jchunk, iblk), iblk fastest
   int n_pairs;
-  int pair_a[3], pair_b[3];
+  int pair_a[6], pair_b[6];  // unordered pairs (forward, single-GPU weights) or ordered pairs (multi-GPU weights)
   int n_iblk, n_jtile, n_jchunk, jpc;
   int n_iblk_items;  // row blocks per work item index: n_iblk (cta_group::1) or n_iblk / 2 (CTA pairs)
   int num_items;
@@ -697,6 +697,9 @@ void tc_bwd_matrix_dims(const bsc_infonce_desc* d, int* n_iblk_pad, int* n_j64) 
 
 int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStream_t st) {
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
+  // mode 2: all rows local, one weight block per UNORDERED pair serves both sides.  Mode 3 (several GPUs): this rank's
+  // rows of modality a against all rows of b, one block per ORDERED pair (the other side's block lives on other ranks).
+  const bool ordered = L.bwd_gstore == 3;
   const void* xunit[3] = {nullptr, nullptr, nullptr};
   for (int a = 0; a < 3; ++a)
     if (d->xh[a]) {
@@ -706,23 +709,25 @@ int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaS
       xunit[a] = dst;
     }
   SimParams p{};
-  int np = 0;
+  int np = 0, first = -1;
   for (int a = 0; a < 3; ++a) {
     if (d->xh[a]) {
       int rc = make_tmap_2d(&p.tmap[a], d->xh[a], d->x16_dtype, d->n_global, d->d, 128);
       if (rc) return rc;
+      if (first < 0) first = a;
     }
     p.inv[a] = d->inv[a];
-    for (int b = a + 1; b < 3; ++b)
-      if (d->xh[a] && d->xh[b]) {
+    for (int b = ordered ? 0 : a + 1; b < 3; ++b)
+      if (b != a && d->xh[a] && d->xh[b]) {
         p.pair_a[np] = a;
         p.pair_b[np] = b;
         ++np;
       }
   }
   for (int a = 0; a < 3; ++a)
-    if (!d->xh[a]) p.tmap[a] = p.tmap[p.pair_a[0]];
+    if (!d->xh[a]) p.tmap[a] = p.tmap[first];
   p.n_pairs = np;
+  // the forward's tiling was sized for its own pair count; the item count only has to cover np * n_jchunk * n_iblk
   p.n_iblk = L.n_iblk;
   p.n_jtile = L.n_jtile;
   p.n_jchunk = L.n_jchunk;
@@ -753,7 +758,7 @@ int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaS
   int rc = launch_sim<EPI_WEIGHTS, 0>(p, st);
   timing_end(1, st);
   if (rc) return rc;
-  return tc_bwd_gemms(d, L, ws, xunit, p.n_iblk_pad, p.n_j64, st);
+  return tc_bwd_gemms(d, L, ws, xunit, p.n_iblk_pad, p.n_j64, np, p.pair_a, p.pair_b, ordered ? 1 : 0, st);
 }
 
 // ---- retrieval ---------------------------------------------------------------------------------------

@@ -210,7 +210,8 @@ int bsc_taxonomy_eval(const int64_t* indices, int64_t nq, int k, const int32_t* 
  * bsc_last_bwd_mode: how the most recent bsc_infonce_bwd in TC16 mode formed the gradients --
  *   0 the sweep recomputes S per ordered pair (any number of GPUs), 1 pair sweep per unordered pair + its stored
  *   weight spans (one GPU, BSC_BWD_GSTORE=1), 2 weight matrix written once + two GEMMs per pair (one GPU, default);
- *   -1 before the first call.
+ *   3 several GPUs, default: weight blocks of this rank's rows per ordered pair + one GEMM each (BSC_BWD_GSTORE=0
+ *   selects the pair sweep); -1 before the first call.
  * ---------------------------------------------------------------------------------------------- */
 int bsc_set_timing(int enabled);
 float bsc_last_kernel_ms(int which);

@@ -151,6 +151,22 @@ def test_tc16_backward_modes_match_oracle_and_each_other(n, d, present, labels, 
             assert (ga - gb).abs().max().item() <= 1.5e-3 * gb.abs().max().item()
 
 
+def test_tc16_backward_falls_back_to_recomputing_sweep_above_the_memory_cap(monkeypatch):
+    """The weight matrix is the one N x N-sized buffer of the design: above BSC_BWD_GSTORE_GB the backward recomputes."""
+    from bsc import _lib
+
+    feats, lab = loss_inputs(512, 768, (True, True, True), seed=3, labels="multi", dtype=torch.bfloat16)
+    ref_in = [f.float() for f in feats]
+    ref_loss, ref_grads = loss_oracle.closed_form_grads(ref_in, lab)
+    monkeypatch.setenv("BSC_BWD_GSTORE_GB", "0.0001")  # 107 KB < 3 pairs x 512 x 512 x 2 B
+    loss, grads = _run(ref_in, lab, "tc16")
+    assert _lib.last_bwd_mode() == 0
+    _compare(loss, grads, ref_loss, ref_grads, TC16_TOL)
+    monkeypatch.delenv("BSC_BWD_GSTORE_GB")
+    _run(ref_in, lab, "tc16")
+    assert _lib.last_bwd_mode() == 2
+
+
 def test_tc16_unnormalised_rows_of_mixed_scale():
     """Rows whose norms span 0.05 .. 40: the inverse norms live in the fp32 epilogue and in the weight tile."""
     feats, lab = loss_inputs(640, 768, seed=77, labels="multi", normalised=False, dtype=torch.bfloat16)
