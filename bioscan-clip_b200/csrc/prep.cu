@@ -541,6 +541,7 @@ __global__ void __launch_bounds__(1024) loss_kernel(const float* __restrict__ st
     for (int b = 0; b < 3; ++b) {
       if (b == a || !((present_mask >> b) & 1)) continue;
       const float* se = stats + (int64_t)pair_id(a, b) * n;
+#pragma unroll 8  // the loads of 8 iterations in flight; the double additions keep their order
       for (int64_t i = threadIdx.x; i < n; i += blockDim.x)
         acc += (double)r[i] * (double)logf(se[i]);
     }
