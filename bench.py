@@ -79,6 +79,8 @@ class ClockSampler:
         self.lines = []
 
     def start(self):
+        if os.environ.get("BSC_BENCH_NO_SAMPLER") == "1":  # experiment knob: is the sampler itself disturbing the run?
+            return
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50", "-i",
@@ -257,8 +259,22 @@ def run_native(args):
     if rank == 0:
         sampler.start()
     _lib.set_timing(True)  # the library's event pairs are created during the warm-up as well
-    for _ in range(args.warmup):
+    # W warm-up steps, run in exactly the form of the timed ones (flush, rank barrier, event pair, synchronise, read the
+    # library's kernel events): on a fresh box the SECOND step of that form was 2-4x slower than the others however
+    # many plain steps preceded it (seen at 1, 2, 4 and 8 GPUs; not caused by the clock sampler) -- first-use work that
+    # belongs to the warm-up.
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_()
+        if world > 1:
+            dist.barrier()
+        w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0.record()
         step_resident()
+        w1.record()
+        w1.synchronize()
+        w0.elapsed_time(w1)
+        for which in (0, 1, 3):
+            _lib.last_kernel_ms(which)
     barrier()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     fwd_ms, bwd_ms, rev_ms = [], [], []

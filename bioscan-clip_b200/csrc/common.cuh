@@ -107,6 +107,19 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const 
 int tc_bwd_rev(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_pairs,
                const int* pairs_x, const int* pairs_y, int n_jb, int n_i64, cudaStream_t st);
 int rows_unit_f16_launch(const void* x16, const float* inv, int64_t n, int d, void* out, cudaStream_t st);
+int rows_unit_f16_launch3(const void* const x16[3], const float* const inv[3], int64_t n, int d, void* const out[3],
+                          cudaStream_t st);
+struct ReduceJob {
+  const float* part;
+  int nparts;
+  int64_t part_stride, n;
+  float* out;
+};
+struct ReduceJobs {
+  ReduceJob job[6];
+  int count;
+};
+int reduce_parts_batch_launch(const ReduceJobs& jobs, cudaStream_t st);
 
 int simt_bank_search(const float* q, int64_t nq, const float* bank, int64_t nb, int d, int k, int64_t base_id,
                      float* out_s, int64_t* out_i, char* ws, size_t ws_bytes, cudaStream_t st);

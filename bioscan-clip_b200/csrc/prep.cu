@@ -127,9 +127,19 @@ int rows_to_f16_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx
   return BSC_OK;
 }
 
-// fp16 unit rows from the scaled fp16 rows: out = half(x16 * inv).  B operand of the stored-weight backward (tc_bwd3.cu).
-__global__ void __launch_bounds__(256) rows_unit_f16_kernel(const __half2* __restrict__ x, const float* __restrict__ inv,
-                                                            int64_t n, int d2, __half2* __restrict__ out) {
+// fp16 unit rows from the scaled fp16 rows: out = half(x16 * inv).  B operand of the gradient GEMMs (tc_bwd3.cu).
+// blockIdx.y = modality (absent ones have a null source).
+struct UnitRowsArgs {
+  const __half2* x[3];
+  const float* inv[3];
+  __half2* out[3];
+};
+
+__global__ void __launch_bounds__(256) rows_unit_f16_kernel(const UnitRowsArgs a, int64_t n, int d2) {
+  const __half2* __restrict__ x = a.x[blockIdx.y];
+  if (x == nullptr) return;
+  const float* __restrict__ inv = a.inv[blockIdx.y];
+  __half2* __restrict__ out = a.out[blockIdx.y];
   const int64_t total = n * (int64_t)d2;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const float s = inv[i / d2];
@@ -138,14 +148,28 @@ __global__ void __launch_bounds__(256) rows_unit_f16_kernel(const __half2* __res
   }
 }
 
-int rows_unit_f16_launch(const void* x16, const float* inv, int64_t n, int d, void* out, cudaStream_t st) {
+int rows_unit_f16_launch3(const void* const x16[3], const float* const inv[3], int64_t n, int d, void* const out[3],
+                          cudaStream_t st) {
   if (n == 0) return BSC_OK;
   BSC_REQUIRE(d % 2 == 0, BSC_EUNSUPPORTED, "rows_unit_f16: odd d");
+  UnitRowsArgs a{};
+  for (int m = 0; m < 3; ++m) {
+    a.x[m] = (const __half2*)x16[m];
+    a.inv[m] = inv[m];
+    a.out[m] = (__half2*)out[m];
+  }
   const int64_t total = n * (int64_t)(d / 2);
-  const unsigned grid = (unsigned)((total + 255) / 256 > 148 * 16 ? 148 * 16 : (total + 255) / 256);
-  rows_unit_f16_kernel<<<grid, 256, 0, st>>>((const __half2*)x16, inv, n, d / 2, (__half2*)out);
+  const unsigned gx = (unsigned)((total + 255) / 256 > 148 * 8 ? 148 * 8 : (total + 255) / 256);
+  rows_unit_f16_kernel<<<dim3(gx, 3), 256, 0, st>>>(a, n, d / 2);
   BSC_LAUNCH_CHECK("rows_unit_f16_kernel");
   return BSC_OK;
+}
+
+int rows_unit_f16_launch(const void* x16, const float* inv, int64_t n, int d, void* out, cudaStream_t st) {
+  const void* xs[3] = {x16, nullptr, nullptr};
+  const float* is[3] = {inv, nullptr, nullptr};
+  void* os[3] = {out, nullptr, nullptr};
+  return rows_unit_f16_launch3(xs, is, n, d, os, st);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -515,6 +539,26 @@ __global__ void __launch_bounds__(256) reduce_parts_kernel(const float* __restri
   float acc = 0.f;
   for (int p = 0; p < nparts; ++p) acc += part[p * part_stride + i];
   out[i] = acc;
+}
+
+// Up to 6 reductions in one launch (blockIdx.y = job): the forward's row and column sum-exp vectors of every pair.
+__global__ void __launch_bounds__(256) reduce_parts_batch_kernel(const ReduceJobs jobs) {
+  const ReduceJob j = jobs.job[blockIdx.y];
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= j.n) return;
+  float acc = 0.f;
+  for (int p = 0; p < j.nparts; ++p) acc += j.part[p * j.part_stride + i];
+  j.out[i] = acc;
+}
+
+int reduce_parts_batch_launch(const ReduceJobs& jobs, cudaStream_t st) {
+  int64_t nmax = 0;
+  for (int q = 0; q < jobs.count; ++q) nmax = jobs.job[q].n > nmax ? jobs.job[q].n : nmax;
+  if (jobs.count == 0 || nmax == 0) return BSC_OK;
+  dim3 grid((unsigned)((nmax + 255) / 256), (unsigned)jobs.count);
+  reduce_parts_batch_kernel<<<grid, 256, 0, st>>>(jobs);
+  BSC_LAUNCH_CHECK("reduce_parts_batch_kernel");
+  return BSC_OK;
 }
 
 int reduce_parts_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float* out, cudaStream_t st) {

@@ -1,18 +1,18 @@
-// Reverse-direction gradients of the InfoNCE backward from STORED weight tiles (single-GPU runs).
+// Gradient GEMMs of the InfoNCE backward from STORED fp16 weight images (tcgen05.mma.cta_group::2 on CTA pairs).
 //
 // The weight matrix of an unordered modality pair (x, y) is one matrix:  g_ij = e_ij (u_i + v_j) - 2 T_ij  gives both
-// dXhat = G * Yhat and dYhat = G^T * Xhat.  The pair sweep (tc_bwd2.cu) used to recompute S once per ORDERED pair
-// (24 N^2 D executed for 12 algorithmic); with all rows local it now sweeps the three unordered pairs once, keeps dXhat
-// in TMEM as before and additionally bulk-copies every fp16 weight span it builds (the very bytes its grad MMAs read,
-// [128 j][64 i], 128B-swizzled, i contiguous) to HBM:  gimg[pair][j tile][i64][16 KB].
-// This kernel then forms   dYhat[256 j x 256 d] = sum_i  G^T[j][i] * Xunit[i][d]   as a plain tcgen05 GEMM on CTA pairs
-// (cta_group::2, M = 256, N = 256, K = 64 per stage):
-//   A = a stored span = a K-major SWIZZLE_128B tile [128 j][64 i] as it lies in HBM (raw TMA copy, no swizzle mode),
-//   B = 64 rows of Xunit (fp16 unit rows, d contiguous = MN-major), each CTA 128 of the chunk's 256 d columns,
-//   accumulator [128 lanes = j][256 columns = d] fp32 in TMEM, double-buffered over work items.
-// A stored weight carries gs(x,y) / |y_j| (tc_bwd2.cu folds the operand scale of Y16 into it); the epilogue multiplies
-// row j by gs(y,x) |y_j| / gs(x,y) so that combine_kernel sees exactly what the ordered sweep (y -> x) used to write.
-// Executed work of the backward: 12 N^2 D (sweep) + 6 N^2 D (this kernel) instead of 24 N^2 D.
+// dXhat = G * Yhat and dYhat = G^T * Xhat.  Who writes the images (16 KB each, 128 rows x 64 fp16, 128B-swizzled):
+//   mode 2 / 3  tc_sim_kernel<EPI_WEIGHTS> (tc_sim.cu): G[128 i][64 j], one block per unordered pair (all rows local)
+//               or per ordered pair (this rank's rows of a multi-GPU run);
+//   mode 1      the pair sweep (tc_bwd2.cu), which keeps dXhat in TMEM and streams the spans [128 j][64 i] its grad MMAs
+//               read; a stored weight then carries gs(x,y) / |y_j| and the epilogue here undoes that per row.
+// One persistent kernel runs every job  out[M rows][d] = A[M][K] * unit_in[K][d]:
+//   A = an image as it lies in HBM (raw TMA copy, no swizzle mode): K-major when the image rows are the output rows,
+//       MN-major (halves of two images) when they are the reduction index -- G^T * Xhat from the SAME images;
+//   B = 64 fp16 unit rows (d contiguous = MN-major), each CTA its half of the accumulator's d columns;
+//   accumulators [128 lanes][256 (+128) columns] fp32 in TMEM; epilogue scales a row by gs_pair / gs_stored and writes
+//   dxraw for combine_kernel.
+// Executed work of the backward on one GPU: 6 N^2 D (weights) + 12 N^2 D (here) instead of 24 N^2 D.
 // Warp roles (384 threads): 0 TMA producer, 1 MMA issuer (leader CTA), 2 TMEM allocator, 4..11 epilogue.
 #include <cstdlib>
 

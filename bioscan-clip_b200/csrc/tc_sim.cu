@@ -673,16 +673,16 @@ int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, float*
   rc = sum_rows_launch(p.rowpos, np * L.n_jchunk * NG, L.n_local_pad, d->n_local, 0.6931471805599453f,
                        stats + 6 * d->n_global, st);
   if (rc) return rc;
+  ReduceJobs jobs{};
   for (int q = 0; q < np; ++q) {
     const int a = p.pair_a[q], b = p.pair_b[q];
-    rc = reduce_parts_launch(p.rowpart + (int64_t)q * L.n_jchunk * NG * L.n_local_pad, L.n_jchunk * NG, L.n_local_pad,
-                             d->n_local, stats + (int64_t)pair_id(a, b) * d->n_global + d->row0, st);
-    if (rc) return rc;
-    rc = reduce_parts_launch(p.colpart + (int64_t)q * L.n_iblk * L.n_global_pad, L.n_iblk, L.n_global_pad,
-                             d->n_global, stats + (int64_t)pair_id(b, a) * d->n_global, st);
-    if (rc) return rc;
+    jobs.job[jobs.count++] = ReduceJob{p.rowpart + (int64_t)q * L.n_jchunk * NG * L.n_local_pad, L.n_jchunk * NG,
+                                       L.n_local_pad, d->n_local,
+                                       stats + (int64_t)pair_id(a, b) * d->n_global + d->row0};
+    jobs.job[jobs.count++] = ReduceJob{p.colpart + (int64_t)q * L.n_iblk * L.n_global_pad, L.n_iblk, L.n_global_pad,
+                                       d->n_global, stats + (int64_t)pair_id(b, a) * d->n_global};
   }
-  return BSC_OK;
+  return reduce_parts_batch_launch(jobs, st);
 }
 
 // ---- weight-matrix backward (one GPU) -------------------------------------------------------------------
@@ -701,13 +701,13 @@ int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaS
   // rows of modality a against all rows of b, one block per ORDERED pair (the other side's block lives on other ranks).
   const bool ordered = L.bwd_gstore == 3;
   const void* xunit[3] = {nullptr, nullptr, nullptr};
-  for (int a = 0; a < 3; ++a)
-    if (d->xh[a]) {
-      void* dst = ws + L.xunit + (size_t)a * d->n_global * d->d * 2;
-      int rc = rows_unit_f16_launch(d->xh[a], d->inv[a], d->n_global, d->d, dst, st);
-      if (rc) return rc;
-      xunit[a] = dst;
-    }
+  {
+    void* dst[3] = {nullptr, nullptr, nullptr};
+    for (int a = 0; a < 3; ++a)
+      if (d->xh[a]) xunit[a] = dst[a] = ws + L.xunit + (size_t)a * d->n_global * d->d * 2;
+    int rc = rows_unit_f16_launch3(d->xh, d->inv, d->n_global, d->d, dst, st);
+    if (rc) return rc;
+  }
   SimParams p{};
   int np = 0, first = -1;
   for (int a = 0; a < 3; ++a) {
