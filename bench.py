@@ -87,6 +87,12 @@ class ClockSampler:
                  str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
+            # Wait for the first sample: on a fresh box nvidia-smi / NVML are paged in from a cold disk and attach to
+            # the driver hundreds of ms after the spawn -- that attach stalled the launches of the second timed step
+            # (15 -> 22-45 ms in the first process of every box, never in later ones).
+            t0 = time.perf_counter()
+            while not self.lines and time.perf_counter() - t0 < 15.0 and self.proc.poll() is None:
+                time.sleep(0.01)
         except Exception:
             self.proc = None
 
@@ -259,10 +265,14 @@ def run_native(args):
     if rank == 0:
         sampler.start()
     _lib.set_timing(True)  # the library's event pairs are created during the warm-up as well
+    # No cyclic-GC passes inside the timed regions (a CPU stall starves the launch queue and shows up as GPU time).
+    import gc
+
+    gc.collect()
+    gc.freeze()
+    gc.disable()
     # W warm-up steps, run in exactly the form of the timed ones (flush, rank barrier, event pair, synchronise, read the
-    # library's kernel events): on a fresh box the SECOND step of that form was 2-4x slower than the others however
-    # many plain steps preceded it (seen at 1, 2, 4 and 8 GPUs; not caused by the clock sampler) -- first-use work that
-    # belongs to the warm-up.
+    # library's kernel events).
     for _ in range(max(args.warmup, 3)):
         flush.zero_()
         if world > 1:
@@ -384,6 +394,8 @@ def run_native(args):
         dist.all_reduce(e2e_total, op=dist.ReduceOp.MAX)
     e2e_value = n_global / (float(e2e_total.item()) / e2e_steps * 1e-3)
     e2e_loss = float(host_loss)
+
+    gc.enable()
 
     # ---------------- roofline of the dominant kernel (backward sweep) ----------------
     peaks = measured_peaks()

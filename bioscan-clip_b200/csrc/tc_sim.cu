@@ -553,16 +553,16 @@ int launch_sim(const SimParams& p_in, cudaStream_t st) {
   SimParams p = p_in;
   p.n_iblk_items = p.n_iblk;
   if (p.num_items <= 0) return BSC_OK;
-  // Measured (B200, N = 32768): the forward sweep already keeps the tensor pipe 80 % busy at the power-capped clock and
-  // is 9 % SLOWER on CTA pairs (3.85 vs 3.54 ms: two epilogues run in lock step); the bulk bank scan is 1 % faster.
-  // The weights sweep of the single-GPU backward (store traffic on top of the operand stream) gains 15 % from pairs
-  // (5.1 -> 4.3 ms: a third less operand traffic per SM, and the same ring covers 50 % more MMA time).
-  // Default: pairs for the scan and the weights sweep.  BSC_SIM_PAIR=1 forces pairs everywhere, =0 disables them.
+  // CTA pairs (cta_group::2, M = 256): a third less operand traffic per SM (58 -> 39 GB from L2 per sweep), and the same
+  // ring covers 50 % more MMA time.  Measured (B200, N = 32768): bank scan +1 %, weights sweep 5.1 -> 4.3 ms.  The
+  // forward sweep timed alone after an idle gap was 9 % slower on pairs (3.85 vs 3.54 ms), but inside the step, where
+  // every kernel runs at the power cap, it is 5 % faster (4.20 -> 3.97 ms, three alternating runs) -- pairs everywhere.
+  // BSC_SIM_PAIR=0 disables them.
   static const int pair_env = []() {
     const char* e = getenv("BSC_SIM_PAIR");
     return e ? (e[0] == '0' ? 0 : 1) : -1;
   }();
-  const bool pair_ok = pair_env < 0 ? (EPI == EPI_TOPK || EPI == EPI_WEIGHTS) : (pair_env == 1);
+  const bool pair_ok = pair_env != 0;
   // CTA pairs need an even number of row blocks (the two CTAs of a pair take blocks 2m and 2m+1 of one column chunk)
   if (pair_ok && p.n_iblk >= 2 && (p.n_iblk % 2) == 0 && num_sms() >= 2) {
     auto kern = tc_sim_kernel<EPI, FMT, 1>;
