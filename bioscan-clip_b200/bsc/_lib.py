@@ -12,7 +12,7 @@ from ctypes import POINTER, byref, c_char_p, c_float, c_int, c_int32, c_int64, c
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbsc_hot.so")
+LIB_PATH = os.environ.get("BSC_LIB_PATH") or os.path.join(_HERE, "libbsc_hot.so")  # override: A/B of two builds
 
 BSC_F32, BSC_BF16, BSC_F16 = 0, 1, 2
 MODE_F32, MODE_TC16 = 0, 1

@@ -450,7 +450,8 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const 
       p.job_slot[job] = slot_of(d, mo, mi);
       p.job_nk[job] = nk64;  // K blocks of 64 columns j (side 0) / 64 rows i (side 1, where n_local == n_global)
       p.job_fnum[job] = 2 * pair_id(mo, mi);
-      p.job_fden[job] = 17;  // 1 / gs of the stored weights
+      // mode 2: weights scaled by gsbuf[16], combine expects gs(mo, mi); mode 3: the weights already carry gs(mo, mi)
+      p.job_fden[job] = ordered ? 2 * pair_id(mo, mi) + 1 : 17;
       p.job_finv[job] = 0;
     }
   }

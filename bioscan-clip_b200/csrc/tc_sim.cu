@@ -67,6 +67,8 @@ struct SimParams {
   const float* gsbuf;  // [16] = gs of the stored weights
   uint8_t* gimg;       // [pair][n_iblk_pad][n_j64][16 KB]
   int n_iblk_pad, n_j64;
+  int fold_inv;  // 1: the weights carry 1/|b_j| and gs of the ordered pair (mode 3: the GEMM's B operand is the scaled
+                 // fp16 rows themselves, exact for bf16 inputs); 0: unscaled weights for fp16 unit rows (mode 2)
   int dbg;  // experiment knob BSC_DBG_W: 1 = no stores, 2 = no label compare (results invalid)
 };
 
@@ -285,7 +287,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
       float ugs_i = 0.f, gsw = 0.f;
       const float* vcol_g = nullptr;
       if (EPI == EPI_WEIGHTS) {
-        gsw = p.gsbuf[16];
+        gsw = p.fold_inv ? p.gsbuf[2 * pair_id(p.pair_a[pair], p.pair_b[pair])] : p.gsbuf[16];
         if (row_ok) {
           inv_i = p.inv[p.pair_a[pair]][p.a_row0 + arow];
           rep_i = p.rep[p.a_row0 + arow];
@@ -326,12 +328,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
         if (EPI == EPI_WEIGHTS) {
           // column facts of the tile: k1 / |b_j|, gs * v_j, label class (the column-sum scratch is free in this mode)
           float* vgb = &tail->cs[0][0][0] + buf * BN;
+          float* wfb = &tail->cs[0][2][0] + buf * BN;
           int* repb = reinterpret_cast<int*>(&tail->cs[1][0][0]) + buf * BN;
           for (int col = grp * GC + et; col < (grp + 1) * GC; col += 128) {
             const int64_t j = col0 + col;
             const bool ok = j < p.b_rows;
             tail->invb[buf][col] = ok ? p.k1 * invb_g[j] : 0.f;
-            vgb[col] = ok ? gsw * vcol_g[j] : 0.f;
+            const float wf = ok ? (p.fold_inv ? invb_g[j] : 1.0f) : 0.f;  // column factor of the weights
+            wfb[col] = wf;
+            vgb[col] = ok ? gsw * vcol_g[j] * wf : 0.f;
             repb[col] = ok ? p.rep[j] : -1;
           }
           ptx::named_bar_sync(2 + 2 * grp, 128);
@@ -386,6 +391,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
             cs[c * 32 + lane] = warp_colsum32(e, lane);
           } else if (EPI == EPI_WEIGHTS) {
             const float* vgb = &tail->cs[0][0][0] + buf * BN + c * 32;
+            const float* wfb = &tail->cs[0][2][0] + buf * BN + c * 32;
             const int* repb = reinterpret_cast<const int*>(&tail->cs[1][0][0]) + buf * BN + c * 32;
             const float m2g = -2.0f * gsw;
             uint32_t pk[16];
@@ -396,8 +402,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
 #pragma unroll
                 for (int z = 0; z < 2; ++z) {
                   const float ex = ptx::ex2(fmaf(__uint_as_float(raw[t + z]), inv_i * ivb[c * 32 + t + z], -p.k2));
-                  const float tv = (repb[t + z] == rep_i) ? m2g : 0.f;
-                  g2[z] = fmaf(ex, ugs_i + vgb[t + z], tv);
+                  const float tv = (repb[t + z] == rep_i) ? m2g * wfb[t + z] : 0.f;
+                  g2[z] = fmaf(ex, fmaf(ugs_i, wfb[t + z], vgb[t + z]), tv);
                 }
                 const __half2 hh = __floats2half2_rn(g2[0], g2[1]);
                 pk[t >> 1] = *reinterpret_cast<const uint32_t*>(&hh);
@@ -409,7 +415,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
 #pragma unroll
                 for (int z = 0; z < 2; ++z) {
                   const float ex = ptx::ex2(fmaf(__uint_as_float(raw[t + z]), inv_i * ivb[c * 32 + t + z], -p.k2));
-                  g2[z] = ex * (ugs_i + vgb[t + z]);
+                  g2[z] = ex * fmaf(ugs_i, wfb[t + z], vgb[t + z]);
                 }
                 const __half2 hh = __floats2half2_rn(g2[0], g2[1]);
                 pk[t >> 1] = *reinterpret_cast<const uint32_t*>(&hh);
@@ -700,8 +706,12 @@ int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaS
   // mode 2: all rows local, one weight block per UNORDERED pair serves both sides.  Mode 3 (several GPUs): this rank's
   // rows of modality a against all rows of b, one block per ORDERED pair (the other side's block lives on other ranks).
   const bool ordered = L.bwd_gstore == 3;
+  // B operand of the gradient GEMMs: fp16 unit rows (mode 2); mode 3 folds 1/|b_j| into the weights and multiplies by the
+  // gathered scaled rows themselves -- no conversion pass, and exact operands for bf16 inputs
   const void* xunit[3] = {nullptr, nullptr, nullptr};
-  {
+  if (ordered) {
+    for (int a = 0; a < 3; ++a) xunit[a] = d->xh[a];
+  } else {
     void* dst[3] = {nullptr, nullptr, nullptr};
     for (int a = 0; a < 3; ++a)
       if (d->xh[a]) xunit[a] = dst[a] = ws + L.xunit + (size_t)a * d->n_global * d->d * 2;
@@ -744,6 +754,7 @@ int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaS
   p.uv = (const float*)(ws + L.uv);
   p.gsbuf = (const float*)(ws + L.gs);
   p.gimg = (uint8_t*)(ws + L.gimg);
+  p.fold_inv = ordered ? 1 : 0;
   tc_bwd_matrix_dims(d, &p.n_iblk_pad, &p.n_j64);
   p.jrange = (const int2*)(ws + L.jrange);
   {

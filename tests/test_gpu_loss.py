@@ -167,6 +167,47 @@ def test_tc16_backward_falls_back_to_recomputing_sweep_above_the_memory_cap(monk
     assert _lib.last_bwd_mode() == 2
 
 
+@pytest.mark.parametrize("n,d,present,labels,shared,world,normalised", [
+    (512, 768, (True, True, True), "multi", 0.5, 2, True),
+    (1024, 768, (True, True, True), "arange", 0.5, 4, True),
+    (768, 512, (True, False, True), "multi", 0.5, 2, True),      # 384 rows per rank: three row blocks, d = 2 x 256
+    (2048, 768, (True, True, True), "multi", 0.5, 8, True),
+    (1024, 768, (True, True, True), "multi", 0.5, 2, False),     # row norms 0.5 .. 2 x sqrt(d): 1/|row| in the weights
+])
+@pytest.mark.parametrize("mode", ["3", "0"])
+def test_tc16_rank_stripes_replayed_on_one_gpu(n, d, present, labels, shared, world, normalised, mode, monkeypatch):
+    """The kernels a rank of a multi-GPU job runs (row stripe x all columns: forward statistics, then the backward
+    from one weight block per ORDERED pair -- mode 3 -- or the recomputing sweep -- mode 0) on ONE GPU: every rank's
+    stripe in turn, statistics summed as the all-reduce would, loss and gradient stripes against the oracle on the
+    whole batch (loss_func.py:122-162: every rank evaluates the global loss, the gradient reaches the local rows)."""
+    from bsc import _lib
+    from bsc.loss import _default_ops
+    from tests.stripe import first_pass, rank_step
+
+    monkeypatch.setenv("BSC_BWD_GSTORE", mode)
+    feats, lab = loss_inputs(n, d, present, seed=n + world, labels=labels, shared=shared, dtype=torch.bfloat16,
+                             normalised=normalised)
+    ref_in = [None if f is None else f.float() for f in feats]
+    ref_loss, ref_grads = loss_oracle.closed_form_grads(ref_in, lab)
+    ops = _default_ops()
+    dev_feats = [None if f is None else f.cuda() for f in ref_in]
+    dev_lab = lab.cuda()
+    nl = n // world
+    stats_sum = first_pass(ops, world, dev_feats, dev_lab)
+    grads = [None if f is None else torch.empty_like(f) for f in dev_feats]
+    losses = []
+    for r in range(world):
+        loss, leaves = rank_step(ops, r, world, dev_feats, dev_lab, stats_sum)
+        assert _lib.last_bwd_mode() == int(mode)
+        losses.append(float(loss))
+        for g, l in zip(grads, leaves):
+            if g is not None:
+                g[r * nl:(r + 1) * nl] = l.grad
+    torch.cuda.synchronize()
+    assert all(x == losses[0] for x in losses)  # every rank reports the loss of the global batch, same bits
+    _compare(losses[0], [None if g is None else g.cpu() for g in grads], ref_loss, ref_grads, TC16_TOL)
+
+
 def test_tc16_unnormalised_rows_of_mixed_scale():
     """Rows whose norms span 0.05 .. 40: the inverse norms live in the fp32 epilogue and in the weight tile."""
     feats, lab = loss_inputs(640, 768, seed=77, labels="multi", normalised=False, dtype=torch.bfloat16)

@@ -1,0 +1,39 @@
+"""Kernel times of ONE rank's share of the bench workload, replayed on one GPU (rank 0 of W at N = 32768): what a rank of
+a W-GPU job spends in the library's forward and backward, without the exchange.
+    python tools/stripe_step.py [world] [n] [steps]      (BSC_BWD_GSTORE=0/3 selects the backward)"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "bioscan-clip_b200"))
+import torch  # noqa: E402
+
+import bench  # noqa: E402
+from bsc import _lib  # noqa: E402
+from bsc.loss import _default_ops  # noqa: E402
+from tests.stripe import first_pass, rank_step  # noqa: E402
+
+world = int(sys.argv[1]) if len(sys.argv) > 1 else 2
+n = int(sys.argv[2]) if len(sys.argv) > 2 else 32768
+steps = int(sys.argv[3]) if len(sys.argv) > 3 else 5
+torch.cuda.set_device(0)
+dev = torch.device("cuda", 0)
+feats, labels = bench.synth_loss_rows(torch, n, 0, n, dev, torch.bfloat16)
+ops = _default_ops()
+stats = first_pass(ops, world, feats, labels, bench.SCALE)
+_lib.set_timing(True)
+f, b, w = [], [], []
+for k in range(2 + steps):
+    t0 = torch.cuda.Event(enable_timing=True)
+    t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    loss, _ = rank_step(ops, 0, world, feats, labels, stats, bench.SCALE)
+    t1.record()
+    torch.cuda.synchronize()
+    if k >= 2:
+        f.append(_lib.last_kernel_ms(0))
+        b.append(_lib.last_kernel_ms(1))
+        w.append(t0.elapsed_time(t1))
+print("world %d n %d mode %d loss %.6f fwd_ms %.3f bwd_ms %.3f step_ms %.3f (step includes the stand-in gather)" % (
+    world, n, _lib.last_bwd_mode(), float(loss), sum(f) / len(f), sum(b) / len(b), sum(w) / len(w)))
