@@ -3,6 +3,8 @@
 // All of them are HBM- or latency-bound; none touches an N x N float matrix.
 #include "common.cuh"
 
+#include <cooperative_groups.h>
+
 namespace bsc {
 
 template <typename T>
@@ -502,27 +504,51 @@ int rep_range_launch(const int32_t* rep, int64_t n, int tile, int2* out, cudaStr
   return BSC_OK;
 }
 
-// Deterministic single-block sum (double accumulation, fixed order) of nparts rows of n floats:
-// out[0] = scale * sum_p sum_{i<n} part[p*stride + i].
-__global__ void __launch_bounds__(1024) sum_rows_kernel(const float* __restrict__ part, int nparts,
-                                                        int64_t part_stride, int64_t n, float scale,
-                                                        float* __restrict__ out) {
-  __shared__ double sh[1024];
-  double acc = 0.0;
-  for (int p = 0; p < nparts; ++p)
-    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) acc += (double)part[p * part_stride + i];
+// Scalar reductions run on ONE cluster of 8 CTAs x 1024 threads (a single block spent 34 - 56 us streaming N-sized
+// vectors, a fixed cost of every step however many ranks share the batch).  Every thread accumulates a fixed subset in
+// double, every CTA tree-reduces in shared memory and stores its partial into CTA 0's shared memory over DSMEM; CTA 0
+// adds the 8 partials in rank order: the result does not depend on scheduling.
+constexpr int kRedCtas = 8;
+
+__device__ __forceinline__ double cluster_sum_to_cta0(double acc, double* sh /*[1024]*/, double* slots /*[kRedCtas]*/) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
   sh[threadIdx.x] = acc;
   __syncthreads();
   for (int s = 512; s > 0; s >>= 1) {
     if ((int)threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
     __syncthreads();
   }
-  if (threadIdx.x == 0) out[0] = (float)((double)scale * sh[0]);
+  if (threadIdx.x == 0) cluster.map_shared_rank(slots, 0)[cluster.block_rank()] = sh[0];
+  cluster.sync();
+  double total = 0.0;
+  if (cluster.block_rank() == 0 && threadIdx.x == 0)
+    for (int c = 0; c < kRedCtas; ++c) total += slots[c];
+  return total;  // meaningful in thread 0 of CTA 0
+}
+
+// out[0] = scale * sum_p sum_{i<n} part[p*stride + i]  (double accumulation, fixed order).
+__global__ void __cluster_dims__(kRedCtas, 1, 1) __launch_bounds__(1024)
+    sum_rows_kernel(const float* __restrict__ part, int nparts, int64_t part_stride, int64_t n, float scale,
+                    float* __restrict__ out) {
+  __shared__ double sh[1024];
+  __shared__ double slots[kRedCtas];
+  double acc = 0.0;
+  // work items = (part row, 1024-column chunk), dealt round-robin to the CTAs
+  const int64_t nchunk = (n + 1023) / 1024;
+  const int64_t items = (int64_t)nparts * nchunk;
+#pragma unroll 4
+  for (int64_t q = blockIdx.x; q < items; q += kRedCtas) {
+    const int64_t p = q / nchunk, i = (q - p * nchunk) * 1024 + threadIdx.x;
+    if (i < n) acc += (double)part[p * part_stride + i];
+  }
+  const double total = cluster_sum_to_cta0(acc, sh, slots);
+  if (blockIdx.x == 0 && threadIdx.x == 0) out[0] = (float)((double)scale * total);
 }
 
 int sum_rows_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float scale, float* out,
                     cudaStream_t st) {
-  sum_rows_kernel<<<1, 1024, 0, st>>>(part, nparts, part_stride, n, scale, out);
+  sum_rows_kernel<<<kRedCtas, 1024, 0, st>>>(part, nparts, part_stride, n, scale, out);
   BSC_LAUNCH_CHECK("sum_rows_kernel");
   return BSC_OK;
 }
@@ -571,12 +597,13 @@ int reduce_parts_launch(const float* part, int nparts, int64_t part_stride, int6
 // ---------------------------------------------------------------------------------------------
 // Loss scalar (loss_func.py:54).  With a_ij = s*S_ij - s and sumexp_i = sum_j exp(a_ij):
 //   L = c * [ sum over ordered pairs sum_i r_i log(sumexp_i)  -  2 * sum over unordered pairs sum_ij T_ij a_ij ],
-// c = 1 / (N * M(M-1))  (r_i*s cancels against the s inside a_ij).  Single block, double accumulation, fixed order.
+// c = 1 / (N * M(M-1))  (r_i*s cancels against the s inside a_ij).  One cluster, double accumulation, fixed order.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) loss_kernel(const float* __restrict__ stats, const float* __restrict__ r,
-                                                    int64_t n, unsigned present_mask, float scale,
-                                                    float* __restrict__ loss) {
+__global__ void __cluster_dims__(kRedCtas, 1, 1) __launch_bounds__(1024)
+    loss_kernel(const float* __restrict__ stats, const float* __restrict__ r, int64_t n, unsigned present_mask,
+                float scale, float* __restrict__ loss) {
   __shared__ double sh[1024];
+  __shared__ double slots[kRedCtas];
   double acc = 0.0;
   int m = 0;
   for (int a = 0; a < 3; ++a) m += (present_mask >> a) & 1;
@@ -585,49 +612,55 @@ __global__ void __launch_bounds__(1024) loss_kernel(const float* __restrict__ st
     for (int b = 0; b < 3; ++b) {
       if (b == a || !((present_mask >> b) & 1)) continue;
       const float* se = stats + (int64_t)pair_id(a, b) * n;
-#pragma unroll 8  // the loads of 8 iterations in flight; the double additions keep their order
-      for (int64_t i = threadIdx.x; i < n; i += blockDim.x)
+#pragma unroll 4  // the loads of 4 iterations in flight; the double additions keep their order
+      for (int64_t i = (int64_t)blockIdx.x * 1024 + threadIdx.x; i < n; i += kRedCtas * 1024)
         acc += (double)r[i] * (double)logf(se[i]);
     }
   }
-  sh[threadIdx.x] = acc;
-  __syncthreads();
-  for (int s = 512; s > 0; s >>= 1) {
-    if ((int)threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) {
+  const double total = cluster_sum_to_cta0(acc, sh, slots);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
     const double pos = (double)stats[6 * n];
     const double c = 1.0 / ((double)n * m * (m - 1));
-    loss[0] = (float)(c * (sh[0] - 2.0 * pos));
+    loss[0] = (float)(c * (total - 2.0 * pos));
     (void)scale;
   }
 }
 
 int loss_launch(const float* stats, const float* r, int64_t n, unsigned present_mask, float scale, float* loss,
                 cudaStream_t st) {
-  loss_kernel<<<1, 1024, 0, st>>>(stats, r, n, present_mask, scale, loss);
+  loss_kernel<<<kRedCtas, 1024, 0, st>>>(stats, r, n, present_mask, scale, loss);
   BSC_LAUNCH_CHECK("loss_kernel");
   return BSC_OK;
 }
 
-// Largest inverse row norm of every present modality (grid = 3 blocks): bounds the fp16 range of the
-// gradient-weight tile in TC16 mode, where 1/||y_j|| is folded into the weights.
-__global__ void __launch_bounds__(256) invmax_kernel(const float* __restrict__ i0, const float* __restrict__ i1,
-                                                     const float* __restrict__ i2, int64_t n,
-                                                     float* __restrict__ out) {
+// Largest inverse row norm of every present modality (one cluster of 8 CTAs per modality; max is order-free): bounds
+// the fp16 range of the gradient-weight tile in TC16 mode, where 1/||y_j|| is folded into the weights.
+__global__ void __cluster_dims__(kRedCtas, 1, 1) __launch_bounds__(256)
+    invmax_kernel(const float* __restrict__ i0, const float* __restrict__ i1, const float* __restrict__ i2, int64_t n,
+                  float* __restrict__ out) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
   __shared__ float sh[8];
-  const float* src = blockIdx.x == 0 ? i0 : (blockIdx.x == 1 ? i1 : i2);
+  __shared__ float slots[kRedCtas];
+  const float* src = blockIdx.y == 0 ? i0 : (blockIdx.y == 1 ? i1 : i2);
   float m = 0.f;
-  if (src != nullptr)
-    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) m = fmaxf(m, src[i]);
+  if (src != nullptr) {
+#pragma unroll 4
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += kRedCtas * 256) m = fmaxf(m, src[i]);
+  }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
   if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = m;
   __syncthreads();
   if (threadIdx.x == 0) {
     for (int w = 1; w < 8; ++w) m = fmaxf(m, sh[w]);
-    out[blockIdx.x] = src != nullptr ? m : 1.0f;
+    cluster.map_shared_rank(slots, 0)[cluster.block_rank()] = m;
+  }
+  cluster.sync();
+  if (cluster.block_rank() == 0 && threadIdx.x == 0) {
+    float t = slots[0];
+    for (int c = 1; c < kRedCtas; ++c) t = fmaxf(t, slots[c]);
+    out[blockIdx.y] = src != nullptr ? t : 1.0f;
   }
 }
 
@@ -663,7 +696,7 @@ __global__ void __launch_bounds__(256) uv_kernel(const float* __restrict__ stats
 
 int uv_launch(const float* stats, const float* r, int64_t n, const float* rmax, const float* const* inv, int use_gs,
               float* uv, float* gsbuf, float* invmax, cudaStream_t st) {
-  invmax_kernel<<<3, 256, 0, st>>>(use_gs ? inv[0] : nullptr, use_gs ? inv[1] : nullptr, use_gs ? inv[2] : nullptr, n,
+  invmax_kernel<<<dim3(kRedCtas, 3), 256, 0, st>>>(use_gs ? inv[0] : nullptr, use_gs ? inv[1] : nullptr, use_gs ? inv[2] : nullptr, n,
                                    invmax);
   BSC_LAUNCH_CHECK("invmax_kernel");
   uv_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(stats, r, n, rmax, invmax, use_gs, uv, gsbuf);
@@ -734,15 +767,160 @@ __global__ void __launch_bounds__(256) combine_kernel(CombineArgs a) {
   }
 }
 
+// Four consecutive columns per lane, 16- / 8-byte accesses.
+template <typename T>
+__device__ __forceinline__ void load4(const T* p, float (&o)[4]);
+template <>
+__device__ __forceinline__ void load4<float>(const float* p, float (&o)[4]) {
+  const float4 v = *reinterpret_cast<const float4*>(p);
+  o[0] = v.x, o[1] = v.y, o[2] = v.z, o[3] = v.w;
+}
+template <>
+__device__ __forceinline__ void load4<__nv_bfloat16>(const __nv_bfloat16* p, float (&o)[4]) {
+  const uint2 v = *reinterpret_cast<const uint2*>(p);
+  o[0] = __uint_as_float(v.x << 16), o[1] = __uint_as_float(v.x & 0xffff0000u);
+  o[2] = __uint_as_float(v.y << 16), o[3] = __uint_as_float(v.y & 0xffff0000u);
+}
+template <>
+__device__ __forceinline__ void load4<__half>(const __half* p, float (&o)[4]) {
+  const uint2 v = *reinterpret_cast<const uint2*>(p);
+  const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&v.x));
+  const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
+  o[0] = a.x, o[1] = a.y, o[2] = b.x, o[3] = b.y;
+}
+template <typename T>
+__device__ __forceinline__ void store4(T* p, const float (&o)[4]);
+template <>
+__device__ __forceinline__ void store4<float>(float* p, const float (&o)[4]) {
+  *reinterpret_cast<float4*>(p) = make_float4(o[0], o[1], o[2], o[3]);
+}
+template <>
+__device__ __forceinline__ void store4<__nv_bfloat16>(__nv_bfloat16* p, const float (&o)[4]) {
+  const __nv_bfloat162 a = __floats2bfloat162_rn(o[0], o[1]), b = __floats2bfloat162_rn(o[2], o[3]);
+  *reinterpret_cast<uint2*>(p) =
+      make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+}
+template <>
+__device__ __forceinline__ void store4<__half>(__half* p, const float (&o)[4]) {
+  const __half2 a = __floats2half2_rn(o[0], o[1]), b = __floats2half2_rn(o[2], o[3]);
+  *reinterpret_cast<uint2*>(p) =
+      make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+}
+
+// Same arithmetic for d % 128 == 0, d <= 128 * NV and 4-element-aligned rows: the row and its raw gradient stay in
+// registers (each read ONCE, all loads of a row in flight together) -- the per-column version above is bound by the
+// latency of its 4-byte loads (0.36 ms for 4096 rows x 3 modalities with 4 partial sums; 8 % of a step on 8 GPUs).
+template <typename T, int NV>
+__global__ void __launch_bounds__(256) combine_rows4_kernel(CombineArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t il = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int m = blockIdx.y;
+  if (il >= a.n_local || a.x[m] == nullptr) return;
+  int mcount = 0;
+  for (int q = 0; q < 3; ++q) mcount += (a.present_mask >> q) & 1;
+  const float c = 1.0f / ((float)a.n_global * (float)(mcount * (mcount - 1)));
+  const float cs = c * a.scale;
+  float inv_gs[2] = {0.f, 0.f};
+  {
+    int slot = 0;
+    for (int y = 0; y < 3; ++y)
+      if (y != m && ((a.present_mask >> y) & 1)) inv_gs[slot++] = a.gsbuf[2 * pair_id(m, y) + 1];
+  }
+  const float gout = a.grad_out[0];
+  const T* xr = (const T*)a.x[m] + il * a.ldx + lane * 4;
+  T* gr = (T*)a.grad[m] + il * a.ldx + lane * 4;
+  const int64_t part_stride = a.n_local * (int64_t)a.d;
+  const float* raw0 = a.raw[m] + il * (int64_t)a.d + lane * 4;
+  const float* raw1 = raw0 + a.n_parts * part_stride;
+  const int nv = a.d >> 7;
+
+  float x[NV][4], g[NV][4];
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+    if (v < nv) load4<T>(xr + v * 128, x[v]);
+#pragma unroll
+  for (int v = 0; v < NV; ++v) {
+    if (v >= nv) continue;
+    float s0[4], s1[4] = {0.f, 0.f, 0.f, 0.f};
+    load4<float>(raw0 + v * 128, s0);
+    for (int q = 1; q < a.n_parts; ++q) {  // fixed order: deterministic
+      float t[4];
+      load4<float>(raw0 + q * part_stride + v * 128, t);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) s0[e] += t[e];
+    }
+    if (a.n_slots > 1) {
+      load4<float>(raw1 + v * 128, s1);
+      for (int q = 1; q < a.n_parts; ++q) {
+        float t[4];
+        load4<float>(raw1 + q * part_stride + v * 128, t);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) s1[e] += t[e];
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) g[v][e] = cs * fmaf(s1[e], inv_gs[1], s0[e] * inv_gs[0]);
+  }
+  float ss = 0.f;
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+    if (v < nv)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) ss = fmaf(x[v][e], x[v][e], ss);
+  ss = warp_sum(ss);
+  const float nrm = sqrtf(ss);
+  const bool clamped = nrm < 1e-12f;
+  const float inv = 1.0f / fmaxf(nrm, 1e-12f);
+  float dot = 0.f;
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+    if (v < nv)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) dot = fmaf(x[v][e] * inv, g[v][e], dot);
+  dot = warp_sum(dot);
+  if (clamped) dot = 0.f;
+#pragma unroll
+  for (int v = 0; v < NV; ++v) {
+    if (v >= nv) continue;
+    float o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) o[e] = gout * inv * (g[v][e] - x[v][e] * inv * dot);
+    store4<T>(gr + v * 128, o);
+  }
+}
+
+template <typename T>
+static bool combine_rows4_ok(const CombineArgs& a) {
+  if (a.d % 128 != 0 || a.d > 1024 || a.ldx % 4 != 0) return false;
+  for (int m = 0; m < 3; ++m) {
+    if (a.x[m] == nullptr) continue;
+    if (((uintptr_t)a.x[m] | (uintptr_t)a.grad[m]) % (4 * sizeof(T)) != 0 || (uintptr_t)a.raw[m] % 16 != 0) return false;
+  }
+  return true;
+}
+
+template <typename T>
+static void combine_dispatch(const CombineArgs& a, dim3 grid, cudaStream_t st) {
+  if (combine_rows4_ok<T>(a)) {
+    if (a.d <= 512)
+      combine_rows4_kernel<T, 4><<<grid, 256, 0, st>>>(a);
+    else if (a.d <= 768)
+      combine_rows4_kernel<T, 6><<<grid, 256, 0, st>>>(a);
+    else
+      combine_rows4_kernel<T, 8><<<grid, 256, 0, st>>>(a);
+  } else
+    combine_kernel<T><<<grid, 256, 0, st>>>(a);
+}
+
 int combine_launch(const CombineArgs& a, int x_dtype, cudaStream_t st) {
   if (a.n_local == 0) return BSC_OK;
   dim3 grid((unsigned)((a.n_local + 7) / 8), 3);
   if (x_dtype == BSC_F32)
-    combine_kernel<float><<<grid, 256, 0, st>>>(a);
+    combine_dispatch<float>(a, grid, st);
   else if (x_dtype == BSC_BF16)
-    combine_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(a);
+    combine_dispatch<__nv_bfloat16>(a, grid, st);
   else if (x_dtype == BSC_F16)
-    combine_kernel<__half><<<grid, 256, 0, st>>>(a);
+    combine_dispatch<__half>(a, grid, st);
   else {
     set_error("bsc_infonce_bwd: unknown x_dtype %d", x_dtype);
     return BSC_EINVAL;

@@ -3,6 +3,7 @@ a W-GPU job spends in the library's forward and backward, without the exchange.
     python tools/stripe_step.py [world] [n] [steps]      (BSC_BWD_GSTORE=0/3 selects the backward)"""
 import os
 import sys
+import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -23,17 +24,20 @@ feats, labels = bench.synth_loss_rows(torch, n, 0, n, dev, torch.bfloat16)
 ops = _default_ops()
 stats = first_pass(ops, world, feats, labels, bench.SCALE)
 _lib.set_timing(True)
-f, b, w = [], [], []
+f, b, w, h = [], [], [], []
 for k in range(2 + steps):
     t0 = torch.cuda.Event(enable_timing=True)
     t1 = torch.cuda.Event(enable_timing=True)
     t0.record()
+    c0 = time.perf_counter()
     loss, _ = rank_step(ops, 0, world, feats, labels, stats, bench.SCALE)
+    h1 = time.perf_counter() - c0  # host time to queue the step
     t1.record()
     torch.cuda.synchronize()
     if k >= 2:
         f.append(_lib.last_kernel_ms(0))
         b.append(_lib.last_kernel_ms(1))
         w.append(t0.elapsed_time(t1))
-print("world %d n %d mode %d loss %.6f fwd_ms %.3f bwd_ms %.3f step_ms %.3f (step includes the stand-in gather)" % (
-    world, n, _lib.last_bwd_mode(), float(loss), sum(f) / len(f), sum(b) / len(b), sum(w) / len(w)))
+        h.append(h1 * 1e3)
+print("world %d n %d mode %d loss %.6f fwd_ms %.3f bwd_ms %.3f step_ms %.3f host_ms %.3f (step includes the stand-in gather)" % (
+    world, n, _lib.last_bwd_mode(), float(loss), sum(f) / len(f), sum(b) / len(b), sum(w) / len(w), sum(h) / len(h)))
