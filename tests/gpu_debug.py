@@ -1,5 +1,5 @@
 """Bring-up helper run on the GPU box: each stage in its own process so one fault does not hide the rest.
-Writes a readable log to gpurun_out/debug_*.log.  Not part of the product or the tests."""
+Writes a readable log to gpurun_out/debug_*.log.  A checker like the tests (it calls the oracle), hence kept under tests/; not collected by pytest."""
 import os
 import subprocess
 import sys
