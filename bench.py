@@ -206,7 +206,7 @@ def run_reference(args):
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -468,7 +468,7 @@ def run_native(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_loss_baseline(CPU_SAMPLE_N)
     if rank == 0:
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -580,8 +580,30 @@ def bench_retrieval(args, torch, dist, bsc, _lib, device, rank, world, peaks):
     return res
 
 
+_JSON_FD = None
+
+
+def _stdout_for_json_only():
+    """Libraries write to file descriptor 1 behind Python's back (NCCL prints its version banner there when the box
+    sets NCCL_DEBUG): everything but the result line goes to stderr, so that stdout holds exactly ONE JSON line."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
     args = parse_args()
+    _stdout_for_json_only()
     if args.impl == "reference":
         run_reference(args)
     else:

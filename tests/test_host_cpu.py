@@ -121,3 +121,22 @@ def test_extracted_feature_container_round_trip(tmp_path):
     assert k2["all_key_features_label"] == keys["label_list"] * 3
     import json
     assert set(json.load(open(labels))) == {"seen_gt_dict", "unseen_gt_dict", "key_gt_dict"}
+
+
+def test_bench_reference_arm_prints_exactly_one_json_line():
+    """bench.py contract: stdout is ONE JSON line (library chatter on fd 1 is routed to stderr); the reference arm
+    runs on the host cores without a GPU."""
+    import json
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1",
+                        "--warmup", "0"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1, r.stdout[:500]
+    line = json.loads(lines[0])
+    assert line["impl"] == "reference" and line["cpu_baseline"]["kind"] == "port"
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "e2e"):
+        assert key in line
