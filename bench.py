@@ -279,8 +279,8 @@ def run_native(args):
             dist.barrier()
         w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         w0.record()
-        step_resident()
-        w1.record()
+        loss, leaves = step_resident()  # held across the next step as in the timed loop: the caching allocator reaches
+        w1.record()                     # its steady state here (a cudaMalloc in timed step 1 cost 0.7-0.9 ms at 4-8 GPUs)
         w1.synchronize()
         w0.elapsed_time(w1)
         for which in (0, 1, 3):
@@ -379,7 +379,9 @@ def run_native(args):
         return keep
 
     e2e_steps = max(10, min(args.steps, 40))
-    run_e2e(3)
+    # warm-up with the SAME number of steps: run_e2e keeps every step's gradients alive until the end, so a shorter
+    # warm-up would leave the timed run allocating fresh device memory (cudaMalloc stalls the launch queue) in most steps
+    run_e2e(e2e_steps)
     barrier()
     a, b_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
