@@ -35,6 +35,16 @@ def test_library_exports_every_declared_symbol(built_lib):
     assert set(_lib.EXPORTS) == declared
 
 
+def test_every_entry_point_is_documented_for_the_reference_maintainer():
+    """INTEGRATION.md names every entry point of include/bsc_hot.h (with the reference lines it stands in for)."""
+    header = open(os.path.join(ROOT, "include", "bsc_hot.h")).read()
+    declared = set(re.findall(r"^\s*(?:const\s+)?[a-z_0-9]+\*?\s+\*?(bsc_[a-z0-9_]+)\s*\(", header, re.M))
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    missing = sorted(n for n in declared if f"`{n}`" not in doc and f"`{n}(" not in doc and n not in doc)
+    assert not missing, missing
+    assert "loss_func.py" in header and "inference_and_eval.py" in header  # the header cites the reference
+
+
 def test_sass_contains_blackwell_tensor_and_tma_ops(built_lib):
     out = subprocess.run(["cuobjdump", "-sass", built_lib], capture_output=True, text=True).stdout
     assert "UTCHMMA" in out, "tcgen05.mma missing from the SASS"
