@@ -406,24 +406,20 @@ def run_native(args):
     rev_avg = sum(rev_ms) / len(rev_ms) if rev_ms and min(rev_ms) > 0 else None
     bwd_mode = _lib.last_bwd_mode()
     # Algorithmic work: one forward GEMM + two gradient GEMMs per unordered pair, 3 pairs = 18 n N D per
-    # step; recomputing S in the backward is NOT counted.  Which kernel forms the gradient GEMMs depends on the mode:
-    #   0 (several GPUs) tc_bwd_duo_kernel recomputes S per ordered pair and forms both GEMMs of a pair: 12 n N D.
-    #   1 tc_bwd_duo_kernel per unordered pair: one GEMM per pair (6 n N D), tc_bwd_rev_kernel the other (6 n N D).
-    #   2 (one GPU, default) tc_sim_kernel<EPI_WEIGHTS> writes the weight matrix (0 algorithmic, executes 6 n N D),
-    #     tc_bwd_rev_kernel forms both GEMMs of every pair from it: 12 n N D -- the dominant kernel.
-    #   3 (several GPUs, default) the same two kernels per ORDERED pair on this rank's rows: weights execute 12 n N D,
-    #     the GEMMs 12 n N D (all algorithmic).
+    # step; recomputing S in the backward is NOT counted.  Which kernel forms the gradient GEMMs depends on the strategy
+    # (include/bsc_hot.h BSC_BWD_*):
+    #   4 scatter (default): tc_sim_kernel<EPI_WEIGHTS> writes one weight block per UNORDERED pair (0 algorithmic,
+    #     executes 6 n N D), tc_bwd_rev_kernel forms both GEMMs of every pair from it (12 n N D, all algorithmic; its
+    #     epilogue stores the partial sums of the other ranks' rows into their exchange buffers) -- the dominant kernel.
+    #   3 blocks (ranks without peer memory): one block per ORDERED pair (executes 12 n N D), the GEMMs 12 n N D.
+    #   0 recompute: tc_bwd_duo_kernel recomputes S per ordered pair and forms both GEMMs: 12 n N D of 24 executed.
     unit = float(n_local) * n_global * DIM
     fwd_flops = 6.0 * unit
     roofline = None
     if bwd_avg:
-        if bwd_mode in (2, 3) and rev_avg:
+        if bwd_mode in (3, 4) and rev_avg:
             kernel, k_ms, k_flops, k_exec = "tc_bwd_rev_kernel", rev_avg, 12.0 * unit, 12.0 * unit
-            # r1_bwd_gemms.txt: dram__bytes_read.sum + dram__bytes_write.sum of one launch
             traffic = TRAFFIC_GEMMS if (world == 1 and n_global == 32768) else None
-        elif bwd_mode == 1 and rev_avg:
-            kernel, k_ms, k_flops, k_exec = "tc_bwd_duo_kernel", bwd_avg, 6.0 * unit, 12.0 * unit
-            traffic = 8.566e9 if (world == 1 and n_global == 32768) else None
         else:
             kernel, k_ms, k_flops, k_exec = "tc_bwd_duo_kernel", bwd_avg, 12.0 * unit, 24.0 * unit
             traffic = 2.164e9 if (world == 1 and n_global == 32768) else None  # profiles/r1_bwd_duo.txt

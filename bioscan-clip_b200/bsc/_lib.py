@@ -16,13 +16,16 @@ LIB_PATH = os.environ.get("BSC_LIB_PATH") or os.path.join(_HERE, "libbsc_hot.so"
 
 BSC_F32, BSC_BF16, BSC_F16 = 0, 1, 2
 MODE_F32, MODE_TC16 = 0, 1
+BWD_AUTO, BWD_RECOMPUTE, BWD_BLOCKS, BWD_SCATTER = -1, 0, 3, 4
+BWD_NAMES = {"auto": BWD_AUTO, "recompute": BWD_RECOMPUTE, "blocks": BWD_BLOCKS, "scatter": BWD_SCATTER}
+ABI_VERSION = 200
 NORM_TORCH, NORM_SKLEARN = 0, 1
 
 EXPORTS = [
     "bsc_version", "bsc_last_error", "bsc_device_check", "bsc_l2norm_fwd", "bsc_rows_to_f16", "bsc_label_stats", "bsc_label_stats_workspace_bytes",
     "bsc_gather_layout", "bsc_gather_push",
-    "bsc_infonce_stats_len", "bsc_infonce_workspace_bytes", "bsc_infonce_fwd", "bsc_infonce_loss",
-    "bsc_infonce_bwd", "bsc_bank_search_workspace_bytes", "bsc_bank_search", "bsc_bank_screen_parts", "bsc_bank_screen", "bsc_bank_rescore", "bsc_topk_merge", "bsc_taxonomy_eval",
+    "bsc_infonce_stats_len", "bsc_infonce_plan", "bsc_infonce_fwd", "bsc_infonce_loss",
+    "bsc_infonce_bwd_partials", "bsc_infonce_bwd_finish", "bsc_bank_search_workspace_bytes", "bsc_bank_search", "bsc_bank_screen_parts", "bsc_bank_screen", "bsc_bank_rescore", "bsc_topk_merge", "bsc_taxonomy_eval",
     "bsc_set_timing", "bsc_last_kernel_ms", "bsc_launch_count", "bsc_last_bwd_mode",
 ]
 
@@ -36,7 +39,13 @@ class InfoNceDesc(ctypes.Structure):
         ("n_global", c_int64), ("n_local", c_int64), ("row0", c_int64),
         ("d", c_int32), ("mode", c_int32), ("logit_scale", c_float), ("x16_dtype", c_int32),
         ("xh", c_void_p * 3), ("inv", c_void_p * 3), ("r", c_void_p), ("rep", c_void_p), ("next", c_void_p), ("rmax", c_void_p),
+        ("bwd_mode", c_int32), ("world", c_int32), ("rank", c_int32), ("reserved", c_int32),
     ]
+
+
+class InfoNcePlan(ctypes.Structure):
+    _fields_ = [("bwd_mode", c_int32), ("reserved", c_int32), ("fwd_workspace_bytes", c_size_t),
+                ("bwd_workspace_bytes", c_size_t), ("exchange_bytes", c_size_t)]
 
 
 _lib = None
@@ -73,11 +82,13 @@ def lib():
                                   POINTER(c_void_p), c_int, c_void_p]
     L.bsc_infonce_stats_len.argtypes = [c_int64]
     L.bsc_infonce_stats_len.restype = c_int64
-    L.bsc_infonce_workspace_bytes.argtypes = [POINTER(InfoNceDesc), POINTER(c_size_t)]
+    L.bsc_infonce_plan.argtypes = [POINTER(InfoNceDesc), c_int, c_int, c_size_t, POINTER(InfoNcePlan)]
     L.bsc_infonce_fwd.argtypes = [POINTER(InfoNceDesc), c_void_p, c_void_p, c_size_t, c_void_p]
     L.bsc_infonce_loss.argtypes = [POINTER(InfoNceDesc), c_void_p, c_void_p, c_void_p]
-    L.bsc_infonce_bwd.argtypes = [POINTER(InfoNceDesc), c_void_p, POINTER(c_void_p), c_int, c_int64, c_void_p,
-                                  POINTER(c_void_p), c_void_p, c_size_t, c_void_p]
+    L.bsc_infonce_bwd_partials.argtypes = [POINTER(InfoNceDesc), c_void_p, POINTER(c_void_p), c_void_p, c_size_t,
+                                           c_void_p]
+    L.bsc_infonce_bwd_finish.argtypes = [POINTER(InfoNceDesc), POINTER(c_void_p), c_int, POINTER(c_int64), c_void_p,
+                                         POINTER(c_void_p), c_void_p, c_void_p, c_size_t, c_void_p]
     L.bsc_bank_search_workspace_bytes.argtypes = [c_int64, c_int64, c_int, c_int, c_int, POINTER(c_size_t)]
     L.bsc_bank_search.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int64, c_int, c_void_p,
                                   c_void_p, c_void_p, c_size_t, c_void_p]

@@ -23,15 +23,16 @@ import torch
 import torch.nn as nn
 
 from ._lib import MODE_F32, MODE_TC16
-from .ops import Problem
+from .ops import Problem, requested_bwd_mode
 
 TOO_FEW = "Too less element for calculating the contrastive loss."  # loss_func.py:35,142
 
 
 class LocalComm:
-    """world_size == 1: no exchange."""
+    """world_size == 1: no exchange; the scatter strategy's exchange buffer is ordinary device memory."""
     rank = 0
     world_size = 1
+    peer_memory = True
 
     def all_gather_rows(self, t: torch.Tensor) -> torch.Tensor:
         return t
@@ -39,9 +40,18 @@ class LocalComm:
     def all_reduce_sum(self, t: torch.Tensor) -> torch.Tensor:
         return t
 
+    def exchange(self, nbytes: int, device):
+        buf = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=device)
+        return buf, [buf.data_ptr()]
+
+    def exchange_barrier(self, device) -> None:
+        return None
+
 
 class TorchDistComm:
-    """torch.distributed plumbing (NCCL on the GPU box, gloo in the CPU tests)."""
+    """torch.distributed plumbing (NCCL on the GPU box, gloo in the CPU tests).  No peer-mapped memory: the backward
+    uses the strategy that needs no exchange (weight blocks per ordered pair)."""
+    peer_memory = False
 
     def __init__(self, rank: int, world_size: int, group=None):
         import torch.distributed as dist
@@ -62,50 +72,91 @@ class TorchDistComm:
 
 
 class SymmMemComm(TorchDistComm):
-    """TorchDistComm whose TC16 gather is ONE kernel over NVLink peer memory instead of seven NCCL calls.
+    """TorchDistComm over NVLink peer memory (torch symmetric memory, one node):
 
-    Every rank owns two buffers of ``bsc_gather_layout`` bytes in torch symmetric memory (mapped into all ranks of
-    the node).  ``bsc_gather_push`` prepares the fp16 operands and stores each local row -- fp16 values, scale,
-    label -- into every rank's buffer; a symmetric-memory barrier on the stream follows.  The two buffers alternate
-    by step: a rank only starts pushing step k+2 after the barrier of step k+1, which every rank passes after its
-    step-k kernels (same stream), so no rank still reads the buffer being overwritten.
-    """
+    * the TC16 gather is ONE kernel: ``bsc_gather_push`` prepares the fp16 operands and stores each local row -- fp16
+      values, scale, label -- into every rank's buffer, then a symmetric-memory barrier on the stream.  Two buffers
+      alternate by forward: a rank starts pushing forward k+2 only after the barrier of forward k+1, which every rank
+      passes after its forward-k kernels.  A problem whose backward is still outstanding when its buffer is about to
+      be reused (two forwards before one backward, evaluation forwards in between) is moved to private copies first.
+    * the scatter backward's exchange buffers (``bsc_infonce_bwd_partials`` stores partial gradients straight into the
+      owners' buffers) live there too, two alternating by backward, with one barrier between the two phases.
 
-    def __init__(self, rank: int, world_size: int, group=None):
+    ``strict=False`` ('auto'): if the set-up fails on ANY rank all ranks agree (one all_reduce at set-up time) to
+    continue on plain NCCL collectives; ``strict=True`` ('on') raises instead."""
+    MAX_SHAPES = 2  # symmetric allocations are never returned to a pool: keep the cache of shapes small
+
+    def __init__(self, rank: int, world_size: int, group=None, strict: bool = False):
         super().__init__(rank, world_size, group)
-        self._state = {}
+        self.strict = strict
+        self.disabled = False
+        self._gather = {}     # (n_global, d, device) -> state
+        self._exchange = {}   # (nbytes, device) -> state
 
-    def _setup(self, n_global: int, d: int, device):
-        import ctypes
+    @property
+    def peer_memory(self) -> bool:
+        return not self.disabled and self.world_size <= 16
+
+    # -- set-up with a collective verdict ---------------------------------------------------------
+    def _agree(self, ok: bool, device) -> bool:
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=device)
+        self.dist.all_reduce(flag, op=self.dist.ReduceOp.MIN, group=self.group)
+        return bool(int(flag.item()))
+
+    def _symm_buffers(self, nbytes: int, device, count: int):
+        """``count`` symmetric uint8 buffers of nbytes, rendezvoused; None when any rank failed (non-strict)."""
+        import warnings
 
         import torch.distributed._symmetric_memory as symm
 
-        from . import _lib
-
-        offx, offi = (ctypes.c_size_t * 3)(), (ctypes.c_size_t * 3)()
-        offl, total = ctypes.c_size_t(0), ctypes.c_size_t(0)
-        _lib.check(_lib.lib().bsc_gather_layout(n_global, d, offx, offi, ctypes.byref(offl), ctypes.byref(total)))
         group = self.group if self.group is not None else self.dist.group.WORLD
-        bufs, handles, peers = [], [], []
-        for _ in range(2):
-            t = symm.empty(int(total.value), dtype=torch.uint8, device=device)
-            h = symm.rendezvous(t, group)
-            ptrs = list(h.buffer_ptrs)
-            if len(ptrs) != self.world_size or h.rank != self.rank:
-                raise RuntimeError("symmetric memory group does not match the ClipLoss rank / world_size")
-            bufs.append(t)
-            handles.append(h)
-            peers.append((ctypes.c_void_p * self.world_size)(*ptrs))
-        return {"bufs": bufs, "handles": handles, "peers": peers, "offx": list(offx), "offi": list(offi),
-                "offl": int(offl.value), "step": 0}
+        err = None
+        bufs = []
+        try:
+            bufs = [symm.empty(int(nbytes), dtype=torch.uint8, device=device) for _ in range(count)]
+        except Exception as e:  # noqa: BLE001 -- reported below, decided collectively
+            err = e
+        if not self._agree(err is None, device):
+            if self.strict:
+                raise err if err is not None else RuntimeError("symmetric memory allocation failed on a peer")
+            warnings.warn(f"bsc: NVLink peer memory unavailable ({err!r} on this or another rank); using NCCL collectives")
+            self.disabled = True
+            return None
+        handles, peers = [], []
+        try:
+            for t in bufs:
+                h = symm.rendezvous(t, group)
+                ptrs = list(h.buffer_ptrs)
+                if len(ptrs) != self.world_size or h.rank != self.rank:
+                    raise RuntimeError("symmetric memory group does not match the ClipLoss rank / world_size")
+                handles.append(h)
+                peers.append(ptrs)
+        except Exception as e:  # noqa: BLE001
+            err = e
+        if not self._agree(err is None, device):
+            if self.strict:
+                raise err if err is not None else RuntimeError("symmetric memory rendezvous failed on a peer")
+            warnings.warn(f"bsc: NVLink peer mapping unavailable ({err!r} on this or another rank); using NCCL collectives")
+            self.disabled = True
+            return None
+        return bufs, handles, peers
 
+    def _cache_put(self, cache: dict, key, value) -> None:
+        while len(cache) >= self.MAX_SHAPES:
+            cache.pop(next(iter(cache)))
+        cache[key] = value
+
+    # -- forward gather -----------------------------------------------------------------------------
     def gather_tc16(self, feats, labels):
-        """-> (xh[3], inv[3], all_labels) as views of this rank's symmetric buffer, or None when the inputs do not
-        qualify (mixed dtypes, strided rows) and the caller must take the NCCL path."""
+        """-> (xh[3], inv[3], all_labels, token) as views of this rank's symmetric buffer, or None when the inputs do
+        not qualify (mixed dtypes, strided elements) or peer memory is unavailable: the caller takes the NCCL path."""
         import ctypes
+        import weakref
 
         from . import _lib
 
+        if self.disabled:
+            return None
         present = [f for f in feats if f is not None]
         f0 = present[0]
         if any(f.dtype != f0.dtype or f.stride(1) != 1 for f in present) or f0.shape[1] % 8 != 0:
@@ -115,11 +166,30 @@ class SymmMemComm(TorchDistComm):
         n_local, d = f0.shape
         n_global = n_local * self.world_size
         key = (n_global, d, f0.device)
-        st = self._state.get(key)
+        st = self._gather.get(key)
         if st is None:
-            st = self._state[key] = self._setup(n_global, d, f0.device)
+            offx, offi = (ctypes.c_size_t * 3)(), (ctypes.c_size_t * 3)()
+            offl, total = ctypes.c_size_t(0), ctypes.c_size_t(0)
+            _lib.check(_lib.lib().bsc_gather_layout(n_global, d, offx, offi, ctypes.byref(offl), ctypes.byref(total)))
+            made = self._symm_buffers(int(total.value), f0.device, 2)
+            if made is None:
+                return None
+            bufs, handles, peers = made
+            st = {"bufs": bufs, "handles": handles,
+                  "peers": [(ctypes.c_void_p * self.world_size)(*pp) for pp in peers],
+                  "offx": list(offx), "offi": list(offi), "offl": int(offl.value), "step": 0, "pending": [None, None]}
+            self._cache_put(self._gather, key, st)
         b = st["step"] & 1
         st["step"] += 1
+        # the OTHER buffer is overwritten by the peers' next forward, which they may start as soon as this rank has
+        # arrived at the barrier below: a problem still waiting for its backward there moves to private memory now
+        for slot in (b ^ 1, b):
+            ref = st["pending"][slot]
+            prob = ref() if ref is not None else None
+            if prob is not None and not getattr(prob, "done", False):
+                prob.rebind([None if t is None else t.clone() for t in prob.xh],
+                            [None if t is None else t.clone() for t in prob.inv], prob.all_labels.clone())
+            st["pending"][slot] = None
         labels = labels.detach().to(torch.int64).contiguous()
         x = (ctypes.c_void_p * 3)(*[None if f is None else f.data_ptr() for f in feats])
         ldx = (ctypes.c_int64 * 3)(*[0 if f is None else f.stride(0) for f in feats])
@@ -138,31 +208,77 @@ class SymmMemComm(TorchDistComm):
             xh.append(buf[st["offx"][m]:st["offx"][m] + n_global * d * 2].view(torch.float16).view(n_global, d))
             inv.append(buf[st["offi"][m]:st["offi"][m] + n_global * 4].view(torch.float32))
         all_labels = buf[st["offl"]:st["offl"] + n_global * 8].view(torch.int64)
-        return xh, inv, all_labels
+
+        def bind(prob, st=st, b=b):
+            st["pending"][b] = weakref.ref(prob)
+
+        return xh, inv, all_labels, bind
+
+    # -- backward exchange ----------------------------------------------------------------------------
+    def prepare_exchange(self, nbytes: int, device) -> bool:
+        """Allocate and map the scatter backward's exchange buffers (collective).  False: peer memory is unavailable
+        and every rank must plan again without it."""
+        if self.disabled:
+            return False
+        key = (int(nbytes), device)
+        if key in self._exchange:
+            return True
+        made = self._symm_buffers(int(nbytes), device, 2)
+        if made is None:
+            return False
+        bufs, handles, peers = made
+        self._cache_put(self._exchange, key, {"bufs": bufs, "handles": handles, "peers": peers, "step": 0})
+        return True
+
+    def exchange(self, nbytes: int, device):
+        st = self._exchange.get((int(nbytes), device))
+        if st is None:
+            raise RuntimeError("scatter backward without prepared exchange buffers (prepare_exchange runs in the forward)")
+        b = st["step"] & 1
+        st["step"] += 1
+        self._ex_handle = st["handles"][b]
+        return st["bufs"][b], st["peers"][b]
+
+    def exchange_barrier(self, device) -> None:
+        with torch.cuda.device(device):
+            self._ex_handle.barrier(channel=1)
 
 
 def resolve_mode(precision: str, feats: Sequence[torch.Tensor]) -> int:
+    d = feats[0].shape[1]
     if precision == "fp32":
         return MODE_F32
     if precision in ("tc16", "bf16", "fp16"):
+        if d % 128 != 0:
+            from ._lib import BscError
+
+            raise BscError(f"the tensor-core mode needs an embedding dimension that is a multiple of 128 (got {d}); "
+                           "use precision='fp32' (BSC_MODE_F32) or 'auto'")
         return MODE_TC16
     if precision != "auto":
         raise ValueError(f"precision must be 'auto', 'fp32' or 'tc16' (got {precision!r})")
-    # auto: the reference computes in the input dtype -> fp32 inputs take the exact path
-    return MODE_F32 if all(f.dtype == torch.float32 for f in feats) else MODE_TC16
+    # auto: the reference computes in the input dtype -> fp32 inputs take the exact path; so do widths the
+    # tensor-core kernels do not tile
+    if all(f.dtype == torch.float32 for f in feats) or d % 128 != 0:
+        return MODE_F32
+    return MODE_TC16
 
 
-def infonce_forward(ops, comm, feats: List[Optional[torch.Tensor]], labels: torch.Tensor, scale: float, mode: int):
+def infonce_forward(ops, comm, feats: List[Optional[torch.Tensor]], labels: torch.Tensor, scale: float, mode: int,
+                    want_grad: bool = True, bwd_request: int = -1):
     """Forward of the fused loss.  Returns (loss, saved-for-backward)."""
     present = [f for f in feats if f is not None]
     n_local, d = present[0].shape
     for f in present:
         if f.shape != (n_local, d):
             raise ValueError("all modalities must have the same [batch, dim] shape")
+        if f.dtype != present[0].dtype:
+            raise ValueError("all modalities must share one dtype (the reference computes in one dtype, float32)")
     if labels.shape[0] != n_local:
         raise ValueError("label batch does not match the feature batch")
     inv = None
     all_labels = None
+    bind = None
     if mode == MODE_F32:
         xh = [None if f is None else comm.all_gather_rows(ops.normalize(f.detach(), torch.float32)) for f in feats]
     else:
@@ -172,7 +288,8 @@ def infonce_forward(ops, comm, feats: List[Optional[torch.Tensor]], labels: torc
         fused = comm.gather_tc16([None if f is None else f.detach() for f in feats], labels) \
             if hasattr(comm, "gather_tc16") else None
         if fused is not None:
-            xh, inv, all_labels = fused
+            xh, inv, all_labels = fused[:3]
+            bind = fused[3] if len(fused) > 3 else None
         else:
             xh, inv = [], []
             for f in feats:
@@ -188,26 +305,48 @@ def infonce_forward(ops, comm, feats: List[Optional[torch.Tensor]], labels: torc
     n_global = all_labels.shape[0]
     r, rep, nxt, rmax = ops.label_stats(all_labels)
     prob = Problem(xh=xh, n_global=n_global, n_local=n_local, row0=comm.rank * n_local, d=d, mode=mode,
-                   scale=scale, r=r, rep=rep, nxt=nxt, rmax=rmax, inv=inv)
+                   scale=scale, r=r, rep=rep, nxt=nxt, rmax=rmax, inv=inv, all_labels=all_labels,
+                   world=comm.world_size, rank=comm.rank)
+    ops.plan(prob, bwd_request, peer_memory=bool(getattr(comm, "peer_memory", False)))
+    if want_grad and prob.exchange_bytes and comm.world_size > 1:
+        if not comm.prepare_exchange(prob.exchange_bytes, present[0].device):  # collective verdict
+            ops.plan(prob, bwd_request, peer_memory=False)
+    if bind is not None and want_grad:
+        bind(prob)
     stats = ops.infonce_fwd(prob)
     stats = comm.all_reduce_sum(stats)
     loss = ops.infonce_loss(prob, stats)
     return loss, (prob, stats)
 
 
-def infonce_backward(ops, saved, feats, grad_out: torch.Tensor, grad_gain: float = 1.0):
+def infonce_backward(ops, comm, saved, feats, grad_out: torch.Tensor, grad_gain: float = 1.0):
+    from ._lib import BWD_SCATTER
+
     prob, stats = saved
     if grad_gain != 1.0:
         grad_out = grad_out * grad_gain
-    return ops.infonce_bwd(prob, stats, [None if f is None else f.detach() for f in feats], grad_out)
+    xs = [None if f is None else f.detach() for f in feats]
+    dev = next(x for x in xs if x is not None).device
+    own, ptrs = (None, None)
+    if prob.mode == MODE_TC16 and prob.bwd_mode == BWD_SCATTER:
+        own, ptrs = comm.exchange(prob.exchange_bytes, dev)
+    ops.infonce_bwd_partials(prob, stats, ptrs)
+    if own is not None:
+        comm.exchange_barrier(dev)  # every rank's partial sums have landed before anyone adds them up
+    grads = ops.infonce_bwd_finish(prob, xs, grad_out, own)
+    prob.done = True
+    prob.bwd_workspace = None
+    return grads
 
 
 class _InfoNCEFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, ops, comm, scale, mode, grad_gain, labels, image, dna, text):
+    def forward(ctx, ops, comm, scale, mode, grad_gain, bwd_request, labels, image, dna, text):
         feats = [image, dna, text]
-        loss, saved = infonce_forward(ops, comm, feats, labels, scale, mode)
+        want_grad = any(f is not None and f.requires_grad for f in feats)
+        loss, saved = infonce_forward(ops, comm, feats, labels, scale, mode, want_grad, bwd_request)
         ctx.ops = ops
+        ctx.comm = comm
         ctx.saved_state = saved
         ctx.save_for_backward(image, dna, text)
         ctx.grad_gain = grad_gain
@@ -216,12 +355,15 @@ class _InfoNCEFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_out):
         feats = list(ctx.saved_tensors)
-        grads = infonce_backward(ctx.ops, ctx.saved_state, feats, grad_out, ctx.grad_gain)
+        if ctx.saved_state is None:
+            raise RuntimeError("bsc loss: backward called twice on the same graph; evaluate the loss again instead "
+                               "(the operands of the first pass are released after its backward)")
+        grads = infonce_backward(ctx.ops, ctx.comm, ctx.saved_state, feats, grad_out, ctx.grad_gain)
         ctx.saved_state = None
         out = []
         for f, g in zip(feats, grads):
             out.append(g if (f is not None and f.requires_grad) else None)
-        return (None, None, None, None, None, None, *out)
+        return (None, None, None, None, None, None, None, *out)
 
 
 def _check_criterion(criterion) -> None:
@@ -236,6 +378,16 @@ def _check_criterion(criterion) -> None:
             "label smoothing, no class weights), which is what the reference constructs")
 
 
+def _plain_scale(logit_scale) -> float:
+    """The temperature is a constant in the reference (scripts/train_cl.py:190; the learnable one is commented out,
+    simple_clip.py:54-79): a tensor that wants a gradient would silently lose it here, so it is refused."""
+    if isinstance(logit_scale, torch.Tensor):
+        if logit_scale.requires_grad:
+            raise NotImplementedError("bsc losses take a constant logit_scale (no gradient flows to it)")
+        return float(logit_scale.detach())
+    return float(logit_scale)
+
+
 def _default_ops():
     from .ops import CudaOps
 
@@ -245,12 +397,13 @@ def _default_ops():
 class ContrastiveLoss(nn.Module):
     """Single-process multi-modal InfoNCE with multi-positive labels (loss_func.py:23-54)."""
 
-    def __init__(self, criterion=None, logit_scale=1 / 0.07, precision: str = "auto"):
+    def __init__(self, criterion=None, logit_scale=1 / 0.07, precision: str = "auto", backward: str = "auto"):
         super().__init__()
         _check_criterion(criterion)
         self.criterion = criterion
-        self.logit_scale = logit_scale
+        self.logit_scale = _plain_scale(logit_scale)
         self.precision = precision
+        self.backward_mode = backward  # auto | scatter | blocks | recompute (BSC_BWD_MODE overrides)
         self._ops = None
 
     def forward(self, image_features, dna_features, text_features, label, logit_scale=1 / 0.07):
@@ -262,14 +415,16 @@ class ContrastiveLoss(nn.Module):
         if self._ops is None:
             self._ops = _default_ops()
         mode = resolve_mode(self.precision, present)
-        return _InfoNCEFn.apply(self._ops, LocalComm(), float(self.logit_scale), mode, 1.0, label, *feats)
+        return _InfoNCEFn.apply(self._ops, LocalComm(), float(self.logit_scale), mode, 1.0,
+                                requested_bwd_mode(self.backward_mode), label, *feats)
 
 
 class ClipLoss(nn.Module):
     """Distributed twin (loss_func.py:94-165): every rank returns the loss of the GLOBAL batch."""
 
     def __init__(self, local_loss=False, gather_with_grad=False, cache_labels=False, rank=0, world_size=1,
-                 use_horovod=False, criterion=None, precision: str = "auto", group=None, fused_gather: str = "auto"):
+                 use_horovod=False, criterion=None, precision: str = "auto", group=None, fused_gather: str = "auto",
+                 backward: str = "auto"):
         super().__init__()
         if use_horovod:
             raise NotImplementedError("horovod gathers are not implemented; use torch.distributed (NCCL)")
@@ -286,35 +441,22 @@ class ClipLoss(nn.Module):
         if fused_gather not in ("auto", "on", "off"):
             raise ValueError("fused_gather must be 'auto', 'on' or 'off'")
         self.fused_gather = fused_gather
+        self.backward_mode = backward
         self._ops = None
         self._comm = None
 
     def _make_comm(self, device):
-        """NCCL plumbing, with the one-kernel NVLink gather (SymmMemComm) on top when the ranks share a node's
-        symmetric memory.  'auto' falls back to plain NCCL collectives (still on the GPU) if the set-up fails."""
+        """NCCL plumbing, with NVLink peer memory (SymmMemComm: one-kernel gather, scatter backward) on top when the
+        ranks share a node.  'auto' continues on plain NCCL collectives when the set-up fails on any rank (decided
+        collectively); 'on' raises; 'off' never tries."""
         import os
-        import warnings
 
         want = self.fused_gather
         if os.environ.get("BSC_FUSED_GATHER") == "0":
             want = "off"
         if want == "off" or device.type != "cuda":
             return TorchDistComm(self.rank, self.world_size, self.group)
-        comm = SymmMemComm(self.rank, self.world_size, self.group)
-        if want == "on":
-            return comm
-        inner = comm.gather_tc16
-
-        def guarded(feats, labels):
-            try:
-                return inner(feats, labels)
-            except Exception as e:  # set-up or peer mapping failed: keep training on the NCCL collectives
-                warnings.warn(f"bsc: fused NVLink gather unavailable ({type(e).__name__}: {e}); using NCCL all_gather")
-                comm.gather_tc16 = lambda feats, labels: None
-                return None
-
-        comm.gather_tc16 = guarded
-        return comm
+        return SymmMemComm(self.rank, self.world_size, self.group, strict=(want == "on"))
 
     def forward(self, image_features, dna_features, text_features, labels, logit_scale, output_dict=False):
         feats = [image_features, dna_features, text_features]
@@ -328,5 +470,6 @@ class ClipLoss(nn.Module):
         comm = self._comm
         mode = resolve_mode(self.precision, present)
         gain = float(self.world_size) if (self.gather_with_grad and self.world_size > 1) else 1.0
-        total = _InfoNCEFn.apply(self._ops, comm, float(logit_scale), mode, gain, labels, *feats)
+        total = _InfoNCEFn.apply(self._ops, comm, _plain_scale(logit_scale), mode, gain,
+                                 requested_bwd_mode(self.backward_mode), labels, *feats)
         return {"contrastive_loss": total} if output_dict else total

@@ -21,7 +21,7 @@ from ._lib import MODE_F32, MODE_TC16, NORM_SKLEARN, NORM_TORCH, InfoNceDesc, ch
 class Problem:
     """One InfoNCE evaluation: the gathered, normalised global batch and this rank's row range."""
     # 3 entries or None: F32 mode -> [n_global, d] float32 L2-normalised rows;
-    # TC16 mode -> [n_global, d] RAW bfloat16 / float16 rows plus their inverse norms in ``inv``
+    # TC16 mode -> [n_global, d] float16 rows (the caller's values times a power of two) plus their inverse norms in ``inv``
     xh: List[Optional[torch.Tensor]]
     n_global: int
     n_local: int
@@ -34,8 +34,46 @@ class Problem:
     nxt: torch.Tensor = None    # [n_global] int32     next member of the class
     rmax: torch.Tensor = None   # [1] float32
     inv: List[Optional[torch.Tensor]] = None  # TC16: [n_global] float32 1 / max(||row||, 1e-12) per modality
-    workspace: torch.Tensor = None
+    all_labels: torch.Tensor = None
+    world: int = 1
+    rank: int = 0
+    # resolved by CudaOps.plan (bsc_infonce_plan)
+    bwd_mode: int = None
+    fwd_workspace_bytes: int = 0
+    bwd_workspace_bytes: int = 0
+    exchange_bytes: int = 0
+    bwd_workspace: torch.Tensor = None
     _desc: InfoNceDesc = field(default=None, repr=False)
+
+    def rebind(self, xh, inv, all_labels):
+        """Point the problem at private copies of its operands (the symmetric gather buffer is about to be reused)."""
+        self.xh, self.inv, self.all_labels = xh, inv, all_labels
+        self._desc = None
+
+
+def requested_bwd_mode(default: str = "auto") -> int:
+    """The backward strategy the caller asked for: argument of the loss module, overridden by BSC_BWD_MODE
+    (auto | recompute | blocks | scatter).  Read on the host once per forward; the library never reads it."""
+    import os
+
+    name = os.environ.get("BSC_BWD_MODE", default).strip().lower()
+    if name not in _lib.BWD_NAMES:
+        raise ValueError(f"backward mode must be one of {sorted(_lib.BWD_NAMES)} (got {name!r})")
+    return _lib.BWD_NAMES[name]
+
+
+def memory_budget(device) -> int:
+    """Bytes the backward may claim: what the driver reports free plus what torch's caching allocator holds unused,
+    minus a margin; BSC_BWD_MEM_GB caps it (the stored weight blocks are the one N^2-sized buffer of the design)."""
+    import os
+
+    free, _ = torch.cuda.mem_get_info(device)
+    cached = torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)
+    budget = int(0.9 * (free + max(cached, 0)))
+    cap = os.environ.get("BSC_BWD_MEM_GB")
+    if cap:
+        budget = min(budget, int(float(cap) * (1 << 30)))
+    return max(budget, 1)
 
 
 class CudaOps:
@@ -111,6 +149,8 @@ class CudaOps:
                 d.xh[m] = ptr(p.xh[m]) or None
                 d.inv[m] = (ptr(p.inv[m]) if p.inv is not None else 0) or None
             d.r, d.rep, d.next, d.rmax = p.r.data_ptr(), p.rep.data_ptr(), p.nxt.data_ptr(), p.rmax.data_ptr()
+            d.bwd_mode = p.bwd_mode if p.bwd_mode is not None else _lib.BWD_RECOMPUTE
+            d.world, d.rank = p.world, p.rank
             p._desc = d
         return p._desc
 
@@ -120,20 +160,30 @@ class CudaOps:
     def stats_len(self, n_global: int) -> int:
         return int(lib().bsc_infonce_stats_len(n_global))
 
-    def _ensure_workspace(self, p: Problem) -> None:
-        if p.workspace is None:
-            nbytes = c_size_t(0)
-            check(lib().bsc_infonce_workspace_bytes(byref(self._desc(p)), byref(nbytes)))
-            p.workspace = torch.empty(int(nbytes.value), dtype=torch.uint8, device=self._device(p))
+    def plan(self, p: Problem, requested: int = _lib.BWD_AUTO, peer_memory: bool = True) -> None:
+        """Resolve the backward strategy once (bsc_infonce_plan) and record the buffer sizes in ``p``."""
+        dev = self._device(p)
+        _lib.require_device(dev)
+        out = _lib.InfoNcePlan()
+        p._desc = None
+        budget = memory_budget(dev) if (requested == _lib.BWD_AUTO and p.mode == MODE_TC16) else 0
+        check(lib().bsc_infonce_plan(byref(self._desc(p)), requested, 1 if peer_memory else 0, budget, byref(out)))
+        p.bwd_mode = int(out.bwd_mode)
+        p.fwd_workspace_bytes = int(out.fwd_workspace_bytes)
+        p.bwd_workspace_bytes = int(out.bwd_workspace_bytes)
+        p.exchange_bytes = int(out.exchange_bytes)
+        p._desc = None
 
     def infonce_fwd(self, p: Problem) -> torch.Tensor:
         dev = self._device(p)
         _lib.require_device(dev)
-        self._ensure_workspace(p)
+        if p.bwd_mode is None:
+            self.plan(p)
+        ws = torch.empty(max(p.fwd_workspace_bytes, 256), dtype=torch.uint8, device=dev)  # lives for the forward only
         stats = torch.empty(self.stats_len(p.n_global), dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
-            check(lib().bsc_infonce_fwd(byref(self._desc(p)), stats.data_ptr(), p.workspace.data_ptr(),
-                                        p.workspace.numel(), stream_ptr(dev)))
+            check(lib().bsc_infonce_fwd(byref(self._desc(p)), stats.data_ptr(), ws.data_ptr(), ws.numel(),
+                                        stream_ptr(dev)))
         return stats
 
     def infonce_loss(self, p: Problem, stats: torch.Tensor) -> torch.Tensor:
@@ -143,19 +193,38 @@ class CudaOps:
             check(lib().bsc_infonce_loss(byref(self._desc(p)), stats.data_ptr(), loss.data_ptr(), stream_ptr(dev)))
         return loss
 
-    def infonce_bwd(self, p: Problem, stats: torch.Tensor, xs, grad_out: torch.Tensor):
-        """xs: this rank's original rows per modality (None when absent).  Returns grads of the same shapes."""
+    def infonce_bwd_partials(self, p: Problem, stats: torch.Tensor, exchange_ptrs=None) -> None:
+        """Phase 1 of the backward: raw gradient sums into the (lazily allocated) backward workspace and, in the
+        scatter strategy, into the owners' exchange buffers (``exchange_ptrs``: one device address per rank)."""
+        dev = self._device(p)
+        if p.bwd_workspace is None:
+            p.bwd_workspace = torch.empty(max(p.bwd_workspace_bytes, 256), dtype=torch.uint8, device=dev)
+        ex = None
+        if p.mode == MODE_TC16 and p.bwd_mode == _lib.BWD_SCATTER:
+            if exchange_ptrs is None or len(exchange_ptrs) != p.world:
+                raise _lib.BscError("the scatter backward needs one exchange buffer address per rank")
+            ex = (c_void_p * p.world)(*exchange_ptrs)
+        with torch.cuda.device(dev):
+            check(lib().bsc_infonce_bwd_partials(byref(self._desc(p)), stats.data_ptr(), ex, p.bwd_workspace.data_ptr(),
+                                                 p.bwd_workspace.numel(), stream_ptr(dev)))
+
+    def infonce_bwd_finish(self, p: Problem, xs, grad_out: torch.Tensor, own_exchange: torch.Tensor = None):
+        """Phase 2: xs = this rank's original rows per modality (None when absent; rows may be strided, elements must
+        be contiguous).  Returns dense gradients of the same shapes and dtype."""
         dev = self._device(p)
         grad_out = grad_out.to(device=dev, dtype=torch.float32).reshape(1).contiguous()
-        first = next(x for x in xs if x is not None)
-        xs = [None if x is None else (x if x.is_contiguous() else x.contiguous()) for x in xs]
-        grads = [None if x is None else torch.empty_like(x) for x in xs]
+        xs = [None if x is None else (x if x.stride(1) == 1 else x.contiguous()) for x in xs]
+        present = [x for x in xs if x is not None]
+        if any(x.dtype != present[0].dtype for x in present):
+            raise _lib.BscError("all modalities must share one dtype (float32, bfloat16 or float16)")
+        grads = [None if x is None else torch.empty(x.shape, dtype=x.dtype, device=dev) for x in xs]
         xp = (c_void_p * 3)(*[ptr(x) or None for x in xs])
         gp = (c_void_p * 3)(*[ptr(g) or None for g in grads])
+        ldx = (ctypes.c_int64 * 3)(*[0 if x is None else x.stride(0) for x in xs])
         with torch.cuda.device(dev):
-            check(lib().bsc_infonce_bwd(byref(self._desc(p)), stats.data_ptr(), xp, _lib.dtype_code(first.dtype),
-                                        first.stride(0), grad_out.data_ptr(), gp, p.workspace.data_ptr(),
-                                        p.workspace.numel(), stream_ptr(dev)))
+            check(lib().bsc_infonce_bwd_finish(byref(self._desc(p)), xp, _lib.dtype_code(present[0].dtype), ldx,
+                                               grad_out.data_ptr(), gp, ptr(own_exchange) or None,
+                                               p.bwd_workspace.data_ptr(), p.bwd_workspace.numel(), stream_ptr(dev)))
         return grads
 
     # ---- retrieval ------------------------------------------------------------------------------

@@ -10,7 +10,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "bsc", "libbsc_hot.so")
-SOURCES = ["api.cu", "prep.cu", "simt_f32.cu", "tc_sim.cu", "tc_bwd.cu", "tc_bwd2.cu", "tc_bwd3.cu", "taxo.cu", "rescore.cu"]
+SOURCES = ["api.cu", "prep.cu", "simt_f32.cu", "tc_sim.cu", "tc_bwd2.cu", "tc_bwd3.cu", "taxo.cu", "rescore.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",

@@ -34,6 +34,7 @@ int loss_launch(const float* stats, const float* r, int64_t n, unsigned present_
                 cudaStream_t st);
 int uv_launch(const float* stats, const float* r, int64_t n, const float* rmax, const float* const* inv, int use_gs,
               float* uv, float* gsbuf, float* invmax, cudaStream_t st);
+int rep_range_launch(const int32_t* rep, int64_t n, int tile, int2* out, cudaStream_t st);
 int combine_launch(const CombineArgs& a, int x_dtype, cudaStream_t st);
 int topk_merge_launch(const float* cs, const int64_t* ci, int parts, int64_t nq, int k, float* os, int64_t* oi,
                       cudaStream_t st);
@@ -64,6 +65,26 @@ int cuda_fail(cudaError_t e, const char* what) {
 }
 
 void count_launch(int n) { g_launches += n; }
+
+int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev;
+}
+
+int device_sm_count() {
+  static std::atomic<int> cache[128];
+  const int dev = current_device();
+  if (dev >= 0 && dev < 128) {
+    const int c = cache[dev].load();
+    if (c > 0) return c;
+  }
+  int n = 0;
+  cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  if (n <= 0) n = 148;
+  if (dev >= 0 && dev < 128) cache[dev].store(n);
+  return n;
+}
 
 void timing_begin(int which, cudaStream_t st) {
   if (!g_timing) return;
@@ -143,10 +164,15 @@ static int present_count(const bsc_infonce_desc* p, unsigned* mask) {
   return m;
 }
 
-InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p) {
-  InfoNceWs L{};
+static size_t take(size_t& off, size_t bytes) {
+  const size_t o = off;
+  off += align_up(bytes, 256);
+  return o;
+}
+
+InfoNceFwdWs infonce_fwd_layout(const bsc_infonce_desc* p) {
+  InfoNceFwdWs L{};
   const int64_t N = p->n_global, n = p->n_local;
-  const int D = p->d;
   const int m = present_count(p, nullptr);
   const int n_pairs = m * (m - 1) / 2;
   if (p->mode == BSC_MODE_TC16) {
@@ -159,32 +185,57 @@ InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p) {
   }
   L.n_local_pad = (int64_t)align_up((size_t)(n > 0 ? n : 1), 64);
   L.n_global_pad = (int64_t)align_up((size_t)(N > 0 ? N : 1), 64);
-  L.g_rows = n < 2048 ? (n > 0 ? n : 1) : 2048;
   size_t off = 0;
-  auto take = [&](size_t bytes) {
-    size_t o = off;
-    off += align_up(bytes, 256);
-    return o;
-  };
-  L.uv = take((size_t)6 * N * sizeof(float));
-  L.gs = take(32 * sizeof(float));  // [6][2] {gs, 1/gs} per ordered pair, [12..14] max inverse norms, [16..17] {gs, 1/gs} of unscaled weights
   // x2: the tensor-core forward sweep keeps one partial per epilogue warp group (tc_sim.cu NG)
-  L.rowpart = take((size_t)3 * 2 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
-  L.rowpos = take((size_t)3 * 2 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
-  L.jrange = take((size_t)(L.n_jtile > 0 ? L.n_jtile : 1) * 2 * sizeof(int));
-  L.colpart = take((size_t)3 * (L.n_iblk > 0 ? L.n_iblk : 1) * L.n_global_pad * sizeof(float));
-  L.bwd_gstore = tc_bwd_gstore(p);
-  L.bwd_jsplit = L.bwd_gstore >= 2 ? tc_bwd_gemm_ksplit(p, L.bwd_gstore) : tc_bwd_duo_jsplit(p);
-  L.dxraw = take((size_t)3 * 2 * L.bwd_jsplit * (n > 0 ? n : 1) * D * sizeof(float));
-  if (L.bwd_gstore) {
-    L.xunit = take((size_t)3 * N * D * 2);
-    L.gimg = take(tc_bwd_gimg_bytes(p, L.bwd_gstore));
+  L.rowpart = take(off, (size_t)3 * 2 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
+  L.rowpos = take(off, (size_t)3 * 2 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
+  L.jrange = take(off, (size_t)(L.n_jtile > 0 ? L.n_jtile : 1) * 2 * sizeof(int));
+  L.colpart = take(off, (size_t)3 * (L.n_iblk > 0 ? L.n_iblk : 1) * L.n_global_pad * sizeof(float));
+  L.total = off;
+  return L;
+}
+
+// number of raw-gradient slabs [n_local][d] the strategy keeps in the workspace (before the K / column split)
+static int bwd_local_slots(const bsc_infonce_desc* p) {
+  const int m = present_count(p, nullptr);
+  // SCATTER: one K-major job per present pair; the others address slabs as (modality * 2 + partner slot), modality 0..2
+  return (p->mode == BSC_MODE_TC16 && p->bwd_mode == BSC_BWD_SCATTER) ? m * (m - 1) / 2 : 6;
+}
+
+InfoNceBwdWs infonce_bwd_layout(const bsc_infonce_desc* p) {
+  InfoNceBwdWs L{};
+  const int64_t N = p->n_global, n = p->n_local;
+  const int D = p->d;
+  const int m = present_count(p, nullptr);
+  const int n_pairs = m * (m - 1) / 2;
+  L.mode = p->mode == BSC_MODE_TC16 ? p->bwd_mode : BSC_BWD_RECOMPUTE;
+  const bool stored = p->mode == BSC_MODE_TC16 && (L.mode == BSC_BWD_BLOCKS || L.mode == BSC_BWD_SCATTER);
+  if (p->mode == BSC_MODE_TC16)
+    tc_fwd_tiling(n, N, n_pairs, &L.n_iblk, &L.n_jtile, &L.jtiles_per_chunk, &L.n_jchunk);
+  L.g_rows = n < 2048 ? (n > 0 ? n : 1) : 2048;
+  L.kparts = 1;
+  if (p->mode == BSC_MODE_TC16) L.kparts = stored ? tc_bwd_gemm_kparts(p) : tc_bwd_duo_jsplit(p);
+  size_t off = 0;
+  L.uv = take(off, (size_t)6 * N * sizeof(float));
+  L.gs = take(off, 32 * sizeof(float));  // [6][2] {gs, 1/gs} per ordered pair, [12..14] max inverse norms
+  L.jrange = take(off, (size_t)((N + kTcBNF - 1) / kTcBNF + 1) * 2 * sizeof(int));
+  L.dxraw = take(off, (size_t)bwd_local_slots(p) * L.kparts * (n > 0 ? n : 1) * D * sizeof(float));
+  if (stored) {
+    L.xunit = take(off, (size_t)3 * (n > 0 ? n : 1) * D * 2);
+    L.gimg = take(off, tc_bwd_gimg_bytes(p));
   } else {
     L.xunit = L.gimg = off;
   }
-  L.gscratch = (p->mode == BSC_MODE_F32) ? take((size_t)L.g_rows * N * sizeof(float)) : off;
+  L.gscratch = (p->mode == BSC_MODE_F32) ? take(off, (size_t)L.g_rows * N * sizeof(float)) : off;
   L.total = off;
   return L;
+}
+
+static size_t exchange_bytes_of(const bsc_infonce_desc* p) {
+  if (p->mode != BSC_MODE_TC16 || p->bwd_mode != BSC_BWD_SCATTER) return 0;
+  const int m = present_count(p, nullptr);
+  return (size_t)p->world * (size_t)(m * (m - 1) / 2) * (size_t)(p->n_local > 0 ? p->n_local : 1) * p->d *
+         sizeof(float);
 }
 
 static int check_desc(const bsc_infonce_desc* p, const char* who) {
@@ -197,7 +248,11 @@ static int check_desc(const bsc_infonce_desc* p, const char* who) {
   BSC_REQUIRE(present_count(p, nullptr) >= 2, BSC_EINVAL, "%s: Too less element for calculating the contrastive loss.",
               who);
   BSC_REQUIRE(p->r && p->rep && p->next && p->rmax, BSC_EINVAL, "%s: label statistics pointers are null", who);
+  BSC_REQUIRE(p->world >= 1 && p->world <= kMaxPeers && p->rank >= 0 && p->rank < p->world, BSC_EINVAL,
+              "%s: bad rank %d / world %d (1..%d ranks)", who, p->rank, p->world, kMaxPeers);
   if (p->mode == BSC_MODE_TC16) {
+    BSC_REQUIRE(p->d % 128 == 0, BSC_EUNSUPPORTED, "%s: TC16 mode needs d %% 128 == 0 (got %d); use BSC_MODE_F32", who,
+                p->d);
     BSC_REQUIRE(p->x16_dtype == BSC_F16, BSC_EUNSUPPORTED,
                 "%s: TC16 mode takes float16 rows prepared by bsc_rows_to_f16 (exact for bfloat16 values); "
                 "tcgen05 kind::f16 cannot mix the fp16 weight tile with bfloat16 rows (x16_dtype=%d)",
@@ -319,11 +374,61 @@ int bsc_label_stats(const int64_t* labels, int64_t n, float* r, int32_t* rep, in
 
 int64_t bsc_infonce_stats_len(int64_t n_global) { return 6 * n_global + kStatsExtra; }
 
-int bsc_infonce_workspace_bytes(const bsc_infonce_desc* p, size_t* bytes) {
-  int rc = check_desc(p, "bsc_infonce_workspace_bytes");
+// Is `mode` a strategy this problem can run?  (message in g_err when not)
+static int bwd_mode_ok(const bsc_infonce_desc* p, int mode, int peer_memory, const char* who) {
+  if (p->mode == BSC_MODE_F32) {
+    BSC_REQUIRE(mode == BSC_BWD_RECOMPUTE, BSC_EUNSUPPORTED, "%s: BSC_MODE_F32 has one backward (BSC_BWD_RECOMPUTE)", who);
+    return BSC_OK;
+  }
+  switch (mode) {
+    case BSC_BWD_RECOMPUTE:
+      BSC_REQUIRE(tc_bwd_duo_covers(p), BSC_EUNSUPPORTED,
+                  "%s: the recomputing sweep covers d in {256, 512, 768} only (got %d)", who, p->d);
+      return BSC_OK;
+    case BSC_BWD_BLOCKS:
+      return BSC_OK;
+    case BSC_BWD_SCATTER:
+      BSC_REQUIRE(p->n_global == (int64_t)p->world * p->n_local && p->row0 == (int64_t)p->rank * p->n_local,
+                  BSC_EUNSUPPORTED, "%s: BSC_BWD_SCATTER needs equal row blocks (n_global = world * n_local, row0 = "
+                  "rank * n_local)", who);
+      BSC_REQUIRE(p->world == 1 || peer_memory, BSC_EUNSUPPORTED,
+                  "%s: BSC_BWD_SCATTER over %d ranks needs peer-mapped exchange buffers", who, p->world);
+      return BSC_OK;
+  }
+  set_error("%s: unknown backward mode %d", who, mode);
+  return BSC_EINVAL;
+}
+
+int bsc_infonce_plan(const bsc_infonce_desc* p_in, int requested, int peer_memory, size_t budget,
+                     bsc_infonce_plan_t* plan) {
+  BSC_REQUIRE(p_in != nullptr && plan != nullptr, BSC_EINVAL, "bsc_infonce_plan: null pointer");
+  bsc_infonce_desc p = *p_in;
+  p.bwd_mode = BSC_BWD_RECOMPUTE;
+  int rc = check_desc(&p, "bsc_infonce_plan");
   if (rc) return rc;
-  BSC_REQUIRE(bytes != nullptr, BSC_EINVAL, "bsc_infonce_workspace_bytes: bytes is null");
-  *bytes = infonce_ws_layout(p).total;
+  int mode;
+  if (requested != BSC_BWD_AUTO) {
+    rc = bwd_mode_ok(&p, requested, peer_memory, "bsc_infonce_plan");
+    if (rc) return rc;
+    mode = requested;
+  } else if (p.mode == BSC_MODE_F32) {
+    mode = BSC_BWD_RECOMPUTE;
+  } else {
+    const bool scatter_ok = p.n_global == (int64_t)p.world * p.n_local && p.row0 == (int64_t)p.rank * p.n_local &&
+                            (p.world == 1 || peer_memory);
+    mode = scatter_ok ? BSC_BWD_SCATTER : BSC_BWD_BLOCKS;
+    if (budget > 0 && tc_bwd_duo_covers(&p)) {
+      p.bwd_mode = mode;
+      if (infonce_bwd_layout(&p).total + exchange_bytes_of(&p) > budget) mode = BSC_BWD_RECOMPUTE;
+    }
+  }
+  p.bwd_mode = mode;
+  plan->bwd_mode = mode;
+  plan->reserved = 0;
+  plan->fwd_workspace_bytes = infonce_fwd_layout(&p).total;
+  plan->bwd_workspace_bytes = infonce_bwd_layout(&p).total;
+  plan->exchange_bytes = exchange_bytes_of(&p);
+  if (plan->fwd_workspace_bytes == 0) plan->fwd_workspace_bytes = 256;
   return BSC_OK;
 }
 
@@ -331,7 +436,7 @@ int bsc_infonce_fwd(const bsc_infonce_desc* p, float* stats, void* workspace, si
   int rc = check_desc(p, "bsc_infonce_fwd");
   if (rc) return rc;
   BSC_REQUIRE(stats && workspace, BSC_EINVAL, "bsc_infonce_fwd: null pointer");
-  const InfoNceWs L = infonce_ws_layout(p);
+  const InfoNceFwdWs L = infonce_fwd_layout(p);
   BSC_REQUIRE(workspace_bytes >= L.total, BSC_EWORKSPACE, "bsc_infonce_fwd: workspace %zu < %zu", workspace_bytes,
               L.total);
   cudaStream_t st = (cudaStream_t)stream;
@@ -352,48 +457,110 @@ int bsc_infonce_loss(const bsc_infonce_desc* p, const float* stats, float* loss,
   return loss_launch(stats, p->r, p->n_global, mask, p->logit_scale, loss, (cudaStream_t)stream);
 }
 
-int bsc_infonce_bwd(const bsc_infonce_desc* p, const float* stats, const void* const* x, int x_dtype, int64_t ldx,
-                    const float* grad_out, void* const* grad, void* workspace, size_t workspace_bytes, void* stream) {
-  int rc = check_desc(p, "bsc_infonce_bwd");
+int bsc_infonce_bwd_partials(const bsc_infonce_desc* p, const float* stats, void* const* exchange, void* workspace,
+                             size_t workspace_bytes, void* stream) {
+  int rc = check_desc(p, "bsc_infonce_bwd_partials");
   if (rc) return rc;
-  BSC_REQUIRE(stats && x && grad && grad_out && workspace, BSC_EINVAL, "bsc_infonce_bwd: null pointer");
-  BSC_REQUIRE(ldx >= p->d, BSC_EINVAL, "bsc_infonce_bwd: ldx < d");
-  const InfoNceWs L = infonce_ws_layout(p);
-  BSC_REQUIRE(workspace_bytes >= L.total, BSC_EWORKSPACE, "bsc_infonce_bwd: workspace %zu < %zu", workspace_bytes,
-              L.total);
+  rc = bwd_mode_ok(p, p->mode == BSC_MODE_F32 ? BSC_BWD_RECOMPUTE : p->bwd_mode, 1, "bsc_infonce_bwd_partials");
+  if (rc) return rc;
+  BSC_REQUIRE(stats && workspace, BSC_EINVAL, "bsc_infonce_bwd_partials: null pointer");
+  const InfoNceBwdWs L = infonce_bwd_layout(p);
+  BSC_REQUIRE(workspace_bytes >= L.total, BSC_EWORKSPACE, "bsc_infonce_bwd_partials: workspace %zu < %zu",
+              workspace_bytes, L.total);
   cudaStream_t st = (cudaStream_t)stream;
   char* ws = (char*)workspace;
   const int64_t N = p->n_global;
-  unsigned mask = 0;
-  const int m = present_count(p, &mask);
-  for (int a = 0; a < 3; ++a)
-    BSC_REQUIRE(!p->xh[a] || (x[a] && grad[a]), BSC_EINVAL, "bsc_infonce_bwd: x/grad pointer missing for modality %d",
-                a);
   if (p->n_local == 0) return BSC_OK;
   rc = uv_launch(stats, p->r, N, p->rmax, p->inv, p->mode == BSC_MODE_TC16, (float*)(ws + L.uv), (float*)(ws + L.gs),
                  (float*)(ws + L.gs) + 12, st);
   if (rc) return rc;
-  if (p->mode == BSC_MODE_TC16) g_bwd_mode.store(L.bwd_gstore);
-  rc = (p->mode == BSC_MODE_F32) ? simt_bwd_raw(p, L, ws, st) : tc_bwd_raw(p, L, ws, st);
+  if (p->mode == BSC_MODE_F32) return simt_bwd_raw(p, L, ws, st);
+  g_bwd_mode.store(L.mode);
+  if (L.mode == BSC_BWD_RECOMPUTE) return tc_bwd_duo(p, L, ws, st);
+  ScatterDst dst{};
+  dst.world = p->world;
+  dst.rank = p->rank;
+  if (L.mode == BSC_BWD_SCATTER) {
+    BSC_REQUIRE(exchange != nullptr, BSC_EINVAL, "bsc_infonce_bwd_partials: BSC_BWD_SCATTER needs the exchange buffers");
+    for (int r = 0; r < p->world; ++r) {
+      BSC_REQUIRE(exchange[r] != nullptr && ((uintptr_t)exchange[r] & 15) == 0, BSC_EINVAL,
+                  "bsc_infonce_bwd_partials: exchange buffer of rank %d is null or not 16-byte aligned", r);
+      dst.peer[r] = (float*)exchange[r];
+    }
+  }
+  int np = 0, pa[6], pb[6];
+  rc = tc_bwd_weights(p, L, ws, &np, pa, pb, st);
   if (rc) return rc;
+  return tc_bwd_gemms(p, L, ws, np, pa, pb, dst, st);
+}
+
+int bsc_infonce_bwd_finish(const bsc_infonce_desc* p, const void* const* x, int x_dtype, const int64_t* ldx,
+                           const float* grad_out, void* const* grad, const void* own_exchange, void* workspace,
+                           size_t workspace_bytes, void* stream) {
+  int rc = check_desc(p, "bsc_infonce_bwd_finish");
+  if (rc) return rc;
+  BSC_REQUIRE(x && ldx && grad && grad_out && workspace, BSC_EINVAL, "bsc_infonce_bwd_finish: null pointer");
+  const InfoNceBwdWs L = infonce_bwd_layout(p);
+  BSC_REQUIRE(workspace_bytes >= L.total, BSC_EWORKSPACE, "bsc_infonce_bwd_finish: workspace %zu < %zu",
+              workspace_bytes, L.total);
+  unsigned mask = 0;
+  const int m = present_count(p, &mask);
+  for (int a = 0; a < 3; ++a) {
+    BSC_REQUIRE(!p->xh[a] || (x[a] && grad[a]), BSC_EINVAL,
+                "bsc_infonce_bwd_finish: x/grad pointer missing for modality %d", a);
+    BSC_REQUIRE(!p->xh[a] || ldx[a] >= p->d, BSC_EINVAL, "bsc_infonce_bwd_finish: ldx[%d] < d", a);
+  }
+  const bool scatter = p->mode == BSC_MODE_TC16 && L.mode == BSC_BWD_SCATTER;
+  BSC_REQUIRE(!scatter || own_exchange, BSC_EINVAL, "bsc_infonce_bwd_finish: BSC_BWD_SCATTER needs own_exchange");
+  if (p->n_local == 0) return BSC_OK;
+  char* ws = (char*)workspace;
+  const int64_t slab = p->n_local * (int64_t)p->d;
+  const float* dxraw = (const float*)(ws + L.dxraw);
   CombineArgs ca{};
+  int pair_index[3][3];  // unordered pair (a < b) -> its index among the present pairs
+  {
+    int q = 0;
+    for (int a = 0; a < 3; ++a)
+      for (int b = a + 1; b < 3; ++b) pair_index[a][b] = pair_index[b][a] = (p->xh[a] && p->xh[b]) ? q++ : -1;
+  }
+  const int np = m * (m - 1) / 2;
   for (int a = 0; a < 3; ++a) {
     ca.x[a] = p->xh[a] ? x[a] : nullptr;
     ca.grad[a] = p->xh[a] ? grad[a] : nullptr;
-    ca.raw[a] = (const float*)(ws + L.dxraw) + (size_t)a * 2 * L.bwd_jsplit * p->n_local * p->d;
+    ca.ldx[a] = ldx[a];
+    if (!p->xh[a]) continue;
+    int slot = 0;
+    for (int y = 0; y < 3; ++y) {
+      if (y == a || !p->xh[y]) continue;
+      CombineSrc& s = ca.src[a][slot];
+      s.gs_index = 2 * pair_id(a, y) + 1;
+      if (!scatter) {
+        // one slab group per (modality, partner slot): RECOMPUTE, BLOCKS and the fp32 path
+        s.src = dxraw + (int64_t)(a * 2 + slot) * L.kparts * slab;
+        // BLOCKS / RECOMPUTE with two modalities only: slots are still addressed as (a * 2 + slot)
+        s.stride = slab;
+        s.nparts = L.kparts;
+      } else if (a < y) {  // K-major job of pair (a, y): local partial sums
+        s.src = dxraw + (int64_t)pair_index[a][y] * L.kparts * slab;
+        s.stride = slab;
+        s.nparts = L.kparts;
+      } else {             // MN-major job of pair (y, a): one partial sum per source rank in the exchange buffer
+        s.src = (const float*)own_exchange + (int64_t)pair_index[a][y] * slab;
+        s.stride = (int64_t)np * slab;
+        s.nparts = p->world;
+      }
+      ++slot;
+    }
   }
   ca.gsbuf = (const float*)(ws + L.gs);
   ca.grad_out = grad_out;
-  ca.row0 = p->row0;
   ca.n_local = p->n_local;
-  ca.n_global = N;
-  ca.ldx = ldx;
+  ca.n_global = p->n_global;
   ca.d = p->d;
   ca.n_slots = m - 1;
-  ca.n_parts = L.bwd_jsplit;
   ca.present_mask = mask;
   ca.scale = p->logit_scale;
-  return combine_launch(ca, x_dtype, st);
+  return combine_launch(ca, x_dtype, (cudaStream_t)stream);
 }
 
 int bsc_bank_search_workspace_bytes(int64_t nq, int64_t nb, int d, int k, int mode, size_t* bytes) {

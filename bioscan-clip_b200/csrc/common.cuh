@@ -43,72 +43,112 @@ void count_launch(int n = 1);
 // Ordered pair (a,b), a != b, of modality slots 0..2 -> 0..5.
 __host__ __device__ inline int pair_id(int a, int b) { return a * 2 + (b > a ? b - 1 : b); }
 
-constexpr int kMaxPeers = 16;  // ranks of one NVLink domain addressed by the fused gather
+constexpr int kMaxPeers = 16;  // ranks of one NVLink domain addressed by the fused gather / gradient scatter
 constexpr int kStatsExtra = 4;  // scalars after the 6*N sum-exp rows; [0] = sum over unordered pairs and local rows of
                                 // sum_j T_ij (s*S_ij - s)
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-// ---- workspace layout of the infonce calls -----------------------------------------------------
-struct InfoNceWs {
-  size_t uv;        // float [6][N]          r_i / sumexp
-  size_t gs;        // float [4]             {gs, 1/gs}
-  size_t rowpart;   // float [3][n_jchunk][n_local_pad]   row sum-exp partials
-  size_t rowpos;    // float [3][n_jchunk][n_local_pad]   positive-pair partials
-  size_t colpart;   // float [3][n_iblk][N_pad]
+// ---- workspace layouts of the infonce calls -----------------------------------------------------
+// Forward and backward own separate caller-allocated workspaces (bsc_infonce_plan reports both sizes): the forward
+// of an evaluation-only call never pays for the backward's buffers.
+struct InfoNceFwdWs {
+  size_t rowpart;   // float [pairs][n_jchunk][2][n_local_pad]   row sum-exp partials (2 epilogue warp groups)
+  size_t rowpos;    // float [pairs][n_jchunk][2][n_local_pad]   positive-pair partials
+  size_t colpart;   // float [pairs][n_iblk][N_pad]
   size_t jrange;    // int2  [n_jtile]       label-class range of every column tile
-  size_t dxraw;     // float [3][2][bwd_jsplit][n_local][D]
-  size_t gscratch;  // float [g_rows][N]     fp32 mode only
-  size_t xunit;     // half  [3][N][D]       unit rows (stored-weight backward only)
-  size_t gimg;      // half  [pairs][2*n_steps][2*n_iblk][128][64]  weight spans of the backward sweep (stored-weight only)
   size_t total;
-  // tiling facts shared by host and kernels
   int n_iblk, n_jtile, n_jchunk, jtiles_per_chunk;
-  int bwd_jsplit;   // dxraw parts per (modality, slot): > 1 only for the CTA-pair backward sweep (tc_bwd2.cu)
-  int bwd_gstore;   // tc_bwd_gstore(): 0 recompute, 1 stored spans of the pair sweep, 2 weight matrix + GEMMs
-  int64_t n_local_pad, n_global_pad, g_rows;
+  int64_t n_local_pad, n_global_pad;
 };
 
-InfoNceWs infonce_ws_layout(const bsc_infonce_desc* p);
+struct InfoNceBwdWs {
+  size_t uv;        // float [6][N]          r_i / sumexp
+  size_t gs;        // float [32]            {gs, 1/gs} per ordered pair, max inverse norms
+  size_t jrange;    // int2  [n_jtile]
+  size_t dxraw;     // float [3 K-major jobs... see tc_bwd3.cu][kparts][n_local][D]   local partial gradients
+  size_t xunit;     // half  [3][n_local][D]  unit rows of the LOCAL rows (B operand of the MN-major jobs)
+  size_t gimg;      // half  weight images [blocks][n_iblk_pad][n_j64][128][64]
+  size_t gscratch;  // float [g_rows][N]     fp32 (SIMT) mode only
+  size_t total;
+  int n_iblk, n_jtile, n_jchunk, jtiles_per_chunk;  // tiling of the weights sweep (the forward's)
+  int kparts;       // K split of the K-major gradient GEMMs (BLOCKS / SCATTER) or column split of the recomputing sweep
+  int mode;         // resolved BSC_BWD_* (== p->bwd_mode after validation)
+  int64_t g_rows;
+};
 
+InfoNceFwdWs infonce_fwd_layout(const bsc_infonce_desc* p);
+InfoNceBwdWs infonce_bwd_layout(const bsc_infonce_desc* p);
+
+// Once-per-(kernel, device) guard: function attributes (dynamic shared-memory opt-in) are per device, so an index that
+// spans several GPUs in one process must set them on every device it launches on.
+struct PerDeviceOnce {
+  unsigned long long mask[2] = {0ull, 0ull};  // device ordinals 0..127
+  // returns true the first time it is asked about the current device (racing threads may both see true: harmless)
+  bool first(int dev) {
+    if (dev < 0 || dev >= 128) return true;
+    const unsigned long long bit = 1ull << (dev & 63);
+    unsigned long long& m = mask[dev >> 6];
+    if (m & bit) return false;
+    m |= bit;
+    return true;
+  }
+};
+int current_device();
+int device_sm_count();  // SM count of the CURRENT device (cached per device)
+
+#define BSC_SET_SMEM_ONCE(kernel, bytes)                                                                   \
+  do {                                                                                                     \
+    static ::bsc::PerDeviceOnce once__;                                                                    \
+    if (once__.first(::bsc::current_device()))                                                             \
+      BSC_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)));   \
+  } while (0)
 
 // ---- argument blocks of the O(N*D) kernels in prep.cu ----------------------------------------------
+// Raw gradient sources of one (modality, partner) slot: nparts partial sums [n_local][d], part q at src + q * stride,
+// summed in the order q = 0, 1, ... (fixed: the result does not depend on scheduling or on which rank wrote what).
+struct CombineSrc {
+  const float* src;
+  int64_t stride;   // elements between parts
+  int nparts;
+  int gs_index;     // gsbuf[gs_index] = 1 / gs of the slot's sums
+};
+
 struct CombineArgs {
   const void* x[3];      // original local rows (un-normalised), null when the modality is absent
-  void* grad[3];
-  const float* raw[3];   // [2][n_local][d] per modality
+  void* grad[3];         // dense [n_local][d]
+  CombineSrc src[3][2];
+  int64_t ldx[3];        // row stride of x[m] in elements
   const float* gsbuf;
   const float* grad_out;
-  int64_t row0, n_local, n_global, ldx;
+  int64_t n_local, n_global;
   int d, n_slots;
-  int n_parts;           // partial sums per slot (column-sweep parts of the backward), >= 1
   unsigned present_mask;
   float scale;
 };
 
 // ---- sub-launchers implemented in the .cu files ---------------------------------------------------
-int simt_fwd_stats(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, float* stats, cudaStream_t st);
-int simt_bwd_raw(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st);
-int tc_fwd_stats(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, float* stats, cudaStream_t st);
-int tc_bwd_raw(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st);
-// CTA-pair (cta_group::2) sweep; returns 1 when the shape is not covered and the caller must use tc_bwd_raw's own kernels
-int tc_bwd_duo(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st);
+int simt_fwd_stats(const bsc_infonce_desc* p, const InfoNceFwdWs& L, char* ws, float* stats, cudaStream_t st);
+int simt_bwd_raw(const bsc_infonce_desc* p, const InfoNceBwdWs& L, char* ws, cudaStream_t st);
+int tc_fwd_stats(const bsc_infonce_desc* p, const InfoNceFwdWs& L, char* ws, float* stats, cudaStream_t st);
+// recomputing CTA-pair sweep (BSC_BWD_RECOMPUTE), d in {256, 512, 768}
+bool tc_bwd_duo_covers(const bsc_infonce_desc* p);
+int tc_bwd_duo(const bsc_infonce_desc* p, const InfoNceBwdWs& L, char* ws, cudaStream_t st);
 int tc_bwd_duo_jsplit(const bsc_infonce_desc* p);
-// stored-weight backward (all rows local): is it used for this problem, and how many bytes of weight spans it keeps
-// 0 = recomputing sweep, 1 = pair sweep per unordered pair + stored spans, 2 = weight matrix + two GEMMs per pair
-// (all rows local), 3 = weight blocks per ordered pair + one GEMM each (this rank's rows of a multi-GPU run)
-int tc_bwd_gstore(const bsc_infonce_desc* p);
-size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* p, int mode);
+// stored-weight backward (BSC_BWD_BLOCKS / BSC_BWD_SCATTER): weight images, then the gradient GEMMs
+size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* p);
 void tc_bwd_matrix_dims(const bsc_infonce_desc* d, int* n_iblk_pad, int* n_j64);
-int tc_bwd_gemm_ksplit(const bsc_infonce_desc* d, int mode);
-int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStream_t st);
-int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_iblk_pad,
-                 int n_j64, int n_pairs, const int* pairs_a, const int* pairs_b, int ordered, cudaStream_t st);
-int tc_bwd_rev(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_pairs,
-               const int* pairs_x, const int* pairs_y, int n_jb, int n_i64, cudaStream_t st);
-int rows_unit_f16_launch(const void* x16, const float* inv, int64_t n, int d, void* out, cudaStream_t st);
-int rows_unit_f16_launch3(const void* const x16[3], const float* const inv[3], int64_t n, int d, void* const out[3],
-                          cudaStream_t st);
+int tc_bwd_gemm_kparts(const bsc_infonce_desc* d);
+int tc_bwd_weights(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, int* n_pairs, int* pairs_a,
+                   int* pairs_b, cudaStream_t st);
+struct ScatterDst {
+  float* peer[kMaxPeers];  // exchange buffer of every rank (index = rank), [world src][3][n_local][d] float
+  int world, rank;
+};
+int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, int n_pairs, const int* pairs_a,
+                 const int* pairs_b, const ScatterDst& dst, cudaStream_t st);
+int rows_unit_f16_launch3(const void* const x16[3], const float* const inv[3], int64_t row0, int64_t n, int d,
+                          void* const out[3], cudaStream_t st);
 struct ReduceJob {
   const float* part;
   int nparts;

@@ -129,49 +129,53 @@ int rows_to_f16_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx
   return BSC_OK;
 }
 
-// fp16 unit rows from the scaled fp16 rows: out = half(x16 * inv).  B operand of the gradient GEMMs (tc_bwd3.cu).
-// blockIdx.y = modality (absent ones have a null source).
+// fp16 unit rows of rows [row0, row0 + n) from the scaled fp16 rows: out[l] = half(x16[row0 + l] * inv[row0 + l]).
+// B operand of the MN-major gradient GEMMs (tc_bwd3.cu).  blockIdx.y = modality (absent ones have a null source).
+// 8 elements (16 bytes) per thread and pass.
 struct UnitRowsArgs {
-  const __half2* x[3];
+  const uint4* x[3];
   const float* inv[3];
-  __half2* out[3];
+  uint4* out[3];
 };
 
-__global__ void __launch_bounds__(256) rows_unit_f16_kernel(const UnitRowsArgs a, int64_t n, int d2) {
-  const __half2* __restrict__ x = a.x[blockIdx.y];
+__global__ void __launch_bounds__(256) rows_unit_f16_kernel(const UnitRowsArgs a, int64_t row0, int64_t n, int d8) {
+  const uint4* __restrict__ x = a.x[blockIdx.y];
   if (x == nullptr) return;
-  const float* __restrict__ inv = a.inv[blockIdx.y];
-  __half2* __restrict__ out = a.out[blockIdx.y];
-  const int64_t total = n * (int64_t)d2;
+  const float* __restrict__ inv = a.inv[blockIdx.y] + row0;
+  uint4* __restrict__ out = a.out[blockIdx.y];
+  x += row0 * d8;
+  const int64_t total = n * (int64_t)d8;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const float s = inv[i / d2];
-    const float2 v = __half22float2(x[i]);
-    out[i] = __floats2half2_rn(v.x * s, v.y * s);
+    const float s = inv[i / d8];
+    uint4 v = x[i];
+    __half2* h = reinterpret_cast<__half2*>(&v);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const float2 f = __half22float2(h[t]);
+      h[t] = __floats2half2_rn(f.x * s, f.y * s);
+    }
+    out[i] = v;
   }
 }
 
-int rows_unit_f16_launch3(const void* const x16[3], const float* const inv[3], int64_t n, int d, void* const out[3],
-                          cudaStream_t st) {
+int rows_unit_f16_launch3(const void* const x16[3], const float* const inv[3], int64_t row0, int64_t n, int d,
+                          void* const out[3], cudaStream_t st) {
   if (n == 0) return BSC_OK;
-  BSC_REQUIRE(d % 2 == 0, BSC_EUNSUPPORTED, "rows_unit_f16: odd d");
+  BSC_REQUIRE(d % 8 == 0, BSC_EUNSUPPORTED, "rows_unit_f16: d %% 8 != 0");
   UnitRowsArgs a{};
+  bool any = false;
   for (int m = 0; m < 3; ++m) {
-    a.x[m] = (const __half2*)x16[m];
+    a.x[m] = out[m] ? (const uint4*)x16[m] : nullptr;
     a.inv[m] = inv[m];
-    a.out[m] = (__half2*)out[m];
+    a.out[m] = (uint4*)out[m];
+    any = any || a.x[m] != nullptr;
   }
-  const int64_t total = n * (int64_t)(d / 2);
+  if (!any) return BSC_OK;
+  const int64_t total = n * (int64_t)(d / 8);
   const unsigned gx = (unsigned)((total + 255) / 256 > 148 * 8 ? 148 * 8 : (total + 255) / 256);
-  rows_unit_f16_kernel<<<dim3(gx, 3), 256, 0, st>>>(a, n, d / 2);
+  rows_unit_f16_kernel<<<dim3(gx, 3), 256, 0, st>>>(a, row0, n, d / 8);
   BSC_LAUNCH_CHECK("rows_unit_f16_kernel");
   return BSC_OK;
-}
-
-int rows_unit_f16_launch(const void* x16, const float* inv, int64_t n, int d, void* out, cudaStream_t st) {
-  const void* xs[3] = {x16, nullptr, nullptr};
-  const float* is[3] = {inv, nullptr, nullptr};
-  void* os[3] = {out, nullptr, nullptr};
-  return rows_unit_f16_launch3(xs, is, n, d, os, st);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -721,19 +725,14 @@ __global__ void __launch_bounds__(256) combine_kernel(CombineArgs a) {
   for (int q = 0; q < 3; ++q) mcount += (a.present_mask >> q) & 1;
   const float c = 1.0f / ((float)a.n_global * (float)(mcount * (mcount - 1)));
   const float cs = c * a.scale;
-  // raw0 / raw1 are the sweeps against the first / second other present modality
-  float inv_gs[2] = {0.f, 0.f};
-  {
-    int slot = 0;
-    for (int y = 0; y < 3; ++y)
-      if (y != m && ((a.present_mask >> y) & 1)) inv_gs[slot++] = a.gsbuf[2 * pair_id(m, y) + 1];
-  }
+  // slot 0 / 1 hold the partial sums against the first / second other present modality
+  const CombineSrc s0src = a.src[m][0], s1src = a.src[m][1];
+  const float inv_gs[2] = {a.gsbuf[s0src.gs_index], a.n_slots > 1 ? a.gsbuf[s1src.gs_index] : 0.f};
   const float gout = a.grad_out[0];
-  const T* xr = (const T*)a.x[m] + il * a.ldx;
-  T* gr = (T*)a.grad[m] + il * a.ldx;
-  const int64_t part_stride = a.n_local * (int64_t)a.d;
-  const float* raw0 = a.raw[m] + il * (int64_t)a.d;
-  const float* raw1 = raw0 + a.n_parts * part_stride;
+  const T* xr = (const T*)a.x[m] + il * a.ldx[m];
+  T* gr = (T*)a.grad[m] + il * (int64_t)a.d;
+  const float* raw0 = s0src.src + il * (int64_t)a.d;
+  const float* raw1 = a.n_slots > 1 ? s1src.src + il * (int64_t)a.d : raw0;
 
   float ss = 0.f;
   for (int cidx = lane; cidx < a.d; cidx += 32) {
@@ -747,11 +746,11 @@ __global__ void __launch_bounds__(256) combine_kernel(CombineArgs a) {
 
   auto ghat_at = [&](int cidx) -> float {
     float s0 = raw0[cidx];
-    for (int q = 1; q < a.n_parts; ++q) s0 += raw0[q * part_stride + cidx];  // fixed order: deterministic
+    for (int q = 1; q < s0src.nparts; ++q) s0 += raw0[q * s0src.stride + cidx];  // fixed order: deterministic
     float raw = s0 * inv_gs[0];
     if (a.n_slots > 1) {
       float s1 = raw1[cidx];
-      for (int q = 1; q < a.n_parts; ++q) s1 += raw1[q * part_stride + cidx];
+      for (int q = 1; q < s1src.nparts; ++q) s1 += raw1[q * s1src.stride + cidx];
       raw = fmaf(s1, inv_gs[1], raw);
     }
     return cs * raw;
@@ -820,18 +819,13 @@ __global__ void __launch_bounds__(256) combine_rows4_kernel(CombineArgs a) {
   for (int q = 0; q < 3; ++q) mcount += (a.present_mask >> q) & 1;
   const float c = 1.0f / ((float)a.n_global * (float)(mcount * (mcount - 1)));
   const float cs = c * a.scale;
-  float inv_gs[2] = {0.f, 0.f};
-  {
-    int slot = 0;
-    for (int y = 0; y < 3; ++y)
-      if (y != m && ((a.present_mask >> y) & 1)) inv_gs[slot++] = a.gsbuf[2 * pair_id(m, y) + 1];
-  }
+  const CombineSrc s0src = a.src[m][0], s1src = a.src[m][1];
+  const float inv_gs[2] = {a.gsbuf[s0src.gs_index], a.n_slots > 1 ? a.gsbuf[s1src.gs_index] : 0.f};
   const float gout = a.grad_out[0];
-  const T* xr = (const T*)a.x[m] + il * a.ldx + lane * 4;
-  T* gr = (T*)a.grad[m] + il * a.ldx + lane * 4;
-  const int64_t part_stride = a.n_local * (int64_t)a.d;
-  const float* raw0 = a.raw[m] + il * (int64_t)a.d + lane * 4;
-  const float* raw1 = raw0 + a.n_parts * part_stride;
+  const T* xr = (const T*)a.x[m] + il * a.ldx[m] + lane * 4;
+  T* gr = (T*)a.grad[m] + il * (int64_t)a.d + lane * 4;
+  const float* raw0 = s0src.src + il * (int64_t)a.d + lane * 4;
+  const float* raw1 = a.n_slots > 1 ? s1src.src + il * (int64_t)a.d + lane * 4 : raw0;
   const int nv = a.d >> 7;
 
   float x[NV][4], g[NV][4];
@@ -843,17 +837,17 @@ __global__ void __launch_bounds__(256) combine_rows4_kernel(CombineArgs a) {
     if (v >= nv) continue;
     float s0[4], s1[4] = {0.f, 0.f, 0.f, 0.f};
     load4<float>(raw0 + v * 128, s0);
-    for (int q = 1; q < a.n_parts; ++q) {  // fixed order: deterministic
+    for (int q = 1; q < s0src.nparts; ++q) {  // fixed order: deterministic
       float t[4];
-      load4<float>(raw0 + q * part_stride + v * 128, t);
+      load4<float>(raw0 + q * s0src.stride + v * 128, t);
 #pragma unroll
       for (int e = 0; e < 4; ++e) s0[e] += t[e];
     }
     if (a.n_slots > 1) {
       load4<float>(raw1 + v * 128, s1);
-      for (int q = 1; q < a.n_parts; ++q) {
+      for (int q = 1; q < s1src.nparts; ++q) {
         float t[4];
-        load4<float>(raw1 + q * part_stride + v * 128, t);
+        load4<float>(raw1 + q * s1src.stride + v * 128, t);
 #pragma unroll
         for (int e = 0; e < 4; ++e) s1[e] += t[e];
       }
@@ -891,10 +885,12 @@ __global__ void __launch_bounds__(256) combine_rows4_kernel(CombineArgs a) {
 
 template <typename T>
 static bool combine_rows4_ok(const CombineArgs& a) {
-  if (a.d % 128 != 0 || a.d > 1024 || a.ldx % 4 != 0) return false;
+  if (a.d % 128 != 0 || a.d > 1024) return false;
   for (int m = 0; m < 3; ++m) {
     if (a.x[m] == nullptr) continue;
-    if (((uintptr_t)a.x[m] | (uintptr_t)a.grad[m]) % (4 * sizeof(T)) != 0 || (uintptr_t)a.raw[m] % 16 != 0) return false;
+    if (a.ldx[m] % 4 != 0 || ((uintptr_t)a.x[m] | (uintptr_t)a.grad[m]) % (4 * sizeof(T)) != 0) return false;
+    for (int sl = 0; sl < a.n_slots; ++sl)
+      if ((uintptr_t)a.src[m][sl].src % 16 != 0 || a.src[m][sl].stride % 4 != 0) return false;
   }
   return true;
 }

@@ -270,7 +270,7 @@ __global__ void topk_init_kernel(float* s, int64_t* i, int64_t n) {
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
-int simt_fwd_stats(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, float* stats, cudaStream_t st) {
+int simt_fwd_stats(const bsc_infonce_desc* p, const InfoNceFwdWs& L, char* ws, float* stats, cudaStream_t st) {
   const int64_t N = p->n_global;
   int pair = 0;
   int npairs_done = 0;
@@ -308,7 +308,7 @@ int simt_fwd_stats(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, floa
   return sum_rows_launch((float*)(ws + L.rowpart), npairs_done, L.n_local_pad, p->n_local, 1.0f, stats + 6 * N, st);
 }
 
-int simt_bwd_raw(const bsc_infonce_desc* p, const InfoNceWs& L, char* ws, cudaStream_t st) {
+int simt_bwd_raw(const bsc_infonce_desc* p, const InfoNceBwdWs& L, char* ws, cudaStream_t st) {
   const int64_t N = p->n_global;
   const float* uv = (const float*)(ws + L.uv);
   float* g = (float*)(ws + L.gscratch);

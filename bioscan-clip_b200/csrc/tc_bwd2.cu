@@ -29,8 +29,6 @@
 //   g_free[c] (CTA c) commit multicast 1<<c after the grad MMAs of tile 2s+c
 //   acc_full  (each)  commit multicast 0b11          acc_free (L) 16
 // Warp roles (384 threads): 0 TMA producer, 1 MMA issuer (L) / forwarder (CTA 1), 2 TMEM allocator, 4..11 epilogue.
-#include <cstdlib>
-
 #include "tc_common.cuh"
 
 namespace bsc {
@@ -62,11 +60,6 @@ struct DuoParams {
   const float* gsbuf;   // [6][2]
   const float* inv[3];
   float* dxraw;         // [3][2][jsplit][n_local][d]
-  // stored-weight mode (all rows local, one item list over the UNORDERED pairs): every weight span is also copied to
-  // gimg[(xy * 2 n_steps + j tile) * n_i64 + (2 iblk + h)][16 KB] for tc_bwd_rev_kernel (tc_bwd3.cu); null = off
-  uint8_t* gimg;
-  int n_i64;
-  int dbg_nostore;  // experiment knob (BSC_DBG_NOSTORE=1): stored-weight item list without the copies (results invalid)
 };
 
 // item -> (ordered pair, row block, part of the column sweep); steps [s_lo, s_hi) of part `part`
@@ -405,24 +398,6 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
             ptx::bulk_copy_to_peer(peer_dst, dst_local + piece, 4096u, ship_bar);
           }
         }
-        if (p.gimg != nullptr && p.dbg_nostore != 1) {
-          // The same bytes at the same offsets of the span's image in HBM: the warp reads its own 4 KB piece back from
-          // shared memory so that every store instruction covers 512 contiguous bytes, after the hand-over above.
-          // Measured (N = 32768, sweep alone): 8.4 ms without the stores, 8.7 ms with the read-back only, 10.2-10.6 ms
-          // with the stores -- the same for a bulk copy out of shared memory, for 16-byte stores from registers and for
-          // stores that hit one L2-resident buffer: bytes LEAVING the SM slow the pair MMAs, whatever their route.
-          const int64_t span = ((int64_t)xy * (2 * p.n_steps) + (2 * s + (int)crank)) * p.n_i64 + (2 * iblk + h);
-          uint8_t* gdst = p.gimg + span * GSPAN + piece + lane * 16;
-          const uint32_t src = dst_local + piece + lane * 16;
-#pragma unroll
-          for (int t = 0; t < 8; ++t) {
-            uint4 v;
-            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
-                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                         : "r"(src + t * 512));
-            __stcs(reinterpret_cast<uint4*>(gdst + t * 512), v);
-          }
-        }
       }
 
       // ---- drain: lane = d (this CTA's 128 of every 256-block), column = i ----
@@ -463,83 +438,25 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_duo_kernel(const __grid_constan
   }
 }
 
-int sm_count2() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
-
 }  // namespace
 
-// measured on 2 GPUs (N = 32768): weight blocks per ordered pair + K-major GEMMs 7.4 ms against 8.6 ms for the pair sweep
-// (same 24 n N D executed; the GEMM kernels run closer to the tensor peak), step 11.96 -> 10.49 ms
-constexpr int kMultiGpuDefaultMode = 3;
-
-static bool duo_covers(const bsc_infonce_desc* d) {
-  static const bool enabled = []() {
-    const char* e = getenv("BSC_BWD_DUO");
-    return !(e && e[0] == '0');
-  }();
-  return enabled && d->mode == BSC_MODE_TC16 && d->x16_dtype == BSC_F16 && d->d % 256 == 0 && d->d <= 768 &&
-         sm_count2() >= 2;
-}
-
-// Stored-weight backward: with all rows on this GPU the weight matrix of an unordered pair serves both directions, so
-// the sweep runs once per unordered pair, copies its fp16 weight spans to HBM (2 N^2 bytes per pair) and a plain GEMM
-// (tc_bwd3.cu) forms the other side.  BSC_BWD_GSTORE=0 turns it off; spans above BSC_BWD_GSTORE_GB (default 48) too.
-size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* d, int mode) {
-  int m = 0;
-  for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
-  const size_t pairs = (size_t)(m * (m - 1) / 2);
-  if (mode >= 2) {
-    int n_iblk_pad, n_j64;
-    tc_bwd_matrix_dims(d, &n_iblk_pad, &n_j64);
-    return (mode == 3 ? 2 : 1) * pairs * (size_t)n_iblk_pad * (size_t)n_j64 * GSPAN;
-  }
-  const size_t n_iblk = (size_t)((d->n_local + BM - 1) / BM);
-  const size_t n_steps = (size_t)(((d->n_global + BN - 1) / BN + 1) / 2);
-  return pairs * (2 * n_steps) * (2 * n_iblk) * GSPAN;
-}
-
-// BSC_BWD_GSTORE = 0 | 1 | 2 | 3 picks the mode where it applies (1 and 2 need all rows local, 3 is their multi-GPU
-// counterpart); default: 2 on one GPU, BSC_BWD_MULTI (0 or 3, default below) otherwise.  Weight storage above
-// BSC_BWD_GSTORE_GB (default 48) falls back to the recomputing sweep.
-int tc_bwd_gstore(const bsc_infonce_desc* d) {
-  if (!duo_covers(d)) return 0;
-  const bool all_local = d->n_local == d->n_global && d->row0 == 0;
-  int mode = all_local ? 2 : kMultiGpuDefaultMode;
-  const char* e = getenv("BSC_BWD_GSTORE");
-  if (e && e[0] >= '0' && e[0] <= '3') mode = e[0] - '0';
-  if (all_local && mode == 3) mode = 2;
-  if (!all_local && (mode == 1 || mode == 2)) mode = 3;
-  if (mode == 0 || d->n_local == 0) return 0;
-  const char* g = getenv("BSC_BWD_GSTORE_GB");
-  const double cap = (g ? atof(g) : 48.0) * 1073741824.0;
-  return (double)tc_bwd_gimg_bytes(d, mode) <= cap ? mode : 0;
+// The recomputing sweep (BSC_BWD_RECOMPUTE): S is formed once more per ORDERED pair and nothing N^2-sized reaches HBM.
+bool tc_bwd_duo_covers(const bsc_infonce_desc* d) {
+  return d->mode == BSC_MODE_TC16 && d->x16_dtype == BSC_F16 && d->d % 256 == 0 && d->d <= 768 && device_sm_count() >= 2;
 }
 
 // In how many parts to cut every (ordered pair, row block) column sweep: the clusters take whole items, so with few
 // row blocks (n_local small: many ranks) ceil(items / clusters) wastes up to a whole sweep.  Cost model per item:
 // steps * (cycles per step) + a fixed fill / drain cost; pick the split in {1, 2, 4, 8} with the lowest makespan.
 int tc_bwd_duo_jsplit(const bsc_infonce_desc* d) {
-  if (!duo_covers(d)) return 1;
-  static const int forced = []() {
-    const char* e = getenv("BSC_BWD_JSPLIT");
-    return e ? atoi(e) : 0;
-  }();
+  if (!tc_bwd_duo_covers(d)) return 1;
   int m = 0;
   for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
-  const int64_t items0 = (int64_t)m * (m - 1) / (tc_bwd_gstore(d) == 1 ? 2 : 1) * ((d->n_local + BM - 1) / BM);
+  const int64_t items0 = (int64_t)m * (m - 1) * ((d->n_local + BM - 1) / BM);
   const int64_t steps = ((d->n_global + BN - 1) / BN + 1) / 2;
-  const int clusters = sm_count2() / 2;
+  const int clusters = device_sm_count() / 2;
   if (items0 <= 0 || steps <= 0) return 1;
-  if (forced > 0) return (int)(forced > steps ? steps : forced);
-  // measured on B200 (1 GPU, N = 8192 and 32768, BSC_BWD_JSPLIT = 1, 2, 4, 8): T = K0 + rounds * (steps * c + F) fits
+  // measured on B200 (1 GPU, N = 8192 and 32768, forced splits 1, 2, 4, 8): T = K0 + rounds * (steps * c + F) fits
   // with c = 5.2 us (9.9 k cycles) per step and F = 10 us (19 k cycles) per item; K0 (86 us per launch) is common
   const double step_cost = 9900.0, item_cost = 19000.0;
   int best = 1;
@@ -556,10 +473,8 @@ int tc_bwd_duo_jsplit(const bsc_infonce_desc* d) {
   return best;
 }
 
-// Returns BSC_OK when the paired kernel ran, 1 when this shape is not covered (caller falls back), < 0 on error.
-int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStream_t st) {
-  if (!duo_covers(d)) return 1;
-  if (L.bwd_gstore >= 2) return tc_bwd_matrix(d, L, ws, st);
+int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, cudaStream_t st) {
+  BSC_REQUIRE(tc_bwd_duo_covers(d), BSC_EUNSUPPORTED, "the recomputing sweep covers d in {256, 512, 768} (got %d)", d->d);
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
   DuoParams p{};
   int first = -1;
@@ -577,19 +492,16 @@ int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
       p.tmap128[a] = p.tmap128[first];
       p.tmap64[a] = p.tmap64[first];
     }
-  const bool gstore = L.bwd_gstore == 1;
   int n = 0;
   for (int x = 0; x < 3; ++x) {
     if (!d->xh[x]) continue;
     int slot = 0;
     for (int y = 0; y < 3; ++y) {
       if (y == x || !d->xh[y]) continue;
-      if (!gstore || y > x) {  // stored-weight mode: unordered pairs x < y; y's side comes from tc_bwd_rev
-        p.xy_x[n] = x;
-        p.xy_y[n] = y;
-        p.xy_slot[n] = slot;
-        ++n;
-      }
+      p.xy_x[n] = x;
+      p.xy_y[n] = y;
+      p.xy_slot[n] = slot;
+      ++n;
       ++slot;
     }
   }
@@ -599,7 +511,7 @@ int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
   p.n_steps = (p.n_jtile + 1) / 2;
   p.kblocks = d->d / BK;
   p.nblk = d->d / 256;
-  p.jsplit = L.bwd_jsplit > 0 ? L.bwd_jsplit : 1;
+  p.jsplit = L.kparts > 0 ? L.kparts : 1;
   if (p.jsplit > p.n_steps) p.jsplit = p.n_steps > 0 ? p.n_steps : 1;
   p.num_items = n * p.n_iblk * p.jsplit;
   p.d = d->d;
@@ -613,20 +525,10 @@ int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
   p.rep = d->rep;
   p.gsbuf = (const float*)(ws + L.gs);
   p.dxraw = (float*)(ws + L.dxraw);
-  p.gimg = gstore ? (uint8_t*)(ws + L.gimg) : nullptr;
-  p.n_i64 = 2 * p.n_iblk;
-  {
-    const char* e = getenv("BSC_DBG_NOSTORE");
-    p.dbg_nostore = e ? atoi(e) : 0;
-  }
   if (p.num_items == 0 || p.n_jtile == 0) return BSC_OK;
 
-  static bool attr_done = false;
-  if (!attr_done) {
-    BSC_CUDA(cudaFuncSetAttribute(tc_bwd_duo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DUO_SMEM_BYTES));
-    attr_done = true;
-  }
-  int clusters = sm_count2() / 2;
+  BSC_SET_SMEM_ONCE(tc_bwd_duo_kernel, DUO_SMEM_BYTES);
+  int clusters = device_sm_count() / 2;
   if (clusters > p.num_items) clusters = p.num_items;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)(2 * clusters));
@@ -644,23 +546,6 @@ int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStre
   BSC_CUDA(cudaLaunchKernelEx(&cfg, tc_bwd_duo_kernel, p));
   timing_end(1, st);
   BSC_LAUNCH_CHECK("tc_bwd_duo_kernel");
-  if (gstore) {
-    // unit rows of every modality that is the x side of a pair, then the y sides from the stored spans
-    const void* xunit[3] = {nullptr, nullptr, nullptr};
-    int px[3], py[3];
-    for (int q = 0; q < n; ++q) {
-      px[q] = p.xy_x[q];
-      py[q] = p.xy_y[q];
-      const int a = px[q];
-      if (!xunit[a]) {
-        void* dst = ws + L.xunit + (size_t)a * d->n_global * d->d * 2;
-        int rc = rows_unit_f16_launch(d->xh[a], d->inv[a], d->n_global, d->d, dst, st);
-        if (rc) return rc;
-        xunit[a] = dst;
-      }
-    }
-    return tc_bwd_rev(d, L, ws, xunit, n, px, py, p.n_steps, p.n_i64, st);
-  }
   return BSC_OK;
 }
 

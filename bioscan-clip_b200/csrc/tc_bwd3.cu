@@ -1,20 +1,28 @@
-// Gradient GEMMs of the InfoNCE backward from STORED fp16 weight images (tcgen05.mma.cta_group::2 on CTA pairs).
+// Gradient GEMMs of the InfoNCE backward from STORED fp16 weight blocks (tcgen05.mma.cta_group::2 on CTA pairs), fused
+// with the reduce-scatter of the partial gradients over NVLink peer memory.
 //
-// The weight matrix of an unordered modality pair (x, y) is one matrix:  g_ij = e_ij (u_i + v_j) - 2 T_ij  gives both
-// dXhat = G * Yhat and dYhat = G^T * Xhat.  Who writes the images (16 KB each, 128 rows x 64 fp16, 128B-swizzled):
-//   mode 2 / 3  tc_sim_kernel<EPI_WEIGHTS> (tc_sim.cu): G[128 i][64 j], one block per unordered pair (all rows local)
-//               or per ordered pair (this rank's rows of a multi-GPU run);
-//   mode 1      the pair sweep (tc_bwd2.cu), which keeps dXhat in TMEM and streams the spans [128 j][64 i] its grad MMAs
-//               read; a stored weight then carries gs(x,y) / |y_j| and the epilogue here undoes that per row.
-// One persistent kernel runs every job  out[M rows][d] = A[M][K] * unit_in[K][d]:
-//   A = an image as it lies in HBM (raw TMA copy, no swizzle mode): K-major when the image rows are the output rows,
-//       MN-major (halves of two images) when they are the reduction index -- G^T * Xhat from the SAME images;
-//   B = 64 fp16 unit rows (d contiguous = MN-major), each CTA its half of the accumulator's d columns;
-//   accumulators [128 lanes][256 (+128) columns] fp32 in TMEM; epilogue scales a row by gs_pair / gs_stored and writes
-//   dxraw for combine_kernel.
-// Executed work of the backward on one GPU: 6 N^2 D (weights) + 12 N^2 D (here) instead of 24 N^2 D.
+// tc_sim_kernel<EPI_WEIGHTS> (tc_sim.cu) wrote, for every pair q = (a, b), the block G_q[local rows i][all columns j],
+//     g_ij = gs(a,b) (e_ij (u_i + v_j) - 2 T_ij) / |b_j|,
+// as 128B-swizzled images [128 i][64 j] (16 KB each).  One persistent kernel runs every gradient GEMM from them:
+//   K-major job   dA[local i][d]  = sum_j G[i][j] * B16[j][d]      A = an image as it lies in HBM (raw TMA copy), K = j over
+//                                   ALL rows of b (the gathered fp16 rows: 1/|b_j| is in the weights, operands exact)
+//   MN-major job  dB[all j][d]    = sum_i G[i][j] * Aunit[i][d]    A = halves of two images read MN-major, K = i over the
+//                                   LOCAL rows only; B = fp16 unit rows of the local rows of a.  Each rank obtains a
+//                                   PARTIAL sum for every row j of the global batch; the epilogue stores row block q of
+//                                   the result straight into rank q's exchange buffer (slot = this rank): a GEMM whose
+//                                   epilogue is the reduce-scatter.  combine (prep.cu) adds the W slots in rank order.
+// BSC_BWD_BLOCKS (no peer memory): ordered pairs, K-major jobs only.  BSC_BWD_SCATTER: unordered pairs, both jobs --
+// every rank executes 6 + 12 n N D in the backward, what a single GPU executes for its n = N rows.
+//   B operand = 64 rows x {256 | 384} d (MN-major), each CTA its half of the accumulator's d columns;
+//   accumulators [128 lanes][256 (+128) columns] fp32 in TMEM.
+// Work items are equal in size by construction (the K-major jobs are K-split `world` ways, so that both kinds run n/64
+// K blocks) and are dealt to the CTA pairs from a host-built schedule that alternates rounds of scattered and local
+// items: the NVLink stores are spread over the whole kernel and over all SMs, and rank r starts with the row blocks
+// of rank r+1 so that no two ranks target the same peer at the same time.
 // Warp roles (384 threads): 0 TMA producer, 1 MMA issuer (leader CTA), 2 TMEM allocator, 4..11 epilogue.
-#include <cstdlib>
+#include <algorithm>
+#include <cstring>
+#include <vector>
 
 #include "tc_common.cuh"
 
@@ -25,15 +33,17 @@ int make_tmap_raw128(CUtensorMap* out, const void* base, int64_t rows, int box_r
 namespace {
 
 constexpr int BK = 64;
-constexpr int A_BYTES = 16384;            // one stored span
-constexpr int B_BOX = 8192;               // [64 i][64 d] fp16
+constexpr int A_BYTES = 16384;            // one stored image
+constexpr int B_BOX = 8192;               // [64 rows][64 d] fp16
 constexpr int TMEM_COLS = 512;
 constexpr int MAX_STAGES = 6;
+constexpr int MAX_JOBS = 6;
+constexpr int MAX_SCHED = 6144;           // schedule entries carried in the kernel parameters (24 KB)
+constexpr int STG_BYTES = 2048;           // per epilogue warp: 32 rows x 16 floats staged for coalesced scatter stores
 // WIDE = 0: 256 d columns per item, one accumulator (N = 256), TMEM double-buffered over items, 6 x 32 KB stages.
 // WIDE = 1: 384 d columns per item, two accumulators (N = 256 and N = 128) fed by the SAME A tile -- d = 768 is covered
-//           by two items instead of three, i.e. the weight images are read twice per GEMM instead of three times (the
-//           three sibling clusters of WIDE = 0 share them through L2 only partly: 25-31 GB of DRAM reads per launch
-//           where 2 x 2 x 6.4 GB are needed); one TMEM buffer (384 of 512 columns), 5 x 40 KB stages.
+//           by two items instead of three, i.e. the weight images are read twice per GEMM instead of three times;
+//           one TMEM buffer (384 of 512 columns), 5 x 40 KB stages.
 template <int WIDE>
 struct Cfg {
   static constexpr int BN = WIDE ? 384 : 256;
@@ -41,26 +51,32 @@ struct Cfg {
   static constexpr int STAGE_BYTES = A_BYTES + NBOX * B_BOX;
   static constexpr int STAGES = WIDE ? 5 : 6;
   static constexpr int NBUF = WIDE ? 1 : 2;
-  static constexpr size_t SMEM = 1024 + (size_t)STAGES * STAGE_BYTES + 256;
+  static constexpr size_t SMEM = 1024 + (size_t)STAGES * STAGE_BYTES + 8 * STG_BYTES + 256;
 };
+static_assert(Cfg<1>::SMEM <= 232448 && Cfg<0>::SMEM <= 232448, "gradient GEMM kernel exceeds 227 KB of shared memory");
 
 struct RevParams {
   CUtensorMap tmap_g128;  // gimg as [rows][64] fp16, box 64 x 128, no swizzle (the bytes are already swizzled)
   CUtensorMap tmap_g64;   // same, box 64 x 64: half an image (MN-major jobs)
-  CUtensorMap tmap_u[3];  // unit rows per modality, box 64 d x 64 rows, SWIZZLE_128B
-  // job = one gradient GEMM  out[M rows][d] = A[M][K] * unit_in[K][d];  image(pair, r, c) = (pair * img_r + r) * img_c + c
+  CUtensorMap tmap_in[MAX_JOBS];  // B operand rows of every job, box 64 d x 64 rows, SWIZZLE_128B
+  // job = one gradient GEMM  out[M rows][d] = A[M][K] * in[K][d];  image(pair, r, c) = (pair * img_r + r) * img_c + c
   //   K-major job:  A block (128 rows mblk, 64 K kb)  = image(pair, mblk, kb)
   //   MN-major job: A block (128 rows mblk, 64 K kb)  = rows 64 (kb & 1) .. + 63 of images (pair, kb >> 1, 2 mblk + {0, 1})
   int n_jobs;
-  int job_pair[6], job_mn[6], job_out[6], job_in[6], job_slot[6], job_nk[6];
-  int job_fnum[6], job_fden[6], job_finv[6];  // epilogue row factor gsbuf[fnum] * gsbuf[fden] (/ inv_out[row] if finv)
+  int job_pair[MAX_JOBS], job_mn[MAX_JOBS], job_nk[MAX_JOBS], job_kparts[MAX_JOBS];
+  int64_t job_rows[MAX_JOBS];      // valid output rows
+  float* job_out[MAX_JOBS];        // local jobs: [kparts][rows][d]; scattered jobs: null
+  int job_xslot[MAX_JOBS];         // scattered jobs: pair slot inside the exchange buffers
+  int job_fnum[MAX_JOBS], job_fden[MAX_JOBS];  // epilogue row factor gsbuf[fnum] * gsbuf[fden] ...
+  const float* job_finv[MAX_JOBS];             // ... / finv[row] when not null
   int img_r, img_c;
-  int n_mb, nchunk, kparts, num_items, d;
-  int wide;  // 384-wide items (two accumulators), d % 384 == 0
-  int64_t n;
-  const float* inv[3];
+  int num_items, d;
+  // scatter destinations: exchange buffer of rank q = float [world][n_xslots][n_local][d]
+  float* peer[kMaxPeers];
+  int world, rank, n_xslots;
+  int64_t n_local;
   const float* gsbuf;
-  float* dxraw;  // [3][2][kparts][n][d]
+  uint32_t sched[MAX_SCHED];  // item -> job (3 bits) | d chunk (3) | K part (8) | 256-row block (18)
 };
 
 struct __align__(8) RevTail {
@@ -74,17 +90,20 @@ struct __align__(8) RevTail {
 
 static_assert(sizeof(RevTail) <= 256, "tail budget");
 
+__host__ __device__ inline uint32_t pack_item(int job, int c, int part, int mb) {
+  return (uint32_t)job | ((uint32_t)c << 3) | ((uint32_t)part << 6) | ((uint32_t)mb << 14);
+}
+
 __device__ __forceinline__ void rev_item(const RevParams& p, int item, int& job, int& mb, int& part, int& c, int& kb_lo,
                                          int& kb_hi) {
-  c = item % p.nchunk;  // the d chunks of one (row block, K part) run on neighbouring clusters: they share A through L2
-  int rest = item / p.nchunk;
-  part = rest % p.kparts;
-  rest /= p.kparts;
-  mb = rest % p.n_mb;
-  job = rest / p.n_mb;
-  const int nk = p.job_nk[job];
-  kb_lo = (int)((int64_t)part * nk / p.kparts);
-  kb_hi = (int)((int64_t)(part + 1) * nk / p.kparts);
+  const uint32_t w = p.sched[item];
+  job = (int)(w & 7u);
+  c = (int)((w >> 3) & 7u);
+  part = (int)((w >> 6) & 255u);
+  mb = (int)(w >> 14);
+  const int nk = p.job_nk[job], kp = p.job_kparts[job];
+  kb_lo = (int)((int64_t)part * nk / kp);
+  kb_hi = (int)((int64_t)(part + 1) * nk / kp);
 }
 
 template <int WIDE>
@@ -96,7 +115,8 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
   const uint32_t ring = (raw_addr + 1023u) & ~1023u;
-  RevTail* tail = reinterpret_cast<RevTail*>(smem_raw + (ring - raw_addr) + (size_t)STAGES * STAGE_BYTES);
+  uint8_t* stg_base = smem_raw + (ring - raw_addr) + (size_t)STAGES * STAGE_BYTES;
+  RevTail* tail = reinterpret_cast<RevTail*>(stg_base + 8 * STG_BYTES);
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t crank = ptx::cluster_ctarank();
@@ -117,7 +137,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&p.tmap_g128);
     ptx::prefetch_tmap(&p.tmap_g64);
-    for (int a = 0; a < 3; ++a) ptx::prefetch_tmap(&p.tmap_u[a]);
+    for (int a = 0; a < p.n_jobs; ++a) ptx::prefetch_tmap(&p.tmap_in[a]);
   }
   if (warp == 2) {
     ptx::tmem_alloc_2cta(ptx::smem_u32(&tail->tmem_base), TMEM_COLS);
@@ -136,7 +156,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
       for (int item = item0; item < p.num_items; item += item_step) {
         int job, mb, part, c, kb_lo, kb_hi;
         rev_item(p, item, job, mb, part, c, kb_lo, kb_hi);
-        const CUtensorMap* mu = &p.tmap_u[p.job_in[job]];
+        const CUtensorMap* mu = &p.tmap_in[job];
         const int mblk = 2 * mb + (int)crank;
         const int64_t pair0 = (int64_t)p.job_pair[job] * p.img_r;
         const bool mn = p.job_mn[job] != 0;
@@ -157,6 +177,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
             ptx::tma_load_2d_2cta(sa, &p.tmap_g64, full_l, 0, r0);
             ptx::tma_load_2d_2cta(sa + A_BYTES / 2, &p.tmap_g64, full_l, 0, r0 + 128);
           }
+          // columns past d (d % 256 == 128 leaves the odd CTA's half of the last chunk empty) are zero-filled by TMA
           ptx::tma_load_2d_2cta(sa + A_BYTES, mu, full_l, d0, kb * BK);
           ptx::tma_load_2d_2cta(sa + A_BYTES + B_BOX, mu, full_l, d0 + 64, kb * BK);
           if (WIDE) ptx::tma_load_2d_2cta(sa + A_BYTES + 2 * B_BOX, mu, full_l, d1, kb * BK);
@@ -221,49 +242,82 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
     const int grp = (warp - 4) >> 2;  // column half of the item's accumulators
     constexpr int CPG = BN / 64;      // 32-column chunks per warp group
     const uint32_t empty_l0 = ptx::mapa(ptx::smem_u32(&tail->tmem_empty[0]), 0);
+    uint8_t* stg = stg_base + (warp - 4) * STG_BYTES;
     uint32_t count = 0;
     for (int item = item0; item < p.num_items; item += item_step, ++count) {
       int job, mb, part, c, kb_lo, kb_hi;
       rev_item(p, item, job, mb, part, c, kb_lo, kb_hi);
-      const int mo = p.job_out[job];
       const uint32_t buf = NBUF == 2 ? (count & 1u) : 0u;
       const uint32_t use = NBUF == 2 ? (count >> 1) : count;
-      const int64_t row = ((int64_t)(2 * mb + (int)crank)) * 128 + q * 32 + lane;
+      const int64_t rows = p.job_rows[job];
+      const int64_t row_w0 = ((int64_t)(2 * mb + (int)crank)) * 128 + q * 32;  // first row of this warp
+      const int64_t row = row_w0 + lane;
       float f = 0.f;
-      if (row < p.n) {
+      if (row < rows) {
         f = p.gsbuf[p.job_fnum[job]] * p.gsbuf[p.job_fden[job]];
-        if (p.job_finv[job]) {
-          const float iv = p.inv[mo][row];
+        if (p.job_finv[job] != nullptr) {
+          const float iv = p.job_finv[job][row];
           f = iv > 0.f ? f / iv : 0.f;
         }
       }
-      float* out = p.dxraw + (((int64_t)(mo * 2 + p.job_slot[job]) * p.kparts + part) * p.n + row) * p.d + BN * c;
-      if (kb_hi > kb_lo) {
-        ptx::mbar_wait(ptx::smem_u32(&tail->tmem_full[buf]), use & 1u, 400 + buf);
-        ptx::tc_fence_after();
-      }
+      ptx::mbar_wait(ptx::smem_u32(&tail->tmem_full[buf]), use & 1u, 400 + buf);
+      ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN;
+      float* out_local = p.job_out[job];
+      if (out_local != nullptr) {
+        // ---- local partial sums: every thread stores its own row, 128 contiguous bytes per chunk ----
+        float* out = out_local + ((int64_t)part * rows + row) * p.d + BN * c;
 #pragma unroll 1
-      for (int cc = grp * CPG; cc < grp * CPG + CPG; ++cc) {
-        uint32_t raw[32];
-        if (kb_hi > kb_lo) {
+        for (int cc = grp * CPG; cc < grp * CPG + CPG; ++cc) {
+          uint32_t raw[32];
           ptx::tmem_ld_32x32(taddr + cc * 32, raw);
           ptx::tmem_ld_wait();
-        } else {
+          if (row < rows && BN * c + cc * 32 < p.d) {
+            float4* o4 = reinterpret_cast<float4*>(out + cc * 32);
 #pragma unroll
-          for (int t = 0; t < 32; ++t) raw[t] = 0u;
+            for (int t = 0; t < 8; ++t)
+              o4[t] = make_float4(f * __uint_as_float(raw[4 * t]), f * __uint_as_float(raw[4 * t + 1]),
+                                  f * __uint_as_float(raw[4 * t + 2]), f * __uint_as_float(raw[4 * t + 3]));
+          }
         }
-        if (row < p.n) {
-          float4* o4 = reinterpret_cast<float4*>(out + cc * 32);
+      } else {
+        // ---- scattered partial sums: row j of the global batch belongs to rank j / n_local.  16 columns at a time are
+        // staged through 2 KB of shared memory per warp so that four lanes store the 64 contiguous bytes of one row
+        // (peer stores travel over NVLink: 16-byte stores to 32 different rows would waste most of every packet).
+        // Staging slot of (row r, 16-byte chunk u) = u ^ ((r >> 1) & 3): conflict-free both ways.
+        const int64_t slab = p.n_local * (int64_t)p.d;
+        const int64_t src_off = ((int64_t)p.rank * p.n_xslots + p.job_xslot[job]) * slab + BN * c;
+        const int t4 = lane & 3;
+#pragma unroll 1
+        for (int cc = grp * 2 * CPG; cc < grp * 2 * CPG + 2 * CPG; ++cc) {  // 16-column chunks
+          uint32_t raw[16];
+          ptx::tmem_ld_32x16(taddr + cc * 16, raw);
+          ptx::tmem_ld_wait();
 #pragma unroll
-          for (int t = 0; t < 8; ++t)
-            o4[t] = make_float4(f * __uint_as_float(raw[4 * t]), f * __uint_as_float(raw[4 * t + 1]),
-                                f * __uint_as_float(raw[4 * t + 2]), f * __uint_as_float(raw[4 * t + 3]));
+          for (int u = 0; u < 4; ++u)
+            *reinterpret_cast<float4*>(stg + lane * 64 + ((u ^ ((lane >> 1) & 3)) << 4)) =
+                make_float4(f * __uint_as_float(raw[4 * u]), f * __uint_as_float(raw[4 * u + 1]),
+                            f * __uint_as_float(raw[4 * u + 2]), f * __uint_as_float(raw[4 * u + 3]));
+          __syncwarp();
+          if (BN * c + cc * 16 < p.d) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const int r = 8 * k + (lane >> 2);
+              const int64_t j = row_w0 + r;
+              if (j < rows) {
+                const float4 v = *reinterpret_cast<const float4*>(stg + r * 64 + ((t4 ^ ((r >> 1) & 3)) << 4));
+                const int dest = (int)(j / p.n_local);
+                const int64_t jl = j - (int64_t)dest * p.n_local;
+                *reinterpret_cast<float4*>(p.peer[dest] + src_off + jl * p.d + cc * 16 + t4 * 4) = v;
+              }
+            }
+          }
+          __syncwarp();
         }
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0 && kb_hi > kb_lo) ptx::mbar_arrive_remote_nodata(empty_l0 + buf * 8u);
+      if (lane == 0) ptx::mbar_arrive_remote_nodata(empty_l0 + buf * 8u);
     }
   }
 
@@ -276,31 +330,13 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
   }
 }
 
-int sm_count3() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
-
 }  // namespace
 
-static int rev_launch(RevParams& p, cudaStream_t st) {
+static int rev_launch(RevParams& p, bool wide, cudaStream_t st) {
   if (p.num_items == 0) return BSC_OK;
-  const bool wide = p.wide != 0;
-  static bool attr_done = false;
-  if (!attr_done) {
-    BSC_CUDA(cudaFuncSetAttribute(tc_bwd_rev_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)Cfg<0>::SMEM));
-    BSC_CUDA(cudaFuncSetAttribute(tc_bwd_rev_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)Cfg<1>::SMEM));
-    attr_done = true;
-  }
-  int clusters = sm_count3() / 2;
+  BSC_SET_SMEM_ONCE(tc_bwd_rev_kernel<0>, Cfg<0>::SMEM);
+  BSC_SET_SMEM_ONCE(tc_bwd_rev_kernel<1>, Cfg<1>::SMEM);
+  int clusters = device_sm_count() / 2;
   if (clusters > p.num_items) clusters = p.num_items;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)(2 * clusters));
@@ -324,39 +360,6 @@ static int rev_launch(RevParams& p, cudaStream_t st) {
   return BSC_OK;
 }
 
-static int rev_common(RevParams& p, const bsc_infonce_desc* d, const InfoNceWs& L, char* ws,
-                      const void* const xunit[3], int64_t img_rows) {
-  const int64_t N = d->n_global;
-  int rc = make_tmap_raw128(&p.tmap_g128, ws + L.gimg, img_rows, 128);
-  if (rc) return rc;
-  rc = make_tmap_raw128(&p.tmap_g64, ws + L.gimg, img_rows, 64);
-  if (rc) return rc;
-  int first = -1;
-  for (int a = 0; a < 3; ++a)
-    if (xunit[a]) {
-      rc = make_tmap_2d(&p.tmap_u[a], xunit[a], BSC_F16, N, d->d, 64);
-      if (rc) return rc;
-      if (first < 0) first = a;
-    }
-  BSC_REQUIRE(first >= 0, BSC_EINVAL, "tc_bwd_rev: no unit rows");
-  for (int a = 0; a < 3; ++a) {
-    if (!xunit[a]) p.tmap_u[a] = p.tmap_u[first];
-    p.inv[a] = d->inv[a];
-  }
-  {
-    const char* e = getenv("BSC_BWD_WIDE");  // 0 forces 256-wide items
-    p.wide = (d->d % 384 == 0 && !(e && e[0] == '0')) ? 1 : 0;
-  }
-  p.nchunk = d->d / (p.wide ? 384 : 256);
-  p.kparts = L.bwd_jsplit > 0 ? L.bwd_jsplit : 1;
-  p.d = d->d;
-  p.n = N;
-  p.n_mb = (int)((N + 255) / 256);
-  p.gsbuf = (const float*)(ws + L.gs);
-  p.dxraw = (float*)(ws + L.dxraw);
-  return BSC_OK;
-}
-
 // slot of partner modality `other` among the present modalities other than `m`, ascending
 static int slot_of(const bsc_infonce_desc* d, int m, int other) {
   int slot = 0;
@@ -365,48 +368,22 @@ static int slot_of(const bsc_infonce_desc* d, int m, int other) {
   return slot;
 }
 
-// Stored-span mode (L.bwd_gstore == 1): dYhat of every unordered pair from the spans the pair sweep stored,
-// gimg[(pair * 2 n_steps + j tile) * n_i64 + i64] = [128 j][64 i].  `pairs_x/y` list the pairs in the sweep's order;
-// xunit[a] = fp16 unit rows of modality a (only the x side of a pair is read).
-int tc_bwd_rev(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_pairs,
-               const int* pairs_x, const int* pairs_y, int n_jb, int n_i64, cudaStream_t st) {
-  RevParams p{};
-  int rc = rev_common(p, d, L, ws, xunit, (int64_t)n_pairs * 2 * n_jb * n_i64 * 128);
-  if (rc) return rc;
-  p.img_r = 2 * n_jb;
-  p.img_c = n_i64;
-  p.n_jobs = n_pairs;
-  for (int q = 0; q < n_pairs; ++q) {
-    const int x = pairs_x[q], y = pairs_y[q];
-    p.job_pair[q] = q;
-    p.job_mn[q] = 0;
-    p.job_out[q] = y;
-    p.job_in[q] = x;
-    p.job_slot[q] = slot_of(d, y, x);
-    p.job_nk[q] = n_i64;
-    // a stored weight carries gs(x,y) / |y_j|; combine expects gs(y,x) * sum
-    p.job_fnum[q] = 2 * pair_id(y, x);
-    p.job_fden[q] = 2 * pair_id(x, y) + 1;
-    p.job_finv[q] = 1;
-  }
-  BSC_REQUIRE(p.kparts <= n_i64, BSC_EUNSUPPORTED, "tc_bwd_rev: column split %d exceeds the %d row spans", p.kparts,
-              n_i64);
-  p.num_items = p.n_jobs * p.n_mb * p.kparts * p.nchunk;
-  return rev_launch(p, st);
-}
+static bool rev_wide(const bsc_infonce_desc* d) { return d->d % 384 == 0; }
 
-// K split of the gradient GEMMs (= dxraw parts that combine_kernel sums in a fixed order): the clusters take whole items,
-// so a few hundred items on 74 clusters (many ranks: 192 at 8 GPUs) would leave the last round mostly idle.
-int tc_bwd_gemm_ksplit(const bsc_infonce_desc* d, int mode) {
+// K split of the K-major gradient GEMMs (= local partial sums that combine adds in a fixed order).
+//   SCATTER over W > 1 ranks: W parts, so that a K-major item (N / W / 64 K blocks) is as long as an MN-major item
+//   (n_local / 64 K blocks) and the static round-robin over equal items stays balanced;
+//   otherwise: the split that minimises the makespan when a few hundred items meet 74 clusters.
+int tc_bwd_gemm_kparts(const bsc_infonce_desc* d) {
   int m = 0;
   for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
-  const int64_t jobs = (int64_t)m * (m - 1);  // 2 per unordered pair (mode 2) = 1 per ordered pair (mode 3)
-  const int64_t n_mb = (d->n_local + 255) / 256;
-  const int64_t nchunk = d->d % 384 == 0 ? d->d / 384 : d->d / 256;
-  const int64_t items0 = jobs * n_mb * nchunk;
   const int64_t nk = (d->n_global + 63) / 64;
-  const int clusters = sm_count3() / 2;
-  (void)mode;
+  if (d->bwd_mode == BSC_BWD_SCATTER && d->world > 1) return (int)(d->world < nk ? d->world : nk);
+  const int64_t jobs = (int64_t)m * (m - 1);  // 2 per unordered pair (SCATTER, one GPU) = 1 per ordered pair (BLOCKS)
+  const int64_t n_mb = (d->n_local + 255) / 256;
+  const int64_t nchunk = rev_wide(d) ? d->d / 384 : (d->d + 255) / 256;
+  const int64_t items0 = jobs * n_mb * nchunk;
+  const int clusters = device_sm_count() / 2;
   if (items0 <= 0) return 1;
   int best = 1;
   double best_cost = 1e300;
@@ -423,43 +400,128 @@ int tc_bwd_gemm_ksplit(const bsc_infonce_desc* d, int mode) {
   return best;
 }
 
-// Weight-matrix modes: the gradient GEMMs from the images gimg[(pair * n_iblk_pad + iblk) * n_j64 + j64] = G[128 i][64 j]
-// that tc_bwd_matrix wrote.
-//   mode 2 (all rows local, unordered pairs (x, y)):  dXhat = G * Yunit (A K-major: image rows are i, K runs over j) and
-//                                                     dYhat = G^T * Xunit (A MN-major from the same images, K over i);
-//   mode 3 (ordered pairs (a, b), this rank's rows of a):  dAhat = G_ab * Bunit, K-major only.
-int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, const void* const xunit[3], int n_iblk_pad,
-                 int n_j64, int n_pairs, const int* pairs_a, const int* pairs_b, int ordered, cudaStream_t st) {
-  RevParams p{};
-  int rc = rev_common(p, d, L, ws, xunit, (int64_t)n_pairs * n_iblk_pad * n_j64 * 128);
+// Gradient GEMMs from the images gimg[(pair * n_iblk_pad + iblk) * n_j64 + j64] = G[128 i][64 j] that tc_bwd_weights wrote
+// for the pairs (pairs_a[q], pairs_b[q]): ordered pairs in BSC_BWD_BLOCKS, unordered (a < b) in BSC_BWD_SCATTER.
+int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, int n_pairs, const int* pairs_a,
+                 const int* pairs_b, const ScatterDst& dst, cudaStream_t st) {
+  const bool scatter = L.mode == BSC_BWD_SCATTER;
+  const int64_t N = d->n_global, n = d->n_local;
+  int n_iblk_pad, n_j64;
+  tc_bwd_matrix_dims(d, &n_iblk_pad, &n_j64);
+  static thread_local RevParams p;  // 26 KB: kept off the stack
+  memset(&p, 0, sizeof(p));
+  const int64_t img_rows = (int64_t)n_pairs * n_iblk_pad * n_j64 * 128;
+  int rc = make_tmap_raw128(&p.tmap_g128, ws + L.gimg, img_rows, 128);
   if (rc) return rc;
+  rc = make_tmap_raw128(&p.tmap_g64, ws + L.gimg, img_rows, 64);
+  if (rc) return rc;
+  const bool wide = rev_wide(d);
+  const int BNW = wide ? 384 : 256;
+  const int nchunk = (d->d + BNW - 1) / BNW;
+  BSC_REQUIRE(nchunk <= 8, BSC_EUNSUPPORTED, "tc_bwd_gemms: d = %d needs more than 8 column chunks", d->d);
   p.img_r = n_iblk_pad;
   p.img_c = n_j64;
-  p.n = d->n_local;  // output rows (== n_global in mode 2)
-  p.n_mb = (int)((d->n_local + 255) / 256);
-  const int nk64 = (int)((d->n_global + 63) / 64);
-  int job = 0;
-  for (int q = 0; q < n_pairs; ++q) {
-    const int x = pairs_a[q], y = pairs_b[q];
-    for (int side = 0; side < (ordered ? 1 : 2); ++side, ++job) {
-      const int mo = side == 0 ? x : y, mi = side == 0 ? y : x;
-      p.job_pair[job] = q;
-      p.job_mn[job] = side;
-      p.job_out[job] = mo;
-      p.job_in[job] = mi;
-      p.job_slot[job] = slot_of(d, mo, mi);
-      p.job_nk[job] = nk64;  // K blocks of 64 columns j (side 0) / 64 rows i (side 1, where n_local == n_global)
-      p.job_fnum[job] = 2 * pair_id(mo, mi);
-      // mode 2: weights scaled by gsbuf[16], combine expects gs(mo, mi); mode 3: the weights already carry gs(mo, mi)
-      p.job_fden[job] = ordered ? 2 * pair_id(mo, mi) + 1 : 17;
-      p.job_finv[job] = 0;
+  p.d = d->d;
+  p.gsbuf = (const float*)(ws + L.gs);
+  p.world = dst.world;
+  p.rank = dst.rank;
+  p.n_xslots = n_pairs;
+  p.n_local = n;
+  for (int r = 0; r < dst.world && r < kMaxPeers; ++r) p.peer[r] = dst.peer[r];
+  const int64_t slab = n * (int64_t)d->d;
+  float* dxraw = (float*)(ws + L.dxraw);
+  const int nk_all = (int)((N + 63) / 64), nk_loc = (int)((n + 63) / 64);
+
+  // unit rows of the local rows of every modality that is the `a` side of a scattered pair
+  if (scatter) {
+    const void* src[3] = {nullptr, nullptr, nullptr};
+    void* out[3] = {nullptr, nullptr, nullptr};
+    for (int q = 0; q < n_pairs; ++q) {
+      const int a = pairs_a[q];
+      src[a] = d->xh[a];
+      out[a] = ws + L.xunit + (size_t)a * n * d->d * 2;
     }
+    rc = rows_unit_f16_launch3(src, d->inv, d->row0, n, d->d, out, st);
+    if (rc) return rc;
+  }
+
+  int job = 0;
+  int job_nmb[MAX_JOBS];
+  for (int q = 0; q < n_pairs; ++q) {
+    const int a = pairs_a[q], b = pairs_b[q];
+    // K-major: dA[local rows] = G_q * B16 (all rows of b); the weights carry gs(a,b) / |b_j|
+    p.job_pair[job] = q;
+    p.job_mn[job] = 0;
+    p.job_nk[job] = nk_all;
+    p.job_kparts[job] = L.kparts;
+    p.job_rows[job] = n;
+    p.job_out[job] = dxraw + (int64_t)(scatter ? q : a * 2 + slot_of(d, a, b)) * L.kparts * slab;
+    p.job_fnum[job] = 2 * pair_id(a, b);
+    p.job_fden[job] = 2 * pair_id(a, b) + 1;  // factor 1: combine divides by gs(a,b)
+    p.job_finv[job] = nullptr;
+    job_nmb[job] = (int)((n + 255) / 256);
+    rc = make_tmap_2d(&p.tmap_in[job], d->xh[b], BSC_F16, N, d->d, 64);
+    if (rc) return rc;
+    ++job;
+    if (!scatter) continue;
+    // MN-major: partial dB[all rows] = G_q^T * Aunit (local rows of a); undo gs(a,b) / |b_j| per output row and hand
+    // combine the sums in units of gs(b,a)
+    p.job_pair[job] = q;
+    p.job_mn[job] = 1;
+    p.job_nk[job] = nk_loc;
+    p.job_kparts[job] = 1;
+    p.job_rows[job] = N;
+    p.job_out[job] = nullptr;
+    p.job_xslot[job] = q;
+    p.job_fnum[job] = 2 * pair_id(b, a);
+    p.job_fden[job] = 2 * pair_id(a, b) + 1;
+    p.job_finv[job] = d->inv[b];
+    job_nmb[job] = (int)((N + 255) / 256);
+    rc = make_tmap_2d(&p.tmap_in[job], ws + L.xunit + (size_t)a * n * d->d * 2, BSC_F16, n, d->d, 64);
+    if (rc) return rc;
+    ++job;
   }
   p.n_jobs = job;
-  BSC_REQUIRE(p.kparts >= 1 && p.kparts <= nk64, BSC_EUNSUPPORTED, "tc_bwd_gemms: K split %d of %d blocks", p.kparts,
-              nk64);
-  p.num_items = p.n_jobs * p.n_mb * p.kparts * p.nchunk;
-  return rev_launch(p, st);
+  for (int z = job; z < MAX_JOBS; ++z) p.tmap_in[z] = p.tmap_in[0];
+  BSC_REQUIRE(L.kparts >= 1 && L.kparts <= nk_all && L.kparts <= 255, BSC_EUNSUPPORTED,
+              "tc_bwd_gemms: K split %d of %d blocks", L.kparts, nk_all);
+
+  // ---- schedule: two lists (scattered items, local items), each ordered (row block, K part, job, d chunk) so that the
+  // d chunks of one A tile run on neighbouring clusters (they share it through L2); rounds of `clusters` items alternate
+  // between the lists.  A rank starts its scattered list at the row blocks of the next rank.
+  std::vector<uint32_t> lists[2];
+  for (int kind = 0; kind < 2; ++kind) {  // 0 = scattered (MN-major), 1 = local (K-major)
+    int nmb = 0, kp = 1;
+    for (int z = 0; z < job; ++z)
+      if ((p.job_out[z] == nullptr) == (kind == 0)) {
+        nmb = job_nmb[z];
+        kp = p.job_kparts[z];
+      }
+    const int rot = (kind == 0 && dst.world > 1) ? (int)(((int64_t)(dst.rank + 1) % dst.world) * nmb / dst.world) : 0;
+    for (int mbi = 0; mbi < nmb; ++mbi)
+      for (int part = 0; part < kp; ++part)
+        for (int z = 0; z < job; ++z) {
+          if ((p.job_out[z] == nullptr) != (kind == 0)) continue;
+          for (int c = 0; c < nchunk; ++c) lists[kind].push_back(pack_item(z, c, part, (mbi + rot) % nmb));
+        }
+  }
+  const size_t total = lists[0].size() + lists[1].size();
+  BSC_REQUIRE(total <= (size_t)MAX_SCHED, BSC_EUNSUPPORTED,
+              "tc_bwd_gemms: %zu work items exceed the schedule capacity %d (batch too large for the stored-weight "
+              "backward)", total, MAX_SCHED);
+  {
+    const size_t round = (size_t)(device_sm_count() / 2);
+    size_t pos[2] = {0, 0}, w = 0;
+    int kind = 0;
+    while (w < total) {
+      if (pos[kind] >= lists[kind].size()) kind ^= 1;
+      const size_t take = std::min(round, lists[kind].size() - pos[kind]);
+      for (size_t t = 0; t < take; ++t) p.sched[w++] = lists[kind][pos[kind]++];
+      kind ^= 1;
+    }
+  }
+  p.num_items = (int)total;
+  return rev_launch(p, wide, st);
 }
 
 }  // namespace bsc

@@ -4,7 +4,9 @@
 //   EPI_STATS  exp(s*S - s) row sums and column sums            (InfoNCE forward, loss_func.py:46-51)
 //   EPI_TOPK   per-row running top-k over the B rows            (IndexFlatIP.search, inference_and_eval.py:421)
 // Warp roles (256 threads): 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator, 4..7 = epilogue.
+#ifdef BSC_EXPERIMENTS
 #include <cstdlib>
+#endif
 
 #include "tc_common.cuh"
 
@@ -61,15 +63,17 @@ struct SimParams {
   int64_t base_id;
   float* cand_s;     // [jchunk][a_rows][k]
   int64_t* cand_i;
-  // EPI_WEIGHTS: the fp16 weight matrix of every unordered pair, G_ij = gs (e_ij (u_i + v_j) - 2 T_ij), written as
+  // EPI_WEIGHTS: the fp16 weight block of every pair, G_ij = gs (e_ij (u_i + v_j) - 2 T_ij) / |b_j|, written as
   // 128B-swizzled [128 i][64 j] images (K-major A operand over j, MN-major A operand over i: tc_bwd3.cu)
   const float* uv;     // [6][N]
   const float* gsbuf;  // [16] = gs of the stored weights
   uint8_t* gimg;       // [pair][n_iblk_pad][n_j64][16 KB]
   int n_iblk_pad, n_j64;
-  int fold_inv;  // 1: the weights carry 1/|b_j| and gs of the ordered pair (mode 3: the GEMM's B operand is the scaled
-                 // fp16 rows themselves, exact for bf16 inputs); 0: unscaled weights for fp16 unit rows (mode 2)
+  // The weights carry 1 / |b_j| and gs of the ordered pair (a, b): the K-major GEMM's B operand is then the scaled fp16
+  // rows themselves (exact for bf16 inputs), the MN-major GEMM undoes the column factor per output row (tc_bwd3.cu).
+#ifdef BSC_EXPERIMENTS
   int dbg;  // experiment knob BSC_DBG_W: 1 = no stores, 2 = no label compare (results invalid)
+#endif
 };
 
 struct __align__(8) SimSmemTail {
@@ -287,7 +291,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
       float ugs_i = 0.f, gsw = 0.f;
       const float* vcol_g = nullptr;
       if (EPI == EPI_WEIGHTS) {
-        gsw = p.fold_inv ? p.gsbuf[2 * pair_id(p.pair_a[pair], p.pair_b[pair])] : p.gsbuf[16];
+        gsw = p.gsbuf[2 * pair_id(p.pair_a[pair], p.pair_b[pair])];
         if (row_ok) {
           inv_i = p.inv[p.pair_a[pair]][p.a_row0 + arow];
           rep_i = p.rep[p.a_row0 + arow];
@@ -334,7 +338,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
             const int64_t j = col0 + col;
             const bool ok = j < p.b_rows;
             tail->invb[buf][col] = ok ? p.k1 * invb_g[j] : 0.f;
-            const float wf = ok ? (p.fold_inv ? invb_g[j] : 1.0f) : 0.f;  // column factor of the weights
+            const float wf = ok ? invb_g[j] : 0.f;  // column factor of the weights
             wfb[col] = wf;
             vgb[col] = ok ? gsw * vcol_g[j] * wf : 0.f;
             repb[col] = ok ? p.rep[j] : -1;
@@ -395,7 +399,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
             const int* repb = reinterpret_cast<const int*>(&tail->cs[1][0][0]) + buf * BN + c * 32;
             const float m2g = -2.0f * gsw;
             uint32_t pk[16];
-            if (tile_pos && p.dbg != 2) {  // some (row of this warp, column of this tile) pair may share a label
+#ifdef BSC_EXPERIMENTS
+            const bool want_pos = tile_pos && p.dbg != 2;
+#else
+            const bool want_pos = tile_pos;
+#endif
+            if (want_pos) {  // some (row of this warp, column of this tile) pair may share a label
 #pragma unroll
               for (int t = 0; t < 32; t += 2) {
                 float g2[2];
@@ -444,7 +453,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
               const int u = t4 ^ (r & 3);               // the chunk that belongs at 16-byte slot t4 of the row's half
               const uint4 v = *reinterpret_cast<const uint4*>(stg + r * 64 + ((u ^ ((r >> 1) & 3)) << 4));
               const int half_off = (((c & 1) * 4) ^ (rt & 4)) << 4;  // 128B swizzle: slot = chunk ^ (row & 7)
+#ifdef BSC_EXPERIMENTS
               if (p.dbg != 1 || v.x == 0x12345678u)
+#endif
                 __stcs(reinterpret_cast<uint4*>(img_base + (rt >> 3) * 1024 + (rt & 7) * 128 + half_off + (t4 << 4)), v);
             }
             __syncwarp();
@@ -543,16 +554,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
   }
 }
 
-int num_sms() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
+inline int num_sms() { return device_sm_count(); }
 
 template <int EPI, int FMT>
 int launch_sim(const SimParams& p_in, cudaStream_t st) {
@@ -563,20 +565,11 @@ int launch_sim(const SimParams& p_in, cudaStream_t st) {
   // ring covers 50 % more MMA time.  Measured (B200, N = 32768): bank scan +1 %, weights sweep 5.1 -> 4.3 ms.  The
   // forward sweep timed alone after an idle gap was 9 % slower on pairs (3.85 vs 3.54 ms), but inside the step, where
   // every kernel runs at the power cap, it is 5 % faster (4.20 -> 3.97 ms, three alternating runs) -- pairs everywhere.
-  // BSC_SIM_PAIR=0 disables them.
-  static const int pair_env = []() {
-    const char* e = getenv("BSC_SIM_PAIR");
-    return e ? (e[0] == '0' ? 0 : 1) : -1;
-  }();
-  const bool pair_ok = pair_env != 0;
+  const bool pair_ok = true;
   // CTA pairs need an even number of row blocks (the two CTAs of a pair take blocks 2m and 2m+1 of one column chunk)
   if (pair_ok && p.n_iblk >= 2 && (p.n_iblk % 2) == 0 && num_sms() >= 2) {
     auto kern = tc_sim_kernel<EPI, FMT, 1>;
-    static bool attr_done = false;
-    if (!attr_done) {
-      BSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SIM_SMEM_BYTES));
-      attr_done = true;
-    }
+    BSC_SET_SMEM_ONCE(kern, SIM_SMEM_BYTES);
     p.n_iblk_items = p.n_iblk / 2;
     p.num_items = p.num_items / 2;
     int clusters = num_sms() / 2;
@@ -598,11 +591,7 @@ int launch_sim(const SimParams& p_in, cudaStream_t st) {
     return BSC_OK;
   }
   auto kern = tc_sim_kernel<EPI, FMT, 0>;
-  static bool attr_done = false;
-  if (!attr_done) {
-    BSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SIM_SMEM_BYTES));
-    attr_done = true;
-  }
+  BSC_SET_SMEM_ONCE(kern, SIM_SMEM_BYTES);
   const int grid = p.num_items < num_sms() ? p.num_items : num_sms();
   kern<<<grid, NTHREADS, SIM_SMEM_BYTES, st>>>(p);
   BSC_LAUNCH_CHECK("tc_sim_kernel");
@@ -629,7 +618,7 @@ void tc_fwd_tiling(int64_t n_local, int64_t n_global, int n_pairs, int* n_iblk, 
   *n_jchunk = (*n_jtile + *jpc - 1) / *jpc;
 }
 
-int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, float* stats, cudaStream_t st) {
+int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceFwdWs& L, char* ws, float* stats, cudaStream_t st) {
   BSC_REQUIRE(d->d % BK == 0, BSC_EUNSUPPORTED, "TC16 mode needs d %% 64 == 0 (got %d); use BSC_MODE_F32", d->d);
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
   SimParams p{};
@@ -691,33 +680,30 @@ int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, float*
   return reduce_parts_batch_launch(jobs, st);
 }
 
-// ---- weight-matrix backward (one GPU) -------------------------------------------------------------------
-// 1. this file's sweep with the EPI_WEIGHTS epilogue recomputes S per unordered pair (the forward's 128 x 256 tiles,
-//    cta_group::1) and writes G = gs (e (u + v) - 2 T) as fp16 images; 2. tc_bwd_gemms (tc_bwd3.cu) forms G * Yunit and
-//    G^T * Xunit.  Executes 6 + 12 N^2 D like the stored-span mode, but every kernel is a plain pipelined GEMM.
+// ---- stored-weight backward: the weight blocks ------------------------------------------------------------
+// This file's sweep with the EPI_WEIGHTS epilogue recomputes S[local rows, all columns] per pair (the forward's
+// 128 x 256 tiles on CTA pairs) and writes G = gs (e (u + v) - 2 T) / |b_j| as fp16 images; tc_bwd_gemms (tc_bwd3.cu)
+// forms the gradient GEMMs from them.  BSC_BWD_SCATTER: one block per UNORDERED pair (a < b) serves both sides;
+// BSC_BWD_BLOCKS: one block per ORDERED pair.
 void tc_bwd_matrix_dims(const bsc_infonce_desc* d, int* n_iblk_pad, int* n_j64) {
   const int n_iblk = (int)((d->n_local + BM - 1) / BM);
   *n_iblk_pad = 2 * ((n_iblk + 1) / 2);
   *n_j64 = 4 * (int)((d->n_global + BN - 1) / BN);
 }
 
-int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaStream_t st) {
+size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* d) {
+  int m = 0;
+  for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
+  const size_t blocks = (size_t)(d->bwd_mode == BSC_BWD_SCATTER ? m * (m - 1) / 2 : m * (m - 1));
+  int n_iblk_pad, n_j64;
+  tc_bwd_matrix_dims(d, &n_iblk_pad, &n_j64);
+  return blocks * (size_t)n_iblk_pad * (size_t)n_j64 * 16384;
+}
+
+int tc_bwd_weights(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, int* n_pairs, int* pairs_a,
+                   int* pairs_b, cudaStream_t st) {
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
-  // mode 2: all rows local, one weight block per UNORDERED pair serves both sides.  Mode 3 (several GPUs): this rank's
-  // rows of modality a against all rows of b, one block per ORDERED pair (the other side's block lives on other ranks).
-  const bool ordered = L.bwd_gstore == 3;
-  // B operand of the gradient GEMMs: fp16 unit rows (mode 2); mode 3 folds 1/|b_j| into the weights and multiplies by the
-  // gathered scaled rows themselves -- no conversion pass, and exact operands for bf16 inputs
-  const void* xunit[3] = {nullptr, nullptr, nullptr};
-  if (ordered) {
-    for (int a = 0; a < 3; ++a) xunit[a] = d->xh[a];
-  } else {
-    void* dst[3] = {nullptr, nullptr, nullptr};
-    for (int a = 0; a < 3; ++a)
-      if (d->xh[a]) xunit[a] = dst[a] = ws + L.xunit + (size_t)a * d->n_global * d->d * 2;
-    int rc = rows_unit_f16_launch3(d->xh, d->inv, d->n_global, d->d, dst, st);
-    if (rc) return rc;
-  }
+  const bool ordered = L.mode == BSC_BWD_BLOCKS;
   SimParams p{};
   int np = 0, first = -1;
   for (int a = 0; a < 3; ++a) {
@@ -729,11 +715,12 @@ int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaS
     p.inv[a] = d->inv[a];
     for (int b = ordered ? 0 : a + 1; b < 3; ++b)
       if (b != a && d->xh[a] && d->xh[b]) {
-        p.pair_a[np] = a;
-        p.pair_b[np] = b;
+        p.pair_a[np] = pairs_a[np] = a;
+        p.pair_b[np] = pairs_b[np] = b;
         ++np;
       }
   }
+  *n_pairs = np;
   for (int a = 0; a < 3; ++a)
     if (!d->xh[a]) p.tmap[a] = p.tmap[first];
   p.n_pairs = np;
@@ -754,22 +741,22 @@ int tc_bwd_matrix(const bsc_infonce_desc* d, const InfoNceWs& L, char* ws, cudaS
   p.uv = (const float*)(ws + L.uv);
   p.gsbuf = (const float*)(ws + L.gs);
   p.gimg = (uint8_t*)(ws + L.gimg);
-  p.fold_inv = ordered ? 1 : 0;
   tc_bwd_matrix_dims(d, &p.n_iblk_pad, &p.n_j64);
   p.jrange = (const int2*)(ws + L.jrange);
   {
     int rc = rep_range_launch(d->rep, d->n_global, BN, (int2*)(ws + L.jrange), st);
     if (rc) return rc;
   }
+#ifdef BSC_EXPERIMENTS
   {
     const char* e = getenv("BSC_DBG_W");
     p.dbg = e ? atoi(e) : 0;
   }
+#endif
   timing_begin(1, st);
   int rc = launch_sim<EPI_WEIGHTS, 0>(p, st);
   timing_end(1, st);
-  if (rc) return rc;
-  return tc_bwd_gemms(d, L, ws, xunit, p.n_iblk_pad, p.n_j64, np, p.pair_a, p.pair_b, ordered ? 1 : 0, st);
+  return rc;
 }
 
 // ---- retrieval ---------------------------------------------------------------------------------------

@@ -16,7 +16,11 @@
  *     (torch tensors in the Python host code) unless its name starts with h_; scratch space is one
  *     caller-allocated workspace whose size comes from the matching *_workspace_bytes call;
  *   - every launch goes to the cudaStream_t passed as `stream` (as void*); no function synchronises
- *     the host with the device, allocates device memory or keeps global mutable state;
+ *     the host with the device or allocates device memory.  Nothing a result depends on is global: the
+ *     backward strategy travels in the descriptor (bsc_infonce_plan resolves it once), no entry point
+ *     reads the environment.  The only process-wide state is instrumentation (launch counter, the event
+ *     pairs behind bsc_last_kernel_ms) and per-device caches of immutable facts (SM count, shared-memory
+ *     opt-in of each kernel);
  *   - there is no CPU fallback: without an sm_100 device the launches fail and the error is returned.
  *
  * Row-major everywhere; `ld` arguments are row strides in ELEMENTS.
@@ -31,7 +35,7 @@
 extern "C" {
 #endif
 
-#define BSC_VERSION 100
+#define BSC_VERSION 200
 
 /* error codes */
 #define BSC_OK 0
@@ -129,28 +133,73 @@ typedef struct bsc_infonce_desc {
   const int32_t* rep;  /* [n_global]                                               */
   const int32_t* next; /* [n_global]                                               */
   const float* rmax;   /* [1]                                                      */
+  int32_t bwd_mode;    /* BSC_BWD_* as resolved by bsc_infonce_plan (never BSC_BWD_AUTO here) */
+  int32_t world;       /* ranks sharing the global batch (>= 1)                    */
+  int32_t rank;        /* this rank; BSC_BWD_SCATTER needs row0 == rank * n_local and n_global == world * n_local */
+  int32_t reserved;
 } bsc_infonce_desc;
+
+/* Backward strategies of BSC_MODE_TC16 (BSC_MODE_F32 always recomputes through its fp32 slab).
+ *   BSC_BWD_RECOMPUTE  one fused sweep per ORDERED pair that recomputes S tile by tile and keeps the gradient block in
+ *                      TMEM: nothing N^2-sized ever reaches HBM (d in {256, 512, 768}); executes 24 n N D.
+ *   BSC_BWD_BLOCKS     the fp16 weight block G_ab[local rows, all columns] of every ORDERED pair is written once
+ *                      (2 n N bytes each) and one GEMM per block forms dA = G B: no exchange between ranks
+ *                      (gather_with_grad=False semantics, loss_func.py:84-89); executes 24 n N D.
+ *   BSC_BWD_SCATTER    one weight block per UNORDERED pair serves both sides: dA_local = G B (local rows) and the
+ *                      partial dB_all = G^T A_local for ALL rows, whose row blocks are stored straight into their
+ *                      owners' exchange buffers (peer memory over NVLink: a fused GEMM + reduce-scatter, the backward
+ *                      of the autograd-aware all_gather of loss_func.py:81-82); bsc_infonce_bwd_finish sums the W
+ *                      sources in rank order.  Executes 18 n N D -- the single-GPU count on every rank.
+ * Stored-weight workspace: (pairs or ordered pairs) * 2 * n_local * n_global bytes -- the one N^2-sized buffer. */
+#define BSC_BWD_AUTO (-1)
+#define BSC_BWD_RECOMPUTE 0
+#define BSC_BWD_BLOCKS 3
+#define BSC_BWD_SCATTER 4
+
+typedef struct bsc_infonce_plan_t {
+  int32_t bwd_mode;            /* resolved strategy                                                              */
+  int32_t reserved;
+  size_t fwd_workspace_bytes;  /* bsc_infonce_fwd                                                                */
+  size_t bwd_workspace_bytes;  /* bsc_infonce_bwd_partials / _finish (allocate only when a backward will run)    */
+  size_t exchange_bytes;       /* BSC_BWD_SCATTER: this rank's exchange buffer float[world][pairs][n_local][d], mapped
+                                  into every peer when world > 1 (torch symmetric memory); 0 for the other modes   */
+} bsc_infonce_plan_t;
 
 /* number of floats in the statistics vector: 6 ordered-pair sum-exp rows of n_global + 4 scalars */
 int64_t bsc_infonce_stats_len(int64_t n_global);
-int bsc_infonce_workspace_bytes(const bsc_infonce_desc* p, size_t* bytes);
+
+/* Resolve the backward strategy and size the buffers.  p->bwd_mode is ignored; requested_bwd_mode = BSC_BWD_AUTO picks
+ * SCATTER when all rows are local or the ranks can map each other's memory (peer_memory != 0), BLOCKS otherwise, and
+ * falls back to RECOMPUTE when the stored weights would exceed memory_budget_bytes (0 = no limit).  An explicit request
+ * that cannot be honoured is an error (BSC_EUNSUPPORTED), never a silent substitution. */
+int bsc_infonce_plan(const bsc_infonce_desc* p, int requested_bwd_mode, int peer_memory, size_t memory_budget_bytes,
+                     bsc_infonce_plan_t* plan);
 
 /* Forward sweep.  stats (bsc_infonce_stats_len floats, overwritten) receives, for every ordered pair
  * (a,b) of present modalities, sum_j exp(S_ab[i,j] - s) for the rows this rank can complete and the
  * PARTIAL column sums over its local rows, plus (slot 6*n_global) the local part of
  * sum over unordered pairs sum_ij T_ij (S_ab[i,j] - s), taken from the same logits as the exponentials.
- * With more than one rank the caller sums `stats` over ranks (one all_reduce) before the next two calls. */
+ * With more than one rank the caller sums `stats` over ranks (one all_reduce) before the next calls. */
 int bsc_infonce_fwd(const bsc_infonce_desc* p, float* stats, void* workspace, size_t workspace_bytes,
                     void* stream);
 
 /* loss[0] = the scalar of loss_func.py:54 / :163 from the (rank-summed) statistics. */
 int bsc_infonce_loss(const bsc_infonce_desc* p, const float* stats, float* loss, void* stream);
 
-/* Backward.  x[m] are this rank's ORIGINAL (un-normalised) local rows, dtype x_dtype, row stride ldx;
- * grad[m] (same dtype, same stride) receives grad_out[0] * dLoss/dx[m] for the local rows.        */
-int bsc_infonce_bwd(const bsc_infonce_desc* p, const float* stats, const void* const* x, int x_dtype,
-                    int64_t ldx, const float* grad_out, void* const* grad, void* workspace,
-                    size_t workspace_bytes, void* stream);
+/* Backward, phase 1: raw gradient sums.  Writes the local partial sums into the workspace and, in BSC_BWD_SCATTER, the
+ * partial sums that belong to rank q's rows into exchange[q] (slot p->rank).  exchange = p->world device pointers in
+ * THIS process's address space (exchange[p->rank] = own buffer); NULL for the other strategies.  With world > 1 the
+ * caller runs a cross-rank barrier on the stream between this call and bsc_infonce_bwd_finish, and must not start the
+ * next step's phase 1 before every rank has finished reading its buffer (the forward's barrier of the next step). */
+int bsc_infonce_bwd_partials(const bsc_infonce_desc* p, const float* stats, void* const* exchange, void* workspace,
+                             size_t workspace_bytes, void* stream);
+
+/* Backward, phase 2: x[m] are this rank's ORIGINAL (un-normalised) local rows, dtype x_dtype, row stride ldx[m]
+ * elements; grad[m] (same dtype, DENSE [n_local][d]) receives grad_out[0] * dLoss/dx[m]: fixed-order sum of the partial
+ * sums (workspace and own_exchange), then the chain through F.normalize. */
+int bsc_infonce_bwd_finish(const bsc_infonce_desc* p, const void* const* x, int x_dtype, const int64_t* ldx,
+                           const float* grad_out, void* const* grad, const void* own_exchange, void* workspace,
+                           size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Retrieval -- IndexFlatIP.search on one bank shard (inference_and_eval.py:418-421).
@@ -205,13 +254,10 @@ int bsc_taxonomy_eval(const int64_t* indices, int64_t nq, int k, const int32_t* 
 /* ------------------------------------------------------------------------------------------------
  * Instrumentation for bench.py: CUDA-event time of the dominant kernel of the last call made with
  * bsc_set_timing(1) on this thread (milliseconds, -1 if none).  which: 0 = infonce forward sweep,
- * 1 = infonce backward sweep (mode 2 below: the weight-matrix kernel), 2 = bank scan, 3 = gradient GEMMs from stored
- * weights (backward modes 1 and 2).  Reading it synchronises on the recorded events only.
- * bsc_last_bwd_mode: how the most recent bsc_infonce_bwd in TC16 mode formed the gradients --
- *   0 the sweep recomputes S per ordered pair (any number of GPUs), 1 pair sweep per unordered pair + its stored
- *   weight spans (one GPU, BSC_BWD_GSTORE=1), 2 weight matrix written once + two GEMMs per pair (one GPU, default);
- *   3 several GPUs, default: weight blocks of this rank's rows per ordered pair + one GEMM each (BSC_BWD_GSTORE=0
- *   selects the pair sweep); -1 before the first call.
+ * 1 = infonce backward sweep (stored-weight strategies: the weight-block kernel), 2 = bank scan, 3 = gradient GEMMs
+ * from the stored weight blocks.  Reading it synchronises on the recorded events only.
+ * bsc_last_bwd_mode: the BSC_BWD_* strategy of the most recent bsc_infonce_bwd_partials in TC16 mode (-1 before the
+ * first call).
  * ---------------------------------------------------------------------------------------------- */
 int bsc_set_timing(int enabled);
 float bsc_last_kernel_ms(int which);

@@ -145,3 +145,74 @@ def clip_loss_rank(features, labels, logit_scale, rank: int, world_size: int, dt
     gathered = [None if f is None else (gather_rows_default(f, rank, world_size) if world_size > 1 else f)
                 for f in features]
     return contrastive_loss(gathered, all_labels, logit_scale, dtype)
+
+
+# ---------------------------------------------------------------------------------------------
+# Block-wise evaluation for the headline sizes (N = 32768): never holds an N x N tensor.
+# ---------------------------------------------------------------------------------------------
+
+def blockwise_loss_and_grad_rows(features, labels, logit_scale=1 / 0.07, sample_rows=None, dtype=torch.float64,
+                                 device=None, block=2048):
+    """The closed form of ``closed_form_grads`` (loss_func.py:29-54 and its autograd) evaluated in row blocks.
+
+    Pass 1: for every unordered pair (a, b) and every row block I, S = s * A^[I] B^^T (block x N) gives the row
+    log-sum-exps of S_ab for I, a log-add-exp update of the column log-sum-exps (= the row log-sum-exps of S_ba)
+    and the positive term sum_ij T_ij S_ij.  Pass 2: for ``sample_rows`` (1-D int64 tensor of row indices, the same
+    rows for every modality; None = all rows) the gradient rows
+        dA^_i = s * sum_j G_ij B^_j,   G_ij = c (r_i e^{S_ij - lse_ab[i]} + r_j e^{S_ij - lse_ba[j]} - 2 T_ij)
+    chained through F.normalize.  Returns (loss, [grad rows per modality or None]) in ``dtype`` on the CPU.
+    ``device`` may be a CUDA device: the matmuls are then plain torch fp64/fp32 GEMMs there -- test infrastructure
+    on the same footing as running the reference module on that device.
+    """
+    idx = [k for k, f in enumerate(features) if f is not None]
+    if len(idx) < 2:
+        raise ValueError(TOO_FEW)
+    dev = torch.device(device) if device is not None else features[idx[0]].device
+    xs = [features[k].to(device=dev, dtype=dtype) for k in idx]
+    lab = labels.to(dev)
+    m, n = len(xs), xs[0].shape[0]
+    norms = [x.norm(dim=1, keepdim=True).clamp_min(1e-12) for x in xs]
+    hats = [x / nn for x, nn in zip(xs, norms)]
+    # r_i = #{j: label_j == label_i} without the N x N matrix
+    _, inverse, counts = torch.unique(lab, return_inverse=True, return_counts=True)
+    r = counts[inverse].to(dtype)
+    c = 1.0 / (n * m * (m - 1))
+    neg_inf = float("-inf")
+    lse = {}
+    pos_total = torch.zeros((), dtype=dtype, device=dev)
+    for a in range(m):
+        for b in range(a + 1, m):
+            row_lse = torch.empty(n, dtype=dtype, device=dev)
+            col_lse = torch.full((n,), neg_inf, dtype=dtype, device=dev)
+            for lo in range(0, n, block):
+                hi = min(n, lo + block)
+                s = logit_scale * hats[a][lo:hi] @ hats[b].T
+                row_lse[lo:hi] = torch.logsumexp(s, dim=1)
+                col_lse = torch.logaddexp(col_lse, torch.logsumexp(s, dim=0))
+                t = (lab[lo:hi, None] == lab[None, :])
+                pos_total = pos_total + (s * t).sum()
+                del s, t
+            lse[(a, b)] = row_lse
+            lse[(b, a)] = col_lse
+    loss = torch.zeros((), dtype=dtype, device=dev)
+    for key, v in lse.items():
+        loss = loss + (r * v).sum()
+    loss = c * (loss - 2.0 * pos_total)  # every unordered pair's positive term appears in both directions
+
+    rows = torch.arange(n, device=dev) if sample_rows is None else sample_rows.to(dev)
+    out = [None] * len(features)
+    for a in range(m):
+        ghat = torch.zeros((rows.numel(), xs[a].shape[1]), dtype=dtype, device=dev)
+        for b in range(m):
+            if b == a:
+                continue
+            for lo in range(0, rows.numel(), block):
+                sel = rows[lo:lo + block]
+                s = logit_scale * hats[a][sel] @ hats[b].T
+                g = r[sel, None] * torch.exp(s - lse[(a, b)][sel, None]) + r[None, :] * torch.exp(s - lse[(b, a)][None, :])
+                g = g - 2.0 * (lab[sel, None] == lab[None, :]).to(dtype)
+                ghat[lo:lo + block] += (c * logit_scale) * (g @ hats[b])
+                del s, g
+        h = hats[a][rows]
+        out[idx[a]] = ((ghat - h * (h * ghat).sum(1, keepdim=True)) / norms[a][rows]).cpu()
+    return loss.cpu(), out

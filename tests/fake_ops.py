@@ -21,8 +21,10 @@ class FakeOps:
         return (x / n.clamp_min(1e-12)).to(torch.float64)
 
     def rows_to_f16(self, x):
+        """(operand rows, per-row scale) with cos_ij = <row_i, row_j> * scale_i * scale_j: the stand-in hands out
+        the unit rows themselves and unit scales, so its formulas can ignore the scales."""
         x = x.double()
-        return x, 1.0 / x.norm(dim=1).clamp_min(1e-12)
+        return x / x.norm(dim=1, keepdim=True).clamp_min(1e-12), torch.ones(x.shape[0], dtype=torch.float64)
 
     def label_stats(self, labels):
         t = (labels[None, :] == labels[:, None])
@@ -61,24 +63,67 @@ class FakeOps:
                     tot = tot + (p.r * torch.log(stats[pair_id(a, b) * n: pair_id(a, b) * n + n])).sum()
         return ((tot - 2.0 * stats[6 * n]) / (n * m * (m - 1))).float()
 
-    def infonce_bwd(self, p, stats, xs, grad_out):
+    # ---- backward: the two phases of include/bsc_hot.h -------------------------------------------------------
+    def plan(self, p, requested=-1, peer_memory=True):
+        """bsc_infonce_plan: scatter when the ranks can reach each other's exchange buffers, blocks otherwise."""
+        present = [m for m in range(3) if p.xh[m] is not None]
+        np_ = len(present) * (len(present) - 1) // 2
+        p.bwd_mode = requested if requested >= 0 else (4 if peer_memory else 3)
+        p.exchange_bytes = p.world * np_ * p.n_local * p.d * 8 if p.bwd_mode == 4 else 0
+
+    def _weights(self, p, stats, x, y):
+        """G_xy[local rows, all columns] = e (u + v) - 2 T."""
+        n = p.n_global
+        sl = slice(p.row0, p.row0 + p.n_local)
+        e = torch.exp(p.scale * p.xh[x][sl] @ p.xh[y].T - p.scale)
+        u = p.r[sl] / stats[pair_id(x, y) * n: pair_id(x, y) * n + n][sl]
+        v = p.r / stats[pair_id(y, x) * n: pair_id(y, x) * n + n]
+        return e * (u[:, None] + v[None, :]) - 2 * p.rep.double()[sl]
+
+    def infonce_bwd_partials(self, p, stats, exchange_ptrs=None):
+        present = [m for m in range(3) if p.xh[m] is not None]
+        sl = slice(p.row0, p.row0 + p.n_local)
+        p.fake_local = {}
+        if p.bwd_mode != 4:  # every ordered pair from this rank's own weight block: no exchange
+            for x in present:
+                for y in present:
+                    if y != x:
+                        p.fake_local[(x, y)] = self._weights(p, stats, x, y) @ p.xh[y]
+            return
+        # scatter: one weight block per unordered pair; dA for the local rows, the PARTIAL dB of every global row goes
+        # to its owner's buffer (exchange_ptrs = outbox [dest rank][pair][n_local][d] of the test comm)
+        outbox = exchange_ptrs
+        q = 0
+        for ia, a in enumerate(present):
+            for b in present[ia + 1:]:
+                g = self._weights(p, stats, a, b)
+                p.fake_local[(a, b)] = g @ p.xh[b]
+                part = g.T @ p.xh[a][sl]  # [n_global, d]
+                outbox[:, q] = part.reshape(p.world, p.n_local, p.d)
+                q += 1
+
+    def infonce_bwd_finish(self, p, xs, grad_out, own_exchange=None):
         n = p.n_global
         present = [m for m in range(3) if p.xh[m] is not None]
         m = len(present)
         c = 1.0 / (n * m * (m - 1))
-        sl = slice(p.row0, p.row0 + p.n_local)
-        t = p.rep.double()
+        pair_index = {}
+        for ia, a in enumerate(present):
+            for b in present[ia + 1:]:
+                pair_index[(a, b)] = len(pair_index)
         grads = [None, None, None]
         for x in present:
             ghat = torch.zeros(p.n_local, p.d, dtype=torch.float64)
             for y in present:
                 if y == x:
                     continue
-                e = torch.exp(p.scale * p.xh[x][sl] @ p.xh[y].T - p.scale)
-                u = p.r[sl] / stats[pair_id(x, y) * n: pair_id(x, y) * n + n][sl]
-                v = p.r / stats[pair_id(y, x) * n: pair_id(y, x) * n + n]
-                g = e * (u[:, None] + v[None, :]) - 2 * t[sl]
-                ghat += c * p.scale * g @ p.xh[y]
+                if (x, y) in p.fake_local:
+                    ghat += c * p.scale * p.fake_local[(x, y)]
+                else:  # fixed-order sum over the source ranks
+                    acc = torch.zeros(p.n_local, p.d, dtype=torch.float64)
+                    for src in range(p.world):
+                        acc += own_exchange[src, pair_index[(y, x)]]
+                    ghat += c * p.scale * acc
             xl = xs[x].double()
             nrm = xl.norm(dim=1, keepdim=True).clamp_min(1e-12)
             xh = xl / nrm

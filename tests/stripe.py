@@ -1,24 +1,36 @@
-"""One rank of a W-rank loss job replayed on a single GPU (test stand-in for the exchange step only: the kernels
-are the product's).  Used by tests/test_gpu_loss.py and tools/stripe_step.py."""
+"""A W-rank loss job replayed on a single GPU (test stand-in for the exchange steps only: every kernel is the
+product's, called through the C ABI).  Used by tests/test_gpu_loss.py and tools/stripe_step.py.
+
+The replay runs the ranks one after the other, phase by phase, which is exactly the dependency order of the real job:
+  1. forward of every rank's row stripe          -> the statistics are summed as the all-reduce would
+  2. bsc_infonce_bwd_partials of every rank      -> in the scatter strategy every rank stores its partial gradients
+                                                    into ALL ranks' exchange buffers (W tensors on the one device, handed
+                                                    out as "peer" addresses)
+  3. bsc_infonce_bwd_finish of every rank        -> fixed-order sum of the W sources + normalize backward
+"""
 import torch
 
 
 class StripeComm:
-    """One rank of a W-rank job, replayed on a single GPU: the gather returns the operands of the WHOLE batch
-    (prepared row by row, so they equal what the ranks would have exchanged), the statistics all-reduce returns the
-    sum the test accumulated over a first pass through every rank."""
+    """One rank of a W-rank job: the gather returns the operands of the WHOLE batch (prepared row by row, so they equal
+    what the ranks would have exchanged), the statistics all-reduce returns the sum accumulated over a first pass."""
+    peer_memory = True
 
-    def __init__(self, ops, rank, world, feats_all, labels_all, stats_sum=None):
+    def __init__(self, ops, rank, world, feats_all, labels_all, stats_sum=None, shared=None):
         self.ops, self.rank, self.world_size = ops, rank, world
         self.feats_all, self.labels_all = feats_all, labels_all
         self.stats_sum, self.stats_local = stats_sum, None
+        self.shared = shared if shared is not None else {}
 
     def gather_tc16(self, feats, labels):
-        xh, inv = [], []
-        for f in self.feats_all:
-            y16, iv = (None, None) if f is None else self.ops.rows_to_f16(f)
-            xh.append(y16)
-            inv.append(iv)
+        if "gathered" not in self.shared:
+            xh, inv = [], []
+            for f in self.feats_all:
+                y16, iv = (None, None) if f is None else self.ops.rows_to_f16(f)
+                xh.append(y16)
+                inv.append(iv)
+            self.shared["gathered"] = (xh, inv)
+        xh, inv = self.shared["gathered"]
         return xh, inv, self.labels_all
 
     def all_gather_rows(self, t):
@@ -28,6 +40,9 @@ class StripeComm:
         self.stats_local = t.clone()
         return t if self.stats_sum is None else self.stats_sum.clone()
 
+    def prepare_exchange(self, nbytes, device):
+        return True
+
 
 def _local(feats_all, labels_all, rank, world):
     nl = labels_all.shape[0] // world
@@ -35,29 +50,50 @@ def _local(feats_all, labels_all, rank, world):
     return [None if f is None else f[sl].clone() for f in feats_all], labels_all[sl].contiguous()
 
 
-def first_pass(ops, world, feats_all, labels_all, scale=1 / 0.07):
+def first_pass(ops, world, feats_all, labels_all, scale=1 / 0.07, shared=None):
     """Forward of every rank's stripe; returns the summed statistics vector (what the all-reduce would hand out)."""
     from bsc._lib import MODE_TC16
-    from bsc.loss import _InfoNCEFn
+    from bsc.loss import infonce_forward
 
     total = None
+    shared = shared if shared is not None else {}
     for r in range(world):
-        comm = StripeComm(ops, r, world, feats_all, labels_all)
+        comm = StripeComm(ops, r, world, feats_all, labels_all, shared=shared)
         local, lab = _local(feats_all, labels_all, r, world)
-        with torch.no_grad():
-            _InfoNCEFn.apply(ops, comm, scale, MODE_TC16, 1.0, lab, *local)
+        infonce_forward(ops, comm, local, lab, scale, MODE_TC16, want_grad=False)
         total = comm.stats_local if total is None else total + comm.stats_local
     return total
 
 
-def rank_step(ops, rank, world, feats_all, labels_all, stats_sum, scale=1 / 0.07):
-    """Forward + backward of one rank's stripe with the global statistics; returns (loss, leaves with .grad)."""
-    from bsc._lib import MODE_TC16
-    from bsc.loss import _InfoNCEFn
+def replay(ops, world, feats_all, labels_all, request, scale=1 / 0.07, grad_out=1.0):
+    """Whole job: returns (loss per rank, gradient per modality for ALL rows, resolved backward mode)."""
+    from bsc._lib import BWD_SCATTER, MODE_TC16
+    from bsc.loss import infonce_forward
 
-    comm = StripeComm(ops, rank, world, feats_all, labels_all, stats_sum)
-    local, lab = _local(feats_all, labels_all, rank, world)
-    leaves = [None if f is None else f.requires_grad_(True) for f in local]
-    loss = _InfoNCEFn.apply(ops, comm, scale, MODE_TC16, 1.0, lab, *leaves)
-    loss.backward()
-    return loss.detach(), leaves
+    shared = {}
+    stats_sum = first_pass(ops, world, feats_all, labels_all, scale, shared)
+    nl = labels_all.shape[0] // world
+    ranks = []
+    for r in range(world):
+        comm = StripeComm(ops, r, world, feats_all, labels_all, stats_sum, shared)
+        local, lab = _local(feats_all, labels_all, r, world)
+        loss, (prob, stats) = infonce_forward(ops, comm, local, lab, scale, MODE_TC16, True, request)
+        ranks.append((loss, prob, stats, local))
+    mode = ranks[0][1].bwd_mode
+    dev = labels_all.device
+    bufs, ptrs = [None] * world, None
+    if mode == BWD_SCATTER:
+        # poisoned: a slot nobody writes shows up as NaN in the result
+        bufs = [torch.full((max(ranks[0][1].exchange_bytes // 4, 4),), float("nan"), dtype=torch.float32, device=dev)
+                for _ in range(world)]
+        ptrs = [b.data_ptr() for b in bufs]
+    for loss, prob, stats, local in ranks:
+        ops.infonce_bwd_partials(prob, stats, ptrs)
+    g_out = torch.tensor(grad_out, dtype=torch.float32, device=dev)
+    grads = [None if f is None else torch.empty_like(f) for f in feats_all]
+    for r, (loss, prob, stats, local) in enumerate(ranks):
+        gl = ops.infonce_bwd_finish(prob, local, g_out, bufs[r])
+        for g, l in zip(grads, gl):
+            if g is not None:
+                g[r * nl:(r + 1) * nl] = l
+    return [float(x[0]) for x in ranks], grads, mode

@@ -11,7 +11,58 @@ NAMES = ["image", "dna", "text"]
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _worker(rank, world, port, feats, labels, gather_with_grad, ret):
+class GlooScatterComm:
+    """Test stand-in for SymmMemComm on CPU: the 'peer memory' of the scatter backward is an outbox that the barrier
+    delivers with an all_gather (rank r keeps block [r] of every rank's outbox, indexed by source rank)."""
+    peer_memory = True
+
+    def __init__(self, base):
+        self.base, self.rank, self.world_size = base, base.rank, base.world_size
+        self.all_gather_rows, self.all_reduce_sum = base.all_gather_rows, base.all_reduce_sum
+
+    def prepare_exchange(self, nbytes, device):
+        self.shape = None
+        return True
+
+    def exchange(self, nbytes, device):
+        import torch
+
+        self.outbox = torch.zeros(nbytes // 8, dtype=torch.float64)
+        self.inbox = torch.zeros(nbytes // 8, dtype=torch.float64)
+        return self.inbox, self.outbox
+
+    def exchange_barrier(self, device):
+        import torch
+        import torch.distributed as dist
+
+        boxes = [torch.zeros_like(self.outbox) for _ in range(self.world_size)]
+        dist.all_gather(boxes, self.outbox)
+        w = self.world_size
+        per = self.outbox.numel() // w
+        for src in range(w):
+            self.inbox.view(w, per)[src] = boxes[src].view(w, per)[self.rank]
+
+
+class _ShapedOps:
+    """Gives the flat exchange tensors of GlooScatterComm the [rank][pair][n_local][d] shape FakeOps works on."""
+
+    def __init__(self, ops):
+        self.ops = ops
+
+    def __getattr__(self, name):
+        return getattr(self.ops, name)
+
+    def _shape(self, p, t):
+        return t.view(p.world, -1, p.n_local, p.d)
+
+    def infonce_bwd_partials(self, p, stats, exchange_ptrs=None):
+        return self.ops.infonce_bwd_partials(p, stats, None if exchange_ptrs is None else self._shape(p, exchange_ptrs))
+
+    def infonce_bwd_finish(self, p, xs, grad_out, own_exchange=None):
+        return self.ops.infonce_bwd_finish(p, xs, grad_out, None if own_exchange is None else self._shape(p, own_exchange))
+
+
+def _worker(rank, world, port, feats, labels, gather_with_grad, ret, scatter=False):
     import sys
 
     for p in (ROOT, os.path.join(ROOT, "bioscan-clip_b200")):
@@ -30,25 +81,36 @@ def _worker(rank, world, port, feats, labels, gather_with_grad, ret):
     sl = slice(rank * n, (rank + 1) * n)
     local = [None if f is None else f[sl].contiguous() for f in feats]
     ops, comm = FakeOps(), TorchDistComm(rank, world)
-    loss, saved = infonce_forward(ops, comm, local, labels[sl].contiguous(), 1 / 0.07, MODE_F32)
+    if scatter:
+        ops, comm = _ShapedOps(ops), GlooScatterComm(comm)
+    from bsc._lib import MODE_TC16
+
+    # the TC16 host path (rows_to_f16 + gathers of rows and inverse norms) when the scatter backward is exercised
+    mode = MODE_TC16 if scatter else MODE_F32
+    loss, saved = infonce_forward(ops, comm, local, labels[sl].contiguous(), 1 / 0.07, mode)
+    assert saved[0].bwd_mode == (4 if scatter else 3)
     gain = float(world) if gather_with_grad else 1.0
-    grads = infonce_backward(ops, saved, local, torch.ones(()), gain)
+    grads = infonce_backward(ops, comm, saved, local, torch.ones(()), gain)
     ret[rank] = (float(loss), [None if g is None else g.numpy() for g in grads])
     dist.destroy_process_group()
 
 
-def _run(feats, labels, gather_with_grad=False, port=29633):
+def _run(feats, labels, gather_with_grad=False, port=29633, scatter=False):
     mgr = mp.Manager()
     ret = mgr.dict()
-    mp.spawn(_worker, args=(2, port, feats, labels, gather_with_grad, ret), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, port, feats, labels, gather_with_grad, ret, scatter), nprocs=2, join=True)
     return ret
 
 
-def test_two_ranks_match_reference_cliploss_fixture(golden_dir):
+@pytest.mark.parametrize("scatter", [False, True])
+def test_two_ranks_match_reference_cliploss_fixture(golden_dir, scatter):
+    """scatter=False: every rank forms its gradient from its own weight blocks (no backward exchange); scatter=True:
+    the host protocol of the reduce-scatter backward (plan -> exchange buffers -> partials -> barrier -> finish).  Both
+    against the reference's own 2-rank ClipLoss run."""
     z = np.load(os.path.join(golden_dir, "cliploss_w2.npz"))
     feats = [torch.from_numpy(z[f"x_{n}"]) for n in NAMES]
     labels = torch.from_numpy(z["labels"])
-    ret = _run(feats, labels)
+    ret = _run(feats, labels, scatter=scatter, port=29633 + (2 if scatter else 0))
     for r in range(2):
         loss, grads = ret[r]
         assert abs(loss - float(z[f"loss_rank{r}"])) <= 1e-5 * abs(float(z[f"loss_rank{r}"]))
@@ -63,7 +125,7 @@ def test_two_ranks_missing_modality_and_gather_with_grad():
 
     feats, labels = loss_inputs(24, 16, (True, False, True), seed=2, normalised=False, labels="multi")
     ref_loss, ref_grads = loss_oracle.closed_form_grads(feats, labels)
-    ret = _run(feats, labels, gather_with_grad=True, port=29634)
+    ret = _run(feats, labels, gather_with_grad=True, port=29634, scatter=True)
     for r in range(2):
         loss, grads = ret[r]
         assert abs(loss - float(ref_loss)) <= 1e-5 * abs(float(ref_loss))

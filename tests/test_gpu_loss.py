@@ -125,46 +125,72 @@ def test_tc16_mode_matches_oracle_on_16bit_inputs(n, d, present, labels, shared,
         assert (err <= bound + 1e-12).all(), (err.max().item(), gr.abs().max().item())
 
 
+BWD_CODE = {"scatter": 4, "blocks": 3, "recompute": 0}
+
+
 @pytest.mark.parametrize("n,d,present,labels,shared", TC16_CASES)
 def test_tc16_backward_modes_match_oracle_and_each_other(n, d, present, labels, shared, monkeypatch):
-    """On one GPU the backward writes the fp16 weight matrix of every unordered pair once and forms both gradient
-    GEMMs from it (mode 2, the default, exercised by the test above).  BSC_BWD_GSTORE=1 selects the pair sweep that
-    keeps one side in TMEM and stores its weight spans for the other; =0 the sweep that recomputes S per ordered pair
-    -- the path every rank of a multi-GPU run takes.  All three against the oracle, and against each other."""
+    """Three backward strategies (include/bsc_hot.h BSC_BWD_*).  scatter (the default): the fp16 weight block of every
+    UNORDERED pair is written once and serves both gradient GEMMs; blocks: one block per ORDERED pair, one GEMM each
+    (the multi-GPU path without peer memory); recompute: the fused sweep that never stores anything N^2-sized.
+    All three against the oracle, and against each other."""
     from bsc import _lib
 
     feats, lab = loss_inputs(n, d, present, seed=n + 1, labels=labels, shared=shared, dtype=torch.bfloat16)
     ref_in = [None if f is None else f.float() for f in feats]
     ref_loss, ref_grads = loss_oracle.closed_form_grads(ref_in, lab)
     results = {}
-    for mode in ("2", "1", "0"):
-        monkeypatch.setenv("BSC_BWD_GSTORE", mode)
+    for mode in ("scatter", "blocks", "recompute"):
+        monkeypatch.setenv("BSC_BWD_MODE", mode)
         results[mode] = _run(ref_in, lab, "tc16")
-        assert _lib.last_bwd_mode() == int(mode)
+        assert _lib.last_bwd_mode() == BWD_CODE[mode]
         _compare(results[mode][0], results[mode][1], ref_loss, ref_grads, TC16_TOL)
-    for mode in ("2", "1"):
-        assert float(results[mode][0]) == float(results["0"][0])  # the forward does not depend on the backward mode
-        for ga, gb in zip(results[mode][1], results["0"][1]):
+    for mode in ("scatter", "blocks"):
+        assert float(results[mode][0]) == float(results["recompute"][0])  # the forward does not depend on the backward
+        for ga, gb in zip(results[mode][1], results["recompute"][1]):
             if gb is None:
                 assert ga is None
                 continue
             assert (ga - gb).abs().max().item() <= 1.5e-3 * gb.abs().max().item()
 
 
+@pytest.mark.parametrize("n,d,present", [(512, 128, (True, True, True)), (384, 384, (True, True, False)),
+                                         (300, 1024, (True, True, True)), (256, 640, (False, True, True)),
+                                         (200, 1152, (True, True, True))])
+@pytest.mark.parametrize("mode", ["scatter", "blocks"])
+def test_tc16_embedding_widths_other_than_768(n, d, present, mode, monkeypatch):
+    """d = any multiple of 128: 384-wide items where d % 384 == 0, 256-wide otherwise (a last half-empty chunk when
+    d % 256 == 128).  The recomputing sweep covers {256, 512, 768} only and must refuse the others loudly."""
+    import bsc
+    from bsc import _lib
+
+    feats, lab = loss_inputs(n, d, present, seed=d, labels="multi", dtype=torch.bfloat16)
+    ref_in = [None if f is None else f.float() for f in feats]
+    ref_loss, ref_grads = loss_oracle.closed_form_grads(ref_in, lab)
+    monkeypatch.setenv("BSC_BWD_MODE", mode)
+    loss, grads = _run(ref_in, lab, "tc16")
+    assert _lib.last_bwd_mode() == BWD_CODE[mode]
+    _compare(loss, grads, ref_loss, ref_grads, TC16_TOL)
+    monkeypatch.setenv("BSC_BWD_MODE", "recompute")
+    with pytest.raises(bsc.BscError, match="256, 512, 768"):
+        _run(ref_in, lab, "tc16")
+
+
 def test_tc16_backward_falls_back_to_recomputing_sweep_above_the_memory_cap(monkeypatch):
-    """The weight matrix is the one N x N-sized buffer of the design: above BSC_BWD_GSTORE_GB the backward recomputes."""
+    """The weight blocks are the one N x N-sized buffer of the design: when they do not fit the memory budget
+    (free device memory, or BSC_BWD_MEM_GB) the backward recomputes instead."""
     from bsc import _lib
 
     feats, lab = loss_inputs(512, 768, (True, True, True), seed=3, labels="multi", dtype=torch.bfloat16)
     ref_in = [f.float() for f in feats]
     ref_loss, ref_grads = loss_oracle.closed_form_grads(ref_in, lab)
-    monkeypatch.setenv("BSC_BWD_GSTORE_GB", "0.0001")  # 107 KB < 3 pairs x 512 x 512 x 2 B
+    monkeypatch.setenv("BSC_BWD_MEM_GB", "0.0001")  # 107 KB < 3 pairs x 512 x 512 x 2 B
     loss, grads = _run(ref_in, lab, "tc16")
     assert _lib.last_bwd_mode() == 0
     _compare(loss, grads, ref_loss, ref_grads, TC16_TOL)
-    monkeypatch.delenv("BSC_BWD_GSTORE_GB")
+    monkeypatch.delenv("BSC_BWD_MEM_GB")
     _run(ref_in, lab, "tc16")
-    assert _lib.last_bwd_mode() == 2
+    assert _lib.last_bwd_mode() == 4
 
 
 @pytest.mark.parametrize("n,d,present,labels,shared,world,normalised", [
@@ -173,39 +199,67 @@ def test_tc16_backward_falls_back_to_recomputing_sweep_above_the_memory_cap(monk
     (768, 512, (True, False, True), "multi", 0.5, 2, True),      # 384 rows per rank: three row blocks, d = 2 x 256
     (2048, 768, (True, True, True), "multi", 0.5, 8, True),
     (1024, 768, (True, True, True), "multi", 0.5, 2, False),     # row norms 0.5 .. 2 x sqrt(d): 1/|row| in the weights
+    (1200, 768, (True, True, True), "multi", 0.5, 4, True),      # 300 rows per rank: row blocks straddle two owners
+    (1040, 384, (True, True, True), "multi", 0.5, 8, False),     # 130 rows per rank, d = one 384-wide item
 ])
-@pytest.mark.parametrize("mode", ["3", "0"])
-def test_tc16_rank_stripes_replayed_on_one_gpu(n, d, present, labels, shared, world, normalised, mode, monkeypatch):
-    """The kernels a rank of a multi-GPU job runs (row stripe x all columns: forward statistics, then the backward
-    from one weight block per ORDERED pair -- mode 3 -- or the recomputing sweep -- mode 0) on ONE GPU: every rank's
-    stripe in turn, statistics summed as the all-reduce would, loss and gradient stripes against the oracle on the
-    whole batch (loss_func.py:122-162: every rank evaluates the global loss, the gradient reaches the local rows)."""
-    from bsc import _lib
+@pytest.mark.parametrize("mode", ["scatter", "blocks", "recompute"])
+def test_tc16_ranks_replayed_on_one_gpu(n, d, present, labels, shared, world, normalised, mode):
+    """The kernels the ranks of a multi-GPU job run, replayed on ONE GPU rank by rank and phase by phase (tests/stripe.py):
+    forward statistics of every row stripe, summed as the all-reduce would; then the backward --
+      scatter    weight block per UNORDERED pair on the local rows, dA locally, the partial dB of ALL rows stored into the
+                 owners' exchange buffers (here W buffers on the one device), fixed-order sum in the finish phase;
+      blocks     weight block per ORDERED pair, no exchange;     recompute   the fused sweep, no exchange.
+    Loss and gradients of the whole batch against the oracle (loss_func.py:122-162: every rank evaluates the global loss,
+    the gradient reaches the local rows; with the scatter strategy through the backward of the autograd-aware
+    all_gather, loss_func.py:81-82, whose sum over ranks is exactly this reduce-scatter)."""
+    from bsc._lib import BWD_NAMES
     from bsc.loss import _default_ops
-    from tests.stripe import first_pass, rank_step
+    from tests.stripe import replay
 
-    monkeypatch.setenv("BSC_BWD_GSTORE", mode)
+    if mode == "recompute" and d not in (256, 512, 768):
+        pytest.skip("the recomputing sweep covers d in {256, 512, 768}")
     feats, lab = loss_inputs(n, d, present, seed=n + world, labels=labels, shared=shared, dtype=torch.bfloat16,
                              normalised=normalised)
     ref_in = [None if f is None else f.float() for f in feats]
     ref_loss, ref_grads = loss_oracle.closed_form_grads(ref_in, lab)
     ops = _default_ops()
     dev_feats = [None if f is None else f.cuda() for f in ref_in]
-    dev_lab = lab.cuda()
-    nl = n // world
-    stats_sum = first_pass(ops, world, dev_feats, dev_lab)
-    grads = [None if f is None else torch.empty_like(f) for f in dev_feats]
-    losses = []
-    for r in range(world):
-        loss, leaves = rank_step(ops, r, world, dev_feats, dev_lab, stats_sum)
-        assert _lib.last_bwd_mode() == int(mode)
-        losses.append(float(loss))
-        for g, l in zip(grads, leaves):
-            if g is not None:
-                g[r * nl:(r + 1) * nl] = l.grad
+    losses, grads, resolved = replay(ops, world, dev_feats, lab.cuda(), BWD_NAMES[mode])
     torch.cuda.synchronize()
+    assert resolved == BWD_CODE[mode]
     assert all(x == losses[0] for x in losses)  # every rank reports the loss of the global batch, same bits
     _compare(losses[0], [None if g is None else g.cpu() for g in grads], ref_loss, ref_grads, TC16_TOL)
+
+
+def test_strided_rows_and_mixed_dtypes():
+    """Inputs as encoders hand them over: a CLS slice hidden[:, 0] (row stride T*D) and a column slice [:, :d].  The
+    forward reads them in place; the backward must neither read nor write outside the rows (the gradients come back
+    dense).  Mixed dtypes are refused up front."""
+    import bsc
+
+    n, d, t = 192, 256, 3
+    feats, lab = loss_inputs(n, d, seed=21, labels="multi", dtype=torch.bfloat16)
+    ref_in = [f.float() for f in feats]
+    ref_loss, ref_grads = loss_oracle.closed_form_grads(ref_in, lab)
+    hidden = torch.full((n, t, d), 7.0, device="cuda")
+    hidden[:, 0] = ref_in[0].cuda()
+    wide = torch.full((n, 2 * d), -3.0, device="cuda")
+    wide[:, :d] = ref_in[1].cuda()
+    leaves = [hidden.clone().requires_grad_(True), wide.clone().requires_grad_(True),
+              ref_in[2].cuda().requires_grad_(True)]
+    views = [leaves[0][:, 0], leaves[1][:, :d], leaves[2]]
+    assert not views[0].is_contiguous() and not views[1].is_contiguous()
+    for precision, tol in (("tc16", TC16_TOL), ("fp32", TC16_TOL)):
+        for l in leaves:
+            l.grad = None
+        loss = bsc.ContrastiveLoss(None, 1 / 0.07, precision=precision)(views[0], views[1], views[2], lab.cuda())
+        loss.backward()
+        torch.cuda.synchronize()
+        got = [leaves[0].grad[:, 0].cpu(), leaves[1].grad[:, :d].cpu(), leaves[2].grad.cpu()]
+        _compare(loss.detach().cpu(), got, ref_loss, ref_grads, tol)
+        assert leaves[0].grad[:, 1:].abs().max().item() == 0.0 and leaves[1].grad[:, d:].abs().max().item() == 0.0
+    with pytest.raises(ValueError, match="one dtype"):
+        bsc.ContrastiveLoss(None, 1 / 0.07)(views[0], views[1].bfloat16(), None, lab.cuda())
 
 
 def test_tc16_unnormalised_rows_of_mixed_scale():
@@ -238,9 +292,64 @@ def test_tc16_config2_4096_three_modalities():
         assert ((g.double() - gr.double()).abs() <= TC16_TOL * gr.abs().max() + _bf16_round_bound(gr)).all()
 
 
+def _sampled_check(feats, lab, run, rows, tol):
+    """Loss and a strided sample of gradient rows against the block-wise fp64 closed form evaluated on the device."""
+    ref_in = [None if f is None else f.float() for f in feats]
+    ref_loss, ref_rows = loss_oracle.blockwise_loss_and_grad_rows(ref_in, lab, sample_rows=rows, device="cuda")
+    loss, grads = run()
+    rel_loss = abs(float(loss) - float(ref_loss)) / abs(float(ref_loss))
+    assert rel_loss <= tol, (float(loss), float(ref_loss))
+    worst = 0.0
+    for g, gr in zip(grads, ref_rows):
+        if gr is None:
+            continue
+        # the bound is relative to the largest gradient entry of the WHOLE batch; the sample's own maximum is a lower
+        # bound of it, so the check is the stricter one
+        err = (g[rows].double() - gr.double()).abs().max().item() / gr.abs().max().item()
+        worst = max(worst, err)
+        assert err <= tol, err
+    return rel_loss, worst
+
+
+@pytest.mark.parametrize("mode", ["scatter", "recompute"])
+def test_config3_32768_against_blockwise_oracle(mode, monkeypatch):
+    """BASELINE config 3 on one GPU (global batch 32768, three modalities, bf16-representable inputs held in float32
+    so that the returned gradients are not re-rounded): loss and 1536 gradient rows per modality against the fp64 closed
+    form of the reference maths, evaluated block-wise (2048 rows x all columns at a time, plain torch fp64 matmuls on
+    the device: the reference module itself needs > 100 GB of N x N tensors at this size)."""
+    n = 32768
+    feats, lab = loss_inputs(n, 768, seed=3, labels="multi", dtype=torch.bfloat16)
+    rows = torch.arange(5, n, 21)[:1536]
+    monkeypatch.setenv("BSC_BWD_MODE", mode)
+    rel_loss, worst = _sampled_check(feats, lab, lambda: _run([f.float() for f in feats], lab, "tc16"), rows, TC16_TOL)
+    print(f"N=32768 {mode}: loss rel err {rel_loss:.2e}, gradient max err / max |g| {worst:.2e}")
+
+
+def test_config3_32768_eight_ranks_replayed_against_blockwise_oracle():
+    """Same batch through the 8-rank code path (4096 rows per rank, scatter backward) replayed on one GPU."""
+    from bsc._lib import BWD_SCATTER
+    from bsc.loss import _default_ops
+    from tests.stripe import replay
+
+    n = 32768
+    feats, lab = loss_inputs(n, 768, seed=3, labels="multi", dtype=torch.bfloat16)
+    rows = torch.arange(5, n, 21)[:1536]
+    dev = [f.float().cuda() for f in feats]
+    out = {}
+
+    def run():
+        losses, grads, mode = replay(_default_ops(), 8, dev, lab.cuda(), BWD_SCATTER)
+        torch.cuda.synchronize()
+        assert mode == BWD_SCATTER and all(x == losses[0] for x in losses)
+        out["loss"] = losses[0]
+        return losses[0], [g.cpu() for g in grads]
+
+    rel_loss, worst = _sampled_check(feats, lab, run, rows, TC16_TOL)
+    print(f"N=32768 as 8 ranks: loss rel err {rel_loss:.2e}, gradient max err / max |g| {worst:.2e}")
+
+
 def test_properties_at_full_size():
-    """Size-independent checks at N = 32768 (the oracle cannot run there): permutation invariance of the
-    batch, and agreement of the two arithmetic modes on a strided sample of gradient rows."""
+    """Size-independent checks at N = 32768: permutation invariance of the batch and run-to-run determinism."""
     n = 32768
     feats, lab = loss_inputs(n, 768, seed=3, labels="multi", dtype=torch.bfloat16)
     loss, grads = _run(feats, lab, "tc16")
@@ -271,6 +380,14 @@ def test_error_behaviour():
     y = torch.randn(8, 72, device="cuda", dtype=torch.bfloat16)
     with pytest.raises(bsc.BscError, match="BSC_MODE_F32"):
         bsc.ContrastiveLoss(None, 1 / 0.07, precision="tc16")(y, y, None, torch.arange(8).cuda())
+    # ... while 'auto' takes the fp32 path for widths the tensor-core kernels do not tile
+    la = bsc.ContrastiveLoss(None, 1 / 0.07, precision="auto")(y.requires_grad_(True), y.detach(), None,
+                                                               torch.arange(8).cuda())
+    la.backward()
+    assert torch.isfinite(la) and y.grad is not None
+    # a temperature that wants a gradient is refused (the reference's is a constant, train_cl.py:190)
+    with pytest.raises(NotImplementedError, match="constant logit_scale"):
+        bsc.ClipLoss()(x, x, None, torch.arange(8).cuda(), torch.tensor(14.0, device="cuda", requires_grad=True))
 
 
 def test_cliploss_single_rank_output_dict():

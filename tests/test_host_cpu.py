@@ -24,12 +24,12 @@ def test_library_exports_every_declared_symbol(built_lib):
 
     header = open(os.path.join(ROOT, "include", "bsc_hot.h")).read()
     declared = set(re.findall(r"^\s*(?:const\s+)?[a-z_0-9]+\*?\s+\*?(bsc_[a-z0-9_]+)\s*\(", header, re.M))
-    assert {"bsc_infonce_fwd", "bsc_infonce_bwd", "bsc_bank_search", "bsc_topk_merge", "bsc_l2norm_fwd"} <= declared
+    assert {"bsc_infonce_fwd", "bsc_infonce_plan", "bsc_infonce_bwd_partials", "bsc_infonce_bwd_finish", "bsc_bank_search", "bsc_topk_merge", "bsc_l2norm_fwd"} <= declared
     lib = ctypes.CDLL(built_lib)
     for name in sorted(declared):
         assert hasattr(lib, name), f"{name} declared in bsc_hot.h but not exported"
     lib.bsc_version.restype = ctypes.c_int
-    assert lib.bsc_version() == 100
+    assert lib.bsc_version() == 200
     from bsc import _lib
 
     assert set(_lib.EXPORTS) == declared
@@ -65,9 +65,27 @@ def test_argument_errors_without_gpu(built_lib):
     assert L.bsc_bank_search_workspace_bytes(10, 100, 64, 5, 7, ctypes.byref(nbytes)) == -1
     assert L.bsc_bank_search_workspace_bytes(10, 100, 64, 5, 0, ctypes.byref(nbytes)) == 0 and nbytes.value > 0
     d = _lib.InfoNceDesc()
-    d.n_global, d.n_local, d.row0, d.d, d.mode = 8, 8, 0, 64, 1
-    assert L.bsc_infonce_workspace_bytes(ctypes.byref(d), ctypes.byref(nbytes)) == -1
+    d.n_global, d.n_local, d.row0, d.d, d.mode, d.world = 8, 8, 0, 128, 1, 1
+    plan = _lib.InfoNcePlan()
+    assert L.bsc_infonce_plan(ctypes.byref(d), _lib.BWD_AUTO, 1, 0, ctypes.byref(plan)) == -1
     assert b"Too less element" in L.bsc_last_error()
+    # the plan itself needs no device: strategy and buffer sizes of BASELINE config 3 on 8 ranks
+    one = ctypes.c_void_p(256)  # never dereferenced by the plan
+    d.n_global, d.n_local, d.row0, d.d, d.x16_dtype, d.world, d.rank = 32768, 4096, 4096, 768, _lib.BSC_F16, 8, 1
+    for m in range(3):
+        d.xh[m] = one
+        d.inv[m] = one
+    d.r = d.rep = d.next = d.rmax = one
+    assert L.bsc_infonce_plan(ctypes.byref(d), _lib.BWD_AUTO, 1, 0, ctypes.byref(plan)) == 0, L.bsc_last_error()
+    assert plan.bwd_mode == _lib.BWD_SCATTER
+    assert plan.exchange_bytes == 8 * 3 * 4096 * 768 * 4
+    assert 3 * 2 * 4096 * 32768 <= plan.bwd_workspace_bytes <= 3 * 2 * 4096 * 32768 + (1 << 30)
+    assert L.bsc_infonce_plan(ctypes.byref(d), _lib.BWD_AUTO, 0, 0, ctypes.byref(plan)) == 0
+    assert plan.bwd_mode == _lib.BWD_BLOCKS and plan.exchange_bytes == 0   # no peer memory: ordered-pair blocks
+    assert L.bsc_infonce_plan(ctypes.byref(d), _lib.BWD_SCATTER, 0, 0, ctypes.byref(plan)) == -2  # explicit request refused
+    assert b"peer-mapped" in L.bsc_last_error()
+    assert L.bsc_infonce_plan(ctypes.byref(d), _lib.BWD_AUTO, 1, 1 << 20, ctypes.byref(plan)) == 0
+    assert plan.bwd_mode == _lib.BWD_RECOMPUTE                              # 1 MB budget: recompute instead of storing
 
 
 def test_modules_refuse_cpu_tensors(built_lib):
@@ -91,10 +109,15 @@ def test_resolve_mode():
     from bsc._lib import MODE_F32, MODE_TC16
     from bsc.loss import resolve_mode
 
-    f32, b16 = torch.zeros(1), torch.zeros(1, dtype=torch.bfloat16)
+    f32, b16 = torch.zeros(1, 256), torch.zeros(1, 256, dtype=torch.bfloat16)
     assert resolve_mode("auto", [f32, f32]) == MODE_F32
     assert resolve_mode("auto", [f32, b16]) == MODE_TC16
     assert resolve_mode("tc16", [f32]) == MODE_TC16 and resolve_mode("fp32", [b16]) == MODE_F32
+    odd = torch.zeros(1, 72, dtype=torch.bfloat16)
+    assert resolve_mode("auto", [odd, odd]) == MODE_F32  # widths the tensor-core kernels do not tile
+    import bsc
+    with pytest.raises(bsc.BscError, match="multiple of 128"):
+        resolve_mode("tc16", [odd])
     with pytest.raises(ValueError):
         resolve_mode("fp8", [f32])
 
