@@ -152,29 +152,53 @@ def synth_loss_rows(torch, n_global, row0, n_local, device, dtype):
     return feats, labels
 
 
-def cpu_loss_baseline(n, repeats=2):
-    """The reference's loss maths (oracle port of loss_func.py:29-54) fwd+bwd in fp32 on the host cores."""
-    import torch
+def reference_loss_step(torch):
+    """-> (step(feats, labels) running one fwd+bwd, kind, description).  The timed CPU arm is the REFERENCE MODULE ITSELF
+    (bioscanclip/model/loss_func.py ContrastiveLoss, staged unmodified in oracle/_ref by oracle/build_ref.py) built as
+    scripts/train_cl.py:190 builds it; only when no staged copy exists does the oracle port stand in."""
+    from oracle import build_ref, loss_oracle
 
-    from oracle import loss_oracle
+    classes = build_ref.load_reference_loss()
+    if classes is not None:
+        crit = classes[0](criterion=torch.nn.CrossEntropyLoss(), logit_scale=SCALE)
+
+        def step(feats, labels):
+            leaves = [f.detach().clone().requires_grad_(True) for f in feats]
+            loss = crit(leaves[0], leaves[1], leaves[2], labels)  # train_epoch.py:37
+            loss.backward()                                       # train_epoch.py:38
+            return float(loss.detach())
+
+        return step, "reference", "bioscanclip/model/loss_func.py ContrastiveLoss (unmodified, oracle/_ref)"
+
+    def step(feats, labels):
+        loss, _ = loss_oracle.contrastive_loss_and_grads(feats, labels, SCALE)
+        return float(loss)
+
+    return step, "port", "oracle port of loss_func.py ContrastiveLoss (oracle/_ref was never staged)"
+
+
+def cpu_loss_baseline(n, repeats=2):
+    """The reference's loss fwd+bwd in fp32 on the host cores (bounded sample: N rows of the 32768-row workload)."""
+    import torch
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     feats, labels = synth_loss_rows(torch, n, 0, n, "cpu", torch.float32)
-    loss_oracle.contrastive_loss_and_grads(feats, labels, SCALE)  # warm-up
+    step, kind, what = reference_loss_step(torch)
+    step(feats, labels)  # warm-up
     best = float("inf")
     for _ in range(repeats):
         t0 = time.perf_counter()
-        loss_oracle.contrastive_loss_and_grads(feats, labels, SCALE)
+        step(feats, labels)
         best = min(best, time.perf_counter() - t0)
-    return {"value": n / best, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"oracle port of ContrastiveLoss fwd+bwd, fp32, 3 modalities, N={n} (N=32768 needs >100 GB of "
-                      f"N x N tensors on the CPU path and is not runnable as written); best of {repeats}",
+    return {"value": n / best, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{what}, fwd+bwd, fp32, 3 modalities, N={n} (N=32768 needs >100 GB of N x N tensors on the CPU "
+                      f"path and is not runnable as written); best of {repeats}",
             "seconds": best}
 
 
 # ---------------------------------------------------------------------------------------------
-# reference arm: the reference's CPU path (oracle port) on the host cores
+# reference arm: the reference's own CPU implementation on the host cores
 # ---------------------------------------------------------------------------------------------
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
@@ -182,29 +206,29 @@ def run_reference(args):
         return
     import torch
 
-    from oracle import loss_oracle
-
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     n = CPU_SAMPLE_N
     feats, labels = synth_loss_rows(torch, n, 0, n, "cpu", torch.float32)
+    step, kind, what = reference_loss_step(torch)
     for _ in range(max(1, args.warmup)):
-        loss_oracle.contrastive_loss_and_grads(feats, labels, SCALE)
+        step(feats, labels)
     steps = max(1, args.steps)
     t0 = time.perf_counter()
     for _ in range(steps):
-        loss_oracle.contrastive_loss_and_grads(feats, labels, SCALE)
+        loss = step(feats, labels)
     dt = (time.perf_counter() - t0) / steps
     value = n / dt
-    sample = (f"each step = fwd+bwd of the oracle port of loss_func.py ContrastiveLoss, fp32, 3 modalities, N={n} "
-              f"rows (bounded sample of the 32768-row workload, which the CPU path cannot hold in memory)")
+    sample = (f"each step = fwd+bwd of {what}, fp32, 3 modalities, N={n} rows (bounded sample of the 32768-row "
+              f"workload, which the CPU path cannot hold in memory)")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "image-DNA-text 3-pair InfoNCE fwd+bwd, global batch 32768, 768-d", "sample_rows": n},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "loss": loss,
     }
     emit(line)
 

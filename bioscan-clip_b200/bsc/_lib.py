@@ -79,7 +79,7 @@ def lib():
     L.bsc_gather_layout.argtypes = [c_int64, c_int, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t),
                                     POINTER(c_size_t)]
     L.bsc_gather_push.argtypes = [POINTER(c_void_p), c_int, POINTER(c_int64), c_void_p, c_int64, c_int64, c_int64, c_int,
-                                  POINTER(c_void_p), c_int, c_void_p]
+                                  POINTER(c_void_p), c_void_p, c_int, c_void_p]
     L.bsc_infonce_stats_len.argtypes = [c_int64]
     L.bsc_infonce_stats_len.restype = c_int64
     L.bsc_infonce_plan.argtypes = [POINTER(InfoNceDesc), c_int, c_int, c_size_t, POINTER(InfoNcePlan)]

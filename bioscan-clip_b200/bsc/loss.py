@@ -27,6 +27,17 @@ from .ops import Problem, requested_bwd_mode
 
 TOO_FEW = "Too less element for calculating the contrastive loss."  # loss_func.py:35,142
 
+# Phase marks for tools/dist_phases.py: when a list is installed here, every phase boundary of a loss evaluation
+# records a CUDA event on the current stream (instrumentation only; None in normal use).
+PHASE_MARKS = None
+
+
+def _mark(name: str) -> None:
+    if PHASE_MARKS is not None:
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        PHASE_MARKS.append((name, ev))
+
 
 class LocalComm:
     """world_size == 1: no exchange; the scatter strategy's exchange buffer is ordinary device memory."""
@@ -89,6 +100,7 @@ class SymmMemComm(TorchDistComm):
     def __init__(self, rank: int, world_size: int, group=None, strict: bool = False):
         super().__init__(rank, world_size, group)
         self.strict = strict
+        self.gather_path = "symm_mem"  # "symm_mem+multicast" once a buffer with an NVSwitch multicast address is in use
         self.disabled = False
         self._gather = {}     # (n_global, d, device) -> state
         self._exchange = {}   # (nbytes, device) -> state
@@ -175,12 +187,20 @@ class SymmMemComm(TorchDistComm):
             if made is None:
                 return None
             bufs, handles, peers = made
-            st = {"bufs": bufs, "handles": handles,
+            import os
+
+            # NVSwitch multicast address of each buffer (0 / absent when the fabric has no NVLS): one multimem.st per
+            # 16 bytes reaches every rank.  All ranks see the same capability, so the choice needs no agreement.
+            mcast = [int(getattr(h, "multicast_ptr", 0) or 0) for h in handles]
+            if os.environ.get("BSC_GATHER_MULTICAST") == "0":
+                mcast = [0 for _ in handles]
+            st = {"bufs": bufs, "handles": handles, "mcast": mcast,
                   "peers": [(ctypes.c_void_p * self.world_size)(*pp) for pp in peers],
                   "offx": list(offx), "offi": list(offi), "offl": int(offl.value), "step": 0, "pending": [None, None]}
             self._cache_put(self._gather, key, st)
         b = st["step"] & 1
         st["step"] += 1
+        self.gather_path = "symm_mem+multicast" if st["mcast"][b] else "symm_mem"
         # the OTHER buffer is overwritten by the peers' next forward, which they may start as soon as this rank has
         # arrived at the barrier below: a problem still waiting for its backward there moves to private memory now
         for slot in (b ^ 1, b):
@@ -195,9 +215,12 @@ class SymmMemComm(TorchDistComm):
         ldx = (ctypes.c_int64 * 3)(*[0 if f is None else f.stride(0) for f in feats])
         with torch.cuda.device(f0.device):
             _lib.check(_lib.lib().bsc_gather_push(x, _lib.dtype_code(f0.dtype), ldx, labels.data_ptr(), n_local,
-                                                  self.rank * n_local, n_global, d, st["peers"][b], self.world_size,
+                                                  self.rank * n_local, n_global, d, st["peers"][b],
+                                                  st["mcast"][b] or None, self.world_size,
                                                   _lib.stream_ptr(f0.device)))
+            _mark("gather_push")
             st["handles"][b].barrier(channel=0)
+            _mark("gather_barrier")
         buf = st["bufs"][b]
         xh, inv = [], []
         for m, f in enumerate(feats):
@@ -279,6 +302,7 @@ def infonce_forward(ops, comm, feats: List[Optional[torch.Tensor]], labels: torc
     inv = None
     all_labels = None
     bind = None
+    _mark("start")
     if mode == MODE_F32:
         xh = [None if f is None else comm.all_gather_rows(ops.normalize(f.detach(), torch.float32)) for f in feats]
     else:
@@ -303,7 +327,9 @@ def infonce_forward(ops, comm, feats: List[Optional[torch.Tensor]], labels: torc
     if all_labels is None:
         all_labels = comm.all_gather_rows(labels.detach().to(torch.int64).contiguous())
     n_global = all_labels.shape[0]
+    _mark("gather")
     r, rep, nxt, rmax = ops.label_stats(all_labels)
+    _mark("label_stats")
     prob = Problem(xh=xh, n_global=n_global, n_local=n_local, row0=comm.rank * n_local, d=d, mode=mode,
                    scale=scale, r=r, rep=rep, nxt=nxt, rmax=rmax, inv=inv, all_labels=all_labels,
                    world=comm.world_size, rank=comm.rank)
@@ -314,8 +340,11 @@ def infonce_forward(ops, comm, feats: List[Optional[torch.Tensor]], labels: torc
     if bind is not None and want_grad:
         bind(prob)
     stats = ops.infonce_fwd(prob)
+    _mark("fwd_sweep")
     stats = comm.all_reduce_sum(stats)
+    _mark("stats_all_reduce")
     loss = ops.infonce_loss(prob, stats)
+    _mark("loss")
     return loss, (prob, stats)
 
 
@@ -330,10 +359,14 @@ def infonce_backward(ops, comm, saved, feats, grad_out: torch.Tensor, grad_gain:
     own, ptrs = (None, None)
     if prob.mode == MODE_TC16 and prob.bwd_mode == BWD_SCATTER:
         own, ptrs = comm.exchange(prob.exchange_bytes, dev)
+    _mark("bwd_start")
     ops.infonce_bwd_partials(prob, stats, ptrs)
+    _mark("bwd_partials")
     if own is not None:
         comm.exchange_barrier(dev)  # every rank's partial sums have landed before anyone adds them up
+        _mark("exchange_barrier")
     grads = ops.infonce_bwd_finish(prob, xs, grad_out, own)
+    _mark("bwd_finish")
     prob.done = True
     prob.bwd_workspace = None
     return grads

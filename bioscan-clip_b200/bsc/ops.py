@@ -7,6 +7,7 @@ stand-in defined under ``tests/`` -- the product modules always construct ``Cuda
 from __future__ import annotations
 
 import ctypes
+import os
 from ctypes import byref, c_int, c_size_t, c_void_p
 from dataclasses import dataclass, field
 from typing import List, Optional
@@ -78,6 +79,9 @@ def memory_budget(device) -> int:
 
 class CudaOps:
     name = "cuda"
+
+    def __init__(self):
+        self._plans = {}
 
     # ---- K1 -------------------------------------------------------------------------------------
     def normalize(self, x: torch.Tensor, out_dtype: torch.dtype, zero_rule: int = NORM_TORCH,
@@ -161,18 +165,29 @@ class CudaOps:
         return int(lib().bsc_infonce_stats_len(n_global))
 
     def plan(self, p: Problem, requested: int = _lib.BWD_AUTO, peer_memory: bool = True) -> None:
-        """Resolve the backward strategy once (bsc_infonce_plan) and record the buffer sizes in ``p``."""
+        """Resolve the backward strategy (bsc_infonce_plan) and record the buffer sizes in ``p``.  The verdict depends
+        on the shape of the problem only, so it is asked for once per shape (querying the free device memory costs a
+        driver call per step otherwise); ``forget_plans`` drops the cache, e.g. after an out-of-memory error."""
         dev = self._device(p)
         _lib.require_device(dev)
-        out = _lib.InfoNcePlan()
+        key = (p.n_global, p.n_local, p.row0, p.d, p.mode, tuple(t is not None for t in p.xh), p.world, p.rank,
+               requested, bool(peer_memory), dev, os.environ.get("BSC_BWD_MEM_GB"))
+        hit = self._plans.get(key)
+        if hit is None:
+            out = _lib.InfoNcePlan()
+            p._desc = None
+            budget = memory_budget(dev) if (requested == _lib.BWD_AUTO and p.mode == MODE_TC16) else 0
+            check(lib().bsc_infonce_plan(byref(self._desc(p)), requested, 1 if peer_memory else 0, budget, byref(out)))
+            hit = (int(out.bwd_mode), int(out.fwd_workspace_bytes), int(out.bwd_workspace_bytes),
+                   int(out.exchange_bytes))
+            if len(self._plans) > 64:
+                self._plans.clear()
+            self._plans[key] = hit
+        p.bwd_mode, p.fwd_workspace_bytes, p.bwd_workspace_bytes, p.exchange_bytes = hit
         p._desc = None
-        budget = memory_budget(dev) if (requested == _lib.BWD_AUTO and p.mode == MODE_TC16) else 0
-        check(lib().bsc_infonce_plan(byref(self._desc(p)), requested, 1 if peer_memory else 0, budget, byref(out)))
-        p.bwd_mode = int(out.bwd_mode)
-        p.fwd_workspace_bytes = int(out.fwd_workspace_bytes)
-        p.bwd_workspace_bytes = int(out.bwd_workspace_bytes)
-        p.exchange_bytes = int(out.exchange_bytes)
-        p._desc = None
+
+    def forget_plans(self) -> None:
+        self._plans.clear()
 
     def infonce_fwd(self, p: Problem) -> torch.Tensor:
         dev = self._device(p)

@@ -26,8 +26,8 @@ int taxo_launch(const int64_t* indices, int64_t nq, int k, const int32_t* key_id
                 cudaStream_t st);
 void gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3], size_t* off_labels, size_t* total);
 int gather_push_launch(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels,
-                       int64_t n_local, int64_t row0, int64_t n_global, int d, void* const* peers, int world,
-                       cudaStream_t st);
+                       int64_t n_local, int64_t row0, int64_t n_global, int d, void* const* peers, void* multicast,
+                       int world, cudaStream_t st);
 int label_stats_launch(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax, char* ws,
                        cudaStream_t st);
 int loss_launch(const float* stats, const float* r, int64_t n, unsigned present_mask, float scale, float* loss,
@@ -330,7 +330,8 @@ int bsc_gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[
 }
 
 int bsc_gather_push(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels, int64_t n_local,
-                    int64_t row0, int64_t n_global, int d, void* const* peer_buffers, int world, void* stream) {
+                    int64_t row0, int64_t n_global, int d, void* const* peer_buffers, void* multicast_buffer, int world,
+                    void* stream) {
   BSC_REQUIRE(x && ldx && peer_buffers, BSC_EINVAL, "bsc_gather_push: null pointer");
   BSC_REQUIRE(world >= 1 && world <= kMaxPeers, BSC_EUNSUPPORTED, "bsc_gather_push: world=%d (1..%d supported)", world,
               kMaxPeers);
@@ -341,7 +342,9 @@ int bsc_gather_push(const void* const x[3], int x_dtype, const int64_t ldx[3], c
   for (int m = 0; m < 3; ++m)
     BSC_REQUIRE(!x[m] || ldx[m] >= d, BSC_EINVAL, "bsc_gather_push: ldx[%d] < d", m);
   for (int r = 0; r < world; ++r) BSC_REQUIRE(peer_buffers[r], BSC_EINVAL, "bsc_gather_push: peer %d is null", r);
-  return gather_push_launch(x, x_dtype, ldx, labels, n_local, row0, n_global, d, peer_buffers, world,
+  BSC_REQUIRE(multicast_buffer == nullptr || ((uintptr_t)multicast_buffer & 15) == 0, BSC_EINVAL,
+              "bsc_gather_push: multicast address is not 16-byte aligned");
+  return gather_push_launch(x, x_dtype, ldx, labels, n_local, row0, n_global, d, peer_buffers, multicast_buffer, world,
                             (cudaStream_t)stream);
 }
 

@@ -192,11 +192,26 @@ struct GatherPushArgs {
   int64_t ldx[3];
   const int64_t* labels;  // local labels
   char* peer[kMaxPeers];  // base of every rank's symmetric buffer (index = rank)
+  char* mc;               // NVSwitch multicast address of the same buffer (one store reaches every rank), or null
   int world;
   int64_t n_local, n_global, row0;
   int d;
   size_t off_xh[3], off_inv[3], off_labels;
 };
+
+// One store to the multicast address is replicated by the NVSwitch into every rank's buffer: the gather then costs each
+// rank its OWN rows of NVLink egress (19 MB at 8 x 4096 x 768 x 3) instead of one copy per peer (132 MB, 0.25 ms).
+__device__ __forceinline__ void mc_store16(void* addr, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void mc_store8(void* addr, uint2 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(addr), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ void mc_store4(void* addr, uint32_t v) {
+  asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
 
 template <typename TI>
 __global__ void __launch_bounds__(256) gather_push_kernel(const GatherPushArgs a) {
@@ -242,15 +257,28 @@ __global__ void __launch_bounds__(256) gather_push_kernel(const GatherPushArgs a
 #pragma unroll
     for (int t = 0; t < 8; ++t) hv[t] = __float2half_rn(to_f32<TI>(xr[c0 + t]) * scale);
     const uint4 pk = *reinterpret_cast<const uint4*>(hv);
-    for (int r = 0; r < a.world; ++r)
-      *reinterpret_cast<uint4*>(a.peer[r] + a.off_xh[m] + ((size_t)g * d + c0) * 2) = pk;
+    const size_t off = a.off_xh[m] + ((size_t)g * d + c0) * 2;
+    if (a.mc != nullptr) {
+      mc_store16(a.mc + off, pk);
+    } else {
+      for (int r = 0; r < a.world; ++r) *reinterpret_cast<uint4*>(a.peer[r] + off) = pk;
+    }
   }
-  if (lane < a.world) *reinterpret_cast<float*>(a.peer[lane] + a.off_inv[m] + (size_t)g * 4) = inv_row;
   // the label of the row travels with the first present modality's warp
   int first = 0;
   while (first < 3 && a.x[first] == nullptr) ++first;
-  if (m == first && a.labels != nullptr && lane < a.world)
-    *reinterpret_cast<int64_t*>(a.peer[lane] + a.off_labels + (size_t)g * 8) = a.labels[l];
+  const bool with_label = m == first && a.labels != nullptr;
+  if (a.mc != nullptr) {
+    if (lane == 0) mc_store4(a.mc + a.off_inv[m] + (size_t)g * 4, __float_as_uint(inv_row));
+    if (lane == 1 && with_label) {
+      const int64_t lab = a.labels[l];
+      mc_store8(a.mc + a.off_labels + (size_t)g * 8, make_uint2((uint32_t)lab, (uint32_t)((uint64_t)lab >> 32)));
+    }
+  } else {
+    if (lane < a.world) *reinterpret_cast<float*>(a.peer[lane] + a.off_inv[m] + (size_t)g * 4) = inv_row;
+    if (with_label && lane < a.world)
+      *reinterpret_cast<int64_t*>(a.peer[lane] + a.off_labels + (size_t)g * 8) = a.labels[l];
+  }
 }
 
 void gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3], size_t* off_labels, size_t* total) {
@@ -265,8 +293,8 @@ void gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3],
 }
 
 int gather_push_launch(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels,
-                       int64_t n_local, int64_t row0, int64_t n_global, int d, void* const* peers, int world,
-                       cudaStream_t st) {
+                       int64_t n_local, int64_t row0, int64_t n_global, int d, void* const* peers, void* multicast,
+                       int world, cudaStream_t st) {
   if (n_local == 0) return BSC_OK;
   GatherPushArgs a{};
   for (int m = 0; m < 3; ++m) {
@@ -275,6 +303,7 @@ int gather_push_launch(const void* const x[3], int x_dtype, const int64_t ldx[3]
   }
   a.labels = labels;
   for (int r = 0; r < world; ++r) a.peer[r] = (char*)peers[r];
+  a.mc = (char*)multicast;
   a.world = world;
   a.n_local = n_local;
   a.n_global = n_global;

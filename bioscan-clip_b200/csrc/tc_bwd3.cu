@@ -510,14 +510,15 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, int
               "tc_bwd_gemms: %zu work items exceed the schedule capacity %d (batch too large for the stored-weight "
               "backward)", total, MAX_SCHED);
   {
-    const size_t round = (size_t)(device_sm_count() / 2);
-    size_t pos[2] = {0, 0}, w = 0;
-    int kind = 0;
-    while (w < total) {
+    // item w runs on cluster w % C in its round w / C: neighbouring cluster PAIRS (the two d chunks of one A tile) take
+    // opposite kinds and every cluster alternates between the kinds, so that at any time half of the SMs are in a
+    // scattered item -- all of them at once would push 29 MB at the NVLink ports in one burst at the end of a round
+    const size_t C = (size_t)(device_sm_count() / 2);
+    size_t pos[2] = {0, 0};
+    for (size_t w = 0; w < total; ++w) {
+      int kind = (int)(((w / C) + ((w % C) / (size_t)nchunk)) & 1u);
       if (pos[kind] >= lists[kind].size()) kind ^= 1;
-      const size_t take = std::min(round, lists[kind].size() - pos[kind]);
-      for (size_t t = 0; t < take; ++t) p.sched[w++] = lists[kind][pos[kind]++];
-      kind ^= 1;
+      p.sched[w] = lists[kind][pos[kind]++];
     }
   }
   p.num_items = (int)total;

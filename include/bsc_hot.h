@@ -90,11 +90,15 @@ int bsc_rows_to_f16(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, v
  * row row0 + l (fp16 row, scale, label) into EVERY rank's buffer.  The caller must run a cross-rank barrier on the
  * stream after the call before any rank reads its buffer, and must not push into a buffer a peer may still read
  * (alternate two buffers by step).  All modalities share x_dtype; x[m] = NULL marks an absent modality.
+ * multicast_buffer: the NVSwitch multicast address of the same buffer (torch symmetric memory: multicast_ptr) or NULL.
+ * When given, every row is stored ONCE with multimem.st and the switch replicates it into all ranks' buffers: the
+ * gather costs a rank the NVLink egress of its own rows instead of one copy per peer.
  * ---------------------------------------------------------------------------------------------- */
 int bsc_gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3], size_t* off_labels,
                       size_t* total_bytes);
 int bsc_gather_push(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels, int64_t n_local,
-                    int64_t row0, int64_t n_global, int d, void* const* peer_buffers, int world, void* stream);
+                    int64_t row0, int64_t n_global, int d, void* const* peer_buffers, void* multicast_buffer, int world,
+                    void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * K2  label statistics replacing construct_label_metrix (loss_func.py:18-21): for labels[n]
