@@ -14,7 +14,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("BSC_LIB_PATH") or os.path.join(_HERE, "libbsc_hot.so")  # override: A/B of two builds
 
-BSC_F32, BSC_BF16, BSC_F16 = 0, 1, 2
+BSC_F32, BSC_BF16, BSC_F16, BSC_F64 = 0, 1, 2, 3
 MODE_F32, MODE_TC16 = 0, 1
 BWD_AUTO, BWD_RECOMPUTE, BWD_BLOCKS, BWD_SCATTER = -1, 0, 3, 4
 BWD_NAMES = {"auto": BWD_AUTO, "recompute": BWD_RECOMPUTE, "blocks": BWD_BLOCKS, "scatter": BWD_SCATTER}
@@ -134,6 +134,8 @@ def dtype_code(dt: torch.dtype) -> int:
         return BSC_BF16
     if dt == torch.float16:
         return BSC_F16
+    if dt == torch.float64:
+        return BSC_F64  # accepted by bsc_l2norm_fwd only (the reference's float64 eval features)
     raise BscError(f"unsupported dtype {dt}: bsc ops take float32, bfloat16 or float16")
 
 

@@ -82,6 +82,7 @@ class CudaOps:
 
     def __init__(self):
         self._plans = {}
+        self._ws = {}
 
     # ---- K1 -------------------------------------------------------------------------------------
     def normalize(self, x: torch.Tensor, out_dtype: torch.dtype, zero_rule: int = NORM_TORCH,
@@ -243,6 +244,14 @@ class CudaOps:
         return grads
 
     # ---- retrieval ------------------------------------------------------------------------------
+    def _scratch(self, key, nbytes: int, device) -> torch.Tensor:
+        """Workspace kept between searches (one per device and role): a search of the same shape allocates nothing."""
+        buf = self._ws.get((key, device))
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+            self._ws[(key, device)] = buf
+        return buf
+
     def bank_search(self, queries: torch.Tensor, bank: torch.Tensor, k: int, base_id: int, mode: int):
         dev = bank.device
         _lib.require_device(dev)
@@ -250,7 +259,7 @@ class CudaOps:
         nb = bank.shape[0]
         nbytes = c_size_t(0)
         check(lib().bsc_bank_search_workspace_bytes(nq, nb, d, k, mode, byref(nbytes)))
-        ws = torch.empty(int(nbytes.value), dtype=torch.uint8, device=dev)
+        ws = self._scratch("search", int(nbytes.value), dev)
         scores = torch.empty((nq, k), dtype=torch.float32, device=dev)
         ids = torch.empty((nq, k), dtype=torch.int64, device=dev)
         with torch.cuda.device(dev):
@@ -259,23 +268,24 @@ class CudaOps:
                                         stream_ptr(dev)))
         return scores, ids
 
-    def bank_search_exact(self, queries32: torch.Tensor, bank32: torch.Tensor, bank16: torch.Tensor, k: int,
-                          base_id: int, max_row_norm: float, min_parts: int = 16):
-        """Exact float32 top-k through the bf16 screening pass + float32 re-scoring; queries whose result the bound
-        cannot prove are re-run with the exhaustive float32 kernel.  Returns (scores, ids, n_rechecked)."""
+    def bank_search_exact_launch(self, queries32: torch.Tensor, bank32: torch.Tensor, bank16: torch.Tensor, k: int,
+                                 base_id: int, max_row_norm: float, min_parts: int = 16):
+        """Exact float32 top-k, device side only: bf16 screening pass + float32 re-scoring + per-query proof.  Returns
+        (scores, ids, unsure flags, n_unsure) without synchronising; ``bank_search_exact_finish`` re-runs the unproven
+        queries.  None when the shape is outside the screening kernel's range (the caller searches exhaustively)."""
         dev = bank32.device
         _lib.require_device(dev)
         nq, d = queries32.shape
         nb = bank32.shape[0]
         if k > 8 or d % 64 != 0 or nb == 0 or nq == 0:
-            s, i = self.bank_search(queries32, bank32, k, base_id, MODE_F32)
-            return s, i, nq
+            return None
         parts = c_int(0)
         check(lib().bsc_bank_screen_parts(nq, nb, min_parts, byref(parts)))
         parts = int(parts.value)
         q16 = queries32.to(torch.bfloat16).contiguous()
-        cs = torch.empty((parts, nq, 8), dtype=torch.float32, device=dev)
-        ci = torch.empty((parts, nq, 8), dtype=torch.int64, device=dev)
+        cand = self._scratch("screen", parts * nq * 8 * 12, dev)
+        cs = cand[:parts * nq * 8 * 4].view(torch.float32).view(parts, nq, 8)
+        ci = cand[parts * nq * 8 * 4:parts * nq * 8 * 12].view(torch.int64).view(parts, nq, 8)
         scores = torch.empty((nq, k), dtype=torch.float32, device=dev)
         ids = torch.empty((nq, k), dtype=torch.int64, device=dev)
         unsure = torch.empty(nq, dtype=torch.int32, device=dev)
@@ -288,6 +298,11 @@ class CudaOps:
             check(lib().bsc_bank_rescore(queries32.data_ptr(), nq, bank32.data_ptr(), nb, d, base_id, cs.data_ptr(),
                                          ci.data_ptr(), parts, k, eps_scale, scores.data_ptr(), ids.data_ptr(),
                                          unsure.data_ptr(), n_unsure.data_ptr(), stream_ptr(dev)))
+        return scores, ids, unsure, n_unsure
+
+    def bank_search_exact_finish(self, launched, queries32, bank32, k: int, base_id: int):
+        """Second half of the exact search: one host read of the unproven count, exhaustive re-search of those."""
+        scores, ids, unsure, n_unsure = launched
         n_bad = int(n_unsure.item())
         if n_bad:
             rows = torch.nonzero(unsure, as_tuple=False).flatten()
@@ -295,6 +310,16 @@ class CudaOps:
             scores[rows] = s2
             ids[rows] = i2
         return scores, ids, n_bad
+
+    def bank_search_exact(self, queries32: torch.Tensor, bank32: torch.Tensor, bank16: torch.Tensor, k: int,
+                          base_id: int, max_row_norm: float, min_parts: int = 16):
+        """Exact float32 top-k through the bf16 screening pass + float32 re-scoring; queries whose result the bound
+        cannot prove are re-run with the exhaustive float32 kernel.  Returns (scores, ids, n_rechecked)."""
+        launched = self.bank_search_exact_launch(queries32, bank32, bank16, k, base_id, max_row_norm, min_parts)
+        if launched is None:
+            s, i = self.bank_search(queries32, bank32, k, base_id, MODE_F32)
+            return s, i, queries32.shape[0]
+        return self.bank_search_exact_finish(launched, queries32, bank32, k, base_id)
 
     def topk_merge(self, cand_scores: torch.Tensor, cand_ids: torch.Tensor):
         """[parts, nq, k] candidate lists -> [nq, k] (score desc, id asc)."""

@@ -9,10 +9,11 @@
 
 The bank lives in HBM, split row-wise over ``devices`` at ``add`` time (one shard per GPU); a search scans
 every shard on its own GPU and merges the per-shard top-k with ``bsc_topk_merge``.
-``precision="fp32"`` is the exact mode (float32 bank, indices comparable bit for bit with a float32 CPU
-search, exhaustive CUDA-core kernel); ``precision="exact"`` returns the same float32 results at tensor-core speed
-(bf16 screening pass + exact re-scoring of the candidates + a proof per query, unproven queries re-run
-exhaustively); ``precision="bf16"`` stores the bank in bfloat16 and scans it with the tcgen05 kernel.
+``precision="exact"`` (the default) returns float32 results -- indices comparable bit for bit with a float32 CPU search,
+which is what faiss ``IndexFlatIP`` computes -- at tensor-core speed: bf16 screening pass + exact re-scoring of the
+candidates + a proof per query, unproven queries re-run exhaustively.  ``precision="fp32"`` is the exhaustive CUDA-core
+float32 kernel itself (same results, the small-problem checker); ``precision="bf16"`` stores the bank in bfloat16 and
+scans it with the tcgen05 kernel (bandwidth mode: bf16-rounded scores).
 """
 from __future__ import annotations
 
@@ -34,7 +35,7 @@ def _as_f32_tensor(x, device) -> torch.Tensor:
 
 
 class IndexFlatIP:
-    def __init__(self, d: int, precision: str = "fp32", devices: Optional[Sequence] = None, ops=None,
+    def __init__(self, d: int, precision: str = "exact", devices: Optional[Sequence] = None, ops=None,
                  base_id: int = 0):
         if precision not in ("fp32", "bf16", "exact"):
             raise ValueError("precision must be 'fp32', 'bf16' or 'exact'")
@@ -93,26 +94,48 @@ class IndexFlatIP:
         self.ntotal += n
 
     def search_device(self, q, k: int):
-        """Search returning device tensors (scores, ids) on the first device."""
+        """Search returning device tensors (scores, ids) on the first device.  Every shard is scanned on its own GPU, on
+        that GPU's current stream: all launches are queued before the first host read, so the shards run concurrently."""
         dev0 = self.devices[0]
         q0 = _as_f32_tensor(q, dev0)
         self.last_rechecked = 0
         if q0.shape[1] != self.d:
             raise ValueError(f"expected queries of dimension {self.d}, got {q0.shape[1]}")
-        cand_s, cand_i = [], []
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream(dev0))
+        pending = []   # (device, queries on it, rows, base, launched-or-result)
         for kdev, dev in enumerate(self.devices):
             if not self._chunks[kdev]:
                 continue
-            qd = q0.to(dev).to(self._dtype).contiguous()
-            for ci, (base, rows) in enumerate(zip(self._bases[kdev], self._chunks[kdev])):
-                if self.precision == "exact":
-                    rows16, max_norm = self._screen[kdev][ci]
-                    s, i, nbad = self._ops.bank_search_exact(qd, rows, rows16, k, base, max_norm)
+            with torch.cuda.device(dev):
+                if dev != dev0:
+                    torch.cuda.current_stream(dev).wait_event(ready)
+                qd = q0.to(dev, non_blocking=True).to(self._dtype).contiguous()
+                for ci, (base, rows) in enumerate(zip(self._bases[kdev], self._chunks[kdev])):
+                    if self.precision == "exact":
+                        rows16, max_norm = self._screen[kdev][ci]
+                        launched = self._ops.bank_search_exact_launch(qd, rows, rows16, k, base, max_norm)
+                        if launched is None:
+                            launched = self._ops.bank_search(qd, rows, k, base, MODE_F32) + (None, None)
+                            self.last_rechecked += qd.shape[0]
+                        pending.append((dev, qd, rows, base, launched))
+                    else:
+                        pending.append((dev, qd, rows, base, self._ops.bank_search(qd, rows, k, base, self._mode)))
+        cand_s, cand_i = [], []
+        for dev, qd, rows, base, res in pending:
+            with torch.cuda.device(dev):
+                if self.precision == "exact" and res[2] is not None:
+                    s, i, nbad = self._ops.bank_search_exact_finish(res, qd, rows, k, base)
                     self.last_rechecked += nbad
                 else:
-                    s, i = self._ops.bank_search(qd, rows, k, base, self._mode)
-                cand_s.append(s.to(dev0))
-                cand_i.append(i.to(dev0))
+                    s, i = res[0], res[1]
+                if dev != dev0:
+                    done = torch.cuda.Event()
+                    done.record(torch.cuda.current_stream(dev))
+                    s, i = s.to(dev0, non_blocking=True), i.to(dev0, non_blocking=True)
+                    torch.cuda.current_stream(dev0).wait_event(done)
+            cand_s.append(s)
+            cand_i.append(i)
         nq = q0.shape[0]
         if not cand_s:
             cs = torch.empty((0, nq, k), dtype=torch.float32, device=dev0)
@@ -120,7 +143,8 @@ class IndexFlatIP:
         elif len(cand_s) == 1:
             return cand_s[0], cand_i[0]
         else:
-            cs, ci = torch.stack(cand_s), torch.stack(cand_i)
+            with torch.cuda.device(dev0):
+                cs, ci = torch.stack(cand_s), torch.stack(cand_i)
         return self._ops.topk_merge(cs, ci)
 
     def search(self, q, k: int):
@@ -128,8 +152,24 @@ class IndexFlatIP:
         return s.cpu().numpy(), i.cpu().numpy()
 
 
+def _normalized_f32(ops, x, device) -> torch.Tensor:
+    """sklearn ``normalize(x, norm='l2', axis=1).astype(np.float32)`` (inference_and_eval.py:416-417) on the device.
+    float64 input (what inference_epoch.py:67 produces) is normalised IN float64 and rounded once, like the reference;
+    float32 input is normalised in float32, as sklearn does for float32 arrays."""
+    if isinstance(x, torch.Tensor):
+        t = x.to(device)
+        if t.dtype not in (torch.float32, torch.float64):
+            t = t.to(torch.float32)
+    else:
+        arr = np.asarray(x)
+        if arr.dtype not in (np.float32, np.float64):
+            arr = arr.astype(np.float64)
+        t = torch.from_numpy(np.ascontiguousarray(arr)).to(device)
+    return ops.normalize(t.contiguous(), torch.float32, NORM_SKLEARN)
+
+
 def make_prediction(query_feature, keys_feature, keys_label, with_similarity=False, with_indices=False, max_k=5,
-                    precision: str = "fp32", devices=None, ops=None):
+                    precision: str = "exact", devices=None, ops=None):
     """scripts/inference_and_eval.py:414-445 on the GPU: L2-normalise both sides with sklearn's zero rule,
     float32, inner-product top-max_k, then map the hits to their taxonomy labels."""
     if ops is None:
@@ -138,13 +178,18 @@ def make_prediction(query_feature, keys_feature, keys_label, with_similarity=Fal
         ops = CudaOps()
     index = IndexFlatIP(keys_feature.shape[-1], precision=precision, devices=devices, ops=ops)
     dev0 = index.devices[0]
-    keys = ops.normalize(_as_f32_tensor(keys_feature, dev0), torch.float32, NORM_SKLEARN)
-    queries = ops.normalize(_as_f32_tensor(query_feature, dev0), torch.float32, NORM_SKLEARN)
+    keys = _normalized_f32(ops, keys_feature, dev0)
+    queries = _normalized_f32(ops, query_feature, dev0)
     index.add(keys)
     similarities, indices = index.search(queries, max_k)
-    pred_list = []
-    for key_indices in indices:
-        pred_list.append({level: [keys_label[int(i)][level] for i in key_indices] for level in LEVELS})
+    # label mapping of :422-433, one object-array gather per level instead of a Python loop over every hit
+    # (bsc.TaxonomyEval does the accuracy bookkeeping on the device without building these lists at all)
+    per_level = {}
+    for level in LEVELS:
+        names = np.empty(len(keys_label), dtype=object)
+        names[:] = [kl[level] for kl in keys_label]
+        per_level[level] = names[indices].tolist()  # a padding id -1 indexes from the end, as keys_label[-1] does there
+    pred_list = [{level: per_level[level][q] for level in LEVELS} for q in range(indices.shape[0])]
     out = [pred_list]
     if with_similarity:
         out.append(similarities)

@@ -322,6 +322,35 @@ int gather_push_launch(const void* const x[3], int x_dtype, const int64_t ldx[3]
   return BSC_OK;
 }
 
+// float64 rows (the reference's eval features, inference_epoch.py:67): sum of squares, square root and the quotient in
+// float64, ONE rounding to the output type -- normalize(x).astype(float32) of inference_and_eval.py:416-417.
+template <typename TO>
+__global__ void __launch_bounds__(256) l2norm_rows_f64_kernel(const double* __restrict__ x, int64_t n, int d,
+                                                              int64_t ldx, TO* __restrict__ y16,
+                                                              float* __restrict__ y32, float* __restrict__ inv_norm,
+                                                              int zero_rule) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= n) return;
+  const double* xr = x + row * ldx;
+  double ss = 0.0;
+  for (int c = lane; c < d; c += 32) ss = fma(xr[c], xr[c], ss);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  const double nrm = sqrt(ss);
+  double div;
+  if (zero_rule == BSC_NORM_SKLEARN)
+    div = (nrm < 2.220446049250313e-15) ? 1.0 : nrm;  // 10 * eps(float64): the row is left as it is
+  else
+    div = fmax(nrm, 1e-12);
+  if (inv_norm != nullptr && lane == 0) inv_norm[row] = (float)(1.0 / div);
+  for (int c = lane; c < d; c += 32) {
+    const float v = (float)(xr[c] / div);
+    if (y16 != nullptr) y16[row * (int64_t)d + c] = from_f32<TO>(v);
+    if (y32 != nullptr) y32[row * (int64_t)d + c] = v;
+  }
+}
+
 template <typename TI>
 static int l2norm_dispatch_out(const void* x, int64_t n, int d, int64_t ldx, void* y16, int y16_dtype, float* y32,
                                float* inv_norm, int zero_rule, cudaStream_t st) {
@@ -343,6 +372,17 @@ static int l2norm_dispatch_out(const void* x, int64_t n, int d, int64_t ldx, voi
 int l2norm_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, int y16_dtype, float* y32,
                   float* inv_norm, int zero_rule, cudaStream_t st) {
   if (n == 0) return BSC_OK;
+  if (x_dtype == BSC_F64) {
+    dim3 block(256), grid((unsigned)((n + 7) / 8));
+    if (y16 != nullptr && y16_dtype == BSC_BF16)
+      l2norm_rows_f64_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const double*)x, n, d, ldx, (__nv_bfloat16*)y16,
+                                                                    y32, inv_norm, zero_rule);
+    else
+      l2norm_rows_f64_kernel<__half><<<grid, block, 0, st>>>((const double*)x, n, d, ldx, (__half*)y16, y32, inv_norm,
+                                                             zero_rule);
+    BSC_LAUNCH_CHECK("l2norm_rows_f64_kernel");
+    return BSC_OK;
+  }
   switch (x_dtype) {
     case BSC_F32: return l2norm_dispatch_out<float>(x, n, d, ldx, y16, y16_dtype, y32, inv_norm, zero_rule, st);
     case BSC_BF16:

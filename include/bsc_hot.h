@@ -48,6 +48,7 @@ extern "C" {
 #define BSC_F32 0
 #define BSC_BF16 1
 #define BSC_F16 2
+#define BSC_F64 3 /* input of bsc_l2norm_fwd only: the reference's eval features are float64 numpy arrays */
 
 /* arithmetic modes */
 #define BSC_MODE_F32 0  /* SIMT fp32 path: exact-parity mode (1e-5 vs the fp32 reference)          */
@@ -70,6 +71,8 @@ int bsc_device_check(void);
  *     simple_clip.py:34-49, inference_and_eval.py:416-417.
  *     y16 (BSC_F16 or BSC_BF16, may be NULL) and y32 (float, may be NULL) receive x * inv_norm;
  *     inv_norm[n] (may be NULL) receives the factor itself.
+ *     x_dtype BSC_F64: norm and quotient are formed in float64 and rounded ONCE to the output type, as
+ *     sklearn normalize(float64 array).astype(float32) does (inference_and_eval.py:416-417).
  * ---------------------------------------------------------------------------------------------- */
 int bsc_l2norm_fwd(const void* x, int x_dtype, int64_t n, int d, int64_t ldx,
                    void* y16, int y16_dtype, float* y32, float* inv_norm, int zero_rule, void* stream);

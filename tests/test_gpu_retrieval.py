@@ -228,3 +228,92 @@ def test_exact_mode_screen_and_rescore_equals_exhaustive_float32(nb, nq, d, n_ra
     idx2 = bsc.IndexFlatIP(d, precision="exact")
     idx2.add(bank * scale)
     assert np.array_equal(idx2.search(q, 5)[1], ro.search_ip(bank * scale, q, 5)[1])
+
+
+def test_concatenated_feature_width_1536_and_per_k_searches():
+    """The shapes the reference's eval uses besides 768-d: `concatenated_feature` (image + DNA, 1536-d,
+    scripts/inference_and_eval.py:753-754) and one search per k in k_list on ONE index
+    (bioscanclip/epoch/eval_epoch.py:199-203): k = 1, 3, 5 must be prefixes of each other."""
+    import bsc
+
+    bank, q, pi = bank_inputs(9000, 70, 1536, seed=5, n_random=8)
+    want_s, want_i = ro.search_ip(bank, q, 5)
+    for precision in ("exact", "fp32"):
+        index = bsc.IndexFlatIP(1536, precision=precision)
+        index.add(bank)
+        got = {}
+        for k in (1, 3, 5):
+            s, i = index.search(q, k)
+            assert s.shape == (70, k) and i.dtype == np.int64
+            got[k] = i
+            np.testing.assert_array_equal(i, want_i[:, :k])
+            np.testing.assert_allclose(s, want_s[:, :k], rtol=0, atol=4e-6)
+        assert np.array_equal(got[5][:, :1], got[1]) and np.array_equal(got[5][:, :3], got[3])
+    index = bsc.IndexFlatIP(1536, precision="bf16")
+    index.add(bank)
+    np.testing.assert_array_equal(index.search(q[:60], 5)[1][:, 0], pi[:60])  # planted neighbours (random tail excluded)
+
+
+def test_default_precision_is_the_exact_float32_search():
+    """A drop-in user (`import bsc as faiss`) gets float32 results from the tensor-core path, not the slow checker."""
+    import bsc
+
+    bank, q, _ = bank_inputs(30000, 64, 768, seed=6, n_random=16)
+    index = bsc.IndexFlatIP(768)
+    assert index.precision == "exact"
+    index.add(bank)
+    s, i = index.search(q, 5)
+    np.testing.assert_array_equal(i, ro.search_ip(bank, q, 5)[1])
+    # the second search of the same shape reuses the cached workspaces: same answer
+    s2, i2 = index.search(q, 5)
+    assert np.array_equal(i, i2) and np.array_equal(s, s2)
+
+
+def test_make_prediction_normalises_float64_in_float64():
+    """inference_and_eval.py:416-417: normalize(float64 array).astype(float32).  The operands of the search must be
+    the SAME float32 numbers the reference feeds faiss, bit for bit (rounding the rows to float32 before normalising
+    changes the last bit of about a third of them)."""
+    import bsc
+    from bsc.retrieval import _normalized_f32
+    from bsc.ops import CudaOps
+
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((500, 768)) * rng.uniform(0.1, 30.0, size=(500, 1))
+    x[7] = 0.0  # sklearn leaves zero rows alone
+    want = ro.l2_normalize_rows(x).astype(np.float32)
+    got = _normalized_f32(CudaOps(), x, torch.device("cuda")).cpu().numpy()
+    assert np.array_equal(got[7], np.zeros(768, np.float32))
+    mism = (got != want).mean()
+    # float64 sqrt / division are correctly rounded on both sides; only the summation order of the norm differs
+    assert mism <= 1e-4, mism
+    naive = ro.l2_normalize_rows(x.astype(np.float32)).astype(np.float32)
+    assert (naive != want).mean() > 0.05  # the order of rounding matters: this is what the float64 path avoids
+    labels = [{lv: f"{lv}_{i % 11}" for lv in ro.LEVELS} for i in range(500)]
+    q = x[:40] + 0.01 * rng.standard_normal((40, 768))
+    ref = ro.make_prediction(q, x, labels, True, True, 5)
+    out = bsc.make_prediction(q, x, labels, True, True, 5)
+    assert out[0] == ref[0]
+    np.testing.assert_array_equal(out[2], ref[2])
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs two GPUs")
+@pytest.mark.parametrize("precision", ["exact", "bf16", "fp32"])
+def test_index_sharded_over_two_devices_in_one_process(precision):
+    """IndexFlatIP(devices=[cuda:0, cuda:1]): function attributes and SM counts are per device, the shards are scanned
+    concurrently, duplicates across the shard boundary keep the lowest id."""
+    import bsc
+
+    bank, q, pi = bank_inputs(40000, 200, 768, seed=9, n_random=20)
+    bank[30000] = bank[100]  # a tie across the two shards
+    q[0] = bank[100]
+    index = bsc.IndexFlatIP(768, precision=precision, devices=["cuda:0", "cuda:1"])
+    index.add(bank)
+    s, i = index.search(q, 5)
+    if precision == "bf16":
+        rb = torch.from_numpy(bank).bfloat16().float().numpy()
+        rq = torch.from_numpy(q).bfloat16().float().numpy()
+        want = ro.search_ip(rb, rq, 5)[1]
+        np.testing.assert_array_equal(i[:, 0], want[:, 0])
+    else:
+        np.testing.assert_array_equal(i, ro.search_ip(bank, q, 5)[1])
+    assert i[0, 0] == 100 and i[0, 1] == 30000
