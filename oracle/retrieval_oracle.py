@@ -132,3 +132,36 @@ def search_ip_topk_torch(keys, queries, k: int, block: int = 262144, threads: in
         ms, mi = torch.topk(cs, k, dim=1)
         best_s, best_i = ms, torch.gather(ci, 1, mi)
     return best_s.numpy(), best_i.numpy()
+
+
+def search_ip_blocked_topk(keys, queries, k: int, slack: int = 8, block: int = 262144, threads: int = 0):
+    """search_ip for large banks: per bank block a float32 sgemm and ``torch.topk(k + slack)`` pick candidates, the
+    final order (score desc, id asc) is decided by one lexsort over the few hundred candidates of a query -- the same
+    result as search_ip unless more than k + slack rows of ONE block tie exactly at a query's k-th score.  Used by
+    bench.py as the checker of the 5M-row search and as its timed CPU baseline (blocked sgemm + k-selection is how a
+    CPU IndexFlatIP spends its time, inference_and_eval.py:418-421)."""
+    import torch
+
+    if threads:
+        torch.set_num_threads(threads)
+    kt = torch.as_tensor(np.ascontiguousarray(keys, dtype=np.float32)) if not hasattr(keys, "numpy") else keys
+    qt = torch.as_tensor(np.ascontiguousarray(queries, dtype=np.float32))
+    nq, nb = qt.shape[0], kt.shape[0]
+    cs, ci = [], []
+    for lo in range(0, nb, block):
+        hi = min(nb, lo + block)
+        s = qt @ kt[lo:hi].T
+        kk = min(k + slack, hi - lo)
+        ts, ti = torch.topk(s, kk, dim=1)
+        cs.append(ts)
+        ci.append(ti + lo)
+    cand_s = torch.cat(cs, dim=1).numpy()
+    cand_i = torch.cat(ci, dim=1).numpy()
+    order = np.lexsort((cand_i, -cand_s.astype(np.float64)), axis=1)[:, :k]
+    out_s = np.take_along_axis(cand_s, order, axis=1)
+    out_i = np.take_along_axis(cand_i, order, axis=1)
+    if out_s.shape[1] < k:  # fewer keys than k: faiss pads
+        pad = k - out_s.shape[1]
+        out_s = np.concatenate([out_s, np.full((nq, pad), FAISS_NEG, np.float32)], axis=1)
+        out_i = np.concatenate([out_i, np.full((nq, pad), -1, np.int64)], axis=1)
+    return out_s.astype(np.float32), out_i.astype(np.int64)

@@ -165,3 +165,20 @@ def test_staged_reference_module_agrees_with_the_port():
     for leaf, gp, gc in zip(leaves, port_grads, cf_grads):
         assert (leaf.grad - gp).abs().max().item() <= 2e-6 * gp.abs().max().item()
         assert (leaf.grad.double() - gc).abs().max().item() <= 2e-6 * gc.abs().max().item()
+
+
+def test_blocked_topk_search_equals_search_ip():
+    """The large-bank checker of bench.py (per-block torch.topk + final (score, id) sort) against search_ip, with
+    duplicated rows inside and across blocks."""
+    rng = np.random.default_rng(2)
+    bank = rng.standard_normal((3000, 48)).astype(np.float32)
+    bank[10] = bank[5]
+    bank[2500] = bank[5]
+    q = (bank[rng.integers(0, 3000, 40)] + 0.1 * rng.standard_normal((40, 48))).astype(np.float32)
+    q[0] = bank[5]
+    want_s, want_i = retrieval_oracle.search_ip(bank, q, 5)
+    got_s, got_i = retrieval_oracle.search_ip_blocked_topk(bank, q, 5, block=700)
+    assert np.array_equal(got_i, want_i) and np.allclose(got_s, want_s, atol=1e-6)
+    assert list(got_i[0, :3]) == [5, 10, 2500]
+    s2, i2 = retrieval_oracle.search_ip_blocked_topk(bank[:3], q, 5)
+    assert np.array_equal(i2, retrieval_oracle.search_ip(bank[:3], q, 5)[1])
