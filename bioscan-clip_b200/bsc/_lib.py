@@ -23,8 +23,8 @@ NORM_TORCH, NORM_SKLEARN = 0, 1
 
 EXPORTS = [
     "bsc_version", "bsc_last_error", "bsc_device_check", "bsc_l2norm_fwd", "bsc_rows_to_f16", "bsc_label_stats", "bsc_label_stats_workspace_bytes",
-    "bsc_gather_layout", "bsc_gather_push",
-    "bsc_infonce_stats_len", "bsc_infonce_plan", "bsc_infonce_fwd", "bsc_infonce_loss",
+    "bsc_gather_layout", "bsc_gather_push", "bsc_gather_push_labels",
+    "bsc_infonce_stats_len", "bsc_infonce_aux_len", "bsc_infonce_loss_scratch_bytes", "bsc_infonce_plan", "bsc_infonce_fwd", "bsc_infonce_loss",
     "bsc_infonce_bwd_partials", "bsc_infonce_bwd_finish", "bsc_bank_search_workspace_bytes", "bsc_bank_search", "bsc_bank_screen_parts", "bsc_bank_screen", "bsc_bank_rescore", "bsc_topk_merge", "bsc_taxonomy_eval",
     "bsc_set_timing", "bsc_last_kernel_ms", "bsc_launch_count", "bsc_last_bwd_mode",
 ]
@@ -41,6 +41,11 @@ class InfoNceDesc(ctypes.Structure):
         ("xh", c_void_p * 3), ("inv", c_void_p * 3), ("r", c_void_p), ("rep", c_void_p), ("next", c_void_p), ("rmax", c_void_p),
         ("bwd_mode", c_int32), ("world", c_int32), ("rank", c_int32), ("reserved", c_int32),
     ]
+
+
+class InfoNceExchange(ctypes.Structure):
+    _fields_ = [("stats_peers", POINTER(c_void_p)), ("stats_multicast", c_void_p), ("arrive", c_void_p),
+                ("arrive_target", ctypes.c_uint64)]
 
 
 class InfoNcePlan(ctypes.Structure):
@@ -76,19 +81,25 @@ def lib():
                                    c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
     L.bsc_taxonomy_eval.argtypes = [c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_int, POINTER(c_int32), c_int,
                                     POINTER(c_int64), c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
-    L.bsc_gather_layout.argtypes = [c_int64, c_int, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t),
-                                    POINTER(c_size_t)]
+    L.bsc_gather_layout.argtypes = [c_int64, c_int, c_int, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t),
+                                    POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)]
+    L.bsc_gather_push_labels.argtypes = [c_void_p, c_int64, c_int64, c_int64, c_int, POINTER(c_void_p), c_void_p, c_int,
+                                         c_void_p]
     L.bsc_gather_push.argtypes = [POINTER(c_void_p), c_int, POINTER(c_int64), c_void_p, c_int64, c_int64, c_int64, c_int,
-                                  POINTER(c_void_p), c_void_p, c_int, c_void_p]
+                                  POINTER(c_void_p), c_void_p, c_int, c_int, c_int, ctypes.c_uint64, c_void_p]
+    L.bsc_infonce_aux_len.argtypes = [c_int64]
+    L.bsc_infonce_aux_len.restype = c_int64
     L.bsc_infonce_stats_len.argtypes = [c_int64]
     L.bsc_infonce_stats_len.restype = c_int64
     L.bsc_infonce_plan.argtypes = [POINTER(InfoNceDesc), c_int, c_int, c_size_t, POINTER(InfoNcePlan)]
-    L.bsc_infonce_fwd.argtypes = [POINTER(InfoNceDesc), c_void_p, c_void_p, c_size_t, c_void_p]
-    L.bsc_infonce_loss.argtypes = [POINTER(InfoNceDesc), c_void_p, c_void_p, c_void_p]
+    L.bsc_infonce_fwd.argtypes = [POINTER(InfoNceDesc), c_void_p, POINTER(InfoNceExchange), c_void_p, c_size_t, c_void_p]
+    L.bsc_infonce_loss.argtypes = [POINTER(InfoNceDesc), c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
+    L.bsc_infonce_loss_scratch_bytes.argtypes = []
+    L.bsc_infonce_loss_scratch_bytes.restype = c_size_t
     L.bsc_infonce_bwd_partials.argtypes = [POINTER(InfoNceDesc), c_void_p, POINTER(c_void_p), c_void_p, c_size_t,
                                            c_void_p]
-    L.bsc_infonce_bwd_finish.argtypes = [POINTER(InfoNceDesc), POINTER(c_void_p), c_int, POINTER(c_int64), c_void_p,
-                                         POINTER(c_void_p), c_void_p, c_void_p, c_size_t, c_void_p]
+    L.bsc_infonce_bwd_finish.argtypes = [POINTER(InfoNceDesc), c_void_p, POINTER(c_void_p), c_int, POINTER(c_int64),
+                                         c_void_p, POINTER(c_void_p), c_void_p, c_void_p, c_size_t, c_void_p]
     L.bsc_bank_search_workspace_bytes.argtypes = [c_int64, c_int64, c_int, c_int, c_int, POINTER(c_size_t)]
     L.bsc_bank_search.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int64, c_int, c_void_p,
                                   c_void_p, c_void_p, c_size_t, c_void_p]

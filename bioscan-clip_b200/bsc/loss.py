@@ -48,8 +48,8 @@ class LocalComm:
     def all_gather_rows(self, t: torch.Tensor) -> torch.Tensor:
         return t
 
-    def all_reduce_sum(self, t: torch.Tensor) -> torch.Tensor:
-        return t
+    def share_stats(self, record: torch.Tensor) -> torch.Tensor:
+        return record[None]
 
     def exchange(self, nbytes: int, device):
         buf = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=device)
@@ -77,9 +77,12 @@ class TorchDistComm:
         self.dist.all_gather_into_tensor(out, t.contiguous(), group=self.group)
         return out
 
-    def all_reduce_sum(self, t: torch.Tensor) -> torch.Tensor:
-        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
-        return t
+    def share_stats(self, record: torch.Tensor) -> torch.Tensor:
+        """Every rank's statistics record, [world, len] in rank order (bsc_infonce_loss adds them in that order: the
+        result is the same on every rank and from run to run, which an all_reduce does not promise)."""
+        out = torch.empty(self.world_size * record.shape[0], dtype=record.dtype, device=record.device)
+        self.dist.all_gather_into_tensor(out, record.contiguous(), group=self.group)
+        return out.view(self.world_size, record.shape[0])
 
 
 class SymmMemComm(TorchDistComm):
@@ -100,7 +103,8 @@ class SymmMemComm(TorchDistComm):
     def __init__(self, rank: int, world_size: int, group=None, strict: bool = False):
         super().__init__(rank, world_size, group)
         self.strict = strict
-        self.gather_path = "symm_mem"  # "symm_mem+multicast" once a buffer with an NVSwitch multicast address is in use
+        self.gather_path = "symm_mem"
+        self._side = None
         self.disabled = False
         self._gather = {}     # (n_global, d, device) -> state
         self._exchange = {}   # (nbytes, device) -> state
@@ -160,9 +164,21 @@ class SymmMemComm(TorchDistComm):
 
     # -- forward gather -----------------------------------------------------------------------------
     def gather_tc16(self, feats, labels):
-        """-> (xh[3], inv[3], all_labels, token) as views of this rank's symmetric buffer, or None when the inputs do
-        not qualify (mixed dtypes, strided elements) or peer memory is unavailable: the caller takes the NCCL path."""
+        """The forward's exchange over peer memory.  Returns None when the inputs do not qualify (strided elements,
+        unsupported dtype) or peer memory is unavailable -- the caller takes the NCCL path -- else a dict:
+          xh[3], inv[3], labels   views of this rank's symmetric buffer (the gathered global batch)
+          bind(problem)           registers the problem that will read them in its backward
+          exchange                argument of CudaOps.infonce_fwd: where the statistics records go, and -- in the
+                                  overlapped mode -- the arrival counters the sweep waits on
+          records()               call after the forward sweep: barrier, then the [world, len] records of all ranks
+
+        Overlapped mode (row blocks that are whole column tiles; BSC_GATHER_OVERLAP=0 turns it off): the labels go first
+        (tiny, one barrier), then a SIDE stream prepares the rows in this rank's own buffer and lets the copy engines
+        carry them to one destination at a time, while the main stream already runs the label statistics and the
+        similarity sweep, which waits per source rank on arrival flags and starts with this rank's own columns.  Every GPU has to receive (W-1)/W of the batch (0.22 ms of NVLink ingress at
+        8 x 4096 rows); this hides it behind the sweep instead of adding it to the step."""
         import ctypes
+        import os
         import weakref
 
         from . import _lib
@@ -177,30 +193,38 @@ class SymmMemComm(TorchDistComm):
             return None
         n_local, d = f0.shape
         n_global = n_local * self.world_size
-        key = (n_global, d, f0.device)
+        dev = f0.device
+        key = (n_global, d, dev)
         st = self._gather.get(key)
+        L = _lib.lib()
         if st is None:
             offx, offi = (ctypes.c_size_t * 3)(), (ctypes.c_size_t * 3)()
-            offl, total = ctypes.c_size_t(0), ctypes.c_size_t(0)
-            _lib.check(_lib.lib().bsc_gather_layout(n_global, d, offx, offi, ctypes.byref(offl), ctypes.byref(total)))
-            made = self._symm_buffers(int(total.value), f0.device, 2)
+            offl, offs, offf, total = (ctypes.c_size_t(0) for _ in range(4))
+            _lib.check(L.bsc_gather_layout(n_global, d, self.world_size, offx, offi, ctypes.byref(offl),
+                                           ctypes.byref(offs), ctypes.byref(offf), ctypes.byref(total)))
+            made = self._symm_buffers(int(total.value), dev, 2)
             if made is None:
                 return None
             bufs, handles, peers = made
-            import os
-
-            # NVSwitch multicast address of each buffer (0 / absent when the fabric has no NVLS): one multimem.st per
-            # 16 bytes reaches every rank.  All ranks see the same capability, so the choice needs no agreement.
+            for t in bufs:
+                t[int(offf.value):].zero_()  # arrival counters start at 0 and only ever grow
+            torch.cuda.synchronize(dev)
+            self.dist.barrier(group=self.group)  # nobody pushes before every counter is zeroed
+            # NVSwitch multicast address of each buffer (0 / absent when the fabric has no NVLS): one multimem.st
+            # reaches every rank.  All ranks see the same capability, so the choice needs no agreement.
             mcast = [int(getattr(h, "multicast_ptr", 0) or 0) for h in handles]
             if os.environ.get("BSC_GATHER_MULTICAST") == "0":
                 mcast = [0 for _ in handles]
-            st = {"bufs": bufs, "handles": handles, "mcast": mcast,
+            st = {"bufs": bufs, "handles": handles, "mcast": mcast, "ptrs": peers,
                   "peers": [(ctypes.c_void_p * self.world_size)(*pp) for pp in peers],
-                  "offx": list(offx), "offi": list(offi), "offl": int(offl.value), "step": 0, "pending": [None, None]}
+                  "offx": list(offx), "offi": list(offi), "offl": int(offl.value), "offs": int(offs.value),
+                  "offf": int(offf.value), "step": 0, "pending": [None, None], "pushes": [0, 0],
+                  "stats_len": int(L.bsc_infonce_stats_len(n_global))}
             self._cache_put(self._gather, key, st)
         b = st["step"] & 1
         st["step"] += 1
-        self.gather_path = "symm_mem+multicast" if st["mcast"][b] else "symm_mem"
+        overlap = n_local % 256 == 0 and os.environ.get("BSC_GATHER_OVERLAP") != "0"
+        self.gather_path = "symm_mem" + ("+overlapped" if overlap else "") + ("+multicast" if st["mcast"][b] else "")
         # the OTHER buffer is overwritten by the peers' next forward, which they may start as soon as this rank has
         # arrived at the barrier below: a problem still waiting for its backward there moves to private memory now
         for slot in (b ^ 1, b):
@@ -213,14 +237,40 @@ class SymmMemComm(TorchDistComm):
         labels = labels.detach().to(torch.int64).contiguous()
         x = (ctypes.c_void_p * 3)(*[None if f is None else f.data_ptr() for f in feats])
         ldx = (ctypes.c_int64 * 3)(*[0 if f is None else f.stride(0) for f in feats])
-        with torch.cuda.device(f0.device):
-            _lib.check(_lib.lib().bsc_gather_push(x, _lib.dtype_code(f0.dtype), ldx, labels.data_ptr(), n_local,
-                                                  self.rank * n_local, n_global, d, st["peers"][b],
-                                                  st["mcast"][b] or None, self.world_size,
-                                                  _lib.stream_ptr(f0.device)))
-            _mark("gather_push")
-            st["handles"][b].barrier(channel=0)
-            _mark("gather_barrier")
+        handle, mc = st["handles"][b], st["mcast"][b] or None
+        exchange = {"stats_peers": [pp + st["offs"] for pp in st["ptrs"][b]],
+                    "stats_multicast": (st["mcast"][b] + st["offs"]) if st["mcast"][b] else 0}
+        side_done = None
+        with torch.cuda.device(dev):
+            main = torch.cuda.current_stream(dev)
+            if overlap:
+                _lib.check(L.bsc_gather_push_labels(labels.data_ptr(), n_local, self.rank * n_local, n_global, d,
+                                                    st["peers"][b], mc, self.world_size, main.cuda_stream))
+                handle.barrier(channel=0)
+                _mark("labels_barrier")
+                # the inputs exist, every rank is past whatever read this buffer two steps ago, and the two tiny
+                # launches above do not have to compete with the push for SM slots
+                ready = torch.cuda.Event()
+                ready.record(main)
+                if self._side is None:
+                    self._side = torch.cuda.Stream(dev)
+                st["pushes"][b] += 1
+                with torch.cuda.stream(self._side):
+                    self._side.wait_event(ready)
+                    _lib.check(L.bsc_gather_push(x, _lib.dtype_code(f0.dtype), ldx, None, n_local, self.rank * n_local,
+                                                 n_global, d, st["peers"][b], None, self.world_size, self.rank, 1,
+                                                 st["pushes"][b], self._side.cuda_stream))
+                    side_done = torch.cuda.Event()
+                    side_done.record(self._side)
+                exchange["arrive"] = st["ptrs"][b][self.rank] + st["offf"]
+                exchange["arrive_target"] = st["pushes"][b]
+            else:
+                _lib.check(L.bsc_gather_push(x, _lib.dtype_code(f0.dtype), ldx, labels.data_ptr(), n_local,
+                                             self.rank * n_local, n_global, d, st["peers"][b], mc, self.world_size,
+                                             self.rank, 0, 0, main.cuda_stream))
+                _mark("gather_push")
+                handle.barrier(channel=0)
+                _mark("gather_barrier")
         buf = st["bufs"][b]
         xh, inv = [], []
         for m, f in enumerate(feats):
@@ -235,7 +285,17 @@ class SymmMemComm(TorchDistComm):
         def bind(prob, st=st, b=b):
             st["pending"][b] = weakref.ref(prob)
 
-        return xh, inv, all_labels, bind
+        def records(st=st, b=b, handle=handle, side_done=side_done, keep=feats):
+            """After the sweep: every rank's record has been stored into every rank's area -> barrier -> read."""
+            with torch.cuda.device(dev):
+                if side_done is not None:
+                    torch.cuda.current_stream(dev).wait_event(side_done)  # long done: the sweep saw every counter
+                handle.barrier(channel=1)
+            n = st["stats_len"]
+            return st["bufs"][b][st["offs"]:st["offs"] + self.world_size * n * 4].view(torch.float32).view(
+                self.world_size, n)
+
+        return {"xh": xh, "inv": inv, "labels": all_labels, "bind": bind, "exchange": exchange, "records": records}
 
     # -- backward exchange ----------------------------------------------------------------------------
     def prepare_exchange(self, nbytes: int, device) -> bool:
@@ -302,6 +362,7 @@ def infonce_forward(ops, comm, feats: List[Optional[torch.Tensor]], labels: torc
     inv = None
     all_labels = None
     bind = None
+    fused = None
     _mark("start")
     if mode == MODE_F32:
         xh = [None if f is None else comm.all_gather_rows(ops.normalize(f.detach(), torch.float32)) for f in feats]
@@ -312,8 +373,8 @@ def infonce_forward(ops, comm, feats: List[Optional[torch.Tensor]], labels: torc
         fused = comm.gather_tc16([None if f is None else f.detach() for f in feats], labels) \
             if hasattr(comm, "gather_tc16") else None
         if fused is not None:
-            xh, inv, all_labels = fused[:3]
-            bind = fused[3] if len(fused) > 3 else None
+            xh, inv, all_labels = fused["xh"], fused["inv"], fused["labels"]
+            bind = fused.get("bind")
         else:
             xh, inv = [], []
             for f in feats:
@@ -339,19 +400,25 @@ def infonce_forward(ops, comm, feats: List[Optional[torch.Tensor]], labels: torc
             ops.plan(prob, bwd_request, peer_memory=False)
     if bind is not None and want_grad:
         bind(prob)
-    stats = ops.infonce_fwd(prob)
-    _mark("fwd_sweep")
-    stats = comm.all_reduce_sum(stats)
-    _mark("stats_all_reduce")
-    loss = ops.infonce_loss(prob, stats)
+    if fused is not None and fused.get("records") is not None:
+        # the sweep stores this rank's statistics record straight into every rank's record area (peer memory)
+        ops.infonce_fwd(prob, fused.get("exchange"))
+        _mark("fwd_sweep")
+        records = fused["records"]()
+    else:
+        record = ops.infonce_fwd(prob)
+        _mark("fwd_sweep")
+        records = comm.share_stats(record)
+    _mark("stats_exchange")
+    loss, stats, aux = ops.infonce_loss(prob, records)
     _mark("loss")
-    return loss, (prob, stats)
+    return loss, (prob, aux)
 
 
 def infonce_backward(ops, comm, saved, feats, grad_out: torch.Tensor, grad_gain: float = 1.0):
     from ._lib import BWD_SCATTER
 
-    prob, stats = saved
+    prob, aux = saved
     if grad_gain != 1.0:
         grad_out = grad_out * grad_gain
     xs = [None if f is None else f.detach() for f in feats]
@@ -360,12 +427,12 @@ def infonce_backward(ops, comm, saved, feats, grad_out: torch.Tensor, grad_gain:
     if prob.mode == MODE_TC16 and prob.bwd_mode == BWD_SCATTER:
         own, ptrs = comm.exchange(prob.exchange_bytes, dev)
     _mark("bwd_start")
-    ops.infonce_bwd_partials(prob, stats, ptrs)
+    ops.infonce_bwd_partials(prob, aux, ptrs)
     _mark("bwd_partials")
     if own is not None:
         comm.exchange_barrier(dev)  # every rank's partial sums have landed before anyone adds them up
         _mark("exchange_barrier")
-    grads = ops.infonce_bwd_finish(prob, xs, grad_out, own)
+    grads = ops.infonce_bwd_finish(prob, aux, xs, grad_out, own)
     _mark("bwd_finish")
     prob.done = True
     prob.bwd_workspace = None

@@ -190,26 +190,50 @@ class CudaOps:
     def forget_plans(self) -> None:
         self._plans.clear()
 
-    def infonce_fwd(self, p: Problem) -> torch.Tensor:
+    def infonce_fwd(self, p: Problem, exchange: dict = None) -> torch.Tensor:
+        """Forward sweep -> this rank's statistics record.  ``exchange`` (peer memory, see bsc_infonce_exchange):
+        {"stats_peers": [addresses], "stats_multicast": address or 0, "arrive": address or 0, "arrive_target": int}."""
         dev = self._device(p)
         _lib.require_device(dev)
         if p.bwd_mode is None:
             self.plan(p)
         ws = torch.empty(max(p.fwd_workspace_bytes, 256), dtype=torch.uint8, device=dev)  # lives for the forward only
         stats = torch.empty(self.stats_len(p.n_global), dtype=torch.float32, device=dev)
+        ex = None
+        if exchange:
+            ex = _lib.InfoNceExchange()
+            peers = exchange.get("stats_peers")
+            keep = (c_void_p * len(peers))(*peers) if peers else None
+            ex.stats_peers = keep
+            ex.stats_multicast = exchange.get("stats_multicast") or None
+            ex.arrive = exchange.get("arrive") or None
+            ex.arrive_target = int(exchange.get("arrive_target") or 0)
         with torch.cuda.device(dev):
-            check(lib().bsc_infonce_fwd(byref(self._desc(p)), stats.data_ptr(), ws.data_ptr(), ws.numel(),
-                                        stream_ptr(dev)))
+            check(lib().bsc_infonce_fwd(byref(self._desc(p)), stats.data_ptr(), byref(ex) if ex is not None else None,
+                                        ws.data_ptr(), ws.numel(), stream_ptr(dev)))
         return stats
 
-    def infonce_loss(self, p: Problem, stats: torch.Tensor) -> torch.Tensor:
+    def infonce_loss(self, p: Problem, records: torch.Tensor):
+        """records: [n_records, stats_len] per-rank statistics records (this rank's own as [1, stats_len] when all rows
+        are local).  Returns (loss, combined record, aux = the backward's factors)."""
         dev = self._device(p)
+        if records.dim() == 1:
+            records = records[None]
+        records = records.contiguous()
         loss = torch.empty((), dtype=torch.float32, device=dev)
+        stats = torch.empty(self.stats_len(p.n_global), dtype=torch.float32, device=dev)
+        aux = torch.empty(int(lib().bsc_infonce_aux_len(p.n_global)), dtype=torch.float32, device=dev)
+        key = ("loss_scratch", dev, torch.cuda.current_stream(dev).cuda_stream)
+        scratch = self._ws.get(key)
+        if scratch is None:  # zeroed once; every call leaves it zeroed (ticket counter + block partial sums)
+            scratch = self._ws[key] = torch.zeros(int(lib().bsc_infonce_loss_scratch_bytes()), dtype=torch.uint8,
+                                                  device=dev)
         with torch.cuda.device(dev):
-            check(lib().bsc_infonce_loss(byref(self._desc(p)), stats.data_ptr(), loss.data_ptr(), stream_ptr(dev)))
-        return loss
+            check(lib().bsc_infonce_loss(byref(self._desc(p)), records.data_ptr(), records.shape[0], stats.data_ptr(),
+                                         aux.data_ptr(), loss.data_ptr(), scratch.data_ptr(), stream_ptr(dev)))
+        return loss, stats, aux
 
-    def infonce_bwd_partials(self, p: Problem, stats: torch.Tensor, exchange_ptrs=None) -> None:
+    def infonce_bwd_partials(self, p: Problem, aux: torch.Tensor, exchange_ptrs=None) -> None:
         """Phase 1 of the backward: raw gradient sums into the (lazily allocated) backward workspace and, in the
         scatter strategy, into the owners' exchange buffers (``exchange_ptrs``: one device address per rank)."""
         dev = self._device(p)
@@ -221,10 +245,11 @@ class CudaOps:
                 raise _lib.BscError("the scatter backward needs one exchange buffer address per rank")
             ex = (c_void_p * p.world)(*exchange_ptrs)
         with torch.cuda.device(dev):
-            check(lib().bsc_infonce_bwd_partials(byref(self._desc(p)), stats.data_ptr(), ex, p.bwd_workspace.data_ptr(),
+            check(lib().bsc_infonce_bwd_partials(byref(self._desc(p)), aux.data_ptr(), ex, p.bwd_workspace.data_ptr(),
                                                  p.bwd_workspace.numel(), stream_ptr(dev)))
 
-    def infonce_bwd_finish(self, p: Problem, xs, grad_out: torch.Tensor, own_exchange: torch.Tensor = None):
+    def infonce_bwd_finish(self, p: Problem, aux: torch.Tensor, xs, grad_out: torch.Tensor,
+                           own_exchange: torch.Tensor = None):
         """Phase 2: xs = this rank's original rows per modality (None when absent; rows may be strided, elements must
         be contiguous).  Returns dense gradients of the same shapes and dtype."""
         dev = self._device(p)
@@ -238,9 +263,10 @@ class CudaOps:
         gp = (c_void_p * 3)(*[ptr(g) or None for g in grads])
         ldx = (ctypes.c_int64 * 3)(*[0 if x is None else x.stride(0) for x in xs])
         with torch.cuda.device(dev):
-            check(lib().bsc_infonce_bwd_finish(byref(self._desc(p)), xp, _lib.dtype_code(present[0].dtype), ldx,
-                                               grad_out.data_ptr(), gp, ptr(own_exchange) or None,
-                                               p.bwd_workspace.data_ptr(), p.bwd_workspace.numel(), stream_ptr(dev)))
+            check(lib().bsc_infonce_bwd_finish(byref(self._desc(p)), aux.data_ptr(), xp,
+                                               _lib.dtype_code(present[0].dtype), ldx, grad_out.data_ptr(), gp,
+                                               ptr(own_exchange) or None, p.bwd_workspace.data_ptr(),
+                                               p.bwd_workspace.numel(), stream_ptr(dev)))
         return grads
 
     # ---- retrieval ------------------------------------------------------------------------------

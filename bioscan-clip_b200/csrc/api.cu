@@ -24,22 +24,23 @@ int taxo_launch(const int64_t* indices, int64_t nq, int k, const int32_t* key_id
                 int levels, const int32_t* k_list, int nk, const int64_t* class_off, int64_t total_classes,
                 int32_t* pred_ids, uint8_t* first_hit, int64_t* micro, int32_t* pred_counts, int32_t* gt_counts,
                 cudaStream_t st);
-void gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3], size_t* off_labels, size_t* total);
+void gather_layout(int64_t n_global, int d, int world, size_t off_xh[3], size_t off_inv[3], size_t* off_labels,
+                   size_t* off_stats, size_t* off_flags, size_t* total);
+int gather_blocks_per_dest(int64_t n_local);
+int gather_labels_launch(const int64_t* labels, int64_t n_local, int64_t row0, int64_t n_global, int d,
+                         void* const* peers, void* multicast, int world, cudaStream_t st);
 int gather_push_launch(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels,
                        int64_t n_local, int64_t row0, int64_t n_global, int d, void* const* peers, void* multicast,
-                       int world, cudaStream_t st);
+                       int world, int rank, int ordered, uint64_t epoch, cudaStream_t st);
 int label_stats_launch(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax, char* ws,
                        cudaStream_t st);
-int loss_launch(const float* stats, const float* r, int64_t n, unsigned present_mask, float scale, float* loss,
-                cudaStream_t st);
-int uv_launch(const float* stats, const float* r, int64_t n, const float* rmax, const float* const* inv, int use_gs,
-              float* uv, float* gsbuf, float* invmax, cudaStream_t st);
 int rep_range_launch(const int32_t* rep, int64_t n, int tile, int2* out, cudaStream_t st);
 int combine_launch(const CombineArgs& a, int x_dtype, cudaStream_t st);
 int topk_merge_launch(const float* cs, const int64_t* ci, int parts, int64_t nq, int k, float* os, int64_t* oi,
                       cudaStream_t st);
-void tc_fwd_tiling(int64_t n_local, int64_t n_global, int n_pairs, int* n_iblk, int* n_jtile, int* jpc,
+void tc_fwd_tiling(int64_t n_local, int64_t n_global, int n_pairs, int world, int* n_iblk, int* n_jtile, int* jpc,
                    int* n_jchunk);
+bool tc_fwd_source_aligned(int64_t n_local, int64_t n_global, int world);
 
 // ---- thread-local state -----------------------------------------------------------------------
 // The error text is per thread.  Launch counter and timing slots are per process: torch runs the backward of
@@ -176,7 +177,7 @@ InfoNceFwdWs infonce_fwd_layout(const bsc_infonce_desc* p) {
   const int m = present_count(p, nullptr);
   const int n_pairs = m * (m - 1) / 2;
   if (p->mode == BSC_MODE_TC16) {
-    tc_fwd_tiling(n, N, n_pairs, &L.n_iblk, &L.n_jtile, &L.jtiles_per_chunk, &L.n_jchunk);
+    tc_fwd_tiling(n, N, n_pairs, p->world, &L.n_iblk, &L.n_jtile, &L.jtiles_per_chunk, &L.n_jchunk);
   } else {
     L.n_iblk = (int)((n + kSimtT - 1) / kSimtT);
     L.n_jtile = (int)((N + kSimtT - 1) / kSimtT);
@@ -211,13 +212,11 @@ InfoNceBwdWs infonce_bwd_layout(const bsc_infonce_desc* p) {
   L.mode = p->mode == BSC_MODE_TC16 ? p->bwd_mode : BSC_BWD_RECOMPUTE;
   const bool stored = p->mode == BSC_MODE_TC16 && (L.mode == BSC_BWD_BLOCKS || L.mode == BSC_BWD_SCATTER);
   if (p->mode == BSC_MODE_TC16)
-    tc_fwd_tiling(n, N, n_pairs, &L.n_iblk, &L.n_jtile, &L.jtiles_per_chunk, &L.n_jchunk);
+    tc_fwd_tiling(n, N, n_pairs, p->world, &L.n_iblk, &L.n_jtile, &L.jtiles_per_chunk, &L.n_jchunk);
   L.g_rows = n < 2048 ? (n > 0 ? n : 1) : 2048;
   L.kparts = 1;
   if (p->mode == BSC_MODE_TC16) L.kparts = stored ? tc_bwd_gemm_kparts(p) : tc_bwd_duo_jsplit(p);
   size_t off = 0;
-  L.uv = take(off, (size_t)6 * N * sizeof(float));
-  L.gs = take(off, 32 * sizeof(float));  // [6][2] {gs, 1/gs} per ordered pair, [12..14] max inverse norms
   L.jrange = take(off, (size_t)((N + kTcBNF - 1) / kTcBNF + 1) * 2 * sizeof(int));
   L.dxraw = take(off, (size_t)bwd_local_slots(p) * L.kparts * (n > 0 ? n : 1) * D * sizeof(float));
   if (stored) {
@@ -321,31 +320,51 @@ int bsc_rows_to_f16(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, v
   return rows_to_f16_launch(x, x_dtype, n, d, ldx, y16, inv, (cudaStream_t)stream);
 }
 
-int bsc_gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3], size_t* off_labels,
-                      size_t* total_bytes) {
-  BSC_REQUIRE(off_xh && off_inv && off_labels && total_bytes, BSC_EINVAL, "bsc_gather_layout: null pointer");
-  BSC_REQUIRE(n_global >= 0 && d >= 1, BSC_EINVAL, "bsc_gather_layout: bad shape");
-  gather_layout(n_global, d, off_xh, off_inv, off_labels, total_bytes);
+int bsc_gather_layout(int64_t n_global, int d, int world, size_t off_xh[3], size_t off_inv[3], size_t* off_labels,
+                      size_t* off_stats, size_t* off_flags, size_t* total_bytes) {
+  BSC_REQUIRE(off_xh && off_inv && off_labels && off_stats && off_flags && total_bytes, BSC_EINVAL,
+              "bsc_gather_layout: null pointer");
+  BSC_REQUIRE(n_global >= 0 && d >= 1 && world >= 1 && world <= kMaxPeers, BSC_EINVAL, "bsc_gather_layout: bad shape");
+  gather_layout(n_global, d, world, off_xh, off_inv, off_labels, off_stats, off_flags, total_bytes);
   return BSC_OK;
+}
+
+static int check_peers(void* const* peer_buffers, int world, const char* who) {
+  BSC_REQUIRE(peer_buffers != nullptr, BSC_EINVAL, "%s: null peer list", who);
+  BSC_REQUIRE(world >= 1 && world <= kMaxPeers, BSC_EUNSUPPORTED, "%s: world=%d (1..%d supported)", who, world, kMaxPeers);
+  for (int r = 0; r < world; ++r) BSC_REQUIRE(peer_buffers[r], BSC_EINVAL, "%s: peer %d is null", who, r);
+  return BSC_OK;
+}
+
+int bsc_gather_push_labels(const int64_t* labels, int64_t n_local, int64_t row0, int64_t n_global, int d,
+                           void* const* peer_buffers, void* multicast_buffer, int world, void* stream) {
+  int rc = check_peers(peer_buffers, world, "bsc_gather_push_labels");
+  if (rc) return rc;
+  BSC_REQUIRE(labels || n_local == 0, BSC_EINVAL, "bsc_gather_push_labels: null labels");
+  BSC_REQUIRE(n_local >= 0 && row0 >= 0 && row0 + n_local <= n_global && d >= 1, BSC_EINVAL,
+              "bsc_gather_push_labels: bad shape");
+  return gather_labels_launch(labels, n_local, row0, n_global, d, peer_buffers, multicast_buffer, world,
+                              (cudaStream_t)stream);
 }
 
 int bsc_gather_push(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels, int64_t n_local,
                     int64_t row0, int64_t n_global, int d, void* const* peer_buffers, void* multicast_buffer, int world,
-                    void* stream) {
-  BSC_REQUIRE(x && ldx && peer_buffers, BSC_EINVAL, "bsc_gather_push: null pointer");
-  BSC_REQUIRE(world >= 1 && world <= kMaxPeers, BSC_EUNSUPPORTED, "bsc_gather_push: world=%d (1..%d supported)", world,
-              kMaxPeers);
+                    int rank, int ordered, uint64_t epoch, void* stream) {
+  BSC_REQUIRE(x && ldx, BSC_EINVAL, "bsc_gather_push: null pointer");
+  int rc = check_peers(peer_buffers, world, "bsc_gather_push");
+  if (rc) return rc;
+  BSC_REQUIRE(rank >= 0 && rank < world, BSC_EINVAL, "bsc_gather_push: rank %d of %d", rank, world);
   BSC_REQUIRE(d >= 8 && d % 8 == 0, BSC_EUNSUPPORTED, "bsc_gather_push: d %% 8 != 0 (got %d)", d);
   BSC_REQUIRE(n_local >= 0 && row0 >= 0 && row0 + n_local <= n_global, BSC_EINVAL,
               "bsc_gather_push: rows [%lld, %lld) outside the global batch of %lld", (long long)row0,
               (long long)(row0 + n_local), (long long)n_global);
   for (int m = 0; m < 3; ++m)
     BSC_REQUIRE(!x[m] || ldx[m] >= d, BSC_EINVAL, "bsc_gather_push: ldx[%d] < d", m);
-  for (int r = 0; r < world; ++r) BSC_REQUIRE(peer_buffers[r], BSC_EINVAL, "bsc_gather_push: peer %d is null", r);
   BSC_REQUIRE(multicast_buffer == nullptr || ((uintptr_t)multicast_buffer & 15) == 0, BSC_EINVAL,
               "bsc_gather_push: multicast address is not 16-byte aligned");
+  BSC_REQUIRE(!ordered || epoch > 0, BSC_EINVAL, "bsc_gather_push: ordered pushes are numbered from 1");
   return gather_push_launch(x, x_dtype, ldx, labels, n_local, row0, n_global, d, peer_buffers, multicast_buffer, world,
-                            (cudaStream_t)stream);
+                            rank, ordered ? 1 : 0, epoch, (cudaStream_t)stream);
 }
 
 int bsc_taxonomy_eval(const int64_t* indices, int64_t nq, int k, const int32_t* key_ids, int64_t nb,
@@ -375,7 +394,8 @@ int bsc_label_stats(const int64_t* labels, int64_t n, float* r, int32_t* rep, in
   return label_stats_launch(labels, n, r, rep, next, rmax, (char*)workspace, (cudaStream_t)stream);
 }
 
-int64_t bsc_infonce_stats_len(int64_t n_global) { return 6 * n_global + kStatsExtra; }
+int64_t bsc_infonce_stats_len(int64_t n_global) { return stats_record_len(n_global); }
+int64_t bsc_infonce_aux_len(int64_t n_global) { return 6 * n_global + 32; }
 
 // Is `mode` a strategy this problem can run?  (message in g_err when not)
 static int bwd_mode_ok(const bsc_infonce_desc* p, int mode, int peer_memory, const char* who) {
@@ -435,51 +455,75 @@ int bsc_infonce_plan(const bsc_infonce_desc* p_in, int requested, int peer_memor
   return BSC_OK;
 }
 
-int bsc_infonce_fwd(const bsc_infonce_desc* p, float* stats, void* workspace, size_t workspace_bytes, void* stream) {
+int bsc_infonce_fwd(const bsc_infonce_desc* p, float* stats, const bsc_infonce_exchange* ex, void* workspace,
+                    size_t workspace_bytes, void* stream) {
   int rc = check_desc(p, "bsc_infonce_fwd");
   if (rc) return rc;
   BSC_REQUIRE(stats && workspace, BSC_EINVAL, "bsc_infonce_fwd: null pointer");
   const InfoNceFwdWs L = infonce_fwd_layout(p);
   BSC_REQUIRE(workspace_bytes >= L.total, BSC_EWORKSPACE, "bsc_infonce_fwd: workspace %zu < %zu", workspace_bytes,
               L.total);
+  if (ex != nullptr) {
+    BSC_REQUIRE(p->mode == BSC_MODE_TC16 || (!ex->arrive && !ex->stats_peers && !ex->stats_multicast), BSC_EUNSUPPORTED,
+                "bsc_infonce_fwd: the peer-memory exchange is implemented for BSC_MODE_TC16");
+    if (ex->stats_peers)
+      for (int r = 0; r < p->world; ++r)
+        BSC_REQUIRE(ex->stats_peers[r] != nullptr, BSC_EINVAL, "bsc_infonce_fwd: stats area of rank %d is null", r);
+  }
   cudaStream_t st = (cudaStream_t)stream;
   char* ws = (char*)workspace;
   const int64_t N = p->n_global;
   BSC_CUDA(cudaMemsetAsync(stats, 0, (size_t)bsc_infonce_stats_len(N) * sizeof(float), st));
   if (p->n_local == 0) return BSC_OK;
   if (p->mode == BSC_MODE_F32) return simt_fwd_stats(p, L, ws, stats, st);
-  return tc_fwd_stats(p, L, ws, stats, st);
+  return tc_fwd_stats(p, L, ws, stats, ex, st);
 }
 
-int bsc_infonce_loss(const bsc_infonce_desc* p, const float* stats, float* loss, void* stream) {
+size_t bsc_infonce_loss_scratch_bytes(void) { return stats_finish_scratch_bytes(); }
+
+int bsc_infonce_loss(const bsc_infonce_desc* p, const float* records, int n_records, float* stats, float* aux,
+                     float* loss, void* scratch, void* stream) {
   int rc = check_desc(p, "bsc_infonce_loss");
   if (rc) return rc;
-  BSC_REQUIRE(stats && loss, BSC_EINVAL, "bsc_infonce_loss: null pointer");
+  BSC_REQUIRE(records && stats && aux && loss && scratch, BSC_EINVAL, "bsc_infonce_loss: null pointer");
+  BSC_REQUIRE(((uintptr_t)scratch & 15) == 0, BSC_EINVAL, "bsc_infonce_loss: scratch must be 16-byte aligned");
+  BSC_REQUIRE(n_records >= 1 && n_records <= kMaxPeers, BSC_EINVAL, "bsc_infonce_loss: %d records", n_records);
   unsigned mask = 0;
   present_count(p, &mask);
-  return loss_launch(stats, p->r, p->n_global, mask, p->logit_scale, loss, (cudaStream_t)stream);
+  StatsFinishArgs a{};
+  a.slots = records;
+  a.world = n_records;
+  a.n = p->n_global;
+  a.record_len = stats_record_len(p->n_global);
+  a.r = p->r;
+  a.rmax = p->rmax;
+  for (int m = 0; m < 3; ++m) a.inv[m] = p->mode == BSC_MODE_TC16 ? p->inv[m] : nullptr;
+  a.present_mask = mask;
+  a.use_gs = p->mode == BSC_MODE_TC16 ? 1 : 0;
+  a.stats = stats;
+  a.uv = aux;
+  a.gsbuf = aux + 6 * p->n_global;
+  a.loss = loss;
+  a.scratch = (char*)scratch;
+  return stats_finish_launch(a, (cudaStream_t)stream);
 }
 
-int bsc_infonce_bwd_partials(const bsc_infonce_desc* p, const float* stats, void* const* exchange, void* workspace,
+int bsc_infonce_bwd_partials(const bsc_infonce_desc* p, const float* aux, void* const* exchange, void* workspace,
                              size_t workspace_bytes, void* stream) {
   int rc = check_desc(p, "bsc_infonce_bwd_partials");
   if (rc) return rc;
   rc = bwd_mode_ok(p, p->mode == BSC_MODE_F32 ? BSC_BWD_RECOMPUTE : p->bwd_mode, 1, "bsc_infonce_bwd_partials");
   if (rc) return rc;
-  BSC_REQUIRE(stats && workspace, BSC_EINVAL, "bsc_infonce_bwd_partials: null pointer");
+  BSC_REQUIRE(aux && workspace, BSC_EINVAL, "bsc_infonce_bwd_partials: null pointer");
   const InfoNceBwdWs L = infonce_bwd_layout(p);
   BSC_REQUIRE(workspace_bytes >= L.total, BSC_EWORKSPACE, "bsc_infonce_bwd_partials: workspace %zu < %zu",
               workspace_bytes, L.total);
   cudaStream_t st = (cudaStream_t)stream;
   char* ws = (char*)workspace;
-  const int64_t N = p->n_global;
   if (p->n_local == 0) return BSC_OK;
-  rc = uv_launch(stats, p->r, N, p->rmax, p->inv, p->mode == BSC_MODE_TC16, (float*)(ws + L.uv), (float*)(ws + L.gs),
-                 (float*)(ws + L.gs) + 12, st);
-  if (rc) return rc;
-  if (p->mode == BSC_MODE_F32) return simt_bwd_raw(p, L, ws, st);
+  if (p->mode == BSC_MODE_F32) return simt_bwd_raw(p, L, ws, aux, st);
   g_bwd_mode.store(L.mode);
-  if (L.mode == BSC_BWD_RECOMPUTE) return tc_bwd_duo(p, L, ws, st);
+  if (L.mode == BSC_BWD_RECOMPUTE) return tc_bwd_duo(p, L, ws, aux, st);
   ScatterDst dst{};
   dst.world = p->world;
   dst.rank = p->rank;
@@ -492,17 +536,17 @@ int bsc_infonce_bwd_partials(const bsc_infonce_desc* p, const float* stats, void
     }
   }
   int np = 0, pa[6], pb[6];
-  rc = tc_bwd_weights(p, L, ws, &np, pa, pb, st);
+  rc = tc_bwd_weights(p, L, ws, aux, &np, pa, pb, st);
   if (rc) return rc;
-  return tc_bwd_gemms(p, L, ws, np, pa, pb, dst, st);
+  return tc_bwd_gemms(p, L, ws, aux, np, pa, pb, dst, st);
 }
 
-int bsc_infonce_bwd_finish(const bsc_infonce_desc* p, const void* const* x, int x_dtype, const int64_t* ldx,
+int bsc_infonce_bwd_finish(const bsc_infonce_desc* p, const float* aux, const void* const* x, int x_dtype, const int64_t* ldx,
                            const float* grad_out, void* const* grad, const void* own_exchange, void* workspace,
                            size_t workspace_bytes, void* stream) {
   int rc = check_desc(p, "bsc_infonce_bwd_finish");
   if (rc) return rc;
-  BSC_REQUIRE(x && ldx && grad && grad_out && workspace, BSC_EINVAL, "bsc_infonce_bwd_finish: null pointer");
+  BSC_REQUIRE(aux && x && ldx && grad && grad_out && workspace, BSC_EINVAL, "bsc_infonce_bwd_finish: null pointer");
   const InfoNceBwdWs L = infonce_bwd_layout(p);
   BSC_REQUIRE(workspace_bytes >= L.total, BSC_EWORKSPACE, "bsc_infonce_bwd_finish: workspace %zu < %zu",
               workspace_bytes, L.total);
@@ -555,7 +599,7 @@ int bsc_infonce_bwd_finish(const bsc_infonce_desc* p, const void* const* x, int 
       ++slot;
     }
   }
-  ca.gsbuf = (const float*)(ws + L.gs);
+  ca.gsbuf = aux + 6 * p->n_global;
   ca.grad_out = grad_out;
   ca.n_local = p->n_local;
   ca.n_global = p->n_global;

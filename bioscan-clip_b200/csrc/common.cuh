@@ -45,7 +45,12 @@ __host__ __device__ inline int pair_id(int a, int b) { return a * 2 + (b > a ? b
 
 constexpr int kMaxPeers = 16;  // ranks of one NVLink domain addressed by the fused gather / gradient scatter
 constexpr int kStatsExtra = 4;  // scalars after the 6*N sum-exp rows; [0] = sum over unordered pairs and local rows of
-                                // sum_j T_ij (s*S_ij - s)
+                                // sum_j T_ij (s*S_ij - s) (float copy, informational in a per-rank record)
+constexpr int kPosParts = 64;   // the same sum as kPosParts double partial sums (fixed assignment of rows to parts):
+                                // what the loss is computed from, added over parts and ranks in a fixed order
+// One statistics record = 6 N floats | kStatsExtra floats | kPosParts doubles
+__host__ __device__ inline int64_t stats_record_len(int64_t n) { return (6 * n + kStatsExtra + 2 * kPosParts + 3) / 4 * 4; }
+__host__ __device__ inline int64_t stats_pos_offset(int64_t n) { return (6 * n + kStatsExtra + 1) / 2 * 2; }  // float index, 8-byte aligned
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -63,8 +68,6 @@ struct InfoNceFwdWs {
 };
 
 struct InfoNceBwdWs {
-  size_t uv;        // float [6][N]          r_i / sumexp
-  size_t gs;        // float [32]            {gs, 1/gs} per ordered pair, max inverse norms
   size_t jrange;    // int2  [n_jtile]
   size_t dxraw;     // float [3 K-major jobs... see tc_bwd3.cu][kparts][n_local][D]   local partial gradients
   size_t xunit;     // half  [3][n_local][D]  unit rows of the LOCAL rows (B operand of the MN-major jobs)
@@ -129,24 +132,26 @@ struct CombineArgs {
 
 // ---- sub-launchers implemented in the .cu files ---------------------------------------------------
 int simt_fwd_stats(const bsc_infonce_desc* p, const InfoNceFwdWs& L, char* ws, float* stats, cudaStream_t st);
-int simt_bwd_raw(const bsc_infonce_desc* p, const InfoNceBwdWs& L, char* ws, cudaStream_t st);
-int tc_fwd_stats(const bsc_infonce_desc* p, const InfoNceFwdWs& L, char* ws, float* stats, cudaStream_t st);
+// aux = uv[6][N] (r_i / sumexp per ordered pair) followed by gsbuf[32], written by bsc_infonce_loss
+int simt_bwd_raw(const bsc_infonce_desc* p, const InfoNceBwdWs& L, char* ws, const float* aux, cudaStream_t st);
+int tc_fwd_stats(const bsc_infonce_desc* p, const InfoNceFwdWs& L, char* ws, float* stats,
+                 const bsc_infonce_exchange* ex, cudaStream_t st);
 // recomputing CTA-pair sweep (BSC_BWD_RECOMPUTE), d in {256, 512, 768}
 bool tc_bwd_duo_covers(const bsc_infonce_desc* p);
-int tc_bwd_duo(const bsc_infonce_desc* p, const InfoNceBwdWs& L, char* ws, cudaStream_t st);
+int tc_bwd_duo(const bsc_infonce_desc* p, const InfoNceBwdWs& L, char* ws, const float* aux, cudaStream_t st);
 int tc_bwd_duo_jsplit(const bsc_infonce_desc* p);
 // stored-weight backward (BSC_BWD_BLOCKS / BSC_BWD_SCATTER): weight images, then the gradient GEMMs
 size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* p);
 void tc_bwd_matrix_dims(const bsc_infonce_desc* d, int* n_iblk_pad, int* n_j64);
 int tc_bwd_gemm_kparts(const bsc_infonce_desc* d);
-int tc_bwd_weights(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, int* n_pairs, int* pairs_a,
-                   int* pairs_b, cudaStream_t st);
+int tc_bwd_weights(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, const float* aux, int* n_pairs,
+                   int* pairs_a, int* pairs_b, cudaStream_t st);
 struct ScatterDst {
   float* peer[kMaxPeers];  // exchange buffer of every rank (index = rank), [world src][3][n_local][d] float
   int world, rank;
 };
-int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, int n_pairs, const int* pairs_a,
-                 const int* pairs_b, const ScatterDst& dst, cudaStream_t st);
+int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, const float* aux, int n_pairs,
+                 const int* pairs_a, const int* pairs_b, const ScatterDst& dst, cudaStream_t st);
 int rows_unit_f16_launch3(const void* const x16[3], const float* const inv[3], int64_t row0, int64_t n, int d,
                           void* const out[3], cudaStream_t st);
 struct ReduceJob {
@@ -158,8 +163,37 @@ struct ReduceJob {
 struct ReduceJobs {
   ReduceJob job[6];
   int count;
+  // positive-pair term: pos_out[b] = scale * sum over the elements (p, i) dealt to part b, b < kPosParts (double)
+  const float* pos_part;
+  int pos_nparts;
+  int64_t pos_stride, pos_n;
+  float pos_scale;
+  double* pos_out;
+  // copies of everything written above into the records of other ranks: an address inside [local_base, local_base + len)
+  // is mirrored at the same offset from peer_base[r] (r < n_peers) or, when mc_base is set, by ONE multicast store
+  const float* local_base;
+  float* peer_base[kMaxPeers];
+  float* mc_base;
+  int n_peers;
 };
 int reduce_parts_batch_launch(const ReduceJobs& jobs, cudaStream_t st);
+struct StatsFinishArgs {
+  const float* slots;   // [world][record_len] per-rank records
+  int world;
+  int64_t n, record_len;
+  const float* r;       // [n]
+  const float* rmax;    // [1]
+  const float* inv[3];  // TC16: inverse row norms (null in fp32 mode)
+  unsigned present_mask;
+  int use_gs;
+  float* stats;         // [record_len] combined record
+  float* uv;            // [6][n]
+  float* gsbuf;         // [32]
+  float* loss;          // [1]
+  char* scratch;        // stats_finish_scratch_bytes(), zeroed once by the caller, left zero by every call
+};
+int stats_finish_launch(const StatsFinishArgs& a, cudaStream_t st);
+size_t stats_finish_scratch_bytes();
 
 int simt_bank_search(const float* q, int64_t nq, const float* bank, int64_t nb, int d, int k, int64_t base_id,
                      float* out_s, int64_t* out_i, char* ws, size_t ws_bytes, cudaStream_t st);

@@ -190,17 +190,21 @@ int rows_unit_f16_launch3(const void* const x16[3], const float* const inv[3], i
 struct GatherPushArgs {
   const void* x[3];   // local rows per modality (null = absent)
   int64_t ldx[3];
-  const int64_t* labels;  // local labels
+  const int64_t* labels;  // local labels (null: they travelled with bsc_gather_push_labels)
   char* peer[kMaxPeers];  // base of every rank's symmetric buffer (index = rank)
   char* mc;               // NVSwitch multicast address of the same buffer (one store reaches every rank), or null
-  int world;
+  int world, rank;
+  int ordered;            // 1: own buffer only (the DMA ring forwards the rows), 0: every rank's buffer
+  int blocks_per_dest;
   int64_t n_local, n_global, row0;
   int d;
-  size_t off_xh[3], off_inv[3], off_labels;
+  size_t off_xh[3], off_inv[3], off_labels, off_flags;
 };
 
-// One store to the multicast address is replicated by the NVSwitch into every rank's buffer: the gather then costs each
-// rank its OWN rows of NVLink egress (19 MB at 8 x 4096 x 768 x 3) instead of one copy per peer (132 MB, 0.25 ms).
+// One store to the multicast address is replicated by the NVSwitch into every rank's buffer.  It does not shorten the
+// gather of the rows themselves -- every GPU still has to RECEIVE (W-1)/W of the global batch, 132 MB at 8 x 4096 x 768 x
+// 3 fp16, 0.22 ms of NVLink ingress however the bytes are sent (measured: the same time as one store per peer) -- but it
+// makes the small exchanges (labels, statistics records) one store instead of W.
 __device__ __forceinline__ void mc_store16(void* addr, uint4 v) {
   asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "r"(v.x), "r"(v.y),
                "r"(v.z), "r"(v.w)
@@ -213,9 +217,13 @@ __device__ __forceinline__ void mc_store4(void* addr, uint32_t v) {
   asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
 }
 
+// One warp per (modality, local row).  self_only = 0: the row goes into EVERY rank's buffer (or once through the
+// multicast address); the caller runs a cross-rank barrier before anyone reads.  self_only = 1: the row goes into this
+// rank's own buffer only -- the first step of the DMA ring below.
 template <typename TI>
 __global__ void __launch_bounds__(256) gather_push_kernel(const GatherPushArgs a) {
   const int lane = threadIdx.x & 31;
+  const int dest = a.ordered ? a.rank : -1;
   const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int m = (int)(w / a.n_local);
   const int64_t l = w % a.n_local;
@@ -251,14 +259,16 @@ __global__ void __launch_bounds__(256) gather_push_kernel(const GatherPushArgs a
     inv_row = n2 > 0.f ? (true_nrm >= 1e-12f ? 1.0f / n2 : exp2f((float)-k) * 1e12f) : 0.f;
   }
   const int64_t g = a.row0 + l;  // global row
-  // 8 fp16 per lane per pass (d % 8 == 0 is checked by the launcher): one 16-byte store per peer
+  // 8 fp16 per lane per pass (d % 8 == 0 is checked by the launcher): one 16-byte store per destination
   for (int c0 = lane * 8; c0 < d; c0 += 256) {
     __half hv[8];
 #pragma unroll
     for (int t = 0; t < 8; ++t) hv[t] = __float2half_rn(to_f32<TI>(xr[c0 + t]) * scale);
     const uint4 pk = *reinterpret_cast<const uint4*>(hv);
     const size_t off = a.off_xh[m] + ((size_t)g * d + c0) * 2;
-    if (a.mc != nullptr) {
+    if (dest >= 0) {
+      *reinterpret_cast<uint4*>(a.peer[dest] + off) = pk;
+    } else if (a.mc != nullptr) {
       mc_store16(a.mc + off, pk);
     } else {
       for (int r = 0; r < a.world; ++r) *reinterpret_cast<uint4*>(a.peer[r] + off) = pk;
@@ -268,7 +278,10 @@ __global__ void __launch_bounds__(256) gather_push_kernel(const GatherPushArgs a
   int first = 0;
   while (first < 3 && a.x[first] == nullptr) ++first;
   const bool with_label = m == first && a.labels != nullptr;
-  if (a.mc != nullptr) {
+  if (dest >= 0) {
+    if (lane == 0) *reinterpret_cast<float*>(a.peer[dest] + a.off_inv[m] + (size_t)g * 4) = inv_row;
+    if (lane == 1 && with_label) *reinterpret_cast<int64_t*>(a.peer[dest] + a.off_labels + (size_t)g * 8) = a.labels[l];
+  } else if (a.mc != nullptr) {
     if (lane == 0) mc_store4(a.mc + a.off_inv[m] + (size_t)g * 4, __float_as_uint(inv_row));
     if (lane == 1 && with_label) {
       const int64_t lab = a.labels[l];
@@ -281,7 +294,44 @@ __global__ void __launch_bounds__(256) gather_push_kernel(const GatherPushArgs a
   }
 }
 
-void gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3], size_t* off_labels, size_t* total) {
+// Ring step of the fused all-gather: after the copy engines have moved this rank's fp16 rows into destination `dst`
+// (cudaMemcpyAsync on the same stream), one small block forwards the inverse norms (3 x n_local floats) and then
+// publishes the arrival: arrive[source] = epoch in the destination's buffer, release at system scope.  The rows travel
+// by DMA because SM stores that back up behind a saturated NVLink port stall EVERY memory operation of their SM --
+// measured on 2 GPUs: label statistics 46 -> 209 us, similarity sweep +4 % while a store-based push ran beside them.
+__global__ void __launch_bounds__(256) gather_signal_kernel(const char* own, char* dst, size_t off_inv0, size_t off_inv1,
+                                                            size_t off_inv2, unsigned present_mask, int64_t row0,
+                                                            int64_t n_local, unsigned long long* flag,
+                                                            unsigned long long epoch) {
+  const size_t off[3] = {off_inv0, off_inv1, off_inv2};
+  if (dst != own) {
+    for (int m = 0; m < 3; ++m) {
+      if (!((present_mask >> m) & 1)) continue;
+      const float* s = reinterpret_cast<const float*>(own + off[m]) + row0;
+      float* t = reinterpret_cast<float*>(dst + off[m]) + row0;
+      for (int64_t i = threadIdx.x; i < n_local; i += blockDim.x) t[i] = s[i];
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"(epoch) : "memory");
+}
+
+// labels only: tiny, every rank needs ALL labels before its label statistics can start
+__global__ void __launch_bounds__(256) gather_labels_kernel(const int64_t* __restrict__ labels, int64_t n_local,
+                                                            int64_t row0, GatherPushArgs a) {
+  const int64_t l = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= n_local) return;
+  const int64_t lab = labels[l];
+  const size_t off = a.off_labels + (size_t)(row0 + l) * 8;
+  if (a.mc != nullptr) {
+    mc_store8(a.mc + off, make_uint2((uint32_t)lab, (uint32_t)((uint64_t)lab >> 32)));
+  } else {
+    for (int r = 0; r < a.world; ++r) *reinterpret_cast<int64_t*>(a.peer[r] + off) = lab;
+  }
+}
+
+void gather_layout(int64_t n_global, int d, int world, size_t off_xh[3], size_t off_inv[3], size_t* off_labels,
+                   size_t* off_stats, size_t* off_flags, size_t* total) {
   const size_t ax = align_up((size_t)n_global * d * 2, 256);
   const size_t ai = align_up((size_t)n_global * 4, 256);
   for (int m = 0; m < 3; ++m) {
@@ -289,29 +339,53 @@ void gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3],
     off_inv[m] = 3 * ax + (size_t)m * ai;
   }
   *off_labels = 3 * ax + 3 * ai;
-  *total = *off_labels + align_up((size_t)n_global * 8, 256);
+  *off_stats = *off_labels + align_up((size_t)n_global * 8, 256);
+  *off_flags = *off_stats + align_up((size_t)(world > 0 ? world : 1) * stats_record_len(n_global) * sizeof(float), 256);
+  *total = *off_flags + align_up((size_t)kMaxPeers * 8, 256);
 }
 
-int gather_push_launch(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels,
-                       int64_t n_local, int64_t row0, int64_t n_global, int d, void* const* peers, void* multicast,
-                       int world, cudaStream_t st) {
-  if (n_local == 0) return BSC_OK;
-  GatherPushArgs a{};
-  for (int m = 0; m < 3; ++m) {
-    a.x[m] = x[m];
-    a.ldx[m] = ldx[m];
-  }
-  a.labels = labels;
+int gather_blocks_per_dest(int64_t n_local) { return (int)((3 * n_local + 7) / 8); }
+
+static void gather_fill(GatherPushArgs& a, int64_t n_local, int64_t row0, int64_t n_global, int d, void* const* peers,
+                        void* multicast, int world, int rank) {
   for (int r = 0; r < world; ++r) a.peer[r] = (char*)peers[r];
   a.mc = (char*)multicast;
   a.world = world;
+  a.rank = rank;
   a.n_local = n_local;
   a.n_global = n_global;
   a.row0 = row0;
   a.d = d;
-  size_t total;
-  gather_layout(n_global, d, a.off_xh, a.off_inv, &a.off_labels, &total);
-  dim3 block(256), grid((unsigned)((3 * n_local + 7) / 8));
+  size_t off_stats, total;
+  gather_layout(n_global, d, world, a.off_xh, a.off_inv, &a.off_labels, &off_stats, &a.off_flags, &total);
+}
+
+int gather_labels_launch(const int64_t* labels, int64_t n_local, int64_t row0, int64_t n_global, int d,
+                         void* const* peers, void* multicast, int world, cudaStream_t st) {
+  if (n_local == 0) return BSC_OK;
+  GatherPushArgs a{};
+  gather_fill(a, n_local, row0, n_global, d, peers, multicast, world, 0);
+  gather_labels_kernel<<<(unsigned)((n_local + 255) / 256), 256, 0, st>>>(labels, n_local, row0, a);
+  BSC_LAUNCH_CHECK("gather_labels_kernel");
+  return BSC_OK;
+}
+
+int gather_push_launch(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels,
+                       int64_t n_local, int64_t row0, int64_t n_global, int d, void* const* peers, void* multicast,
+                       int world, int rank, int ordered, uint64_t epoch, cudaStream_t st) {
+  if (n_local == 0) return BSC_OK;
+  GatherPushArgs a{};
+  unsigned mask = 0;
+  for (int m = 0; m < 3; ++m) {
+    a.x[m] = x[m];
+    a.ldx[m] = ldx[m];
+    if (x[m]) mask |= 1u << m;
+  }
+  a.labels = labels;
+  gather_fill(a, n_local, row0, n_global, d, peers, multicast, world, rank);
+  a.ordered = ordered;
+  a.blocks_per_dest = gather_blocks_per_dest(n_local);
+  dim3 block(256), grid((unsigned)a.blocks_per_dest);
   switch (x_dtype) {
     case BSC_F32: gather_push_kernel<float><<<grid, block, 0, st>>>(a); break;
     case BSC_BF16: gather_push_kernel<__nv_bfloat16><<<grid, block, 0, st>>>(a); break;
@@ -319,6 +393,25 @@ int gather_push_launch(const void* const x[3], int x_dtype, const int64_t ldx[3]
     default: set_error("bsc_gather_push: unknown x_dtype %d", x_dtype); return BSC_EINVAL;
   }
   BSC_LAUNCH_CHECK("gather_push_kernel");
+  if (!ordered) return BSC_OK;
+  // the DMA ring: own rows first (already in place: publish), then rank+1, rank+2, ... -- every receiver hears from one
+  // sender at a time, in the order rank, rank-1, rank-2, ... in which its sweep will want the sources
+  char* own = a.peer[rank];
+  const size_t row_bytes = (size_t)d * 2;
+  for (int k = 0; k < world; ++k) {
+    const int dest = (rank + k) % world;
+    char* dst = a.peer[dest];
+    if (k > 0)
+      for (int m = 0; m < 3; ++m)
+        if (x[m]) {
+          const size_t off = a.off_xh[m] + (size_t)row0 * row_bytes;
+          BSC_CUDA(cudaMemcpyAsync(dst + off, own + off, (size_t)n_local * row_bytes, cudaMemcpyDefault, st));
+        }
+    unsigned long long* flag = reinterpret_cast<unsigned long long*>(dst + a.off_flags) + rank;
+    gather_signal_kernel<<<1, 256, 0, st>>>(own, dst, a.off_inv[0], a.off_inv[1], a.off_inv[2], mask, row0, n_local,
+                                            flag, (unsigned long long)epoch);
+    BSC_LAUNCH_CHECK("gather_signal_kernel");
+  }
   return BSC_OK;
 }
 
@@ -603,7 +696,7 @@ __device__ __forceinline__ double cluster_sum_to_cta0(double acc, double* sh /*[
 // out[0] = scale * sum_p sum_{i<n} part[p*stride + i]  (double accumulation, fixed order).
 __global__ void __cluster_dims__(kRedCtas, 1, 1) __launch_bounds__(1024)
     sum_rows_kernel(const float* __restrict__ part, int nparts, int64_t part_stride, int64_t n, float scale,
-                    float* __restrict__ out) {
+                    float* __restrict__ out, double* __restrict__ out64) {
   __shared__ double sh[1024];
   __shared__ double slots[kRedCtas];
   double acc = 0.0;
@@ -616,12 +709,15 @@ __global__ void __cluster_dims__(kRedCtas, 1, 1) __launch_bounds__(1024)
     if (i < n) acc += (double)part[p * part_stride + i];
   }
   const double total = cluster_sum_to_cta0(acc, sh, slots);
-  if (blockIdx.x == 0 && threadIdx.x == 0) out[0] = (float)((double)scale * total);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    out[0] = (float)((double)scale * total);
+    if (out64 != nullptr) out64[0] = (double)scale * total;
+  }
 }
 
 int sum_rows_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float scale, float* out,
-                    cudaStream_t st) {
-  sum_rows_kernel<<<kRedCtas, 1024, 0, st>>>(part, nparts, part_stride, n, scale, out);
+                    double* out64, cudaStream_t st) {
+  sum_rows_kernel<<<kRedCtas, 1024, 0, st>>>(part, nparts, part_stride, n, scale, out, out64);
   BSC_LAUNCH_CHECK("sum_rows_kernel");
   return BSC_OK;
 }
@@ -641,20 +737,61 @@ __global__ void __launch_bounds__(256) reduce_parts_kernel(const float* __restri
 }
 
 // Up to 6 reductions in one launch (blockIdx.y = job): the forward's row and column sum-exp vectors of every pair.
+// blockIdx.y == jobs.count: the positive-pair term as kPosParts double partial sums (rows are dealt to the parts
+// round-robin in chunks of 256, so the result does not depend on the grid).  Every value is also stored into the
+// records of the other ranks (statistics exchange over NVLink peer memory: one multicast store or one store per peer).
+__device__ __forceinline__ void mirror_f32(const ReduceJobs& jobs, float* local_addr, float v) {
+  const int64_t off = local_addr - jobs.local_base;
+  if (jobs.mc_base != nullptr) {
+    asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(jobs.mc_base + off), "f"(v) : "memory");
+  } else {
+    for (int r = 0; r < jobs.n_peers; ++r) jobs.peer_base[r][off] = v;
+  }
+}
+
 __global__ void __launch_bounds__(256) reduce_parts_batch_kernel(const ReduceJobs jobs) {
-  const ReduceJob j = jobs.job[blockIdx.y];
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= j.n) return;
-  float acc = 0.f;
-  for (int p = 0; p < j.nparts; ++p) acc += j.part[p * j.part_stride + i];
-  j.out[i] = acc;
+  if ((int)blockIdx.y < jobs.count) {
+    const ReduceJob j = jobs.job[blockIdx.y];
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= j.n) return;
+    float acc = 0.f;
+    for (int p = 0; p < j.nparts; ++p) acc += j.part[p * j.part_stride + i];
+    j.out[i] = acc;
+    if (jobs.local_base != nullptr) mirror_f32(jobs, j.out + i, acc);
+    return;
+  }
+  if ((int)blockIdx.x >= kPosParts || jobs.pos_out == nullptr) return;
+  __shared__ double sh[256];
+  double acc = 0.0;
+  const int64_t nchunk = (jobs.pos_n + 255) / 256;
+  const int64_t items = (int64_t)jobs.pos_nparts * nchunk;
+  for (int64_t q = blockIdx.x; q < items; q += kPosParts) {
+    const int64_t p = q / nchunk, i = (q - p * nchunk) * 256 + threadIdx.x;
+    if (i < jobs.pos_n) acc += (double)jobs.pos_part[p * jobs.pos_stride + i];
+  }
+  sh[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s2 = 128; s2 > 0; s2 >>= 1) {
+    if ((int)threadIdx.x < s2) sh[threadIdx.x] += sh[threadIdx.x + s2];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double v = (double)jobs.pos_scale * sh[0];
+    jobs.pos_out[blockIdx.x] = v;
+    if (jobs.local_base != nullptr) {
+      float* lo = reinterpret_cast<float*>(jobs.pos_out + blockIdx.x);
+      const long long bits = __double_as_longlong(v);
+      mirror_f32(jobs, lo, __int_as_float((int)(bits & 0xffffffffll)));
+      mirror_f32(jobs, lo + 1, __int_as_float((int)(bits >> 32)));
+    }
+  }
 }
 
 int reduce_parts_batch_launch(const ReduceJobs& jobs, cudaStream_t st) {
-  int64_t nmax = 0;
+  int64_t nmax = jobs.pos_out ? (int64_t)kPosParts * 256 : 0;
   for (int q = 0; q < jobs.count; ++q) nmax = jobs.job[q].n > nmax ? jobs.job[q].n : nmax;
-  if (jobs.count == 0 || nmax == 0) return BSC_OK;
-  dim3 grid((unsigned)((nmax + 255) / 256), (unsigned)jobs.count);
+  if ((jobs.count == 0 && !jobs.pos_out) || nmax == 0) return BSC_OK;
+  dim3 grid((unsigned)((nmax + 255) / 256), (unsigned)(jobs.count + (jobs.pos_out ? 1 : 0)));
   reduce_parts_batch_kernel<<<grid, 256, 0, st>>>(jobs);
   BSC_LAUNCH_CHECK("reduce_parts_batch_kernel");
   return BSC_OK;
@@ -668,112 +805,124 @@ int reduce_parts_launch(const float* part, int nparts, int64_t part_stride, int6
 }
 
 // ---------------------------------------------------------------------------------------------
-// Loss scalar (loss_func.py:54).  With a_ij = s*S_ij - s and sumexp_i = sum_j exp(a_ij):
-//   L = c * [ sum over ordered pairs sum_i r_i log(sumexp_i)  -  2 * sum over unordered pairs sum_ij T_ij a_ij ],
-// c = 1 / (N * M(M-1))  (r_i*s cancels against the s inside a_ij).  One cluster, double accumulation, fixed order.
+// Statistics finish: one launch turns the per-rank records into everything the rest of the step needs --
+//   stats[p][i] = sum over ranks (in rank order) of the records' sum-exp rows          (the all-reduce, deterministic)
+//   uv[p][i]    = r_i / stats[p][i]                                                     (backward weights)
+//   loss        = c [ sum over ordered pairs sum_i r_i log(stats[p][i]) - 2 pos ],  c = 1 / (N M(M-1))   (loss_func.py:54;
+//                 with a_ij = s*S_ij - s the r_i*s terms cancel against the s inside a_ij); pos = sum over ranks and
+//                 parts of the double partial sums, fixed order
+//   gsbuf       = {gs, 1/gs} per ordered pair (x, y): the power of two that keeps the fp16 weight tile
+//                 |gs (e (u + v) - 2 T) / |y_j|| <= 4 gs rmax max_j(1/|y_j|) in range; max inverse norms at [12..14]
+// Double accumulation, every thread a fixed subset, block partials added in block order by whichever block finishes
+// last (ticket counter): independent of scheduling.
 // ---------------------------------------------------------------------------------------------
-__global__ void __cluster_dims__(kRedCtas, 1, 1) __launch_bounds__(1024)
-    loss_kernel(const float* __restrict__ stats, const float* __restrict__ r, int64_t n, unsigned present_mask,
-                float scale, float* __restrict__ loss) {
-  __shared__ double sh[1024];
-  __shared__ double slots[kRedCtas];
+constexpr int kFinishBlocks = 256;  // grid cap = partial sums kept in the scratch
+
+// scratch layout (caller-zeroed once, left zero): u32 ticket | pad | double part[kFinishBlocks] | float vmax[3][kFinishBlocks]
+__global__ void __launch_bounds__(256) stats_finish_kernel(const StatsFinishArgs a) {
+  __shared__ double sh[256];
+  __shared__ float mx[3][8];
+  __shared__ bool last;
+  unsigned* ticket = reinterpret_cast<unsigned*>(a.scratch);
+  double* part = reinterpret_cast<double*>(a.scratch + 16);
+  float* vpart = reinterpret_cast<float*>(a.scratch + 16 + kFinishBlocks * 8);
+  const int64_t n = a.n;
   double acc = 0.0;
-  int m = 0;
-  for (int a = 0; a < 3; ++a) m += (present_mask >> a) & 1;
-  for (int a = 0; a < 3; ++a) {
-    if (!((present_mask >> a) & 1)) continue;
-    for (int b = 0; b < 3; ++b) {
-      if (b == a || !((present_mask >> b) & 1)) continue;
-      const float* se = stats + (int64_t)pair_id(a, b) * n;
-#pragma unroll 4  // the loads of 4 iterations in flight; the double additions keep their order
-      for (int64_t i = (int64_t)blockIdx.x * 1024 + threadIdx.x; i < n; i += kRedCtas * 1024)
-        acc += (double)r[i] * (double)logf(se[i]);
+  float vmax[3] = {0.f, 0.f, 0.f};
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
+    const float ri = a.r[i];
+    float se[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int w = 0; w < a.world; ++w) {  // rank order: the sum is the same on every rank and in every run
+      const float* rec = a.slots + (int64_t)w * a.record_len + i;
+#pragma unroll
+      for (int p = 0; p < 6; ++p) se[p] += rec[(int64_t)p * n];
     }
-  }
-  const double total = cluster_sum_to_cta0(acc, sh, slots);
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    const double pos = (double)stats[6 * n];
-    const double c = 1.0 / ((double)n * m * (m - 1));
-    loss[0] = (float)(c * (total - 2.0 * pos));
-    (void)scale;
-  }
-}
-
-int loss_launch(const float* stats, const float* r, int64_t n, unsigned present_mask, float scale, float* loss,
-                cudaStream_t st) {
-  loss_kernel<<<kRedCtas, 1024, 0, st>>>(stats, r, n, present_mask, scale, loss);
-  BSC_LAUNCH_CHECK("loss_kernel");
-  return BSC_OK;
-}
-
-// Largest inverse row norm of every present modality (one cluster of 8 CTAs per modality; max is order-free): bounds
-// the fp16 range of the gradient-weight tile in TC16 mode, where 1/||y_j|| is folded into the weights.
-__global__ void __cluster_dims__(kRedCtas, 1, 1) __launch_bounds__(256)
-    invmax_kernel(const float* __restrict__ i0, const float* __restrict__ i1, const float* __restrict__ i2, int64_t n,
-                  float* __restrict__ out) {
-  namespace cg = cooperative_groups;
-  cg::cluster_group cluster = cg::this_cluster();
-  __shared__ float sh[8];
-  __shared__ float slots[kRedCtas];
-  const float* src = blockIdx.y == 0 ? i0 : (blockIdx.y == 1 ? i1 : i2);
-  float m = 0.f;
-  if (src != nullptr) {
-#pragma unroll 4
-    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += kRedCtas * 256) m = fmaxf(m, src[i]);
+#pragma unroll
+    for (int p = 0; p < 6; ++p) {
+      a.stats[(int64_t)p * n + i] = se[p];
+      a.uv[(int64_t)p * n + i] = se[p] > 0.f ? ri / se[p] : 0.f;
+      const int x = p >> 1, y = (p & 1) + ((p & 1) >= x ? 1 : 0);  // pair_id(x, y) = p
+      if (((a.present_mask >> x) & 1) && ((a.present_mask >> y) & 1)) acc += (double)ri * (double)logf(se[p]);
+    }
+#pragma unroll
+    for (int m = 0; m < 3; ++m)
+      if (a.use_gs && a.inv[m] != nullptr) vmax[m] = fmaxf(vmax[m], a.inv[m][i]);
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = m;
+  for (int m = 0; m < 3; ++m) {
+    float v = vmax[m];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if ((threadIdx.x & 31) == 0) mx[m][threadIdx.x >> 5] = v;
+  }
+  sh[threadIdx.x] = acc;
   __syncthreads();
+  for (int s2 = 128; s2 > 0; s2 >>= 1) {
+    if ((int)threadIdx.x < s2) sh[threadIdx.x] += sh[threadIdx.x + s2];
+    __syncthreads();
+  }
   if (threadIdx.x == 0) {
-    for (int w = 1; w < 8; ++w) m = fmaxf(m, sh[w]);
-    cluster.map_shared_rank(slots, 0)[cluster.block_rank()] = m;
+    part[blockIdx.x] = sh[0];
+    for (int m = 0; m < 3; ++m) {
+      float v = mx[m][0];
+      for (int w = 1; w < 8; ++w) v = fmaxf(v, mx[m][w]);
+      vpart[m * kFinishBlocks + blockIdx.x] = v;
+    }
+    __threadfence();
+    last = atomicAdd(ticket, 1u) == gridDim.x - 1;  // whoever comes last adds the partial sums in BLOCK order
   }
-  cluster.sync();
-  if (cluster.block_rank() == 0 && threadIdx.x == 0) {
-    float t = slots[0];
-    for (int c = 1; c < kRedCtas; ++c) t = fmaxf(t, slots[c]);
-    out[blockIdx.y] = src != nullptr ? t : 1.0f;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  // positive-pair term: world x kPosParts double partial sums, loaded by as many threads, added by one in a fixed order
+  __shared__ double pp[kMaxPeers * kPosParts];
+  const int64_t pos_off = stats_pos_offset(n);
+  const int nparts = a.world * kPosParts;
+  for (int t = threadIdx.x; t < nparts; t += 256)
+    pp[t] = reinterpret_cast<const double*>(a.slots + (int64_t)(t / kPosParts) * a.record_len + pos_off)[t % kPosParts];
+  double* cp = reinterpret_cast<double*>(a.stats + pos_off);
+  if (threadIdx.x >= 1 && threadIdx.x < kPosParts) cp[threadIdx.x] = 0.0;
+  sh[threadIdx.x] = threadIdx.x < gridDim.x ? __ldcg(part + threadIdx.x) : 0.0;
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  *ticket = 0u;  // ready for the next call on this stream
+  double total = 0.0;
+  for (int c = 0; c < (int)gridDim.x; ++c) total += sh[c];
+  double pos = 0.0;
+  for (int t = 0; t < nparts; ++t) pos += pp[t];
+  int m = 0;
+  for (int q = 0; q < 3; ++q) m += (a.present_mask >> q) & 1;
+  const double c = 1.0 / ((double)n * m * (m - 1));
+  a.loss[0] = (float)(c * (total - 2.0 * pos));
+  a.stats[6 * n] = (float)pos;
+  for (int q = 1; q < kStatsExtra; ++q) a.stats[6 * n + q] = 0.f;
+  cp[0] = pos;
+  float invmax[3];
+  for (int q = 0; q < 3; ++q) {
+    float t = 0.f;
+    for (int cc = 0; cc < (int)gridDim.x; ++cc) t = fmaxf(t, __ldcg(vpart + q * kFinishBlocks + cc));
+    invmax[q] = (a.use_gs && a.inv[q] != nullptr) ? t : 1.0f;
+    a.gsbuf[12 + q] = invmax[q];
   }
+  const float rm = fmaxf(a.rmax[0], 1.0f);
+  for (int x = 0; x < 3; ++x)
+    for (int y = 0; y < 3; ++y) {
+      if (x == y) continue;
+      float gs = 1.0f;
+      if (a.use_gs) gs = exp2f(floorf(log2f(8192.0f / (rm * fmaxf(invmax[y], 1e-30f)))));
+      a.gsbuf[2 * pair_id(x, y)] = gs;
+      a.gsbuf[2 * pair_id(x, y) + 1] = 1.0f / gs;
+    }
 }
 
-// uv[pid][i] = r_i / sumexp_pid[i];  gsbuf[pid] = {gs, 1/gs} with gs the power of two that keeps the weight tile
-// of the ordered pair (x, y), |gs * (e*(u+v) - 2T) / ||y_j||| <= 4 * gs * rmax * max_j(1/||y_j||), inside fp16.
-__global__ void __launch_bounds__(256) uv_kernel(const float* __restrict__ stats, const float* __restrict__ r,
-                                                 int64_t n, const float* __restrict__ rmax,
-                                                 const float* __restrict__ invmax, int use_gs,
-                                                 float* __restrict__ uv, float* __restrict__ gsbuf) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0) {
-    for (int x = 0; x < 3; ++x)
-      for (int y = 0; y < 3; ++y) {
-        if (x == y) continue;
-        float gs = 1.0f;
-        if (use_gs) gs = exp2f(floorf(log2f(8192.0f / (fmaxf(rmax[0], 1.0f) * fmaxf(invmax[y], 1e-30f)))));
-        gsbuf[2 * pair_id(x, y)] = gs;
-        gsbuf[2 * pair_id(x, y) + 1] = 1.0f / gs;
-      }
-    // weights kept without an operand scale (weight-matrix backward): |gs (e (u + v) - 2 T)| <= 4 gs rmax <= 32768
-    const float gw = use_gs ? exp2f(floorf(log2f(8192.0f / fmaxf(rmax[0], 1.0f)))) : 1.0f;
-    gsbuf[16] = gw;
-    gsbuf[17] = 1.0f / gw;
-  }
-  if (i >= n) return;
-  const float ri = r[i];
-#pragma unroll
-  for (int p = 0; p < 6; ++p) {
-    const float se = stats[(int64_t)p * n + i];
-    uv[(int64_t)p * n + i] = se > 0.f ? ri / se : 0.f;
-  }
-}
+size_t stats_finish_scratch_bytes() { return 16 + (size_t)kFinishBlocks * 8 + 3 * (size_t)kFinishBlocks * 4; }
 
-int uv_launch(const float* stats, const float* r, int64_t n, const float* rmax, const float* const* inv, int use_gs,
-              float* uv, float* gsbuf, float* invmax, cudaStream_t st) {
-  invmax_kernel<<<dim3(kRedCtas, 3), 256, 0, st>>>(use_gs ? inv[0] : nullptr, use_gs ? inv[1] : nullptr, use_gs ? inv[2] : nullptr, n,
-                                   invmax);
-  BSC_LAUNCH_CHECK("invmax_kernel");
-  uv_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(stats, r, n, rmax, invmax, use_gs, uv, gsbuf);
-  BSC_LAUNCH_CHECK("uv_kernel");
+int stats_finish_launch(const StatsFinishArgs& a, cudaStream_t st) {
+  int64_t blocks = (a.n + 255) / 256;
+  if (blocks > kFinishBlocks) blocks = kFinishBlocks;
+  if (blocks < 1) blocks = 1;
+  stats_finish_kernel<<<(unsigned)blocks, 256, 0, st>>>(a);
+  BSC_LAUNCH_CHECK("stats_finish_kernel");
   return BSC_OK;
 }
 

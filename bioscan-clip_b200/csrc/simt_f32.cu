@@ -8,7 +8,7 @@ namespace bsc {
 
 int reduce_parts_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float* out, cudaStream_t st);
 int sum_rows_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float scale, float* out,
-                    cudaStream_t st);
+                    double* out64, cudaStream_t st);
 
 namespace {
 
@@ -305,12 +305,14 @@ int simt_fwd_stats(const bsc_infonce_desc* p, const InfoNceFwdWs& L, char* ws, f
       if (rc) return rc;
       ++npairs_done;
     }
-  return sum_rows_launch((float*)(ws + L.rowpart), npairs_done, L.n_local_pad, p->n_local, 1.0f, stats + 6 * N, st);
+  // the record's positive term: float copy at [6N], the value the loss is computed from as part 0 of the double parts
+  return sum_rows_launch((float*)(ws + L.rowpart), npairs_done, L.n_local_pad, p->n_local, 1.0f, stats + 6 * N,
+                         reinterpret_cast<double*>(stats + stats_pos_offset(N)), st);
 }
 
-int simt_bwd_raw(const bsc_infonce_desc* p, const InfoNceBwdWs& L, char* ws, cudaStream_t st) {
+int simt_bwd_raw(const bsc_infonce_desc* p, const InfoNceBwdWs& L, char* ws, const float* aux, cudaStream_t st) {
   const int64_t N = p->n_global;
-  const float* uv = (const float*)(ws + L.uv);
+  const float* uv = aux;
   float* g = (float*)(ws + L.gscratch);
   for (int x = 0; x < 3; ++x) {
     if (!p->xh[x]) continue;

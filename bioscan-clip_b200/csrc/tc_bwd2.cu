@@ -473,7 +473,7 @@ int tc_bwd_duo_jsplit(const bsc_infonce_desc* d) {
   return best;
 }
 
-int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, cudaStream_t st) {
+int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, const float* aux, cudaStream_t st) {
   BSC_REQUIRE(tc_bwd_duo_covers(d), BSC_EUNSUPPORTED, "the recomputing sweep covers d in {256, 512, 768} (got %d)", d->d);
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
   DuoParams p{};
@@ -521,9 +521,9 @@ int tc_bwd_duo(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, cudaS
   const float log2e = 1.4426950408889634f;
   p.k1 = d->logit_scale * log2e;
   p.k2 = d->logit_scale * log2e;
-  p.uv = (const float*)(ws + L.uv);
+  p.uv = aux;
   p.rep = d->rep;
-  p.gsbuf = (const float*)(ws + L.gs);
+  p.gsbuf = aux + 6 * d->n_global;
   p.dxraw = (float*)(ws + L.dxraw);
   if (p.num_items == 0 || p.n_jtile == 0) return BSC_OK;
 

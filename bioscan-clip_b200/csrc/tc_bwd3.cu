@@ -39,6 +39,7 @@ constexpr int TMEM_COLS = 512;
 constexpr int MAX_STAGES = 6;
 constexpr int MAX_JOBS = 6;
 constexpr int MAX_SCHED = 6144;           // schedule entries carried in the kernel parameters (24 KB)
+constexpr int MAX_CLUSTERS = 96;          // CTA pairs of the grid (74 on a B200)
 constexpr int STG_BYTES = 2048;           // per epilogue warp: 32 rows x 16 floats staged for coalesced scatter stores
 // WIDE = 0: 256 d columns per item, one accumulator (N = 256), TMEM double-buffered over items, 6 x 32 KB stages.
 // WIDE = 1: 384 d columns per item, two accumulators (N = 256 and N = 128) fed by the SAME A tile -- d = 768 is covered
@@ -70,13 +71,14 @@ struct RevParams {
   int job_fnum[MAX_JOBS], job_fden[MAX_JOBS];  // epilogue row factor gsbuf[fnum] * gsbuf[fden] ...
   const float* job_finv[MAX_JOBS];             // ... / finv[row] when not null
   int img_r, img_c;
-  int num_items, d;
+  int num_items, d, n_clusters;
   // scatter destinations: exchange buffer of rank q = float [world][n_xslots][n_local][d]
   float* peer[kMaxPeers];
   int world, rank, n_xslots;
   int64_t n_local;
   const float* gsbuf;
-  uint32_t sched[MAX_SCHED];  // item -> job (3 bits) | d chunk (3) | K part (8) | 256-row block (18)
+  int sched_off[MAX_CLUSTERS + 1];  // cluster c runs sched[sched_off[c]] .. sched[sched_off[c + 1] - 1], in this order
+  uint32_t sched[MAX_SCHED];        // item -> job (3 bits) | d chunk (3) | K part (8) | 256-row block (18)
 };
 
 struct __align__(8) RevTail {
@@ -94,9 +96,9 @@ __host__ __device__ inline uint32_t pack_item(int job, int c, int part, int mb) 
   return (uint32_t)job | ((uint32_t)c << 3) | ((uint32_t)part << 6) | ((uint32_t)mb << 14);
 }
 
-__device__ __forceinline__ void rev_item(const RevParams& p, int item, int& job, int& mb, int& part, int& c, int& kb_lo,
+__device__ __forceinline__ void rev_item(const RevParams& p, int idx, int& job, int& mb, int& part, int& c, int& kb_lo,
                                          int& kb_hi) {
-  const uint32_t w = p.sched[item];
+  const uint32_t w = p.sched[idx];
   job = (int)(w & 7u);
   c = (int)((w >> 3) & 7u);
   part = (int)((w >> 6) & 255u);
@@ -120,8 +122,8 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t crank = ptx::cluster_ctarank();
-  const int item0 = (int)ptx::cluster_id_x();
-  const int item_step = (int)ptx::n_clusters_x();
+  const int item0 = p.sched_off[ptx::cluster_id_x()];      // this cluster's slice of the host-built schedule
+  const int item_end = p.sched_off[ptx::cluster_id_x() + 1];
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -153,7 +155,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
     if (ptx::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int item = item0; item < p.num_items; item += item_step) {
+      for (int item = item0; item < item_end; ++item) {
         int job, mb, part, c, kb_lo, kb_hi;
         rev_item(p, item, job, mb, part, c, kb_lo, kb_hi);
         const CUtensorMap* mu = &p.tmap_in[job];
@@ -200,7 +202,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
       int stage = 0;
       uint32_t phase = 0;
       uint32_t count = 0;
-      for (int item = item0; item < p.num_items; item += item_step, ++count) {
+      for (int item = item0; item < item_end; ++item, ++count) {
         int job, mb, part, c, kb_lo, kb_hi;
         rev_item(p, item, job, mb, part, c, kb_lo, kb_hi);
         const bool mn = p.job_mn[job] != 0;
@@ -244,7 +246,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
     const uint32_t empty_l0 = ptx::mapa(ptx::smem_u32(&tail->tmem_empty[0]), 0);
     uint8_t* stg = stg_base + (warp - 4) * STG_BYTES;
     uint32_t count = 0;
-    for (int item = item0; item < p.num_items; item += item_step, ++count) {
+    for (int item = item0; item < item_end; ++item, ++count) {
       int job, mb, part, c, kb_lo, kb_hi;
       rev_item(p, item, job, mb, part, c, kb_lo, kb_hi);
       const uint32_t buf = NBUF == 2 ? (count & 1u) : 0u;
@@ -336,8 +338,7 @@ static int rev_launch(RevParams& p, bool wide, cudaStream_t st) {
   if (p.num_items == 0) return BSC_OK;
   BSC_SET_SMEM_ONCE(tc_bwd_rev_kernel<0>, Cfg<0>::SMEM);
   BSC_SET_SMEM_ONCE(tc_bwd_rev_kernel<1>, Cfg<1>::SMEM);
-  int clusters = device_sm_count() / 2;
-  if (clusters > p.num_items) clusters = p.num_items;
+  const int clusters = p.n_clusters;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)(2 * clusters));
   cfg.blockDim = dim3(384);
@@ -378,7 +379,19 @@ int tc_bwd_gemm_kparts(const bsc_infonce_desc* d) {
   int m = 0;
   for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
   const int64_t nk = (d->n_global + 63) / 64;
-  if (d->bwd_mode == BSC_BWD_SCATTER && d->world > 1) return (int)(d->world < nk ? d->world : nk);
+  // SCATTER over W > 1 ranks: the MN-major items run n_local / 64 K blocks, a K-major item N / 64; the schedule
+  // balances unequal items (longest first), so the K-major jobs are only split enough to give every cluster a few
+  // long items -- each extra part is one more [n_local][d] fp32 slab written here and read again by combine
+  if (d->bwd_mode == BSC_BWD_SCATTER && d->world > 1) {
+    const int64_t pairs = (int64_t)m * (m - 1) / 2;
+    const int64_t n_mb = (d->n_local + 255) / 256;
+    const int64_t nchunk = rev_wide(d) ? d->d / 384 : (d->d + 255) / 256;
+    const int64_t items0 = pairs * n_mb * nchunk;
+    const int clusters = device_sm_count() / 2;
+    int s = 1;
+    while (items0 * s < 2 * clusters && s < d->world && 2 * s <= nk) s *= 2;
+    return s;
+  }
   const int64_t jobs = (int64_t)m * (m - 1);  // 2 per unordered pair (SCATTER, one GPU) = 1 per ordered pair (BLOCKS)
   const int64_t n_mb = (d->n_local + 255) / 256;
   const int64_t nchunk = rev_wide(d) ? d->d / 384 : (d->d + 255) / 256;
@@ -402,8 +415,8 @@ int tc_bwd_gemm_kparts(const bsc_infonce_desc* d) {
 
 // Gradient GEMMs from the images gimg[(pair * n_iblk_pad + iblk) * n_j64 + j64] = G[128 i][64 j] that tc_bwd_weights wrote
 // for the pairs (pairs_a[q], pairs_b[q]): ordered pairs in BSC_BWD_BLOCKS, unordered (a < b) in BSC_BWD_SCATTER.
-int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, int n_pairs, const int* pairs_a,
-                 const int* pairs_b, const ScatterDst& dst, cudaStream_t st) {
+int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, const float* aux, int n_pairs,
+                 const int* pairs_a, const int* pairs_b, const ScatterDst& dst, cudaStream_t st) {
   const bool scatter = L.mode == BSC_BWD_SCATTER;
   const int64_t N = d->n_global, n = d->n_local;
   int n_iblk_pad, n_j64;
@@ -422,7 +435,7 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, int
   p.img_r = n_iblk_pad;
   p.img_c = n_j64;
   p.d = d->d;
-  p.gsbuf = (const float*)(ws + L.gs);
+  p.gsbuf = aux + 6 * d->n_global;
   p.world = dst.world;
   p.rank = dst.rank;
   p.n_xslots = n_pairs;
@@ -486,41 +499,99 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, int
   BSC_REQUIRE(L.kparts >= 1 && L.kparts <= nk_all && L.kparts <= 255, BSC_EUNSUPPORTED,
               "tc_bwd_gemms: K split %d of %d blocks", L.kparts, nk_all);
 
-  // ---- schedule: two lists (scattered items, local items), each ordered (row block, K part, job, d chunk) so that the
-  // d chunks of one A tile run on neighbouring clusters (they share it through L2); rounds of `clusters` items alternate
-  // between the lists.  A rank starts its scattered list at the row blocks of the next rank.
-  std::vector<uint32_t> lists[2];
-  for (int kind = 0; kind < 2; ++kind) {  // 0 = scattered (MN-major), 1 = local (K-major)
-    int nmb = 0, kp = 1;
-    for (int z = 0; z < job; ++z)
-      if ((p.job_out[z] == nullptr) == (kind == 0)) {
-        nmb = job_nmb[z];
-        kp = p.job_kparts[z];
-      }
-    const int rot = (kind == 0 && dst.world > 1) ? (int)(((int64_t)(dst.rank + 1) % dst.world) * nmb / dst.world) : 0;
-    for (int mbi = 0; mbi < nmb; ++mbi)
-      for (int part = 0; part < kp; ++part)
-        for (int z = 0; z < job; ++z) {
-          if ((p.job_out[z] == nullptr) != (kind == 0)) continue;
-          for (int c = 0; c < nchunk; ++c) lists[kind].push_back(pack_item(z, c, part, (mbi + rot) % nmb));
-        }
+  // ---- schedule.  Items differ in length (K blocks), so they are dealt to the clusters by longest-processing-time
+  // first: sorted by length (stable: the d chunks of one A tile stay adjacent and land on neighbouring clusters, where
+  // they share the tile through L2), each item goes to the least-loaded cluster.  Inside a cluster the local and the
+  // scattered items are then interleaved, and neighbouring cluster pairs start with opposite kinds, so that at any time
+  // about half of the SMs are in a scattered item: all of them at once would push ~29 MB at the NVLink ports in one
+  // burst.  A rank starts its scattered list at the row blocks of the next rank (no two ranks target the same peer).
+  struct Item {
+    uint32_t code;
+    int cost, kind;
+  };
+  // the schedule depends on the shape only: built once per shape and thread, copied on the later calls
+  struct SchedKey {
+    int64_t n, N;
+    int d, pairs, mode, world, rank, kparts, sms;
+    bool operator==(const SchedKey& o) const {
+      return n == o.n && N == o.N && d == o.d && pairs == o.pairs && mode == o.mode && world == o.world &&
+             rank == o.rank && kparts == o.kparts && sms == o.sms;
+    }
+  };
+  struct SchedCache {
+    SchedKey key{};
+    bool valid = false;
+    int num_items = 0, n_clusters = 0;
+    int off[MAX_CLUSTERS + 1];
+    std::vector<uint32_t> sched;
+  };
+  static thread_local SchedCache cache;
+  const SchedKey key{n, N, d->d, n_pairs, L.mode, dst.world, dst.rank, L.kparts, device_sm_count()};
+  if (cache.valid && cache.key == key) {
+    memcpy(p.sched_off, cache.off, sizeof(cache.off));
+    memcpy(p.sched, cache.sched.data(), cache.sched.size() * sizeof(uint32_t));
+    p.num_items = cache.num_items;
+    p.n_clusters = cache.n_clusters;
+    return rev_launch(p, wide, st);
   }
-  const size_t total = lists[0].size() + lists[1].size();
+  std::vector<Item> items;
+  for (int kind = 0; kind < 2; ++kind) {  // 0 = scattered (MN-major), 1 = local (K-major)
+    for (int z = 0; z < job; ++z) {
+      if ((p.job_out[z] == nullptr) != (kind == 0)) continue;
+      const int nmb = job_nmb[z], kp = p.job_kparts[z];
+      const int rot = (kind == 0 && dst.world > 1) ? (int)(((int64_t)(dst.rank + 1) % dst.world) * nmb / dst.world) : 0;
+      for (int mbi = 0; mbi < nmb; ++mbi)
+        for (int part = 0; part < kp; ++part) {
+          const int nkb = (int)((int64_t)(part + 1) * p.job_nk[z] / kp - (int64_t)part * p.job_nk[z] / kp);
+          for (int c = 0; c < nchunk; ++c)
+            items.push_back(Item{pack_item(z, c, part, (mbi + rot) % nmb), nkb + 6 /* fill + drain */, kind});
+        }
+    }
+  }
+  const size_t total = items.size();
   BSC_REQUIRE(total <= (size_t)MAX_SCHED, BSC_EUNSUPPORTED,
               "tc_bwd_gemms: %zu work items exceed the schedule capacity %d (batch too large for the stored-weight "
               "backward)", total, MAX_SCHED);
+  int clusters = device_sm_count() / 2;
+  if (clusters > MAX_CLUSTERS) clusters = MAX_CLUSTERS;
+  if ((size_t)clusters > total) clusters = (int)total;
+  if (clusters < 1) clusters = 1;
   {
-    // item w runs on cluster w % C in its round w / C: neighbouring cluster PAIRS (the two d chunks of one A tile) take
-    // opposite kinds and every cluster alternates between the kinds, so that at any time half of the SMs are in a
-    // scattered item -- all of them at once would push 29 MB at the NVLink ports in one burst at the end of a round
-    const size_t C = (size_t)(device_sm_count() / 2);
-    size_t pos[2] = {0, 0};
-    for (size_t w = 0; w < total; ++w) {
-      int kind = (int)(((w / C) + ((w % C) / (size_t)nchunk)) & 1u);
-      if (pos[kind] >= lists[kind].size()) kind ^= 1;
-      p.sched[w] = lists[kind][pos[kind]++];
+    std::stable_sort(items.begin(), items.end(), [](const Item& x, const Item& y) { return x.cost > y.cost; });
+    std::vector<std::vector<Item>> per(clusters);
+    std::vector<long long> load(clusters, 0);
+    for (const Item& it : items) {
+      int best = 0;
+      for (int cl = 1; cl < clusters; ++cl)
+        if (load[cl] < load[best]) best = cl;
+      per[best].push_back(it);
+      load[best] += it.cost;
     }
+    int w = 0;
+    for (int cl = 0; cl < clusters; ++cl) {
+      p.sched_off[cl] = w;
+      std::vector<Item> lst[2];
+      for (const Item& it : per[cl]) lst[it.kind].push_back(it);
+      // proportional interleave of the two kinds, the starting kind alternating between neighbouring cluster pairs
+      const int first = (cl >> 1) & 1;
+      size_t pos[2] = {0, 0};
+      const size_t n0 = lst[first].size(), n1 = lst[first ^ 1].size();
+      for (size_t t = 0; t < n0 + n1; ++t) {
+        // take from `first` while its share of the emitted items is not ahead of its share of the total
+        const bool take_first = pos[1] >= n1 || (pos[0] < n0 && pos[0] * (n0 + n1) <= t * n0);
+        const int kind = take_first ? first : first ^ 1;
+        p.sched[w++] = lst[kind][pos[take_first ? 0 : 1]++].code;
+      }
+    }
+    for (int cl = clusters; cl <= MAX_CLUSTERS; ++cl) p.sched_off[cl] = w;
   }
+  p.n_clusters = clusters;
+  cache.key = key;
+  cache.num_items = (int)total;
+  cache.n_clusters = clusters;
+  memcpy(cache.off, p.sched_off, sizeof(cache.off));
+  cache.sched.assign(p.sched, p.sched + total);
+  cache.valid = true;
   p.num_items = (int)total;
   return rev_launch(p, wide, st);
 }

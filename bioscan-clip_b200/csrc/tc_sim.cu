@@ -15,7 +15,7 @@ namespace bsc {
 int reduce_parts_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float* out, cudaStream_t st);
 int rep_range_launch(const int32_t* rep, int64_t n, int tile, int2* out, cudaStream_t st);
 int sum_rows_launch(const float* part, int nparts, int64_t part_stride, int64_t n, float scale, float* out,
-                    cudaStream_t st);
+                    double* out64, cudaStream_t st);
 int topk_merge_launch(const float* cs, const int64_t* ci, int parts, int64_t nq, int k, float* os, int64_t* oi,
                       cudaStream_t st);
 
@@ -69,6 +69,14 @@ struct SimParams {
   const float* gsbuf;  // [16] = gs of the stored weights
   uint8_t* gimg;       // [pair][n_iblk_pad][n_j64][16 KB]
   int n_iblk_pad, n_j64;
+  // Fused all-gather (EPI_STATS, several ranks): the operand rows of source rank s (rows [s * src_rows, (s+1) * src_rows)
+  // of every matrix, their inverse norms) are complete once arrive[s] >= arrive_target; null = complete on entry.
+  // Items are then ordered (arrival position of the column chunk, pair, row block): the sweep starts on the rank's own
+  // columns while the peers' rows are still in flight (gather_push_kernel, ordered mode).
+  const unsigned long long* arrive;
+  unsigned long long arrive_target;
+  int src_rows, my_rank, world;
+  int chunk_major, cps;  // cps = column chunks per source rank
   // The weights carry 1 / |b_j| and gs of the ordered pair (a, b): the K-major GEMM's B operand is then the scaled fp16
   // rows themselves (exact for bf16 inputs), the MN-major GEMM undoes the column factor per output row (tc_bwd3.cu).
 #ifdef BSC_EXPERIMENTS
@@ -94,8 +102,37 @@ static_assert(STAGES2 * STAGE2_BYTES == STAGES * STAGE_BYTES, "both ring shapes 
 __device__ __forceinline__ void decode_item(const SimParams& p, int item, int& pair, int& jchunk, int& iblk) {
   iblk = item % p.n_iblk_items;
   const int rest = item / p.n_iblk_items;
-  jchunk = rest % p.n_jchunk;
-  pair = rest / p.n_jchunk;
+  if (p.chunk_major) {
+    pair = rest % p.n_pairs;
+    const int pos = rest / p.n_pairs;  // arrival position: this rank's own columns first, then rank - 1, rank - 2, ...
+    const int src = (p.my_rank - pos / p.cps + p.world) % p.world;
+    jchunk = src * p.cps + pos % p.cps;
+  } else {
+    jchunk = rest % p.n_jchunk;
+    pair = rest / p.n_jchunk;
+  }
+}
+
+// Block until the rows of source rank `src` have landed in this rank's buffer (acquire at system scope pairs with the
+// red.release of the sender's last store).  Bounded: a lost sender must surface as a launch failure, not as a hung GPU.
+__device__ __forceinline__ void wait_source(const SimParams& p, int src, uint32_t& seen) {
+  if (seen & (1u << src)) return;
+  const unsigned long long* f = p.arrive + src;
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+  if (v < p.arrive_target) {
+    const long long t0 = clock64();
+    do {
+      __nanosleep(64);
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+      if (clock64() - t0 > 8000000000LL) {
+        printf("bsc: rows of rank %d never arrived (counter %llu, expected %llu) block=%d\n", src, v, p.arrive_target,
+               (int)blockIdx.x);
+        __trap();
+      }
+    } while (v < p.arrive_target);
+  }
+  seen |= 1u << src;
 }
 
 // Butterfly transpose-reduce: on entry every lane holds 32 column values of its own row; on exit lane l
@@ -170,6 +207,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
     if (ptx::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      uint32_t seen = 0;
       for (int item = item0; item < p.num_items; item += item_step) {
         int pair, jchunk, iblk;
         decode_item(p, item, pair, jchunk, iblk);
@@ -178,6 +216,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
         const CUtensorMap* mb = &p.tmap[p.pair_b[pair]];
         const int arow = (int)(p.a_row0 + (int64_t)iblk * BM);
         const int jt_end = min(p.n_jtile, (jchunk + 1) * p.jpc);
+        if (EPI == EPI_STATS && p.arrive != nullptr) {
+          // the A rows are this rank's own, the B rows of a chunk all come from one source (chunks do not straddle ranks)
+          const uint32_t before = seen;
+          wait_source(p, p.my_rank, seen);
+          wait_source(p, jchunk / p.cps, seen);
+          // the rows were written through the generic proxy (by another GPU); TMA reads them through the async proxy
+          if (seen != before) ptx::fence_proxy_async_all();
+        }
         for (int jt = jchunk * p.jpc; jt < jt_end; ++jt) {
           const int brow = jt * BN;
           for (int kb = 0; kb < p.kblocks; ++kb) {
@@ -261,6 +307,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
     const int row_in_tile = q * 32 + lane;
     const int et = (threadIdx.x - 128) & 127;  // 0..127 inside the group
     uint32_t tile_count = 0;
+    uint32_t seen_e = 0;
     const uint32_t empty_l0 = PAIR ? ptx::mapa(ptx::smem_u32(&tail->tmem_empty[0]), 0) : 0u;
     for (int item = item0; item < p.num_items; item += item_step) {
       int pair, jchunk, iblk;
@@ -275,6 +322,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
       int rep_i = -2, wmin = 0, wmax = -1;
       float inv_i = 0.f;
       const float* invb_g = nullptr;
+      if (EPI == EPI_STATS && p.arrive != nullptr) {
+        // the inverse norms of the rows and of the chunk's columns travel with the operand rows
+        if (lane == 0) {
+          wait_source(p, p.my_rank, seen_e);
+          wait_source(p, jchunk / p.cps, seen_e);
+        }
+        __syncwarp();
+      }
       if (EPI == EPI_STATS) {
         if (row_ok) inv_i = p.inv[p.pair_a[pair]][p.a_row0 + arow];
         invb_g = p.inv[p.pair_b[pair]];
@@ -610,15 +665,45 @@ static int pick_jpc(int n_iblk, int n_jtile, int n_pairs) {
   return jpc;
 }
 
-void tc_fwd_tiling(int64_t n_local, int64_t n_global, int n_pairs, int* n_iblk, int* n_jtile, int* jpc,
+// Several ranks with row blocks that are whole column tiles (n_local % 256 == 0): column chunks never straddle two
+// source ranks (what the fused all-gather needs), and the chunk length is the divisor of the tiles per source that
+// wastes the least of the last round of items.
+bool tc_fwd_source_aligned(int64_t n_local, int64_t n_global, int world) {
+  return world > 1 && n_local > 0 && n_local % BN == 0 && n_global == (int64_t)world * n_local;
+}
+
+void tc_fwd_tiling(int64_t n_local, int64_t n_global, int n_pairs, int world, int* n_iblk, int* n_jtile, int* jpc,
                    int* n_jchunk) {
   *n_iblk = (int)((n_local + BM - 1) / BM);
   *n_jtile = (int)((n_global + BN - 1) / BN);
+  if (tc_fwd_source_aligned(n_local, n_global, world)) {
+    const int tps = (int)(n_local / BN);
+    const int np = n_pairs > 0 ? n_pairs : 1;
+    const int units = (*n_iblk % 2 == 0 && *n_iblk >= 2) ? num_sms() / 2 : num_sms();
+    const int iblk_items = (*n_iblk % 2 == 0 && *n_iblk >= 2) ? *n_iblk / 2 : *n_iblk;
+    int best = tps;
+    double best_cost = 1e300;
+    for (int dv = 1; dv <= tps; ++dv) {
+      if (tps % dv) continue;
+      const int64_t items = (int64_t)np * world * (tps / dv) * iblk_items;
+      if (items > 64ll * units) continue;  // keep the partial-sum buffers small
+      const double rounds = (double)((items + units - 1) / units);
+      const double cost = rounds * (dv + 0.5);  // tiles per item + half a tile of fill / drain
+      if (cost < best_cost * 0.999) {
+        best_cost = cost;
+        best = dv;
+      }
+    }
+    *jpc = best;
+    *n_jchunk = world * (tps / best);
+    return;
+  }
   *jpc = pick_jpc(*n_iblk, *n_jtile, n_pairs > 0 ? n_pairs : 1);
   *n_jchunk = (*n_jtile + *jpc - 1) / *jpc;
 }
 
-int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceFwdWs& L, char* ws, float* stats, cudaStream_t st) {
+int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceFwdWs& L, char* ws, float* stats,
+                 const bsc_infonce_exchange* ex, cudaStream_t st) {
   BSC_REQUIRE(d->d % BK == 0, BSC_EUNSUPPORTED, "TC16 mode needs d %% 64 == 0 (got %d); use BSC_MODE_F32", d->d);
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
   SimParams p{};
@@ -658,16 +743,26 @@ int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceFwdWs& L, char* ws, flo
   p.jrange = (const int2*)(ws + L.jrange);
   p.a_pad = L.n_local_pad;
   p.b_pad = L.n_global_pad;
+  if (ex != nullptr && ex->arrive != nullptr) {
+    BSC_REQUIRE(tc_fwd_source_aligned(d->n_local, d->n_global, d->world), BSC_EUNSUPPORTED,
+                "the fused all-gather needs n_local %% 256 == 0 and equal row blocks");
+    p.arrive = (const unsigned long long*)ex->arrive;
+    p.arrive_target = ex->arrive_target;
+    p.src_rows = (int)d->n_local;
+    p.my_rank = d->rank;
+    p.world = d->world;
+    p.chunk_major = 1;
+    p.cps = L.n_jchunk / d->world;
+  }
   int rc = rep_range_launch(d->rep, d->n_global, BN, (int2*)(ws + L.jrange), st);
   if (rc) return rc;
   timing_begin(0, st);
   rc = d->x16_dtype == BSC_BF16 ? launch_sim<EPI_STATS, 1>(p, st) : launch_sim<EPI_STATS, 0>(p, st);
   timing_end(0, st);
   if (rc) return rc;
-  // sum_ij T_ij (s*S_ij - s) over the local rows and all pairs, in natural-log units
-  rc = sum_rows_launch(p.rowpos, np * L.n_jchunk * NG, L.n_local_pad, d->n_local, 0.6931471805599453f,
-                       stats + 6 * d->n_global, st);
-  if (rc) return rc;
+  // One launch reduces the partial sums into this rank's statistics record -- sum-exp rows of the local rows, partial
+  // column sums, the positive term sum_ij T_ij (s*S_ij - s) in natural-log units -- and mirrors it into slot `rank` of
+  // every peer's record area (the statistics exchange: no NCCL call)
   ReduceJobs jobs{};
   for (int q = 0; q < np; ++q) {
     const int a = p.pair_a[q], b = p.pair_b[q];
@@ -676,6 +771,22 @@ int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceFwdWs& L, char* ws, flo
                                        stats + (int64_t)pair_id(a, b) * d->n_global + d->row0};
     jobs.job[jobs.count++] = ReduceJob{p.colpart + (int64_t)q * L.n_iblk * L.n_global_pad, L.n_iblk, L.n_global_pad,
                                        d->n_global, stats + (int64_t)pair_id(b, a) * d->n_global};
+  }
+  jobs.pos_part = p.rowpos;
+  jobs.pos_nparts = np * L.n_jchunk * NG;
+  jobs.pos_stride = L.n_local_pad;
+  jobs.pos_n = d->n_local;
+  jobs.pos_scale = 0.6931471805599453f;
+  jobs.pos_out = reinterpret_cast<double*>(stats + stats_pos_offset(d->n_global));
+  if (ex != nullptr && (ex->stats_peers != nullptr || ex->stats_multicast != nullptr)) {
+    const int64_t slot = (int64_t)d->rank * stats_record_len(d->n_global);
+    jobs.local_base = stats;
+    if (ex->stats_multicast != nullptr) {
+      jobs.mc_base = (float*)ex->stats_multicast + slot;
+    } else {
+      jobs.n_peers = d->world;
+      for (int r = 0; r < d->world; ++r) jobs.peer_base[r] = (float*)ex->stats_peers[r] + slot;
+    }
   }
   return reduce_parts_batch_launch(jobs, st);
 }
@@ -700,8 +811,8 @@ size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* d) {
   return blocks * (size_t)n_iblk_pad * (size_t)n_j64 * 16384;
 }
 
-int tc_bwd_weights(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, int* n_pairs, int* pairs_a,
-                   int* pairs_b, cudaStream_t st) {
+int tc_bwd_weights(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, const float* aux, int* n_pairs,
+                   int* pairs_a, int* pairs_b, cudaStream_t st) {
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
   const bool ordered = L.mode == BSC_BWD_BLOCKS;
   SimParams p{};
@@ -738,8 +849,8 @@ int tc_bwd_weights(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, i
   p.k1 = d->logit_scale * log2e;
   p.k2 = d->logit_scale * log2e;
   p.rep = d->rep;
-  p.uv = (const float*)(ws + L.uv);
-  p.gsbuf = (const float*)(ws + L.gs);
+  p.uv = aux;
+  p.gsbuf = aux + 6 * d->n_global;
   p.gimg = (uint8_t*)(ws + L.gimg);
   tc_bwd_matrix_dims(d, &p.n_iblk_pad, &p.n_j64);
   p.jrange = (const int2*)(ws + L.jrange);

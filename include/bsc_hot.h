@@ -84,24 +84,39 @@ int bsc_l2norm_fwd(const void* x, int x_dtype, int64_t n, int d, int64_t ldx,
 int bsc_rows_to_f16(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, float* inv, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
- * K1+gather  TC16 operand preparation fused with the all_gather of gather_features (loss_func.py:58-91, the
- * default gather_with_grad=False branch :84-89 where only values cross ranks) over NVLink peer memory.
- * Every rank owns a buffer of bsc_gather_layout().total_bytes that is mapped into all ranks of the node
- * (peer_buffers[r] = address of rank r's buffer in THIS process, e.g. torch symmetric memory):
- *     xh[m]  at off_xh[m]:  n_global x d fp16      inv[m] at off_inv[m]: n_global fp32      labels at off_labels: int64
- * bsc_gather_push computes, for the n_local rows of every present modality, what bsc_rows_to_f16 computes and stores
- * row row0 + l (fp16 row, scale, label) into EVERY rank's buffer.  The caller must run a cross-rank barrier on the
- * stream after the call before any rank reads its buffer, and must not push into a buffer a peer may still read
- * (alternate two buffers by step).  All modalities share x_dtype; x[m] = NULL marks an absent modality.
- * multicast_buffer: the NVSwitch multicast address of the same buffer (torch symmetric memory: multicast_ptr) or NULL.
- * When given, every row is stored ONCE with multimem.st and the switch replicates it into all ranks' buffers: the
- * gather costs a rank the NVLink egress of its own rows instead of one copy per peer.
+ * K1+gather  TC16 operand preparation fused with the all_gather of gather_features (loss_func.py:58-91) and of the
+ * labels (:122) over NVLink peer memory.  Every rank owns a buffer of bsc_gather_layout().total_bytes that is mapped
+ * into all ranks of the node (peer_buffers[r] = address of rank r's buffer in THIS process, e.g. torch symmetric memory;
+ * multicast_buffer = the NVSwitch multicast address of the same buffer or NULL):
+ *     xh[m]  at off_xh[m]: n_global x d fp16     inv[m] at off_inv[m]: n_global fp32     labels at off_labels: int64
+ *     statistics records at off_stats: float[world][bsc_infonce_stats_len]     arrival counters at off_flags: u64[16]
+ * bsc_gather_push_labels stores the local labels into every rank's buffer (all labels are needed before the label
+ * statistics can start; a cross-rank barrier follows).
+ * bsc_gather_push computes, for the n_local rows of every present modality, what bsc_rows_to_f16 computes and stores row
+ * row0 + l (fp16 row, scale, and the label when `labels` is given) into every rank's buffer.
+ *   ordered = 0: all destinations at once (one multimem.st per 16 bytes when multicast_buffer is given); the caller runs a
+ *                cross-rank barrier before any rank reads.
+ *   ordered = 1: the fused all-gather -> similarity sweep.  The kernel writes the rows into this rank's OWN buffer; the
+ *                call then queues, on the same stream, one ring step per destination (rank, rank+1, ...): the copy
+ *                engines move the fp16 rows (cudaMemcpyAsync between the peer-mapped buffers, no SM involved), a small
+ *                kernel forwards the inverse norms and publishes arrive[source rank] = epoch in the destination's
+ *                buffer with release semantics.  A receiver hears from one sender at a time.  epoch = number of ordered
+ *                pushes into this buffer so far, this one included (1, 2, ...).  The consumer (bsc_infonce_fwd with
+ *                bsc_infonce_exchange.arrive, arrive_target = epoch) waits per source rank and sweeps the sources in
+ *                their order of arrival while the later ones are still in flight.  No barrier; call it on a side stream.
+ * The caller must not push into a buffer a peer may still read (alternate two buffers by step; every step contains at
+ * least one cross-rank barrier).  All modalities share x_dtype; x[m] = NULL marks an absent modality.
+ * Measured on 8 x B200: the gather delivers (W-1)/W of the global batch into every GPU, 132 MB of NVLink ingress =
+ * 0.22 ms whichever way the bytes are sent -- it can be overlapped, not shortened.  SM stores that back up behind a
+ * saturated NVLink port stall every memory operation of their SM (co-resident kernels ran up to 4x slower), hence DMA.
  * ---------------------------------------------------------------------------------------------- */
-int bsc_gather_layout(int64_t n_global, int d, size_t off_xh[3], size_t off_inv[3], size_t* off_labels,
-                      size_t* total_bytes);
+int bsc_gather_layout(int64_t n_global, int d, int world, size_t off_xh[3], size_t off_inv[3], size_t* off_labels,
+                      size_t* off_stats, size_t* off_flags, size_t* total_bytes);
+int bsc_gather_push_labels(const int64_t* labels, int64_t n_local, int64_t row0, int64_t n_global, int d,
+                           void* const* peer_buffers, void* multicast_buffer, int world, void* stream);
 int bsc_gather_push(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels, int64_t n_local,
                     int64_t row0, int64_t n_global, int d, void* const* peer_buffers, void* multicast_buffer, int world,
-                    void* stream);
+                    int rank, int ordered, uint64_t epoch, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * K2  label statistics replacing construct_label_metrix (loss_func.py:18-21): for labels[n]
@@ -172,8 +187,11 @@ typedef struct bsc_infonce_plan_t {
                                   into every peer when world > 1 (torch symmetric memory); 0 for the other modes   */
 } bsc_infonce_plan_t;
 
-/* number of floats in the statistics vector: 6 ordered-pair sum-exp rows of n_global + 4 scalars */
+/* A statistics RECORD: bsc_infonce_stats_len(n_global) floats = 6 ordered-pair sum-exp rows of n_global | 4 scalars |
+ * 64 double partial sums of the positive-pair term.  bsc_infonce_aux_len floats hold what the backward needs from the
+ * combined statistics: uv[6][n_global] = r_i / sum-exp, then 32 scale factors. */
 int64_t bsc_infonce_stats_len(int64_t n_global);
+int64_t bsc_infonce_aux_len(int64_t n_global);
 
 /* Resolve the backward strategy and size the buffers.  p->bwd_mode is ignored; requested_bwd_mode = BSC_BWD_AUTO picks
  * SCATTER when all rows are local or the ranks can map each other's memory (peer_memory != 0), BLOCKS otherwise, and
@@ -182,29 +200,43 @@ int64_t bsc_infonce_stats_len(int64_t n_global);
 int bsc_infonce_plan(const bsc_infonce_desc* p, int requested_bwd_mode, int peer_memory, size_t memory_budget_bytes,
                      bsc_infonce_plan_t* plan);
 
-/* Forward sweep.  stats (bsc_infonce_stats_len floats, overwritten) receives, for every ordered pair
- * (a,b) of present modalities, sum_j exp(S_ab[i,j] - s) for the rows this rank can complete and the
- * PARTIAL column sums over its local rows, plus (slot 6*n_global) the local part of
- * sum over unordered pairs sum_ij T_ij (S_ab[i,j] - s), taken from the same logits as the exponentials.
- * With more than one rank the caller sums `stats` over ranks (one all_reduce) before the next calls. */
-int bsc_infonce_fwd(const bsc_infonce_desc* p, float* stats, void* workspace, size_t workspace_bytes,
-                    void* stream);
+/* Peer-memory side of the forward (all fields optional; NULL = none). */
+typedef struct bsc_infonce_exchange {
+  void* const* stats_peers;  /* [world] the statistics-record area (float[world][stats_len]) of every rank's buffer: the
+                                forward also stores its record into slot p->rank of each -- the statistics exchange
+                                without an NCCL call; the caller runs a barrier before bsc_infonce_loss               */
+  void* stats_multicast;     /* multicast address of the same area: one store per value instead of `world`            */
+  const uint64_t* arrive;    /* [world] arrival counters in THIS rank's gather buffer (bsc_gather_push ordered = 1):
+                                the sweep waits per source rank; NULL: the operands are complete on entry             */
+  uint64_t arrive_target;    /* the epoch of the push whose rows this forward reads                                   */
+} bsc_infonce_exchange;
 
-/* loss[0] = the scalar of loss_func.py:54 / :163 from the (rank-summed) statistics. */
-int bsc_infonce_loss(const bsc_infonce_desc* p, const float* stats, float* loss, void* stream);
+/* Forward sweep.  stats (one record, overwritten) receives, for every ordered pair (a,b) of present modalities,
+ * sum_j exp(S_ab[i,j] - s) for the rows this rank can complete and the PARTIAL column sums over its local rows, plus the
+ * local part of sum over unordered pairs sum_ij T_ij (S_ab[i,j] - s), taken from the same logits as the exponentials. */
+int bsc_infonce_fwd(const bsc_infonce_desc* p, float* stats, const bsc_infonce_exchange* exchange, void* workspace,
+                    size_t workspace_bytes, void* stream);
+
+/* Statistics finish: records = n_records per-rank records (this rank's own one when n_records == 1), added in rank
+ * order (deterministic); stats receives the combined record, aux the backward's factors, loss[0] the scalar of
+ * loss_func.py:54 / :163.  scratch: bsc_infonce_loss_scratch_bytes() of device memory that the caller zeroes ONCE; every
+ * call leaves it zeroed again (a ticket counter and per-block partial sums; one scratch per stream in flight). */
+size_t bsc_infonce_loss_scratch_bytes(void);
+int bsc_infonce_loss(const bsc_infonce_desc* p, const float* records, int n_records, float* stats, float* aux,
+                     float* loss, void* scratch, void* stream);
 
 /* Backward, phase 1: raw gradient sums.  Writes the local partial sums into the workspace and, in BSC_BWD_SCATTER, the
  * partial sums that belong to rank q's rows into exchange[q] (slot p->rank).  exchange = p->world device pointers in
  * THIS process's address space (exchange[p->rank] = own buffer); NULL for the other strategies.  With world > 1 the
  * caller runs a cross-rank barrier on the stream between this call and bsc_infonce_bwd_finish, and must not start the
  * next step's phase 1 before every rank has finished reading its buffer (the forward's barrier of the next step). */
-int bsc_infonce_bwd_partials(const bsc_infonce_desc* p, const float* stats, void* const* exchange, void* workspace,
+int bsc_infonce_bwd_partials(const bsc_infonce_desc* p, const float* aux, void* const* exchange, void* workspace,
                              size_t workspace_bytes, void* stream);
 
 /* Backward, phase 2: x[m] are this rank's ORIGINAL (un-normalised) local rows, dtype x_dtype, row stride ldx[m]
  * elements; grad[m] (same dtype, DENSE [n_local][d]) receives grad_out[0] * dLoss/dx[m]: fixed-order sum of the partial
  * sums (workspace and own_exchange), then the chain through F.normalize. */
-int bsc_infonce_bwd_finish(const bsc_infonce_desc* p, const void* const* x, int x_dtype, const int64_t* ldx,
+int bsc_infonce_bwd_finish(const bsc_infonce_desc* p, const float* aux, const void* const* x, int x_dtype, const int64_t* ldx,
                            const float* grad_out, void* const* grad, const void* own_exchange, void* workspace,
                            size_t workspace_bytes, void* stream);
 

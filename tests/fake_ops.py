@@ -31,7 +31,7 @@ class FakeOps:
         r = t.sum(1).double()
         return r, t, None, r.max().reshape(1)
 
-    def infonce_fwd(self, p):
+    def infonce_fwd(self, p, exchange=None):
         n = p.n_global
         stats = torch.zeros(6 * n + 4, dtype=torch.float64)
         sl = slice(p.row0, p.row0 + p.n_local)
@@ -52,7 +52,11 @@ class FakeOps:
         stats[6 * n] = pos
         return stats
 
-    def infonce_loss(self, p, stats):
+    def infonce_loss(self, p, records):
+        """bsc_infonce_loss: per-rank records added in rank order -> (loss, combined record, aux)."""
+        stats = torch.zeros_like(records[0])
+        for w in range(records.shape[0]):
+            stats = stats + records[w]
         n = p.n_global
         present = [m for m in range(3) if p.xh[m] is not None]
         m = len(present)
@@ -61,7 +65,7 @@ class FakeOps:
             for b in present:
                 if a != b:
                     tot = tot + (p.r * torch.log(stats[pair_id(a, b) * n: pair_id(a, b) * n + n])).sum()
-        return ((tot - 2.0 * stats[6 * n]) / (n * m * (m - 1))).float()
+        return ((tot - 2.0 * stats[6 * n]) / (n * m * (m - 1))).float(), stats, stats
 
     # ---- backward: the two phases of include/bsc_hot.h -------------------------------------------------------
     def plan(self, p, requested=-1, peer_memory=True):
@@ -102,7 +106,7 @@ class FakeOps:
                 outbox[:, q] = part.reshape(p.world, p.n_local, p.d)
                 q += 1
 
-    def infonce_bwd_finish(self, p, xs, grad_out, own_exchange=None):
+    def infonce_bwd_finish(self, p, stats, xs, grad_out, own_exchange=None):
         n = p.n_global
         present = [m for m in range(3) if p.xh[m] is not None]
         m = len(present)

@@ -2,7 +2,7 @@
 product's, called through the C ABI).  Used by tests/test_gpu_loss.py and tools/stripe_step.py.
 
 The replay runs the ranks one after the other, phase by phase, which is exactly the dependency order of the real job:
-  1. forward of every rank's row stripe          -> the statistics are summed as the all-reduce would
+  1. forward of every rank's row stripe          -> the per-rank statistics records, handed out as the exchange would
   2. bsc_infonce_bwd_partials of every rank      -> in the scatter strategy every rank stores its partial gradients
                                                     into ALL ranks' exchange buffers (W tensors on the one device, handed
                                                     out as "peer" addresses)
@@ -16,10 +16,10 @@ class StripeComm:
     what the ranks would have exchanged), the statistics all-reduce returns the sum accumulated over a first pass."""
     peer_memory = True
 
-    def __init__(self, ops, rank, world, feats_all, labels_all, stats_sum=None, shared=None):
+    def __init__(self, ops, rank, world, feats_all, labels_all, records=None, shared=None):
         self.ops, self.rank, self.world_size = ops, rank, world
         self.feats_all, self.labels_all = feats_all, labels_all
-        self.stats_sum, self.stats_local = stats_sum, None
+        self.records, self.stats_local = records, None
         self.shared = shared if shared is not None else {}
 
     def gather_tc16(self, feats, labels):
@@ -31,14 +31,20 @@ class StripeComm:
                 inv.append(iv)
             self.shared["gathered"] = (xh, inv)
         xh, inv = self.shared["gathered"]
-        return xh, inv, self.labels_all
+        return {"xh": xh, "inv": inv, "labels": self.labels_all}
 
     def all_gather_rows(self, t):
         raise AssertionError("the TC16 path gathers through gather_tc16")
 
-    def all_reduce_sum(self, t):
-        self.stats_local = t.clone()
-        return t if self.stats_sum is None else self.stats_sum.clone()
+    def share_stats(self, record):
+        """First pass (records is None): remember this rank's record.  Second pass: hand out all ranks' records, this
+        rank's slot refreshed with the record just computed -- what the exchange over peer memory / all_gather yields."""
+        self.stats_local = record.clone()
+        if self.records is None:
+            return record[None]
+        out = self.records.clone()
+        out[self.rank] = record
+        return out
 
     def prepare_exchange(self, nbytes, device):
         return True
@@ -51,18 +57,18 @@ def _local(feats_all, labels_all, rank, world):
 
 
 def first_pass(ops, world, feats_all, labels_all, scale=1 / 0.07, shared=None):
-    """Forward of every rank's stripe; returns the summed statistics vector (what the all-reduce would hand out)."""
+    """Forward of every rank's stripe; returns the [world, len] statistics records (what the exchange hands out)."""
     from bsc._lib import MODE_TC16
     from bsc.loss import infonce_forward
 
-    total = None
+    recs = []
     shared = shared if shared is not None else {}
     for r in range(world):
         comm = StripeComm(ops, r, world, feats_all, labels_all, shared=shared)
         local, lab = _local(feats_all, labels_all, r, world)
         infonce_forward(ops, comm, local, lab, scale, MODE_TC16, want_grad=False)
-        total = comm.stats_local if total is None else total + comm.stats_local
-    return total
+        recs.append(comm.stats_local)
+    return torch.stack(recs)
 
 
 def replay(ops, world, feats_all, labels_all, request, scale=1 / 0.07, grad_out=1.0):
@@ -71,14 +77,14 @@ def replay(ops, world, feats_all, labels_all, request, scale=1 / 0.07, grad_out=
     from bsc.loss import infonce_forward
 
     shared = {}
-    stats_sum = first_pass(ops, world, feats_all, labels_all, scale, shared)
+    records = first_pass(ops, world, feats_all, labels_all, scale, shared)
     nl = labels_all.shape[0] // world
     ranks = []
     for r in range(world):
-        comm = StripeComm(ops, r, world, feats_all, labels_all, stats_sum, shared)
+        comm = StripeComm(ops, r, world, feats_all, labels_all, records, shared)
         local, lab = _local(feats_all, labels_all, r, world)
-        loss, (prob, stats) = infonce_forward(ops, comm, local, lab, scale, MODE_TC16, True, request)
-        ranks.append((loss, prob, stats, local))
+        loss, (prob, aux) = infonce_forward(ops, comm, local, lab, scale, MODE_TC16, True, request)
+        ranks.append((loss, prob, aux, local))
     mode = ranks[0][1].bwd_mode
     dev = labels_all.device
     bufs, ptrs = [None] * world, None
@@ -87,12 +93,12 @@ def replay(ops, world, feats_all, labels_all, request, scale=1 / 0.07, grad_out=
         bufs = [torch.full((max(ranks[0][1].exchange_bytes // 4, 4),), float("nan"), dtype=torch.float32, device=dev)
                 for _ in range(world)]
         ptrs = [b.data_ptr() for b in bufs]
-    for loss, prob, stats, local in ranks:
-        ops.infonce_bwd_partials(prob, stats, ptrs)
+    for loss, prob, aux, local in ranks:
+        ops.infonce_bwd_partials(prob, aux, ptrs)
     g_out = torch.tensor(grad_out, dtype=torch.float32, device=dev)
     grads = [None if f is None else torch.empty_like(f) for f in feats_all]
-    for r, (loss, prob, stats, local) in enumerate(ranks):
-        gl = ops.infonce_bwd_finish(prob, local, g_out, bufs[r])
+    for r, (loss, prob, aux, local) in enumerate(ranks):
+        gl = ops.infonce_bwd_finish(prob, aux, local, g_out, bufs[r])
         for g, l in zip(grads, gl):
             if g is not None:
                 g[r * nl:(r + 1) * nl] = l

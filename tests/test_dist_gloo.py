@@ -18,7 +18,7 @@ class GlooScatterComm:
 
     def __init__(self, base):
         self.base, self.rank, self.world_size = base, base.rank, base.world_size
-        self.all_gather_rows, self.all_reduce_sum = base.all_gather_rows, base.all_reduce_sum
+        self.all_gather_rows, self.share_stats = base.all_gather_rows, base.share_stats
 
     def prepare_exchange(self, nbytes, device):
         self.shape = None
@@ -58,8 +58,9 @@ class _ShapedOps:
     def infonce_bwd_partials(self, p, stats, exchange_ptrs=None):
         return self.ops.infonce_bwd_partials(p, stats, None if exchange_ptrs is None else self._shape(p, exchange_ptrs))
 
-    def infonce_bwd_finish(self, p, xs, grad_out, own_exchange=None):
-        return self.ops.infonce_bwd_finish(p, xs, grad_out, None if own_exchange is None else self._shape(p, own_exchange))
+    def infonce_bwd_finish(self, p, stats, xs, grad_out, own_exchange=None):
+        return self.ops.infonce_bwd_finish(p, stats, xs, grad_out,
+                                           None if own_exchange is None else self._shape(p, own_exchange))
 
 
 def _worker(rank, world, port, feats, labels, gather_with_grad, ret, scatter=False):

@@ -1,0 +1,6 @@
+#!/bin/bash
+cd /root/repo; mkdir -p gpurun_out
+W=${1:-8}
+timeout 900 python -m pytest tests/test_gpu_loss.py -x -q -m gpu 2>&1 | tail -4
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $W --master-addr 127.0.0.1 --master-port 29544 tools/dist_phases.py 32768 10 2>&1 | grep "^rank\|Error\|error" | tee gpurun_out/r2d_phases_w$W.log
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $W --master-addr 127.0.0.1 --master-port 29541 tools/dist_check.py 4096 2>&1 | grep "^rank 0\|dist_check\|Error\|error" 

@@ -110,7 +110,7 @@ with torch.no_grad():
     crit(lb[0], lb[1], lb[2], local_labels, bench.SCALE)
 (loss_a + loss_b).backward()
 torch.cuda.synchronize()
-assert float(loss_a) == float(base[0]) and float(loss_b) == float(base_other[0])
+assert float(loss_a.detach()) == float(base[0]) and float(loss_b.detach()) == float(base_other[0])
 for got, want in ((la, base[1]), (lb, base_other[1])):
     for leaf, g in zip(got, want):
         assert torch.equal(leaf.grad, g), "delayed backward read operands that a later forward had overwritten"

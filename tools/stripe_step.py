@@ -25,7 +25,7 @@ dev = torch.device("cuda", 0)
 feats, labels = bench.synth_loss_rows(torch, n, 0, n, dev, torch.bfloat16)
 ops = _default_ops()
 shared = {}
-stats_sum = first_pass(ops, world, feats, labels, bench.SCALE, shared)
+records = first_pass(ops, world, feats, labels, bench.SCALE, shared)
 local, lab = _local(feats, labels, 0, world)
 g_out = torch.ones((), device=dev)
 bufs = None
@@ -37,12 +37,12 @@ for k in range(2 + steps):
     shared.pop("gathered", None)  # the stand-in gather (operand preparation of all N rows) is part of the step
     t0.record()
     c0 = time.perf_counter()
-    comm = StripeComm(ops, 0, world, feats, labels, stats_sum, shared)
-    loss, (prob, stats) = infonce_forward(ops, comm, local, lab, bench.SCALE, _lib.MODE_TC16, True, request)
+    comm = StripeComm(ops, 0, world, feats, labels, records, shared)
+    loss, (prob, aux) = infonce_forward(ops, comm, local, lab, bench.SCALE, _lib.MODE_TC16, True, request)
     if prob.exchange_bytes and bufs is None:
         bufs = [torch.zeros(prob.exchange_bytes // 4, dtype=torch.float32, device=dev) for _ in range(world)]
-    ops.infonce_bwd_partials(prob, stats, None if bufs is None else [t.data_ptr() for t in bufs])
-    ops.infonce_bwd_finish(prob, local, g_out, None if bufs is None else bufs[0])
+    ops.infonce_bwd_partials(prob, aux, None if bufs is None else [t.data_ptr() for t in bufs])
+    ops.infonce_bwd_finish(prob, aux, local, g_out, None if bufs is None else bufs[0])
     h1 = time.perf_counter() - c0  # host time to queue the step
     t1.record()
     torch.cuda.synchronize()
