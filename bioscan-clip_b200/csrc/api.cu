@@ -187,9 +187,9 @@ InfoNceFwdWs infonce_fwd_layout(const bsc_infonce_desc* p) {
   L.n_local_pad = (int64_t)align_up((size_t)(n > 0 ? n : 1), 64);
   L.n_global_pad = (int64_t)align_up((size_t)(N > 0 ? N : 1), 64);
   size_t off = 0;
-  // x2: the tensor-core forward sweep keeps one partial per epilogue warp group (tc_sim.cu NG)
-  L.rowpart = take(off, (size_t)3 * 2 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
-  L.rowpos = take(off, (size_t)3 * 2 * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
+  // the tensor-core forward sweep keeps one partial per epilogue warp group (tc_sim.cu NG)
+  L.rowpart = take(off, (size_t)3 * kSimNG * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
+  L.rowpos = take(off, (size_t)3 * kSimNG * (L.n_jchunk > 0 ? L.n_jchunk : 1) * L.n_local_pad * sizeof(float));
   L.jrange = take(off, (size_t)(L.n_jtile > 0 ? L.n_jtile : 1) * 2 * sizeof(int));
   L.colpart = take(off, (size_t)3 * (L.n_iblk > 0 ? L.n_iblk : 1) * L.n_global_pad * sizeof(float));
   L.total = off;

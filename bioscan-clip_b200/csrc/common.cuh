@@ -203,6 +203,7 @@ size_t simt_bank_ws(int64_t nq, int64_t nb, int d, int k);
 size_t tc_bank_ws(int64_t nq, int64_t nb, int d, int k);
 
 // tile shapes of the tensor-core kernels (host needs them for the workspace layout)
+constexpr int kSimNG = 3;    // epilogue warp groups of the similarity sweep (partial-sum slabs per column chunk)
 constexpr int kTcBM = 128;   // rows per CTA tile (TMEM lanes)
 constexpr int kTcBNF = 256;  // forward: columns per tile
 constexpr int kTcBNB = 128;  // backward: columns per tile

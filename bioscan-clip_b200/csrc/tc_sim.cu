@@ -32,8 +32,14 @@ constexpr int STAGE_BYTES = A_BYTES + B_BYTES;  // 48 KB
 constexpr int STAGE2_BYTES = A_BYTES + B_BYTES / 2;  // 32 KB
 constexpr int TMEM_COLS = 512;
 constexpr int KTOP = 8;  // register-resident top-k capacity of the TOPK epilogue
-constexpr int NG = 2;    // epilogue warp groups: each takes BN / NG columns of every tile (2 warps per SM sub-partition)
+// Epilogue warp groups: 12 warps (3 per SM sub-partition) share the 8 column chunks (32 columns each) of a tile 3 / 3 / 2.
+// With 2 groups (4 chunks per warp) the epilogue of a tile took longer than its MMAs -- the tensor pipe was 71 % (weights)
+// and 84 % (statistics) active, the epilogue warps stalled on shared-memory and TMEM latencies with 2 warps per scheduler.
+constexpr int NG = kSimNG;
 constexpr int NTHREADS = 128 + NG * 128;
+__device__ __forceinline__ int chunk_lo(int grp) { return grp == 0 ? 0 : (grp == 1 ? 3 : 6); }
+__device__ __forceinline__ int chunk_hi(int grp) { return grp == 0 ? 3 : (grp == 1 ? 6 : 8); }
+static_assert(NG == 3 && kTcBNF == 256, "chunk_lo / chunk_hi split 8 chunks of 32 columns over 3 groups");
 
 enum { EPI_STATS = 0, EPI_TOPK = 1, EPI_WEIGHTS = 2 };
 
@@ -93,10 +99,11 @@ struct __align__(8) SimSmemTail {
   uint32_t pad;
   float cs[2][4][BN];  // per-warp column partial sums, double-buffered by tile parity
   float invb[2][BN];   // k1 * inverse norms of the tile's columns, double-buffered by tile parity
-  __align__(16) uint8_t wst[8][2048];  // EPI_WEIGHTS: per-warp staging of 32 half rows (64 bytes each)
+  __align__(16) uint8_t wst[4 * NG][2048];  // EPI_WEIGHTS: per-warp staging of 32 half rows (64 bytes each)
 };
 
-constexpr size_t SIM_SMEM_BYTES = 1024 /*align slack*/ + (size_t)STAGES * STAGE_BYTES + sizeof(SimSmemTail);
+constexpr size_t SIM_SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + sizeof(SimSmemTail);
+static_assert(SIM_SMEM_BYTES <= 232448, "similarity sweep exceeds 227 KB of shared memory");
 static_assert(STAGES2 * STAGE2_BYTES == STAGES * STAGE_BYTES, "both ring shapes use the same shared memory");
 
 __device__ __forceinline__ void decode_item(const SimParams& p, int item, int& pair, int& jchunk, int& iblk) {
@@ -162,10 +169,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
   const uint32_t crank = PAIR ? ptx::cluster_ctarank() : 0u;
   const int item0 = PAIR ? (int)ptx::cluster_id_x() : (int)blockIdx.x;
   const int item_step = PAIR ? (int)ptx::n_clusters_x() : (int)gridDim.x;
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t raw_addr = ptx::smem_u32(smem_raw);
-  const uint32_t ring = (raw_addr + 1023u) & ~1023u;
-  uint8_t* ring_ptr = smem_raw + (ring - raw_addr);
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t ring = ptx::smem_u32(smem_raw);
+  if ((ring & 1023u) != 0) {
+    if (threadIdx.x == 0) printf("bsc: dynamic shared memory is not 1024-byte aligned (0x%x)\n", ring);
+    __trap();
+  }
+  uint8_t* ring_ptr = smem_raw;
   SimSmemTail* tail = reinterpret_cast<SimSmemTail*>(ring_ptr + (size_t)NST * SB);
 
   const int warp = threadIdx.x >> 5;
@@ -303,7 +313,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
     // ================= epilogue (4 warps, thread <-> TMEM lane) =================
     const int q = warp & 3;            // TMEM lane quarter this warp may read
     const int grp = (warp - 4) >> 2;   // column group of the tile
-    constexpr int GC = BN / NG;        // columns per group
+    const int col_lo = 32 * chunk_lo(grp), col_hi = 32 * chunk_hi(grp);  // this group's columns of every tile
     const int row_in_tile = q * 32 + lane;
     const int et = (threadIdx.x - 128) & 127;  // 0..127 inside the group
     uint32_t tile_count = 0;
@@ -378,7 +388,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
         const int64_t col0 = (int64_t)jt * BN;
         if (EPI == EPI_STATS) {
           // stage k1 / ||b_j|| of the tile's columns (2 per thread) while the MMAs of this tile are in flight
-          for (int col = grp * GC + et; col < (grp + 1) * GC; col += 128) {
+          for (int col = col_lo + et; col < col_hi; col += 128) {
             const int64_t j = col0 + col;
             tail->invb[buf][col] = j < p.b_rows ? p.k1 * invb_g[j] : 0.f;
           }
@@ -389,7 +399,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
           float* vgb = &tail->cs[0][0][0] + buf * BN;
           float* wfb = &tail->cs[0][2][0] + buf * BN;
           int* repb = reinterpret_cast<int*>(&tail->cs[1][0][0]) + buf * BN;
-          for (int col = grp * GC + et; col < (grp + 1) * GC; col += 128) {
+          for (int col = col_lo + et; col < col_hi; col += 128) {
             const int64_t j = col0 + col;
             const bool ok = j < p.b_rows;
             tail->invb[buf][col] = ok ? p.k1 * invb_g[j] : 0.f;
@@ -413,7 +423,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
           tile_pos = (wmax >= jr.x) && (wmin <= jr.y);
         }
 #pragma unroll 1
-        for (int c = grp * (GC / 32); c < (grp + 1) * (GC / 32); ++c) {
+        for (int c = chunk_lo(grp); c < chunk_hi(grp); ++c) {
           uint32_t raw[32];
           ptx::tmem_ld_32x32(taddr + c * 32, raw);
           ptx::tmem_ld_wait();
@@ -569,7 +579,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
         if (EPI == EPI_STATS) {
           ptx::named_bar_sync(1 + 2 * grp, 128);
           float* out = p.colpart + ((int64_t)pair * p.n_iblk + iblk) * p.b_pad + col0;
-          for (int col = grp * GC + et; col < (grp + 1) * GC; col += 128) {
+          for (int col = col_lo + et; col < col_hi; col += 128) {
             if (col0 + col < p.b_rows)
               out[col] = (tail->cs[buf][0][col] + tail->cs[buf][1][col]) +
                          (tail->cs[buf][2][col] + tail->cs[buf][3][col]);
