@@ -23,7 +23,7 @@ NORM_TORCH, NORM_SKLEARN = 0, 1
 
 EXPORTS = [
     "bsc_version", "bsc_last_error", "bsc_device_check", "bsc_l2norm_fwd", "bsc_rows_to_f16", "bsc_label_stats", "bsc_label_stats_workspace_bytes",
-    "bsc_gather_layout", "bsc_gather_push", "bsc_gather_push_labels",
+    "bsc_gather_layout", "bsc_gather_push", "bsc_gather_push_labels", "bsc_gather_ring",
     "bsc_infonce_stats_len", "bsc_infonce_aux_len", "bsc_infonce_loss_scratch_bytes", "bsc_infonce_plan", "bsc_infonce_fwd", "bsc_infonce_loss",
     "bsc_infonce_bwd_partials", "bsc_infonce_bwd_finish", "bsc_bank_search_workspace_bytes", "bsc_bank_search", "bsc_bank_screen_parts", "bsc_bank_screen", "bsc_bank_rescore", "bsc_topk_merge", "bsc_taxonomy_eval",
     "bsc_set_timing", "bsc_last_kernel_ms", "bsc_launch_count", "bsc_last_bwd_mode",
@@ -87,6 +87,8 @@ def lib():
                                          c_void_p]
     L.bsc_gather_push.argtypes = [POINTER(c_void_p), c_int, POINTER(c_int64), c_void_p, c_int64, c_int64, c_int64, c_int,
                                   POINTER(c_void_p), c_void_p, c_int, c_int, c_int, ctypes.c_uint64, c_void_p]
+    L.bsc_gather_ring.argtypes = [POINTER(c_void_p), c_int, c_int, c_int64, c_int64, c_int64, c_int, ctypes.c_uint,
+                                  c_void_p]
     L.bsc_infonce_aux_len.argtypes = [c_int64]
     L.bsc_infonce_aux_len.restype = c_int64
     L.bsc_infonce_stats_len.argtypes = [c_int64]

@@ -173,8 +173,8 @@ class SymmMemComm(TorchDistComm):
           records()               call after the forward sweep: barrier, then the [world, len] records of all ranks
 
         Overlapped mode (row blocks that are whole column tiles; BSC_GATHER_OVERLAP=0 turns it off): the labels go first
-        (tiny, one barrier), then a SIDE stream prepares the rows in this rank's own buffer and lets the copy engines
-        carry them to one destination at a time, while the main stream already runs the label statistics and the
+        (tiny, one barrier), the rows are prepared in this rank's own buffer, then a SIDE stream lets the copy engines
+        carry them to one destination at a time while the main stream already runs the label statistics and the
         similarity sweep, which waits per source rank on arrival flags and starts with this rank's own columns.  Every GPU has to receive (W-1)/W of the batch (0.22 ms of NVLink ingress at
         8 x 4096 rows); this hides it behind the sweep instead of adding it to the step."""
         import ctypes
@@ -248,22 +248,27 @@ class SymmMemComm(TorchDistComm):
                                                     st["peers"][b], mc, self.world_size, main.cuda_stream))
                 handle.barrier(channel=0)
                 _mark("labels_barrier")
-                # the inputs exist, every rank is past whatever read this buffer two steps ago, and the two tiny
-                # launches above do not have to compete with the push for SM slots
+                # own rows into the own buffer + own arrival flag, on the MAIN stream: done before the sweep starts
+                st["pushes"][b] += 1
+                _lib.check(L.bsc_gather_push(x, _lib.dtype_code(f0.dtype), ldx, None, n_local, self.rank * n_local,
+                                             n_global, d, st["peers"][b], None, self.world_size, self.rank, 1,
+                                             st["pushes"][b], main.cuda_stream))
                 ready = torch.cuda.Event()
                 ready.record(main)
                 if self._side is None:
                     self._side = torch.cuda.Stream(dev)
-                st["pushes"][b] += 1
+                mask = sum(1 << m for m, f in enumerate(feats) if f is not None)
                 with torch.cuda.stream(self._side):
+                    # copy engines only (no kernel could be scheduled beside the persistent sweep): rows, inverse
+                    # norms and the arrival flag to rank+1, rank+2, ...
                     self._side.wait_event(ready)
-                    _lib.check(L.bsc_gather_push(x, _lib.dtype_code(f0.dtype), ldx, None, n_local, self.rank * n_local,
-                                                 n_global, d, st["peers"][b], None, self.world_size, self.rank, 1,
-                                                 st["pushes"][b], self._side.cuda_stream))
+                    _lib.check(L.bsc_gather_ring(st["peers"][b], self.world_size, self.rank, n_local,
+                                                 self.rank * n_local, n_global, d, mask, self._side.cuda_stream))
                     side_done = torch.cuda.Event()
                     side_done.record(self._side)
                 exchange["arrive"] = st["ptrs"][b][self.rank] + st["offf"]
                 exchange["arrive_target"] = st["pushes"][b]
+                _mark("own_rows")
             else:
                 _lib.check(L.bsc_gather_push(x, _lib.dtype_code(f0.dtype), ldx, labels.data_ptr(), n_local,
                                              self.rank * n_local, n_global, d, st["peers"][b], mc, self.world_size,

@@ -27,6 +27,8 @@ int taxo_launch(const int64_t* indices, int64_t nq, int k, const int32_t* key_id
 void gather_layout(int64_t n_global, int d, int world, size_t off_xh[3], size_t off_inv[3], size_t* off_labels,
                    size_t* off_stats, size_t* off_flags, size_t* total);
 int gather_blocks_per_dest(int64_t n_local);
+int gather_ring_launch(void* const* peers, int world, int rank, int64_t n_local, int64_t row0, int64_t n_global, int d,
+                       unsigned present_mask, cudaStream_t st);
 int gather_labels_launch(const int64_t* labels, int64_t n_local, int64_t row0, int64_t n_global, int d,
                          void* const* peers, void* multicast, int world, cudaStream_t st);
 int gather_push_launch(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels,
@@ -365,6 +367,16 @@ int bsc_gather_push(const void* const x[3], int x_dtype, const int64_t ldx[3], c
   BSC_REQUIRE(!ordered || epoch > 0, BSC_EINVAL, "bsc_gather_push: ordered pushes are numbered from 1");
   return gather_push_launch(x, x_dtype, ldx, labels, n_local, row0, n_global, d, peer_buffers, multicast_buffer, world,
                             rank, ordered ? 1 : 0, epoch, (cudaStream_t)stream);
+}
+
+int bsc_gather_ring(void* const* peer_buffers, int world, int rank, int64_t n_local, int64_t row0, int64_t n_global,
+                    int d, unsigned present_mask, void* stream) {
+  int rc = check_peers(peer_buffers, world, "bsc_gather_ring");
+  if (rc) return rc;
+  BSC_REQUIRE(rank >= 0 && rank < world, BSC_EINVAL, "bsc_gather_ring: rank %d of %d", rank, world);
+  BSC_REQUIRE(n_local >= 0 && row0 >= 0 && row0 + n_local <= n_global && d >= 8 && d % 8 == 0, BSC_EINVAL,
+              "bsc_gather_ring: bad shape");
+  return gather_ring_launch(peer_buffers, world, rank, n_local, row0, n_global, d, present_mask, (cudaStream_t)stream);
 }
 
 int bsc_taxonomy_eval(const int64_t* indices, int64_t nq, int k, const int32_t* key_ids, int64_t nb,

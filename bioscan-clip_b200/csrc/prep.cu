@@ -294,25 +294,11 @@ __global__ void __launch_bounds__(256) gather_push_kernel(const GatherPushArgs a
   }
 }
 
-// Ring step of the fused all-gather: after the copy engines have moved this rank's fp16 rows into destination `dst`
-// (cudaMemcpyAsync on the same stream), one small block forwards the inverse norms (3 x n_local floats) and then
-// publishes the arrival: arrive[source] = epoch in the destination's buffer, release at system scope.  The rows travel
-// by DMA because SM stores that back up behind a saturated NVLink port stall EVERY memory operation of their SM --
-// measured on 2 GPUs: label statistics 46 -> 209 us, similarity sweep +4 % while a store-based push ran beside them.
-__global__ void __launch_bounds__(256) gather_signal_kernel(const char* own, char* dst, size_t off_inv0, size_t off_inv1,
-                                                            size_t off_inv2, unsigned present_mask, int64_t row0,
-                                                            int64_t n_local, unsigned long long* flag,
-                                                            unsigned long long epoch) {
-  const size_t off[3] = {off_inv0, off_inv1, off_inv2};
-  if (dst != own) {
-    for (int m = 0; m < 3; ++m) {
-      if (!((present_mask >> m) & 1)) continue;
-      const float* s = reinterpret_cast<const float*>(own + off[m]) + row0;
-      float* t = reinterpret_cast<float*>(dst + off[m]) + row0;
-      for (int64_t i = threadIdx.x; i < n_local; i += blockDim.x) t[i] = s[i];
-    }
-  }
-  __syncthreads();
+// Publishes this rank's own rows: arrive[rank] = epoch in its OWN buffer (the value the DMA ring then copies into the
+// peers' buffers as their arrival flag).  Runs on the stream of the preparation kernel, i.e. BEFORE the sweep: nothing
+// of the ring needs an SM later -- the persistent sweep owns every register of every SM (512 threads x 128 registers),
+// a kernel queued beside it would never be scheduled, and a sweep waiting for that kernel's flag would never end.
+__global__ void gather_signal_kernel(unsigned long long* flag, unsigned long long epoch) {
   if (threadIdx.x == 0) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"(epoch) : "memory");
 }
 
@@ -394,23 +380,39 @@ int gather_push_launch(const void* const x[3], int x_dtype, const int64_t ldx[3]
   }
   BSC_LAUNCH_CHECK("gather_push_kernel");
   if (!ordered) return BSC_OK;
-  // the DMA ring: own rows first (already in place: publish), then rank+1, rank+2, ... -- every receiver hears from one
-  // sender at a time, in the order rank, rank-1, rank-2, ... in which its sweep will want the sources
-  char* own = a.peer[rank];
+  unsigned long long* flag = reinterpret_cast<unsigned long long*>(a.peer[rank] + a.off_flags) + rank;
+  gather_signal_kernel<<<1, 32, 0, st>>>(flag, (unsigned long long)epoch);
+  BSC_LAUNCH_CHECK("gather_signal_kernel");
+  return BSC_OK;
+}
+
+// The DMA ring of the fused all-gather -> similarity sweep: copy engines only, no kernel.  For destination rank+1,
+// rank+2, ...: the fp16 rows of every present modality, their inverse norms, then the arrival flag (8 bytes copied from
+// this rank's own flag, which holds the epoch) -- copies of one stream complete in order, so a peer that sees the flag
+// sees the rows.  Every receiver hears from one sender at a time, in the order rank-1, rank-2, ... in which its sweep
+// takes the sources.  The rows travel by DMA because SM stores that back up behind a saturated NVLink port stall every
+// memory operation of their SM (measured on 2 GPUs: label statistics 46 -> 209 us, sweep +4 % beside a store-based push).
+int gather_ring_launch(void* const* peers, int world, int rank, int64_t n_local, int64_t row0, int64_t n_global, int d,
+                       unsigned present_mask, cudaStream_t st) {
+  if (n_local == 0 || world <= 1) return BSC_OK;
+  GatherPushArgs a{};
+  gather_fill(a, n_local, row0, n_global, d, peers, nullptr, world, rank);
+  const char* own = a.peer[rank];
   const size_t row_bytes = (size_t)d * 2;
-  for (int k = 0; k < world; ++k) {
-    const int dest = (rank + k) % world;
-    char* dst = a.peer[dest];
-    if (k > 0)
-      for (int m = 0; m < 3; ++m)
-        if (x[m]) {
-          const size_t off = a.off_xh[m] + (size_t)row0 * row_bytes;
-          BSC_CUDA(cudaMemcpyAsync(dst + off, own + off, (size_t)n_local * row_bytes, cudaMemcpyDefault, st));
-        }
-    unsigned long long* flag = reinterpret_cast<unsigned long long*>(dst + a.off_flags) + rank;
-    gather_signal_kernel<<<1, 256, 0, st>>>(own, dst, a.off_inv[0], a.off_inv[1], a.off_inv[2], mask, row0, n_local,
-                                            flag, (unsigned long long)epoch);
-    BSC_LAUNCH_CHECK("gather_signal_kernel");
+  for (int k = 1; k < world; ++k) {
+    char* dst = a.peer[(rank + k) % world];
+    for (int m = 0; m < 3; ++m)
+      if ((present_mask >> m) & 1) {
+        const size_t off = a.off_xh[m] + (size_t)row0 * row_bytes;
+        BSC_CUDA(cudaMemcpyAsync(dst + off, own + off, (size_t)n_local * row_bytes, cudaMemcpyDefault, st));
+      }
+    for (int m = 0; m < 3; ++m)
+      if ((present_mask >> m) & 1) {
+        const size_t off = a.off_inv[m] + (size_t)row0 * 4;
+        BSC_CUDA(cudaMemcpyAsync(dst + off, own + off, (size_t)n_local * 4, cudaMemcpyDefault, st));
+      }
+    const size_t foff = a.off_flags + (size_t)rank * 8;
+    BSC_CUDA(cudaMemcpyAsync(dst + foff, own + foff, 8, cudaMemcpyDefault, st));
   }
   return BSC_OK;
 }

@@ -96,14 +96,15 @@ int bsc_rows_to_f16(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, v
  * row0 + l (fp16 row, scale, and the label when `labels` is given) into every rank's buffer.
  *   ordered = 0: all destinations at once (one multimem.st per 16 bytes when multicast_buffer is given); the caller runs a
  *                cross-rank barrier before any rank reads.
- *   ordered = 1: the fused all-gather -> similarity sweep.  The kernel writes the rows into this rank's OWN buffer; the
- *                call then queues, on the same stream, one ring step per destination (rank, rank+1, ...): the copy
- *                engines move the fp16 rows (cudaMemcpyAsync between the peer-mapped buffers, no SM involved), a small
- *                kernel forwards the inverse norms and publishes arrive[source rank] = epoch in the destination's
- *                buffer with release semantics.  A receiver hears from one sender at a time.  epoch = number of ordered
- *                pushes into this buffer so far, this one included (1, 2, ...).  The consumer (bsc_infonce_fwd with
+ *   ordered = 1: the fused all-gather -> similarity sweep.  The call writes the rows into this rank's OWN buffer only
+ *                and then publishes arrive[rank] = epoch there (epoch = number of ordered pushes into this buffer so far,
+ *                this one included: 1, 2, ...).  bsc_gather_ring, queued on a SIDE stream after this call has been
+ *                reached, lets the COPY ENGINES carry rows, inverse norms and finally the flag to rank+1, rank+2, ...
+ *                (cudaMemcpyAsync between the peer-mapped buffers; copies of a stream complete in order, so a peer that
+ *                sees the flag sees the rows; a receiver hears from one sender at a time).  No kernel is involved: the
+ *                persistent sweep may own every register of every SM.  The consumer (bsc_infonce_fwd with
  *                bsc_infonce_exchange.arrive, arrive_target = epoch) waits per source rank and sweeps the sources in
- *                their order of arrival while the later ones are still in flight.  No barrier; call it on a side stream.
+ *                their order of arrival while the later ones are still in flight.  No barrier.
  * The caller must not push into a buffer a peer may still read (alternate two buffers by step; every step contains at
  * least one cross-rank barrier).  All modalities share x_dtype; x[m] = NULL marks an absent modality.
  * Measured on 8 x B200: the gather delivers (W-1)/W of the global batch into every GPU, 132 MB of NVLink ingress =
@@ -117,6 +118,8 @@ int bsc_gather_push_labels(const int64_t* labels, int64_t n_local, int64_t row0,
 int bsc_gather_push(const void* const x[3], int x_dtype, const int64_t ldx[3], const int64_t* labels, int64_t n_local,
                     int64_t row0, int64_t n_global, int d, void* const* peer_buffers, void* multicast_buffer, int world,
                     int rank, int ordered, uint64_t epoch, void* stream);
+int bsc_gather_ring(void* const* peer_buffers, int world, int rank, int64_t n_local, int64_t row0, int64_t n_global,
+                    int d, unsigned present_mask, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * K2  label statistics replacing construct_label_metrix (loss_func.py:18-21): for labels[n]
