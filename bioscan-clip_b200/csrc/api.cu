@@ -123,7 +123,21 @@ static EncodeTiledFn get_encoder() {
   return fn;
 }
 
+// cuTensorMapEncodeTiled is a DRIVER call: it needs the device's primary context bound to the calling thread, which the
+// runtime does lazily.  torch runs the backward of an autograd function on its own worker thread; when every buffer
+// comes out of the caching allocator no runtime call precedes the first tensor map there (CUDA_ERROR_INVALID_CONTEXT,
+// seen in the 8-GPU train step).  One cudaFree(0) per (thread, device) binds it.
+static void bind_context() {
+  static thread_local int bound_dev = -1;
+  const int dev = current_device();
+  if (dev != bound_dev) {
+    cudaFree(nullptr);
+    bound_dev = dev;
+  }
+}
+
 int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, int64_t rows, int64_t cols, int box_rows) {
+  bind_context();
   EncodeTiledFn enc = get_encoder();
   BSC_REQUIRE(enc != nullptr, BSC_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
   BSC_REQUIRE(((uintptr_t)base & 15) == 0, BSC_EINVAL, "TMA operand base must be 16-byte aligned");
@@ -140,6 +154,7 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, int64_t rows, in
 }
 
 int make_tmap_raw128(CUtensorMap* out, const void* base, int64_t rows, int box_rows) {
+  bind_context();
   EncodeTiledFn enc = get_encoder();
   BSC_REQUIRE(enc != nullptr, BSC_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
   BSC_REQUIRE(((uintptr_t)base & 127) == 0 && rows > 0, BSC_EINVAL, "raw TMA operand must be 128-byte aligned");

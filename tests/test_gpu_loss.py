@@ -455,3 +455,27 @@ def test_synthetic_train_step_with_fused_loss():
     ref, _ = loss_oracle.closed_form_grads([o.float().cpu() for o in outs], batch[3].cpu())
     got = crit(*[o.detach().requires_grad_(True) for o in outs], batch[3])
     assert abs(float(got) - float(ref)) <= FP32_TOL * abs(float(ref)) + LOSS_FLOOR
+
+
+def test_backward_on_the_autograd_worker_thread_with_a_warm_allocator():
+    """torch runs the backward on its own worker thread.  When every buffer comes out of the caching allocator, the first
+    CUDA call of that thread is this library's tensor-map encoding (a DRIVER call): the context must be bound by the
+    library itself (CUDA_ERROR_INVALID_CONTEXT in the 8-GPU train step otherwise).  Fresh process, warm allocator."""
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, torch\n"
+        f"sys.path.insert(0, {root!r}); sys.path.insert(0, {os.path.join(root, 'bioscan-clip_b200')!r})\n"
+        "import bsc\n"
+        "warm = torch.empty(1 << 30, dtype=torch.uint8, device='cuda'); del warm\n"
+        "g = torch.Generator(device='cuda').manual_seed(0)\n"
+        "x = [torch.nn.functional.normalize(torch.randn(512, 768, device='cuda', generator=g), dim=1).bfloat16()"
+        ".requires_grad_(True) for _ in range(3)]\n"
+        "loss = bsc.ContrastiveLoss(None, 1 / 0.07, precision='tc16')(x[0], x[1], x[2], torch.arange(512, device='cuda'))\n"
+        "loss.backward(); torch.cuda.synchronize()\n"
+        "assert all(torch.isfinite(t.grad).all() for t in x)\n"
+        "print('ok', float(loss))\n")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-1500:]

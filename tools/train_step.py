@@ -57,9 +57,23 @@ b.record()
 b.synchronize()
 ms = a.elapsed_time(b) / steps
 fwd_loss_ms = sum(x.elapsed_time(y) for x, y in t_loss) / steps
+# the loss alone (forward + backward) on embeddings of the same shape and dtype as the encoders hand over
+with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+    outs = model(*batch[:3])
+c, d2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+for k in range(2 + steps):
+    if k == 2:
+        c.record()
+    leaves = [o.detach().requires_grad_(True) for o in outs]
+    crit(*leaves, batch[3], *extra).backward()
+d2.record()
+d2.synchronize()
+loss_ms = c.elapsed_time(d2) / steps
 if rank == 0:
     print(json.dumps({"workload": "LoRA ViT-B/16 + BarcodeBERT + BERT-small train step, synthetic, bf16 autocast",
                       "n_gpus": world, "batch_per_gpu": bpg, "global_batch": bpg * world, "ms_per_step": ms,
-                      "samples_per_s": bpg * world / (ms * 1e-3), "loss_forward_ms": fwd_loss_ms, "loss": float(loss)}))
+                      "samples_per_s": bpg * world / (ms * 1e-3), "loss_forward_ms_inside_the_step": fwd_loss_ms,
+                      "loss_fwd_bwd_ms_alone": loss_ms, "loss_share_of_step": loss_ms / ms,
+                      "embedding_dtype": str(outs[0].dtype), "loss": float(loss)}))
 if world > 1:
     dist.destroy_process_group()
