@@ -23,6 +23,7 @@ NORM_TORCH, NORM_SKLEARN = 0, 1
 
 EXPORTS = [
     "bsc_version", "bsc_last_error", "bsc_device_check", "bsc_l2norm_fwd", "bsc_rows_to_f16", "bsc_label_stats", "bsc_label_stats_workspace_bytes",
+    "bsc_label_stats_static",
     "bsc_gather_layout", "bsc_gather_push", "bsc_gather_push_labels", "bsc_gather_ring",
     "bsc_infonce_stats_len", "bsc_infonce_aux_len", "bsc_infonce_loss_scratch_bytes", "bsc_infonce_plan", "bsc_infonce_fwd", "bsc_infonce_loss",
     "bsc_infonce_bwd_partials", "bsc_infonce_bwd_finish", "bsc_bank_search_workspace_bytes", "bsc_bank_search", "bsc_bank_screen_parts", "bsc_bank_screen", "bsc_bank_rescore", "bsc_topk_merge", "bsc_taxonomy_eval",
@@ -75,6 +76,7 @@ def lib():
     L.bsc_label_stats.argtypes = [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                   c_void_p]
     L.bsc_label_stats_workspace_bytes.argtypes = [c_int64, POINTER(c_size_t)]
+    L.bsc_label_stats_static.argtypes = [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
     L.bsc_bank_screen_parts.argtypes = [c_int64, c_int64, c_int, POINTER(c_int)]
     L.bsc_bank_screen.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p]
     L.bsc_bank_rescore.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p, c_int, c_int,

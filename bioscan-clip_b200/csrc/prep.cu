@@ -5,6 +5,8 @@
 
 #include <cooperative_groups.h>
 
+#include <atomic>
+
 namespace bsc {
 
 template <typename T>
@@ -1215,3 +1217,61 @@ int topk_merge_launch(const float* cs, const int64_t* ci, int parts, int64_t nq,
 }
 
 }  // namespace bsc
+
+// ---------------------------------------------------------------------------------------------
+// bsc_label_stats_static: K2 for callers that may not allocate (CUDA graph capture, serving loops, harnesses that
+// forbid cudaMalloc).  Same kernels as bsc_label_stats; the hash table / head / count / minidx scratch lives in ONE
+// file-scope device array of fixed size (every GPU that loads the library holds these 1.25 MiB until exit), so the
+// call takes inputs and outputs only and reaches no cudaMalloc / cudaFree / allocating library routine.
+//
+// g_label_static_scratch is a HOST-SIDE STAND-IN in host code, not a device address: its address on the current
+// device is resolved with cudaGetSymbolAddress once per device (below, in this translation unit) and that pointer is
+// what the kernels receive.
+// ---------------------------------------------------------------------------------------------
+namespace bsc {
+
+constexpr int64_t kLabelStaticMaxN = BSC_LABEL_STATS_STATIC_MAX_N;
+// slots[2 * max n] | head[max n] | count[max n] | minidx[max n], int32 each (label_stats_ws_bytes of the maximum)
+constexpr size_t kLabelStaticBytes = (size_t)(2 * kLabelStaticMaxN + 3 * kLabelStaticMaxN) * 4;
+static_assert((kLabelStaticMaxN & (kLabelStaticMaxN - 1)) == 0 && kLabelStaticMaxN >= 1024,
+              "the table of the maximum size must be exactly 2 * max n slots");
+
+static __device__ __align__(256) unsigned char g_label_static_scratch[kLabelStaticBytes];
+
+// Device address of the array on the CURRENT device (resolved on the first call per device, then cached).
+static int label_static_scratch(char** out) {
+  static std::atomic<char*> cache[128];
+  const int dev = current_device();
+  if (dev >= 0 && dev < 128) {
+    char* p = cache[dev].load(std::memory_order_acquire);
+    if (p) {
+      *out = p;
+      return BSC_OK;
+    }
+  }
+  char* p = nullptr;
+  BSC_CUDA(cudaGetSymbolAddress((void**)&p, g_label_static_scratch));
+  BSC_REQUIRE(p != nullptr, BSC_ECUDA, "bsc_label_stats_static: cudaGetSymbolAddress returned a null address");
+  if (dev >= 0 && dev < 128) cache[dev].store(p, std::memory_order_release);
+  *out = p;
+  return BSC_OK;
+}
+
+}  // namespace bsc
+
+extern "C" int bsc_label_stats_static(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next,
+                                      float* rmax, void* stream) {
+  using namespace bsc;
+  BSC_REQUIRE(labels && r && rep && next && rmax, BSC_EINVAL, "bsc_label_stats_static: null pointer");
+  BSC_REQUIRE(n >= 0, BSC_EINVAL, "bsc_label_stats_static: negative n");
+  BSC_REQUIRE(n <= kLabelStaticMaxN && label_stats_ws_bytes(n) <= kLabelStaticBytes, BSC_EUNSUPPORTED,
+              "bsc_label_stats_static: n = %lld exceeds the static scratch (at most %lld labels per call); use "
+              "bsc_label_stats with a caller-owned workspace",
+              (long long)n, (long long)kLabelStaticMaxN);
+  char* scratch = nullptr;
+  const int rc = label_static_scratch(&scratch);
+  if (rc != BSC_OK) return rc;
+  // label_stats_launch clears what must start empty (table slots, counts, minima, rmax) on `stream` before the
+  // kernels; the array keeps the previous call's contents otherwise.
+  return label_stats_launch(labels, n, r, rep, next, rmax, scratch, (cudaStream_t)stream);
+}

@@ -133,6 +133,20 @@ int bsc_label_stats_workspace_bytes(int64_t n, size_t* bytes);
 int bsc_label_stats(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
                     void* workspace, size_t workspace_bytes, void* stream);
 
+/* bsc_label_stats without a workspace argument and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same kernels and same results as bsc_label_stats; the scratch is a
+ * file-scope __device__ array inside the library (1.25 MiB, held by every GPU that loads the library until exit), its
+ * device address resolved with cudaGetSymbolAddress on the first call per device.  The call reaches no cudaMalloc,
+ * cudaFree or allocating library routine.
+ *   limit: n <= BSC_LABEL_STATS_STATIC_MAX_N, larger n -> BSC_EUNSUPPORTED (use bsc_label_stats).
+ *   every call on a device shares the one array, which keeps the previous call's contents; the call itself clears what
+ *   must start empty, on `stream`.  Calls that overlap on the GPU (different streams, no ordering between them) RACE:
+ *   serialise them. */
+#define BSC_LABEL_STATS_STATIC_MAX_N 65536
+int bsc_label_stats_static(const int64_t* labels, int64_t n, float* r, int32_t* rep, int32_t* next, float* rmax,
+                           void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * InfoNCE loss -- ContrastiveLoss.forward / ClipLoss.forward.
  *
