@@ -15,14 +15,15 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("BSC_LIB_PATH") or os.path.join(_HERE, "libbsc_hot.so")  # override: A/B of two builds
 
 BSC_F32, BSC_BF16, BSC_F16, BSC_F64 = 0, 1, 2, 3
-MODE_F32, MODE_TC16 = 0, 1
+MODE_F32, MODE_TC16, MODE_TC16X3 = 0, 1, 2
+TC_MODES = (MODE_TC16, MODE_TC16X3)
 BWD_AUTO, BWD_RECOMPUTE, BWD_BLOCKS, BWD_SCATTER = -1, 0, 3, 4
 BWD_NAMES = {"auto": BWD_AUTO, "recompute": BWD_RECOMPUTE, "blocks": BWD_BLOCKS, "scatter": BWD_SCATTER}
 ABI_VERSION = 200
 NORM_TORCH, NORM_SKLEARN = 0, 1
 
 EXPORTS = [
-    "bsc_version", "bsc_last_error", "bsc_device_check", "bsc_l2norm_fwd", "bsc_rows_to_f16", "bsc_label_stats", "bsc_label_stats_workspace_bytes",
+    "bsc_version", "bsc_last_error", "bsc_device_check", "bsc_l2norm_fwd", "bsc_rows_to_f16", "bsc_rows_to_f16x3", "bsc_label_stats", "bsc_label_stats_workspace_bytes",
     "bsc_label_stats_static",
     "bsc_gather_layout", "bsc_gather_push", "bsc_gather_push_labels", "bsc_gather_ring",
     "bsc_infonce_stats_len", "bsc_infonce_aux_len", "bsc_infonce_loss_scratch_bytes", "bsc_infonce_plan", "bsc_infonce_fwd", "bsc_infonce_loss",
@@ -73,6 +74,7 @@ def lib():
     L.bsc_l2norm_fwd.argtypes = [c_void_p, c_int, c_int64, c_int, c_int64, c_void_p, c_int, c_void_p, c_void_p,
                                  c_int, c_void_p]
     L.bsc_rows_to_f16.argtypes = [c_void_p, c_int, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p]
+    L.bsc_rows_to_f16x3.argtypes = [c_void_p, c_int, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p]
     L.bsc_label_stats.argtypes = [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                   c_void_p]
     L.bsc_label_stats_workspace_bytes.argtypes = [c_int64, POINTER(c_size_t)]

@@ -22,7 +22,7 @@ from typing import List, Optional, Sequence
 import torch
 import torch.nn as nn
 
-from ._lib import MODE_F32, MODE_TC16
+from ._lib import MODE_F32, MODE_TC16, MODE_TC16X3, TC_MODES
 from .ops import Problem, requested_bwd_mode
 
 TOO_FEW = "Too less element for calculating the contrastive loss."  # loss_func.py:35,142
@@ -332,23 +332,33 @@ class SymmMemComm(TorchDistComm):
             self._ex_handle.barrier(channel=1)
 
 
-def resolve_mode(precision: str, feats: Sequence[torch.Tensor]) -> int:
+X3_MIN_ROWS = 2048  # 'auto' with float32 inputs: batches from this size on take the split-operand tensor-core mode
+
+
+def resolve_mode(precision: str, feats: Sequence[torch.Tensor], n_global: Optional[int] = None) -> int:
+    """'fp32'   SIMT float32 tiles (BSC_MODE_F32): the small-batch checker, any width;
+    'fp32x3' float32-grade arithmetic on the tensor cores (BSC_MODE_TC16X3: hi + lo fp16 parts, three MMA terms);
+    'tc16'   the 16-bit throughput mode (BSC_MODE_TC16);
+    'auto'   the reference computes in the input dtype: float32 inputs take a float32-grade mode ('fp32x3' from
+             X3_MIN_ROWS rows of the global batch on, 'fp32' below), 16-bit inputs 'tc16'; widths the tensor-core
+             kernels do not tile take 'fp32'."""
     d = feats[0].shape[1]
     if precision == "fp32":
         return MODE_F32
-    if precision in ("tc16", "bf16", "fp16"):
+    if precision in ("tc16", "bf16", "fp16", "fp32x3"):
         if d % 128 != 0:
             from ._lib import BscError
 
-            raise BscError(f"the tensor-core mode needs an embedding dimension that is a multiple of 128 (got {d}); "
+            raise BscError(f"the tensor-core modes need an embedding dimension that is a multiple of 128 (got {d}); "
                            "use precision='fp32' (BSC_MODE_F32) or 'auto'")
-        return MODE_TC16
+        return MODE_TC16X3 if precision == "fp32x3" else MODE_TC16
     if precision != "auto":
-        raise ValueError(f"precision must be 'auto', 'fp32' or 'tc16' (got {precision!r})")
-    # auto: the reference computes in the input dtype -> fp32 inputs take the exact path; so do widths the
-    # tensor-core kernels do not tile
-    if all(f.dtype == torch.float32 for f in feats) or d % 128 != 0:
+        raise ValueError(f"precision must be 'auto', 'fp32', 'fp32x3' or 'tc16' (got {precision!r})")
+    if d % 128 != 0:
         return MODE_F32
+    if all(f.dtype == torch.float32 for f in feats):
+        rows = n_global if n_global is not None else feats[0].shape[0]
+        return MODE_TC16X3 if rows >= X3_MIN_ROWS else MODE_F32
     return MODE_TC16
 
 
@@ -371,6 +381,18 @@ def infonce_forward(ops, comm, feats: List[Optional[torch.Tensor]], labels: torc
     _mark("start")
     if mode == MODE_F32:
         xh = [None if f is None else comm.all_gather_rows(ops.normalize(f.detach(), torch.float32)) for f in feats]
+    elif mode == MODE_TC16X3:
+        # float32-grade tensor-core mode: hi | lo fp16 parts of every row and the float32 inverse norms, gathered with
+        # plain collectives (the fused NVLink gather carries BSC_MODE_TC16 rows only)
+        xh, inv = [], []
+        for f in feats:
+            if f is None:
+                xh.append(None)
+                inv.append(None)
+                continue
+            hl, iv = ops.rows_to_f16x3(f.detach())
+            xh.append(comm.all_gather_rows(hl))
+            inv.append(comm.all_gather_rows(iv))
     else:
         # tensor-core mode: the MMA operands are the caller's values times an exact per-row power of two, held in
         # float16 (exact for bf16 / fp16 inputs; float32 inputs are rounded once to 11 bits).  Normalised rows are
@@ -429,7 +451,7 @@ def infonce_backward(ops, comm, saved, feats, grad_out: torch.Tensor, grad_gain:
     xs = [None if f is None else f.detach() for f in feats]
     dev = next(x for x in xs if x is not None).device
     own, ptrs = (None, None)
-    if prob.mode == MODE_TC16 and prob.bwd_mode == BWD_SCATTER:
+    if prob.mode in TC_MODES and prob.bwd_mode == BWD_SCATTER:
         own, ptrs = comm.exchange(prob.exchange_bytes, dev)
     _mark("bwd_start")
     ops.infonce_bwd_partials(prob, aux, ptrs)
@@ -503,6 +525,7 @@ class ContrastiveLoss(nn.Module):
     """Single-process multi-modal InfoNCE with multi-positive labels (loss_func.py:23-54)."""
 
     def __init__(self, criterion=None, logit_scale=1 / 0.07, precision: str = "auto", backward: str = "auto"):
+        # precision: 'auto' | 'fp32' | 'fp32x3' | 'tc16' (resolve_mode)
         super().__init__()
         _check_criterion(criterion)
         self.criterion = criterion
@@ -573,7 +596,7 @@ class ClipLoss(nn.Module):
         if self._comm is None:
             self._comm = self._make_comm(present[0].device) if self.world_size > 1 else LocalComm()
         comm = self._comm
-        mode = resolve_mode(self.precision, present)
+        mode = resolve_mode(self.precision, present, present[0].shape[0] * max(int(self.world_size), 1))
         gain = float(self.world_size) if (self.gather_with_grad and self.world_size > 1) else 1.0
         total = _InfoNCEFn.apply(self._ops, comm, _plain_scale(logit_scale), mode, gain,
                                  requested_bwd_mode(self.backward_mode), labels, *feats)

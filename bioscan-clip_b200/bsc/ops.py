@@ -15,7 +15,7 @@ from typing import List, Optional
 import torch
 
 from . import _lib
-from ._lib import MODE_F32, MODE_TC16, NORM_SKLEARN, NORM_TORCH, InfoNceDesc, check, lib, ptr, stream_ptr
+from ._lib import MODE_F32, MODE_TC16, TC_MODES, NORM_SKLEARN, NORM_TORCH, InfoNceDesc, check, lib, ptr, stream_ptr
 
 
 @dataclass
@@ -23,6 +23,7 @@ class Problem:
     """One InfoNCE evaluation: the gathered, normalised global batch and this rank's row range."""
     # 3 entries or None: F32 mode -> [n_global, d] float32 L2-normalised rows;
     # TC16 mode -> [n_global, d] float16 rows (the caller's values times a power of two) plus their inverse norms in ``inv``
+    # TC16X3 mode -> [n_global, 2 d] float16 rows (hi | lo parts) plus ``inv``; ``d`` stays the embedding width
     xh: List[Optional[torch.Tensor]]
     n_global: int
     n_local: int
@@ -124,6 +125,20 @@ class CudaOps:
                                         inv.data_ptr(), stream_ptr(x.device)))
         return y, inv
 
+    def rows_to_f16x3(self, x: torch.Tensor):
+        """BSC_MODE_TC16X3 operands: ([n, 2 d] float16 = hi | lo parts of x * 2^k_row, 2^-k_row / max(||x_row||, 1e-12))."""
+        _lib.require_device(x.device)
+        assert x.dim() == 2
+        if x.stride(1) != 1:
+            x = x.contiguous()
+        n, d = x.shape
+        hl = torch.empty((n, 2 * d), dtype=torch.float16, device=x.device)
+        inv = torch.empty(n, dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            check(lib().bsc_rows_to_f16x3(x.data_ptr(), _lib.dtype_code(x.dtype), n, d, x.stride(0), hl.data_ptr(),
+                                          inv.data_ptr(), stream_ptr(x.device)))
+        return hl, inv
+
     # ---- K2 -------------------------------------------------------------------------------------
     def label_stats(self, labels: torch.Tensor):
         _lib.require_device(labels.device)
@@ -149,7 +164,7 @@ class CudaOps:
             d.n_global, d.n_local, d.row0 = p.n_global, p.n_local, p.row0
             d.d, d.mode, d.logit_scale = p.d, p.mode, float(p.scale)
             first = next(t for t in p.xh if t is not None)
-            d.x16_dtype = _lib.dtype_code(first.dtype) if p.mode == MODE_TC16 else 0
+            d.x16_dtype = _lib.dtype_code(first.dtype) if p.mode in TC_MODES else 0
             for m in range(3):
                 d.xh[m] = ptr(p.xh[m]) or None
                 d.inv[m] = (ptr(p.inv[m]) if p.inv is not None else 0) or None
@@ -177,7 +192,7 @@ class CudaOps:
         if hit is None:
             out = _lib.InfoNcePlan()
             p._desc = None
-            budget = memory_budget(dev) if (requested == _lib.BWD_AUTO and p.mode == MODE_TC16) else 0
+            budget = memory_budget(dev) if (requested == _lib.BWD_AUTO and p.mode in TC_MODES) else 0
             check(lib().bsc_infonce_plan(byref(self._desc(p)), requested, 1 if peer_memory else 0, budget, byref(out)))
             hit = (int(out.bwd_mode), int(out.fwd_workspace_bytes), int(out.bwd_workspace_bytes),
                    int(out.exchange_bytes))
@@ -240,7 +255,7 @@ class CudaOps:
         if p.bwd_workspace is None:
             p.bwd_workspace = torch.empty(max(p.bwd_workspace_bytes, 256), dtype=torch.uint8, device=dev)
         ex = None
-        if p.mode == MODE_TC16 and p.bwd_mode == _lib.BWD_SCATTER:
+        if p.mode in TC_MODES and p.bwd_mode == _lib.BWD_SCATTER:
             if exchange_ptrs is None or len(exchange_ptrs) != p.world:
                 raise _lib.BscError("the scatter backward needs one exchange buffer address per rank")
             ex = (c_void_p * p.world)(*exchange_ptrs)

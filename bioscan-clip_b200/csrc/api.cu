@@ -13,6 +13,8 @@ int l2norm_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, voi
                   float* inv_norm, int zero_rule, cudaStream_t st);
 int rows_to_f16_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, float* inv,
                        cudaStream_t st);
+int rows_to_f16x3_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* hl, float* inv,
+                         cudaStream_t st);
 size_t label_stats_ws_bytes(int64_t n);
 int tc_bank_screen_parts(int64_t nq, int64_t nb, int min_parts);
 int tc_bank_screen(const void* q, int64_t nq, const void* bank, int64_t nb, int d, int64_t base_id, int min_parts,
@@ -137,13 +139,20 @@ static void bind_context() {
 }
 
 int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, int64_t rows, int64_t cols, int box_rows) {
+  return make_tmap_2d_ld(out, base, dtype, rows, cols, cols, box_rows);
+}
+
+// [rows][cols] 16-bit elements with a row stride of ld elements (a column slice of a wider matrix), box {64, box_rows}
+int make_tmap_2d_ld(CUtensorMap* out, const void* base, int dtype, int64_t rows, int64_t cols, int64_t ld,
+                    int box_rows) {
   bind_context();
   EncodeTiledFn enc = get_encoder();
   BSC_REQUIRE(enc != nullptr, BSC_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
   BSC_REQUIRE(((uintptr_t)base & 15) == 0, BSC_EINVAL, "TMA operand base must be 16-byte aligned");
-  BSC_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0, BSC_EINVAL, "TMA operand needs rows > 0 and cols %% 8 == 0");
+  BSC_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && ld >= cols && ld % 8 == 0, BSC_EINVAL,
+              "TMA operand needs rows > 0, cols %% 8 == 0 and a row stride that is a multiple of 8 elements");
   cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t gstride[1] = {(cuuint64_t)cols * 2};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
   cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1u, 1u};
   CUtensorMapDataType dt = dtype == BSC_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
@@ -193,7 +202,7 @@ InfoNceFwdWs infonce_fwd_layout(const bsc_infonce_desc* p) {
   const int64_t N = p->n_global, n = p->n_local;
   const int m = present_count(p, nullptr);
   const int n_pairs = m * (m - 1) / 2;
-  if (p->mode == BSC_MODE_TC16) {
+  if (mode_is_tc(p->mode)) {
     tc_fwd_tiling(n, N, n_pairs, p->world, &L.n_iblk, &L.n_jtile, &L.jtiles_per_chunk, &L.n_jchunk);
   } else {
     L.n_iblk = (int)((n + kSimtT - 1) / kSimtT);
@@ -217,7 +226,7 @@ InfoNceFwdWs infonce_fwd_layout(const bsc_infonce_desc* p) {
 static int bwd_local_slots(const bsc_infonce_desc* p) {
   const int m = present_count(p, nullptr);
   // SCATTER: one K-major job per present pair; the others address slabs as (modality * 2 + partner slot), modality 0..2
-  return (p->mode == BSC_MODE_TC16 && p->bwd_mode == BSC_BWD_SCATTER) ? m * (m - 1) / 2 : 6;
+  return (mode_is_tc(p->mode) && p->bwd_mode == BSC_BWD_SCATTER) ? m * (m - 1) / 2 : 6;
 }
 
 InfoNceBwdWs infonce_bwd_layout(const bsc_infonce_desc* p) {
@@ -226,18 +235,18 @@ InfoNceBwdWs infonce_bwd_layout(const bsc_infonce_desc* p) {
   const int D = p->d;
   const int m = present_count(p, nullptr);
   const int n_pairs = m * (m - 1) / 2;
-  L.mode = p->mode == BSC_MODE_TC16 ? p->bwd_mode : BSC_BWD_RECOMPUTE;
-  const bool stored = p->mode == BSC_MODE_TC16 && (L.mode == BSC_BWD_BLOCKS || L.mode == BSC_BWD_SCATTER);
-  if (p->mode == BSC_MODE_TC16)
+  L.mode = mode_is_tc(p->mode) ? p->bwd_mode : BSC_BWD_RECOMPUTE;
+  const bool stored = mode_is_tc(p->mode) && (L.mode == BSC_BWD_BLOCKS || L.mode == BSC_BWD_SCATTER);
+  if (mode_is_tc(p->mode))
     tc_fwd_tiling(n, N, n_pairs, p->world, &L.n_iblk, &L.n_jtile, &L.jtiles_per_chunk, &L.n_jchunk);
   L.g_rows = n < 2048 ? (n > 0 ? n : 1) : 2048;
   L.kparts = 1;
-  if (p->mode == BSC_MODE_TC16) L.kparts = stored ? tc_bwd_gemm_kparts(p) : tc_bwd_duo_jsplit(p);
+  if (mode_is_tc(p->mode)) L.kparts = stored ? tc_bwd_gemm_kparts(p) : tc_bwd_duo_jsplit(p);
   size_t off = 0;
   L.jrange = take(off, (size_t)((N + kTcBNF - 1) / kTcBNF + 1) * 2 * sizeof(int));
   L.dxraw = take(off, (size_t)bwd_local_slots(p) * L.kparts * (n > 0 ? n : 1) * D * sizeof(float));
   if (stored) {
-    L.xunit = take(off, (size_t)3 * (n > 0 ? n : 1) * D * 2);
+    L.xunit = take(off, (size_t)3 * (n > 0 ? n : 1) * D * 2 * mode_parts(p->mode));
     L.gimg = take(off, tc_bwd_gimg_bytes(p));
   } else {
     L.xunit = L.gimg = off;
@@ -248,7 +257,7 @@ InfoNceBwdWs infonce_bwd_layout(const bsc_infonce_desc* p) {
 }
 
 static size_t exchange_bytes_of(const bsc_infonce_desc* p) {
-  if (p->mode != BSC_MODE_TC16 || p->bwd_mode != BSC_BWD_SCATTER) return 0;
+  if (!mode_is_tc(p->mode) || p->bwd_mode != BSC_BWD_SCATTER) return 0;
   const int m = present_count(p, nullptr);
   return (size_t)p->world * (size_t)(m * (m - 1) / 2) * (size_t)(p->n_local > 0 ? p->n_local : 1) * p->d *
          sizeof(float);
@@ -256,7 +265,7 @@ static size_t exchange_bytes_of(const bsc_infonce_desc* p) {
 
 static int check_desc(const bsc_infonce_desc* p, const char* who) {
   BSC_REQUIRE(p != nullptr, BSC_EINVAL, "%s: null descriptor", who);
-  BSC_REQUIRE(p->mode == BSC_MODE_F32 || p->mode == BSC_MODE_TC16, BSC_EINVAL, "%s: unknown mode %d", who, p->mode);
+  BSC_REQUIRE(p->mode == BSC_MODE_F32 || mode_is_tc(p->mode), BSC_EINVAL, "%s: unknown mode %d", who, p->mode);
   BSC_REQUIRE(p->n_global >= 1 && p->n_local >= 0 && p->row0 >= 0 && p->row0 + p->n_local <= p->n_global, BSC_EINVAL,
               "%s: bad row partition (n_global=%lld n_local=%lld row0=%lld)", who, (long long)p->n_global,
               (long long)p->n_local, (long long)p->row0);
@@ -266,9 +275,9 @@ static int check_desc(const bsc_infonce_desc* p, const char* who) {
   BSC_REQUIRE(p->r && p->rep && p->next && p->rmax, BSC_EINVAL, "%s: label statistics pointers are null", who);
   BSC_REQUIRE(p->world >= 1 && p->world <= kMaxPeers && p->rank >= 0 && p->rank < p->world, BSC_EINVAL,
               "%s: bad rank %d / world %d (1..%d ranks)", who, p->rank, p->world, kMaxPeers);
-  if (p->mode == BSC_MODE_TC16) {
-    BSC_REQUIRE(p->d % 128 == 0, BSC_EUNSUPPORTED, "%s: TC16 mode needs d %% 128 == 0 (got %d); use BSC_MODE_F32", who,
-                p->d);
+  if (mode_is_tc(p->mode)) {
+    BSC_REQUIRE(p->d % 128 == 0, BSC_EUNSUPPORTED,
+                "%s: the tensor-core modes need d %% 128 == 0 (got %d); use BSC_MODE_F32", who, p->d);
     BSC_REQUIRE(p->x16_dtype == BSC_F16, BSC_EUNSUPPORTED,
                 "%s: TC16 mode takes float16 rows prepared by bsc_rows_to_f16 (exact for bfloat16 values); "
                 "tcgen05 kind::f16 cannot mix the fp16 weight tile with bfloat16 rows (x16_dtype=%d)",
@@ -335,6 +344,13 @@ int bsc_rows_to_f16(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, v
   BSC_REQUIRE(n >= 0 && d >= 1 && ldx >= d, BSC_EINVAL, "bsc_rows_to_f16: bad shape n=%lld d=%d ldx=%lld", (long long)n,
               d, (long long)ldx);
   return rows_to_f16_launch(x, x_dtype, n, d, ldx, y16, inv, (cudaStream_t)stream);
+}
+
+int bsc_rows_to_f16x3(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* hl, float* inv, void* stream) {
+  BSC_REQUIRE((x && hl && inv) || n == 0, BSC_EINVAL, "bsc_rows_to_f16x3: null pointer");
+  BSC_REQUIRE(n >= 0 && d >= 1 && ldx >= d, BSC_EINVAL, "bsc_rows_to_f16x3: bad shape n=%lld d=%d ldx=%lld",
+              (long long)n, d, (long long)ldx);
+  return rows_to_f16x3_launch(x, x_dtype, n, d, ldx, hl, inv, (cudaStream_t)stream);
 }
 
 int bsc_gather_layout(int64_t n_global, int d, int world, size_t off_xh[3], size_t off_inv[3], size_t* off_labels,
@@ -432,6 +448,8 @@ static int bwd_mode_ok(const bsc_infonce_desc* p, int mode, int peer_memory, con
   }
   switch (mode) {
     case BSC_BWD_RECOMPUTE:
+      BSC_REQUIRE(p->mode != BSC_MODE_TC16X3, BSC_EUNSUPPORTED,
+                  "%s: BSC_MODE_TC16X3 runs the stored-weight backwards only (BSC_BWD_BLOCKS / BSC_BWD_SCATTER)", who);
       BSC_REQUIRE(tc_bwd_duo_covers(p), BSC_EUNSUPPORTED,
                   "%s: the recomputing sweep covers d in {256, 512, 768} only (got %d)", who, p->d);
       return BSC_OK;
@@ -491,8 +509,10 @@ int bsc_infonce_fwd(const bsc_infonce_desc* p, float* stats, const bsc_infonce_e
   BSC_REQUIRE(workspace_bytes >= L.total, BSC_EWORKSPACE, "bsc_infonce_fwd: workspace %zu < %zu", workspace_bytes,
               L.total);
   if (ex != nullptr) {
-    BSC_REQUIRE(p->mode == BSC_MODE_TC16 || (!ex->arrive && !ex->stats_peers && !ex->stats_multicast), BSC_EUNSUPPORTED,
-                "bsc_infonce_fwd: the peer-memory exchange is implemented for BSC_MODE_TC16");
+    BSC_REQUIRE(mode_is_tc(p->mode) || (!ex->arrive && !ex->stats_peers && !ex->stats_multicast), BSC_EUNSUPPORTED,
+                "bsc_infonce_fwd: the peer-memory exchange is implemented for the tensor-core modes");
+    BSC_REQUIRE(p->mode != BSC_MODE_TC16X3 || !ex->arrive, BSC_EUNSUPPORTED,
+                "bsc_infonce_fwd: the fused all-gather (arrival counters) carries BSC_MODE_TC16 rows only");
     if (ex->stats_peers)
       for (int r = 0; r < p->world; ++r)
         BSC_REQUIRE(ex->stats_peers[r] != nullptr, BSC_EINVAL, "bsc_infonce_fwd: stats area of rank %d is null", r);
@@ -524,9 +544,9 @@ int bsc_infonce_loss(const bsc_infonce_desc* p, const float* records, int n_reco
   a.record_len = stats_record_len(p->n_global);
   a.r = p->r;
   a.rmax = p->rmax;
-  for (int m = 0; m < 3; ++m) a.inv[m] = p->mode == BSC_MODE_TC16 ? p->inv[m] : nullptr;
+  for (int m = 0; m < 3; ++m) a.inv[m] = mode_is_tc(p->mode) ? p->inv[m] : nullptr;
   a.present_mask = mask;
-  a.use_gs = p->mode == BSC_MODE_TC16 ? 1 : 0;
+  a.use_gs = mode_is_tc(p->mode) ? 1 : 0;
   a.stats = stats;
   a.uv = aux;
   a.gsbuf = aux + 6 * p->n_global;
@@ -584,7 +604,7 @@ int bsc_infonce_bwd_finish(const bsc_infonce_desc* p, const float* aux, const vo
                 "bsc_infonce_bwd_finish: x/grad pointer missing for modality %d", a);
     BSC_REQUIRE(!p->xh[a] || ldx[a] >= p->d, BSC_EINVAL, "bsc_infonce_bwd_finish: ldx[%d] < d", a);
   }
-  const bool scatter = p->mode == BSC_MODE_TC16 && L.mode == BSC_BWD_SCATTER;
+  const bool scatter = mode_is_tc(p->mode) && L.mode == BSC_BWD_SCATTER;
   BSC_REQUIRE(!scatter || own_exchange, BSC_EINVAL, "bsc_infonce_bwd_finish: BSC_BWD_SCATTER needs own_exchange");
   if (p->n_local == 0) return BSC_OK;
   char* ws = (char*)workspace;

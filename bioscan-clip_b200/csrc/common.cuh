@@ -54,6 +54,20 @@ __host__ __device__ inline int64_t stats_pos_offset(int64_t n) { return (6 * n +
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// tensor-core modes: BSC_MODE_TC16 (one fp16 part per row) and BSC_MODE_TC16X3 (hi + lo parts, three MMA terms)
+inline bool mode_is_tc(int mode) { return mode == BSC_MODE_TC16 || mode == BSC_MODE_TC16X3; }
+inline int mode_terms(int mode) { return mode == BSC_MODE_TC16X3 ? 3 : 1; }
+inline int mode_parts(int mode) { return mode == BSC_MODE_TC16X3 ? 2 : 1; }  // fp16 parts stored per value
+// tcgen05.mma accumulates TOWARD ZERO: every instruction (K = 16) truncates the fp32 accumulator, so a dot product whose
+// partial sums grow steadily comes out too small by a data-independent share -- measured on B200 (tools/acc_probe.py,
+// profiles/r2_acc_probe.log: always negative, 0.19-0.31 ulp per instruction with bf16 operands; 0.48 ulp per
+// instruction of the hi*hi term with the fp16 parts of BSC_MODE_TC16X3, where it showed as a 2.7e-6 bias of every
+// cosine at d = 768, i.e. 3e-5 of a peaked-softmax loss).  BSC_MODE_TC16X3 multiplies the similarities by the inverse
+// of the expected shrinkage (first-order compensation; the spread around it, ~1e-7, stays).
+constexpr double kX3AccUlpPerStep = 0.48;
+inline double x3_accumulator_gain(int d) { return 1.0 + kX3AccUlpPerStep * (d / 16) * 1.1920928955078125e-7; }
+constexpr float kX3UnitScale = 256.0f;  // BSC_MODE_TC16X3: the unit rows of the MN-major GEMMs are stored times 2^8
+
 // ---- workspace layouts of the infonce calls -----------------------------------------------------
 // Forward and backward own separate caller-allocated workspaces (bsc_infonce_plan reports both sizes): the forward
 // of an evaluation-only call never pays for the backward's buffers.
@@ -154,6 +168,9 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, con
                  const int* pairs_a, const int* pairs_b, const ScatterDst& dst, cudaStream_t st);
 int rows_unit_f16_launch3(const void* const x16[3], const float* const inv[3], int64_t row0, int64_t n, int d,
                           void* const out[3], cudaStream_t st);
+// BSC_MODE_TC16X3: hl16[m] = [rows][2 d] (hi | lo); out[m] = [n][2 d] (hi | lo) of kX3UnitScale * unit rows
+int rows_unit_f16x3_launch3(const void* const hl16[3], const float* const inv[3], int64_t row0, int64_t n, int d,
+                            void* const out[3], cudaStream_t st);
 struct ReduceJob {
   const float* part;
   int nparts;

@@ -131,6 +131,71 @@ int rows_to_f16_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx
   return BSC_OK;
 }
 
+// BSC_MODE_TC16X3 operand preparation: hl[i] = [hi | lo] (2 d fp16) with hi = fp16(x 2^k), lo = fp16(x 2^k - hi), i.e.
+// hi + lo carries 22 significant bits of every element; the row maximum lands in [128, 256) -- fp16 keeps the lo part
+// (about 2^-12 of the element) a NORMAL number for every element down to 2^-10 of the row maximum, and products of
+// two scaled rows (< 2^16 each, 2^26 per row) are far inside fp32.  inv[i] = 2^-k / max(||x_i||, 1e-12) as in TC16.
+constexpr int kX3RowExp = 7;
+
+template <typename TI>
+__global__ void __launch_bounds__(256) rows_to_f16x3_kernel(const TI* __restrict__ x, int64_t n, int d, int64_t ldx,
+                                                            __half* __restrict__ hl, float* __restrict__ inv) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= n) return;
+  const TI* xr = x + row * ldx;
+  float amax = 0.f;
+  for (int c = lane; c < d; c += 32) amax = fmaxf(amax, fabsf(to_f32<TI>(xr[c])));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+  int k = 0;
+  if (amax > 0.f && amax < 3.0e38f) k = kX3RowExp - ilogbf(amax);
+  k = max(-120, min(120, k));
+  const float scale = exp2f((float)k);
+  // norm of the SCALED row (never overflows or flushes), sum of squares in double: the inverse norm multiplies every
+  // logit of the row, so its rounding is a systematic error of that row
+  double s2 = 0.0;
+  for (int c = lane; c < d; c += 32) {
+    const double v = (double)(to_f32<TI>(xr[c]) * scale);
+    s2 = fma(v, v, s2);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+  const double n2 = sqrt(s2);                             // ||x|| * 2^k
+  const double true_nrm = n2 * exp2((double)-k);
+  const float inv_row = n2 > 0.0 ? (float)(true_nrm >= 1e-12 ? 1.0 / n2 : exp2((double)-k) * 1e12) : 0.f;
+  if (lane == 0) inv[row] = inv_row;
+  __half* out = hl + row * (int64_t)(2 * d);
+  for (int c = lane; c < d; c += 32) {
+    const float v = to_f32<TI>(xr[c]) * scale;
+    const __half h = __float2half_rn(v);
+    out[c] = h;
+    out[d + c] = __float2half_rn(v - __half2float(h));
+  }
+}
+
+int rows_to_f16x3_launch(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* hl, float* inv,
+                         cudaStream_t st) {
+  if (n == 0) return BSC_OK;
+  dim3 block(256), grid((unsigned)((n + 7) / 8));
+  switch (x_dtype) {
+    case BSC_F32:
+      rows_to_f16x3_kernel<float><<<grid, block, 0, st>>>((const float*)x, n, d, ldx, (__half*)hl, inv);
+      break;
+    case BSC_BF16:
+      rows_to_f16x3_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)x, n, d, ldx, (__half*)hl, inv);
+      break;
+    case BSC_F16:
+      rows_to_f16x3_kernel<__half><<<grid, block, 0, st>>>((const __half*)x, n, d, ldx, (__half*)hl, inv);
+      break;
+    default:
+      set_error("bsc_rows_to_f16x3: unknown x_dtype %d", x_dtype);
+      return BSC_EINVAL;
+  }
+  BSC_LAUNCH_CHECK("rows_to_f16x3_kernel");
+  return BSC_OK;
+}
+
 // fp16 unit rows of rows [row0, row0 + n) from the scaled fp16 rows: out[l] = half(x16[row0 + l] * inv[row0 + l]).
 // B operand of the MN-major gradient GEMMs (tc_bwd3.cu).  blockIdx.y = modality (absent ones have a null source).
 // 8 elements (16 bytes) per thread and pass.
@@ -177,6 +242,56 @@ int rows_unit_f16_launch3(const void* const x16[3], const float* const inv[3], i
   const unsigned gx = (unsigned)((total + 255) / 256 > 148 * 8 ? 148 * 8 : (total + 255) / 256);
   rows_unit_f16_kernel<<<dim3(gx, 3), 256, 0, st>>>(a, row0, n, d / 8);
   BSC_LAUNCH_CHECK("rows_unit_f16_kernel");
+  return BSC_OK;
+}
+
+// BSC_MODE_TC16X3: unit rows of rows [row0, row0 + n) as hi | lo fp16 parts of kX3UnitScale * (hi + lo) * inv, from the
+// [rows][2 d] hi | lo operand rows.  One thread per 8 elements.
+__global__ void __launch_bounds__(256) rows_unit_f16x3_kernel(const UnitRowsArgs a, int64_t row0, int64_t n, int d8) {
+  const uint4* __restrict__ x = a.x[blockIdx.y];
+  if (x == nullptr) return;
+  const float* __restrict__ inv = a.inv[blockIdx.y] + row0;
+  uint4* __restrict__ out = a.out[blockIdx.y];
+  x += row0 * 2 * d8;
+  const int64_t total = n * (int64_t)d8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = i / d8;
+    const int c8 = (int)(i - row * d8);
+    const float s = inv[row] * kX3UnitScale;
+    uint4 vh = x[row * 2 * d8 + c8], vl = x[row * 2 * d8 + d8 + c8];
+    __half2* h = reinterpret_cast<__half2*>(&vh);
+    __half2* l = reinterpret_cast<__half2*>(&vl);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const float2 fh = __half22float2(h[t]), fl = __half22float2(l[t]);
+      const float ux = (fh.x + fl.x) * s, uy = (fh.y + fl.y) * s;  // hi + lo is exact in fp32 (22 bits)
+      const __half2 uh = __floats2half2_rn(ux, uy);
+      const float2 back = __half22float2(uh);
+      h[t] = uh;
+      l[t] = __floats2half2_rn(ux - back.x, uy - back.y);
+    }
+    out[row * 2 * d8 + c8] = vh;
+    out[row * 2 * d8 + d8 + c8] = vl;
+  }
+}
+
+int rows_unit_f16x3_launch3(const void* const hl16[3], const float* const inv[3], int64_t row0, int64_t n, int d,
+                            void* const out[3], cudaStream_t st) {
+  if (n == 0) return BSC_OK;
+  BSC_REQUIRE(d % 8 == 0, BSC_EUNSUPPORTED, "rows_unit_f16x3: d %% 8 != 0");
+  UnitRowsArgs a{};
+  bool any = false;
+  for (int m = 0; m < 3; ++m) {
+    a.x[m] = out[m] ? (const uint4*)hl16[m] : nullptr;
+    a.inv[m] = inv[m];
+    a.out[m] = (uint4*)out[m];
+    any = any || a.x[m] != nullptr;
+  }
+  if (!any) return BSC_OK;
+  const int64_t total = n * (int64_t)(d / 8);
+  const unsigned gx = (unsigned)((total + 255) / 256 > 148 * 8 ? 148 * 8 : (total + 255) / 256);
+  rows_unit_f16x3_kernel<<<dim3(gx, 3), 256, 0, st>>>(a, row0, n, d / 8);
+  BSC_LAUNCH_CHECK("rows_unit_f16x3_kernel");
   return BSC_OK;
 }
 

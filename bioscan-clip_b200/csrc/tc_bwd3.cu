@@ -60,6 +60,12 @@ struct RevParams {
   CUtensorMap tmap_g128;  // gimg as [rows][64] fp16, box 64 x 128, no swizzle (the bytes are already swizzled)
   CUtensorMap tmap_g64;   // same, box 64 x 64: half an image (MN-major jobs)
   CUtensorMap tmap_in[MAX_JOBS];  // B operand rows of every job, box 64 d x 64 rows, SWIZZLE_128B
+  CUtensorMap tmap_in_lo[MAX_JOBS];  // BSC_MODE_TC16X3: the lo parts of the same rows
+  // terms = 1: out = G * in.  terms = 3 (BSC_MODE_TC16X3): G = Ghi + Glo (two image sets, the lo set lo_img0 images after
+  // the hi set), in = hi + lo; every item runs its K range three times into the SAME accumulator, small terms first:
+  //   Glo * in_hi,  Ghi * in_lo,  Ghi * in_hi
+  int terms;
+  int64_t lo_img0;
   // job = one gradient GEMM  out[M rows][d] = A[M][K] * in[K][d];  image(pair, r, c) = (pair * img_r + r) * img_c + c
   //   K-major job:  A block (128 rows mblk, 64 K kb)  = image(pair, mblk, kb)
   //   MN-major job: A block (128 rows mblk, 64 K kb)  = rows 64 (kb & 1) .. + 63 of images (pair, kb >> 1, 2 mblk + {0, 1})
@@ -70,6 +76,7 @@ struct RevParams {
   int job_xslot[MAX_JOBS];         // scattered jobs: pair slot inside the exchange buffers
   int job_fnum[MAX_JOBS], job_fden[MAX_JOBS];  // epilogue row factor gsbuf[fnum] * gsbuf[fden] ...
   const float* job_finv[MAX_JOBS];             // ... / finv[row] when not null
+  float job_fmul[MAX_JOBS];                    // ... times a constant (undoes the 2^8 of the X3 unit rows)
   int img_r, img_c;
   int num_items, d, n_clusters;
   // scatter destinations: exchange buffer of rank q = float [world][n_xslots][n_local][d]
@@ -164,28 +171,32 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
         const bool mn = p.job_mn[job] != 0;
         const int d0 = BN * c + 128 * (int)crank;       // this CTA's half of the N = 256 accumulator
         const int d1 = BN * c + 256 + 64 * (int)crank;  // ... and of the N = 128 accumulator (WIDE)
-        for (int kb = kb_lo; kb < kb_hi; ++kb) {
-          ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 100 + stage);
-          const uint32_t full = ptx::smem_u32(&tail->full[stage]);
-          const uint32_t full_l = ptx::mapa(full, 0);
-          const uint32_t sa = ring + stage * STAGE_BYTES;
-          if (crank == 0) ptx::mbar_arrive_expect_tx(full, 2 * STAGE_BYTES);
-          if (!mn) {
-            const int64_t img = (pair0 + mblk) * p.img_c + kb;
-            ptx::tma_load_2d_2cta(sa, &p.tmap_g128, full_l, 0, (int32_t)(img * 128));
-          } else {
-            const int64_t img = (pair0 + (kb >> 1)) * p.img_c + 2 * mblk;
-            const int32_t r0 = (int32_t)(img * 128) + 64 * (kb & 1);
-            ptx::tma_load_2d_2cta(sa, &p.tmap_g64, full_l, 0, r0);
-            ptx::tma_load_2d_2cta(sa + A_BYTES / 2, &p.tmap_g64, full_l, 0, r0 + 128);
-          }
-          // columns past d (d % 256 == 128 leaves the odd CTA's half of the last chunk empty) are zero-filled by TMA
-          ptx::tma_load_2d_2cta(sa + A_BYTES, mu, full_l, d0, kb * BK);
-          ptx::tma_load_2d_2cta(sa + A_BYTES + B_BOX, mu, full_l, d0 + 64, kb * BK);
-          if (WIDE) ptx::tma_load_2d_2cta(sa + A_BYTES + 2 * B_BOX, mu, full_l, d1, kb * BK);
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1u;
+        for (int term = 0; term < p.terms; ++term) {
+          if (p.terms == 3) mu = term == 1 ? &p.tmap_in_lo[job] : &p.tmap_in[job];
+          const int64_t set0 = (p.terms == 3 && term == 0) ? p.lo_img0 : 0;  // first image of the set this term reads
+          for (int kb = kb_lo; kb < kb_hi; ++kb) {
+            ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 100 + stage);
+            const uint32_t full = ptx::smem_u32(&tail->full[stage]);
+            const uint32_t full_l = ptx::mapa(full, 0);
+            const uint32_t sa = ring + stage * STAGE_BYTES;
+            if (crank == 0) ptx::mbar_arrive_expect_tx(full, 2 * STAGE_BYTES);
+            if (!mn) {
+              const int64_t img = set0 + (pair0 + mblk) * p.img_c + kb;
+              ptx::tma_load_2d_2cta(sa, &p.tmap_g128, full_l, 0, (int32_t)(img * 128));
+            } else {
+              const int64_t img = set0 + (pair0 + (kb >> 1)) * p.img_c + 2 * mblk;
+              const int32_t r0 = (int32_t)(img * 128) + 64 * (kb & 1);
+              ptx::tma_load_2d_2cta(sa, &p.tmap_g64, full_l, 0, r0);
+              ptx::tma_load_2d_2cta(sa + A_BYTES / 2, &p.tmap_g64, full_l, 0, r0 + 128);
+            }
+            // columns past d (d % 256 == 128 leaves the odd CTA's half of the last chunk empty) are zero-filled by TMA
+            ptx::tma_load_2d_2cta(sa + A_BYTES, mu, full_l, d0, kb * BK);
+            ptx::tma_load_2d_2cta(sa + A_BYTES + B_BOX, mu, full_l, d0 + 64, kb * BK);
+            if (WIDE) ptx::tma_load_2d_2cta(sa + A_BYTES + 2 * B_BOX, mu, full_l, d1, kb * BK);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1u;
+            }
           }
         }
       }
@@ -215,7 +226,8 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
         ptx::mbar_wait_cluster(ptx::smem_u32(&tail->tmem_empty[buf]), (use & 1u) ^ 1u, 200 + buf);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * BN;
-        for (int kb = kb_lo; kb < kb_hi; ++kb) {
+        const int nsteps = (kb_hi - kb_lo) * p.terms;  // the terms of BSC_MODE_TC16X3 share the accumulator
+        for (int step = 0; step < nsteps; ++step) {
           ptx::mbar_wait(ptx::smem_u32(&tail->full[stage]), phase, 300 + stage);
           ptx::tc_fence_after();
           const uint32_t sa = ring + stage * STAGE_BYTES;
@@ -223,7 +235,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
           const uint64_t db = desc_b + ptx::desc_addr(sa + A_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
-            const uint32_t acc = (kb != kb_lo || k != 0) ? 1u : 0u;
+            const uint32_t acc = (step != 0 || k != 0) ? 1u : 0u;
             ptx::umma_f16_2cta(d_tmem, da + a_step * k, db + (uint64_t)(k * 128), idesc, acc);
             if (WIDE) {
               const uint64_t db2 = desc_b + ptx::desc_addr(sa + A_BYTES + 2 * B_BOX);
@@ -231,7 +243,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
             }
           }
           ptx::umma_commit_2cta(ptx::smem_u32(&tail->empty[stage]), 3);
-          if (kb == kb_hi - 1) ptx::umma_commit_2cta(ptx::smem_u32(&tail->tmem_full[buf]), 3);
+          if (step == nsteps - 1) ptx::umma_commit_2cta(ptx::smem_u32(&tail->tmem_full[buf]), 3);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1u;
@@ -261,6 +273,7 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
           const float iv = p.job_finv[job][row];
           f = iv > 0.f ? f / iv : 0.f;
         }
+        f *= p.job_fmul[job];
       }
       ptx::mbar_wait(ptx::smem_u32(&tail->tmem_full[buf]), use & 1u, 400 + buf);
       ptx::tc_fence_after();
@@ -375,7 +388,25 @@ static bool rev_wide(const bsc_infonce_desc* d) { return d->d % 384 == 0; }
 //   SCATTER over W > 1 ranks: W parts, so that a K-major item (N / W / 64 K blocks) is as long as an MN-major item
 //   (n_local / 64 K blocks) and the static round-robin over equal items stays balanced;
 //   otherwise: the split that minimises the makespan when a few hundred items meet 74 clusters.
+// BSC_MODE_TC16X3: the accumulator is truncated at every MMA instruction (common.cuh, x3_accumulator_gain), an error that
+// grows with the length of the accumulation chain; the K-major GEMMs are therefore cut into chains of at most
+// kX3ChainCols columns (the parts are added in fp32, round to nearest, by combine).
+constexpr int kX3ChainCols = 1024;
+static int tc_bwd_gemm_kparts_tc16(const bsc_infonce_desc* d);
+
 int tc_bwd_gemm_kparts(const bsc_infonce_desc* d) {
+  int s = tc_bwd_gemm_kparts_tc16(d);
+  if (d->mode == BSC_MODE_TC16X3) {
+    const int64_t nk = (d->n_global + 63) / 64;
+    int64_t want = (d->n_global + kX3ChainCols - 1) / kX3ChainCols;
+    if (want > 32) want = 32;  // every part is one more [n_local][d] fp32 slab per job
+    if (want > nk) want = nk;
+    if (s < want) s = (int)want;
+  }
+  return s;
+}
+
+static int tc_bwd_gemm_kparts_tc16(const bsc_infonce_desc* d) {
   int m = 0;
   for (int a = 0; a < 3; ++a) m += d->xh[a] ? 1 : 0;
   const int64_t nk = (d->n_global + 63) / 64;
@@ -423,11 +454,19 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, con
   tc_bwd_matrix_dims(d, &n_iblk_pad, &n_j64);
   static thread_local RevParams p;  // 26 KB: kept off the stack
   memset(&p, 0, sizeof(p));
-  const int64_t img_rows = (int64_t)n_pairs * n_iblk_pad * n_j64 * 128;
+  const bool x3 = d->mode == BSC_MODE_TC16X3;
+  p.terms = mode_terms(d->mode);
+  p.lo_img0 = (int64_t)n_pairs * n_iblk_pad * n_j64;  // the lo image set follows the hi set (tc_bwd_weights)
+  const int64_t img_rows = (int64_t)n_pairs * n_iblk_pad * n_j64 * 128 * mode_parts(d->mode);
+  BSC_REQUIRE(img_rows < (1ll << 31), BSC_EUNSUPPORTED, "tc_bwd_gemms: %lld image rows exceed 32-bit TMA coordinates",
+              (long long)img_rows);
   int rc = make_tmap_raw128(&p.tmap_g128, ws + L.gimg, img_rows, 128);
   if (rc) return rc;
   rc = make_tmap_raw128(&p.tmap_g64, ws + L.gimg, img_rows, 64);
   if (rc) return rc;
+  // B operand rows: [rows][d] fp16, or the hi / lo column halves of [rows][2 d] (BSC_MODE_TC16X3)
+  const int64_t ldb = (x3 ? 2 : 1) * (int64_t)d->d;
+  const size_t unit_bytes = (size_t)n * ldb * 2;  // unit rows of one modality
   const bool wide = rev_wide(d);
   const int BNW = wide ? 384 : 256;
   const int nchunk = (d->d + BNW - 1) / BNW;
@@ -452,9 +491,10 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, con
     for (int q = 0; q < n_pairs; ++q) {
       const int a = pairs_a[q];
       src[a] = d->xh[a];
-      out[a] = ws + L.xunit + (size_t)a * n * d->d * 2;
+      out[a] = ws + L.xunit + (size_t)a * unit_bytes;
     }
-    rc = rows_unit_f16_launch3(src, d->inv, d->row0, n, d->d, out, st);
+    rc = x3 ? rows_unit_f16x3_launch3(src, d->inv, d->row0, n, d->d, out, st)
+            : rows_unit_f16_launch3(src, d->inv, d->row0, n, d->d, out, st);
     if (rc) return rc;
   }
 
@@ -472,9 +512,14 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, con
     p.job_fnum[job] = 2 * pair_id(a, b);
     p.job_fden[job] = 2 * pair_id(a, b) + 1;  // factor 1: combine divides by gs(a,b)
     p.job_finv[job] = nullptr;
+    p.job_fmul[job] = 1.0f;
     job_nmb[job] = (int)((n + 255) / 256);
-    rc = make_tmap_2d(&p.tmap_in[job], d->xh[b], BSC_F16, N, d->d, 64);
+    rc = make_tmap_2d_ld(&p.tmap_in[job], d->xh[b], BSC_F16, N, d->d, ldb, 64);
     if (rc) return rc;
+    if (x3) {
+      rc = make_tmap_2d_ld(&p.tmap_in_lo[job], (const char*)d->xh[b] + (size_t)d->d * 2, BSC_F16, N, d->d, ldb, 64);
+      if (rc) return rc;
+    }
     ++job;
     if (!scatter) continue;
     // MN-major: partial dB[all rows] = G_q^T * Aunit (local rows of a); undo gs(a,b) / |b_j| per output row and hand
@@ -489,13 +534,21 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, con
     p.job_fnum[job] = 2 * pair_id(b, a);
     p.job_fden[job] = 2 * pair_id(a, b) + 1;
     p.job_finv[job] = d->inv[b];
+    p.job_fmul[job] = x3 ? 1.0f / kX3UnitScale : 1.0f;
     job_nmb[job] = (int)((N + 255) / 256);
-    rc = make_tmap_2d(&p.tmap_in[job], ws + L.xunit + (size_t)a * n * d->d * 2, BSC_F16, n, d->d, 64);
+    rc = make_tmap_2d_ld(&p.tmap_in[job], ws + L.xunit + (size_t)a * unit_bytes, BSC_F16, n, d->d, ldb, 64);
     if (rc) return rc;
+    if (x3) {
+      rc = make_tmap_2d_ld(&p.tmap_in_lo[job], ws + L.xunit + (size_t)a * unit_bytes + (size_t)d->d * 2, BSC_F16, n,
+                           d->d, ldb, 64);
+      if (rc) return rc;
+    }
     ++job;
   }
   p.n_jobs = job;
   for (int z = job; z < MAX_JOBS; ++z) p.tmap_in[z] = p.tmap_in[0];
+  for (int z = 0; z < MAX_JOBS; ++z)
+    if (!x3 || z >= job) p.tmap_in_lo[z] = p.tmap_in[0];
   BSC_REQUIRE(L.kparts >= 1 && L.kparts <= nk_all && L.kparts <= 255, BSC_EUNSUPPORTED,
               "tc_bwd_gemms: K split %d of %d blocks", L.kparts, nk_all);
 
@@ -512,10 +565,10 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, con
   // the schedule depends on the shape only: built once per shape and thread, copied on the later calls
   struct SchedKey {
     int64_t n, N;
-    int d, pairs, mode, world, rank, kparts, sms;
+    int d, pairs, mode, world, rank, kparts, sms, terms;
     bool operator==(const SchedKey& o) const {
       return n == o.n && N == o.N && d == o.d && pairs == o.pairs && mode == o.mode && world == o.world &&
-             rank == o.rank && kparts == o.kparts && sms == o.sms;
+             rank == o.rank && kparts == o.kparts && sms == o.sms && terms == o.terms;
     }
   };
   struct SchedCache {
@@ -526,7 +579,7 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, con
     std::vector<uint32_t> sched;
   };
   static thread_local SchedCache cache;
-  const SchedKey key{n, N, d->d, n_pairs, L.mode, dst.world, dst.rank, L.kparts, device_sm_count()};
+  const SchedKey key{n, N, d->d, n_pairs, L.mode, dst.world, dst.rank, L.kparts, device_sm_count(), p.terms};
   if (cache.valid && cache.key == key) {
     memcpy(p.sched_off, cache.off, sizeof(cache.off));
     memcpy(p.sched, cache.sched.data(), cache.sched.size() * sizeof(uint32_t));
@@ -544,7 +597,7 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, con
         for (int part = 0; part < kp; ++part) {
           const int nkb = (int)((int64_t)(part + 1) * p.job_nk[z] / kp - (int64_t)part * p.job_nk[z] / kp);
           for (int c = 0; c < nchunk; ++c)
-            items.push_back(Item{pack_item(z, c, part, (mbi + rot) % nmb), nkb + 6 /* fill + drain */, kind});
+            items.push_back(Item{pack_item(z, c, part, (mbi + rot) % nmb), nkb * p.terms + 6 /* fill + drain */, kind});
         }
     }
   }

@@ -347,6 +347,8 @@ __host__ __device__ constexpr uint32_t umma_idesc(int m, int n, int a_format, in
 
 // Host: encode a 2-D row-major [rows][cols] 16-bit tensor map with a {64 x box_rows} box and 128B swizzle.
 int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, int64_t rows, int64_t cols, int box_rows);
+int make_tmap_2d_ld(CUtensorMap* out, const void* base, int dtype, int64_t rows, int64_t cols, int64_t ld,
+                    int box_rows);
 // Host: [rows][64] 16-bit rows (128 bytes each) copied as they are: {64 x box_rows} box, no swizzle.
 int make_tmap_raw128(CUtensorMap* out, const void* base, int64_t rows, int box_rows);
 

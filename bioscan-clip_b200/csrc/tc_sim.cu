@@ -41,7 +41,8 @@ __device__ __forceinline__ int chunk_lo(int grp) { return grp == 0 ? 0 : (grp ==
 __device__ __forceinline__ int chunk_hi(int grp) { return grp == 0 ? 3 : (grp == 1 ? 6 : 8); }
 static_assert(NG == 3 && kTcBNF == 256, "chunk_lo / chunk_hi split 8 chunks of 32 columns over 3 groups");
 
-enum { EPI_STATS = 0, EPI_TOPK = 1, EPI_WEIGHTS = 2 };
+enum { EPI_STATS = 0, EPI_TOPK = 1, EPI_WEIGHTS = 2, EPI_WEIGHTS_X3 = 3 };
+__host__ __device__ constexpr bool epi_weights(int epi) { return epi == EPI_WEIGHTS || epi == EPI_WEIGHTS_X3; }
 
 struct SimParams {
   CUtensorMap tmap[3];  // per operand matrix: [rows][d], box {64, 128}
@@ -51,7 +52,11 @@ struct SimParams {
   int n_iblk, n_jtile, n_jchunk, jpc;
   int n_iblk_items;  // row blocks per work item index: n_iblk (cta_group::1) or n_iblk / 2 (CTA pairs)
   int num_items;
-  int kblocks;  // d / 64
+  int kblocks;  // d / 64 (BSC_MODE_TC16X3: 3 d / 64)
+  // BSC_MODE_TC16X3 (x3_kt = d / 64, else 0): the operand rows are [hi | lo] of width 2 d and the K loop runs the three
+  // terms lo_a * hi_b, hi_a * lo_b, hi_a * hi_b one after the other -- the small terms first: the accumulator seems to be
+  // rounded toward zero at every step, which biases a sum that sits at its full size while small terms are still added
+  int x3_kt, x3_d;
   int64_t a_rows;    // valid A rows (local rows of the stripe)
   int64_t a_row0;    // first A row inside the A matrix
   int64_t b_rows;    // valid B rows
@@ -74,6 +79,7 @@ struct SimParams {
   const float* uv;     // [6][N]
   const float* gsbuf;  // [16] = gs of the stored weights
   uint8_t* gimg;       // [pair][n_iblk_pad][n_j64][16 KB]
+  uint8_t* gimg_lo;    // EPI_WEIGHTS_X3: the same images of the fp16 remainders g - fp16(g)
   int n_iblk_pad, n_j64;
   // Fused all-gather (EPI_STATS, several ranks): the operand rows of source rank s (rows [s * src_rows, (s+1) * src_rows)
   // of every matrix, their inverse norms) are complete once arrive[s] >= arrive_target; null = complete on entry.
@@ -158,6 +164,32 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
   return v[0];
 }
 
+// EPI_WEIGHTS_X3: 32 rows x 32 columns of fp16 pairs (pk = this lane's row, 16 x half2) -> half rows (64 bytes) of a
+// 128B-swizzled [128 i][64 j] image, staged through 2 KB of shared memory per warp so that four lanes write the 64
+// contiguous bytes of one row (same scheme as the EPI_WEIGHTS branch of the kernel).
+__device__ __forceinline__ void store_image_half_rows(uint8_t* stg, const uint32_t (&pk)[16], uint8_t* img_base, int c,
+                                                      int q, int lane) {
+  {
+    const int r = lane;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      *reinterpret_cast<uint4*>(stg + r * 64 + ((u ^ ((r >> 1) & 3)) << 4)) =
+          make_uint4(pk[4 * u], pk[4 * u + 1], pk[4 * u + 2], pk[4 * u + 3]);
+  }
+  __syncwarp();
+  const int t4 = lane & 3;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int r = 8 * k + (lane >> 2);
+    const int rt = q * 32 + r;
+    const int u = t4 ^ (r & 3);
+    const uint4 v = *reinterpret_cast<const uint4*>(stg + r * 64 + ((u ^ ((r >> 1) & 3)) << 4));
+    const int half_off = (((c & 1) * 4) ^ (rt & 4)) << 4;
+    __stcs(reinterpret_cast<uint4*>(img_base + (rt >> 3) * 1024 + (rt & 7) * 128 + half_off + (t4 << 4)), v);
+  }
+  __syncwarp();
+}
+
 // PAIR = 1: the two CTAs of a 2-CTA cluster own two adjacent row blocks of the SAME column chunk and run every MMA as
 // one tcgen05.mma.cta_group::2 (M = 256, N = 256): each CTA stages its own 128 A rows and half of the B tile, which
 // cuts the shared-memory operand bytes per MMA cycle from 96 to 64 per SM (measured: the cta_group::1 sweep is bound by
@@ -240,17 +272,23 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
             ptx::mbar_wait(ptx::smem_u32(&tail->empty[stage]), phase ^ 1u, 100 + stage);
             const uint32_t full = ptx::smem_u32(&tail->full[stage]);
             const uint32_t sa = ring + stage * SB;
+            int ca = kb * BK, cb = kb * BK;  // first column of the A / B box
+            if (p.x3_kt > 0) {
+              const int term = kb / p.x3_kt, kk = (kb - term * p.x3_kt) * BK;
+              ca = kk + (term == 0 ? p.x3_d : 0);  // term 0: lo_a * hi_b
+              cb = kk + (term == 1 ? p.x3_d : 0);  // term 1: hi_a * lo_b, term 2: hi_a * hi_b
+            }
             if (PAIR) {
               // both CTAs' bytes complete on the leader's barrier; the leader expects the total
               const uint32_t full_l = ptx::mapa(full, 0);
               if (crank == 0) ptx::mbar_arrive_expect_tx(full, 2 * SB);
-              ptx::tma_load_2d_2cta(sa, ma, full_l, kb * BK, arow);
-              ptx::tma_load_2d_2cta(sa + A_BYTES, mb, full_l, kb * BK, brow + 128 * (int)crank);
+              ptx::tma_load_2d_2cta(sa, ma, full_l, ca, arow);
+              ptx::tma_load_2d_2cta(sa + A_BYTES, mb, full_l, cb, brow + 128 * (int)crank);
             } else {
               ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
-              ptx::tma_load_2d(sa, ma, full, kb * BK, arow);
-              ptx::tma_load_2d(sa + A_BYTES, mb, full, kb * BK, brow);
-              ptx::tma_load_2d(sa + A_BYTES + B_BYTES / 2, mb, full, kb * BK, brow + 128);
+              ptx::tma_load_2d(sa, ma, full, ca, arow);
+              ptx::tma_load_2d(sa + A_BYTES, mb, full, cb, brow);
+              ptx::tma_load_2d(sa + A_BYTES + B_BYTES / 2, mb, full, cb, brow + 128);
             }
             if (++stage == NST) {
               stage = 0;
@@ -355,7 +393,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
       }
       float ugs_i = 0.f, gsw = 0.f;
       const float* vcol_g = nullptr;
-      if (EPI == EPI_WEIGHTS) {
+      if (epi_weights(EPI)) {
         gsw = p.gsbuf[2 * pair_id(p.pair_a[pair], p.pair_b[pair])];
         if (row_ok) {
           inv_i = p.inv[p.pair_a[pair]][p.a_row0 + arow];
@@ -394,7 +432,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
           }
           ptx::named_bar_sync(2 + 2 * grp, 128);
         }
-        if (EPI == EPI_WEIGHTS) {
+        if (epi_weights(EPI)) {
           // column facts of the tile: k1 / |b_j|, gs * v_j, label class (the column-sum scratch is free in this mode)
           float* vgb = &tail->cs[0][0][0] + buf * BN;
           float* wfb = &tail->cs[0][2][0] + buf * BN;
@@ -418,7 +456,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
         float* cs = tail->cs[buf][q];
         const float* ivb = tail->invb[buf];
         bool tile_pos = false;  // can any (row of this warp, column of this tile) pair share a label?
-        if (EPI == EPI_STATS || EPI == EPI_WEIGHTS) {
+        if (EPI == EPI_STATS || epi_weights(EPI)) {
           const int2 jr = p.jrange[jt];
           tile_pos = (wmax >= jr.x) && (wmin <= jr.y);
         }
@@ -524,6 +562,35 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
                 __stcs(reinterpret_cast<uint4*>(img_base + (rt >> 3) * 1024 + (rt & 7) * 128 + half_off + (t4 << 4)), v);
             }
             __syncwarp();
+          } else if (EPI == EPI_WEIGHTS_X3) {
+            // float32-grade weights: g is formed as in EPI_WEIGHTS and stored as fp16(g) (image set gimg) and
+            // fp16(g - fp16(g)) (image set gimg_lo); the gradient GEMMs add both (tc_bwd3.cu, three terms)
+            const float* vgb = &tail->cs[0][0][0] + buf * BN + c * 32;
+            const float* wfb = &tail->cs[0][2][0] + buf * BN + c * 32;
+            const int* repb = reinterpret_cast<const int*>(&tail->cs[1][0][0]) + buf * BN + c * 32;
+            const float m2g = -2.0f * gsw;
+#pragma unroll
+            for (int t = 0; t < 32; ++t) {
+              const float ex = ptx::ex2(fmaf(__uint_as_float(raw[t]), inv_i * ivb[c * 32 + t], -p.k2));
+              const float tv = (tile_pos && repb[t] == rep_i) ? m2g * wfb[t] : 0.f;
+              raw[t] = __float_as_uint(fmaf(ex, fmaf(ugs_i, wfb[t], vgb[t]), tv));
+            }
+            const int64_t img = ((int64_t)pair * p.n_iblk_pad + iblk) * p.n_j64 + (int64_t)jt * 4 + (c >> 1);
+#pragma unroll 1
+            for (int part = 0; part < 2; ++part) {
+              uint32_t pk[16];
+#pragma unroll
+              for (int t = 0; t < 32; t += 2) {
+                const float g0 = __uint_as_float(raw[t]), g1 = __uint_as_float(raw[t + 1]);
+                __half2 hh = __floats2half2_rn(g0, g1);
+                if (part) {
+                  const float2 b = __half22float2(hh);
+                  hh = __floats2half2_rn(g0 - b.x, g1 - b.y);
+                }
+                pk[t >> 1] = *reinterpret_cast<const uint32_t*>(&hh);
+              }
+              store_image_half_rows(tail->wst[warp - 4], pk, (part ? p.gimg_lo : p.gimg) + img * 16384, c, q, lane);
+            }
           } else {
             // Scan path (always executed, kept tiny so it stays in the instruction cache): which of the 32 scores beat
             // this row's current KTOP-th best?  Rare path: the union of those columns over the warp is re-read from
@@ -716,11 +783,12 @@ int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceFwdWs& L, char* ws, flo
                  const bsc_infonce_exchange* ex, cudaStream_t st) {
   BSC_REQUIRE(d->d % BK == 0, BSC_EUNSUPPORTED, "TC16 mode needs d %% 64 == 0 (got %d); use BSC_MODE_F32", d->d);
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
+  const bool x3 = d->mode == BSC_MODE_TC16X3;
   SimParams p{};
   int np = 0;
   for (int a = 0; a < 3; ++a) {
     if (d->xh[a]) {
-      int rc = make_tmap_2d(&p.tmap[a], d->xh[a], d->x16_dtype, d->n_global, d->d, 128);
+      int rc = make_tmap_2d(&p.tmap[a], d->xh[a], d->x16_dtype, d->n_global, (x3 ? 2 : 1) * (int64_t)d->d, 128);
       if (rc) return rc;
     }
     p.inv[a] = d->inv[a];
@@ -739,13 +807,16 @@ int tc_fwd_stats(const bsc_infonce_desc* d, const InfoNceFwdWs& L, char* ws, flo
   p.n_jchunk = L.n_jchunk;
   p.jpc = L.jtiles_per_chunk;
   p.num_items = np * L.n_jchunk * L.n_iblk;
-  p.kblocks = d->d / BK;
+  p.kblocks = (x3 ? 3 : 1) * (d->d / BK);
+  p.x3_kt = x3 ? d->d / BK : 0;
+  p.x3_d = d->d;
   p.a_rows = d->n_local;
   p.a_row0 = d->row0;
   p.b_rows = d->n_global;
   const float log2e = 1.4426950408889634f;
   p.k1 = d->logit_scale * log2e;
   p.k2 = d->logit_scale * log2e;
+  if (x3) p.k1 = (float)((double)p.k1 * x3_accumulator_gain(d->d));
   p.rowpart = (float*)(ws + L.rowpart);
   p.colpart = (float*)(ws + L.colpart);
   p.rowpos = (float*)(ws + L.rowpos);
@@ -818,18 +889,19 @@ size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* d) {
   const size_t blocks = (size_t)(d->bwd_mode == BSC_BWD_SCATTER ? m * (m - 1) / 2 : m * (m - 1));
   int n_iblk_pad, n_j64;
   tc_bwd_matrix_dims(d, &n_iblk_pad, &n_j64);
-  return blocks * (size_t)n_iblk_pad * (size_t)n_j64 * 16384;
+  return blocks * (size_t)n_iblk_pad * (size_t)n_j64 * 16384 * (size_t)mode_parts(d->mode);  // X3: hi set, then lo set
 }
 
 int tc_bwd_weights(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, const float* aux, int* n_pairs,
                    int* pairs_a, int* pairs_b, cudaStream_t st) {
   BSC_REQUIRE(d->n_global < (1ll << 31) - 512, BSC_EUNSUPPORTED, "n_global too large for 32-bit TMA coordinates");
   const bool ordered = L.mode == BSC_BWD_BLOCKS;
+  const bool x3 = d->mode == BSC_MODE_TC16X3;
   SimParams p{};
   int np = 0, first = -1;
   for (int a = 0; a < 3; ++a) {
     if (d->xh[a]) {
-      int rc = make_tmap_2d(&p.tmap[a], d->xh[a], d->x16_dtype, d->n_global, d->d, 128);
+      int rc = make_tmap_2d(&p.tmap[a], d->xh[a], d->x16_dtype, d->n_global, (x3 ? 2 : 1) * (int64_t)d->d, 128);
       if (rc) return rc;
       if (first < 0) first = a;
     }
@@ -851,18 +923,22 @@ int tc_bwd_weights(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, c
   p.n_jchunk = L.n_jchunk;
   p.jpc = L.jtiles_per_chunk;
   p.num_items = np * L.n_jchunk * L.n_iblk;
-  p.kblocks = d->d / BK;
+  p.kblocks = (x3 ? 3 : 1) * (d->d / BK);
+  p.x3_kt = x3 ? d->d / BK : 0;
+  p.x3_d = d->d;
   p.a_rows = d->n_local;
   p.a_row0 = d->row0;
   p.b_rows = d->n_global;
   const float log2e = 1.4426950408889634f;
   p.k1 = d->logit_scale * log2e;
   p.k2 = d->logit_scale * log2e;
+  if (x3) p.k1 = (float)((double)p.k1 * x3_accumulator_gain(d->d));
   p.rep = d->rep;
   p.uv = aux;
   p.gsbuf = aux + 6 * d->n_global;
   p.gimg = (uint8_t*)(ws + L.gimg);
   tc_bwd_matrix_dims(d, &p.n_iblk_pad, &p.n_j64);
+  p.gimg_lo = p.gimg + (size_t)np * p.n_iblk_pad * p.n_j64 * 16384;  // used by EPI_WEIGHTS_X3 only
   p.jrange = (const int2*)(ws + L.jrange);
   {
     int rc = rep_range_launch(d->rep, d->n_global, BN, (int2*)(ws + L.jrange), st);
@@ -875,7 +951,7 @@ int tc_bwd_weights(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, c
   }
 #endif
   timing_begin(1, st);
-  int rc = launch_sim<EPI_WEIGHTS, 0>(p, st);
+  int rc = x3 ? launch_sim<EPI_WEIGHTS_X3, 0>(p, st) : launch_sim<EPI_WEIGHTS, 0>(p, st);
   timing_end(1, st);
   return rc;
 }

@@ -54,6 +54,10 @@ extern "C" {
 #define BSC_MODE_F32 0  /* SIMT fp32 path: exact-parity mode (1e-5 vs the fp32 reference)          */
 #define BSC_MODE_TC16 1 /* tcgen05 path: the caller's 16-bit rows as operands, fp32 accumulate in TMEM,
                            row norms applied as fp32 scales in the epilogue                           */
+#define BSC_MODE_TC16X3 2 /* tcgen05 path at float32 grade: every row is split into two fp16 parts (hi + lo = 22
+                           significant bits) and every product x*y is formed as lo*hi + hi*lo + hi*hi on the
+                           tensor cores with fp32 accumulation (the fp32 sgemm of loss_func.py:46-47 at 3 MMAs
+                           per product); the stored gradient weights are split the same way                */
 
 /* zero-norm rules for bsc_l2norm_fwd */
 #define BSC_NORM_TORCH 0   /* F.normalize: x / max(||x||, 1e-12)            (loss_func.py:43-44)   */
@@ -82,6 +86,11 @@ int bsc_l2norm_fwd(const void* x, int x_dtype, int64_t n, int d, int64_t ldx,
  * cos_ij = <y16_i, y16_j> * inv_i * inv_j equals the reference's normalised dot product without re-rounding
  * any operand (F.normalize, loss_func.py:43-44). */
 int bsc_rows_to_f16(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* y16, float* inv, void* stream);
+
+/* BSC_MODE_TC16X3 operand preparation (same F.normalize lines): hl[n][2 d] (fp16), columns [0, d) = hi and [d, 2 d) = lo
+ * with hi = fp16(x * 2^k_row), lo = fp16(x * 2^k_row - hi) -- the row maximum is scaled into [128, 256) so that the lo
+ * parts of all but negligible elements stay normal fp16 numbers -- and inv[n] = 2^-k_row / max(||x_row||, 1e-12). */
+int bsc_rows_to_f16x3(const void* x, int x_dtype, int64_t n, int d, int64_t ldx, void* hl, float* inv, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * K1+gather  TC16 operand preparation fused with the all_gather of gather_features (loss_func.py:58-91) and of the
@@ -157,6 +166,9 @@ int bsc_label_stats_static(const int64_t* labels, int64_t n, float* r, int32_t* 
  *                  from bsc_rows_to_f16: the caller's values times an exact power of two per row.  The tensor
  *                  cores multiply those rows; cos_ij = <x_i, y_j> * inv_i * inv_j is formed in fp32, so no
  *                  operand is re-rounded.
+ *   BSC_MODE_TC16X3  xh[m] = n_global rows of 2 d fp16 elements (hi | lo) and inv[m][n_global] from bsc_rows_to_f16x3;
+ *                  d is still the embedding width.  Backward strategies: BSC_BWD_BLOCKS / BSC_BWD_SCATTER (the weight
+ *                  blocks are stored as hi and lo images: twice the bytes of BSC_MODE_TC16).
  * ---------------------------------------------------------------------------------------------- */
 typedef struct bsc_infonce_desc {
   int64_t n_global;

@@ -21,6 +21,7 @@ class StripeComm:
         self.feats_all, self.labels_all = feats_all, labels_all
         self.records, self.stats_local = records, None
         self.shared = shared if shared is not None else {}
+        self._x3_calls = 0
 
     def gather_tc16(self, feats, labels):
         if "gathered" not in self.shared:
@@ -34,7 +35,21 @@ class StripeComm:
         return {"xh": xh, "inv": inv, "labels": self.labels_all}
 
     def all_gather_rows(self, t):
-        raise AssertionError("the TC16 path gathers through gather_tc16")
+        """BSC_MODE_TC16X3 gathers with plain collectives, in a fixed order: (hi | lo rows, inverse norms) of every
+        present modality, then the labels.  The stand-in answers each call with the same quantity prepared from the
+        WHOLE batch and checks that the caller's local part is the matching slice of it."""
+        if "x3" not in self.shared:
+            seq = []
+            for f in self.feats_all:
+                if f is not None:
+                    seq.extend(self.ops.rows_to_f16x3(f))
+            seq.append(self.labels_all)
+            self.shared["x3"] = seq
+        full = self.shared["x3"][self._x3_calls]
+        self._x3_calls += 1
+        nl = full.shape[0] // self.world_size
+        assert torch.equal(full[self.rank * nl:(self.rank + 1) * nl], t), "gather order changed: update tests/stripe.py"
+        return full
 
     def share_stats(self, record):
         """First pass (records is None): remember this rank's record.  Second pass: hand out all ranks' records, this
@@ -56,10 +71,12 @@ def _local(feats_all, labels_all, rank, world):
     return [None if f is None else f[sl].clone() for f in feats_all], labels_all[sl].contiguous()
 
 
-def first_pass(ops, world, feats_all, labels_all, scale=1 / 0.07, shared=None):
+def first_pass(ops, world, feats_all, labels_all, scale=1 / 0.07, shared=None, mode=None):
     """Forward of every rank's stripe; returns the [world, len] statistics records (what the exchange hands out)."""
     from bsc._lib import MODE_TC16
     from bsc.loss import infonce_forward
+
+    MODE_TC16 = MODE_TC16 if mode is None else mode
 
     recs = []
     shared = shared if shared is not None else {}
@@ -71,13 +88,15 @@ def first_pass(ops, world, feats_all, labels_all, scale=1 / 0.07, shared=None):
     return torch.stack(recs)
 
 
-def replay(ops, world, feats_all, labels_all, request, scale=1 / 0.07, grad_out=1.0):
-    """Whole job: returns (loss per rank, gradient per modality for ALL rows, resolved backward mode)."""
+def replay(ops, world, feats_all, labels_all, request, scale=1 / 0.07, grad_out=1.0, mode=None):
+    """Whole job: returns (loss per rank, gradient per modality for ALL rows, resolved backward mode).
+    mode: BSC_MODE_TC16 (default) or BSC_MODE_TC16X3."""
     from bsc._lib import BWD_SCATTER, MODE_TC16
     from bsc.loss import infonce_forward
 
+    MODE_TC16 = MODE_TC16 if mode is None else mode
     shared = {}
-    records = first_pass(ops, world, feats_all, labels_all, scale, shared)
+    records = first_pass(ops, world, feats_all, labels_all, scale, shared, mode)
     nl = labels_all.shape[0] // world
     ranks = []
     for r in range(world):

@@ -348,6 +348,89 @@ def test_config3_32768_eight_ranks_replayed_against_blockwise_oracle():
     print(f"N=32768 as 8 ranks: loss rel err {rel_loss:.2e}, gradient max err / max |g| {worst:.2e}")
 
 
+X3_TOL = 1e-5  # north_star: 1e-5 relative in fp32 -- here on the tensor cores (BSC_MODE_TC16X3, precision="fp32x3")
+X3_CASES = [
+    # n, d, present, labels, shared, normalised
+    (512, 768, (True, True, True), "multi", 0.5, True),
+    (1000, 768, (True, True, True), "arange", 0.5, True),     # ragged N, peaked softmax (loss ~ 1e-2)
+    (384, 256, (True, False, True), "multi", 0.0, True),      # flat softmax, two modalities
+    (300, 1024, (True, True, True), "multi", 0.5, False),     # un-normalised rows (norms 0.5 .. 2 sqrt(d)), d = 4 x 256
+    (4096, 768, (True, True, True), "multi", 0.5, True),      # BASELINE config 2 size, full float32 inputs
+    (4096, 768, (True, True, True), "arange", 0.5, True),     # ... with the reference's default labels
+]
+
+
+def _x3_errors(loss, grads, ref_loss, ref_grads):
+    rel_loss = abs(float(loss) - float(ref_loss)) / abs(float(ref_loss))
+    rel_grad = max((g.double() - r.double()).abs().max().item() / r.abs().max().item()
+                   for g, r in zip(grads, ref_grads) if r is not None)
+    return rel_loss, rel_grad
+
+
+@pytest.mark.parametrize("n,d,present,labels,shared,normalised", X3_CASES)
+@pytest.mark.parametrize("mode", ["scatter", "blocks"])
+def test_fp32x3_tensor_core_mode_matches_fp64_closed_form(n, d, present, labels, shared, normalised, mode, monkeypatch):
+    """Float32 inputs (NOT 16-bit representable) through the split-operand tensor-core mode against the fp64 closed form
+    of the reference maths.  With labels that give a loss of order 1 the bound is the plain 1e-5 on the loss and on
+    max |gradient error| / max |gradient|; with the reference's default labels (arange: a peaked softmax and a loss of
+    order 1e-2, where the reference's own float32 arithmetic is itself several 1e-5 away from the closed form) the
+    float32 noise of the reference is allowed on top, as in test_fp32_mode_matches_oracle.  The measured figures are
+    printed either way (pytest -s)."""
+    from bsc import _lib
+
+    feats, lab = loss_inputs(n, d, present, seed=n + 3, labels=labels, shared=shared, normalised=normalised)
+    torch.set_num_threads(os.cpu_count() or 8)
+    ref_loss, ref_grads = loss_oracle.closed_form_grads(feats, lab)
+    nl, ng = _fp32_noise(feats, lab, ref_loss, ref_grads)
+    monkeypatch.setenv("BSC_BWD_MODE", mode)
+    loss, grads = _run(feats, lab, "fp32x3")
+    assert _lib.last_bwd_mode() == BWD_CODE[mode]
+    rel_loss, rel_grad = _x3_errors(loss, grads, ref_loss, ref_grads)
+    ref_gmax = max(r.abs().max().item() for r in ref_grads if r is not None)
+    print(f"fp32x3 N={n} d={d} {labels} {mode}: loss {float(ref_loss):.5f} rel err {rel_loss:.2e}, gradient max err / "
+          f"max|g| {rel_grad:.2e}  (float32 reference port vs the same closed form: {nl / abs(float(ref_loss)):.2e} / "
+          f"{max(ng) / ref_gmax:.2e})")
+    if labels == "arange":
+        _compare(loss, grads, ref_loss, ref_grads, X3_TOL, nl, ng)
+    else:
+        assert rel_loss <= X3_TOL + LOSS_FLOOR / abs(float(ref_loss)), rel_loss
+        assert rel_grad <= X3_TOL, rel_grad
+
+
+@pytest.mark.parametrize("world,mode", [(2, "scatter"), (4, "scatter"), (4, "blocks")])
+def test_fp32x3_ranks_replayed_on_one_gpu(world, mode):
+    """The W-rank job of the fp32x3 mode (rows gathered with plain collectives, scatter backward over the exchange
+    buffers) replayed on one GPU: loss bits equal on every rank, loss and gradients of the whole batch at 1e-5."""
+    from bsc._lib import BWD_NAMES, MODE_TC16X3
+    from bsc.loss import _default_ops
+    from tests.stripe import replay
+
+    n, d = 1024, 768
+    feats, lab = loss_inputs(n, d, seed=n + world, labels="multi", normalised=False)
+    ref_loss, ref_grads = loss_oracle.closed_form_grads(feats, lab)
+    losses, grads, resolved = replay(_default_ops(), world, [f.cuda() for f in feats], lab.cuda(), BWD_NAMES[mode],
+                                     mode=MODE_TC16X3)
+    torch.cuda.synchronize()
+    assert resolved == BWD_CODE[mode] and all(x == losses[0] for x in losses)
+    rel_loss, rel_grad = _x3_errors(losses[0], [g.cpu() for g in grads], ref_loss, ref_grads)
+    print(f"fp32x3 as {world} ranks ({mode}): loss rel err {rel_loss:.2e}, gradient max err / max|g| {rel_grad:.2e}")
+    assert rel_loss <= X3_TOL and rel_grad <= X3_TOL
+
+
+def test_fp32x3_is_what_auto_picks_for_large_float32_batches_and_refuses_the_recomputing_sweep(monkeypatch):
+    import bsc
+    from bsc._lib import MODE_F32, MODE_TC16X3
+    from bsc.loss import resolve_mode
+
+    small, big = [torch.zeros(256, 768)] * 2, [torch.zeros(2048, 768)] * 2
+    assert resolve_mode("auto", small) == MODE_F32 and resolve_mode("auto", big) == MODE_TC16X3
+    assert resolve_mode("auto", small, n_global=8 * 256) == MODE_TC16X3  # the GLOBAL batch decides
+    feats, lab = loss_inputs(256, 768, seed=5, labels="multi")
+    monkeypatch.setenv("BSC_BWD_MODE", "recompute")
+    with pytest.raises(bsc.BscError, match="stored-weight"):
+        _run(feats, lab, "fp32x3")
+
+
 def test_properties_at_full_size():
     """Size-independent checks at N = 32768: permutation invariance of the batch and run-to-run determinism."""
     n = 32768

@@ -106,11 +106,15 @@ def test_modules_refuse_cpu_tensors(built_lib):
 
 
 def test_resolve_mode():
-    from bsc._lib import MODE_F32, MODE_TC16
-    from bsc.loss import resolve_mode
+    from bsc._lib import MODE_F32, MODE_TC16, MODE_TC16X3
+    from bsc.loss import X3_MIN_ROWS, resolve_mode
 
     f32, b16 = torch.zeros(1, 256), torch.zeros(1, 256, dtype=torch.bfloat16)
     assert resolve_mode("auto", [f32, f32]) == MODE_F32
+    big = torch.zeros(X3_MIN_ROWS, 256)
+    assert resolve_mode("auto", [big, big]) == MODE_TC16X3          # float32 inputs, large batch: split operands
+    assert resolve_mode("auto", [f32, f32], n_global=X3_MIN_ROWS) == MODE_TC16X3
+    assert resolve_mode("fp32x3", [f32, f32]) == MODE_TC16X3 and resolve_mode("fp32", [big, big]) == MODE_F32
     assert resolve_mode("auto", [f32, b16]) == MODE_TC16
     assert resolve_mode("tc16", [f32]) == MODE_TC16 and resolve_mode("fp32", [b16]) == MODE_F32
     odd = torch.zeros(1, 72, dtype=torch.bfloat16)
