@@ -22,8 +22,11 @@ def _newer(a: str, b: str) -> bool:
     return not os.path.exists(b) or os.path.getmtime(a) > os.path.getmtime(b)
 
 
-def build_lib(force: bool = False, verbose: bool = False) -> str:
-    objdir = os.path.join(HERE, "build")
+def build_lib(force: bool = False, verbose: bool = False, variant: str = "", defines=()) -> str:
+    """variant / defines: an A/B build with extra -D flags, e.g. build_lib(variant="v2", defines=["-DBSC_SCAN_V2=1"]) ->
+    bsc/libbsc_hot_v2.so (objects under build_v2/); BSC_LIB_PATH selects which library the package loads."""
+    objdir = os.path.join(HERE, "build" + ("_" + variant if variant else ""))
+    out = OUT if not variant else OUT.replace(".so", "_" + variant + ".so")
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     headers.append(os.path.join(HERE, "..", "include", "bsc_hot.h"))
@@ -34,7 +37,7 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
         o = os.path.join(objdir, src.replace(".cu", ".o"))
         objs.append(o)
         if force or _newer(s, o) or any(_newer(h, o) for h in headers):
-            cmd = [NVCC, *FLAGS, "-c", s, "-o", o]
+            cmd = [NVCC, *FLAGS, *defines, "-c", s, "-o", o]
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             jobs.append(cmd)
@@ -49,12 +52,15 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
         for msg in ex.map(run, jobs):
             if verbose and msg:
                 print(msg, file=sys.stderr)
-    if jobs or not os.path.exists(OUT):
-        link = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", OUT, *objs,
+    if jobs or not os.path.exists(out):
+        link = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", out, *objs,
                 "-Xcompiler", "-fPIC", "-cudart", "static"]
         run(link)
-    return OUT
+    return out
 
 
 if __name__ == "__main__":
-    print(build_lib(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    # python build.py [--force] [-v] [--variant NAME -DFLAG=1 ...]
+    name = sys.argv[sys.argv.index("--variant") + 1] if "--variant" in sys.argv else ""
+    print(build_lib(force="--force" in sys.argv, verbose="-v" in sys.argv, variant=name,
+                    defines=[a for a in sys.argv[1:] if a.startswith("-D")]))

@@ -11,6 +11,13 @@
 
 #include "../../include/bsc_hot.h"
 
+// Bank scan with few queries (32-query passes over a shard), second layout: one work item per SM, candidate re-reads in
+// groups of four TMEM columns, block-per-query merge of the candidate lists.  0 = the round-1 layout (two items per SM,
+// single-column re-reads, warp-per-query merge), kept for A/B builds (python build.py --variant).
+#ifndef BSC_SCAN_V2
+#define BSC_SCAN_V2 0
+#endif
+
 namespace bsc {
 
 // ---- error plumbing ---------------------------------------------------------------------------

@@ -1319,6 +1319,99 @@ __global__ void __launch_bounds__(128) topk_merge_kernel(const float* __restrict
   }
 }
 
+#if BSC_SCAN_V2
+// Few queries, many lists (a 32-query pass over a bank shard leaves 3 lists per SM): one BLOCK per query.  Every thread
+// reads its share of the candidates ONCE and keeps its own best KM of them in registers; the 128 short lists meet in
+// shared memory, where warp 0 runs the k selection rounds of topk_merge_kernel (same total order: score desc, id asc, so
+// the result is the same whatever the split).  The warp-per-query kernel walks all parts * k candidates k times with
+// dependent global loads: ~0.2 ms for 888 lists, as long as the scan of a 625k-row shard itself.
+constexpr int KM = 8;
+__device__ __forceinline__ bool cand_before(float s, int64_t i, float s2, int64_t i2) {
+  // (s, i) valid; does it come before (s2, i2) in (score desc, id asc)?  Padding (i2 < 0) comes after everything.
+  return (i2 < 0) || (s > s2) || (s == s2 && i < i2);
+}
+__global__ void __launch_bounds__(128) topk_merge_block_kernel(const float* __restrict__ cs,
+                                                               const int64_t* __restrict__ ci, int parts, int64_t nq,
+                                                               int k, float* __restrict__ os, int64_t* __restrict__ oi) {
+  __shared__ float sh_s[128 * KM];
+  __shared__ int64_t sh_i[128 * KM];
+  const int64_t q = blockIdx.x;
+  constexpr float kLowest = -3.4028234663852886e38f;
+  float ts[KM];
+  int64_t ti[KM];
+#pragma unroll
+  for (int u = 0; u < KM; ++u) {
+    ts[u] = kLowest;
+    ti[u] = -1;
+  }
+  const int total = parts * k;
+  for (int c = threadIdx.x; c < total; c += 128) {
+    const int64_t idx = ((int64_t)(c / k) * nq + q) * k + (c % k);
+    const int64_t id = ci[idx];
+    const float s = cs[idx];
+    if (id < 0 || !cand_before(s, id, ts[KM - 1], ti[KM - 1])) continue;
+    ts[KM - 1] = s;
+    ti[KM - 1] = id;
+#pragma unroll
+    for (int u = KM - 1; u > 0; --u) {
+      if (ti[u] >= 0 && cand_before(ts[u], ti[u], ts[u - 1], ti[u - 1])) {
+        const float fs = ts[u];
+        ts[u] = ts[u - 1];
+        ts[u - 1] = fs;
+        const int64_t fi = ti[u];
+        ti[u] = ti[u - 1];
+        ti[u - 1] = fi;
+      }
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < KM; ++u) {
+    sh_s[u * 128 + threadIdx.x] = ts[u];
+    sh_i[u * 128 + threadIdx.x] = ti[u];
+  }
+  __syncthreads();
+  if (threadIdx.x >= 32) return;
+  const int lane = threadIdx.x;
+  float prev_s = 0.f;
+  int64_t prev_i = -1;
+  int t = 0;
+  for (; t < k; ++t) {
+    float best_s = kLowest;
+    int64_t best_i = -1;
+    for (int c = lane; c < 128 * KM; c += 32) {
+      const int64_t id = sh_i[c];
+      if (id < 0) continue;
+      const float s = sh_s[c];
+      const bool after_prev = (t == 0) || (s < prev_s) || (s == prev_s && id > prev_i);
+      if (after_prev && cand_before(s, id, best_s, best_i)) {
+        best_s = s;
+        best_i = id;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float s2 = __shfl_xor_sync(0xffffffffu, best_s, o);
+      const int64_t i2 = __shfl_xor_sync(0xffffffffu, best_i, o);
+      if (i2 >= 0 && cand_before(s2, i2, best_s, best_i)) {
+        best_s = s2;
+        best_i = i2;
+      }
+    }
+    if (best_i < 0) break;  // only padding is left
+    if (lane == 0) {
+      os[q * k + t] = best_s;
+      oi[q * k + t] = best_i;
+    }
+    prev_s = best_s;
+    prev_i = best_i;
+  }
+  for (int u = t + lane; u < k; u += 32) {
+    os[q * k + u] = kLowest;
+    oi[q * k + u] = -1;
+  }
+}
+#endif
+
 int topk_merge_launch(const float* cs, const int64_t* ci, int parts, int64_t nq, int k, float* os, int64_t* oi,
                       cudaStream_t st) {
   if (nq == 0) return BSC_OK;
@@ -1326,6 +1419,13 @@ int topk_merge_launch(const float* cs, const int64_t* ci, int parts, int64_t nq,
     set_error("bsc_topk_merge: k=%d > 32 unsupported", k);
     return BSC_EUNSUPPORTED;
   }
+#if BSC_SCAN_V2
+  if (k <= KM && nq <= 2048 && (int64_t)parts * k >= 256) {
+    topk_merge_block_kernel<<<(unsigned)nq, 128, 0, st>>>(cs, ci, parts, nq, k, os, oi);
+    BSC_LAUNCH_CHECK("topk_merge_block_kernel");
+    return BSC_OK;
+  }
+#endif
   topk_merge_kernel<<<(unsigned)((nq + 3) / 4), 128, 0, st>>>(cs, ci, parts, nq, k, os, oi);
   BSC_LAUNCH_CHECK("topk_merge_kernel");
   return BSC_OK;

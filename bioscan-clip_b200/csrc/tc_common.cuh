@@ -240,6 +240,13 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16])
       : "r"(taddr)
       : "memory");
 }
+// 32 lanes x 4 columns -> four registers per thread
+__device__ __forceinline__ void tmem_ld_32x32_x4(uint32_t taddr, uint32_t (&v)[4]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+               : "r"(taddr)
+               : "memory");
+}
 // 32 lanes x 1 column -> one register per thread
 __device__ __forceinline__ uint32_t tmem_ld_32x32_x1(uint32_t taddr) {
   uint32_t v;

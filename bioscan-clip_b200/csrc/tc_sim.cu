@@ -72,6 +72,11 @@ struct SimParams {
   // EPI_TOPK
   int k;
   int64_t base_id;
+  // At most 64 queries (spread = 8 or 16, else 0): the queries are laid out `spread` per TMEM lane quarter (query r ->
+  // tile row 32 (r / spread) + r % spread; tmap[2] = the query matrix with a box of `spread` rows), so that all four
+  // epilogue warps of a column group keep lists instead of one: a warp takes the insert path for the union of its
+  // lanes' columns, and 8 queries per warp make that union 4 times sparser than 32 (BSC_SCAN_V2 >= 2).
+  int spread;
   float* cand_s;     // [jchunk][a_rows][k]
   int64_t* cand_i;
   // EPI_WEIGHTS: the fp16 weight block of every pair, G_ij = gs (e_ij (u_i + v_j) - 2 T_ij) / |b_j|, written as
@@ -285,8 +290,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
               ptx::tma_load_2d_2cta(sa, ma, full_l, ca, arow);
               ptx::tma_load_2d_2cta(sa + A_BYTES, mb, full_l, cb, brow + 128 * (int)crank);
             } else {
-              ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
-              ptx::tma_load_2d(sa, ma, full, ca, arow);
+              if (EPI == EPI_TOPK && p.spread > 0) {
+                // `spread` query rows per lane quarter: 8-row atoms (1024 B) 4 g, 4 g + 1 of the A tile; the rows in
+                // between are never written and never read back (their accumulator rows belong to no query)
+                ptx::mbar_arrive_expect_tx(full, 4u * (uint32_t)p.spread * 128u + B_BYTES);
+#pragma unroll
+                for (int g = 0; g < 4; ++g) ptx::tma_load_2d(sa + g * 4096, &p.tmap[2], full, ca, arow + g * p.spread);
+              } else {
+                ptx::mbar_arrive_expect_tx(full, STAGE_BYTES);
+                ptx::tma_load_2d(sa, ma, full, ca, arow);
+              }
               ptx::tma_load_2d(sa + A_BYTES, mb, full, cb, brow);
               ptx::tma_load_2d(sa + A_BYTES + B_BYTES / 2, mb, full, cb, brow + 128);
             }
@@ -361,8 +374,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
       int pair, jchunk, iblk;
       decode_item(p, item, pair, jchunk, iblk);
       if (PAIR) iblk = 2 * iblk + (int)crank;
-      const int64_t arow = (int64_t)iblk * BM + row_in_tile;  // row inside the stripe
-      const bool row_ok = arow < p.a_rows;
+      int64_t arow = (int64_t)iblk * BM + row_in_tile;  // row inside the stripe
+      bool row_ok = arow < p.a_rows;
+      if (EPI == EPI_TOPK && p.spread > 0) {  // queries spread over the lane quarters (iblk == 0)
+        arow = q * p.spread + lane;
+        row_ok = lane < p.spread && arow < p.a_rows;
+      }
       const int jt_end = min(p.n_jtile, (jchunk + 1) * p.jpc);
 
       float rowsum = 0.f;
@@ -605,7 +622,45 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
               const int64_t valid = p.b_rows - jbase;
               m &= valid >= 32 ? 0xffffffffu : (valid <= 0 ? 0u : ((1u << (int)valid) - 1u));
             }
+#if BSC_SCAN_V2
+            if (!row_ok) m = 0;  // rows past the last query (zero-filled by TMA) never compete
+#endif
             uint32_t um = __reduce_or_sync(0xffffffffu, m);
+#if BSC_SCAN_V2
+            // Four adjacent columns per TMEM read: while the lists of a work item are still filling up nearly every
+            // column is in the union, and the latency of the read (not the insertion) is what a column costs.
+            while (um) {
+              const int t0 = (__ffs(um) - 1) & ~3;
+              um &= ~(0xFu << t0);
+              uint32_t v4[4];
+              ptx::tmem_ld_32x32_x4(taddr + c * 32 + t0, v4);
+              ptx::tmem_ld_wait();
+#pragma unroll
+              for (int w = 0; w < 4; ++w) {
+                const int t = t0 + w;
+                const float s = __uint_as_float(v4[w]);
+                if (((m >> t) & 1u) && s > ts[KTOP - 1]) {
+                  const int j = jbase + t;
+                  int pos = KTOP - 1;
+#pragma unroll
+                  for (int u = KTOP - 1; u > 0; --u)
+                    if (pos == u && s > ts[u - 1]) pos = u - 1;
+#pragma unroll
+                  for (int u = KTOP - 1; u > 0; --u)
+                    if (u > pos) {
+                      ts[u] = ts[u - 1];
+                      ti[u] = ti[u - 1];
+                    }
+#pragma unroll
+                  for (int u = 0; u < KTOP; ++u)
+                    if (u == pos) {
+                      ts[u] = s;
+                      ti[u] = j;
+                    }
+                }
+              }
+            }
+#else
             while (um) {
               const int t = __ffs(um) - 1;
               um &= um - 1;
@@ -631,6 +686,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) tc_sim_kernel(const __grid_consta
                   }
               }
             }
+#endif
           }
         }
         // release the accumulator buffer to the MMA warp
@@ -981,11 +1037,38 @@ static void bank_tiling(int64_t nq, int64_t nb, int* n_iblk, int* n_jtile, int* 
       }
     }
   }
+#if BSC_SCAN_V2
+  {
+    // Few query blocks (a 32-query pass: one block): ONE work item per SM / CTA pair.  Every item starts with empty
+    // top-k lists, and until they have filled up nearly every column takes the insert path (32 queries share a warp, so
+    // the union of their insert columns stays dense for the first ~2000 rows): two items per SM pay that twice and
+    // hand twice as many lists to the merge.
+    const bool pairs = (*n_iblk % 2) == 0;
+    const int units = pairs ? num_sms() / 2 : num_sms();
+    const int per_chunk = pairs ? *n_iblk / 2 : *n_iblk;
+    if (per_chunk * 8 <= units) chunks = units / per_chunk;
+  }
+#endif
   if (chunks * NG < min_parts) chunks = (min_parts + NG - 1) / NG;  // screening pass: at least min_parts lists
   if (chunks > *n_jtile) chunks = *n_jtile > 0 ? *n_jtile : 1;
   *jpc = (*n_jtile + chunks - 1) / chunks;
   if (*jpc < 1) *jpc = 1;
   *n_jchunk = (*n_jtile + *jpc - 1) / *jpc;
+}
+
+// At most 64 queries: 8 or 16 per TMEM lane quarter instead of 32 / 64 in the first one or two (SimParams::spread)
+static int spread_queries(SimParams* p, const void* q, int64_t nq, int d) {
+  p->spread = 0;
+#if BSC_SCAN_V2 >= 2
+  if (nq > 64) return BSC_OK;
+  p->spread = nq <= 32 ? 8 : 16;
+  return make_tmap_2d(&p->tmap[2], q, BSC_BF16, nq, d, p->spread);
+#else
+  (void)q;
+  (void)nq;
+  (void)d;
+  return BSC_OK;
+#endif
 }
 
 size_t tc_bank_ws(int64_t nq, int64_t nb, int d, int k) {
@@ -1020,6 +1103,8 @@ int tc_bank_search(const void* q, int64_t nq, const void* bank, int64_t nb, int 
   p.pair_b[0] = 1;
   bank_tiling(nq, nb, &p.n_iblk, &p.n_jtile, &p.jpc, &p.n_jchunk);
   p.num_items = nb > 0 ? p.n_jchunk * p.n_iblk : 0;
+  rc = spread_queries(&p, q, nq, d);
+  if (rc) return rc;
   p.kblocks = d / BK;
   p.a_rows = nq;
   p.a_row0 = 0;
@@ -1068,6 +1153,8 @@ int tc_bank_screen(const void* q, int64_t nq, const void* bank, int64_t nb, int 
   p.pair_b[0] = 1;
   bank_tiling(nq, nb, &p.n_iblk, &p.n_jtile, &p.jpc, &p.n_jchunk, min_parts);
   p.num_items = p.n_jchunk * p.n_iblk;
+  rc = spread_queries(&p, q, nq, d);
+  if (rc) return rc;
   p.kblocks = d / BK;
   p.a_rows = nq;
   p.a_row0 = 0;

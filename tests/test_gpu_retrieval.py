@@ -47,6 +47,37 @@ def test_bf16_scan_matches_oracle_on_rounded_bank(nb, nq, d, k):
         assert gap.max() <= 2e-5
 
 
+@pytest.mark.parametrize("parts,nq,k", [(444, 32, 5), (888, 7, 8), (60, 40, 5), (3, 5000, 5), (500, 3, 1), (51, 2048, 5)])
+def test_topk_merge_matches_numpy(parts, nq, k):
+    """bsc_topk_merge (block-per-query kernel for few queries and many lists, warp-per-query kernel otherwise) against a
+    numpy sort on (score desc, id asc): scores drawn from a handful of values so that ties are everywhere, a third of
+    the entries padding (id -1), one query with fewer than k valid candidates."""
+    from bsc.ops import CudaOps
+
+    rng = np.random.default_rng(parts * 1000 + nq)
+    lowest = np.float32(-3.4028234663852886e38)
+    total = parts * k
+    scores = rng.integers(0, 12, size=(nq, total)).astype(np.float32) / 4
+    ids = np.stack([rng.permutation(total * 3)[:total] for _ in range(nq)]).astype(np.int64)
+    pad = rng.random((nq, total)) < 0.33
+    pad[0] = True
+    pad[0, :max(1, k - 2)] = False  # query 0: fewer than k candidates
+    ids[pad] = -1
+    scores[pad] = lowest
+    want_s = np.full((nq, k), lowest, dtype=np.float32)
+    want_i = np.full((nq, k), -1, dtype=np.int64)
+    for q in range(nq):
+        ok = np.nonzero(ids[q] >= 0)[0]
+        order = ok[np.lexsort((ids[q][ok], -scores[q][ok]))][:k]
+        want_s[q, :len(order)] = scores[q][order]
+        want_i[q, :len(order)] = ids[q][order]
+    cs = torch.from_numpy(scores.reshape(nq, parts, k).transpose(1, 0, 2).copy()).cuda()
+    ci = torch.from_numpy(ids.reshape(nq, parts, k).transpose(1, 0, 2).copy()).cuda()
+    got_s, got_i = CudaOps().topk_merge(cs, ci)
+    np.testing.assert_array_equal(got_i.cpu().numpy(), want_i)
+    np.testing.assert_array_equal(got_s.cpu().numpy(), want_s)
+
+
 def test_make_prediction_forms_and_labels():
     import bsc
 
