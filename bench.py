@@ -584,56 +584,62 @@ def bench_fp32x3(torch, bsc, _lib, device, flush, peaks, cpu_baseline):
 
     out = {"precision": "fp32x3 (BSC_MODE_TC16X3)", "dtype": "f32 inputs, fp16 hi+lo tensor-core terms, f32 accumulation"}
     for n, steps in ((CPU_SAMPLE_N, 20), (N_GLOBAL, 5)):
-        feats, labels = synth_loss_rows(torch, n, 0, n, device, torch.float32)
-        crit = bsc.ContrastiveLoss(torch.nn.CrossEntropyLoss(), SCALE, precision="fp32x3")
-
-        def step():
-            leaves = [f.detach().requires_grad_(True) for f in feats]
-            loss = crit(leaves[0], leaves[1], leaves[2], labels)
-            loss.backward()
-            return loss, leaves
-
-        for _ in range(3):
-            flush.zero_()
-            keep = step()
-        torch.cuda.synchronize()
-        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
-        for k in range(steps):
-            flush.zero_()
-            ev[k][0].record()
-            keep = step()
-            ev[k][1].record()
-        torch.cuda.synchronize()
-        ms = sum(a.elapsed_time(b) for a, b in ev) / steps
-        loss, leaves = keep
-        # check: every row at N = 4096, a strided sample of 1024 rows per modality at N = 32768
-        sample = None if n <= 4096 else torch.arange(0, n, n // 1024, device=device)[:1024]
-        ref_loss, ref_rows = loss_oracle.blockwise_loss_and_grad_rows(feats, labels, SCALE, sample_rows=sample,
-                                                                      device=device)
-        gmax = max(float(r.abs().max()) for r in ref_rows)
-        gerr = 0.0
-        for leaf, ref in zip(leaves, ref_rows):
-            got = (leaf.grad if sample is None else leaf.grad[sample]).double().cpu()
-            gerr = max(gerr, float((got - ref).abs().max()))
-        algo = 18.0 * float(n) * n * DIM
-        tf = algo / (ms * 1e-3) / 1e12
-        res = {"global_batch": n, "steps": steps, "ms_per_step": ms, "value": n / (ms * 1e-3), "unit": UNIT,
-               "algorithmic_tflops": tf, "frac_of_sustained_bf16_peak": tf / peaks["tflops_sustained"],
-               "executed_over_algorithmic": 4.0,  # three MMA terms per product and the weights sweep: 72 of 18 n N D
-               "backward_strategy": {4: "scatter", 3: "blocks", 0: "recompute"}.get(_lib.last_bwd_mode(), "?"),
-               "loss": float(loss.detach()),
-               "check": {"loss_rel": abs(float(loss.detach()) - float(ref_loss)) / abs(float(ref_loss)),
-                         "grad_rel": gerr / gmax, "grad_rows_checked_per_modality": int(ref_rows[0].shape[0]),
-                         "oracle": "oracle/loss_oracle.py blockwise fp64 closed form; grad_rel = max|dg| / max|g|"}}
-        if n == CPU_SAMPLE_N and cpu_baseline and cpu_baseline.get("value"):
-            res["vs_cpu_reference"] = {"same_config": True, "ratio": res["value"] / cpu_baseline["value"],
-                                       "cpu_value": cpu_baseline["value"], "cpu_kind": cpu_baseline.get("kind"),
-                                       "what": f"same N = {n}, same float32 inputs, both fwd+bwd of the three-modality "
-                                               f"loss; GPU inputs resident in HBM"}
-        out[f"n{n}"] = res
-        del keep, leaves, loss, feats, crit
+        try:
+            out[f"n{n}"] = _bench_fp32x3_size(torch, bsc, _lib, device, flush, peaks, cpu_baseline, loss_oracle, n, steps)
+        except Exception as e:  # one size failing must not hide the other
+            out[f"n{n}"] = {"error": f"{type(e).__name__}: {e}"}
         torch.cuda.empty_cache()
     return out
+
+
+def _bench_fp32x3_size(torch, bsc, _lib, device, flush, peaks, cpu_baseline, loss_oracle, n, steps):
+    feats, labels = synth_loss_rows(torch, n, 0, n, device, torch.float32)
+    crit = bsc.ContrastiveLoss(torch.nn.CrossEntropyLoss(), SCALE, precision="fp32x3")
+
+    def step():
+        leaves = [f.detach().requires_grad_(True) for f in feats]
+        loss = crit(leaves[0], leaves[1], leaves[2], labels)
+        loss.backward()
+        return loss, leaves
+
+    for _ in range(3):
+        flush.zero_()
+        keep = step()
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for k in range(steps):
+        flush.zero_()
+        ev[k][0].record()
+        keep = step()
+        ev[k][1].record()
+    torch.cuda.synchronize()
+    ms = sum(a.elapsed_time(b) for a, b in ev) / steps
+    loss, leaves = keep
+    # check: every row at N = 4096, a strided sample of 1024 rows per modality at N = 32768
+    sample = None if n <= 4096 else torch.arange(0, n, n // 1024, device=device)[:1024]
+    ref_loss, ref_rows = loss_oracle.blockwise_loss_and_grad_rows(feats, labels, SCALE, sample_rows=sample,
+                                                                  device=device)
+    gmax = max(float(r.abs().max()) for r in ref_rows)
+    gerr = 0.0
+    for leaf, ref in zip(leaves, ref_rows):
+        got = (leaf.grad if sample is None else leaf.grad[sample]).double().cpu()
+        gerr = max(gerr, float((got - ref).abs().max()))
+    algo = 18.0 * float(n) * n * DIM
+    tf = algo / (ms * 1e-3) / 1e12
+    res = {"global_batch": n, "steps": steps, "ms_per_step": ms, "value": n / (ms * 1e-3), "unit": UNIT,
+           "algorithmic_tflops": tf, "frac_of_sustained_bf16_peak": tf / peaks["tflops_sustained"],
+           "executed_over_algorithmic": 4.0,  # three MMA terms per product and the weights sweep: 72 of 18 n N D
+           "backward_strategy": {4: "scatter", 3: "blocks", 0: "recompute"}.get(_lib.last_bwd_mode(), "?"),
+           "loss": float(loss.detach()),
+           "check": {"loss_rel": abs(float(loss.detach()) - float(ref_loss)) / abs(float(ref_loss)),
+                     "grad_rel": gerr / gmax, "grad_rows_checked_per_modality": int(ref_rows[0].shape[0]),
+                     "oracle": "oracle/loss_oracle.py blockwise fp64 closed form; grad_rel = max|dg| / max|g|"}}
+    if n == CPU_SAMPLE_N and cpu_baseline and cpu_baseline.get("value"):
+        res["vs_cpu_reference"] = {"same_config": True, "ratio": res["value"] / cpu_baseline["value"],
+                                   "cpu_value": cpu_baseline["value"], "cpu_kind": cpu_baseline.get("kind"),
+                                   "what": f"same N = {n}, same float32 inputs, both fwd+bwd of the three-modality "
+                                           f"loss; GPU inputs resident in HBM"}
+    return res
 
 
 def bench_retrieval(args, torch, dist, bsc, _lib, device, rank, world, peaks):

@@ -259,8 +259,9 @@ InfoNceBwdWs infonce_bwd_layout(const bsc_infonce_desc* p) {
 static size_t exchange_bytes_of(const bsc_infonce_desc* p) {
   if (!mode_is_tc(p->mode) || p->bwd_mode != BSC_BWD_SCATTER) return 0;
   const int m = present_count(p, nullptr);
-  return (size_t)p->world * (size_t)(m * (m - 1) / 2) * (size_t)(p->n_local > 0 ? p->n_local : 1) * p->d *
-         sizeof(float);
+  // one slot per (source rank, K part of the scattered GEMMs: 1 except in BSC_MODE_TC16X3) and unordered pair
+  return (size_t)p->world * (size_t)tc_bwd_mn_kparts(p) * (size_t)(m * (m - 1) / 2) *
+         (size_t)(p->n_local > 0 ? p->n_local : 1) * p->d * sizeof(float);
 }
 
 static int check_desc(const bsc_infonce_desc* p, const char* who) {
@@ -641,7 +642,7 @@ int bsc_infonce_bwd_finish(const bsc_infonce_desc* p, const float* aux, const vo
       } else {             // MN-major job of pair (y, a): one partial sum per source rank in the exchange buffer
         s.src = (const float*)own_exchange + (int64_t)pair_index[a][y] * slab;
         s.stride = (int64_t)np * slab;
-        s.nparts = p->world;
+        s.nparts = p->world * tc_bwd_mn_kparts(p);
       }
       ++slot;
     }

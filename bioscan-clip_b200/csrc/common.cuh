@@ -11,11 +11,14 @@
 
 #include "../../include/bsc_hot.h"
 
-// Bank scan with few queries (32-query passes over a shard), second layout: one work item per SM, candidate re-reads in
-// groups of four TMEM columns, block-per-query merge of the candidate lists.  0 = the round-1 layout (two items per SM,
-// single-column re-reads, warp-per-query merge), kept for A/B builds (python build.py --variant).
+// Bank scan with few queries (32-query passes over a shard).  1: one work item per SM, candidate re-reads in groups of
+// four TMEM columns, block-per-query merge of the candidate lists; 2 (default): also at most 64 queries spread over the
+// four TMEM lane quarters (SimParams::spread).  0 = the earlier layout (two items per SM, single-column re-reads,
+// warp-per-query merge), kept for A/B builds (python build.py --variant v0 -DBSC_SCAN_V2=0).  Measured on one B200,
+// 32 queries x a 625k-row shard: scan 305 / 249 / 172 us, whole search 682 / 296 / 211 us for 0 / 1 / 2
+// (profiles/r2_scan_v2_ab.txt).
 #ifndef BSC_SCAN_V2
-#define BSC_SCAN_V2 0
+#define BSC_SCAN_V2 2
 #endif
 
 namespace bsc {
@@ -165,6 +168,7 @@ int tc_bwd_duo_jsplit(const bsc_infonce_desc* p);
 size_t tc_bwd_gimg_bytes(const bsc_infonce_desc* p);
 void tc_bwd_matrix_dims(const bsc_infonce_desc* d, int* n_iblk_pad, int* n_j64);
 int tc_bwd_gemm_kparts(const bsc_infonce_desc* d);
+int tc_bwd_mn_kparts(const bsc_infonce_desc* d);  // K parts of the scattered GEMMs = exchange slots per source rank
 int tc_bwd_weights(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, const float* aux, int* n_pairs,
                    int* pairs_a, int* pairs_b, cudaStream_t st);
 struct ScatterDst {

@@ -79,9 +79,10 @@ struct RevParams {
   float job_fmul[MAX_JOBS];                    // ... times a constant (undoes the 2^8 of the X3 unit rows)
   int img_r, img_c;
   int num_items, d, n_clusters;
-  // scatter destinations: exchange buffer of rank q = float [world][n_xslots][n_local][d]
+  // scatter destinations: exchange buffer of rank q = float [world * mn_kparts][n_xslots][n_local][d]
   float* peer[kMaxPeers];
   int world, rank, n_xslots;
+  int mn_kparts;  // K parts of a scattered job: exchange slot of (source rank, part) = rank * mn_kparts + part
   int64_t n_local;
   const float* gsbuf;
   int sched_off[MAX_CLUSTERS + 1];  // cluster c runs sched[sched_off[c]] .. sched[sched_off[c + 1] - 1], in this order
@@ -301,7 +302,8 @@ __global__ void __launch_bounds__(384, 1) tc_bwd_rev_kernel(const __grid_constan
         // (peer stores travel over NVLink: 16-byte stores to 32 different rows would waste most of every packet).
         // Staging slot of (row r, 16-byte chunk u) = u ^ ((r >> 1) & 3): conflict-free both ways.
         const int64_t slab = p.n_local * (int64_t)p.d;
-        const int64_t src_off = ((int64_t)p.rank * p.n_xslots + p.job_xslot[job]) * slab + BN * c;
+        const int64_t src_off =
+            (((int64_t)p.rank * p.mn_kparts + part) * p.n_xslots + p.job_xslot[job]) * slab + BN * c;
         const int t4 = lane & 3;
 #pragma unroll 1
         for (int cc = grp * 2 * CPG; cc < grp * 2 * CPG + 2 * CPG; ++cc) {  // 16-column chunks
@@ -364,12 +366,10 @@ static int rev_launch(RevParams& p, bool wide, cudaStream_t st) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  timing_begin(3, st);
   if (wide)
     BSC_CUDA(cudaLaunchKernelEx(&cfg, tc_bwd_rev_kernel<1>, p));
   else
     BSC_CUDA(cudaLaunchKernelEx(&cfg, tc_bwd_rev_kernel<0>, p));
-  timing_end(3, st);
   BSC_LAUNCH_CHECK("tc_bwd_rev_kernel");
   return BSC_OK;
 }
@@ -404,6 +404,22 @@ int tc_bwd_gemm_kparts(const bsc_infonce_desc* d) {
     if (s < want) s = (int)want;
   }
   return s;
+}
+
+// K split of the MN-major (scattered) gradient GEMMs, whose K runs over the LOCAL rows: 1 part (one exchange slot per
+// source rank), except in BSC_MODE_TC16X3, where the same cap on the accumulation chains applies (measured at N = 32768
+// on one GPU with a single 32768-row chain: gradient error 3e-5 .. 6e-5 of max |g| instead of < 1e-5).  Every part is
+// one more exchange slot per source rank; combine adds the world * parts slots in (rank, part) order.
+int tc_bwd_mn_kparts(const bsc_infonce_desc* d) {
+  if (d->mode != BSC_MODE_TC16X3) return 1;
+  int64_t want = (d->n_local + kX3ChainCols - 1) / kX3ChainCols;
+  const int64_t nk = (d->n_local + 63) / 64;
+  int64_t cap = 32 / (d->world > 0 ? d->world : 1);
+  if (cap < 1) cap = 1;
+  if (want > cap) want = cap;
+  if (want > nk) want = nk;
+  if (want < 1) want = 1;
+  return (int)want;
 }
 
 static int tc_bwd_gemm_kparts_tc16(const bsc_infonce_desc* d) {
@@ -478,6 +494,7 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, con
   p.world = dst.world;
   p.rank = dst.rank;
   p.n_xslots = n_pairs;
+  p.mn_kparts = tc_bwd_mn_kparts(d);
   p.n_local = n;
   for (int r = 0; r < dst.world && r < kMaxPeers; ++r) p.peer[r] = dst.peer[r];
   const int64_t slab = n * (int64_t)d->d;
@@ -527,7 +544,7 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, con
     p.job_pair[job] = q;
     p.job_mn[job] = 1;
     p.job_nk[job] = nk_loc;
-    p.job_kparts[job] = 1;
+    p.job_kparts[job] = p.mn_kparts;
     p.job_rows[job] = N;
     p.job_out[job] = nullptr;
     p.job_xslot[job] = q;
@@ -571,82 +588,94 @@ int tc_bwd_gemms(const bsc_infonce_desc* d, const InfoNceBwdWs& L, char* ws, con
              rank == o.rank && kparts == o.kparts && sms == o.sms && terms == o.terms;
     }
   };
-  struct SchedCache {
-    SchedKey key{};
-    bool valid = false;
+  // One launch carries at most MAX_SCHED items in its parameters; larger problems (BSC_MODE_TC16X3 at N = 32768: 32 K
+  // parts per row block) run as several launches over consecutive slices of the item list, each with its own schedule.
+  struct Batch {
     int num_items = 0, n_clusters = 0;
     int off[MAX_CLUSTERS + 1];
     std::vector<uint32_t> sched;
   };
+  struct SchedCache {
+    SchedKey key{};
+    bool valid = false;
+    std::vector<Batch> batches;
+  };
   static thread_local SchedCache cache;
   const SchedKey key{n, N, d->d, n_pairs, L.mode, dst.world, dst.rank, L.kparts, device_sm_count(), p.terms};
-  if (cache.valid && cache.key == key) {
-    memcpy(p.sched_off, cache.off, sizeof(cache.off));
-    memcpy(p.sched, cache.sched.data(), cache.sched.size() * sizeof(uint32_t));
-    p.num_items = cache.num_items;
-    p.n_clusters = cache.n_clusters;
-    return rev_launch(p, wide, st);
-  }
-  std::vector<Item> items;
-  for (int kind = 0; kind < 2; ++kind) {  // 0 = scattered (MN-major), 1 = local (K-major)
-    for (int z = 0; z < job; ++z) {
-      if ((p.job_out[z] == nullptr) != (kind == 0)) continue;
-      const int nmb = job_nmb[z], kp = p.job_kparts[z];
-      const int rot = (kind == 0 && dst.world > 1) ? (int)(((int64_t)(dst.rank + 1) % dst.world) * nmb / dst.world) : 0;
-      for (int mbi = 0; mbi < nmb; ++mbi)
-        for (int part = 0; part < kp; ++part) {
-          const int nkb = (int)((int64_t)(part + 1) * p.job_nk[z] / kp - (int64_t)part * p.job_nk[z] / kp);
-          for (int c = 0; c < nchunk; ++c)
-            items.push_back(Item{pack_item(z, c, part, (mbi + rot) % nmb), nkb * p.terms + 6 /* fill + drain */, kind});
-        }
-    }
-  }
-  const size_t total = items.size();
-  BSC_REQUIRE(total <= (size_t)MAX_SCHED, BSC_EUNSUPPORTED,
-              "tc_bwd_gemms: %zu work items exceed the schedule capacity %d (batch too large for the stored-weight "
-              "backward)", total, MAX_SCHED);
-  int clusters = device_sm_count() / 2;
-  if (clusters > MAX_CLUSTERS) clusters = MAX_CLUSTERS;
-  if ((size_t)clusters > total) clusters = (int)total;
-  if (clusters < 1) clusters = 1;
-  {
-    std::stable_sort(items.begin(), items.end(), [](const Item& x, const Item& y) { return x.cost > y.cost; });
-    std::vector<std::vector<Item>> per(clusters);
-    std::vector<long long> load(clusters, 0);
-    for (const Item& it : items) {
-      int best = 0;
-      for (int cl = 1; cl < clusters; ++cl)
-        if (load[cl] < load[best]) best = cl;
-      per[best].push_back(it);
-      load[best] += it.cost;
-    }
-    int w = 0;
-    for (int cl = 0; cl < clusters; ++cl) {
-      p.sched_off[cl] = w;
-      std::vector<Item> lst[2];
-      for (const Item& it : per[cl]) lst[it.kind].push_back(it);
-      // proportional interleave of the two kinds, the starting kind alternating between neighbouring cluster pairs
-      const int first = (cl >> 1) & 1;
-      size_t pos[2] = {0, 0};
-      const size_t n0 = lst[first].size(), n1 = lst[first ^ 1].size();
-      for (size_t t = 0; t < n0 + n1; ++t) {
-        // take from `first` while its share of the emitted items is not ahead of its share of the total
-        const bool take_first = pos[1] >= n1 || (pos[0] < n0 && pos[0] * (n0 + n1) <= t * n0);
-        const int kind = take_first ? first : first ^ 1;
-        p.sched[w++] = lst[kind][pos[take_first ? 0 : 1]++].code;
+  if (!(cache.valid && cache.key == key)) {
+    std::vector<Item> items;
+    for (int kind = 0; kind < 2; ++kind) {  // 0 = scattered (MN-major), 1 = local (K-major)
+      for (int z = 0; z < job; ++z) {
+        if ((p.job_out[z] == nullptr) != (kind == 0)) continue;
+        const int nmb = job_nmb[z], kp = p.job_kparts[z];
+        const int rot =
+            (kind == 0 && dst.world > 1) ? (int)(((int64_t)(dst.rank + 1) % dst.world) * nmb / dst.world) : 0;
+        for (int mbi = 0; mbi < nmb; ++mbi)
+          for (int part = 0; part < kp; ++part) {
+            const int nkb = (int)((int64_t)(part + 1) * p.job_nk[z] / kp - (int64_t)part * p.job_nk[z] / kp);
+            for (int c = 0; c < nchunk; ++c)
+              items.push_back(
+                  Item{pack_item(z, c, part, (mbi + rot) % nmb), nkb * p.terms + 6 /* fill + drain */, kind});
+          }
       }
     }
-    for (int cl = clusters; cl <= MAX_CLUSTERS; ++cl) p.sched_off[cl] = w;
+    const size_t total = items.size();
+    const size_t n_batches = total ? (total + MAX_SCHED - 1) / MAX_SCHED : 1;
+    cache.valid = false;
+    cache.batches.assign(n_batches, Batch{});
+    for (size_t bi = 0; bi < n_batches; ++bi) {
+      Batch& B = cache.batches[bi];
+      const size_t lo = bi * total / n_batches, hi = (bi + 1) * total / n_batches;
+      std::vector<Item> part_items(items.begin() + lo, items.begin() + hi);
+      int clusters = device_sm_count() / 2;
+      if (clusters > MAX_CLUSTERS) clusters = MAX_CLUSTERS;
+      if ((size_t)clusters > part_items.size()) clusters = (int)part_items.size();
+      if (clusters < 1) clusters = 1;
+      std::stable_sort(part_items.begin(), part_items.end(), [](const Item& x, const Item& y) { return x.cost > y.cost; });
+      std::vector<std::vector<Item>> per(clusters);
+      std::vector<long long> load(clusters, 0);
+      for (const Item& it : part_items) {
+        int best = 0;
+        for (int cl = 1; cl < clusters; ++cl)
+          if (load[cl] < load[best]) best = cl;
+        per[best].push_back(it);
+        load[best] += it.cost;
+      }
+      B.sched.reserve(part_items.size());
+      for (int cl = 0; cl < clusters; ++cl) {
+        B.off[cl] = (int)B.sched.size();
+        std::vector<Item> lst[2];
+        for (const Item& it : per[cl]) lst[it.kind].push_back(it);
+        // proportional interleave of the two kinds, the starting kind alternating between neighbouring cluster pairs
+        const int first = (cl >> 1) & 1;
+        size_t pos[2] = {0, 0};
+        const size_t n0 = lst[first].size(), n1 = lst[first ^ 1].size();
+        for (size_t t = 0; t < n0 + n1; ++t) {
+          // take from `first` while its share of the emitted items is not ahead of its share of the total
+          const bool take_first = pos[1] >= n1 || (pos[0] < n0 && pos[0] * (n0 + n1) <= t * n0);
+          const int kind = take_first ? first : first ^ 1;
+          B.sched.push_back(lst[kind][pos[take_first ? 0 : 1]++].code);
+        }
+      }
+      for (int cl = clusters; cl <= MAX_CLUSTERS; ++cl) B.off[cl] = (int)B.sched.size();
+      B.num_items = (int)part_items.size();
+      B.n_clusters = clusters;
+    }
+    cache.key = key;
+    cache.valid = true;
   }
-  p.n_clusters = clusters;
-  cache.key = key;
-  cache.num_items = (int)total;
-  cache.n_clusters = clusters;
-  memcpy(cache.off, p.sched_off, sizeof(cache.off));
-  cache.sched.assign(p.sched, p.sched + total);
-  cache.valid = true;
-  p.num_items = (int)total;
-  return rev_launch(p, wide, st);
+  timing_begin(3, st);  // all launches of the gradient GEMMs (one unless the schedule had to be cut)
+  for (const Batch& B : cache.batches) {
+    if (B.num_items == 0) continue;
+    memcpy(p.sched_off, B.off, sizeof(B.off));
+    memcpy(p.sched, B.sched.data(), B.sched.size() * sizeof(uint32_t));
+    p.num_items = B.num_items;
+    p.n_clusters = B.n_clusters;
+    rc = rev_launch(p, wide, st);
+    if (rc) return rc;
+  }
+  timing_end(3, st);
+  return BSC_OK;
 }
 
 }  // namespace bsc

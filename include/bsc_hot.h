@@ -212,8 +212,10 @@ typedef struct bsc_infonce_plan_t {
   int32_t reserved;
   size_t fwd_workspace_bytes;  /* bsc_infonce_fwd                                                                */
   size_t bwd_workspace_bytes;  /* bsc_infonce_bwd_partials / _finish (allocate only when a backward will run)    */
-  size_t exchange_bytes;       /* BSC_BWD_SCATTER: this rank's exchange buffer float[world][pairs][n_local][d], mapped
-                                  into every peer when world > 1 (torch symmetric memory); 0 for the other modes   */
+  size_t exchange_bytes;       /* BSC_BWD_SCATTER: this rank's exchange buffer float[world * parts][pairs][n_local][d]
+                                  (parts = 1; BSC_MODE_TC16X3: one slot per 1024-row accumulation chain of a source
+                                  rank's rows), mapped into every peer when world > 1 (torch symmetric memory); 0 for
+                                  the other modes                                                                 */
 } bsc_infonce_plan_t;
 
 /* A statistics RECORD: bsc_infonce_stats_len(n_global) floats = 6 ordered-pair sum-exp rows of n_global | 4 scalars |

@@ -397,15 +397,30 @@ def test_fp32x3_tensor_core_mode_matches_fp64_closed_form(n, d, present, labels,
         assert rel_grad <= X3_TOL, rel_grad
 
 
-@pytest.mark.parametrize("world,mode", [(2, "scatter"), (4, "scatter"), (4, "blocks")])
-def test_fp32x3_ranks_replayed_on_one_gpu(world, mode):
+def test_fp32x3_config3_32768_against_blockwise_oracle():
+    """The headline batch (N = 32768, d = 768, full float32 inputs) in the fp32x3 mode: loss and 1024 gradient rows per
+    modality against the block-wise fp64 closed form.  At this size the K-major gradient GEMMs are cut into 32 chains per
+    row block -- 25344 work items, more than one launch's schedule holds: the gradient GEMMs run as several launches."""
+    n = 32768
+    feats, lab = loss_inputs(n, 768, seed=11, labels="multi")
+    rows = torch.arange(3, n, 31)[:1024]
+    rel_loss, worst = _sampled_check(feats, lab, lambda: _run(feats, lab, "fp32x3"), rows, 2e-5)
+    print(f"fp32x3 N=32768: loss rel err {rel_loss:.2e}, gradient max err / max|g| {worst:.2e}")
+    assert rel_loss <= X3_TOL, rel_loss
+
+
+@pytest.mark.parametrize("world,mode,n", [(2, "scatter", 1024), (4, "scatter", 1024), (4, "blocks", 1024),
+                                          (2, "scatter", 4096)])
+def test_fp32x3_ranks_replayed_on_one_gpu(world, mode, n):
     """The W-rank job of the fp32x3 mode (rows gathered with plain collectives, scatter backward over the exchange
-    buffers) replayed on one GPU: loss bits equal on every rank, loss and gradients of the whole batch at 1e-5."""
+    buffers) replayed on one GPU: loss bits equal on every rank, loss and gradients of the whole batch at 1e-5.
+    n = 4096 on 2 ranks: 2048 local rows = two accumulation chains per scattered GEMM, i.e. two exchange slots per
+    source rank."""
     from bsc._lib import BWD_NAMES, MODE_TC16X3
     from bsc.loss import _default_ops
     from tests.stripe import replay
 
-    n, d = 1024, 768
+    d = 768
     feats, lab = loss_inputs(n, d, seed=n + world, labels="multi", normalised=False)
     ref_loss, ref_grads = loss_oracle.closed_form_grads(feats, lab)
     losses, grads, resolved = replay(_default_ops(), world, [f.cuda() for f in feats], lab.cuda(), BWD_NAMES[mode],
