@@ -135,7 +135,7 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-TRAFFIC_GEMMS = 2.425e10  # ncu: 23.66 GB read + 0.59 GB written per launch of tc_bwd_rev_kernel<1> (profiles/r1_bwd_gemms.txt)
+TRAFFIC_GEMMS = 1.808e10  # ncu --set full: 17.49 GB read + 0.59 GB written per launch of tc_bwd_rev_kernel<1> (profiles/r2_step_kernels_n1.txt)
 
 
 def synth_loss_rows(torch, n_global, row0, n_local, device, dtype):
@@ -751,7 +751,9 @@ def bench_retrieval(args, torch, dist, bsc, _lib, device, rank, world, peaks):
     res["roofline"] = {"bound": "hbm", "achieved": bytes_pass / (k32 * 1e-3) / 1e9 if k32 > 0 else None,
                        "peak": peaks["hbm_gbs"], "unit": "GB/s per GPU",
                        "frac": bytes_pass / (k32 * 1e-3) / 1e9 / peaks["hbm_gbs"] if k32 > 0 else None,
-                       "traffic": None, "kernel": "tc_sim_kernel<EPI_TOPK> (32 queries x one bf16 shard)",
+                       "traffic": (7.680e9 if (world == 1 and nb == 5_000_000) else None),  # ncu: dram bytes read = the bank
+                       "kernel": "tc_sim_kernel<EPI_TOPK> (32 queries x one bf16 shard)",
+                       "note": "peak = the measured COPY bandwidth (reads and writes mixed); a read-only stream can exceed it",
                        "kernel_ms": k32, "algorithmic_bytes_per_launch": bytes_pass,
                        "peak_source": peaks["source"] + " hbm_gbs"}
     # ---- e2e: host queries in (numpy, pageable), host ids out, through IndexFlatIP.search + the cross-rank merge ----
