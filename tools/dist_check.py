@@ -53,7 +53,7 @@ def run(crit, feats, labels, *extra):
     return loss.detach(), [l.grad for l in leaves]
 
 
-def errors(loss, grads):
+def errors(loss, grads, ref_loss=ref_loss, ref_grads=ref_grads, gmax=gmax):
     dl = abs(float(loss) - float(ref_loss)) / abs(float(ref_loss))
     if n <= 4096:
         dg = max((g.double().cpu() - r[sl]).abs().max().item() for g, r in zip(grads, ref_grads))
@@ -114,6 +114,31 @@ assert float(loss_a.detach()) == float(base[0]) and float(loss_b.detach()) == fl
 for got, want in ((la, base[1]), (lb, base_other[1])):
     for leaf, g in zip(got, want):
         assert torch.equal(leaf.grad, g), "delayed backward read operands that a later forward had overwritten"
+
+# float32-grade tensor-core mode (precision="fp32x3") on real ranks: full float32 inputs (not 16-bit representable), rows
+# gathered with NCCL, scatter backward over the peer-mapped exchange buffers / blocks backward without any exchange;
+# bound 1e-5 against the fp64 closed form
+X3_TOL = 1e-5
+feats32, _ = bench.synth_loss_rows(torch, n, 0, n, dev, torch.float32)
+local32 = [f[sl].contiguous() for f in feats32]
+if n <= 4096:
+    ref32_loss, ref32_grads = loss_oracle.closed_form_grads([f.cpu() for f in feats32], labels_all.cpu(), bench.SCALE)
+else:
+    ref32_loss, ref32_grads = loss_oracle.blockwise_loss_and_grad_rows(feats32, labels_all, bench.SCALE,
+                                                                       sample_rows=ref_rows, device=dev)
+gmax32 = max(g.abs().max().item() for g in ref32_grads)
+x3 = {}
+for name, kw in (("fp32x3-scatter", dict(backward="auto")), ("fp32x3-blocks", dict(backward="blocks"))):
+    crit = bsc.ClipLoss(rank=rank, world_size=world, precision="fp32x3", **kw)
+    for rep in range(2):
+        loss, grads = run(crit, local32, local_labels, bench.SCALE)
+    dl, dg = errors(loss, grads, ref32_loss, ref32_grads, gmax32)
+    x3[name] = (float(loss), _lib.last_bwd_mode())
+    print(f"rank {rank} {name}: backward mode {_lib.last_bwd_mode()} loss {float(loss):.7f} rel err {dl:.2e} "
+          f"gradient max err / max|g| {dg:.2e}", flush=True)
+    assert dl <= X3_TOL and dg <= X3_TOL, (name, dl, dg)
+assert x3["fp32x3-scatter"][1] == _lib.BWD_SCATTER and x3["fp32x3-blocks"][1] == _lib.BWD_BLOCKS
+assert x3["fp32x3-scatter"][0] == x3["fp32x3-blocks"][0], "both strategies must give the same loss bits"
 dist.barrier()
 if rank == 0:
     print(f"dist_check ok: world {world} n {n}")
