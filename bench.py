@@ -694,12 +694,8 @@ def bench_retrieval(args, torch, dist, bsc, _lib, device, rank, world, peaks):
 
     def search(index, queries):
         s, i = index.search_device(queries, 5)
-        if world > 1:
-            cs = [torch.empty_like(s) for _ in range(world)]
-            ci = [torch.empty_like(i) for _ in range(world)]
-            dist.all_gather(cs, s)
-            dist.all_gather(ci, i)
-            s, i = index._ops.topk_merge(torch.stack(cs), torch.stack(ci))
+        if world > 1:  # one all_gather of the packed per-rank lists + bsc_topk_merge
+            s, i = bsc.merge_across_ranks(s, i, ops=index._ops)
         return s, i
 
     _lib.set_timing(True)

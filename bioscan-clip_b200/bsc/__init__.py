@@ -6,8 +6,8 @@ Host side in Python/PyTorch (device memory, streams, torch.distributed), arithme
 from ._lib import BscError, LIB_PATH  # noqa: F401
 from .extract import get_feature_and_label, get_features_and_label  # noqa: F401
 from .loss import ClipLoss, ContrastiveLoss  # noqa: F401
-from .retrieval import IndexFlatIP, make_prediction  # noqa: F401
+from .retrieval import IndexFlatIP, make_prediction, merge_across_ranks  # noqa: F401
 from .taxonomy import TaxonomyEval, top_k_macro_accuracy, top_k_micro_accuracy  # noqa: F401
 
-__all__ = ["ContrastiveLoss", "ClipLoss", "IndexFlatIP", "make_prediction", "TaxonomyEval", "top_k_micro_accuracy",
+__all__ = ["ContrastiveLoss", "ClipLoss", "IndexFlatIP", "make_prediction", "merge_across_ranks", "TaxonomyEval", "top_k_micro_accuracy",
            "top_k_macro_accuracy", "get_feature_and_label", "get_features_and_label", "BscError", "LIB_PATH"]

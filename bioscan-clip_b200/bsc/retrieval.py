@@ -152,6 +152,31 @@ class IndexFlatIP:
         return s.cpu().numpy(), i.cpu().numpy()
 
 
+def merge_across_ranks(scores: torch.Tensor, ids: torch.Tensor, ops=None, group=None):
+    """One process per GPU, the bank rows sharded over the ranks (every rank's index built with ``base_id`` = its shard's
+    first global row), the queries replicated: this rank's ``[nq, k]`` result of ``IndexFlatIP.search_device`` -> the
+    global ``[nq, k]`` on every rank.  ONE ``all_gather_into_tensor`` carries both lists (the score bits and the id of a
+    candidate travel as an int64 pair), then ``bsc_topk_merge`` orders the world * k candidates of every query
+    (score desc, id asc) -- the merge faiss does inside ``search`` when an index is sharded."""
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group)
+    if world == 1:
+        return scores, ids
+    if ops is None:
+        from .ops import CudaOps
+
+        ops = CudaOps()
+    packed = torch.stack([scores.contiguous().view(torch.int32).to(torch.int64), ids.to(torch.int64)], dim=-1)
+    nq = packed.shape[0]
+    out = torch.empty((world * nq,) + tuple(packed.shape[1:]), dtype=torch.int64, device=packed.device)
+    dist.all_gather_into_tensor(out, packed.contiguous(), group=group)
+    out = out.view((world, nq) + tuple(packed.shape[1:]))
+    cand_s = out[..., 0].contiguous().to(torch.int32).view(torch.float32)
+    cand_i = out[..., 1].contiguous()
+    return ops.topk_merge(cand_s, cand_i)
+
+
 def _normalized_f32(ops, x, device) -> torch.Tensor:
     """sklearn ``normalize(x, norm='l2', axis=1).astype(np.float32)`` (inference_and_eval.py:416-417) on the device.
     float64 input (what inference_epoch.py:67 produces) is normalised IN float64 and rounded once, like the reference;

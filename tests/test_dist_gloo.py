@@ -134,3 +134,59 @@ def test_two_ranks_missing_modality_and_gather_with_grad():
         for k in (0, 2):
             ref = 2.0 * ref_grads[k][r * 12:(r + 1) * 12].numpy()  # gather_with_grad: world_size x the slice
             assert np.abs(grads[k] - ref).max() <= 1e-5 * np.abs(ref).max()
+
+
+class _TorchMerge:
+    """CPU stand-in for CudaOps.topk_merge: [parts, nq, k] candidate lists -> [nq, k] by (score desc, id asc)."""
+
+    def topk_merge(self, cand_s, cand_i):
+        parts, nq, k = cand_s.shape
+        s = cand_s.permute(1, 0, 2).reshape(nq, parts * k).numpy()
+        i = cand_i.permute(1, 0, 2).reshape(nq, parts * k).numpy()
+        out_s, out_i = np.empty((nq, k), np.float32), np.empty((nq, k), np.int64)
+        for q in range(nq):
+            order = np.lexsort((i[q], -s[q].astype(np.float64)))[:k]
+            out_s[q], out_i[q] = s[q][order], i[q][order]
+        return torch.from_numpy(out_s), torch.from_numpy(out_i)
+
+
+def _merge_worker(rank, world, port, bank, queries, ret):
+    import sys
+
+    for p in (ROOT, os.path.join(ROOT, "bioscan-clip_b200")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import torch.distributed as dist
+
+    from bsc.retrieval import merge_across_ranks
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    nb = bank.shape[0] // world
+    shard = bank[rank * nb:(rank + 1) * nb]
+    sc = queries @ shard.T  # this rank's shard, ids offset by its first row; negative scores included
+    s, i = torch.sort(sc, dim=1, descending=True, stable=True)
+    s, i = s[:, :5].contiguous(), (i[:, :5] + rank * nb).contiguous()
+    gs, gi = merge_across_ranks(s, i, ops=_TorchMerge())
+    ret[rank] = (gs.numpy(), gi.numpy())
+    dist.destroy_process_group()
+
+
+def test_two_ranks_merge_of_sharded_search_results():
+    """bsc.merge_across_ranks: the per-rank top-k lists travel in ONE all_gather (score bits + id packed in int64
+    pairs) and come out as the top-k of the whole bank on every rank, negative scores and duplicate rows (ties ->
+    lowest id) included.  The merge kernel itself is replaced by a numpy sort here (its GPU test is test_gpu_retrieval)."""
+    g = torch.Generator().manual_seed(5)
+    bank = torch.randn(64, 16, generator=g)
+    bank[40] = bank[7]  # an exact duplicate on the other shard
+    queries = torch.cat([bank[[7, 3, 50]] + 0.01 * torch.randn(3, 16, generator=g), -bank[[1]]])
+    full = queries @ bank.T
+    want_i = np.stack([np.lexsort((np.arange(64), -full[q].double().numpy()))[:5] for q in range(4)])
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_merge_worker, args=(2, 29641, bank, queries, ret), nprocs=2, join=True)
+    for r in range(2):
+        gs, gi = ret[r]
+        np.testing.assert_array_equal(gi, want_i)
+        np.testing.assert_allclose(gs, np.take_along_axis(full.numpy(), want_i, axis=1), rtol=0, atol=1e-6)
