@@ -2,18 +2,26 @@
 """bench.py -- the driver's measurement contract for the BIOSCAN-CLIP contrastive hot path.
 
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one process per GPU)
-    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path (oracle port) on host cores
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's own loss module on the host cores
 
 One "step" = one fwd+bwd of the three-modality InfoNCE loss (image, DNA, text; 768-d; bf16 inputs; labels =
 arange as util/dataset.py:147) at GLOBAL batch 32768 -- the configuration BASELINE.json's metric is quoted on.
 With N ranks every rank owns 32768/N rows (strong scaling: the global batch is fixed) and the step includes the
-all_gather of the normalised rows and the all_reduce of the sum-exp statistics.
+gather of the rows, the statistics exchange and the reduce-scatter of the partial gradients (NVLink peer memory).
 
-Printed (rank 0, ONE JSON line): metric/value/unit (samples/s, inputs resident in HBM, CUDA-event timed, max over
-ranks), e2e (same metric with pinned-host inputs copied in and loss + gradients copied out inside the timed
-region, the copies of neighbouring steps overlapped with compute on separate streams), roofline of the dominant kernel (the backward sweep; algorithmic FLOPs / CUDA-event kernel time /
-MEASURED_PEAKS.json), cpu_baseline (oracle port on the host cores, bounded sample), clocks, gpu_launches, and a
-`retrieval` object with the second half of the metric (queries/s of the bank scan).
+Printed (rank 0, ONE JSON line):
+  metric / value / unit   samples/s, inputs resident in HBM, CUDA-event timed, max over ranks
+  e2e                     the same with pinned-host inputs copied in and loss + gradients copied out inside the timed
+                          region (copies of neighbouring steps overlapped with compute on separate streams)
+  roofline, step_roofline the dominant kernel (gradient GEMMs) and the whole step: algorithmic FLOPs / CUDA-event time /
+                          MEASURED_PEAKS.json
+  check                   one more step against the block-wise fp64 oracle at the full size (loss, sampled gradient rows)
+  cpu_baseline            the reference module (oracle/_ref) on the host cores, N = 4096 sample
+  fp32x3 (N = 1)          float32 inputs at float32-grade precision on the tensor cores: N = 4096 (same config as the CPU
+                          arm -> a same-config ratio) and N = 32768, each with its own oracle check
+  retrieval               the second half of the metric: 100k queries x 5M bank (exact float32 and bf16 modes), the HBM
+                          roofline of the 32-query pass, host-to-host e2e, ids compared with the oracle on the full bank
+  clocks, gpu_launches, gather, backward_strategy, step_ms
 """
 from __future__ import annotations
 
