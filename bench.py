@@ -143,7 +143,10 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-TRAFFIC_GEMMS = 1.808e10  # ncu --set full: 17.49 GB read + 0.59 GB written per launch of tc_bwd_rev_kernel<1> (profiles/r2_step_kernels_n1.txt)
+# ncu --set full, dram bytes read + written per launch of tc_bwd_rev_kernel<1>: 17.5 + 0.6 GB (profiles/r2_step_kernels_n1.txt)
+# and 28.4 + 0.6 GB (profiles/r2_step_kernels_n1_final.txt, a slower box: 7.6 ms at 1.21 GHz) -- the d chunks of an A tile
+# share it through L2 only while neighbouring clusters run in step; the larger figure is reported.  Floor: 12.9 GB.
+TRAFFIC_GEMMS = 2.902e10
 
 
 def synth_loss_rows(torch, n_global, row0, n_local, device, dtype):
